@@ -1,0 +1,153 @@
+/*
+ * lime_cuda.h -- the C ABI of lime-b200: LiME's classification hot path on one B200.
+ *
+ * The reference (veronicaguerrini/LiME) has no plugin / FFI interface: the path is three
+ * executables that talk through files, and inside each executable one OpenMP parallel
+ * region does the work.  This ABI puts a seam exactly at those regions, so a maintainer
+ * can replace the body of each region with one call (INTEGRATION.md shows the patch):
+ *
+ *   lime_cluster_detect   <->  ClusterLCP.cpp:139-283     (#pragma omp parallel scan of lcp/da)
+ *   lime_similarity       <->  ClusterBWT_DA.cpp:630-670  (clusterAnalyze, :256-358)
+ *   lime_choose           <->  ClusterBWT_DA.cpp:737      (clusterChoose, :361-450)
+ *   lime_classify         <->  Classify.cpp:474-702       (#pragma omp parallel for over reads)
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes; type widths are those of Tools.h (lime_types.h).
+ *   - every function returns 0 on success or a negative LIME_ERR_* code; the message is
+ *     available from lime_last_error(ctx).  Nothing throws across the boundary.
+ *   - one lime_ctx per process and GPU (one process per GPU); a ctx is not thread-safe.
+ *   - pointers are HOST pointers unless the parameter is documented as device memory or the
+ *     call takes a `mem` argument (LIME_MEM_HOST / LIME_MEM_DEVICE).
+ *   - there is no CPU fallback: without a CUDA device lime_init fails with LIME_ERR_CUDA.
+ */
+#ifndef LIME_CUDA_H_
+#define LIME_CUDA_H_
+
+#include <stdint.h>
+#include "lime_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LIME_OK            0
+#define LIME_ERR_ARG      -1   /* bad argument / precondition                                   */
+#define LIME_ERR_CUDA     -2   /* CUDA runtime error (message has the cudaError string)          */
+#define LIME_ERR_MAXLEN   -3   /* a cluster is longer than sizeMaxBuf (ClusterBWT_DA.cpp:558-562) */
+#define LIME_ERR_HALO     -4   /* a straddling cluster runs past the supplied halo               */
+#define LIME_ERR_STATE    -5   /* call order violated (e.g. similarity before cluster_detect)    */
+#define LIME_ERR_NOMEM    -6   /* device or host allocation failed                               */
+#define LIME_ERR_ROWS     -7   /* .res rows not strictly ascending in genome id                  */
+
+#define LIME_MEM_HOST      0
+#define LIME_MEM_DEVICE    1
+
+typedef struct lime_ctx lime_ctx;
+
+/* ---- context ------------------------------------------------------------------------------ */
+
+/* Create a context on CUDA device `device` (cudaSetDevice ordinal). */
+int  lime_init(lime_ctx **ctx, int device);
+void lime_destroy(lime_ctx *ctx);
+const char *lime_last_error(const lime_ctx *ctx);      /* ctx may be NULL: last init error */
+const char *lime_version(void);
+
+/* Launch all work of this ctx on an existing cudaStream_t (passed as void*), e.g. the caller's
+ * current stream so that its CUDA events bracket our kernels.  NULL restores the ctx's own stream. */
+int  lime_set_stream(lime_ctx *ctx, void *cuda_stream);
+
+/* ---- inputs ------------------------------------------------------------------------------- */
+
+/*
+ * Make one strand's arrays resident.  lcp/da have n_own + n_halo elements, ebwt likewise or NULL
+ * (EBWT=0 build, ClusterBWT_DA.cpp:16-18).  Element 0 is global position pos_base.
+ *   n_own    positions this GPU owns: a cluster belongs to the shard that holds the position
+ *            with lcp < alpha which opens it -- the thread-chunk rule of ClusterLCP.cpp:150-202;
+ *   n_halo   positions after the owned range that a straddling cluster may run into (:246-264);
+ *   is_last  non-zero if element n_own+n_halo-1 is the last position of the whole array (:244-245).
+ * Single GPU: n_halo = 0, pos_base = 0, is_last = 1.
+ * mem = LIME_MEM_HOST copies (pageable or pinned) host arrays to the device;
+ * mem = LIME_MEM_DEVICE borrows 16-byte aligned device pointers, which must stay valid.
+ * Loading resets the clusters and zeroes the similarity accumulator.
+ */
+int  lime_load(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint8_t *ebwt,
+               uint64_t n_own, uint64_t n_halo, uint64_t pos_base, int is_last,
+               uint32_t n_reads, uint32_t n_refs, int mem);
+
+/* ---- step 1 : ClusterLCP.cpp:139-283 ------------------------------------------------------ */
+
+/* Detect the alpha-clusters owned by this shard.  n_clusters / max_len are the shard's values of
+ * nClusters / maxLen (reduction(+) / reduction(max), ClusterLCP.cpp:140); clusters are kept on the
+ * device in ascending pStart order (the order of the reference run with threads = 1). */
+int  lime_cluster_detect(lime_ctx *ctx, uint32_t alpha, uint64_t *n_clusters, uint64_t *max_len);
+/* Copy the cluster records ({pStart,len}, global positions) to host memory, e.g. to write .clrs. */
+int  lime_clusters_copy(lime_ctx *ctx, lime_cluster *out, uint64_t cap);
+/* Replace the resident cluster list by caller-supplied records (step 2 started from a .clrs file,
+ * ClusterBWT_DA.cpp:641-654); any order.  pStart is a global position. */
+int  lime_clusters_set(lime_ctx *ctx, const lime_cluster *cl, uint64_t n_clusters, uint64_t max_len);
+
+/* ---- step 2 : ClusterBWT_DA.cpp:256-358, 361-450 ------------------------------------------ */
+
+/* Accumulate t(read, genome) of every resident cluster into the similarity matrix
+ * (SimArray_, ClusterBWT_DA.cpp:606-611).  ebwt_mode 1 = EBWT=1 scoring (:107-190), 0 = EBWT=0
+ * (:192-252).  Cells are exact modulo 256 (uint8 wrap, Tools.h:68).  May be called once per load. */
+int  lime_similarity(lime_ctx *ctx, int ebwt_mode);
+
+/* Bind caller-owned device memory as the accumulator: rows x pitch bytes, pitch a multiple of 16
+ * and >= n_refs, rows >= n_reads; one uint8 cell per (read, genome).  Must be called before
+ * lime_load; used by the multi-GPU host to reduce-scatter partial matrices (uint8 sum wraps like
+ * the reference's cell).  Pass NULL to return to the internal allocation. */
+int  lime_sim_bind(lime_ctx *ctx, void *dev_matrix, uint64_t rows, uint64_t pitch);
+/* Row pitch in bytes the ctx uses for n_refs genomes. */
+uint64_t lime_sim_pitch(uint32_t n_refs);
+/* Dense copy of the matrix, [n_reads][n_refs] uint8 (the SMALL=1 dump, ClusterBWT_DA.cpp:672-681). */
+int  lime_sim_copy(lime_ctx *ctx, uint8_t *out);
+
+/*
+ * clusterChoose for reads [read_begin, read_end): thresholds each row with beta and builds the
+ * images of <fasta>.res.bin / .res.pos for that read range in device memory, stored in strand
+ * slot `slot` (0..3 = mate1 F, mate1 RC, mate2 F, mate2 RC, the argv order of Classify).
+ * Record 0 is the sentinel; pos values index into this range's own record list.
+ * norm = readLen + 1 - alpha (ClusterBWT_DA.cpp:555).  n_records includes the sentinel.
+ */
+int  lime_choose(lime_ctx *ctx, int slot, uint32_t norm, float beta,
+                 uint32_t read_begin, uint32_t read_end, uint64_t *n_records);
+int  lime_choose_copy(lime_ctx *ctx, int slot, lime_pair_sim *bin, uint64_t *pos);
+/* Load a strand slot from host images of .res.bin / .res.pos (step 3 started from files). */
+int  lime_slot_set(lime_ctx *ctx, int slot, const lime_pair_sim *bin, uint64_t n_records,
+                   const uint64_t *pos, uint32_t n_reads_in_slot);
+
+/* ---- step 3 : Classify.cpp:474-702 -------------------------------------------------------- */
+
+/*
+ * Classify the reads of slots 0..n_files-1 (n_files = 2 or 4, Classify.cpp:334-338).
+ *   v_corRef  [n_refs]     genome -> taxid at tax_rank (FixRank, Classify.cpp:33-89)
+ *   m_corRef  [6][n_refs]  genome -> taxid per rank, or NULL      (HIGHER=1, :61-67)
+ *   higher    0/1          the HIGHER build variant (:262-302, 672-677)
+ * Outputs (host, one per read of the slot range): type 'C'/'U'/'A'/'H', taxid, sim
+ * (typeOutput, Tools.h:100-104; Assign, Classify.cpp:157-162).
+ */
+int  lime_classify(lime_ctx *ctx, int n_files, uint32_t n_refs,
+                   const uint32_t *v_corRef, const uint32_t *m_corRef, int tax_rank, int higher,
+                   uint8_t *out_type, uint32_t *out_tax, float *out_sim);
+
+/* ---- instrumentation ---------------------------------------------------------------------- */
+
+/* Kernels launched by this ctx since creation (bench.py's gpu_launches). */
+uint64_t lime_launch_count(const lime_ctx *ctx);
+/* When enabled, every kernel launch is bracketed by CUDA events on the ctx stream. */
+int  lime_prof_enable(lime_ctx *ctx, int on);
+/* Synchronise and report: for kernel family k (0..lime_prof_kernels()-1) its name, launch count
+ * and total device milliseconds since the last lime_prof_reset. */
+int  lime_prof_kernels(void);
+int  lime_prof_get(lime_ctx *ctx, int k, const char **name, uint64_t *launches, double *ms);
+int  lime_prof_reset(lime_ctx *ctx);
+/* Counters of the last lime_similarity call: [0] clusters taken by the warp path, [1] clusters
+ * taken by the block path, [2] (read,genome) updates issued, [3] 1 if the packed uint8 pass
+ * detected a carry and the exact 32-bit pass was run. */
+int  lime_sim_stats(lime_ctx *ctx, uint64_t out[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LIME_CUDA_H_ */

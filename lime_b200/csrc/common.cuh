@@ -1,0 +1,240 @@
+// common.cuh -- shared declarations of the lime-b200 CUDA translation units (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/lime_types.h"
+#include "../../include/lime_cuda.h"
+
+namespace lime {
+
+// ---------------------------------------------------------------------------------------------
+// small device helpers
+// ---------------------------------------------------------------------------------------------
+constexpr unsigned FULL = 0xffffffffu;
+
+__device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31u; }
+
+// 128-bit read-only streaming load (inputs are read once per kernel)
+__device__ __forceinline__ uint4 ldg128(const uint32_t *p)
+{
+    return __ldg(reinterpret_cast<const uint4 *>(p));
+}
+
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long *p)
+{
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long *p, unsigned long long v)
+{
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// ---- decoupled look-back over 64-bit tile descriptors ----------------------------------------
+// descriptor = status (top 2 bits) | value (low 62 bits); the array is zeroed (INVALID) before
+// the launch and tiles are numbered by an atomic ticket so every predecessor is already running.
+constexpr unsigned long long LB_AGG = 1ull << 62;      // tile aggregate published
+constexpr unsigned long long LB_PREFIX = 2ull << 62;   // inclusive prefix published
+constexpr unsigned long long LB_VALUE = (1ull << 62) - 1;
+
+// Called by all 32 lanes of one warp.  Returns the exclusive prefix of `agg` over tiles < tile.
+__device__ __forceinline__ unsigned long long lookback_exclusive(unsigned long long *state,
+                                                                 unsigned tile,
+                                                                 unsigned long long agg)
+{
+    const unsigned lane = lane_id();
+    if (tile == 0) {
+        if (lane == 0) st_relaxed_u64(&state[0], LB_PREFIX | agg);
+        return 0;
+    }
+    if (lane == 0) st_relaxed_u64(&state[tile], LB_AGG | agg);
+    unsigned long long excl = 0;
+    long long idx = (long long)tile - 1;
+    while (true) {
+        long long t = idx - lane;
+        unsigned long long d = LB_PREFIX;   // virtual tile before 0: prefix 0
+        if (t >= 0) {
+            d = ld_relaxed_u64(&state[t]);
+            while ((d >> 62) == 0) d = ld_relaxed_u64(&state[t]);
+        }
+        unsigned pm = __ballot_sync(FULL, (d >> 62) == 2);
+        int first = pm ? (__ffs(pm) - 1) : 32;
+        unsigned long long v = ((int)lane <= first) ? (d & LB_VALUE) : 0ull;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+        excl += v;
+        if (pm) break;
+        idx -= 32;
+    }
+    if (lane == 0) st_relaxed_u64(&state[tile], LB_PREFIX | ((excl + agg) & LB_VALUE));
+    return excl;
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e == cudaSuccess) cap = bytes;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+enum KernelId {
+    KID_K1_DETECT = 0,
+    KID_K2_WARP,
+    KID_K2_BLOCK,
+    KID_K2_NARROW,
+    KID_K3_COUNT,
+    KID_K3_EMIT,
+    KID_K3_CLASSIFY,
+    KID_COUNT
+};
+
+struct Slot {
+    DevBuf bin, pos;
+    uint64_t n_records = 0;
+    uint32_t read_begin = 0, n_reads = 0;
+    bool valid = false;
+};
+
+struct ProfEvent { int kid; cudaEvent_t a, b; };
+
+} // namespace lime
+
+struct lime_ctx {
+    int device = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    std::string err;
+
+    // resident strand
+    const uint32_t *d_lcp = nullptr, *d_da = nullptr;
+    const uint8_t *d_ebwt = nullptr;
+    lime::DevBuf in_lcp, in_da, in_ebwt;
+    uint64_t n_own = 0, n_halo = 0, pos_base = 0;
+    int is_last = 1;
+    uint32_t n_reads = 0, n_refs = 0;
+    bool loaded = false;
+
+    // clusters
+    lime::DevBuf clusters;          // lime_cluster[cl_cap]
+    uint64_t cl_cap = 0, n_clusters = 0, max_len = 0;
+    uint32_t alpha = 0;
+    bool have_clusters = false;
+
+    // step-1 scratch
+    lime::DevBuf tile_state;        // u64 per tile
+    lime::DevBuf scalars;           // small block of device scalars (see abi)
+
+    // similarity accumulator
+    lime::DevBuf sim_own;
+    uint8_t *d_sim = nullptr;       // [sim_rows][sim_pitch] uint8
+    uint64_t sim_rows = 0, sim_pitch = 0;
+    bool sim_bound = false, sim_done = false;
+    lime::DevBuf sim32;             // exact pass scratch
+    lime::DevBuf large_list;        // u64 cluster indices for the block path
+    lime::DevBuf k2_scratch;        // block-path hash tables
+    uint64_t sim_stats[4] = {0, 0, 0, 0};
+
+    // step-2/3 results
+    lime::Slot slots[LIME_MAXFILES];
+    lime::DevBuf row_counts;
+    lime::DevBuf cls_out;           // classify outputs
+    lime::DevBuf tax_tables;        // v_corRef + m_corRef on device
+
+    // instrumentation
+    uint64_t launches = 0;
+    bool prof_on = false;
+    std::vector<lime::ProfEvent> prof_events;
+    uint64_t prof_launches[lime::KID_COUNT] = {0};
+    double prof_ms[lime::KID_COUNT] = {0};
+};
+
+namespace lime {
+
+// launchers implemented in the kernel translation units; all asynchronous on ctx->stream
+struct K1Args {
+    const uint32_t *lcp, *da;
+    uint64_t n_own, n_total, pos_base;
+    int is_last;
+    uint32_t alpha, n_reads;
+    lime_cluster *out;
+    uint64_t out_cap;
+    unsigned long long *tile_state;
+    unsigned int *tile_counter;
+    unsigned long long *n_clusters;   // device scalars
+    unsigned long long *max_len;
+    unsigned int *err;                // bit0: halo exhausted
+};
+cudaError_t launch_k1(const K1Args &a, cudaStream_t s, unsigned *grid_out);
+uint64_t k1_num_tiles(uint64_t n_own);
+
+struct K2Args {
+    const lime_cluster *cl;
+    uint64_t n_cl;
+    const uint32_t *da;
+    const uint8_t *ebwt;              // null in DA-only mode
+    uint64_t pos_base;
+    uint32_t n_reads, n_refs;
+    // packed uint8 accumulator
+    uint8_t *sim8; uint64_t pitch8;
+    // exact 32-bit accumulator for reads [lo, hi)
+    uint32_t *sim32; uint32_t lo, hi;
+    unsigned int *carry;              // set to 1 when a packed add carried out of its byte
+    unsigned long long *large_count;  // block-path work list
+    unsigned long long *large_list;
+    unsigned long long *large_next;   // ticket for the block path
+    unsigned long long *n_updates;    // statistics
+    uint8_t *scratch; uint64_t scratch_per_cta;
+};
+cudaError_t launch_k2_warp(const K2Args &a, bool exact32, cudaStream_t s);
+cudaError_t launch_k2_block(const K2Args &a, bool exact32, cudaStream_t s, int grid);
+uint64_t k2_block_scratch_bytes();
+int k2_block_grid();
+cudaError_t launch_k2_narrow(const uint32_t *sim32, uint32_t lo, uint32_t hi, uint32_t n_refs,
+                             uint8_t *sim8, uint64_t pitch8, cudaStream_t s);
+
+struct K3Args {
+    const uint8_t *sim8; uint64_t pitch8;
+    uint32_t n_refs, read_begin, read_end;
+    uint32_t norm; float beta;
+    unsigned long long *tile_state;
+    unsigned int *tile_counter;
+    unsigned long long *n_records;    // device scalar: records incl. sentinel
+    uint64_t *pos;                    // [read_end-read_begin]
+    lime_pair_sim *bin;               // emit only
+};
+cudaError_t launch_k3_count(const K3Args &a, cudaStream_t s);
+cudaError_t launch_k3_emit(const K3Args &a, cudaStream_t s);
+uint64_t k3_num_tiles(uint32_t n_reads);
+
+struct ClsArgs {
+    int n_files;
+    const lime_pair_sim *bin[LIME_MAXFILES];
+    const uint64_t *pos[LIME_MAXFILES];
+    uint64_t n_records[LIME_MAXFILES];
+    uint32_t n_reads, n_refs;
+    const uint32_t *v;                // [n_refs]
+    const uint32_t *m;                // [6][n_refs] or null
+    int tax_rank, higher;
+    // all-genome summaries for the "every genome is near the maximum" corner of Exam_2
+    uint32_t all_v_same, all_v_tax;
+    uint32_t all_m_same[LIME_RANKS], all_m_tax[LIME_RANKS];
+    uint8_t *out_type; uint32_t *out_tax; float *out_sim;
+    unsigned int *err;                // bit0: row not strictly ascending / out of range
+};
+cudaError_t launch_classify(const ClsArgs &a, cudaStream_t s);
+
+} // namespace lime

@@ -1,0 +1,393 @@
+// k2_similarity.cu -- step 2a, per-cluster read x genome similarity accumulation
+// (replaces clusterAnalyze, ClusterBWT_DA.cpp:256-358, with Update_ref_symb :81-105 and
+// Analysis_and_updating :107-190 (EBWT=1) / :192-252 (EBWT=0)).
+//
+// For every cluster, positions are grouped by document id; a read r gets per-class symbol counts
+// R[16] (uint8, wrapping, :123), a genome g gets G[16] (uint8, saturating at 255, :96-97); every
+// (r, g) present in the cluster adds t(R, G) to SimArray_[r][g] (uint8, wrapping, :183).  The
+// reference sorts each cluster to group equal ids (:316-322); only the grouping matters, so here
+//   * clusters of <= 32 positions (the bulk) are packed several per warp, one lane per position,
+//     and grouped with __match_any_sync on (cluster, id); class counts come from ballots + popc;
+//   * longer clusters (up to sizeMaxBuf = 65536) take one CTA each and are grouped with a hash
+//     table in an L2-resident scratch area.
+// EBWT=0 is the same computation with every symbol in class 0 (t = min(#r, #g)).
+//
+// The accumulator is a dense [n_reads][pitch] matrix of uint8 cells updated with 32-bit atomics
+// on the containing word.  An add that carries out of its byte would corrupt the neighbour, so
+// every add inspects the returned old word and raises a flag; the host then reruns the pass into
+// exact 32-bit cells (reduced mod 256 afterwards), which is the reference's wrap semantics.
+#include "common.cuh"
+
+namespace lime {
+namespace k2 {
+
+// symbol -> class, ClusterBWT_DA.cpp:455-470; every unlisted byte is class 0 (operator[] default)
+__constant__ uint8_t c_class[256];
+
+// ---- scoring -----------------------------------------------------------------------------------
+// count vectors are 16 uint8 packed little-endian into a uint4 (class c = byte c&3 of word c>>2)
+
+// no IUPAC class (4..14) present on either side: t = sum_c min(R[c], G[c])  (:133-144)
+__device__ __forceinline__ uint32_t score_plain(const uint4 &R, const uint4 &G)
+{
+    return __vsadu4(__vminu4(R.x, G.x), 0u) + __vsadu4(__vminu4(R.y, G.y), 0u) +
+           __vsadu4(__vminu4(R.z, G.z), 0u) + __vsadu4(__vminu4(R.w, G.w), 0u);
+}
+
+__device__ __forceinline__ uint32_t byte_of(const uint4 &v, int c)
+{
+    const uint32_t w = (c >> 2) == 0 ? v.x : (c >> 2) == 1 ? v.y : (c >> 2) == 2 ? v.z : v.w;
+    return (w >> ((c & 3) * 8)) & 0xffu;
+}
+
+// class a (4..14) compatible with base i (0..3), ClusterBWT_DA.cpp:472-487, as bit i of entry a
+__device__ __forceinline__ constexpr unsigned compat_bits(int a)
+{
+    return a == 4 ? 0x5u : a == 5 ? 0xau : a == 6 ? 0x6u : a == 7 ? 0x9u : a == 8 ? 0xcu :
+           a == 9 ? 0x3u : a == 10 ? 0xeu : a == 11 ? 0xdu : a == 12 ? 0xbu : a == 13 ? 0x7u :
+           a == 14 ? 0xfu : 0u;
+}
+
+// full matcher incl. the IUPAC cross loop (:146-177).  In the "genome IUPAC vs read base" branch
+// the reference zeroes one operand before subtracting it from the other (:153-154, :158-159), so
+// the other operand keeps its value; t wraps as uint8 (:131), taken mod 256 by the caller.
+__device__ uint32_t score_iupac(const uint4 &R, const uint4 &G)
+{
+    uint32_t rr[16], gg[16], t = 0;
+#pragma unroll
+    for (int c = 0; c < 16; c++) {
+        const uint32_t r = byte_of(R, c), g = byte_of(G, c);
+        if (r > g) { t += g; rr[c] = r - g; gg[c] = 0; }
+        else       { t += r; gg[c] = g - r; rr[c] = 0; }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+#pragma unroll
+        for (int a = 4; a < 15; a++) {
+            if (!((compat_bits(a) >> i) & 1u)) continue;
+            if (gg[a] > 0) {
+                if (gg[a] > rr[i]) { t += rr[i]; rr[i] = 0; }
+                else               { t += gg[a]; gg[a] = 0; }
+            }
+            if (rr[a] > 0) {
+                if (rr[a] > gg[i]) { t += gg[i]; rr[a] -= gg[i]; gg[i] = 0; }
+                else               { t += rr[a]; gg[i] -= rr[a]; rr[a] = 0; }
+            }
+        }
+    }
+    return t;
+}
+
+// ---- accumulator update ----------------------------------------------------------------------
+template <bool EXACT32>
+__device__ __forceinline__ void sim_add(const K2Args &P, uint32_t r, uint32_t g, uint32_t t)
+{
+    if (EXACT32) {
+        if (r >= P.lo && r < P.hi) atomicAdd(&P.sim32[(size_t)(r - P.lo) * P.n_refs + g], t);
+    } else {
+        unsigned *w = reinterpret_cast<unsigned *>(P.sim8 + (size_t)r * P.pitch8) + (g >> 2);
+        const unsigned sh = (g & 3u) * 8u;
+        const unsigned old = atomicAdd(w, t << sh);
+        if (((old >> sh) & 0xffu) + t > 0xffu) *P.carry = 1u;
+    }
+}
+
+// ---- warp path: clusters of <= 32 positions ---------------------------------------------------
+constexpr int WARP_THREADS = 256;
+constexpr int WARPS = WARP_THREADS / 32;
+
+template <bool EBWT, bool EXACT32>
+__global__ void __launch_bounds__(WARP_THREADS) warp_kernel(K2Args P)
+{
+    __shared__ uint8_t s_owner[WARPS][32];
+    const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
+    const uint64_t n_chunks = (P.n_cl + 31) / 32;
+    const uint64_t warp_global = (uint64_t)blockIdx.x * WARPS + warp;
+    const uint64_t warp_stride = (uint64_t)gridDim.x * WARPS;
+    unsigned long long updates = 0;
+
+    for (uint64_t chunk = warp_global; chunk < n_chunks; chunk += warp_stride) {
+        // one cluster descriptor per lane
+        const uint64_t ci = chunk * 32 + lane;
+        uint64_t lstart = 0;
+        uint32_t len = 0;
+        if (ci < P.n_cl) {
+            const ulonglong2 c = *reinterpret_cast<const ulonglong2 *>(&P.cl[ci]);
+            lstart = c.x - P.pos_base;
+            len = c.y > 0xffffffffull ? 0xffffffffu : (uint32_t)c.y;
+        }
+        const bool large = len > 32;
+        {   // hand long clusters to the block path
+            const unsigned lm = __ballot_sync(FULL, large);
+            if (lm) {
+                unsigned long long b = 0;
+                if (lane == 0) b = atomicAdd(P.large_count, (unsigned long long)__popc(lm));
+                b = __shfl_sync(FULL, b, 0);
+                if (large) P.large_list[b + __popc(lm & ((1u << lane) - 1u))] = ci;
+            }
+        }
+        const uint32_t eff = large ? 0u : len;
+        uint32_t incl = eff;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t n = __shfl_up_sync(FULL, incl, o);
+            if (lane >= (unsigned)o) incl += n;
+        }
+        const uint32_t excl = incl - eff;
+
+        // rounds: greedily take the next clusters whose positions fit in 32 lanes
+        int k0 = 0;
+        uint32_t done = 0;
+        while (k0 < 32) {
+            const unsigned fit = __ballot_sync(FULL, (int)lane >= k0 && incl - done <= 32u);
+            const int k1 = k0 + __popc(fit);               // fit is a contiguous run starting at k0
+            const uint32_t total = __shfl_sync(FULL, incl, k1 - 1) - done;
+            if (total > 0) {
+                const bool in_round = (int)lane >= k0 && (int)lane < k1 && eff > 0;
+                const uint32_t rel = excl - done;           // first lane slot of my cluster
+                const unsigned startmask = __reduce_or_sync(FULL, in_round ? (1u << rel) : 0u);
+                if (in_round) s_owner[warp][rel] = (uint8_t)lane;
+                __syncwarp();
+                const bool act = lane < total;
+                const unsigned below = startmask & (0xffffffffu >> (31 - lane));
+                const int st = act ? 31 - __clz(below) : 0;
+                const int own = act ? s_owner[warp][st] : 0;
+                __syncwarp();
+                const uint64_t cstart = __shfl_sync(FULL, lstart, own);
+                const uint32_t clen = __shfl_sync(FULL, eff, own);
+
+                uint32_t id = 0, cls = 0;
+                if (act) {
+                    const uint64_t p = cstart + (lane - st);
+                    id = __ldg(P.da + p);
+                    if (EBWT) cls = c_class[__ldg(P.ebwt + p)];
+                }
+                const bool is_read = id < P.n_reads;
+                const unsigned long long key =
+                    act ? (((unsigned long long)own << 32) | id) : ((0xffull << 40) | lane);
+                const unsigned mm = __match_any_sync(FULL, key);   // lanes with my (cluster, id)
+                const bool leader = act && (__ffs(mm) - 1 == (int)lane);
+
+                // per-class counts of my id: popc(my group & lanes of that class)
+                uint4 vec = make_uint4(0, 0, 0, 0);
+                unsigned present = __reduce_or_sync(FULL, act ? (1u << cls) : 0u);
+                const bool iupac = (present & 0x7ff0u) != 0;
+                while (present) {
+                    const int c = __ffs(present) - 1;
+                    present &= present - 1;
+                    const unsigned b = __ballot_sync(FULL, act && cls == (uint32_t)c);
+                    const unsigned v = (unsigned)__popc(mm & b) << ((c & 3) * 8);
+                    if ((c >> 2) == 0) vec.x |= v; else if ((c >> 2) == 1) vec.y |= v;
+                    else if ((c >> 2) == 2) vec.z |= v; else vec.w |= v;
+                }
+
+                // every read leader against every genome leader of its cluster
+                const unsigned cm = (clen >= 32 ? 0xffffffffu : ((1u << clen) - 1u)) << st;
+                unsigned gl = __ballot_sync(FULL, leader && !is_read) & cm;
+                if (!(leader && is_read)) gl = 0;
+                while (__any_sync(FULL, gl != 0)) {
+                    const int src = gl ? __ffs(gl) - 1 : 0;
+                    uint4 G;
+                    G.x = __shfl_sync(FULL, vec.x, src); G.y = __shfl_sync(FULL, vec.y, src);
+                    G.z = __shfl_sync(FULL, vec.z, src); G.w = __shfl_sync(FULL, vec.w, src);
+                    const uint32_t gid = __shfl_sync(FULL, id, src);
+                    if (gl) {
+                        const uint32_t t = (iupac ? score_iupac(vec, G) : score_plain(vec, G)) & 0xffu;
+                        if (t) { sim_add<EXACT32>(P, id, gid - P.n_reads, t); updates++; }
+                        gl &= gl - 1;
+                    }
+                }
+            }
+            done += total;
+            k0 = k1;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) updates += __shfl_xor_sync(FULL, updates, o);
+    if (lane == 0 && updates) atomicAdd(P.n_updates, updates);
+}
+
+// ---- block path: clusters of 33 .. 65536 positions ---------------------------------------------
+constexpr int BLOCK_THREADS = 256;
+constexpr uint32_t HCAP = 2 * LIME_SIZE_MAX_BUF;     // slots per CTA table
+constexpr uint32_t EMPTY = 0xffffffffu;
+// per-CTA scratch layout: keys[HCAP] u32 | cnt[HCAP][8] u32 (16 x u16, later 16 x u8 in cnt[.][0..3])
+//                         | rlist[65536] u32 | glist[65536] u32
+constexpr uint64_t SCRATCH_BYTES =
+    (uint64_t)HCAP * 4 + (uint64_t)HCAP * 32 + 2ull * LIME_SIZE_MAX_BUF * 4;
+
+__device__ __forceinline__ uint32_t hash32(uint32_t x)
+{
+    x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+    return x;
+}
+
+template <bool EBWT, bool EXACT32>
+__global__ void __launch_bounds__(BLOCK_THREADS) block_kernel(K2Args P)
+{
+    __shared__ unsigned long long s_item;
+    __shared__ unsigned s_nr, s_ng, s_iupac;
+    uint8_t *my = P.scratch + (size_t)blockIdx.x * P.scratch_per_cta;
+    uint32_t *keys = reinterpret_cast<uint32_t *>(my);
+    uint32_t *cnt = keys + HCAP;                       // [HCAP][8]
+    uint32_t *rlist = cnt + (size_t)HCAP * 8;
+    uint32_t *glist = rlist + LIME_SIZE_MAX_BUF;
+    const int tid = threadIdx.x;
+    const unsigned lane = lane_id(), warp = tid >> 5;
+    const unsigned long long n_large = *P.large_count;
+    unsigned long long updates = 0;
+
+    while (true) {
+        if (tid == 0) { s_item = atomicAdd(P.large_next, 1ull); s_nr = 0; s_ng = 0; s_iupac = 0; }
+        __syncthreads();
+        const unsigned long long item = s_item;
+        if (item >= n_large) break;
+        const lime_cluster c = P.cl[P.large_list[item]];
+        const uint64_t start = c.pStart - P.pos_base;
+        const uint32_t len = (uint32_t)c.len;          // <= 65536, checked by the host
+        uint32_t cap = 64;
+        while (cap < 2 * len) cap <<= 1;
+        const uint32_t mask = cap - 1;
+
+        for (uint32_t h = tid; h < cap; h += BLOCK_THREADS) keys[h] = EMPTY;
+        {
+            uint4 *z = reinterpret_cast<uint4 *>(cnt);
+            for (uint32_t h = tid; h < cap * 2; h += BLOCK_THREADS) z[h] = make_uint4(0, 0, 0, 0);
+        }
+        __syncthreads();
+
+        // group by id: per-(id, class) counts as 16 x u16
+        for (uint32_t e = tid; e < len; e += BLOCK_THREADS) {
+            const uint32_t id = __ldg(P.da + start + e);
+            const uint32_t cls = EBWT ? c_class[__ldg(P.ebwt + start + e)] : 0u;
+            uint32_t h = hash32(id) & mask;
+            while (true) {
+                uint32_t k = __ldcg(&keys[h]);
+                if (k == EMPTY) {
+                    k = atomicCAS(&keys[h], EMPTY, id);
+                    if (k == EMPTY) break;          // slot claimed for id
+                }
+                if (k == id) break;
+                h = (h + 1) & mask;
+            }
+            atomicAdd(&cnt[(size_t)h * 8 + (cls >> 1)], 1u << ((cls & 1) * 16));
+            if (cls >= 4 && cls <= 14) s_iupac = 1;
+        }
+        __syncthreads();
+
+        // list reads / genomes; fold counts to uint8: reads wrap (:123), genomes saturate (:96-97)
+        for (uint32_t h = tid; h < cap; h += BLOCK_THREADS) {
+            const uint32_t id = __ldcg(&keys[h]);   // L2: the slot was written by an atomic
+            if (id == EMPTY) continue;
+            const bool is_read = id < P.n_reads;
+            uint32_t out[4];
+#pragma unroll
+            for (int w = 0; w < 4; w++) {
+                uint32_t packed = 0;
+#pragma unroll
+                for (int b = 0; b < 4; b++) {
+                    const int cl = w * 4 + b;
+                    uint32_t v = (__ldcg(&cnt[(size_t)h * 8 + (cl >> 1)]) >> ((cl & 1) * 16)) & 0xffffu;
+                    v = is_read ? (v & 0xffu) : min(v, 255u);
+                    packed |= v << (b * 8);
+                }
+                out[w] = packed;
+            }
+            *reinterpret_cast<uint4 *>(&cnt[(size_t)h * 8]) = make_uint4(out[0], out[1], out[2], out[3]);
+            if (is_read) rlist[atomicAdd(&s_nr, 1u)] = h;
+            else         glist[atomicAdd(&s_ng, 1u)] = h;
+        }
+        __syncthreads();
+
+        // reads x genomes: a warp per read, lanes over genomes
+        const uint32_t nr = s_nr, ng = s_ng;
+        const bool iupac = s_iupac != 0;
+        for (uint32_t ri = warp; ri < nr; ri += BLOCK_THREADS / 32) {
+            const uint32_t hr = __ldcg(&rlist[ri]);
+            const uint32_t r = __ldcg(&keys[hr]);
+            const uint4 R = __ldcg(reinterpret_cast<const uint4 *>(&cnt[(size_t)hr * 8]));
+            for (uint32_t gi = lane; gi < ng; gi += 32) {
+                const uint32_t hg = __ldcg(&glist[gi]);
+                const uint4 G = __ldcg(reinterpret_cast<const uint4 *>(&cnt[(size_t)hg * 8]));
+                const uint32_t t = (iupac ? score_iupac(R, G) : score_plain(R, G)) & 0xffu;
+                if (t) { sim_add<EXACT32>(P, r, __ldcg(&keys[hg]) - P.n_reads, t); updates++; }
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) updates += __shfl_xor_sync(FULL, updates, o);
+    if (lane == 0 && updates) atomicAdd(P.n_updates, updates);
+}
+
+// ---- exact pass epilogue: 32-bit cells -> uint8 cells (mod 256) ---------------------------------
+__global__ void narrow_kernel(const uint32_t *sim32, uint32_t lo, uint32_t hi, uint32_t n_refs,
+                              uint8_t *sim8, uint64_t pitch8)
+{
+    const uint64_t total = (uint64_t)(hi - lo) * n_refs;
+    for (uint64_t x = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; x < total;
+         x += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t r = (uint32_t)(x / n_refs), g = (uint32_t)(x - (uint64_t)r * n_refs);
+        sim8[(size_t)(lo + r) * pitch8 + g] = (uint8_t)(sim32[x] & 0xffu);
+    }
+}
+
+static bool g_class_uploaded[64] = {false};
+
+static cudaError_t upload_class_table()
+{
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && g_class_uploaded[dev]) return cudaSuccess;
+    uint8_t t[256];
+    for (int i = 0; i < 256; i++) t[i] = 0;
+    const char *sym = "ACGTRYSWKMBDHVN";
+    for (int c = 0; c < 15; c++) t[(uint8_t)sym[c]] = (uint8_t)c;
+    t[0] = 15;
+    cudaError_t e = cudaMemcpyToSymbol(c_class, t, 256);
+    if (e == cudaSuccess && dev >= 0 && dev < 64) g_class_uploaded[dev] = true;
+    return e;
+}
+
+} // namespace k2
+
+uint64_t k2_block_scratch_bytes() { return k2::SCRATCH_BYTES; }
+int k2_block_grid() { return 148 * 2; }
+
+cudaError_t launch_k2_warp(const K2Args &a, bool exact32, cudaStream_t s)
+{
+    cudaError_t e = k2::upload_class_table();
+    if (e != cudaSuccess) return e;
+    if (a.n_cl == 0) return cudaSuccess;
+    const uint64_t chunks = (a.n_cl + 31) / 32;
+    const uint64_t want = (chunks + k2::WARPS - 1) / k2::WARPS;
+    const unsigned grid = (unsigned)(want < 148ull * 8 * 4 ? want : 148ull * 8 * 4);
+    const bool ebwt = a.ebwt != nullptr;
+    if (ebwt && !exact32)       k2::warp_kernel<true, false><<<grid, k2::WARP_THREADS, 0, s>>>(a);
+    else if (ebwt && exact32)   k2::warp_kernel<true, true><<<grid, k2::WARP_THREADS, 0, s>>>(a);
+    else if (!ebwt && !exact32) k2::warp_kernel<false, false><<<grid, k2::WARP_THREADS, 0, s>>>(a);
+    else                        k2::warp_kernel<false, true><<<grid, k2::WARP_THREADS, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_k2_block(const K2Args &a, bool exact32, cudaStream_t s, int grid)
+{
+    cudaError_t e = k2::upload_class_table();
+    if (e != cudaSuccess) return e;
+    const bool ebwt = a.ebwt != nullptr;
+    if (ebwt && !exact32)       k2::block_kernel<true, false><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);
+    else if (ebwt && exact32)   k2::block_kernel<true, true><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);
+    else if (!ebwt && !exact32) k2::block_kernel<false, false><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);
+    else                        k2::block_kernel<false, true><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_k2_narrow(const uint32_t *sim32, uint32_t lo, uint32_t hi, uint32_t n_refs,
+                             uint8_t *sim8, uint64_t pitch8, cudaStream_t s)
+{
+    if (hi <= lo || n_refs == 0) return cudaSuccess;
+    k2::narrow_kernel<<<148 * 8, 256, 0, s>>>(sim32, lo, hi, n_refs, sim8, pitch8);
+    return cudaGetLastError();
+}
+
+} // namespace lime

@@ -1,0 +1,173 @@
+// k3_choose.cu -- step 2b, per-read threshold and sparse-row emit
+// (replaces clusterChoose, ClusterBWT_DA.cpp:361-450, BIN=1).
+//
+// Row r of the uint8 similarity matrix -> maxSim and the non-zero cells (:390-402);
+// normSim = (float)maxSim / norm (:404); if normSim > beta the row is written to .res.bin as a
+// header {normSim, count} followed by count x {(float)sim / norm, genome} in ascending genome
+// order (:408-426) and .res.pos[r] is the record index of the header, else 0 (:428-434).
+// Record 0 is the {0.0f, 0} sentinel (:376-382).
+//
+// count_kernel : a warp per row (coalesced word loads, __vmaxu4 / byte-nonzero popc), a block
+//                scan over 256 reads and a decoupled look-back over tiles give every passing
+//                read its record offset in one pass over the matrix; writes pos[].
+// emit_kernel  : re-reads the rows (L2 resident for typical sizes) and writes the records.
+#include "common.cuh"
+
+namespace lime {
+namespace k3 {
+
+constexpr int THREADS = 256;
+constexpr int WARPS = THREADS / 32;
+constexpr int TILE_READS = 256;               // reads per CTA
+constexpr int ROWS_PER_WARP = TILE_READS / WARPS;
+
+// per-byte "non-zero" mask: 0x01 in every byte of w that is non-zero
+__device__ __forceinline__ uint32_t nz_bytes(uint32_t w)
+{
+    return __vcmpne4(w, 0u) & 0x01010101u;
+}
+
+__global__ void __launch_bounds__(THREADS) count_kernel(K3Args P)
+{
+    __shared__ uint32_t s_cnt[TILE_READS];
+    __shared__ uint32_t s_warp_sum[WARPS];
+    __shared__ unsigned s_tile;
+    __shared__ unsigned long long s_excl;
+    const int tid = threadIdx.x;
+    const unsigned lane = lane_id(), warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(P.tile_counter, 1u);
+    __syncthreads();
+    const unsigned tile = s_tile;
+    const uint32_t n = P.read_end - P.read_begin;
+    const uint32_t r0 = tile * TILE_READS;
+    const uint32_t words = (P.n_refs + 3) / 4;
+    const float normf = (float)P.norm;
+
+    for (int k = 0; k < ROWS_PER_WARP; k++) {
+        const uint32_t lr = r0 + warp * ROWS_PER_WARP + k;
+        uint32_t mx = 0, nnz = 0;
+        if (lr < n) {
+            const uint32_t *row = reinterpret_cast<const uint32_t *>(
+                P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8);
+            for (uint32_t w = lane; w < words; w += 32) {
+                const uint32_t v = __ldg(row + w);
+                mx = __vmaxu4(mx, v);
+                nnz += __popc(nz_bytes(v));
+            }
+        }
+        mx = max(max(mx & 0xff, (mx >> 8) & 0xff), max((mx >> 16) & 0xff, mx >> 24));
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mx = max(mx, __shfl_xor_sync(FULL, mx, o));
+            nnz += __shfl_xor_sync(FULL, nnz, o);
+        }
+        if (lane == 0) {
+            const float ns = __fdiv_rn((float)mx, normf);
+            s_cnt[warp * ROWS_PER_WARP + k] = (lr < n && ns > P.beta) ? 1u + nnz : 0u;
+        }
+    }
+    __syncthreads();
+    // block exclusive scan over the 256 per-read record counts
+    const uint32_t c = s_cnt[tid];
+    uint32_t incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(FULL, incl, o);
+        if (lane >= (unsigned)o) incl += v;
+    }
+    if (lane == 31) s_warp_sum[warp] = incl;
+    __syncthreads();
+    uint32_t warp_off = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < WARPS; w++) {
+        const uint32_t s = s_warp_sum[w];
+        if (w < (int)warp) warp_off += s;
+        total += s;
+    }
+    if (warp == 0) {
+        const unsigned long long e = lookback_exclusive(P.tile_state, tile, total);
+        if (lane == 0) {
+            s_excl = e;
+            if (tile == gridDim.x - 1) *P.n_records = 1ull + e + total;
+        }
+    }
+    __syncthreads();
+    const uint32_t lr = r0 + tid;
+    if (lr < n) P.pos[lr] = c ? 1ull + s_excl + warp_off + (incl - c) : 0ull;
+}
+
+__global__ void __launch_bounds__(THREADS) emit_kernel(K3Args P)
+{
+    const unsigned lane = lane_id();
+    const uint32_t n = P.read_end - P.read_begin;
+    const uint64_t warp_global = ((uint64_t)blockIdx.x * THREADS + threadIdx.x) >> 5;
+    const uint64_t warp_stride = ((uint64_t)gridDim.x * THREADS) >> 5;
+    const uint32_t words = (P.n_refs + 3) / 4;
+    const float normf = (float)P.norm;
+    if (warp_global == 0 && lane == 0) { P.bin[0].sim = 0.0f; P.bin[0].idRef = 0; }
+
+    for (uint64_t lr = warp_global; lr < n; lr += warp_stride) {
+        const uint64_t o = P.pos[lr];
+        if (o == 0) continue;
+        const uint32_t *row = reinterpret_cast<const uint32_t *>(
+            P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8);
+        uint32_t mx = 0, written = 0;
+        for (uint32_t w0 = 0; w0 < words; w0 += 32) {
+            const uint32_t w = w0 + lane;
+            const uint32_t v = w < words ? __ldg(row + w) : 0u;
+            mx = __vmaxu4(mx, v);
+            const uint32_t cnt = __popc(nz_bytes(v));
+            uint32_t incl = cnt;
+#pragma unroll
+            for (int s = 1; s < 32; s <<= 1) {
+                const uint32_t x = __shfl_up_sync(FULL, incl, s);
+                if (lane >= (unsigned)s) incl += x;
+            }
+            uint64_t dst = o + 1 + written + (incl - cnt);
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                const uint32_t cell = (v >> (8 * b)) & 0xffu;
+                if (cell) {
+                    lime_pair_sim rec;
+                    rec.sim = __fdiv_rn((float)cell, normf);
+                    rec.idRef = 4 * w + b;
+                    P.bin[dst++] = rec;
+                }
+            }
+            written += __shfl_sync(FULL, incl, 31);
+        }
+        mx = max(max(mx & 0xff, (mx >> 8) & 0xff), max((mx >> 16) & 0xff, mx >> 24));
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) mx = max(mx, __shfl_xor_sync(FULL, mx, s));
+        if (lane == 0) {
+            lime_pair_sim h;
+            h.sim = __fdiv_rn((float)mx, normf);
+            h.idRef = written;
+            P.bin[o] = h;
+        }
+    }
+}
+
+} // namespace k3
+
+uint64_t k3_num_tiles(uint32_t n_reads) { return ((uint64_t)n_reads + k3::TILE_READS - 1) / k3::TILE_READS; }
+
+cudaError_t launch_k3_count(const K3Args &a, cudaStream_t s)
+{
+    const uint64_t tiles = k3_num_tiles(a.read_end - a.read_begin);
+    if (tiles == 0) return cudaSuccess;
+    k3::count_kernel<<<(unsigned)tiles, k3::THREADS, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_k3_emit(const K3Args &a, cudaStream_t s)
+{
+    const uint32_t n = a.read_end - a.read_begin;
+    uint64_t want = ((uint64_t)n + k3::WARPS - 1) / k3::WARPS;
+    if (want == 0) want = 1;                       // still writes the sentinel
+    const unsigned grid = (unsigned)(want < 148ull * 16 ? want : 148ull * 16);
+    k3::emit_kernel<<<grid, k3::THREADS, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+} // namespace lime

@@ -1,0 +1,169 @@
+// lime_abi_steps.cu -- ABI entry points for step 2 (similarity, choose) and instrumentation.
+#include "abi_internal.cuh"
+#include <algorithm>
+#include <vector>
+
+static int run_k2_pass(lime_ctx *ctx, bool ebwt, bool exact32, uint32_t lo, uint32_t hi)
+{
+    K2Args a;
+    a.cl = ctx->clusters.as<lime_cluster>(); a.n_cl = ctx->n_clusters;
+    a.da = ctx->d_da; a.ebwt = ebwt ? ctx->d_ebwt : nullptr;
+    a.pos_base = ctx->pos_base; a.n_reads = ctx->n_reads; a.n_refs = ctx->n_refs;
+    a.sim8 = ctx->d_sim; a.pitch8 = ctx->sim_pitch;
+    a.sim32 = ctx->sim32.as<uint32_t>(); a.lo = lo; a.hi = hi;
+    a.carry = scalar<unsigned int>(ctx, SC_CARRY);
+    a.large_count = scalar<unsigned long long>(ctx, SC_LARGE_COUNT);
+    a.large_next = scalar<unsigned long long>(ctx, SC_LARGE_NEXT);
+    a.n_updates = scalar<unsigned long long>(ctx, SC_NUPDATES);
+    a.large_list = ctx->large_list.as<unsigned long long>();
+    a.scratch = ctx->k2_scratch.as<uint8_t>(); a.scratch_per_cta = k2_block_scratch_bytes();
+    CK(cudaMemsetAsync(ctx->scalars.p, 0, sizeof(unsigned long long) * SC_COUNT, ctx->stream), "memset scalars");
+    {
+        LaunchScope ls(ctx, KID_K2_WARP);
+        CK(launch_k2_warp(a, exact32, ctx->stream), "k2_warp launch");
+    }
+    {
+        LaunchScope ls(ctx, KID_K2_BLOCK);
+        CK(launch_k2_block(a, exact32, ctx->stream, k2_block_grid()), "k2_block launch");
+    }
+    return LIME_OK;
+}
+
+extern "C" {
+
+int lime_similarity(lime_ctx *ctx, int ebwt_mode)
+{
+    if (!ctx) return LIME_ERR_ARG;
+    if (!ctx->loaded || !ctx->have_clusters) return fail(ctx, LIME_ERR_STATE, "lime_similarity: load and detect/set clusters first");
+    if (ctx->sim_done) return fail(ctx, LIME_ERR_STATE, "lime_similarity: already accumulated for this load");
+    if (ebwt_mode && !ctx->d_ebwt) return fail(ctx, LIME_ERR_ARG, "lime_similarity: EBWT mode needs the ebwt array");
+    if (ctx->max_len > LIME_SIZE_MAX_BUF)                        // ClusterBWT_DA.cpp:558-562
+        return fail(ctx, LIME_ERR_MAXLEN, "maximum cluster size is greater than sizeMaxBuf");
+    CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+    for (int i = 0; i < 4; i++) ctx->sim_stats[i] = 0;
+    ctx->sim_done = true;
+    if (ctx->n_clusters == 0 || ctx->n_reads == 0 || ctx->n_refs == 0) return LIME_OK;
+    CK(ctx->large_list.reserve(ctx->n_clusters * 8), "cudaMalloc block-path list");
+    CK(ctx->k2_scratch.reserve(k2_block_scratch_bytes() * (uint64_t)k2_block_grid()), "cudaMalloc block-path scratch");
+
+    int rc = run_k2_pass(ctx, ebwt_mode != 0, false, 0, 0);
+    if (rc) return rc;
+    unsigned long long sc[SC_COUNT];
+    CK(cudaMemcpyAsync(sc, ctx->scalars.p, sizeof(sc), cudaMemcpyDeviceToHost, ctx->stream), "D2H scalars");
+    CK(cudaStreamSynchronize(ctx->stream), "k2 similarity");
+    ctx->sim_stats[1] = sc[SC_LARGE_COUNT];
+    ctx->sim_stats[0] = ctx->n_clusters - sc[SC_LARGE_COUNT];
+    ctx->sim_stats[2] = sc[SC_NUPDATES];
+    if (((unsigned)sc[SC_CARRY]) == 0) return LIME_OK;
+
+    // A packed add carried out of its byte: some cell's true sum exceeds 255.  Redo the pass into
+    // exact 32-bit cells, a bounded band of reads at a time, and store the sums mod 256
+    // (uint8 wrap of SimArray_, ClusterBWT_DA.cpp:183,247; Tools.h:68).
+    ctx->sim_stats[3] = 1;
+    const uint64_t budget = 8ull << 30;
+    uint64_t band = std::max<uint64_t>(1, budget / ((uint64_t)ctx->n_refs * 4));
+    band = std::min<uint64_t>(band, ctx->n_reads);
+    CK(ctx->sim32.reserve(band * ctx->n_refs * 4), "cudaMalloc exact accumulator");
+    for (uint64_t lo = 0; lo < ctx->n_reads; lo += band) {
+        const uint64_t hi = std::min<uint64_t>(lo + band, ctx->n_reads);
+        CK(cudaMemsetAsync(ctx->sim32.p, 0, (hi - lo) * ctx->n_refs * 4, ctx->stream), "memset exact accumulator");
+        rc = run_k2_pass(ctx, ebwt_mode != 0, true, (uint32_t)lo, (uint32_t)hi);
+        if (rc) return rc;
+        {
+            LaunchScope ls(ctx, KID_K2_NARROW);
+            CK(launch_k2_narrow(ctx->sim32.as<uint32_t>(), (uint32_t)lo, (uint32_t)hi, ctx->n_refs,
+                                ctx->d_sim, ctx->sim_pitch, ctx->stream), "k2_narrow launch");
+        }
+    }
+    CK(cudaStreamSynchronize(ctx->stream), "k2 exact pass");
+    return LIME_OK;
+}
+
+int lime_sim_stats(lime_ctx *ctx, uint64_t out[4])
+{
+    if (!ctx || !out) return LIME_ERR_ARG;
+    for (int i = 0; i < 4; i++) out[i] = ctx->sim_stats[i];
+    return LIME_OK;
+}
+
+int lime_sim_copy(lime_ctx *ctx, uint8_t *out)
+{
+    if (!ctx || !out) return LIME_ERR_ARG;
+    if (!ctx->loaded) return fail(ctx, LIME_ERR_STATE, "lime_sim_copy: nothing loaded");
+    if (ctx->n_reads == 0 || ctx->n_refs == 0) return LIME_OK;
+    CK(cudaMemcpy2DAsync(out, ctx->n_refs, ctx->d_sim, ctx->sim_pitch, ctx->n_refs, ctx->n_reads,
+                         cudaMemcpyDeviceToHost, ctx->stream), "D2H similarity matrix");
+    CK(cudaStreamSynchronize(ctx->stream), "D2H similarity matrix");
+    return LIME_OK;
+}
+
+int lime_choose(lime_ctx *ctx, int slot, uint32_t norm, float beta,
+                uint32_t read_begin, uint32_t read_end, uint64_t *n_records)
+{
+    if (!ctx || slot < 0 || slot >= LIME_MAXFILES) return LIME_ERR_ARG;
+    if (!ctx->loaded) return fail(ctx, LIME_ERR_STATE, "lime_choose: nothing loaded");
+    if (read_begin > read_end || read_end > ctx->sim_rows) return fail(ctx, LIME_ERR_ARG, "lime_choose: bad read range");
+    CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+    Slot &S = ctx->slots[slot];
+    S.valid = false;
+    const uint32_t n = read_end - read_begin;
+    const uint64_t tiles = k3_num_tiles(n);
+    CK(ctx->tile_state.reserve(std::max<uint64_t>(tiles, 1) * 8), "cudaMalloc tile state");
+    CK(S.pos.reserve(std::max<uint64_t>(n, 1) * 8), "cudaMalloc pos");
+    CK(cudaMemsetAsync(ctx->scalars.p, 0, sizeof(unsigned long long) * SC_COUNT, ctx->stream), "memset scalars");
+    CK(cudaMemsetAsync(ctx->tile_state.p, 0, std::max<uint64_t>(tiles, 1) * 8, ctx->stream), "memset tile state");
+    K3Args a;
+    a.sim8 = ctx->d_sim; a.pitch8 = ctx->sim_pitch; a.n_refs = ctx->n_refs;
+    a.read_begin = read_begin; a.read_end = read_end; a.norm = norm; a.beta = beta;
+    a.tile_state = ctx->tile_state.as<unsigned long long>();
+    a.tile_counter = scalar<unsigned int>(ctx, SC_TILE_COUNTER);
+    a.n_records = scalar<unsigned long long>(ctx, SC_NRECORDS);
+    a.pos = S.pos.as<uint64_t>(); a.bin = nullptr;
+    unsigned long long total = 1;
+    if (tiles) {
+        {
+            LaunchScope ls(ctx, KID_K3_COUNT);
+            CK(launch_k3_count(a, ctx->stream), "k3_count launch");
+        }
+        CK(cudaMemcpyAsync(&total, a.n_records, 8, cudaMemcpyDeviceToHost, ctx->stream), "D2H record count");
+        CK(cudaStreamSynchronize(ctx->stream), "k3_count");
+    }
+    CK(S.bin.reserve(total * sizeof(lime_pair_sim)), "cudaMalloc records");
+    a.bin = S.bin.as<lime_pair_sim>();
+    {
+        LaunchScope ls(ctx, KID_K3_EMIT);
+        CK(launch_k3_emit(a, ctx->stream), "k3_emit launch");
+    }
+    S.n_records = total; S.read_begin = read_begin; S.n_reads = n; S.valid = true;
+    if (n_records) *n_records = total;
+    return LIME_OK;
+}
+
+int lime_choose_copy(lime_ctx *ctx, int slot, lime_pair_sim *bin, uint64_t *pos)
+{
+    if (!ctx || slot < 0 || slot >= LIME_MAXFILES) return LIME_ERR_ARG;
+    Slot &S = ctx->slots[slot];
+    if (!S.valid) return fail(ctx, LIME_ERR_STATE, "lime_choose_copy: empty slot");
+    if (bin) CK(cudaMemcpyAsync(bin, S.bin.p, S.n_records * sizeof(lime_pair_sim), cudaMemcpyDeviceToHost, ctx->stream), "D2H records");
+    if (pos && S.n_reads) CK(cudaMemcpyAsync(pos, S.pos.p, (uint64_t)S.n_reads * 8, cudaMemcpyDeviceToHost, ctx->stream), "D2H pos");
+    CK(cudaStreamSynchronize(ctx->stream), "D2H slot");
+    return LIME_OK;
+}
+
+int lime_slot_set(lime_ctx *ctx, int slot, const lime_pair_sim *bin, uint64_t n_records,
+                  const uint64_t *pos, uint32_t n_reads)
+{
+    if (!ctx || slot < 0 || slot >= LIME_MAXFILES || (!bin && n_records) || (!pos && n_reads)) return LIME_ERR_ARG;
+    CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+    Slot &S = ctx->slots[slot];
+    S.valid = false;
+    CK(S.bin.reserve(std::max<uint64_t>(n_records, 1) * sizeof(lime_pair_sim)), "cudaMalloc records");
+    CK(S.pos.reserve(std::max<uint64_t>(n_reads, 1) * 8), "cudaMalloc pos");
+    if (n_records) CK(cudaMemcpyAsync(S.bin.p, bin, n_records * sizeof(lime_pair_sim), cudaMemcpyHostToDevice, ctx->stream), "H2D records");
+    if (n_reads) CK(cudaMemcpyAsync(S.pos.p, pos, (uint64_t)n_reads * 8, cudaMemcpyHostToDevice, ctx->stream), "H2D pos");
+    CK(cudaStreamSynchronize(ctx->stream), "H2D slot");
+    S.n_records = n_records; S.read_begin = 0; S.n_reads = n_reads; S.valid = true;
+    return LIME_OK;
+}
+
+} // extern "C"
