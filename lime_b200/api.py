@@ -1,0 +1,181 @@
+"""Python face of the C ABI (include/lime_cuda.h): one `LimeContext` per process and GPU.
+
+This is plumbing for tests, the benchmark and the multi-GPU host; the product is the shared
+library.  Arrays are numpy arrays (host) or raw device pointers (ints, e.g. tensor.data_ptr()).
+"""
+import ctypes as C
+import numpy as np
+
+from . import _lib
+from ._lib import LimeError, MEM_HOST, MEM_DEVICE
+
+CLUSTER_DT = np.dtype([("pStart", "<u8"), ("len", "<u8")])          # Tools.h:85-88
+PAIR_SIM_DT = np.dtype([("sim", "<f4"), ("idRef", "<u4")])          # Tools.h:95-98
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return C.c_void_p(a)
+    assert a.flags["C_CONTIGUOUS"]
+    return C.c_void_p(a.ctypes.data)
+
+
+class LimeContext:
+    def __init__(self, device=0):
+        self.lib = _lib.load()
+        h = C.c_void_p()
+        rc = self.lib.lime_init(C.byref(h), device)
+        if rc != 0:
+            raise LimeError(rc, (self.lib.lime_last_error(None) or b"").decode())
+        self.h = h
+        self._keep = []
+
+    def close(self):
+        if self.h:
+            self.lib.lime_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise LimeError(rc, (self.lib.lime_last_error(self.h) or b"").decode())
+
+    # ---- plumbing -----------------------------------------------------------------------
+    def set_stream(self, stream_ptr):
+        self._ck(self.lib.lime_set_stream(self.h, C.c_void_p(stream_ptr) if stream_ptr else None))
+
+    def launch_count(self):
+        return int(self.lib.lime_launch_count(self.h))
+
+    def prof_enable(self, on=True):
+        self._ck(self.lib.lime_prof_enable(self.h, 1 if on else 0))
+
+    def prof_reset(self):
+        self._ck(self.lib.lime_prof_reset(self.h))
+
+    def prof(self):
+        out = {}
+        for k in range(self.lib.lime_prof_kernels()):
+            name, n, ms = C.c_char_p(), C.c_uint64(), C.c_double()
+            self._ck(self.lib.lime_prof_get(self.h, k, C.byref(name), C.byref(n), C.byref(ms)))
+            out[name.value.decode()] = {"launches": int(n.value), "ms": float(ms.value)}
+        return out
+
+    # ---- inputs -------------------------------------------------------------------------
+    def load(self, lcp, da, ebwt, n_reads, n_refs, n_own=None, n_halo=0, pos_base=0, is_last=True,
+             mem=MEM_HOST, n_total=None):
+        """lime_load.  Host mode takes numpy arrays; device mode takes pointers + n_total."""
+        if mem == MEM_HOST:
+            lcp = np.ascontiguousarray(lcp, dtype=np.uint32)
+            da = np.ascontiguousarray(da, dtype=np.uint32)
+            if ebwt is not None:
+                ebwt = np.ascontiguousarray(ebwt, dtype=np.uint8)
+            n_total = lcp.shape[0]
+            assert da.shape[0] == n_total and (ebwt is None or ebwt.shape[0] == n_total)
+        if n_own is None:
+            n_own = n_total - n_halo
+        assert n_own + n_halo == n_total
+        self._keep = [lcp, da, ebwt]
+        self.n_reads, self.n_refs = int(n_reads), int(n_refs)
+        self._ck(self.lib.lime_load(self.h, _ptr(lcp), _ptr(da), _ptr(ebwt), n_own, n_halo, pos_base,
+                                    1 if is_last else 0, n_reads, n_refs, mem))
+
+    def sim_bind(self, dev_ptr, rows, pitch):
+        self._ck(self.lib.lime_sim_bind(self.h, C.c_void_p(dev_ptr) if dev_ptr else None, rows, pitch))
+
+    def sim_pitch(self, n_refs):
+        return int(self.lib.lime_sim_pitch(n_refs))
+
+    # ---- step 1 ---------------------------------------------------------------------------
+    def cluster_detect(self, alpha):
+        n, mx = C.c_uint64(), C.c_uint64()
+        self._ck(self.lib.lime_cluster_detect(self.h, alpha, C.byref(n), C.byref(mx)))
+        self.n_clusters = int(n.value)
+        return int(n.value), int(mx.value)
+
+    def clusters(self):
+        out = np.empty(self.n_clusters, dtype=CLUSTER_DT)
+        self._ck(self.lib.lime_clusters_copy(self.h, _ptr(out), self.n_clusters))
+        return out
+
+    def clusters_set(self, cl, max_len=0):
+        cl = np.ascontiguousarray(cl, dtype=CLUSTER_DT)
+        self.n_clusters = cl.shape[0]
+        self._ck(self.lib.lime_clusters_set(self.h, _ptr(cl), cl.shape[0], max_len))
+
+    # ---- step 2 ---------------------------------------------------------------------------
+    def similarity(self, ebwt_mode):
+        self._ck(self.lib.lime_similarity(self.h, 1 if ebwt_mode else 0))
+
+    def sim_stats(self):
+        out = (C.c_uint64 * 4)()
+        self._ck(self.lib.lime_sim_stats(self.h, out))
+        return {"warp_clusters": out[0], "block_clusters": out[1], "updates": out[2], "exact_pass": out[3]}
+
+    def sim_matrix(self):
+        out = np.empty((self.n_reads, self.n_refs), dtype=np.uint8)
+        self._ck(self.lib.lime_sim_copy(self.h, _ptr(out)))
+        return out
+
+    def choose(self, slot, norm, beta, read_begin=0, read_end=None):
+        if read_end is None:
+            read_end = self.n_reads
+        n = C.c_uint64()
+        self._ck(self.lib.lime_choose(self.h, slot, norm, beta, read_begin, read_end, C.byref(n)))
+        self._slot_shape = getattr(self, "_slot_shape", {})
+        self._slot_shape[slot] = (int(n.value), read_end - read_begin)
+        return int(n.value)
+
+    def choose_result(self, slot):
+        n_rec, n_reads = self._slot_shape[slot]
+        bin_ = np.empty(n_rec, dtype=PAIR_SIM_DT)
+        pos = np.empty(n_reads, dtype=np.uint64)
+        self._ck(self.lib.lime_choose_copy(self.h, slot, _ptr(bin_), _ptr(pos)))
+        return bin_, pos
+
+    def slot_set(self, slot, bin_, pos):
+        bin_ = np.ascontiguousarray(bin_, dtype=PAIR_SIM_DT)
+        pos = np.ascontiguousarray(pos, dtype=np.uint64)
+        self._ck(self.lib.lime_slot_set(self.h, slot, _ptr(bin_), bin_.shape[0], _ptr(pos), pos.shape[0]))
+        self._slot_shape = getattr(self, "_slot_shape", {})
+        self._slot_shape[slot] = (bin_.shape[0], pos.shape[0])
+
+    # ---- step 3 ---------------------------------------------------------------------------
+    def classify(self, n_files, n_refs, v_corRef, m_corRef=None, tax_rank=1, higher=False):
+        n_reads = self._slot_shape[0][1]
+        v = np.ascontiguousarray(v_corRef, dtype=np.uint32)
+        m = None if m_corRef is None else np.ascontiguousarray(m_corRef, dtype=np.uint32)
+        typ = np.empty(n_reads, dtype=np.uint8)
+        tax = np.empty(n_reads, dtype=np.uint32)
+        sim = np.empty(n_reads, dtype=np.float32)
+        self._ck(self.lib.lime_classify(self.h, n_files, n_refs, _ptr(v), _ptr(m), tax_rank,
+                                        1 if higher else 0, _ptr(typ), _ptr(tax), _ptr(sim)))
+        return typ, tax, sim
+
+
+# ---- host helpers (lime_host.h) -------------------------------------------------------------
+def fix_rank(path, tax_rank, n_refs, higher=False):
+    """FixRank (Classify.cpp:33-89) -> (v_corRef or None on size mismatch, m_corRef, found)."""
+    lib = _lib.load()
+    v = np.zeros(max(n_refs, 1), dtype=np.uint32)
+    m = np.zeros((6, max(n_refs, 1)), dtype=np.uint32) if higher else None
+    found = lib.lime_host_fix_rank(path.encode(), tax_rank, n_refs, _ptr(v), n_refs, _ptr(m))
+    if found < 0:
+        raise FileNotFoundError(path)
+    return (v[:n_refs] if found == n_refs else None), (m[:, :n_refs].copy() if m is not None else None), int(found)
+
+
+def write_csv(path, typ, tax, sim):
+    lib = _lib.load()
+    typ = np.ascontiguousarray(typ, dtype=np.uint8)
+    tax = np.ascontiguousarray(tax, dtype=np.uint32)
+    sim = np.ascontiguousarray(sim, dtype=np.float32)
+    if lib.lime_host_write_csv(path.encode(), typ.shape[0], _ptr(typ), _ptr(tax), _ptr(sim)) != 0:
+        raise OSError(f"cannot write {path}")

@@ -64,6 +64,8 @@ int lime_similarity(lime_ctx *ctx, int ebwt_mode)
     uint64_t band = std::max<uint64_t>(1, budget / ((uint64_t)ctx->n_refs * 4));
     band = std::min<uint64_t>(band, ctx->n_reads);
     CK(ctx->sim32.reserve(band * ctx->n_refs * 4), "cudaMalloc exact accumulator");
+    // carries may also have spilled into the padding bytes of a row: start from a clean matrix
+    CK(cudaMemsetAsync(ctx->d_sim, 0, ctx->sim_rows * ctx->sim_pitch, ctx->stream), "memset similarity matrix");
     for (uint64_t lo = 0; lo < ctx->n_reads; lo += band) {
         const uint64_t hi = std::min<uint64_t>(lo + band, ctx->n_reads);
         CK(cudaMemsetAsync(ctx->sim32.p, 0, (hi - lo) * ctx->n_refs * 4, ctx->stream), "memset exact accumulator");
