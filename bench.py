@@ -1,0 +1,470 @@
+#!/usr/bin/env python
+"""bench.py -- LiME classification hot path on B200: eBWT symbols/s.
+
+    python bench.py --gpus N --steps K --warmup W            (ours; torchrun for N > 1)
+    python bench.py --impl reference --gpus N --steps K ...  (the reference's CPU pipeline)
+
+Workload (BASELINE.json configs[1]): single-end synthetic, 2 M reads x 100 bp + 100 genomes,
+N = 402 M eBWT symbols per strand, two strands (F, RC), EBWT=1, alpha=16, beta=0.25, TaxRank=1.
+One step = the whole job: per strand cluster detection (step 1), similarity accumulation and
+clusterChoose (step 2), then Classify over both strands (step 3).  At N > 1 GPUs the position
+range of every strand is sharded contiguously (weak scaling: every GPU holds 402 M symbols per
+strand and the job has N x 2 M reads).
+
+value  = symbols of all strands / step time, inputs resident in HBM (CUDA events).
+e2e    = the same through the C ABI with HOST buffers: pinned host -> device copies of
+         lcp/da/ebwt and the device -> host copy of the assignments inside the timed region.
+The oracle / reference binaries are used only for cpu_baseline and --impl reference.
+"""
+import argparse
+import json
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WORKLOAD = dict(name="cfg2 single-end synthetic: 2M reads x 100bp + 100 genomes, 402M symbols/strand, "
+                     "2 strands (F,RC), EBWT=1, alpha=16, beta=0.25, TaxRank=1",
+                n=402_000_000, n_reads=2_000_000, n_refs=100, read_len=100, alpha=16, beta=0.25,
+                ebwt=1, n_strands=2, tax_rank=1, seed=20261104 + 2)
+CPU_SAMPLE_N = 1 << 25          # positions per strand of the CPU-timed prefix sample
+METRIC = "ebwt_symbols_per_s"
+UNIT = "symbols/s"
+
+
+def _small(w, n, n_reads):
+    w = dict(w)
+    w.update(n=n, n_reads=n_reads, name=f"REDUCED test shape n={n} n_reads={n_reads} (not the benchmark)")
+    return w
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0, period_ms=50):
+        self.rows, self.proc, self.thr = [], None, None
+        self.cmd = ["nvidia-smi", f"--id={gpu_index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                    "-lms", str(period_ms)]
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(self.cmd, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        def pump():
+            for line in self.proc.stdout:
+                self.rows.append((time.time(), line.strip()))
+        self.thr = threading.Thread(target=pump, daemon=True)
+        self.thr.start()
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        if self.thr:
+            self.thr.join(timeout=2)
+
+    def summary(self, t0, t1):
+        sm, mx, reasons, pw = [], [], set(), []
+        for t, line in self.rows:
+            if t < t0 or t > t1 + 0.05:
+                continue
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm), "power_w_max": max(pw)}
+
+
+# ------------------------------------------------------------------------------------------------
+# the reference's CPU pipeline on a bounded sample (oracle/_ref binaries; the one place bench.py
+# executes anything under oracle/)
+# ------------------------------------------------------------------------------------------------
+def _lineage_file(path, n_refs):
+    from lime_b200.pipeline import synthetic_lineage
+    rows, v, m = synthetic_lineage(n_refs)
+    with open(path, "w") as f:
+        f.write("Acc;Species_TaxID;Genus_TaxID;Family_TaxID;Order_TaxID;Class_TaxID;Phylum_TaxID\n")
+        for r in rows:
+            f.write(";".join(str(x) for x in r) + "\n")
+    return v, m
+
+
+def _scratch_dir():
+    for base in ("/dev/shm", tempfile.gettempdir()):
+        try:
+            if os.path.isdir(base) and shutil.disk_usage(base).free > (4 << 30):
+                return tempfile.mkdtemp(prefix="lime_bench_", dir=base)
+        except OSError:
+            pass
+    return tempfile.mkdtemp(prefix="lime_bench_")
+
+
+class CpuReference:
+    """Runs the unmodified reference (ClusterLCP, ClusterBWT_DA, Classify from oracle/_ref) with
+    the schedule of LiME_paired.sh: ClusterLCP of all strands concurrently (:44-53), ClusterBWT_DA
+    strand after strand (:62-68), one Classify (:79); all with threads = host cores."""
+
+    def __init__(self, w, sample_n):
+        from oracle.oracle import Reference
+        self.ref = Reference()
+        self.kind = "reference" if self.ref.available() else "port"
+        self.w, self.sample_n = w, min(sample_n, w["n"])
+        self.cores = os.cpu_count() or 1
+        self.dir = _scratch_dir()
+        self.fastas = []
+
+    def write_inputs(self, strands_host):
+        """strands_host: list of (ebwt u8, lcp u32, da u32) numpy prefixes."""
+        from lime_b200 import datagen
+        for s, (e, l, d) in enumerate(strands_host):
+            fasta = os.path.join(self.dir, f"strand{s}+Refs.fasta")
+            datagen.write_strand(fasta, e, l, d)
+            self.fastas.append(fasta)
+        self.lineage = os.path.join(self.dir, "lineage.csv")
+        self.v, self.m = _lineage_file(self.lineage, self.w["n_refs"])
+        self.host = strands_host
+
+    def step(self):
+        """One pass of the reference pipeline over the sample; returns wall seconds."""
+        w = self.w
+        t0 = time.perf_counter()
+        if self.kind == "reference":
+            exe = lambda n: os.path.join(self.ref.dir, n)          # noqa: E731
+            procs = [subprocess.Popen([exe("ClusterLCP"), f, str(w["n_reads"]), str(w["n_refs"]), str(w["alpha"]),
+                                       str(self.cores)], cwd=self.dir, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+                     for f in self.fastas]
+            for p in procs:
+                assert p.wait() == 0, "reference ClusterLCP failed"
+            for f in self.fastas:
+                r = subprocess.run([exe("ClusterBWT_DA_ebwt1" if w["ebwt"] else "ClusterBWT_DA_ebwt0"), f,
+                                    str(w["read_len"]), str(w["beta"]), str(self.cores)], cwd=self.dir,
+                                   stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True)
+                assert r.returncode == 0, r.stderr
+            out = os.path.join(self.dir, "out.csv")
+            r = subprocess.run([exe("Classify_higher0"), str(len(self.fastas))] + [f + ".res" for f in self.fastas] +
+                               [str(w["n_reads"]), str(w["n_refs"]), out, self.lineage, str(w["tax_rank"]),
+                                str(self.cores)], cwd=self.dir, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True)
+            assert r.returncode == 0, r.stderr
+        else:                                                    # scalar C port (1 core)
+            from oracle.oracle import Oracle
+            from lime_b200.pipeline import norm_of
+            orc = Oracle()
+            bins, poss = [], []
+            for (e, l, d) in self.host:
+                cl, _ = orc.cluster_detect(l, d, w["n_reads"], w["alpha"])
+                sim = orc.similarity(cl, d, e if w["ebwt"] else None, w["n_reads"], w["n_refs"])
+                b, p = orc.choose(sim, norm_of(w["read_len"], w["alpha"]), np.float32(w["beta"]))
+                bins.append(b); poss.append(p)
+            orc.classify(bins, poss, w["n_refs"], self.v, None, w["tax_rank"], False)
+        return time.perf_counter() - t0
+
+    def describe(self):
+        return (f"prefix of {self.sample_n} positions per strand x {len(self.fastas)} strands of the same workload "
+                f"(all {self.w['n_reads']} reads, {self.w['n_refs']} genomes), files in {os.path.dirname(self.dir) or self.dir}, "
+                f"page cache warm; ClusterLCP x{len(self.fastas)} concurrent, ClusterBWT_DA x{len(self.fastas)} sequential, "
+                f"Classify {len(self.fastas)}; threads={self.cores if self.kind == 'reference' else 1}")
+
+    def close(self):
+        shutil.rmtree(self.dir, ignore_errors=True)
+
+
+def _host_sample(w, sample_n, device):
+    """The first sample_n positions of every strand, as numpy arrays in the file formats."""
+    from lime_b200 import datagen
+    out = []
+    for s in range(w["n_strands"]):
+        e, l, d = datagen.synth_arrays(w["n"], w["n_reads"], w["n_refs"], w["read_len"], seed=w["seed"] + 1000 * s,
+                                       device=device, hi=sample_n)
+        out.append((e.cpu().numpy(), l.cpu().numpy().view(np.uint32), d.cpu().numpy().view(np.uint32)))
+    return out
+
+
+def run_reference_arm(args, w):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    dev = "cuda" if torch.cuda.is_available() else "cpu"
+    cpu = CpuReference(w, args.cpu_sample)
+    try:
+        cpu.write_inputs(_host_sample(w, cpu.sample_n, dev))
+        for _ in range(args.warmup):
+            cpu.step()
+        times = [cpu.step() for _ in range(args.steps)]
+        total = sum(times)
+        symbols = cpu.sample_n * w["n_strands"]
+        value = symbols * args.steps / total
+        line = {
+            "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": w["name"], "sample": cpu.describe()},
+            "reads_per_s": w["n_reads"] * (cpu.sample_n / w["n"]) * args.steps / total,
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cpu.cores if cpu.kind == "reference" else 1,
+                             "kind": cpu.kind, "sample": cpu.describe()},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+        }
+        print(json.dumps(line), flush=True)
+    finally:
+        cpu.close()
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------
+def _alg_bytes(kname, st, w):
+    """Algorithmic bytes of one launch of kernel family `kname` for a strand with stats st
+    (DESIGN.md 'kernels')."""
+    E = 1 if w["ebwt"] else 0
+    n, C, P, nr, ng = st["n"], st["n_clusters"], st["cluster_positions"], st["n_reads_total"], w["n_refs"]
+    if kname == "k1_detect":
+        return 8 * n + 16 * C
+    if kname in ("k2_warp", "k2_block"):
+        return (4 + E) * P + 16 * C          # da (+ebwt) of the clustered positions + the records
+    if kname == "k12_fused":
+        return (8 + E) * n
+    if kname == "k3_count":
+        return nr * ng + 8 * nr
+    if kname == "k3_emit":
+        return nr * ng + 8 * st["n_records"]
+    if kname == "k3_classify":
+        return 8 * st["n_records"] + 8 * nr + 9 * nr
+    return 0
+
+
+def run_ours(args, w):
+    import torch
+    import torch.distributed as dist
+    from lime_b200 import datagen
+    from lime_b200.api import LimeContext, MEM_DEVICE, MEM_HOST
+    from lime_b200.pipeline import run_job, synthetic_lineage
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback; use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        from lime_b200 import multi
+        return multi.bench_main(args, w, METRIC, UNIT, ClockSampler)
+
+    dev = torch.device("cuda", local)
+    ctx = LimeContext(local)
+    stream = torch.cuda.current_stream()
+    ctx.set_stream(stream.cuda_stream)
+    rows, v, m = synthetic_lineage(w["n_refs"])
+
+    # ---- synthetic inputs, resident in HBM ----------------------------------------------------
+    strands_dev, keep = [], []
+    for s in range(w["n_strands"]):
+        e, l, d = datagen.synth_arrays(w["n"], w["n_reads"], w["n_refs"], w["read_len"], seed=w["seed"] + 1000 * s,
+                                       device=dev)
+        keep.append((e, l, d))
+        strands_dev.append({"ebwt": e.data_ptr(), "lcp": l.data_ptr(), "da": d.data_ptr(), "n": w["n"]})
+    torch.cuda.synchronize()
+
+    def step_resident():
+        return run_job(ctx, strands_dev, w["n_reads"], w["n_refs"], w["read_len"], w["alpha"], w["beta"], w["ebwt"],
+                       v, None, w["tax_rank"], False, mem=MEM_DEVICE)
+
+    # ---- warm-up (also gathers the per-strand statistics the roofline needs) -------------------
+    for _ in range(max(args.warmup, 1)):
+        out, stats = step_resident()
+    strand_stats = []
+    for s in range(w["n_strands"]):
+        # cluster statistics of strand s (outside the timed region)
+        ctx.load(strands_dev[s]["lcp"], strands_dev[s]["da"], strands_dev[s]["ebwt"], w["n_reads"], w["n_refs"],
+                 mem=MEM_DEVICE, n_total=w["n"])
+        n_cl, max_len = ctx.cluster_detect(w["alpha"])
+        cl = ctx.clusters()
+        strand_stats.append({"n": w["n"], "n_clusters": int(n_cl), "max_len": int(max_len),
+                             "cluster_positions": int(cl["len"].sum()), "n_records": int(stats[s][2]),
+                             "n_reads_total": w["n_reads"]})
+        del cl
+    out, stats = step_resident()          # leave the slots in a consistent state
+    kinds = {chr(t): int((out[0] == t).sum()) for t in np.unique(out[0])}
+
+    # ---- timed region: K steps, resident inputs -------------------------------------------------
+    clocks = ClockSampler(local)
+    clocks.start()
+    time.sleep(0.3)
+    ctx.prof_enable(True)
+    ctx.prof_reset()
+    l0 = ctx.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    t0 = time.time()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step_resident()
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    t1 = time.time()
+    ms_total = ev0.elapsed_time(ev1)
+    launches = ctx.launch_count() - l0
+    prof = ctx.prof()
+    ctx.prof_enable(False)
+    clk = clocks.summary(t0, t1)
+
+    ms_step = ms_total / args.steps
+    symbols = w["n"] * w["n_strands"]
+    value = symbols / (ms_step * 1e-3)
+
+    # ---- roofline of the dominant kernel ----------------------------------------------------------
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak_gbs, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    kern = {k: x for k, x in prof.items() if x["launches"]}
+    kernel_ms_total = sum(x["ms"] for x in kern.values())
+    top = max(kern, key=lambda k: kern[k]["ms"])
+    per_strand_launches = kern[top]["launches"] / (args.steps * (1 if top == "k3_classify" else w["n_strands"]))
+    if top == "k3_classify":
+        agg = dict(strand_stats[0]); agg["n_records"] = sum(s["n_records"] for s in strand_stats)
+        alg = _alg_bytes(top, agg, w) * args.steps
+    else:
+        alg = sum(_alg_bytes(top, s, w) for s in strand_stats) * args.steps
+    avg_launch_ms = kern[top]["ms"] / kern[top]["launches"]
+    alg_per_launch = alg / kern[top]["launches"]
+    achieved = alg_per_launch / (avg_launch_ms * 1e-3) / 1e9
+    traffic = None
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic = tr.get(top, {}).get("dram_bytes_per_launch")
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
+                "frac": achieved / peak_gbs, "traffic": traffic, "peak_source": peak_src,
+                "alg_bytes_per_launch": alg_per_launch, "avg_launch_ms": avg_launch_ms,
+                "launches_per_strand": per_strand_launches,
+                "kernel_share_of_step": kern[top]["ms"] / ms_total,
+                "kernels_ms_per_step": {k: x["ms"] / args.steps for k, x in kern.items()},
+                "kernel_time_fraction_of_step": kernel_ms_total / ms_total,
+                "job_alg_bytes_per_step": sum((8 + w["ebwt"]) * s["n"] for s in strand_stats),
+                "job_frac_of_peak": sum((8 + w["ebwt"]) * s["n"] for s in strand_stats) / (ms_step * 1e-3) / 1e9 / peak_gbs}
+
+    # ---- e2e: host buffers through the C ABI ----------------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        strands_host, pins = [], []
+        for (e, l, d) in keep:
+            pe = torch.empty(e.shape, dtype=e.dtype, pin_memory=True); pe.copy_(e)
+            pl = torch.empty(l.shape, dtype=l.dtype, pin_memory=True); pl.copy_(l)
+            pd = torch.empty(d.shape, dtype=d.dtype, pin_memory=True); pd.copy_(d)
+            pins.append((pe, pl, pd))
+            strands_host.append({"ebwt": pe.numpy(), "lcp": pl.numpy().view(np.uint32), "da": pd.numpy().view(np.uint32),
+                                 "n": w["n"]})
+        torch.cuda.synchronize()
+
+        def step_host():
+            return run_job(ctx, strands_host, w["n_reads"], w["n_refs"], w["read_len"], w["alpha"], w["beta"],
+                           w["ebwt"], v, None, w["tax_rank"], False, mem=MEM_HOST)
+        out_h, _ = step_host()
+        for a, b in zip(out, out_h):
+            assert a.tobytes() == b.tobytes(), "host-buffer path disagrees with the resident path"
+        e2e_steps = max(1, min(args.steps, 5))
+        torch.cuda.synchronize()
+        ev0.record(stream)
+        tw0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            step_host()
+        ev1.record(stream)
+        torch.cuda.synchronize()
+        tw1 = time.perf_counter()
+        e_ms = max(ev0.elapsed_time(ev1), (tw1 - tw0) * 1e3) / e2e_steps
+        h2d = sum((8 + w["ebwt"]) * w["n"] for _ in range(w["n_strands"])) + 4 * w["n_refs"]
+        d2h = 9 * w["n_reads"]
+        e2e = {"value": symbols / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "ms_per_step": e_ms, "steps": e2e_steps, "reads_per_s": w["n_reads"] / (e_ms * 1e-3),
+               "note": "lime_load(LIME_MEM_HOST) from pinned host arrays per strand + assignments copied back; PCIe-bound"}
+        del pins, strands_host
+
+    # ---- CPU baseline beside it (rank 0, N = 1 only) ----------------------------------------------------
+    cpu_baseline = None
+    if not args.no_cpu:
+        cpu = CpuReference(w, args.cpu_sample)
+        try:
+            sample = []
+            for (e, l, d) in keep:
+                k = cpu.sample_n
+                sample.append((e[:k].cpu().numpy(), l[:k].cpu().numpy().view(np.uint32), d[:k].cpu().numpy().view(np.uint32)))
+            cpu.write_inputs(sample)
+            cpu.step()                                   # warms the page cache
+            t = cpu.step()
+            cpu_baseline = {"value": cpu.sample_n * w["n_strands"] / t, "unit": UNIT,
+                            "cores": cpu.cores if cpu.kind == "reference" else 1, "kind": cpu.kind,
+                            "sample": cpu.describe(), "seconds": t}
+        finally:
+            cpu.close()
+    clocks.stop()
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 1),
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic",
+        "config": {"workload": w["name"], "l2": "inputs (3.6 GB per strand) are larger than L2; no flush needed",
+                   "parallelism": "1 GPU", "symbols_per_step": symbols, "reads_per_step": w["n_reads"],
+                   "strand_stats": strand_stats, "assignments": kinds},
+        "reads_per_s": w["n_reads"] / (ms_step * 1e-3),
+        "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches),
+        "clocks": clk,
+    }
+    print(json.dumps(line), flush=True)
+    ctx.close()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cpu-sample", type=int, default=CPU_SAMPLE_N)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--small", action="store_true", help="reduced shape for functional testing only")
+    args = ap.parse_args()
+    w = dict(WORKLOAD)
+    if args.small:
+        w = _small(w, 4_000_000, 20_000)
+        args.cpu_sample = min(args.cpu_sample, 1 << 20)
+    if args.impl == "reference":
+        run_reference_arm(args, w)
+    else:
+        run_ours(args, w)
+
+
+if __name__ == "__main__":
+    main()

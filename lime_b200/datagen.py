@@ -110,7 +110,7 @@ def _geom_table(torch, p, kmax, device):
 
 def synth_arrays(n, n_reads, n_refs, read_len, seed=20261104, alpha_min=12, p_long=1e-5,
                  trlcp=None, terminator=0x24, device="cpu", chunk=1 << 25, p_mixed=0.35,
-                 max_seg=60000):
+                 max_seg=60000, lo=0, hi=None):
     """Directly synthesise (ebwt u8, lcp i32, da i32) torch tensors of n positions on `device`.
 
     Segment lengths: P(L=1)=0.5, else 2+Geometric(1/6); with probability p_long uniform in
@@ -122,6 +122,8 @@ def synth_arrays(n, n_reads, n_refs, read_len, seed=20261104, alpha_min=12, p_lo
     ebwt: segment-dominant base w.p. 0.9 else uniform ACGT, N w.p. 1e-4, other IUPAC w.p. 1e-6 on
     genome positions, terminator byte w.p. (n_reads+n_refs)/n.
     int32 views are bit-identical to the uint32 file format (all values < 2^31).
+    lo / hi: return only positions [lo, hi) of the n-position model (every value is a function
+    of (seed, position, segment), so a window equals the same slice of the full arrays).
     """
     import torch
     dev = torch.device(device)
@@ -135,9 +137,11 @@ def synth_arrays(n, n_reads, n_refs, read_len, seed=20261104, alpha_min=12, p_lo
     thr_ronly = int((p_mixed + x_r) * T32)
     thr_qm = int(q_m * T32)
 
-    # ---- segments -------------------------------------------------------------------------
+    hi = n if hi is None else min(int(hi), n)
+    lo = max(0, min(int(lo), hi))
+    # ---- segments (only as many as cover [0, hi)) -------------------------------------------
     mean_len = 0.5 * 1 + 0.5 * 7.0 + p_long * (1024 + max_seg) / 2
-    n_seg = int(n / mean_len * 1.08) + 1024
+    n_seg = int(hi / mean_len * 1.08) + 1024
     while True:
         sid = torch.arange(n_seg, dtype=I64, device=dev)
         u1 = _u32(torch, sid, seed, 1)
@@ -149,12 +153,12 @@ def synth_arrays(n, n_reads, n_refs, read_len, seed=20261104, alpha_min=12, p_lo
             long_len = 1024 + (u2 % (max_seg - 1024 + 1))
             seg_len = torch.where(u3 < int(p_long * T32), long_len, seg_len)
         seg_end = torch.cumsum(seg_len, 0)
-        if int(seg_end[-1]) >= n:
+        if int(seg_end[-1]) >= hi:
             break
         n_seg *= 2
-    k = int(torch.searchsorted(seg_end, torch.tensor([n], dtype=I64, device=dev), right=False)[0]) + 1
+    k = int(torch.searchsorted(seg_end, torch.tensor([hi], dtype=I64, device=dev), right=False)[0]) + 1
     seg_end = seg_end[:k].clone()
-    seg_end[-1] = n
+    seg_end[-1] = min(int(seg_end[-1]), n)
     sid = sid[:k]
     seg_start = torch.cat([torch.zeros(1, dtype=I64, device=dev), seg_end[:-1]])
     uk = _u32(torch, sid, seed, 4)
@@ -163,17 +167,17 @@ def synth_arrays(n, n_reads, n_refs, read_len, seed=20261104, alpha_min=12, p_lo
     seg_base = (_u32(torch, sid, seed, 6) & 3).to(torch.int8)
     del u1, u2, u3, uk, geo6, seg_len
 
-    ebwt = torch.empty(n, dtype=torch.uint8, device=dev)
-    lcp = torch.empty(n, dtype=torch.int32, device=dev)
-    da = torch.empty(n, dtype=torch.int32, device=dev)
+    ebwt = torch.empty(hi - lo, dtype=torch.uint8, device=dev)
+    lcp = torch.empty(hi - lo, dtype=torch.int32, device=dev)
+    da = torch.empty(hi - lo, dtype=torch.int32, device=dev)
     geo08 = _geom_table(torch, 0.08, 512, dev)
     acgt = torch.tensor([65, 67, 71, 84], dtype=torch.uint8, device=dev)
     iupac = torch.tensor([ord(c) for c in "RYSWKMBDHV"], dtype=torch.uint8, device=dev)
     thr_term = int(min(0.5, (n_reads + n_refs) / float(n)) * T32)
     reads_per_home = (n_reads + n_refs - 1) // n_refs
 
-    for a in range(0, n, chunk):
-        b = min(n, a + chunk)
+    for a in range(lo, hi, chunk):
+        b = min(hi, a + chunk)
         pos = torch.arange(a, b, dtype=I64, device=dev)
         s = torch.searchsorted(seg_end, pos, right=True)
         head = seg_start[s] == pos
@@ -183,7 +187,7 @@ def synth_arrays(n, n_reads, n_refs, read_len, seed=20261104, alpha_min=12, p_lo
         v = torch.where(head, ul % max(alpha_min, 1), interior)
         if trlcp is not None:
             v = torch.clamp(v, max=trlcp)
-        lcp[a:b] = v.to(torch.int32)
+        lcp[a - lo:b - lo] = v.to(torch.int32)
         # da
         kind = seg_kind[s]
         g = seg_g[s].to(I64)
@@ -194,7 +198,7 @@ def synth_arrays(n, n_reads, n_refs, read_len, seed=20261104, alpha_min=12, p_lo
         r = torch.where(r < n_reads, r, r % n_reads)
         ug = _u32(torch, pos, seed, 13)
         gid = torch.where((ug & 0xFFFF) < 58982, g, (ug >> 16) % n_refs)     # 0.9 * 65536
-        da[a:b] = torch.where(is_read, r, n_reads + gid).to(torch.int32)
+        da[a - lo:b - lo] = torch.where(is_read, r, n_reads + gid).to(torch.int32)
         # ebwt
         ub = _u32(torch, pos, seed, 14)
         base = torch.where((ub & 0xFFFF) < 58982, seg_base[s].to(I64), (ub >> 16) & 3)
@@ -204,8 +208,9 @@ def synth_arrays(n, n_reads, n_refs, read_len, seed=20261104, alpha_min=12, p_lo
         sym = torch.where((~is_read) & (ui >= 429497) & (ui < 429497 + 4295), iupac[(ui >> 3) % 10], sym)  # 1e-6
         ut = _u32(torch, pos, seed, 16)
         sym = torch.where(ut < thr_term, torch.full_like(sym, terminator), sym)
-        ebwt[a:b] = sym
-    lcp[0] = 0
+        ebwt[a - lo:b - lo] = sym
+    if lo == 0 and hi > 0:
+        lcp[0] = 0
     return ebwt, lcp, da
 
 
