@@ -295,7 +295,7 @@ def run_ours(args, w):
 
     def step_resident():
         return run_job(ctx, strands_dev, w["n_reads"], w["n_refs"], w["read_len"], w["alpha"], w["beta"], w["ebwt"],
-                       v, None, w["tax_rank"], False, mem=MEM_DEVICE)
+                       v, None, w["tax_rank"], False, mem=MEM_DEVICE, fused=not args.unfused)
 
     # ---- warm-up (also gathers the per-strand statistics the roofline needs) -------------------
     for _ in range(max(args.warmup, 1)):
@@ -390,7 +390,7 @@ def run_ours(args, w):
 
         def step_host():
             return run_job(ctx, strands_host, w["n_reads"], w["n_refs"], w["read_len"], w["alpha"], w["beta"],
-                           w["ebwt"], v, None, w["tax_rank"], False, mem=MEM_HOST)
+                           w["ebwt"], v, None, w["tax_rank"], False, mem=MEM_HOST, fused=not args.unfused)
         out_h, _ = step_host()
         for a, b in zip(out, out_h):
             assert a.tobytes() == b.tobytes(), "host-buffer path disagrees with the resident path"
@@ -455,6 +455,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--small", action="store_true", help="reduced shape for functional testing only")
+    ap.add_argument("--unfused", action="store_true", help="cluster list between steps 1 and 2 (for comparison)")
     args = ap.parse_args()
     w = dict(WORKLOAD)
     if args.small:

@@ -86,6 +86,20 @@ int  lime_clusters_copy(lime_ctx *ctx, lime_cluster *out, uint64_t cap);
  * ClusterBWT_DA.cpp:641-654); any order.  pStart is a global position. */
 int  lime_clusters_set(lime_ctx *ctx, const lime_cluster *cl, uint64_t n_clusters, uint64_t max_len);
 
+/* ---- steps 1 + 2a fused ------------------------------------------------------------------- */
+
+/*
+ * One pass over lcp / da / ebwt that detects the alpha-clusters of this shard (as
+ * lime_cluster_detect, ClusterLCP.cpp:139-283) AND accumulates their similarity (as
+ * lime_similarity, ClusterBWT_DA.cpp:256-358), without materialising the cluster list: what
+ * `LiME_paired.sh` does with ClusterLCP followed by clusterAnalyze, minus the .clrs round trip.
+ * keep_clusters != 0 also keeps the records on the device for lime_clusters_copy (.clrs output).
+ * n_clusters / max_len are the values ClusterLCP writes to <stem>.out; max_len > sizeMaxBuf is
+ * the error of ClusterBWT_DA.cpp:558-562 (LIME_ERR_MAXLEN).  May be called once per load.
+ */
+int  lime_cluster_similarity(lime_ctx *ctx, uint32_t alpha, int ebwt_mode, int keep_clusters,
+                             uint64_t *n_clusters, uint64_t *max_len);
+
 /* ---- step 2 : ClusterBWT_DA.cpp:256-358, 361-450 ------------------------------------------ */
 
 /* Accumulate t(read, genome) of every resident cluster into the similarity matrix

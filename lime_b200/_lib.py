@@ -39,6 +39,7 @@ SIGNATURES = {
     "lime_clusters_copy": (C.c_int, [vp, vp, C.c_uint64]),
     "lime_clusters_set": (C.c_int, [vp, vp, C.c_uint64, C.c_uint64]),
     "lime_similarity": (C.c_int, [vp, C.c_int]),
+    "lime_cluster_similarity": (C.c_int, [vp, C.c_uint32, C.c_int, C.c_int, u64p, u64p]),
     "lime_sim_bind": (C.c_int, [vp, vp, C.c_uint64, C.c_uint64]),
     "lime_sim_pitch": (C.c_uint64, [C.c_uint32]),
     "lime_sim_copy": (C.c_int, [vp, vp]),

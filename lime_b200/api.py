@@ -110,6 +110,14 @@ class LimeContext:
         self.n_clusters = cl.shape[0]
         self._ck(self.lib.lime_clusters_set(self.h, _ptr(cl), cl.shape[0], max_len))
 
+    # ---- steps 1 + 2a fused ---------------------------------------------------------------
+    def cluster_similarity(self, alpha, ebwt_mode, keep_clusters=False):
+        n, mx = C.c_uint64(), C.c_uint64()
+        self._ck(self.lib.lime_cluster_similarity(self.h, alpha, 1 if ebwt_mode else 0,
+                                                  1 if keep_clusters else 0, C.byref(n), C.byref(mx)))
+        self.n_clusters = int(n.value)
+        return int(n.value), int(mx.value)
+
     # ---- step 2 ---------------------------------------------------------------------------
     def similarity(self, ebwt_mode):
         self._ck(self.lib.lime_similarity(self.h, 1 if ebwt_mode else 0))

@@ -93,7 +93,8 @@ struct DevBuf {
 };
 
 enum KernelId {
-    KID_K1_DETECT = 0,
+    KID_K12_FUSED = 0,
+    KID_K1_DETECT,
     KID_K2_WARP,
     KID_K2_BLOCK,
     KID_K2_NARROW,
@@ -145,6 +146,7 @@ struct lime_ctx {
     bool sim_bound = false, sim_done = false;
     lime::DevBuf sim32;             // exact pass scratch
     lime::DevBuf large_list;        // u64 cluster indices for the block path
+    lime::DevBuf long_recs;         // fused path: records of the clusters left to the block path
     lime::DevBuf k2_scratch;        // block-path hash tables
     uint64_t sim_stats[4] = {0, 0, 0, 0};
 
@@ -165,22 +167,6 @@ struct lime_ctx {
 namespace lime {
 
 // launchers implemented in the kernel translation units; all asynchronous on ctx->stream
-struct K1Args {
-    const uint32_t *lcp, *da;
-    uint64_t n_own, n_total, pos_base;
-    int is_last;
-    uint32_t alpha, n_reads;
-    lime_cluster *out;
-    uint64_t out_cap;
-    unsigned long long *tile_state;
-    unsigned int *tile_counter;
-    unsigned long long *n_clusters;   // device scalars
-    unsigned long long *max_len;
-    unsigned int *err;                // bit0: halo exhausted
-};
-cudaError_t launch_k1(const K1Args &a, cudaStream_t s, unsigned *grid_out);
-uint64_t k1_num_tiles(uint64_t n_own);
-
 struct K2Args {
     const lime_cluster *cl;
     uint64_t n_cl;
@@ -194,7 +180,8 @@ struct K2Args {
     uint32_t *sim32; uint32_t lo, hi;
     unsigned int *carry;              // set to 1 when a packed add carried out of its byte
     unsigned long long *large_count;  // block-path work list
-    unsigned long long *large_list;
+    unsigned long long *large_list;   // indices into cl (cluster-list path) ...
+    const lime_cluster *long_recs;    // ... or, when non-null, the records themselves (fused path)
     unsigned long long *large_next;   // ticket for the block path
     unsigned long long *n_updates;    // statistics
     uint8_t *scratch; uint64_t scratch_per_cta;
@@ -205,6 +192,32 @@ uint64_t k2_block_scratch_bytes();
 int k2_block_grid();
 cudaError_t launch_k2_narrow(const uint32_t *sim32, uint32_t lo, uint32_t hi, uint32_t n_refs,
                              uint8_t *sim8, uint64_t pitch8, cudaStream_t s);
+
+// fused steps 1 + 2a (k12_fused.cu)
+struct K12Args {
+    const uint32_t *lcp, *da;
+    const uint8_t *ebwt;              // null in DA-only mode
+    uint64_t n_own, n_total, pos_base;
+    int is_last;
+    uint32_t alpha, n_reads, n_refs;
+    lime_cluster *out;                // EMIT: records in ascending pStart order
+    uint64_t out_cap;
+    unsigned long long *tile_state;   // EMIT: look-back descriptors
+    unsigned int *tile_counter;       // EMIT: tile tickets
+    unsigned long long *n_clusters;   // device scalars
+    unsigned long long *max_len;
+    unsigned int *err;                // bit0: halo exhausted
+    lime_cluster *long_list;          // clusters the window path does not take
+    unsigned long long *long_count;
+    uint64_t long_cap;
+    uint8_t *sim8; uint64_t pitch8;   // packed uint8 accumulator
+    uint32_t *sim32; uint32_t lo, hi; // exact 32-bit accumulator for reads [lo, hi)
+    unsigned int *carry;
+    unsigned long long *n_updates;
+};
+cudaError_t launch_k12(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s);
+uint64_t k12_num_tiles(uint64_t n_own);
+uint64_t k12_long_cap(uint64_t n_total);
 
 struct K3Args {
     const uint8_t *sim8; uint64_t pitch8;

@@ -17,79 +17,18 @@
 // every add inspects the returned old word and raises a flag; the host then reruns the pass into
 // exact 32-bit cells (reduced mod 256 afterwards), which is the reference's wrap semantics.
 #include "common.cuh"
+#include "score.cuh"
 
 namespace lime {
 namespace k2 {
 
-// symbol -> class, ClusterBWT_DA.cpp:455-470; every unlisted byte is class 0 (operator[] default)
-__constant__ uint8_t c_class[256];
-
-// ---- scoring -----------------------------------------------------------------------------------
-// count vectors are 16 uint8 packed little-endian into a uint4 (class c = byte c&3 of word c>>2)
-
-// no IUPAC class (4..14) present on either side: t = sum_c min(R[c], G[c])  (:133-144)
-__device__ __forceinline__ uint32_t score_plain(const uint4 &R, const uint4 &G)
-{
-    return __vsadu4(__vminu4(R.x, G.x), 0u) + __vsadu4(__vminu4(R.y, G.y), 0u) +
-           __vsadu4(__vminu4(R.z, G.z), 0u) + __vsadu4(__vminu4(R.w, G.w), 0u);
-}
-
-__device__ __forceinline__ uint32_t byte_of(const uint4 &v, int c)
-{
-    const uint32_t w = (c >> 2) == 0 ? v.x : (c >> 2) == 1 ? v.y : (c >> 2) == 2 ? v.z : v.w;
-    return (w >> ((c & 3) * 8)) & 0xffu;
-}
-
-// class a (4..14) compatible with base i (0..3), ClusterBWT_DA.cpp:472-487, as bit i of entry a
-__device__ __forceinline__ constexpr unsigned compat_bits(int a)
-{
-    return a == 4 ? 0x5u : a == 5 ? 0xau : a == 6 ? 0x6u : a == 7 ? 0x9u : a == 8 ? 0xcu :
-           a == 9 ? 0x3u : a == 10 ? 0xeu : a == 11 ? 0xdu : a == 12 ? 0xbu : a == 13 ? 0x7u :
-           a == 14 ? 0xfu : 0u;
-}
-
-// full matcher incl. the IUPAC cross loop (:146-177).  In the "genome IUPAC vs read base" branch
-// the reference zeroes one operand before subtracting it from the other (:153-154, :158-159), so
-// the other operand keeps its value; t wraps as uint8 (:131), taken mod 256 by the caller.
-__device__ uint32_t score_iupac(const uint4 &R, const uint4 &G)
-{
-    uint32_t rr[16], gg[16], t = 0;
-#pragma unroll
-    for (int c = 0; c < 16; c++) {
-        const uint32_t r = byte_of(R, c), g = byte_of(G, c);
-        if (r > g) { t += g; rr[c] = r - g; gg[c] = 0; }
-        else       { t += r; gg[c] = g - r; rr[c] = 0; }
-    }
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-#pragma unroll
-        for (int a = 4; a < 15; a++) {
-            if (!((compat_bits(a) >> i) & 1u)) continue;
-            if (gg[a] > 0) {
-                if (gg[a] > rr[i]) { t += rr[i]; rr[i] = 0; }
-                else               { t += gg[a]; gg[a] = 0; }
-            }
-            if (rr[a] > 0) {
-                if (rr[a] > gg[i]) { t += gg[i]; rr[a] -= gg[i]; gg[i] = 0; }
-                else               { t += rr[a]; gg[i] -= rr[a]; rr[a] = 0; }
-            }
-        }
-    }
-    return t;
-}
-
-// ---- accumulator update ----------------------------------------------------------------------
 template <bool EXACT32>
 __device__ __forceinline__ void sim_add(const K2Args &P, uint32_t r, uint32_t g, uint32_t t)
 {
-    if (EXACT32) {
-        if (r >= P.lo && r < P.hi) atomicAdd(&P.sim32[(size_t)(r - P.lo) * P.n_refs + g], t);
-    } else {
-        unsigned *w = reinterpret_cast<unsigned *>(P.sim8 + (size_t)r * P.pitch8) + (g >> 2);
-        const unsigned sh = (g & 3u) * 8u;
-        const unsigned old = atomicAdd(w, t << sh);
-        if (((old >> sh) & 0xffu) + t > 0xffu) *P.carry = 1u;
-    }
+    SimAcc acc;
+    acc.sim8 = P.sim8; acc.pitch8 = P.pitch8; acc.sim32 = P.sim32; acc.lo = P.lo; acc.hi = P.hi;
+    acc.n_refs = P.n_refs; acc.carry = P.carry;
+    lime::sim_add<EXACT32>(acc, r, g, t);
 }
 
 // ---- warp path: clusters of <= 32 positions ---------------------------------------------------
@@ -160,7 +99,7 @@ __global__ void __launch_bounds__(WARP_THREADS) warp_kernel(K2Args P)
                 if (act) {
                     const uint64_t p = cstart + (lane - st);
                     id = __ldg(P.da + p);
-                    if (EBWT) cls = c_class[__ldg(P.ebwt + p)];
+                    if (EBWT) cls = class_of(__ldg(P.ebwt + p));
                 }
                 const bool is_read = id < P.n_reads;
                 const unsigned long long key =
@@ -242,7 +181,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS) block_kernel(K2Args P)
         __syncthreads();
         const unsigned long long item = s_item;
         if (item >= n_large) break;
-        const lime_cluster c = P.cl[P.large_list[item]];
+        const lime_cluster c = P.long_recs ? P.long_recs[item] : P.cl[P.large_list[item]];
         const uint64_t start = c.pStart - P.pos_base;
         const uint32_t len = (uint32_t)c.len;          // <= 65536, checked by the host
         uint32_t cap = 64;
@@ -259,7 +198,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS) block_kernel(K2Args P)
         // group by id: per-(id, class) counts as 16 x u16
         for (uint32_t e = tid; e < len; e += BLOCK_THREADS) {
             const uint32_t id = __ldg(P.da + start + e);
-            const uint32_t cls = EBWT ? c_class[__ldg(P.ebwt + start + e)] : 0u;
+            const uint32_t cls = EBWT ? class_of(__ldg(P.ebwt + start + e)) : 0u;
             uint32_t h = hash32(id) & mask;
             while (true) {
                 uint32_t k = __ldcg(&keys[h]);
@@ -332,23 +271,6 @@ __global__ void narrow_kernel(const uint32_t *sim32, uint32_t lo, uint32_t hi, u
     }
 }
 
-static bool g_class_uploaded[64] = {false};
-
-static cudaError_t upload_class_table()
-{
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev >= 0 && dev < 64 && g_class_uploaded[dev]) return cudaSuccess;
-    uint8_t t[256];
-    for (int i = 0; i < 256; i++) t[i] = 0;
-    const char *sym = "ACGTRYSWKMBDHVN";
-    for (int c = 0; c < 15; c++) t[(uint8_t)sym[c]] = (uint8_t)c;
-    t[0] = 15;
-    cudaError_t e = cudaMemcpyToSymbol(c_class, t, 256);
-    if (e == cudaSuccess && dev >= 0 && dev < 64) g_class_uploaded[dev] = true;
-    return e;
-}
-
 } // namespace k2
 
 uint64_t k2_block_scratch_bytes() { return k2::SCRATCH_BYTES; }
@@ -356,8 +278,6 @@ int k2_block_grid() { return 148 * 2; }
 
 cudaError_t launch_k2_warp(const K2Args &a, bool exact32, cudaStream_t s)
 {
-    cudaError_t e = k2::upload_class_table();
-    if (e != cudaSuccess) return e;
     if (a.n_cl == 0) return cudaSuccess;
     const uint64_t chunks = (a.n_cl + 31) / 32;
     const uint64_t want = (chunks + k2::WARPS - 1) / k2::WARPS;
@@ -372,8 +292,6 @@ cudaError_t launch_k2_warp(const K2Args &a, bool exact32, cudaStream_t s)
 
 cudaError_t launch_k2_block(const K2Args &a, bool exact32, cudaStream_t s, int grid)
 {
-    cudaError_t e = k2::upload_class_table();
-    if (e != cudaSuccess) return e;
     const bool ebwt = a.ebwt != nullptr;
     if (ebwt && !exact32)       k2::block_kernel<true, false><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);
     else if (ebwt && exact32)   k2::block_kernel<true, true><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);

@@ -43,7 +43,7 @@ void lime_destroy(lime_ctx *ctx)
     cudaStreamSynchronize(ctx->stream);
     for (auto &p : ctx->prof_events) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     DevBuf *bufs[] = {&ctx->in_lcp, &ctx->in_da, &ctx->in_ebwt, &ctx->clusters, &ctx->tile_state,
-                      &ctx->scalars, &ctx->sim_own, &ctx->sim32, &ctx->large_list, &ctx->k2_scratch,
+                      &ctx->scalars, &ctx->sim_own, &ctx->sim32, &ctx->large_list, &ctx->long_recs, &ctx->k2_scratch,
                       &ctx->row_counts, &ctx->cls_out, &ctx->tax_tables};
     for (DevBuf *b : bufs) b->release();
     for (auto &s : ctx->slots) { s.bin.release(); s.pos.release(); }
@@ -125,7 +125,7 @@ int lime_cluster_detect(lime_ctx *ctx, uint32_t alpha, uint64_t *n_clusters, uin
     if (!ctx->loaded) return fail(ctx, LIME_ERR_STATE, "lime_cluster_detect: nothing loaded");
     CK(cudaSetDevice(ctx->device), "cudaSetDevice");
     const uint64_t n_total = ctx->n_own + ctx->n_halo;
-    const uint64_t tiles = k1_num_tiles(ctx->n_own);
+    const uint64_t tiles = k12_num_tiles(ctx->n_own);
     CK(ctx->tile_state.reserve(std::max<uint64_t>(tiles, 1) * 8), "cudaMalloc tile state");
     // capacity guess: mixed clusters are a few percent of the positions; retry once when short
     uint64_t cap = std::max<uint64_t>(ctx->cl_cap, std::max<uint64_t>(1024, n_total / 8));
@@ -135,10 +135,10 @@ int lime_cluster_detect(lime_ctx *ctx, uint32_t alpha, uint64_t *n_clusters, uin
         ctx->cl_cap = ctx->clusters.cap / sizeof(lime_cluster);
         CK(cudaMemsetAsync(ctx->scalars.p, 0, sizeof(unsigned long long) * SC_COUNT, ctx->stream), "memset scalars");
         CK(cudaMemsetAsync(ctx->tile_state.p, 0, std::max<uint64_t>(tiles, 1) * 8, ctx->stream), "memset tile state");
-        K1Args a;
-        a.lcp = ctx->d_lcp; a.da = ctx->d_da;
+        K12Args a = {};
+        a.lcp = ctx->d_lcp; a.da = ctx->d_da; a.ebwt = nullptr;
         a.n_own = ctx->n_own; a.n_total = n_total; a.pos_base = ctx->pos_base; a.is_last = ctx->is_last;
-        a.alpha = alpha; a.n_reads = ctx->n_reads;
+        a.alpha = alpha; a.n_reads = ctx->n_reads; a.n_refs = ctx->n_refs;
         a.out = ctx->clusters.as<lime_cluster>(); a.out_cap = ctx->cl_cap;
         a.tile_state = ctx->tile_state.as<unsigned long long>();
         a.tile_counter = scalar<unsigned int>(ctx, SC_TILE_COUNTER);
@@ -147,7 +147,7 @@ int lime_cluster_detect(lime_ctx *ctx, uint32_t alpha, uint64_t *n_clusters, uin
         a.err = scalar<unsigned int>(ctx, SC_ERR);
         if (tiles) {
             LaunchScope ls(ctx, KID_K1_DETECT);
-            CK(launch_k1(a, ctx->stream, nullptr), "k1_detect launch");
+            CK(launch_k12(a, false, true, false, ctx->stream), "k1_detect launch");
         }
         CK(cudaMemcpyAsync(host_sc, ctx->scalars.p, sizeof(host_sc), cudaMemcpyDeviceToHost, ctx->stream), "D2H scalars");
         CK(cudaStreamSynchronize(ctx->stream), "k1_detect");

@@ -16,6 +16,7 @@ static int run_k2_pass(lime_ctx *ctx, bool ebwt, bool exact32, uint32_t lo, uint
     a.large_next = scalar<unsigned long long>(ctx, SC_LARGE_NEXT);
     a.n_updates = scalar<unsigned long long>(ctx, SC_NUPDATES);
     a.large_list = ctx->large_list.as<unsigned long long>();
+    a.long_recs = nullptr;
     a.scratch = ctx->k2_scratch.as<uint8_t>(); a.scratch_per_cta = k2_block_scratch_bytes();
     CK(cudaMemsetAsync(ctx->scalars.p, 0, sizeof(unsigned long long) * SC_COUNT, ctx->stream), "memset scalars");
     {
@@ -26,6 +27,131 @@ static int run_k2_pass(lime_ctx *ctx, bool ebwt, bool exact32, uint32_t lo, uint
         LaunchScope ls(ctx, KID_K2_BLOCK);
         CK(launch_k2_block(a, exact32, ctx->stream, k2_block_grid()), "k2_block launch");
     }
+    return LIME_OK;
+}
+
+// one fused pass (steps 1 + 2a) plus the block path over the clusters it set aside
+static int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, bool exact32, uint32_t lo, uint32_t hi,
+                        unsigned long long sc[SC_COUNT])
+{
+    const uint64_t n_total = ctx->n_own + ctx->n_halo;
+    K12Args a;
+    a.lcp = ctx->d_lcp; a.da = ctx->d_da; a.ebwt = ebwt ? ctx->d_ebwt : nullptr;
+    a.n_own = ctx->n_own; a.n_total = n_total; a.pos_base = ctx->pos_base; a.is_last = ctx->is_last;
+    a.alpha = alpha; a.n_reads = ctx->n_reads; a.n_refs = ctx->n_refs;
+    a.out = ctx->clusters.as<lime_cluster>(); a.out_cap = emit ? ctx->cl_cap : 0;
+    a.tile_state = ctx->tile_state.as<unsigned long long>();
+    a.tile_counter = scalar<unsigned int>(ctx, SC_TILE_COUNTER);
+    a.n_clusters = scalar<unsigned long long>(ctx, SC_NCLUSTERS);
+    a.max_len = scalar<unsigned long long>(ctx, SC_MAXLEN);
+    a.err = scalar<unsigned int>(ctx, SC_ERR);
+    a.long_list = ctx->long_recs.as<lime_cluster>();
+    a.long_count = scalar<unsigned long long>(ctx, SC_LARGE_COUNT);
+    a.long_cap = ctx->long_recs.cap / sizeof(lime_cluster);
+    a.sim8 = ctx->d_sim; a.pitch8 = ctx->sim_pitch;
+    a.sim32 = ctx->sim32.as<uint32_t>(); a.lo = lo; a.hi = hi;
+    a.carry = scalar<unsigned int>(ctx, SC_CARRY);
+    a.n_updates = scalar<unsigned long long>(ctx, SC_NUPDATES);
+    const uint64_t tiles = k12_num_tiles(ctx->n_own);
+    CK(cudaMemsetAsync(ctx->scalars.p, 0, sizeof(unsigned long long) * SC_COUNT, ctx->stream), "memset scalars");
+    if (emit) CK(cudaMemsetAsync(ctx->tile_state.p, 0, std::max<uint64_t>(tiles, 1) * 8, ctx->stream), "memset tile state");
+    if (tiles) {
+        LaunchScope ls(ctx, KID_K12_FUSED);
+        CK(launch_k12(a, true, emit, exact32, ctx->stream), "k12_fused launch");
+    }
+    CK(cudaMemcpyAsync(sc, ctx->scalars.p, sizeof(unsigned long long) * SC_COUNT, cudaMemcpyDeviceToHost, ctx->stream), "D2H scalars");
+    CK(cudaStreamSynchronize(ctx->stream), "k12_fused");
+    if ((unsigned)sc[SC_ERR] & 1u)
+        return fail(ctx, LIME_ERR_HALO, "lime_cluster_similarity: a cluster runs past the halo of this shard");
+    if (sc[SC_MAXLEN] > LIME_SIZE_MAX_BUF)                       // ClusterBWT_DA.cpp:558-562
+        return fail(ctx, LIME_ERR_MAXLEN, "maximum cluster size is greater than sizeMaxBuf");
+    if (sc[SC_LARGE_COUNT] > a.long_cap)
+        return fail(ctx, LIME_ERR_NOMEM, "lime_cluster_similarity: long-cluster list overflow");
+    if (sc[SC_LARGE_COUNT]) {
+        K2Args b;
+        b.cl = nullptr; b.n_cl = 0; b.da = ctx->d_da; b.ebwt = a.ebwt;
+        b.pos_base = ctx->pos_base; b.n_reads = ctx->n_reads; b.n_refs = ctx->n_refs;
+        b.sim8 = a.sim8; b.pitch8 = a.pitch8; b.sim32 = a.sim32; b.lo = lo; b.hi = hi;
+        b.carry = a.carry; b.large_count = a.long_count; b.large_list = nullptr; b.long_recs = a.long_list;
+        b.large_next = scalar<unsigned long long>(ctx, SC_LARGE_NEXT);
+        b.n_updates = a.n_updates;
+        b.scratch = ctx->k2_scratch.as<uint8_t>(); b.scratch_per_cta = k2_block_scratch_bytes();
+        {
+            LaunchScope ls(ctx, KID_K2_BLOCK);
+            CK(launch_k2_block(b, exact32, ctx->stream, k2_block_grid()), "k2_block launch");
+        }
+        unsigned long long sc2[SC_COUNT];
+        CK(cudaMemcpyAsync(sc2, ctx->scalars.p, sizeof(sc2), cudaMemcpyDeviceToHost, ctx->stream), "D2H scalars");
+        CK(cudaStreamSynchronize(ctx->stream), "k2_block");
+        sc[SC_CARRY] = sc2[SC_CARRY]; sc[SC_NUPDATES] = sc2[SC_NUPDATES];
+    }
+    return LIME_OK;
+}
+
+extern "C" int lime_cluster_similarity(lime_ctx *ctx, uint32_t alpha, int ebwt_mode, int keep_clusters,
+                                       uint64_t *n_clusters, uint64_t *max_len)
+{
+    if (!ctx) return LIME_ERR_ARG;
+    if (!ctx->loaded) return fail(ctx, LIME_ERR_STATE, "lime_cluster_similarity: nothing loaded");
+    if (ctx->sim_done) return fail(ctx, LIME_ERR_STATE, "lime_cluster_similarity: already accumulated for this load");
+    if (ebwt_mode && !ctx->d_ebwt) return fail(ctx, LIME_ERR_ARG, "lime_cluster_similarity: EBWT mode needs the ebwt array");
+    CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+    const uint64_t n_total = ctx->n_own + ctx->n_halo;
+    const uint64_t tiles = k12_num_tiles(ctx->n_own);
+    for (int i = 0; i < 4; i++) ctx->sim_stats[i] = 0;
+    ctx->have_clusters = false;
+    CK(ctx->long_recs.reserve(k12_long_cap(n_total) * sizeof(lime_cluster)), "cudaMalloc long-cluster list");
+    CK(ctx->k2_scratch.reserve(k2_block_scratch_bytes() * (uint64_t)k2_block_grid()), "cudaMalloc block-path scratch");
+    const bool emit = keep_clusters != 0;
+    if (emit) {
+        CK(ctx->tile_state.reserve(std::max<uint64_t>(tiles, 1) * 8), "cudaMalloc tile state");
+        const uint64_t cap = std::max<uint64_t>(ctx->cl_cap, std::max<uint64_t>(1024, n_total / 8));
+        CK(ctx->clusters.reserve(cap * sizeof(lime_cluster)), "cudaMalloc clusters");
+        ctx->cl_cap = ctx->clusters.cap / sizeof(lime_cluster);
+    }
+    unsigned long long sc[SC_COUNT];
+    ctx->sim_done = true;
+    int rc = run_k12_pass(ctx, alpha, ebwt_mode != 0, emit, false, 0, 0, sc);
+    if (rc) return rc;
+    const uint64_t n_cl = sc[SC_NCLUSTERS], mx = sc[SC_MAXLEN];
+    ctx->sim_stats[1] = sc[SC_LARGE_COUNT];
+    ctx->sim_stats[0] = n_cl - sc[SC_LARGE_COUNT];
+    ctx->sim_stats[2] = sc[SC_NUPDATES];
+    ctx->n_clusters = n_cl; ctx->max_len = mx; ctx->alpha = alpha;
+    if (n_clusters) *n_clusters = n_cl;
+    if (max_len) *max_len = mx;
+    if (emit) {
+        if (n_cl > ctx->cl_cap) {
+            // the records did not fit the first guess: produce them with a detection-only pass
+            const bool was_done = ctx->sim_done;
+            rc = lime_cluster_detect(ctx, alpha, nullptr, nullptr);
+            ctx->sim_done = was_done;
+            if (rc) return rc;
+        }
+        ctx->have_clusters = true;
+    }
+    if (((unsigned)sc[SC_CARRY]) == 0) return LIME_OK;
+
+    // A packed add carried out of its byte: redo the pass into exact 32-bit cells, a band of reads
+    // at a time, and store the sums mod 256 (uint8 wrap of SimArray_, ClusterBWT_DA.cpp:183,247).
+    ctx->sim_stats[3] = 1;
+    const uint64_t budget = 8ull << 30;
+    uint64_t band = std::max<uint64_t>(1, budget / ((uint64_t)ctx->n_refs * 4));
+    band = std::min<uint64_t>(band, ctx->n_reads);
+    CK(ctx->sim32.reserve(band * ctx->n_refs * 4), "cudaMalloc exact accumulator");
+    CK(cudaMemsetAsync(ctx->d_sim, 0, ctx->sim_rows * ctx->sim_pitch, ctx->stream), "memset similarity matrix");
+    for (uint64_t lo = 0; lo < ctx->n_reads; lo += band) {
+        const uint64_t hi = std::min<uint64_t>(lo + band, ctx->n_reads);
+        CK(cudaMemsetAsync(ctx->sim32.p, 0, (hi - lo) * ctx->n_refs * 4, ctx->stream), "memset exact accumulator");
+        rc = run_k12_pass(ctx, alpha, ebwt_mode != 0, false, true, (uint32_t)lo, (uint32_t)hi, sc);
+        if (rc) return rc;
+        {
+            LaunchScope ls(ctx, KID_K2_NARROW);
+            CK(launch_k2_narrow(ctx->sim32.as<uint32_t>(), (uint32_t)lo, (uint32_t)hi, ctx->n_refs,
+                                ctx->d_sim, ctx->sim_pitch, ctx->stream), "k2_narrow launch");
+        }
+    }
+    CK(cudaStreamSynchronize(ctx->stream), "k12 exact pass");
     return LIME_OK;
 }
 

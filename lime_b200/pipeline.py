@@ -15,25 +15,30 @@ def norm_of(read_len, alpha):
     return ((int(read_len) & 0xFF) + 1 - int(alpha)) & 0xFFFFFFFF
 
 
-def run_strand(ctx, slot, strand, n_reads, n_refs, read_len, alpha, beta, ebwt_mode, mem=MEM_HOST):
-    """Steps 1 and 2 of one strand into strand slot `slot`.
+def run_strand(ctx, slot, strand, n_reads, n_refs, read_len, alpha, beta, ebwt_mode, mem=MEM_HOST,
+               fused=True, keep_clusters=False):
+    """Steps 1 and 2 of one strand into strand slot `slot` (fused: one pass over the inputs,
+    the cluster list is not materialised unless keep_clusters).
 
     strand: dict with lcp, da, ebwt (numpy arrays for MEM_HOST, device pointers for MEM_DEVICE)
     and n (positions).  Returns (n_clusters, max_len, n_records)."""
     ebwt = strand.get("ebwt") if ebwt_mode else None
     ctx.load(strand["lcp"], strand["da"], ebwt, n_reads, n_refs, mem=mem, n_total=strand["n"])
-    n_cl, max_len = ctx.cluster_detect(alpha)
-    ctx.similarity(ebwt_mode)
+    if fused:
+        n_cl, max_len = ctx.cluster_similarity(alpha, ebwt_mode, keep_clusters)
+    else:
+        n_cl, max_len = ctx.cluster_detect(alpha)
+        ctx.similarity(ebwt_mode)
     n_rec = ctx.choose(slot, norm_of(read_len, alpha), beta)
     return n_cl, max_len, n_rec
 
 
 def run_job(ctx, strands, n_reads, n_refs, read_len, alpha, beta, ebwt_mode, v_corRef, m_corRef=None,
-            tax_rank=1, higher=False, mem=MEM_HOST):
+            tax_rank=1, higher=False, mem=MEM_HOST, fused=True):
     """A whole single-end (2 strands) or paired-end (4 strands) job: steps 1-2 per strand, then
     step 3.  Returns ((type u8, taxid u32, sim f32) per read, per-strand stats)."""
     assert len(strands) in (2, 4)            # Classify.cpp:334-338
-    stats = [run_strand(ctx, s, st, n_reads, n_refs, read_len, alpha, beta, ebwt_mode, mem)
+    stats = [run_strand(ctx, s, st, n_reads, n_refs, read_len, alpha, beta, ebwt_mode, mem, fused)
              for s, st in enumerate(strands)]
     out = ctx.classify(len(strands), n_refs, v_corRef, m_corRef, tax_rank, higher)
     return out, stats

@@ -17,20 +17,33 @@ def ctx():
     c.close()
 
 
-def _check_case(ctx, oracle, case, alpha, ebwt_mode, beta=0.25):
+def _check_case(ctx, oracle, case, alpha, ebwt_mode, beta=0.25, fused=False, keep=True):
+    """fused=False: lime_cluster_detect + lime_similarity (cluster list in between);
+    fused=True: lime_cluster_similarity (one pass, records kept only when keep)."""
+    from lime_b200.api import LimeError
     ebwt = case["ebwt"] if ebwt_mode else None
     ctx.load(case["lcp"], case["da"], ebwt, case["n_reads"], case["n_refs"])
-    n_cl, max_len = ctx.cluster_detect(alpha)
     cl_o, max_o = oracle.cluster_detect(case["lcp"], case["da"], case["n_reads"], alpha)
-    assert (n_cl, max_len) == (cl_o.shape[0], max_o), case["name"]
-    assert np.array_equal(ctx.clusters(), cl_o), case["name"]
-    if max_len > 65536:
-        from lime_b200.api import LimeError
-        with pytest.raises(LimeError) as e:
-            ctx.similarity(ebwt_mode)
-        assert e.value.code == -3
-        return None
-    ctx.similarity(ebwt_mode)
+    if fused:
+        if max_o > 65536:
+            with pytest.raises(LimeError) as e:
+                ctx.cluster_similarity(alpha, ebwt_mode, keep)
+            assert e.value.code == -3
+            return None
+        n_cl, max_len = ctx.cluster_similarity(alpha, ebwt_mode, keep)
+        assert (n_cl, max_len) == (cl_o.shape[0], max_o), case["name"]
+        if keep:
+            assert np.array_equal(ctx.clusters(), cl_o), case["name"]
+    else:
+        n_cl, max_len = ctx.cluster_detect(alpha)
+        assert (n_cl, max_len) == (cl_o.shape[0], max_o), case["name"]
+        assert np.array_equal(ctx.clusters(), cl_o), case["name"]
+        if max_len > 65536:
+            with pytest.raises(LimeError) as e:
+                ctx.similarity(ebwt_mode)
+            assert e.value.code == -3
+            return None
+        ctx.similarity(ebwt_mode)
     sim_o = oracle.similarity(cl_o, case["da"], ebwt, case["n_reads"], case["n_refs"])
     sim = ctx.sim_matrix()
     assert np.array_equal(sim, sim_o), (case["name"], alpha, ebwt_mode, ctx.sim_stats())
@@ -46,22 +59,97 @@ def _check_case(ctx, oracle, case, alpha, ebwt_mode, beta=0.25):
 
 @pytest.mark.parametrize("alpha", [8, 16])
 @pytest.mark.parametrize("ebwt_mode", [1, 0])
-def test_steps_1_2_match_oracle(ctx, oracle, corpus, alpha, ebwt_mode):
+@pytest.mark.parametrize("fused", [False, True])
+def test_steps_1_2_match_oracle(ctx, oracle, corpus, alpha, ebwt_mode, fused):
     saw_exact = False
     for case in corpus:
-        st = _check_case(ctx, oracle, case, alpha, ebwt_mode, beta=0.0 if case["name"] == "wrap" else 0.25)
+        st = _check_case(ctx, oracle, case, alpha, ebwt_mode, beta=0.0 if case["name"] == "wrap" else 0.25,
+                         fused=fused, keep=(alpha == 16))
         if st and st["exact_pass"]:
             saw_exact = True
     assert saw_exact          # the wrap case must have exercised the exact 32-bit pass
 
 
-def test_medium_synthetic(ctx, oracle):
+@pytest.mark.parametrize("fused", [False, True])
+def test_medium_synthetic(ctx, oracle, fused):
     case = C.synth_case("synth_medium", 6_000_000, 30_000, 40, seed=31, p_long=2e-5, max_seg=60000)
     for alpha in (12, 16):
-        st = _check_case(ctx, oracle, case, alpha, 1)
+        st = _check_case(ctx, oracle, case, alpha, 1, fused=fused)
         assert st["warp_clusters"] > 0
-    st = _check_case(ctx, oracle, case, 12, 0)
+    st = _check_case(ctx, oracle, case, 12, 0, fused=fused, keep=False)
     assert st["block_clusters"] > 0
+
+
+@pytest.mark.parametrize("ebwt_mode", [1, 0])
+def test_fused_tile_boundaries(ctx, oracle, ebwt_mode):
+    """Many clusters of 20..400 positions: they straddle the 4096-position tiles, exceed the
+    32-lane window and the 128-position look-ahead of the fused kernel in every combination."""
+    case = C.synth_case("synth_longish", 1_500_000, 4000, 9, seed=41, p_long=2e-2, max_seg=1424)
+    for alpha in (12, 14):
+        st = _check_case(ctx, oracle, case, alpha, ebwt_mode, fused=True)
+        assert st["block_clusters"] > 100 and st["warp_clusters"] > 1000
+
+
+def test_fused_adversarial_layouts(ctx, oracle):
+    """Hand-made head patterns around tile (4096) / word (32) / look-ahead (128) boundaries."""
+    rng = np.random.default_rng(5)
+    n, n_reads, n_refs = 3 * 4096 + 77, 50, 4
+    for trial in range(12):
+        lcp = np.full(n, 20, np.uint32)
+        heads = set([0])
+        for b in (4096, 8192, 12288):
+            for off in rng.integers(-140, 140, size=6):
+                heads.add(int(min(max(b + off, 0), n - 1)))
+        for h in rng.integers(0, n, size=[0, 40, 400, 3000][trial % 4]):
+            heads.add(int(h))
+        if trial % 3 == 0:
+            heads |= set(range(4096 - 3, 4096 + 3)) | set(range(8192 + 120, 8192 + 135))
+        lcp[sorted(heads)] = 3
+        if trial == 11:
+            lcp[0] = 20                       # leading run without a head (A2)
+        da = rng.integers(0, n_reads + n_refs, size=n).astype(np.uint32)
+        if trial % 2:
+            da[rng.random(n) < 0.97] = 0      # mostly one read: mixed only where a genome shows up
+        ebwt = np.frombuffer(bytes(rng.choice(list(b"ACGTN\0R$"), size=n).tolist()), dtype=np.uint8).copy()
+        case = dict(name=f"adv{trial}", lcp=lcp, da=da, ebwt=ebwt, n_reads=n_reads, n_refs=n_refs, read_len=100)
+        _check_case(ctx, oracle, case, 16, 1, beta=0.0, fused=True)
+        _check_case(ctx, oracle, case, 16, 0, beta=0.0, fused=True, keep=False)
+
+
+def test_sharded_loads_union_equals_whole(ctx, oracle):
+    """Position shards with a halo (lime_load n_own / n_halo / pos_base / is_last): the clusters of
+    the shards are a partition of the whole array's clusters and the matrices add up mod 256."""
+    from lime_b200.api import LimeError
+    case = C.synth_case("synth_shard", 900_000, 3000, 6, seed=43, p_long=1e-3, max_seg=700)
+    lcp, da, ebwt = case["lcp"], case["da"], case["ebwt"]
+    n = lcp.shape[0]
+    alpha = 14
+    cl_o, max_o = oracle.cluster_detect(lcp, da, case["n_reads"], alpha)
+    sim_o = oracle.similarity(cl_o, da, ebwt, case["n_reads"], case["n_refs"])
+    cuts = [0, 300_001, 300_001 + 4096 * 50, n]
+    halo = 4096
+    cls, total, mx = [], np.zeros_like(sim_o, dtype=np.uint32), 0
+    for k in range(3):
+        a, b = cuts[k], cuts[k + 1]
+        h = min(halo, n - b)
+        sl = slice(a, b + h)
+        ctx.load(lcp[sl], da[sl], ebwt[sl], case["n_reads"], case["n_refs"], n_own=b - a, n_halo=h,
+                 pos_base=a, is_last=(k == 2))
+        n_cl, max_len = ctx.cluster_similarity(alpha, 1, True)
+        cls.append(ctx.clusters()); mx = max(mx, max_len)
+        total += ctx.sim_matrix()
+    got = np.concatenate(cls)
+    assert np.array_equal(got, cl_o) and mx == max_o
+    assert np.array_equal((total & 0xFF).astype(np.uint8), sim_o)
+    # a halo that is too short for a straddling cluster is an error, not a silent truncation
+    big = np.where(cl_o["len"] > 200)[0]
+    c = cl_o[big[len(big) // 2]]
+    cut = int(c["pStart"]) + 50
+    ctx.load(lcp[:cut + 20], da[:cut + 20], ebwt[:cut + 20], case["n_reads"], case["n_refs"], n_own=cut, n_halo=20,
+             pos_base=0, is_last=False)
+    with pytest.raises(LimeError) as e:
+        ctx.cluster_similarity(alpha, 1, False)
+    assert e.value.code == -4
 
 
 def test_clusters_set_any_order(ctx, oracle, corpus):
