@@ -142,10 +142,10 @@ def test_sharded_loads_union_equals_whole(ctx, oracle):
     assert np.array_equal(got, cl_o) and mx == max_o
     assert np.array_equal((total & 0xFF).astype(np.uint8), sim_o)
     # a halo that is too short for a straddling cluster is an error, not a silent truncation
-    big = np.where(cl_o["len"] > 200)[0]
-    c = cl_o[big[len(big) // 2]]
-    cut = int(c["pStart"]) + 50
-    ctx.load(lcp[:cut + 20], da[:cut + 20], ebwt[:cut + 20], case["n_reads"], case["n_refs"], n_own=cut, n_halo=20,
+    c = cl_o[int(np.argmax(cl_o["len"]))]
+    assert c["len"] >= 12
+    cut, h = int(c["pStart"]) + 3, int(c["len"] - 3) // 2
+    ctx.load(lcp[:cut + h], da[:cut + h], ebwt[:cut + h], case["n_reads"], case["n_refs"], n_own=cut, n_halo=h,
              pos_base=0, is_last=False)
     with pytest.raises(LimeError) as e:
         ctx.cluster_similarity(alpha, 1, False)
