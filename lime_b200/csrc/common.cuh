@@ -214,6 +214,7 @@ struct K12Args {
     uint32_t *sim32; uint32_t lo, hi; // exact 32-bit accumulator for reads [lo, hi)
     unsigned int *carry;
     unsigned long long *n_updates;
+    unsigned dbg;                     // experiment switches (LIME_DEBUG env), 0 in production
 };
 cudaError_t launch_k12(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s);
 uint64_t k12_num_tiles(uint64_t n_own);

@@ -41,6 +41,7 @@ constexpr int GROUPS = EXT / 4;           // 1056 groups of 4 positions
 constexpr int LOADS = (GROUPS + THREADS - 1) / THREADS;   // 5
 constexpr int NONE = 1 << 30;
 constexpr int MAXFAST = 32;               // longest cluster the window path takes
+constexpr int QCAP = 128;                 // queued similarity updates per warp
 
 // x_i |= x_{i-1} while c_i (position i continues the run of i-1); Kogge-Stone, 5 steps
 __device__ __forceinline__ uint32_t fill_up(uint32_t x, uint32_t c)
@@ -72,20 +73,21 @@ struct Smem {
     uint32_t R[WORDS + 4];        // read bitmap
     uint32_t A[WORDS + 4];        // active bitmap
     uint32_t base[WORDS + 4];     // exclusive prefix of popc(A)
-    uint32_t S[WORDS + 4];        // cluster-start bitmap of the compacted stream
     uint32_t cid[EXT];            // compacted document ids
     uint8_t  cmeta[EXT];          // compacted class | start << 4
     uint8_t  cls[256];            // symbol -> class
+    uint2    q[THREADS / 32][QCAP]; // per-warp queue of updates {read, genome << 8 | t}
     uint32_t gHas[NGRP], gUpR[NGRP], gUpG[NGRP], gDnR[NGRP], gDnG[NGRP], gCnt[NGRP];
     uint32_t wsum[THREADS / 32];
     unsigned long long wmax[THREADS / 32];
     int E, hl;
     unsigned tile, tailR, tailG, slow_r, slow_g, smin, nact;
-    unsigned long long end, excl;
+    unsigned cta_clusters, cta_updates;
+    unsigned long long end, excl, cta_maxlen;
 };
 
 template <bool SCORE, bool EMIT, bool EBWT, bool EXACT32>
-__global__ void __launch_bounds__(THREADS, 3) fused_kernel(K12Args P)
+__global__ void __launch_bounds__(THREADS, 4) fused_kernel(K12Args P)
 {
     __shared__ Smem sm;
     const int tid = threadIdx.x;
@@ -95,10 +97,10 @@ __global__ void __launch_bounds__(THREADS, 3) fused_kernel(K12Args P)
     if (tid == 0) {
         sm.tile = EMIT ? atomicAdd(P.tile_counter, 1u) : blockIdx.x;
         sm.E = NONE; sm.hl = -1; sm.tailR = 0; sm.tailG = 0;
+        sm.cta_clusters = 0; sm.cta_updates = 0; sm.cta_maxlen = 0;
     }
     if (SCORE) {
         sm.cls[tid] = d_class_table.v[tid];
-        if (tid < WORDS + 4) sm.S[tid] = 0;
     }
     __syncthreads();
     const unsigned tile = sm.tile;
@@ -349,7 +351,8 @@ __global__ void __launch_bounds__(THREADS, 3) fused_kernel(K12Args P)
             }
         }
     }
-    // tile totals -> global scalars
+    // tile totals: reduced in shared memory, ONE global atomic per CTA and scalar (same-address
+    // atomics from every warp serialise in L2 and were measured to dominate the kernel)
     {
         unsigned c = count;
         unsigned long long mx = max_len;
@@ -358,13 +361,18 @@ __global__ void __launch_bounds__(THREADS, 3) fused_kernel(K12Args P)
             c += __shfl_xor_sync(FULL, c, o);
             mx = max(mx, __shfl_xor_sync(FULL, mx, o));
         }
-        if (lane == 0) {
-            if (!EMIT && c) atomicAdd(P.n_clusters, (unsigned long long)c);
-            if (mx) atomicMax(P.max_len, mx);
+        if (lane == 0 && warp < NGRP) {
+            if (c) atomicAdd(&sm.cta_clusters, c);
+            if (mx) atomicMax(&sm.cta_maxlen, mx);
         }
     }
-    if (!SCORE) return;
     __syncthreads();
+    if (tid == 0 && !(P.dbg & 1u)) {
+        if (!EMIT && sm.cta_clusters) atomicAdd(P.n_clusters, (unsigned long long)sm.cta_clusters);
+        if (sm.cta_maxlen) atomicMax(P.max_len, sm.cta_maxlen);
+    }
+    if (!SCORE) return;
+    if (P.dbg & 8u) return;
 
     // ---- phase C: compact the active positions into a dense stream ----------------------------------
     {
@@ -408,7 +416,6 @@ __global__ void __launch_bounds__(THREADS, 3) fused_kernel(K12Args P)
                         const uint32_t cl = EBWT ? sm.cls[(Eb[k] >> (8 * e)) & 0xffu] : 0u;
                         sm.cid[o] = d[e];
                         sm.cmeta[o] = (uint8_t)(cl | (st << 4));
-                        if (st) atomicOr(&sm.S[o >> 5], 1u << (o & 31));
                         o++;
                     }
                 }
@@ -419,7 +426,7 @@ __global__ void __launch_bounds__(THREADS, 3) fused_kernel(K12Args P)
 
     // ---- phase D: score the clusters of the stream, 32-lane windows --------------------------------
     const int n_act = (int)sm.nact;
-    if (n_act == 0) return;
+    if (n_act == 0 || (P.dbg & 4u)) return;     // CTA-uniform
     SimAcc acc;
     acc.sim8 = P.sim8; acc.pitch8 = P.pitch8; acc.sim32 = P.sim32; acc.lo = P.lo; acc.hi = P.hi;
     acc.n_refs = P.n_refs; acc.carry = P.carry;
@@ -427,15 +434,49 @@ __global__ void __launch_bounds__(THREADS, 3) fused_kernel(K12Args P)
 
     // every warp takes a run of whole clusters: [first start >= warp*chunk, first start >= (warp+1)*chunk)
     auto first_start_ge = [&](int x) -> int {
-        if (x >= n_act) return n_act;
-        int wi = x >> 5;
-        uint32_t m = sm.S[wi] & (0xffffffffu << (x & 31));
-        while (m == 0) {
-            wi++;
-            if (wi * 32 >= n_act) return n_act;
-            m = sm.S[wi];
+        while (x < n_act) {
+            const int k = x + (int)lane;
+            const uint32_t m = __ballot_sync(FULL, k < n_act && (sm.cmeta[k] & 16u));
+            if (m) return x + __ffs(m) - 1;
+            x += 32;
         }
-        return min(n_act, wi * 32 + __ffs(m) - 1);
+        return n_act;
+    };
+    // Updates are queued per warp and applied in bulk so that many atomics are in flight per lane
+    // and their return values (needed for the carry check) are not waited for one by one.
+    uint2 *q = sm.q[warp];
+    int qn = 0;
+    auto drain = [&]() {
+        __syncwarp();
+        if (P.dbg & 2u) { qn = 0; return; }
+        for (int k = (int)lane; k < qn; k += 128) {
+            uint2 e[4];
+            bool on[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) { on[u] = k + 32 * u < qn; if (on[u]) e[u] = q[k + 32 * u]; }
+            if (EXACT32) {
+#pragma unroll
+                for (int u = 0; u < 4; u++) if (on[u]) sim_add<true>(acc, e[u].x, e[u].y >> 8, e[u].y & 0xffu);
+            } else {
+                unsigned old[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    if (on[u]) {
+                        const uint32_t g = e[u].y >> 8;
+                        unsigned *wp = reinterpret_cast<unsigned *>(acc.sim8 + (size_t)e[u].x * acc.pitch8) + (g >> 2);
+                        old[u] = atomicAdd(wp, (e[u].y & 0xffu) << ((g & 3u) * 8u));
+                    }
+                }
+                bool carry = false;
+#pragma unroll
+                for (int u = 0; u < 4; u++)
+                    if (on[u]) carry |= ((old[u] >> (((e[u].y >> 8) & 3u) * 8u)) & 0xffu) + (e[u].y & 0xffu) > 0xffu;
+                if (carry) *acc.carry = 1u;
+            }
+        }
+        updates += (unsigned long long)qn;
+        qn = 0;
+        __syncwarp();
     };
     const int chunk = (n_act + THREADS / 32 - 1) / (THREADS / 32);
     int i = first_start_ge((int)warp * chunk);
@@ -466,19 +507,26 @@ __global__ void __launch_bounds__(THREADS, 3) fused_kernel(K12Args P)
 
         // per-class counts of my id: popc(my group & lanes of that class)
         uint4 vec = make_uint4(0, 0, 0, 0);
-        unsigned present = EBWT ? __reduce_or_sync(FULL, act ? (1u << cls) : 0u) : 1u;
-        const bool wide = (present & ~0xfu) != 0;                          // a class beyond A,C,G,T
-        const bool iupac = (present & 0x7ff0u) != 0;
+        bool wide = false, iupac = false;
         if (!EBWT) {
             vec.x = (unsigned)__popc(mm);
         } else {
-            while (present) {
-                const int c = __ffs(present) - 1;
-                present &= present - 1;
-                const unsigned b = __ballot_sync(FULL, act && cls == (uint32_t)c);
-                const unsigned v = (unsigned)__popc(mm & b) << ((c & 3) * 8);
-                if ((c >> 2) == 0) vec.x |= v; else if ((c >> 2) == 1) vec.y |= v;
-                else if ((c >> 2) == 2) vec.z |= v; else vec.w |= v;
+            const unsigned b0 = __ballot_sync(FULL, act && cls == 0u), b1 = __ballot_sync(FULL, act && cls == 1u);
+            const unsigned b2 = __ballot_sync(FULL, act && cls == 2u), b3 = __ballot_sync(FULL, act && cls == 3u);
+            const unsigned rest = __ballot_sync(FULL, act && cls >= 4u);
+            vec.x = (unsigned)__popc(mm & b0) | ((unsigned)__popc(mm & b1) << 8) |
+                    ((unsigned)__popc(mm & b2) << 16) | ((unsigned)__popc(mm & b3) << 24);
+            wide = rest != 0;                                              // a class beyond A,C,G,T
+            if (wide) {
+                unsigned present = __reduce_or_sync(FULL, (act && cls >= 4u) ? (1u << cls) : 0u);
+                iupac = (present & 0x7ff0u) != 0;
+                while (present) {
+                    const int c = __ffs(present) - 1;
+                    present &= present - 1;
+                    const unsigned b = __ballot_sync(FULL, act && cls == (uint32_t)c);
+                    const unsigned v = (unsigned)__popc(mm & b) << ((c & 3) * 8);
+                    if ((c >> 2) == 1) vec.y |= v; else if ((c >> 2) == 2) vec.z |= v; else vec.w |= v;
+                }
             }
         }
         // reads wrap at 256 (:123,206), genomes saturate at 255 (:96-97,222-223): counts <= 32 here
@@ -495,20 +543,24 @@ __global__ void __launch_bounds__(THREADS, 3) fused_kernel(K12Args P)
                 Gv.w = __shfl_sync(FULL, vec.w, src);
             } else { Gv.y = 0; Gv.z = 0; Gv.w = 0; }
             const uint32_t gid = __shfl_sync(FULL, id, src);
+            uint32_t t = 0;
             if (gl) {
-                uint32_t t;
                 if (!EBWT) t = min(vec.x, Gv.x);
                 else if (!wide) t = score_acgt(vec.x, Gv.x);
                 else t = (iupac ? score_iupac(vec, Gv) : score_plain(vec, Gv)) & 0xffu;
-                if (t) { sim_add<EXACT32>(acc, id, gid - P.n_reads, t); updates++; }
                 gl &= gl - 1;
             }
+            if (qn + 32 > QCAP) drain();
+            const unsigned pm = __ballot_sync(FULL, t != 0);
+            if (t) q[qn + __popc(pm & lt_mask)] = make_uint2(id, ((gid - P.n_reads) << 8) | t);
+            qn += __popc(pm);
         }
         i += take;
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) updates += __shfl_xor_sync(FULL, updates, o);
-    if (lane == 0 && updates) atomicAdd(P.n_updates, updates);
+    drain();
+    if (lane == 0 && updates) atomicAdd(&sm.cta_updates, (unsigned)updates);
+    __syncthreads();
+    if (tid == 0 && sm.cta_updates && !(P.dbg & 1u)) atomicAdd(P.n_updates, (unsigned long long)sm.cta_updates);
 }
 
 } // namespace k12

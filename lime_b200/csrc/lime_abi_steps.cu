@@ -1,6 +1,7 @@
 // lime_abi_steps.cu -- ABI entry points for step 2 (similarity, choose) and instrumentation.
 #include "abi_internal.cuh"
 #include <algorithm>
+#include <cstdlib>
 #include <vector>
 
 static int run_k2_pass(lime_ctx *ctx, bool ebwt, bool exact32, uint32_t lo, uint32_t hi)
@@ -52,6 +53,7 @@ static int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, boo
     a.sim32 = ctx->sim32.as<uint32_t>(); a.lo = lo; a.hi = hi;
     a.carry = scalar<unsigned int>(ctx, SC_CARRY);
     a.n_updates = scalar<unsigned long long>(ctx, SC_NUPDATES);
+    { const char *e = getenv("LIME_DEBUG"); a.dbg = e ? (unsigned)atoi(e) : 0u; }
     const uint64_t tiles = k12_num_tiles(ctx->n_own);
     CK(cudaMemsetAsync(ctx->scalars.p, 0, sizeof(unsigned long long) * SC_COUNT, ctx->stream), "memset scalars");
     if (emit) CK(cudaMemsetAsync(ctx->tile_state.p, 0, std::max<uint64_t>(tiles, 1) * 8, ctx->stream), "memset tile state");
