@@ -151,32 +151,36 @@ __global__ void __launch_bounds__(THREADS, 4) fused_kernel(K12Args P)
     __syncthreads();
 
     // ---- phase B1: per-word segment flags (threads 0..159 own one 32-position word each) ---------
-    uint32_t H = 0xffffffffu, R = 0, G = 0, V = 0, Aw = 0;
-    uint32_t lowmask = 0, himask = 0, upR = 0, upG = 0, dnR = 0, dnG = 0;
-    uint32_t HH = 0, YR = 0, YG = 0, ZR = 0, ZG = 0;
+    // A segment holds a read and a genome iff two neighbours inside it differ in kind:
+    // X_i = (read_i != read_{i+1}) and i+1 is not a head.  One flag to spread over the segment.
+    uint32_t H = 0xffffffffu, X = 0, V = 0, Rw = 0, Aw = 0;
+    uint32_t lowmask = 0, himask = 0, upX = 0, dnX = 0;
+    uint32_t HH = 0, YX = 0, ZX = 0;
     bool hasHead = true;
     const int w = tid;
     if (warp < NGRP) {
         if (w < WORDS) {
             V = mask_lt(Lext - w * 32);
             H = sm.H[w];
-            const uint32_t r = sm.R[w];
-            R = r & V; G = ~r & V;
+            Rw = sm.R[w];
+            const uint32_t Hn = (H >> 1) | (sm.H[w + 1] << 31);
+            const uint32_t Rn = (Rw >> 1) | (sm.R[w + 1] << 31);
+            X = (Rw ^ Rn) & ~Hn & mask_lt(Lext - w * 32 - 1);
         }
         hasHead = H != 0;
         lowmask = hasHead ? ((H & (0u - H)) - 1u) : 0xffffffffu;          // below the first head
         himask = hasHead ? (0xffffffffu << (31 - __clz(H))) : 0xffffffffu; // at / above the last head
-        upR = fill_up(R, ~H); upG = fill_up(G, ~H);
-        dnR = fill_down(R, ~(H >> 1)); dnG = fill_down(G, ~(H >> 1));
+        upX = fill_up(X, ~H);
+        dnX = fill_down(X, ~(H >> 1));
         HH = __ballot_sync(FULL, hasHead);
-        const uint32_t TR = __ballot_sync(FULL, (R & himask) != 0), TG = __ballot_sync(FULL, (G & himask) != 0);
-        const uint32_t LR = __ballot_sync(FULL, (R & lowmask) != 0), LG = __ballot_sync(FULL, (G & lowmask) != 0);
-        YR = fill_up(TR, ~HH); YG = fill_up(TG, ~HH);
-        ZR = fill_down(LR, ~HH); ZG = fill_down(LG, ~HH);
+        const uint32_t TX = __ballot_sync(FULL, (X & himask) != 0);
+        const uint32_t LX = __ballot_sync(FULL, (X & lowmask) != 0);
+        YX = fill_up(TX, ~HH);
+        ZX = fill_down(LX, ~HH);
         if (lane == 0) {
             sm.gHas[warp] = HH != 0;
-            sm.gUpR[warp] = YR >> 31; sm.gUpG[warp] = YG >> 31;
-            sm.gDnR[warp] = ZR & 1u;  sm.gDnG[warp] = ZG & 1u;
+            sm.gUpR[warp] = YX >> 31;
+            sm.gDnR[warp] = ZX & 1u;
         }
         // first head at or after Lt (E), last head before Lt (hl)
         if (w < WORDS) {
@@ -191,32 +195,30 @@ __global__ void __launch_bounds__(THREADS, 4) fused_kernel(K12Args P)
     const bool open_tail = (E == NONE) && hl >= 0;
     const int owned_end = open_tail ? hl : (E == NONE ? 0 : E);
     if (warp < NGRP) {
-        uint32_t cinR = 0, cinG = 0, cdnR = 0, cdnG = 0;
+        uint32_t cin = 0, cdn = 0;
         bool hbg = false;
         for (int k = 0; k < (int)warp; k++) {
-            if (sm.gHas[k]) { cinR = sm.gUpR[k]; cinG = sm.gUpG[k]; hbg = true; }
-            else            { cinR |= sm.gUpR[k]; cinG |= sm.gUpG[k]; }
+            if (sm.gHas[k]) { cin = sm.gUpR[k]; hbg = true; }
+            else            { cin |= sm.gUpR[k]; }
         }
         for (int k = NGRP - 1; k > (int)warp; k--) {
-            if (sm.gHas[k]) { cdnR = sm.gDnR[k]; cdnG = sm.gDnG[k]; }
-            else            { cdnR |= sm.gDnR[k]; cdnG |= sm.gDnG[k]; }
+            if (sm.gHas[k]) cdn = sm.gDnR[k];
+            else            cdn |= sm.gDnR[k];
         }
         const bool none_below = (HH & lt_mask) == 0;
         const bool none_above = lane == 31 || (HH >> (lane + 1)) == 0;
-        const uint32_t ciR = (((YR << 1) >> lane) & 1u) | (none_below ? cinR : 0u);
-        const uint32_t ciG = (((YG << 1) >> lane) & 1u) | (none_below ? cinG : 0u);
-        const uint32_t cdR = (lane < 31 ? ((ZR >> (lane + 1)) & 1u) : 0u) | (none_above ? cdnR : 0u);
-        const uint32_t cdG = (lane < 31 ? ((ZG >> (lane + 1)) & 1u) : 0u) | (none_above ? cdnG : 0u);
+        const uint32_t ci = (((YX << 1) >> lane) & 1u) | (none_below ? cin : 0u);
+        const uint32_t cd = (lane < 31 ? ((ZX >> (lane + 1)) & 1u) : 0u) | (none_above ? cdn : 0u);
         const bool head_before = !none_below || hbg;
-        const uint32_t segR = upR | dnR | (ciR ? lowmask : 0u) | (cdR ? himask : 0u);
-        const uint32_t segG = upG | dnG | (ciG ? lowmask : 0u) | (cdG ? himask : 0u);
+        const uint32_t segX = upX | dnX | (ci ? lowmask : 0u) | (cd ? himask : 0u);
         const uint32_t PB = (hasHead ? ~lowmask : 0u) | (head_before ? lowmask : 0u);
-        Aw = segR & segG & PB & V & mask_lt(owned_end - w * 32);
+        Aw = segX & PB & V & mask_lt(owned_end - w * 32);
         if (w < WORDS) {
             sm.A[w] = Aw;
             if (open_tail && (hl >> 5) == w) {          // in-window part of the segment that leaves the window
-                sm.tailR = (segR >> (hl & 31)) & 1u;
-                sm.tailG = (segG >> (hl & 31)) & 1u;
+                const uint32_t mixed_in = (segX >> (hl & 31)) & 1u, kind = (Rw >> (hl & 31)) & 1u;
+                sm.tailR = mixed_in | kind;
+                sm.tailG = mixed_in | (kind ^ 1u);
             }
         }
         // a non-last shard whose last owned segment ends at the end of the buffer needs more halo
@@ -310,7 +312,14 @@ __global__ void __launch_bounds__(THREADS, 4) fused_kernel(K12Args P)
         rec_base = sm.excl + warp_off + (incl - count);
     }
     {
+        // Only the last head of a word can start a cluster longer than 32 positions (any other has
+        // a later head in the same word).  Without EMIT the lengths of the short clusters are not
+        // needed here (phase D takes their maximum), so only that head is examined.
         uint32_t hb = heads;
+        if (!EMIT && hb) {
+            const uint32_t last = 0x80000000u >> __clz(H);
+            hb = (hb & last) ? last : 0u;
+        }
         while (hb) {
             const int b = __ffs(hb) - 1;
             hb &= hb - 1;
@@ -324,7 +333,7 @@ __global__ void __launch_bounds__(THREADS, 4) fused_kernel(K12Args P)
                 j = x * 32 + __ffs(m) - 1;
             }
             const int len = j - i;
-            max_len = max(max_len, (unsigned long long)len);
+            if (EMIT || len > MAXFAST) max_len = max(max_len, (unsigned long long)len);
             if (EMIT) {
                 if (rec_base < P.out_cap)
                     *reinterpret_cast<ulonglong2 *>(&P.out[rec_base]) = make_ulonglong2(P.pos_base + a + i, (unsigned long long)len);
@@ -369,7 +378,7 @@ __global__ void __launch_bounds__(THREADS, 4) fused_kernel(K12Args P)
     __syncthreads();
     if (tid == 0 && !(P.dbg & 1u)) {
         if (!EMIT && sm.cta_clusters) atomicAdd(P.n_clusters, (unsigned long long)sm.cta_clusters);
-        if (sm.cta_maxlen) atomicMax(P.max_len, sm.cta_maxlen);
+        if (!SCORE && sm.cta_maxlen) atomicMax(P.max_len, sm.cta_maxlen);
     }
     if (!SCORE) return;
     if (P.dbg & 8u) return;
@@ -426,11 +435,15 @@ __global__ void __launch_bounds__(THREADS, 4) fused_kernel(K12Args P)
 
     // ---- phase D: score the clusters of the stream, 32-lane windows --------------------------------
     const int n_act = (int)sm.nact;
-    if (n_act == 0 || (P.dbg & 4u)) return;     // CTA-uniform
+    if (n_act == 0 || (P.dbg & 4u)) {            // CTA-uniform
+        if (tid == 0 && sm.cta_maxlen && !(P.dbg & 1u)) atomicMax(P.max_len, sm.cta_maxlen);
+        return;
+    }
     SimAcc acc;
     acc.sim8 = P.sim8; acc.pitch8 = P.pitch8; acc.sim32 = P.sim32; acc.lo = P.lo; acc.hi = P.hi;
     acc.n_refs = P.n_refs; acc.carry = P.carry;
     unsigned long long updates = 0;
+    unsigned longest = 0;                        // longest cluster this warp scored (warp-uniform)
 
     // every warp takes a run of whole clusters: [first start >= warp*chunk, first start >= (warp+1)*chunk)
     auto first_start_ge = [&](int x) -> int {
@@ -485,25 +498,25 @@ __global__ void __launch_bounds__(THREADS, 4) fused_kernel(K12Args P)
     while (i < end) {
         const int idx = i + (int)lane;
         const bool valid = idx < end;
-        const uint32_t id = valid ? sm.cid[idx] : 0u;
-        const uint32_t meta = valid ? sm.cmeta[idx] : 0u;
-        const uint32_t sb = __ballot_sync(FULL, valid && (meta & 16u));    // bit 0 is set: i is a start
+        const uint32_t id = valid ? sm.cid[idx] : 0xffffffffu;
+        const uint32_t meta = valid ? sm.cmeta[idx] : 16u;                 // lanes past the end: lone starts
+        const uint32_t sb = __ballot_sync(FULL, (meta & 16u) != 0);        // bit 0 is set: i is a start
         int take = min(32, end - i);
-        if (take == 32 && i + 32 < end && !(sm.cmeta[i + 32] & 16u)) {
+        if (end - i > 32 && !(sm.cmeta[i + 32] & 16u)) {
             const int ls = 31 - __clz(sb);                                // the last cluster is cut: leave it
             if (ls > 0) take = ls;
         }
         const bool act = (int)lane < take;
-        const int st = 31 - __clz(sb & (lt_mask | (1u << lane)));         // first lane of my cluster
-        const uint32_t later = sb & ~(lt_mask | (1u << lane));
-        const int ce = min(take, later ? __ffs(later) - 1 : 32);           // one past my cluster's last lane
-        const uint32_t cm = mask_lt(ce) & ~mask_lt(st);
+        const uint32_t le_mask = lt_mask | (1u << lane);
+        const uint32_t start_bit = 0x80000000u >> __clz(sb & le_mask);     // first lane of my cluster
+        const uint32_t later = sb & ~le_mask;
+        const uint32_t upper = (later & (0u - later)) - 1u;                // lanes below the next start (all if none)
+        const uint32_t cm = act ? (upper & ~(start_bit - 1u) & mask_lt(take)) : 0u;   // lanes of my cluster
         const uint32_t cls = meta & 15u;
         const bool is_read = id < P.n_reads;
-        const unsigned long long key =
-            act ? (((unsigned long long)st << 32) | id) : ((0xffull << 40) | lane);
-        const unsigned mm = __match_any_sync(FULL, key);                   // lanes with my (cluster, id)
-        const bool leader = act && (__ffs(mm) - 1 == (int)lane);
+        const unsigned mm = __match_any_sync(FULL, id) & cm;               // lanes with my id in my cluster
+        const bool leader = act && (mm & lt_mask) == 0;
+        longest = max(longest, __reduce_max_sync(FULL, (unsigned)__popc(cm)));
 
         // per-class counts of my id: popc(my group & lanes of that class)
         uint4 vec = make_uint4(0, 0, 0, 0);
@@ -511,8 +524,8 @@ __global__ void __launch_bounds__(THREADS, 4) fused_kernel(K12Args P)
         if (!EBWT) {
             vec.x = (unsigned)__popc(mm);
         } else {
-            const unsigned b0 = __ballot_sync(FULL, act && cls == 0u), b1 = __ballot_sync(FULL, act && cls == 1u);
-            const unsigned b2 = __ballot_sync(FULL, act && cls == 2u), b3 = __ballot_sync(FULL, act && cls == 3u);
+            const unsigned b0 = __ballot_sync(FULL, cls == 0u), b1 = __ballot_sync(FULL, cls == 1u);
+            const unsigned b2 = __ballot_sync(FULL, cls == 2u), b3 = __ballot_sync(FULL, cls == 3u);
             const unsigned rest = __ballot_sync(FULL, act && cls >= 4u);
             vec.x = (unsigned)__popc(mm & b0) | ((unsigned)__popc(mm & b1) << 8) |
                     ((unsigned)__popc(mm & b2) << 16) | ((unsigned)__popc(mm & b3) << 24);
@@ -535,21 +548,21 @@ __global__ void __launch_bounds__(THREADS, 4) fused_kernel(K12Args P)
         unsigned gl = __ballot_sync(FULL, leader && !is_read) & cm;
         if (!(leader && is_read)) gl = 0;
         while (__any_sync(FULL, gl != 0)) {
-            const int src = gl ? __ffs(gl) - 1 : 0;
-            uint4 Gv;
-            Gv.x = __shfl_sync(FULL, vec.x, src);
-            if (wide) {
+            const int src = __ffs(gl) - 1;                                 // -1 (lane 31) when idle: harmless
+            const uint32_t Gx = __shfl_sync(FULL, vec.x, src);
+            const uint32_t gid = __shfl_sync(FULL, id, src);
+            uint32_t t;
+            if (!EBWT) t = min(vec.x, Gx);
+            else if (!wide) t = score_acgt(vec.x, Gx);
+            else {
+                uint4 Gv;
+                Gv.x = Gx;
                 Gv.y = __shfl_sync(FULL, vec.y, src); Gv.z = __shfl_sync(FULL, vec.z, src);
                 Gv.w = __shfl_sync(FULL, vec.w, src);
-            } else { Gv.y = 0; Gv.z = 0; Gv.w = 0; }
-            const uint32_t gid = __shfl_sync(FULL, id, src);
-            uint32_t t = 0;
-            if (gl) {
-                if (!EBWT) t = min(vec.x, Gv.x);
-                else if (!wide) t = score_acgt(vec.x, Gv.x);
-                else t = (iupac ? score_iupac(vec, Gv) : score_plain(vec, Gv)) & 0xffu;
-                gl &= gl - 1;
+                t = (iupac ? score_iupac(vec, Gv) : score_plain(vec, Gv)) & 0xffu;
             }
+            if (gl == 0) t = 0;
+            gl &= gl - 1;
             if (qn + 32 > QCAP) drain();
             const unsigned pm = __ballot_sync(FULL, t != 0);
             if (t) q[qn + __popc(pm & lt_mask)] = make_uint2(id, ((gid - P.n_reads) << 8) | t);
@@ -558,9 +571,15 @@ __global__ void __launch_bounds__(THREADS, 4) fused_kernel(K12Args P)
         i += take;
     }
     drain();
-    if (lane == 0 && updates) atomicAdd(&sm.cta_updates, (unsigned)updates);
+    if (lane == 0) {
+        if (updates) atomicAdd(&sm.cta_updates, (unsigned)updates);
+        if (longest) atomicMax(&sm.cta_maxlen, (unsigned long long)longest);
+    }
     __syncthreads();
-    if (tid == 0 && sm.cta_updates && !(P.dbg & 1u)) atomicAdd(P.n_updates, (unsigned long long)sm.cta_updates);
+    if (tid == 0 && !(P.dbg & 1u)) {
+        if (sm.cta_updates) atomicAdd(P.n_updates, (unsigned long long)sm.cta_updates);
+        if (sm.cta_maxlen) atomicMax(P.max_len, sm.cta_maxlen);
+    }
 }
 
 } // namespace k12
