@@ -312,6 +312,7 @@ def run_ours(args, w):
                              "n_reads_total": w["n_reads"]})
         del cl
     out, stats = step_resident()          # leave the slots in a consistent state
+    out = tuple(x.copy() for x in out)    # classify() returns views of context-owned pinned buffers
     kinds = {chr(t): int((out[0] == t).sum()) for t in np.unique(out[0])}
 
     # ---- timed region: K steps, resident inputs -------------------------------------------------

@@ -56,6 +56,11 @@ const char *lime_version(void);
  * current stream so that its CUDA events bracket our kernels.  NULL restores the ctx's own stream. */
 int  lime_set_stream(lime_ctx *ctx, void *cuda_stream);
 
+/* Page-locked host memory for buffers handed to lime_load / lime_classify / the copy functions:
+ * transfers from / to it run at full PCIe rate and asynchronously.  NULL on failure. */
+void *lime_pinned_alloc(uint64_t bytes);
+void  lime_pinned_free(void *p);
+
 /* ---- inputs ------------------------------------------------------------------------------- */
 
 /*

@@ -33,6 +33,8 @@ SIGNATURES = {
     "lime_last_error": (C.c_char_p, [vp]),
     "lime_version": (C.c_char_p, []),
     "lime_set_stream": (C.c_int, [vp, vp]),
+    "lime_pinned_alloc": (vp, [C.c_uint64]),
+    "lime_pinned_free": (None, [vp]),
     "lime_load": (C.c_int, [vp, vp, vp, vp, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int,
                             C.c_uint32, C.c_uint32, C.c_int]),
     "lime_cluster_detect": (C.c_int, [vp, C.c_uint32, u64p, u64p]),

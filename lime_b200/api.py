@@ -34,8 +34,28 @@ class LimeContext:
 
     def close(self):
         if self.h:
+            for p in getattr(self, "_pinned", {}).values():
+                self.lib.lime_pinned_free(C.c_void_p(p[0]))
+            self._pinned = {}
             self.lib.lime_destroy(self.h)
             self.h = None
+
+    def pinned(self, key, shape, dtype):
+        """A page-locked numpy array owned by the context (reused per key while large enough)."""
+        self._pinned = getattr(self, "_pinned", {})
+        dtype = np.dtype(dtype)
+        nbytes = int(np.prod(shape)) * dtype.itemsize
+        ent = self._pinned.get(key)
+        if ent is None or ent[1] < nbytes:
+            if ent is not None:
+                self.lib.lime_pinned_free(C.c_void_p(ent[0]))
+            ptr = self.lib.lime_pinned_alloc(max(nbytes, 1))
+            if not ptr:
+                raise MemoryError("lime_pinned_alloc failed")
+            ent = (ptr, max(nbytes, 1))
+            self._pinned[key] = ent
+        buf = (C.c_uint8 * max(nbytes, 1)).from_address(ent[0])
+        return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
 
     def __del__(self):
         try:
@@ -160,9 +180,10 @@ class LimeContext:
         n_reads = self._slot_shape[0][1]
         v = np.ascontiguousarray(v_corRef, dtype=np.uint32)
         m = None if m_corRef is None else np.ascontiguousarray(m_corRef, dtype=np.uint32)
-        typ = np.empty(n_reads, dtype=np.uint8)
-        tax = np.empty(n_reads, dtype=np.uint32)
-        sim = np.empty(n_reads, dtype=np.float32)
+        # results land in page-locked arrays owned by the context: valid until the next classify()
+        typ = self.pinned("cls_type", (n_reads,), np.uint8)
+        tax = self.pinned("cls_tax", (n_reads,), np.uint32)
+        sim = self.pinned("cls_sim", (n_reads,), np.float32)
         self._ck(self.lib.lime_classify(self.h, n_files, n_refs, _ptr(v), _ptr(m), tax_rank,
                                         1 if higher else 0, _ptr(typ), _ptr(tax), _ptr(sim)))
         return typ, tax, sim

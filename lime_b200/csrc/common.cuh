@@ -98,6 +98,7 @@ enum KernelId {
     KID_K2_WARP,
     KID_K2_BLOCK,
     KID_K2_NARROW,
+    KID_K3_CHOOSE,
     KID_K3_COUNT,
     KID_K3_EMIT,
     KID_K3_CLASSIFY,
@@ -229,7 +230,9 @@ struct K3Args {
     unsigned long long *n_records;    // device scalar: records incl. sentinel
     uint64_t *pos;                    // [read_end-read_begin]
     lime_pair_sim *bin;               // emit only
+    uint64_t bin_cap;                 // single-pass kernel: capacity of bin (writes are guarded)
 };
+cudaError_t launch_k3_choose(const K3Args &a, cudaStream_t s);
 cudaError_t launch_k3_count(const K3Args &a, cudaStream_t s);
 cudaError_t launch_k3_emit(const K3Args &a, cudaStream_t s);
 uint64_t k3_num_tiles(uint32_t n_reads);

@@ -148,6 +148,152 @@ __global__ void __launch_bounds__(THREADS) emit_kernel(K3Args P)
     }
 }
 
+
+// ---- single pass: count, offsets (look-back) and emit in one kernel ---------------------------------
+// Used when an upper bound of the record count is known beforehand (1 + reads + similarity updates),
+// so the record buffer can be sized without a counting pass.  A row is read once from HBM; the emit
+// step re-reads the CTA's 256 rows from L1/L2.  LPR lanes share a row (16 bytes per lane and step).
+template <int LPR>
+__device__ __forceinline__ void row_stats(const uint8_t *row, uint32_t chunks, unsigned sub, bool on,
+                                          uint32_t &mx, uint32_t &nnz)
+{
+    uint32_t m = 0;
+    nnz = 0;
+    if (on) {
+        for (uint32_t c = sub; c < chunks; c += LPR) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(row) + c);
+            m = __vmaxu4(__vmaxu4(m, v.x), __vmaxu4(__vmaxu4(v.y, v.z), v.w));
+            nnz += __popc(nz_bytes(v.x)) + __popc(nz_bytes(v.y)) + __popc(nz_bytes(v.z)) + __popc(nz_bytes(v.w));
+        }
+    }
+    __syncwarp();
+    mx = max(max(m & 0xff, (m >> 8) & 0xff), max((m >> 16) & 0xff, m >> 24));
+#pragma unroll
+    for (int o = LPR / 2; o > 0; o >>= 1) {
+        mx = max(mx, __shfl_xor_sync(FULL, mx, o));
+        nnz += __shfl_xor_sync(FULL, nnz, o);
+    }
+}
+
+template <int LPR>
+__global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
+{
+    constexpr int RPW = 32 / LPR;                    // rows a warp handles per step
+    __shared__ uint32_t s_cnt[TILE_READS];
+    __shared__ uint32_t s_off[TILE_READS];
+    __shared__ uint32_t s_warp_sum[WARPS];
+    __shared__ unsigned s_tile;
+    __shared__ unsigned long long s_excl;
+    const int tid = threadIdx.x;
+    const unsigned lane = lane_id(), warp = tid >> 5;
+    const unsigned sub = lane % LPR, grp = lane / LPR;
+    if (tid == 0) s_tile = atomicAdd(P.tile_counter, 1u);
+    __syncthreads();
+    const unsigned tile = s_tile;
+    const uint32_t n = P.read_end - P.read_begin;
+    const uint32_t r0 = tile * TILE_READS;
+    const uint32_t chunks = (uint32_t)(P.pitch8 / 16);
+    const float normf = (float)P.norm;
+    if (tile == 0 && tid == 0 && P.bin_cap) { P.bin[0].sim = 0.0f; P.bin[0].idRef = 0; }   // sentinel (:376-382)
+
+    // ---- count ----
+    for (int k = 0; k < ROWS_PER_WARP; k += RPW) {
+        const uint32_t lr = r0 + warp * ROWS_PER_WARP + k + grp;
+        uint32_t mx = 0, nnz = 0;
+        row_stats<LPR>(P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8, chunks, sub, lr < n, mx, nnz);
+        if (sub == 0) {
+            const float ns = __fdiv_rn((float)mx, normf);
+            s_cnt[warp * ROWS_PER_WARP + k + grp] = (lr < n && ns > P.beta) ? 1u + nnz : 0u;
+        }
+    }
+    __syncthreads();
+    // ---- offsets ----
+    const uint32_t c = s_cnt[tid];
+    uint32_t incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(FULL, incl, o);
+        if (lane >= (unsigned)o) incl += v;
+    }
+    if (lane == 31) s_warp_sum[warp] = incl;
+    __syncthreads();
+    uint32_t warp_off = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < WARPS; w++) {
+        const uint32_t s = s_warp_sum[w];
+        if (w < (int)warp) warp_off += s;
+        total += s;
+    }
+    if (warp == 0) {
+        const unsigned long long e = lookback_exclusive(P.tile_state, tile, total);
+        if (lane == 0) {
+            s_excl = e;
+            if (tile == gridDim.x - 1) *P.n_records = 1ull + e + total;
+        }
+    }
+    s_off[tid] = warp_off + (incl - c);
+    __syncthreads();
+    const unsigned long long tile_base = 1ull + s_excl;
+    {
+        const uint32_t lr = r0 + tid;
+        if (lr < n) P.pos[lr] = c ? tile_base + s_off[tid] : 0ull;
+    }
+    // ---- emit ----
+    for (int k = 0; k < ROWS_PER_WARP; k += RPW) {
+        const int slot = warp * ROWS_PER_WARP + k + grp;
+        const uint32_t lr = r0 + slot;
+        const uint32_t cnt = s_cnt[slot];
+        const bool on = lr < n && cnt != 0;
+        const uint8_t *row = P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8;
+        const unsigned long long o = tile_base + s_off[slot];
+        uint32_t mx = 0, written = 0;
+        for (uint32_t c0 = 0; c0 < chunks; c0 += LPR) {
+            const uint32_t ch = c0 + sub;
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (on && ch < chunks) v = __ldg(reinterpret_cast<const uint4 *>(row) + ch);
+            const uint32_t wv[4] = {v.x, v.y, v.z, v.w};
+            uint32_t mine = 0;
+#pragma unroll
+            for (int x = 0; x < 4; x++) { mx = __vmaxu4(mx, wv[x]); mine += __popc(nz_bytes(wv[x])); }
+            uint32_t inc2 = mine;
+#pragma unroll
+            for (int s = 1; s < LPR; s <<= 1) {
+                const uint32_t y = __shfl_up_sync(FULL, inc2, s, LPR);
+                if (sub >= (unsigned)s) inc2 += y;
+            }
+            unsigned long long dst = o + 1 + written + (inc2 - mine);
+            if (mine) {
+#pragma unroll
+                for (int x = 0; x < 4; x++) {
+#pragma unroll
+                    for (int b = 0; b < 4; b++) {
+                        const uint32_t cell = (wv[x] >> (8 * b)) & 0xffu;
+                        if (cell) {
+                            if (dst < P.bin_cap) {
+                                lime_pair_sim rec;
+                                rec.sim = __fdiv_rn((float)cell, normf);
+                                rec.idRef = 16 * ch + 4 * x + b;
+                                P.bin[dst] = rec;
+                            }
+                            dst++;
+                        }
+                    }
+                }
+            }
+            written += __shfl_sync(FULL, inc2, LPR - 1, LPR);
+        }
+        mx = max(max(mx & 0xff, (mx >> 8) & 0xff), max((mx >> 16) & 0xff, mx >> 24));
+#pragma unroll
+        for (int s = LPR / 2; s > 0; s >>= 1) mx = max(mx, __shfl_xor_sync(FULL, mx, s));
+        if (on && sub == 0 && o < P.bin_cap) {
+            lime_pair_sim h;
+            h.sim = __fdiv_rn((float)mx, normf);
+            h.idRef = written;
+            P.bin[o] = h;
+        }
+    }
+}
+
 } // namespace k3
 
 uint64_t k3_num_tiles(uint32_t n_reads) { return ((uint64_t)n_reads + k3::TILE_READS - 1) / k3::TILE_READS; }
@@ -157,6 +303,21 @@ cudaError_t launch_k3_count(const K3Args &a, cudaStream_t s)
     const uint64_t tiles = k3_num_tiles(a.read_end - a.read_begin);
     if (tiles == 0) return cudaSuccess;
     k3::count_kernel<<<(unsigned)tiles, k3::THREADS, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_k3_choose(const K3Args &a, cudaStream_t s)
+{
+    const uint64_t tiles = k3_num_tiles(a.read_end - a.read_begin);
+    if (tiles == 0) return cudaSuccess;
+    const uint64_t chunks = a.pitch8 / 16;
+    const unsigned g = (unsigned)tiles;
+    if (chunks <= 1)       k3::choose_kernel<1><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 2)  k3::choose_kernel<2><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 4)  k3::choose_kernel<4><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 8)  k3::choose_kernel<8><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 16) k3::choose_kernel<16><<<g, k3::THREADS, 0, s>>>(a);
+    else                   k3::choose_kernel<32><<<g, k3::THREADS, 0, s>>>(a);
     return cudaGetLastError();
 }
 

@@ -59,6 +59,14 @@ int lime_set_stream(lime_ctx *ctx, void *cuda_stream)
     return LIME_OK;
 }
 
+void *lime_pinned_alloc(uint64_t bytes)
+{
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void lime_pinned_free(void *p) { if (p) cudaFreeHost(p); }
+
 uint64_t lime_sim_pitch(uint32_t n_refs) { return ((uint64_t)n_refs + 15) / 16 * 16; }
 
 int lime_sim_bind(lime_ctx *ctx, void *dev_matrix, uint64_t rows, uint64_t pitch)

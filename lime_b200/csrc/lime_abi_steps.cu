@@ -248,21 +248,39 @@ int lime_choose(lime_ctx *ctx, int slot, uint32_t norm, float beta,
     a.tile_state = ctx->tile_state.as<unsigned long long>();
     a.tile_counter = scalar<unsigned int>(ctx, SC_TILE_COUNTER);
     a.n_records = scalar<unsigned long long>(ctx, SC_NRECORDS);
-    a.pos = S.pos.as<uint64_t>(); a.bin = nullptr;
+    a.pos = S.pos.as<uint64_t>(); a.bin = nullptr; a.bin_cap = 0;
     unsigned long long total = 1;
-    if (tiles) {
+    // Every non-zero cell received at least one update, so 1 + reads + updates bounds the record
+    // count and the single-pass kernel can run without a counting pass.  Not known for a matrix
+    // bound by the caller: then count first, emit second.
+    const bool single_pass = tiles && ctx->sim_done && !ctx->sim_bound && ctx->n_refs;
+    if (single_pass) {
+        const uint64_t cells = (uint64_t)n * ctx->n_refs;
+        const uint64_t cap = 1 + (uint64_t)n + std::min<uint64_t>(ctx->sim_stats[2], cells);
+        CK(S.bin.reserve(cap * sizeof(lime_pair_sim)), "cudaMalloc records");
+        a.bin = S.bin.as<lime_pair_sim>(); a.bin_cap = S.bin.cap / sizeof(lime_pair_sim);
         {
-            LaunchScope ls(ctx, KID_K3_COUNT);
-            CK(launch_k3_count(a, ctx->stream), "k3_count launch");
+            LaunchScope ls(ctx, KID_K3_CHOOSE);
+            CK(launch_k3_choose(a, ctx->stream), "k3_choose launch");
         }
         CK(cudaMemcpyAsync(&total, a.n_records, 8, cudaMemcpyDeviceToHost, ctx->stream), "D2H record count");
-        CK(cudaStreamSynchronize(ctx->stream), "k3_count");
-    }
-    CK(S.bin.reserve(total * sizeof(lime_pair_sim)), "cudaMalloc records");
-    a.bin = S.bin.as<lime_pair_sim>();
-    {
-        LaunchScope ls(ctx, KID_K3_EMIT);
-        CK(launch_k3_emit(a, ctx->stream), "k3_emit launch");
+        CK(cudaStreamSynchronize(ctx->stream), "k3_choose");
+        if (total > a.bin_cap) return fail(ctx, LIME_ERR_STATE, "lime_choose: record bound violated");
+    } else {
+        if (tiles) {
+            {
+                LaunchScope ls(ctx, KID_K3_COUNT);
+                CK(launch_k3_count(a, ctx->stream), "k3_count launch");
+            }
+            CK(cudaMemcpyAsync(&total, a.n_records, 8, cudaMemcpyDeviceToHost, ctx->stream), "D2H record count");
+            CK(cudaStreamSynchronize(ctx->stream), "k3_count");
+        }
+        CK(S.bin.reserve(total * sizeof(lime_pair_sim)), "cudaMalloc records");
+        a.bin = S.bin.as<lime_pair_sim>();
+        {
+            LaunchScope ls(ctx, KID_K3_EMIT);
+            CK(launch_k3_emit(a, ctx->stream), "k3_emit launch");
+        }
     }
     S.n_records = total; S.read_begin = read_begin; S.n_reads = n; S.valid = true;
     if (n_records) *n_records = total;
