@@ -87,22 +87,24 @@ int lime_load(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint
 {
     if (!ctx) return LIME_ERR_ARG;
     const uint64_t n = n_own + n_halo;
-    if (n > 0 && (!lcp || !da)) return fail(ctx, LIME_ERR_ARG, "lime_load: lcp/da are NULL");
+    // lcp may be NULL when only step 2 runs from a cluster list (ClusterBWT_DA never reads .lcp)
+    if (n > 0 && !da) return fail(ctx, LIME_ERR_ARG, "lime_load: da is NULL");
     if ((uint64_t)n_reads + n_refs > 0xfffffffeull) return fail(ctx, LIME_ERR_ARG, "lime_load: too many documents");
     CK(cudaSetDevice(ctx->device), "cudaSetDevice");
     ctx->loaded = false; ctx->have_clusters = false; ctx->sim_done = false;
     if (mem == LIME_MEM_DEVICE) {
-        if ((reinterpret_cast<uintptr_t>(lcp) & 15) || (reinterpret_cast<uintptr_t>(da) & 15))
-            return fail(ctx, LIME_ERR_ARG, "lime_load: device lcp/da must be 16-byte aligned");
+        if ((reinterpret_cast<uintptr_t>(lcp) & 15) || (reinterpret_cast<uintptr_t>(da) & 15) ||
+            (reinterpret_cast<uintptr_t>(ebwt) & 3))
+            return fail(ctx, LIME_ERR_ARG, "lime_load: device lcp/da must be 16-byte aligned, ebwt 4-byte aligned");
         ctx->d_lcp = lcp; ctx->d_da = da; ctx->d_ebwt = ebwt;
     } else {
-        CK(ctx->in_lcp.reserve(std::max<uint64_t>(n, 4) * 4), "cudaMalloc lcp");
+        if (lcp || n == 0) CK(ctx->in_lcp.reserve(std::max<uint64_t>(n, 4) * 4), "cudaMalloc lcp");
         CK(ctx->in_da.reserve(std::max<uint64_t>(n, 4) * 4), "cudaMalloc da");
         if (n) {
-            CK(cudaMemcpyAsync(ctx->in_lcp.p, lcp, n * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D lcp");
+            if (lcp) CK(cudaMemcpyAsync(ctx->in_lcp.p, lcp, n * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D lcp");
             CK(cudaMemcpyAsync(ctx->in_da.p, da, n * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D da");
         }
-        ctx->d_lcp = ctx->in_lcp.as<uint32_t>(); ctx->d_da = ctx->in_da.as<uint32_t>();
+        ctx->d_lcp = (lcp || n == 0) ? ctx->in_lcp.as<uint32_t>() : nullptr; ctx->d_da = ctx->in_da.as<uint32_t>();
         ctx->d_ebwt = nullptr;
         if (ebwt) {
             CK(ctx->in_ebwt.reserve(std::max<uint64_t>(n, 16)), "cudaMalloc ebwt");
@@ -131,6 +133,7 @@ int lime_cluster_detect(lime_ctx *ctx, uint32_t alpha, uint64_t *n_clusters, uin
 {
     if (!ctx) return LIME_ERR_ARG;
     if (!ctx->loaded) return fail(ctx, LIME_ERR_STATE, "lime_cluster_detect: nothing loaded");
+    if (!ctx->d_lcp && ctx->n_own) return fail(ctx, LIME_ERR_STATE, "lime_cluster_detect: loaded without lcp");
     CK(cudaSetDevice(ctx->device), "cudaSetDevice");
     const uint64_t n_total = ctx->n_own + ctx->n_halo;
     const uint64_t tiles = k12_num_tiles(ctx->n_own);

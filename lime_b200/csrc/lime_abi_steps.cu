@@ -95,6 +95,7 @@ extern "C" int lime_cluster_similarity(lime_ctx *ctx, uint32_t alpha, int ebwt_m
 {
     if (!ctx) return LIME_ERR_ARG;
     if (!ctx->loaded) return fail(ctx, LIME_ERR_STATE, "lime_cluster_similarity: nothing loaded");
+    if (!ctx->d_lcp && ctx->n_own) return fail(ctx, LIME_ERR_STATE, "lime_cluster_similarity: loaded without lcp");
     if (ctx->sim_done) return fail(ctx, LIME_ERR_STATE, "lime_cluster_similarity: already accumulated for this load");
     if (ebwt_mode && !ctx->d_ebwt) return fail(ctx, LIME_ERR_ARG, "lime_cluster_similarity: EBWT mode needs the ebwt array");
     CK(cudaSetDevice(ctx->device), "cudaSetDevice");

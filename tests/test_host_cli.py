@@ -1,0 +1,96 @@
+"""The drop-in executables (lime_b200/host/bin) against the oracle and, where built, against the
+unmodified reference executables: same argv, same files, byte-identical outputs."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import corpus as C
+from lime_b200 import datagen
+from test_oracle_vs_reference import _random_rows
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "lime_b200", "host", "bin")
+
+
+def _run(exe, args, cwd):
+    return subprocess.run([os.path.join(BIN, exe)] + [str(a) for a in args], cwd=cwd,
+                          stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+
+
+def test_executables_are_built_and_print_the_reference_usage():
+    for exe, n in (("ClusterLCP", "fileFasta numReads numGenomes alpha threads"),
+                   ("ClusterBWT_DA", "fileFasta readLen beta threads"),
+                   ("ClusterBWT_DA_ebwt0", "fileFasta readLen beta threads"),
+                   ("Classify", "N fileInput1 fileInput2 ... fileInputN numReads numGenomes fileOutput fileTaxo taxRank numThreads"),
+                   ("Classify_higher1", "N fileInput1")):
+        r = _run(exe, [], ROOT)
+        assert r.returncode == 1 and "Error usage" in r.stderr and n in r.stderr, (exe, r.stderr)
+    r = _run("Classify", [3, "a", "b", "c", 1, 1, "o", "t", 1, 1], ROOT)
+    assert r.returncode == 1 and "allowed number of input files is 2" in r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("alpha", [8, 16])
+def test_steps_1_2_cli_files_match(tmp_path, oracle, corpus, alpha):
+    for case in corpus:
+        n = case["lcp"].shape[0]
+        if n == 0:
+            continue
+        d = tmp_path / f"{case['name']}_{alpha}"
+        d.mkdir()
+        fasta = str(d / "s+Refs.fasta")
+        datagen.write_strand(fasta, case["ebwt"], case["lcp"], case["da"])
+        r = _run("ClusterLCP", [fasta, case["n_reads"], case["n_refs"], alpha, 4], str(d))
+        assert r.returncode == 0, r.stderr
+        cl_o, max_o = oracle.cluster_detect(case["lcp"], case["da"], case["n_reads"], alpha)
+        assert open(f"{fasta}.{alpha}.clrs", "rb").read() == cl_o.tobytes(), case["name"]
+        aux = open(str(d / "s+Refs.out"), "rb").read()
+        exp = (np.array([case["n_reads"], case["n_refs"], alpha], "<u4").tobytes() +
+               np.array([max_o, cl_o.shape[0]], "<u8").tobytes())
+        assert aux == exp, case["name"]
+        assert f"Total number of clusters: {cl_o.shape[0]}." in r.stdout
+        for exe, ebwt in (("ClusterBWT_DA", True), ("ClusterBWT_DA_ebwt0", False)):
+            beta = 0.0 if case["name"] == "wrap" else 0.25
+            r = _run(exe, [fasta, case["read_len"], beta, 4], str(d))
+            if max_o > 65536:
+                assert r.returncode == 1 and "greater than sizeMaxBuf" in r.stderr
+                continue
+            assert r.returncode == 0, r.stderr
+            sim = oracle.similarity(cl_o, case["da"], case["ebwt"] if ebwt else None, case["n_reads"], case["n_refs"])
+            b, p = oracle.choose(sim, (case["read_len"] + 1 - alpha) & 0xFFFFFFFF, np.float32(beta))
+            assert open(fasta + ".res.bin", "rb").read() == b.tobytes(), (case["name"], exe)
+            assert open(fasta + ".res.pos", "rb").read() == p.tobytes(), (case["name"], exe)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_files", [2, 4])
+@pytest.mark.parametrize("higher", [False, True])
+def test_classify_cli_csv_matches(tmp_path, oracle, n_files, higher):
+    rng = np.random.default_rng(50 + n_files + 10 * higher)
+    n_reads, n_refs, tax_rank = 2000, 12, 1
+    lin = str(tmp_path / "lineage.csv")
+    with open(lin, "w", newline="") as f:
+        f.write(C.lineage_text(C.default_lineage(n_refs, holes=True, seed=3), crlf=True, trailing_blank=True))
+    stems, bins, poss = [], [], []
+    for i in range(n_files):
+        b, p = _random_rows(rng, n_reads, n_refs)
+        stem = str(tmp_path / f"strand{i}.res")
+        b.tofile(stem + ".bin"); p.tofile(stem + ".pos")
+        stems.append(stem); bins.append(b); poss.append(p)
+    out = str(tmp_path / "ours.csv")
+    r = _run("Classify_higher1" if higher else "Classify", [n_files] + stems + [n_reads, n_refs, out, lin, tax_rank, 2],
+             str(tmp_path))
+    assert r.returncode == 0, r.stderr
+    v, m, _ = oracle.fix_rank(lin, tax_rank, n_refs, higher)
+    typ, tax, sim = oracle.classify(bins, poss, n_refs, v, m, tax_rank, higher)
+    exp = str(tmp_path / "oracle.csv")
+    oracle.write_csv(exp, typ, tax, sim)
+    assert open(out, "rb").read() == open(exp, "rb").read()
+    assert f"Number of successfully classified reads: {int((typ == ord('C')).sum())}/{n_reads};" in r.stdout
+    # lineage without a final newline loses its last row -> the reference's size-mismatch exit (A15)
+    with open(lin, "w", newline="") as f:
+        f.write(C.lineage_text(C.default_lineage(n_refs), final_newline=False))
+    r = _run("Classify", [n_files] + stems + [n_reads, n_refs, out, lin, tax_rank, 2], str(tmp_path))
+    assert r.returncode == 1 and f"Number of taxIDs = {n_refs - 1}" in r.stderr
