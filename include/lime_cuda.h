@@ -136,6 +136,22 @@ int  lime_choose_copy(lime_ctx *ctx, int slot, lime_pair_sim *bin, uint64_t *pos
 int  lime_slot_set(lime_ctx *ctx, int slot, const lime_pair_sim *bin, uint64_t n_records,
                    const uint64_t *pos, uint32_t n_reads_in_slot);
 
+/* ---- multi-GPU exchange of partial similarity ------------------------------------------------ */
+
+/*
+ * With the position range sharded over GPUs every GPU accumulates a PARTIAL similarity matrix over
+ * all reads.  Reads are owned by contiguous ranges; before lime_choose the owner needs the sum.
+ * lime_sim_export writes the non-zero cells of rows [read_begin, read_end) as triples
+ * {uint32 read, uint32 genome << 8 | count} (ascending read, then genome) to DEVICE memory
+ * `dev_triples` (capacity `cap` triples, 8 bytes each) -- what is sent to the owner of that range;
+ * *n_triples is the number found (LIME_ERR_NOMEM if it exceeds cap: nothing past cap is written).
+ * lime_sim_import adds received triples (DEVICE memory) into this GPU's matrix, uint8 wrap as the
+ * reference's cell (Tools.h:68); (read, genome) keys must be unique within one call.
+ */
+int  lime_sim_export(lime_ctx *ctx, uint32_t read_begin, uint32_t read_end, void *dev_triples,
+                     uint64_t cap, uint64_t *n_triples);
+int  lime_sim_import(lime_ctx *ctx, const void *dev_triples, uint64_t n_triples);
+
 /* ---- step 3 : Classify.cpp:474-702 -------------------------------------------------------- */
 
 /*

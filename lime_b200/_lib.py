@@ -45,6 +45,8 @@ SIGNATURES = {
     "lime_sim_bind": (C.c_int, [vp, vp, C.c_uint64, C.c_uint64]),
     "lime_sim_pitch": (C.c_uint64, [C.c_uint32]),
     "lime_sim_copy": (C.c_int, [vp, vp]),
+    "lime_sim_export": (C.c_int, [vp, C.c_uint32, C.c_uint32, vp, C.c_uint64, u64p]),
+    "lime_sim_import": (C.c_int, [vp, vp, C.c_uint64]),
     "lime_choose": (C.c_int, [vp, C.c_int, C.c_uint32, C.c_float, C.c_uint32, C.c_uint32, u64p]),
     "lime_choose_copy": (C.c_int, [vp, C.c_int, vp, vp]),
     "lime_slot_set": (C.c_int, [vp, C.c_int, vp, C.c_uint64, vp, C.c_uint32]),

@@ -152,6 +152,19 @@ class LimeContext:
         self._ck(self.lib.lime_sim_copy(self.h, _ptr(out)))
         return out
 
+    # ---- multi-GPU exchange -----------------------------------------------------------------
+    def sim_export(self, read_begin, read_end, dev_ptr, cap):
+        """Non-zero cells of rows [read_begin, read_end) as triples into device memory; returns the
+        count (which may exceed cap: then nothing past cap was written and the caller retries)."""
+        n = C.c_uint64()
+        rc = self.lib.lime_sim_export(self.h, read_begin, read_end, C.c_void_p(dev_ptr) if dev_ptr else None, cap, C.byref(n))
+        if rc != 0 and rc != _lib.ERR_NOMEM:
+            self._ck(rc)
+        return int(n.value)
+
+    def sim_import(self, dev_ptr, n):
+        self._ck(self.lib.lime_sim_import(self.h, C.c_void_p(dev_ptr) if dev_ptr else None, n))
+
     def choose(self, slot, norm, beta, read_begin=0, read_end=None):
         if read_end is None:
             read_end = self.n_reads

@@ -99,6 +99,8 @@ enum KernelId {
     KID_K2_BLOCK,
     KID_K2_NARROW,
     KID_K3_CHOOSE,
+    KID_K3_EXPORT,
+    KID_K3_IMPORT,
     KID_K3_COUNT,
     KID_K3_EMIT,
     KID_K3_CLASSIFY,
@@ -233,6 +235,9 @@ struct K3Args {
     uint64_t bin_cap;                 // single-pass kernel: capacity of bin (writes are guarded)
 };
 cudaError_t launch_k3_choose(const K3Args &a, cudaStream_t s);
+cudaError_t launch_k3_export(const K3Args &a, cudaStream_t s);
+cudaError_t launch_k3_import(const lime_pair_sim *tr, uint64_t n, uint8_t *sim8, uint64_t pitch8, uint32_t n_reads,
+                             uint32_t n_refs, unsigned int *err, cudaStream_t s);
 cudaError_t launch_k3_count(const K3Args &a, cudaStream_t s);
 cudaError_t launch_k3_emit(const K3Args &a, cudaStream_t s);
 uint64_t k3_num_tiles(uint32_t n_reads);

@@ -149,6 +149,18 @@ __global__ void __launch_bounds__(THREADS) emit_kernel(K3Args P)
 }
 
 
+__global__ void import_kernel(const lime_pair_sim *tr, uint64_t n, uint8_t *sim8, uint64_t pitch8, uint32_t n_reads,
+                              uint32_t n_refs, unsigned int *err)
+{
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint2 t = __ldg(reinterpret_cast<const uint2 *>(tr) + i);
+        const uint32_t r = t.x, g = t.y >> 8;
+        if (r >= n_reads || g >= n_refs) { atomicOr(err, 1u); continue; }
+        uint8_t *cell = sim8 + (size_t)r * pitch8 + g;
+        *cell = (uint8_t)(*cell + (t.y & 0xffu));
+    }
+}
+
 // ---- single pass: count, offsets (look-back) and emit in one kernel ---------------------------------
 // Used when an upper bound of the record count is known beforehand (1 + reads + similarity updates),
 // so the record buffer can be sized without a counting pass.  A row is read once from HBM; the emit
@@ -175,9 +187,12 @@ __device__ __forceinline__ void row_stats(const uint8_t *row, uint32_t chunks, u
     }
 }
 
-template <int LPR>
+// TRIPLES: instead of .res records, export every non-zero cell of the rows as a triple
+// {read id, genome << 8 | count} (no header, no beta test) -- the multi-GPU exchange format.
+template <int LPR, bool TRIPLES>
 __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
 {
+    constexpr unsigned HDR = TRIPLES ? 0u : 1u;
     constexpr int RPW = 32 / LPR;                    // rows a warp handles per step
     __shared__ uint32_t s_cnt[TILE_READS];
     __shared__ uint32_t s_off[TILE_READS];
@@ -194,7 +209,7 @@ __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
     const uint32_t r0 = tile * TILE_READS;
     const uint32_t chunks = (uint32_t)(P.pitch8 / 16);
     const float normf = (float)P.norm;
-    if (tile == 0 && tid == 0 && P.bin_cap) { P.bin[0].sim = 0.0f; P.bin[0].idRef = 0; }   // sentinel (:376-382)
+    if (!TRIPLES && tile == 0 && tid == 0 && P.bin_cap) { P.bin[0].sim = 0.0f; P.bin[0].idRef = 0; }   // sentinel (:376-382)
 
     // ---- count ----
     for (int k = 0; k < ROWS_PER_WARP; k += RPW) {
@@ -203,7 +218,8 @@ __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
         row_stats<LPR>(P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8, chunks, sub, lr < n, mx, nnz);
         if (sub == 0) {
             const float ns = __fdiv_rn((float)mx, normf);
-            s_cnt[warp * ROWS_PER_WARP + k + grp] = (lr < n && ns > P.beta) ? 1u + nnz : 0u;
+            const bool pass = TRIPLES ? (nnz != 0) : (ns > P.beta);
+            s_cnt[warp * ROWS_PER_WARP + k + grp] = (lr < n && pass) ? HDR + nnz : 0u;
         }
     }
     __syncthreads();
@@ -228,13 +244,13 @@ __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
         const unsigned long long e = lookback_exclusive(P.tile_state, tile, total);
         if (lane == 0) {
             s_excl = e;
-            if (tile == gridDim.x - 1) *P.n_records = 1ull + e + total;
+            if (tile == gridDim.x - 1) *P.n_records = HDR + e + total;
         }
     }
     s_off[tid] = warp_off + (incl - c);
     __syncthreads();
-    const unsigned long long tile_base = 1ull + s_excl;
-    {
+    const unsigned long long tile_base = HDR + s_excl;
+    if (!TRIPLES) {
         const uint32_t lr = r0 + tid;
         if (lr < n) P.pos[lr] = c ? tile_base + s_off[tid] : 0ull;
     }
@@ -261,7 +277,7 @@ __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
                 const uint32_t y = __shfl_up_sync(FULL, inc2, s, LPR);
                 if (sub >= (unsigned)s) inc2 += y;
             }
-            unsigned long long dst = o + 1 + written + (inc2 - mine);
+            unsigned long long dst = o + HDR + written + (inc2 - mine);
             if (mine) {
 #pragma unroll
                 for (int x = 0; x < 4; x++) {
@@ -271,8 +287,13 @@ __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
                         if (cell) {
                             if (dst < P.bin_cap) {
                                 lime_pair_sim rec;
-                                rec.sim = __fdiv_rn((float)cell, normf);
-                                rec.idRef = 16 * ch + 4 * x + b;
+                                if (TRIPLES) {
+                                    rec.sim = __uint_as_float(P.read_begin + lr);
+                                    rec.idRef = ((16 * ch + 4 * x + b) << 8) | cell;
+                                } else {
+                                    rec.sim = __fdiv_rn((float)cell, normf);
+                                    rec.idRef = 16 * ch + 4 * x + b;
+                                }
                                 P.bin[dst] = rec;
                             }
                             dst++;
@@ -285,7 +306,7 @@ __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
         mx = max(max(mx & 0xff, (mx >> 8) & 0xff), max((mx >> 16) & 0xff, mx >> 24));
 #pragma unroll
         for (int s = LPR / 2; s > 0; s >>= 1) mx = max(mx, __shfl_xor_sync(FULL, mx, s));
-        if (on && sub == 0 && o < P.bin_cap) {
+        if (!TRIPLES && on && sub == 0 && o < P.bin_cap) {
             lime_pair_sim h;
             h.sim = __fdiv_rn((float)mx, normf);
             h.idRef = written;
@@ -306,18 +327,31 @@ cudaError_t launch_k3_count(const K3Args &a, cudaStream_t s)
     return cudaGetLastError();
 }
 
-cudaError_t launch_k3_choose(const K3Args &a, cudaStream_t s)
+template <bool TRIPLES>
+static cudaError_t launch_choose_t(const K3Args &a, cudaStream_t s)
 {
     const uint64_t tiles = k3_num_tiles(a.read_end - a.read_begin);
     if (tiles == 0) return cudaSuccess;
     const uint64_t chunks = a.pitch8 / 16;
     const unsigned g = (unsigned)tiles;
-    if (chunks <= 1)       k3::choose_kernel<1><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 2)  k3::choose_kernel<2><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 4)  k3::choose_kernel<4><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 8)  k3::choose_kernel<8><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 16) k3::choose_kernel<16><<<g, k3::THREADS, 0, s>>>(a);
-    else                   k3::choose_kernel<32><<<g, k3::THREADS, 0, s>>>(a);
+    if (chunks <= 1)       k3::choose_kernel<1, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 2)  k3::choose_kernel<2, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 4)  k3::choose_kernel<4, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 8)  k3::choose_kernel<8, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 16) k3::choose_kernel<16, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
+    else                   k3::choose_kernel<32, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
+    return cudaGetLastError();
+}
+cudaError_t launch_k3_choose(const K3Args &a, cudaStream_t s) { return launch_choose_t<false>(a, s); }
+cudaError_t launch_k3_export(const K3Args &a, cudaStream_t s) { return launch_choose_t<true>(a, s); }
+
+// adds triples {read, genome << 8 | count} into uint8 cells (wrapping); keys unique within one call
+cudaError_t launch_k3_import(const lime_pair_sim *tr, uint64_t n, uint8_t *sim8, uint64_t pitch8, uint32_t n_reads,
+                             uint32_t n_refs, unsigned int *err, cudaStream_t s)
+{
+    if (n == 0) return cudaSuccess;
+    const uint64_t want = (n + 255) / 256;
+    k3::import_kernel<<<(unsigned)(want < 148ull * 32 ? want : 148ull * 32), 256, 0, s>>>(tr, n, sim8, pitch8, n_reads, n_refs, err);
     return cudaGetLastError();
 }
 

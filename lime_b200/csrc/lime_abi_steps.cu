@@ -288,6 +288,60 @@ int lime_choose(lime_ctx *ctx, int slot, uint32_t norm, float beta,
     return LIME_OK;
 }
 
+int lime_sim_export(lime_ctx *ctx, uint32_t read_begin, uint32_t read_end, void *dev_triples,
+                    uint64_t cap, uint64_t *n_triples)
+{
+    if (!ctx || (!dev_triples && cap)) return LIME_ERR_ARG;
+    if (!ctx->loaded) return fail(ctx, LIME_ERR_STATE, "lime_sim_export: nothing loaded");
+    if (read_begin > read_end || read_end > ctx->sim_rows) return fail(ctx, LIME_ERR_ARG, "lime_sim_export: bad read range");
+    CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+    const uint32_t n = read_end - read_begin;
+    const uint64_t tiles = k3_num_tiles(n);
+    unsigned long long total = 0;
+    if (tiles) {
+        CK(ctx->tile_state.reserve(tiles * 8), "cudaMalloc tile state");
+        CK(cudaMemsetAsync(ctx->scalars.p, 0, sizeof(unsigned long long) * SC_COUNT, ctx->stream), "memset scalars");
+        CK(cudaMemsetAsync(ctx->tile_state.p, 0, tiles * 8, ctx->stream), "memset tile state");
+        K3Args a;
+        a.sim8 = ctx->d_sim; a.pitch8 = ctx->sim_pitch; a.n_refs = ctx->n_refs;
+        a.read_begin = read_begin; a.read_end = read_end; a.norm = 1; a.beta = 0.0f;
+        a.tile_state = ctx->tile_state.as<unsigned long long>();
+        a.tile_counter = scalar<unsigned int>(ctx, SC_TILE_COUNTER);
+        a.n_records = scalar<unsigned long long>(ctx, SC_NRECORDS);
+        a.pos = nullptr; a.bin = static_cast<lime_pair_sim *>(dev_triples); a.bin_cap = cap;
+        {
+            LaunchScope ls(ctx, KID_K3_EXPORT);
+            CK(launch_k3_export(a, ctx->stream), "k3_export launch");
+        }
+        CK(cudaMemcpyAsync(&total, a.n_records, 8, cudaMemcpyDeviceToHost, ctx->stream), "D2H triple count");
+        CK(cudaStreamSynchronize(ctx->stream), "k3_export");
+    }
+    if (n_triples) *n_triples = total;
+    if (total > cap) return fail(ctx, LIME_ERR_NOMEM, "lime_sim_export: triple buffer too small");
+    return LIME_OK;
+}
+
+int lime_sim_import(lime_ctx *ctx, const void *dev_triples, uint64_t n)
+{
+    if (!ctx || (!dev_triples && n)) return LIME_ERR_ARG;
+    if (!ctx->loaded) return fail(ctx, LIME_ERR_STATE, "lime_sim_import: nothing loaded");
+    CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+    if (n == 0) return LIME_OK;
+    CK(cudaMemsetAsync(scalar<unsigned int>(ctx, SC_ERR), 0, 4, ctx->stream), "memset err");
+    {
+        LaunchScope ls(ctx, KID_K3_IMPORT);
+        CK(launch_k3_import(static_cast<const lime_pair_sim *>(dev_triples), n, ctx->d_sim, ctx->sim_pitch,
+                            (uint32_t)std::min<uint64_t>(ctx->sim_rows, 0xffffffffull), ctx->n_refs,
+                            scalar<unsigned int>(ctx, SC_ERR), ctx->stream), "k3_import launch");
+    }
+    unsigned err = 0;
+    CK(cudaMemcpyAsync(&err, scalar<unsigned int>(ctx, SC_ERR), 4, cudaMemcpyDeviceToHost, ctx->stream), "D2H err");
+    CK(cudaStreamSynchronize(ctx->stream), "k3_import");
+    if (err & 1u) return fail(ctx, LIME_ERR_ARG, "lime_sim_import: triple outside the matrix");
+    ctx->sim_stats[2] += n;            // keeps the record bound of lime_choose valid
+    return LIME_OK;
+}
+
 int lime_choose_copy(lime_ctx *ctx, int slot, lime_pair_sim *bin, uint64_t *pos)
 {
     if (!ctx || slot < 0 || slot >= LIME_MAXFILES) return LIME_ERR_ARG;
