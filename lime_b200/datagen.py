@@ -110,7 +110,7 @@ def _geom_table(torch, p, kmax, device):
 
 def synth_arrays(n, n_reads, n_refs, read_len, seed=20261104, alpha_min=12, p_long=1e-5,
                  trlcp=None, terminator=0x24, device="cpu", chunk=1 << 25, p_mixed=0.35,
-                 max_seg=60000, lo=0, hi=None):
+                 max_seg=60000, lo=0, hi=None, read_frac=None):
     """Directly synthesise (ebwt u8, lcp i32, da i32) torch tensors of n positions on `device`.
 
     Segment lengths: P(L=1)=0.5, else 2+Geometric(1/6); with probability p_long uniform in
@@ -122,13 +122,15 @@ def synth_arrays(n, n_reads, n_refs, read_len, seed=20261104, alpha_min=12, p_lo
     ebwt: segment-dominant base w.p. 0.9 else uniform ACGT, N w.p. 1e-4, other IUPAC w.p. 1e-6 on
     genome positions, terminator byte w.p. (n_reads+n_refs)/n.
     int32 views are bit-identical to the uint32 file format (all values < 2^31).
+    read_frac: share of read positions (default n_reads*(read_len+1)/n); set it when the id range
+    n_reads belongs to a larger job than these n positions (a shard of a multi-GPU run).
     lo / hi: return only positions [lo, hi) of the n-position model (every value is a function
     of (seed, position, segment), so a window equals the same slice of the full arrays).
     """
     import torch
     dev = torch.device(device)
     I64 = torch.int64
-    f_r = min(0.95, n_reads * (read_len + 1) / float(n))
+    f_r = min(0.95, n_reads * (read_len + 1) / float(n)) if read_frac is None else float(read_frac)
     q_m = min(0.8, max(0.2, f_r))
     x_r = f_r - p_mixed * q_m                      # reads-only share
     x_r = min(max(x_r, 0.0), 1.0 - p_mixed)
@@ -173,7 +175,7 @@ def synth_arrays(n, n_reads, n_refs, read_len, seed=20261104, alpha_min=12, p_lo
     geo08 = _geom_table(torch, 0.08, 512, dev)
     acgt = torch.tensor([65, 67, 71, 84], dtype=torch.uint8, device=dev)
     iupac = torch.tensor([ord(c) for c in "RYSWKMBDHV"], dtype=torch.uint8, device=dev)
-    thr_term = int(min(0.5, (n_reads + n_refs) / float(n)) * T32)
+    thr_term = int(min(0.5, (f_r / (read_len + 1)) + n_refs / float(n)) * T32)
     reads_per_home = (n_reads + n_refs - 1) // n_refs
 
     for a in range(lo, hi, chunk):

@@ -1,0 +1,201 @@
+"""Position-sharded multi-GPU driver of the LiME hot path (one process per GPU, torch.distributed).
+
+Sharding (north_star):
+  * every strand's position range is cut into contiguous shards, one per rank; a cluster belongs
+    to the shard that holds its head -- the thread-chunk rule of ClusterLCP.cpp:150-202 -- so each
+    rank also needs the first `halo` positions of the next shard (the "run past the chunk end" of
+    :246-264).  `exchange_halo` moves them rank k+1 -> rank k (point to point over NVLink);
+  * each rank accumulates a PARTIAL similarity matrix over all reads from its positions
+    (lime_cluster_similarity);
+  * reads are owned by contiguous ranges; the non-zero cells of the other ranks' ranges leave as
+    (read, genome, count) triples (lime_sim_export), are routed by read owner with ONE all-to-all
+    (NCCL over NVLink / NVSwitch) and added on arrival (lime_sim_import, uint8 wrap = the
+    reference's cell, so sum-then-wrap equals the single-GPU result);
+  * the owner runs clusterChoose and, after all strands, Classify on its read range; the
+    assignments are gathered.
+nClusters / maxLen are the reference's reduction(+) / reduction(max) (ClusterLCP.cpp:140): one
+all-reduce each.
+
+The compute goes through a small backend object so that the same host logic runs on CUDA
+(`CudaBackend`, the C ABI) and, in the CPU tests (gloo, world size 2), on a checker backend.
+"""
+import numpy as np
+
+from .pipeline import norm_of
+
+
+def read_ranges(n_reads, world):
+    """Contiguous read ownership: rank k owns [lo_k, hi_k)."""
+    per = (n_reads + world - 1) // world
+    return [(min(k * per, n_reads), min((k + 1) * per, n_reads)) for k in range(world)]
+
+
+def shard_ranges(n, world):
+    """Contiguous position shards of an n-position strand."""
+    per = (n + world - 1) // world
+    return [(min(k * per, n), min((k + 1) * per, n)) for k in range(world)]
+
+
+def exchange_halo(dist, rank, world, tensors, n_own, halo):
+    """tensors: 1-D torch tensors with room for n_own + halo elements.  The first `halo` owned
+    elements go to rank-1, the tail [n_own, n_own+halo) is filled from rank+1.  Returns the number
+    of halo elements this rank now holds (0 on the last rank)."""
+    reqs = []
+    for t in tensors:
+        if t is None:
+            continue
+        if rank > 0:
+            reqs.append(dist.isend(t[:halo].contiguous(), rank - 1))
+        if rank < world - 1:
+            reqs.append(dist.irecv(t[n_own:n_own + halo], rank + 1))
+    for r in reqs:
+        r.wait()
+    return halo if rank < world - 1 else 0
+
+
+class CudaBackend:
+    """The C ABI (LimeContext) behind the backend interface; exchange buffers are CUDA tensors."""
+
+    def __init__(self, ctx, torch, device):
+        self.ctx, self.torch, self.device = ctx, torch, device
+
+    def load(self, lcp, da, ebwt, n_own, n_halo, pos_base, is_last, n_reads, n_refs):
+        from ._lib import MEM_DEVICE
+        self._keep = (lcp, da, ebwt)
+        self.ctx.load(lcp.data_ptr(), da.data_ptr(), ebwt.data_ptr() if ebwt is not None else None, n_reads, n_refs,
+                      n_own=n_own, n_halo=n_halo, pos_base=pos_base, is_last=is_last, mem=MEM_DEVICE,
+                      n_total=n_own + n_halo)
+
+    def cluster_similarity(self, alpha, ebwt_mode):
+        return self.ctx.cluster_similarity(alpha, ebwt_mode, False)
+
+    def updates(self):
+        return int(self.ctx.sim_stats()["updates"])
+
+    def new_buffer(self, n):
+        return self.torch.empty(max(int(n), 1), dtype=self.torch.int64, device=self.device)
+
+    def export(self, lo, hi, buf, offset):
+        return self.ctx.sim_export(lo, hi, buf.data_ptr() + 8 * offset, buf.numel() - offset)
+
+    def import_(self, buf, offset, n):
+        self.ctx.sim_import(buf.data_ptr() + 8 * offset, n)
+
+    def choose(self, slot, norm, beta, lo, hi):
+        return self.ctx.choose(slot, norm, beta, lo, hi)
+
+    def classify(self, n_files, n_refs, v, m, tax_rank, higher):
+        return self.ctx.classify(n_files, n_refs, v, m, tax_rank, higher)
+
+
+class ShardedJob:
+    """One classification job (2 or 4 strands) over `world` ranks.
+
+        job = ShardedJob(dist, torch, backend, rank, world, n_reads, n_refs)
+        for s, shard in enumerate(strands):           # this rank's shard of every strand
+            job.run_strand(s, shard, alpha, beta, ebwt_mode, read_len)
+        typ, tax, sim = job.finish(v, m, tax_rank, higher)      # all reads, on every rank
+    """
+
+    def __init__(self, dist, torch, backend, rank, world, n_reads, n_refs, timer=None):
+        self.dist, self.torch, self.be = dist, torch, backend
+        self.rank, self.world = rank, world
+        self.n_reads, self.n_refs = n_reads, n_refs
+        self.ranges = read_ranges(n_reads, world)
+        self.lo, self.hi = self.ranges[rank]
+        self.timer = timer or (lambda name: _NoTimer())
+        self.sendbuf = self.recvbuf = None
+        self.stats = []
+        self.n_strands = 0
+
+    def _cpu_or_dev(self, values):
+        t = self.torch.tensor(values, dtype=self.torch.int64)
+        dev = getattr(self.be, "device", None)
+        return t.to(dev) if dev is not None else t
+
+    def run_strand(self, slot, shard, alpha, beta, ebwt_mode, read_len):
+        """shard: dict(lcp, da, ebwt, n_own, n_halo, pos_base, is_last) -- halo already in place."""
+        be, dist, torch = self.be, self.dist, self.torch
+        with self.timer("compute"):
+            be.load(shard["lcp"], shard["da"], shard["ebwt"] if ebwt_mode else None, shard["n_own"], shard["n_halo"],
+                    shard["pos_base"], shard["is_last"], self.n_reads, self.n_refs)
+            n_cl, max_len = be.cluster_similarity(alpha, ebwt_mode)
+        # ---- export: non-zero cells of the other owners' read ranges, in destination order -----------
+        with self.timer("export"):
+            need = be.updates()                      # every non-zero cell received >= 1 update
+            if self.sendbuf is None or self.sendbuf.numel() < need:
+                self.sendbuf = be.new_buffer(need)
+            send_counts, off = [], 0
+            for dst, (lo, hi) in enumerate(self.ranges):
+                n = 0
+                if dst != self.rank and hi > lo:
+                    n = be.export(lo, hi, self.sendbuf, off)
+                    assert off + n <= self.sendbuf.numel(), "triple bound violated"
+                send_counts.append(n)
+                off += n
+        # ---- route by read owner: counts, then ONE all-to-all of the triples --------------------------
+        with self.timer("all_to_all"):
+            sc = self._cpu_or_dev(send_counts)
+            rc = torch.empty_like(sc)
+            dist.all_to_all_single(rc, sc)
+            recv_counts = [int(x) for x in rc.tolist()]
+            total_in = sum(recv_counts)
+            if self.recvbuf is None or self.recvbuf.numel() < max(total_in, 1):
+                self.recvbuf = be.new_buffer(total_in)
+            dist.all_to_all_single(self.recvbuf[:total_in], self.sendbuf[:off], recv_counts, send_counts)
+        # ---- merge on the owner: one source at a time (keys are unique within a source) --------------
+        with self.timer("import"):
+            o = 0
+            for src, n in enumerate(recv_counts):
+                if n:
+                    be.import_(self.recvbuf, o, n)
+                o += n
+        with self.timer("choose"):
+            n_rec = be.choose(slot, norm_of(read_len, alpha), beta, self.lo, self.hi)
+        # ---- scalars of <stem>.out: reduction(+:nClusters) reduction(max:maxLen), ClusterLCP.cpp:140 ---
+        with self.timer("scalars"):
+            s = self._cpu_or_dev([n_cl])
+            mx = self._cpu_or_dev([max_len])
+            dist.all_reduce(s, op=dist.ReduceOp.SUM)
+            dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        self.stats.append({"n_clusters": int(s.item()), "max_len": int(mx.item()), "n_records_local": int(n_rec),
+                           "triples_sent": int(off), "triples_received": int(total_in)})
+        self.n_strands = max(self.n_strands, slot + 1)
+        return self.stats[-1]
+
+    def finish(self, v, m=None, tax_rank=1, higher=False, gather=True):
+        """Classify on the owned read range, then gather: every rank returns all reads' results."""
+        torch, dist = self.torch, self.dist
+        with self.timer("classify"):
+            typ, tax, sim = self.be.classify(self.n_strands, self.n_refs, v, m, tax_rank, higher)
+        if not gather or self.world == 1:
+            return np.array(typ), np.array(tax), np.array(sim)
+        with self.timer("gather"):
+            per = self.ranges[0][1] - self.ranges[0][0]
+            dev = getattr(self.be, "device", None)
+            pack = np.zeros((per, 3), dtype=np.int32)            # type | taxid | sim bits, one row per read
+            k = self.hi - self.lo
+            pack[:k, 0] = typ
+            pack[:k, 1] = np.asarray(tax).view(np.int32)
+            pack[:k, 2] = np.asarray(sim).view(np.int32)
+            mine = torch.from_numpy(pack)
+            if dev is not None:
+                mine = mine.to(dev)
+            parts = [torch.empty_like(mine) for _ in range(self.world)]
+            dist.all_gather(parts, mine)
+            out = torch.cat(parts).cpu().numpy()
+        T = np.empty(self.n_reads, np.uint8); X = np.empty(self.n_reads, np.uint32); S = np.empty(self.n_reads, np.float32)
+        for r, (lo, hi) in enumerate(self.ranges):
+            blk = out[r * per:r * per + (hi - lo)]
+            T[lo:hi] = blk[:, 0].astype(np.uint8)
+            X[lo:hi] = blk[:, 1].view(np.uint32)
+            S[lo:hi] = blk[:, 2].view(np.float32)
+        return T, X, S
+
+
+class _NoTimer:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False

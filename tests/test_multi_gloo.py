@@ -1,0 +1,138 @@
+"""CPU coverage of the multi-GPU host logic (lime_b200/multi.py): world size 2 (and 3) over gloo.
+The per-rank compute is played by a checker backend built on the oracle (test infrastructure); what
+is under test is the sharding plan, the halo exchange, the routing of (read, genome, count)
+triples by read owner, the merge and the gather -- the result must equal the single-process
+oracle result on the whole arrays, bit for bit."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+import corpus as C
+
+
+class OracleBackend:
+    """Backend interface of lime_b200.multi on top of the oracle (numpy, CPU)."""
+    device = None
+
+    def __init__(self, oracle, torch):
+        self.o, self.torch = oracle, torch
+        self.slots = {}
+
+    def load(self, lcp, da, ebwt, n_own, n_halo, pos_base, is_last, n_reads, n_refs):
+        self.lcp, self.da = lcp.numpy().view(np.uint32), da.numpy().view(np.uint32)
+        self.ebwt = None if ebwt is None else ebwt.numpy()
+        self.n_own, self.n_tot, self.is_last = n_own, n_own + n_halo, is_last
+        self.n_reads, self.n_refs = n_reads, n_refs
+        self.sim = np.zeros((n_reads, n_refs), np.uint8)
+
+    def cluster_similarity(self, alpha, ebwt_mode):
+        lcp, da = self.lcp[:self.n_tot], self.da[:self.n_tot]
+        cl, _ = self.o.cluster_detect(lcp, da, self.n_reads, alpha)
+        cl = cl[cl["pStart"] < self.n_own]                      # ownership: head inside the shard
+        if not self.is_last and cl.shape[0]:
+            assert int(cl["pStart"][-1] + cl["len"][-1]) < self.n_tot, "halo too short for this test"
+        self.sim = self.o.similarity(cl, da, self.ebwt[:self.n_tot] if ebwt_mode else None, self.n_reads, self.n_refs)
+        return int(cl.shape[0]), int(cl["len"].max()) if cl.shape[0] else 0
+
+    def updates(self):
+        return int(np.count_nonzero(self.sim))
+
+    def new_buffer(self, n):
+        return self.torch.zeros(max(int(n), 1), dtype=self.torch.int64)
+
+    def export(self, lo, hi, buf, offset):
+        r, g = np.nonzero(self.sim[lo:hi])
+        c = self.sim[lo:hi][r, g].astype(np.int64)
+        packed = (r.astype(np.int64) + lo) | (((g.astype(np.int64) << 8) | c) << 32)
+        buf[offset:offset + packed.shape[0]] = self.torch.from_numpy(packed)
+        return int(packed.shape[0])
+
+    def import_(self, buf, offset, n):
+        t = buf[offset:offset + n].numpy()
+        r, y = t & 0xFFFFFFFF, t >> 32
+        keys = r * (1 << 32) + (y >> 8)
+        assert np.unique(keys).shape[0] == n                    # unique within one source
+        self.sim[r, y >> 8] = (self.sim[r, y >> 8].astype(np.int64) + (y & 0xFF)).astype(np.uint8)
+
+    def choose(self, slot, norm, beta, lo, hi):
+        self.slots[slot] = self.o.choose(self.sim[lo:hi], norm, np.float32(beta))
+        return int(self.slots[slot][0].shape[0])
+
+    def classify(self, n_files, n_refs, v, m, tax_rank, higher):
+        bins = [self.slots[i][0] for i in range(n_files)]
+        poss = [self.slots[i][1] for i in range(n_files)]
+        return self.o.classify(bins, poss, n_refs, v, m, tax_rank, higher)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, strands, n_reads, n_refs, read_len, alpha, beta, halo, v, m, q):
+    import torch
+    import torch.distributed as dist
+    from oracle.oracle import Oracle
+    from lime_b200 import multi
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    be = OracleBackend(Oracle(), torch)
+    job = multi.ShardedJob(dist, torch, be, rank, world, n_reads, n_refs)
+    for s, (ebwt, lcp, da) in enumerate(strands):
+        n = lcp.shape[0]
+        a, b = multi.shard_ranges(n, world)[rank]
+        h = halo if rank < world - 1 else 0
+        t = [torch.zeros(b - a + halo, dtype=torch.int32) for _ in range(2)] + [torch.zeros(b - a + halo, dtype=torch.uint8)]
+        t[0][:b - a] = torch.from_numpy(lcp[a:b].view(np.int32))
+        t[1][:b - a] = torch.from_numpy(da[a:b].view(np.int32))
+        t[2][:b - a] = torch.from_numpy(ebwt[a:b])
+        got = multi.exchange_halo(dist, rank, world, t, b - a, halo)
+        assert got == h
+        st = job.run_strand(s, dict(lcp=t[0], da=t[1], ebwt=t[2], n_own=b - a, n_halo=h, pos_base=a,
+                                    is_last=rank == world - 1), alpha, beta, 1, read_len)
+    typ, tax, sim = job.finish(v, m, 1, m is not None)
+    q.put((rank, typ, tax, sim, job.stats))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_job_equals_single_process(oracle, world):
+    import torch.multiprocessing as mp
+    n_reads, n_refs, read_len, alpha, beta = 1201, 9, 100, 14, 0.25
+    strands = []
+    for s in range(2):
+        c = C.synth_case(f"mg{s}", 180_001, n_reads, n_refs, seed=60 + s, p_long=1e-3, max_seg=600)
+        strands.append((c["ebwt"], c["lcp"], c["da"]))
+    v = (np.arange(n_refs, dtype=np.uint32) // 2) + 100
+    m = np.tile(np.array([[1], [2], [3], [4], [5], [6]], np.uint32), (1, n_refs))
+    # single-process oracle result
+    bins, poss, scal = [], [], []
+    for (ebwt, lcp, da) in strands:
+        cl, mx = oracle.cluster_detect(lcp, da, n_reads, alpha)
+        sim = oracle.similarity(cl, da, ebwt, n_reads, n_refs)
+        b, p = oracle.choose(sim, read_len + 1 - alpha, np.float32(beta))
+        bins.append(b); poss.append(p); scal.append((cl.shape[0], mx))
+    exp = oracle.classify(bins, poss, n_refs, v, m, 1, True)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, strands, n_reads, n_refs, read_len, alpha, beta, 2048, v, m, q))
+             for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, typ, tax, sim, stats in res:
+        assert typ.tobytes() == exp[0].tobytes() and tax.tobytes() == exp[1].tobytes() and sim.tobytes() == exp[2].tobytes()
+        for s in range(2):
+            assert (stats[s]["n_clusters"], stats[s]["max_len"]) == scal[s]
+        assert stats[0]["triples_sent"] > 0
+    assert set(chr(t) for t in exp[0]) >= {"C", "U"}
