@@ -22,6 +22,12 @@ __device__ __forceinline__ uint4 ldg128(const uint32_t *p)
     return __ldg(reinterpret_cast<const uint4 *>(p));
 }
 
+// 128-bit streaming load, evict-first in L1/L2: keeps the similarity accumulator's lines in L2
+__device__ __forceinline__ uint4 ldcs128(const uint32_t *p)
+{
+    return __ldcs(reinterpret_cast<const uint4 *>(p));
+}
+
 __device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long *p)
 {
     unsigned long long v;
@@ -221,6 +227,8 @@ struct K12Args {
 };
 cudaError_t launch_k12(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s);
 uint64_t k12_num_tiles(uint64_t n_own);
+cudaError_t launch_k12s(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s);   // k12_stream.cu
+uint64_t k12s_num_chunks(uint64_t n_own);
 uint64_t k12_long_cap(uint64_t n_total);
 
 struct K3Args {

@@ -26,6 +26,7 @@
 // Algorithmic traffic: (8 + E) bytes per position, E = 1 with ebwt; + 16 B per cluster if EMIT.
 #include "common.cuh"
 #include "score.cuh"
+#include <cstdlib>
 
 namespace lime {
 namespace k12 {
@@ -122,9 +123,9 @@ __global__ void __launch_bounds__(THREADS, 4) fused_kernel(K12Args P)
                 uint4 L;
                 Eb[k] = 0;
                 if (p + 4 <= P.n_total) {
-                    L = ldg128(P.lcp + p);
-                    D[k] = ldg128(P.da + p);
-                    if (SCORE && EBWT) Eb[k] = __ldg(reinterpret_cast<const uint32_t *>(P.ebwt + p));
+                    L = ldcs128(P.lcp + p);
+                    D[k] = ldcs128(P.da + p);
+                    if (SCORE && EBWT) Eb[k] = __ldcs(reinterpret_cast<const uint32_t *>(P.ebwt + p));
                 } else {
                     uint32_t l[4], d[4];
 #pragma unroll
@@ -472,6 +473,17 @@ __global__ void __launch_bounds__(THREADS, 4) fused_kernel(K12Args P)
                 for (int u = 0; u < 4; u++) if (on[u]) sim_add<true>(acc, e[u].x, e[u].y >> 8, e[u].y & 0xffu);
             } else {
                 unsigned old[4];
+                if (P.dbg & 16u) {                      // experiment: fire-and-forget (no carry check)
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        if (on[u]) {
+                            const uint32_t g = e[u].y >> 8;
+                            unsigned *wp = reinterpret_cast<unsigned *>(acc.sim8 + (size_t)e[u].x * acc.pitch8) + (g >> 2);
+                            atomicAdd(wp, (e[u].y & 0xffu) << ((g & 3u) * 8u));
+                        }
+                    }
+                    continue;
+                }
 #pragma unroll
                 for (int u = 0; u < 4; u++) {
                     if (on[u]) {
@@ -584,12 +596,20 @@ __global__ void __launch_bounds__(THREADS, 4) fused_kernel(K12Args P)
 
 } // namespace k12
 
-uint64_t k12_num_tiles(uint64_t n_own) { return (n_own + k12::TILE - 1) / k12::TILE; }
+static bool use_tile_kernel()
+{
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("LIME_K12"); v = (e && e[0] == 't') ? 1 : 0; }
+    return v == 1;
+}
+// look-back descriptors / long-list slots: sized for the finer of the two decompositions
+uint64_t k12_num_tiles(uint64_t n_own) { return k12s_num_chunks(n_own); }
 uint64_t k12_long_cap(uint64_t n_total) { return n_total / (k12::MAXFAST + 1) + k12_num_tiles(n_total) + 16; }
 
 cudaError_t launch_k12(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s)
 {
-    const uint64_t tiles = k12_num_tiles(a.n_own);
+    if (!use_tile_kernel()) return launch_k12s(a, score, emit, exact32, s);
+    const uint64_t tiles = (a.n_own + k12::TILE - 1) / k12::TILE;
     if (tiles == 0) return cudaSuccess;
     const unsigned grid = (unsigned)tiles;
     const bool ebwt = a.ebwt != nullptr;

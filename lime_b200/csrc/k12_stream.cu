@@ -1,0 +1,546 @@
+// k12_stream.cu -- steps 1 and 2a in ONE pass over lcp / da / ebwt, warp-autonomous version:
+// alpha-cluster detection (ClusterLCP.cpp:139-283) fused with the per-cluster similarity
+// accumulation (clusterAnalyze, ClusterBWT_DA.cpp:256-358).
+//
+// A position i with lcp[i] < alpha is a "head"; a segment is [head, next head); a segment with at
+// least one da < n_reads and one da >= n_reads is an alpha-cluster.  The kernel is persistent: every
+// WARP walks over chunks of 1024 positions (32 words of 32) with a stride of 896, owns the segments
+// whose head lies in the first 896 positions (the chunk ownership rule of ClusterLCP.cpp:150-202,
+// the remaining 128 positions are look-ahead) and never synchronises with another warp:
+//
+//   phase A  lane = position inside a word: 32 coalesced loads of lcp and da, two ballots per word
+//            give the head word (lcp < alpha) and the read word (da < n_reads); lane k keeps word k.
+//            da / ebwt stay in registers.
+//   phase B  lane = word: bit-parallel segmented OR-fills (Kogge-Stone inside the word, the same
+//            routine over the 32 words through ballots) decide which positions lie in a segment
+//            that holds both a read and a genome: the "active" word.  No per-cluster loop.
+//   phase C  active positions (about a fifth of the input) are compacted from registers into the
+//            warp's shared-memory stream (id, symbol | cluster-start flag).
+//   phase D  32-lane windows slide over the stream, one lane per position: equal ids are grouped
+//            with __match_any_sync, symbol classes counted with ballots, every read leader meets
+//            every genome leader of its cluster by shuffle; updates (read, genome, t) are queued per
+//            warp and applied to the similarity matrix in bulk.
+//   Clusters longer than 32 positions or running past the look-ahead are rare; they are appended
+//   to a list that the block-path kernel of k2_similarity.cu consumes afterwards.
+//
+// Algorithmic traffic: (8 + E) bytes per position, E = 1 with ebwt; + 16 B per cluster if EMIT.
+#include "common.cuh"
+#include "score.cuh"
+#include <algorithm>
+
+namespace lime {
+namespace k12s {
+
+constexpr int WARPS = 4;                  // per CTA; warps share nothing but the class table
+constexpr int THREADS = WARPS * 32;
+constexpr int CH = 1024;                  // positions held per warp and chunk (32 words)
+constexpr int OWN = 896;                  // owned positions per chunk (28 words); 128 look-ahead
+constexpr int NONE = 1 << 30;
+constexpr int MAXFAST = 32;               // longest cluster the window path takes
+constexpr int QCAP = 128;                 // queued similarity updates per warp
+constexpr int SCAP = CH + 32;             // stream capacity incl. one window of padding
+
+// x_i |= x_{i-1} while c_i (position i continues the run of i-1); Kogge-Stone, 5 steps
+__device__ __forceinline__ uint32_t fill_up(uint32_t x, uint32_t c)
+{
+    x |= (x << 1) & c;  c &= c << 1;
+    x |= (x << 2) & c;  c &= c << 2;
+    x |= (x << 4) & c;  c &= c << 4;
+    x |= (x << 8) & c;  c &= c << 8;
+    x |= (x << 16) & c;
+    return x;
+}
+// x_i |= x_{i+1} while c_i (position i continues into i+1)
+__device__ __forceinline__ uint32_t fill_down(uint32_t x, uint32_t c)
+{
+    x |= (x >> 1) & c;  c &= c >> 1;
+    x |= (x >> 2) & c;  c &= c >> 2;
+    x |= (x >> 4) & c;  c &= c >> 4;
+    x |= (x >> 8) & c;  c &= c >> 8;
+    x |= (x >> 16) & c;
+    return x;
+}
+__device__ __forceinline__ uint32_t mask_lt(int k)   // bits [0, k), k may be <= 0 or >= 32
+{
+    return k <= 0 ? 0u : (k >= 32 ? 0xffffffffu : ((1u << k) - 1u));
+}
+
+struct WarpSmem {
+    uint4    info[32];            // per word: active, head, exclusive prefix of popc(active), -
+    uint32_t cid[SCAP];           // compacted document ids
+    uint16_t cmeta[SCAP];         // compacted symbol | start << 8
+    uint2    q[QCAP];             // queue of updates {read, genome << 8 | t}
+};
+struct Smem {
+    WarpSmem w[WARPS];
+    uint8_t  cls[256];            // symbol -> class
+};
+
+__device__ __forceinline__ void prefetch_l2(const void *p)
+{
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+
+template <bool SCORE, bool EMIT, bool EBWT, bool EXACT32>
+__global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
+{
+    __shared__ Smem sm;
+    const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    if (SCORE) {
+        for (int i = threadIdx.x; i < 256; i += THREADS) sm.cls[i] = d_class_table.v[i];
+    }
+    __syncthreads();
+    WarpSmem &ws = sm.w[warp];
+    const int w = (int)lane;                                  // the word this lane owns in phase B
+
+    const uint64_t n_chunks = (P.n_own + OWN - 1) / OWN;
+    const uint64_t stride = (uint64_t)gridDim.x * WARPS;
+    unsigned cl_count = 0;                                    // clusters counted by this lane
+    unsigned long long max_len = 0;                           // longest cluster seen by this lane
+    unsigned long long updates = 0;                           // warp-uniform
+
+    SimAcc acc;
+    acc.sim8 = P.sim8; acc.pitch8 = P.pitch8; acc.sim32 = P.sim32; acc.lo = P.lo; acc.hi = P.hi;
+    acc.n_refs = P.n_refs; acc.carry = P.carry;
+    uint2 *q = ws.q;
+    int qn = 0;
+    // Updates are queued per warp and applied in bulk so that many atomics are in flight per lane
+    // and their return values (needed for the carry check) are not waited for one by one.
+    auto drain = [&]() {
+        __syncwarp();
+        if (P.dbg & 2u) { qn = 0; return; }
+        for (int k = (int)lane; k < qn; k += 128) {
+            uint2 e[4];
+            bool on[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) { on[u] = k + 32 * u < qn; if (on[u]) e[u] = q[k + 32 * u]; }
+            if (EXACT32) {
+#pragma unroll
+                for (int u = 0; u < 4; u++) if (on[u]) sim_add<true>(acc, e[u].x, e[u].y >> 8, e[u].y & 0xffu);
+            } else {
+                unsigned old[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    if (on[u]) {
+                        const uint32_t g = e[u].y >> 8;
+                        unsigned *wp = reinterpret_cast<unsigned *>(acc.sim8 + (size_t)e[u].x * acc.pitch8) + (g >> 2);
+                        old[u] = atomicAdd(wp, (e[u].y & 0xffu) << ((g & 3u) * 8u));
+                    }
+                }
+                bool carry = false;
+#pragma unroll
+                for (int u = 0; u < 4; u++)
+                    if (on[u]) carry |= ((old[u] >> (((e[u].y >> 8) & 3u) * 8u)) & 0xffu) + (e[u].y & 0xffu) > 0xffu;
+                if (carry) *acc.carry = 1u;
+            }
+        }
+        updates += (unsigned long long)qn;
+        qn = 0;
+        __syncwarp();
+    };
+
+    for (uint64_t c = (uint64_t)blockIdx.x * WARPS + warp; c < n_chunks; c += stride) {
+        const uint64_t a = c * OWN;                                  // buffer-local start of the chunk
+        const int Lt = (int)min((uint64_t)OWN, P.n_own - a);         // owned positions
+        const int Lext = (int)min((uint64_t)CH, P.n_total - a);      // real positions in the chunk
+
+        // ---- phase A: load, head / read words ------------------------------------------------------
+        uint32_t D[32];
+        uint32_t Eb[8];
+        uint32_t H = 0, R = 0;
+        {
+            const uint32_t *pl = P.lcp + a + lane, *pd = P.da + a + lane;
+            const uint8_t *pe = P.ebwt + a + lane;
+            // pull the next chunk of this warp into L2 while this one is processed
+            if (c + stride < n_chunks) {
+                const uint64_t an = a + stride * OWN;
+                if (an + 32ull * lane < P.n_total) {
+                    prefetch_l2(P.lcp + an + 32ull * lane);
+                    prefetch_l2(P.da + an + 32ull * lane);
+                    if (SCORE && EBWT && lane < 8 && an + 128ull * lane < P.n_total) prefetch_l2(P.ebwt + an + 128ull * lane);
+                }
+            }
+            if (Lext == CH) {
+#pragma unroll
+                for (int k = 0; k < 32; k++) {
+                    const uint32_t l = __ldcs(pl + 32 * k);
+                    D[k] = __ldcs(pd + 32 * k);
+                    const uint32_t hk = __ballot_sync(FULL, l < P.alpha);
+                    const uint32_t rk = __ballot_sync(FULL, D[k] < P.n_reads);
+                    if (w == k) { H = hk; R = rk; }
+                }
+                if (SCORE && EBWT) {
+#pragma unroll
+                    for (int k = 0; k < 32; k++) {
+                        const uint32_t e = __ldcs(pe + 32 * k);
+                        if ((k & 3) == 0) Eb[k >> 2] = e; else Eb[k >> 2] |= e << (8 * (k & 3));
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < 32; k++) {
+                    const bool ok = 32 * k + (int)lane < Lext;
+                    const uint32_t l = ok ? __ldcs(pl + 32 * k) : 0u;              // virtual head
+                    D[k] = ok ? __ldcs(pd + 32 * k) : 0xffffffffu;                 // neither read nor real
+                    const uint32_t hk = __ballot_sync(FULL, l < P.alpha);
+                    const uint32_t rk = __ballot_sync(FULL, D[k] < P.n_reads);
+                    if (w == k) { H = hk; R = rk; }
+                    if (SCORE && EBWT) {
+                        const uint32_t e = ok ? (uint32_t)__ldcs(pe + 32 * k) : 0u;
+                        if ((k & 3) == 0) Eb[k >> 2] = e; else Eb[k >> 2] |= e << (8 * (k & 3));
+                    }
+                }
+            }
+        }
+
+        // ---- phase B: per-word segment flags (lane w owns word w) -------------------------------------
+        // A segment holds a read and a genome iff two neighbours inside it differ in kind:
+        // X_i = (read_i != read_{i+1}) and i+1 is not a head.  One flag to spread over the segment.
+        const uint32_t V = mask_lt(Lext - w * 32);
+        const uint32_t Hup = __shfl_down_sync(FULL, H, 1), Rup = __shfl_down_sync(FULL, R, 1);
+        const uint32_t Hn = (H >> 1) | (Hup << 31), Rn = (R >> 1) | (Rup << 31);
+        const uint32_t X = (R ^ Rn) & ~Hn & mask_lt(Lext - w * 32 - 1);   // the last position has no neighbour
+        const bool hasHead = H != 0;
+        const uint32_t lowmask = hasHead ? ((H & (0u - H)) - 1u) : 0xffffffffu;           // below the first head
+        const uint32_t himask = hasHead ? (0xffffffffu << (31 - __clz(H))) : 0xffffffffu; // at / above the last head
+        const uint32_t upX = fill_up(X, ~H);
+        const uint32_t dnX = fill_down(X, ~(H >> 1));
+        const uint32_t HH = __ballot_sync(FULL, hasHead);
+        const uint32_t TX = __ballot_sync(FULL, (X & himask) != 0);
+        const uint32_t LX = __ballot_sync(FULL, (X & lowmask) != 0);
+        const uint32_t YX = fill_up(TX, ~HH);           // bit w: the run ending at the top of word w has X
+        const uint32_t ZX = fill_down(LX, ~HH);         // bit w: the run starting at the bottom of word w has X
+        const uint32_t ci = ((YX << 1) >> lane) & 1u;
+        const uint32_t cd = lane < 31 ? ((ZX >> (lane + 1)) & 1u) : 0u;
+        const bool head_before = (HH & lt_mask) != 0;
+        const uint32_t segX = upX | dnX | (ci ? lowmask : 0u) | (cd ? himask : 0u);
+        const uint32_t PB = (hasHead ? ~lowmask : 0u) | (head_before ? lowmask : 0u);
+        // first head at or after Lt (E), last head before Lt (hl)
+        int E = NONE, hl = -1;
+        {
+            const uint32_t below_lt = mask_lt(Lt - w * 32);
+            const uint32_t he = H & ~below_lt, hb = H & below_lt;
+            const uint32_t Em = __ballot_sync(FULL, he != 0), Bm = __ballot_sync(FULL, hb != 0);
+            if (Em) {
+                const int src = __ffs(Em) - 1;
+                E = src * 32 + __ffs(__shfl_sync(FULL, he, src)) - 1;
+            }
+            if (Bm) {
+                const int src = 31 - __clz(Bm);
+                hl = src * 32 + 31 - __clz(__shfl_sync(FULL, hb, src));
+            }
+        }
+        const bool open_tail = (E == NONE) && hl >= 0;                    // warp-uniform
+        const int owned_end = open_tail ? hl : (E == NONE ? 0 : E);
+        uint32_t Aw = segX & PB & V & mask_lt(owned_end - w * 32);
+        // a non-last shard whose last owned segment ends at the end of the buffer needs more halo
+        if (lane == 0 && !P.is_last && hl >= 0 && E != NONE && E == Lext && Lext < CH) atomicOr(P.err, 1u);
+
+        // ---- phase B2 (rare): the last owned segment runs past the chunk; find its end ----------------
+        // the warp scans forward 128 positions per step (ClusterLCP.cpp:246-264)
+        bool tail_mixed = false;
+        unsigned long long tail_len = 0;
+        if (open_tail) {
+            const int src = hl >> 5;
+            const uint32_t sx = __shfl_sync(FULL, segX, src), sr = __shfl_sync(FULL, R, src);
+            const uint32_t mixed_in = (sx >> (hl & 31)) & 1u, kind = (sr >> (hl & 31)) & 1u;
+            bool acc_r = (mixed_in | kind) != 0, acc_g = (mixed_in | (kind ^ 1u)) != 0;
+            uint64_t p0 = a + CH;
+            unsigned long long end = P.n_total;
+            while (true) {
+                if (p0 >= P.n_total) {
+                    if (!P.is_last && lane == 0) atomicOr(P.err, 1u);
+                    end = P.n_total;
+                    break;
+                }
+                uint32_t l[4], d[4];
+                const uint64_t p = p0 + 4ull * lane;
+                if (p + 4 <= P.n_total) {
+                    const uint4 lv = ldg128(P.lcp + p), dv = ldg128(P.da + p);
+                    l[0] = lv.x; l[1] = lv.y; l[2] = lv.z; l[3] = lv.w;
+                    d[0] = dv.x; d[1] = dv.y; d[2] = dv.z; d[3] = dv.w;
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 4; e++) {
+                        const bool ok = p + e < P.n_total;
+                        l[e] = ok ? __ldg(P.lcp + p + e) : 0xffffffffu;
+                        d[e] = ok ? __ldg(P.da + p + e) : 0u;
+                    }
+                }
+                unsigned hn = 0;
+#pragma unroll
+                for (int e = 0; e < 4; e++) hn |= (unsigned)(l[e] < P.alpha) << e;
+                const uint32_t hm = __ballot_sync(FULL, hn != 0);
+                unsigned m = 0xffffffffu;                                // offset of the first head in this block
+                if (hm) {
+                    const int s2 = __ffs(hm) - 1;
+                    m = 4u * s2 + __ffs(__shfl_sync(FULL, hn, s2)) - 1;
+                }
+                bool r = false, g = false;
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const bool in = (4u * lane + e < m) && (p + e < P.n_total);
+                    if (in) { if (d[e] < P.n_reads) r = true; else g = true; }
+                }
+                acc_r |= __any_sync(FULL, r) != 0;
+                acc_g |= __any_sync(FULL, g) != 0;
+                if (hm) { end = p0 + m; break; }
+                p0 += 128;
+            }
+            tail_mixed = acc_r && acc_g;
+            tail_len = end - (a + (uint64_t)hl);
+        }
+
+        // ---- phase B3: the clusters owned by this chunk: count, longest, long list, records ------------
+        // position of the first head in the words above this lane's word (every owned head has one)
+        const uint32_t aboveW = lane < 31 ? (HH & (0xfffffffeu << lane)) : 0u;
+        const int xw = aboveW ? __ffs(aboveW) - 1 : 31;
+        const uint32_t Hx = __shfl_sync(FULL, H, xw);
+        const int nh_above = aboveW ? xw * 32 + __ffs(Hx) - 1 : NONE;
+        const uint32_t heads = H & Aw;                                    // heads of owned clusters
+        const bool own_tail = open_tail && tail_mixed && (hl >> 5) == w;
+        const unsigned count = __popc(heads) + (own_tail ? 1u : 0u);
+        cl_count += count;
+        if (own_tail) max_len = max(max_len, tail_len);
+
+        unsigned long long rec_base = 0;
+        if (EMIT) {
+            unsigned incl = count;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned n = __shfl_up_sync(FULL, incl, o);
+                if (lane >= (unsigned)o) incl += n;
+            }
+            const unsigned total = __shfl_sync(FULL, incl, 31);
+            const unsigned long long e = lookback_exclusive(P.tile_state, (unsigned)c, total);
+            const unsigned long long e0 = __shfl_sync(FULL, e, 0);
+            if (lane == 0 && c == n_chunks - 1) *P.n_clusters = e0 + total;
+            rec_base = e0 + (incl - count);
+            // every owned head: length to the next head, record in ascending pStart order
+            uint32_t hb = heads;
+            while (hb) {
+                const int b = __ffs(hb) - 1;
+                hb &= hb - 1;
+                const uint32_t m = H & ~((2u << b) - 1u);              // next head in this word (b < 31 or m == 0)
+                const int j = (b < 31 && m) ? w * 32 + __ffs(m) - 1 : nh_above;
+                const int len = j - (w * 32 + b);
+                max_len = max(max_len, (unsigned long long)len);
+                if (rec_base < P.out_cap)
+                    *reinterpret_cast<ulonglong2 *>(&P.out[rec_base]) = make_ulonglong2(P.pos_base + a + w * 32 + b, (unsigned long long)len);
+                rec_base++;
+            }
+            if (own_tail && rec_base < P.out_cap)
+                *reinterpret_cast<ulonglong2 *>(&P.out[rec_base]) = make_ulonglong2(P.pos_base + a + hl, tail_len);
+        }
+        if (SCORE) {
+            // Only the last head of a word can start a cluster longer than 32 positions (any other has
+            // a later head in the same word): hand those to the block path, drop them from the stream.
+            bool cand = false;
+            int ci0 = 0;
+            if (hasHead) {
+                const int b = 31 - __clz(H);
+                ci0 = w * 32 + b;
+                cand = ((heads >> b) & 1u) && (nh_above - ci0 > MAXFAST);
+            }
+            unsigned lm = __ballot_sync(FULL, cand);
+            while (lm) {                                                  // rare
+                const int src = __ffs(lm) - 1;
+                lm &= lm - 1;
+                const int i = __shfl_sync(FULL, ci0, src), j = __shfl_sync(FULL, nh_above, src);
+                if (!EMIT && w == src) max_len = max(max_len, (unsigned long long)(j - i));
+                if (lane == 0) {
+                    const unsigned long long slot = atomicAdd(P.long_count, 1ull);
+                    if (slot < P.long_cap)
+                        *reinterpret_cast<ulonglong2 *>(&P.long_list[slot]) = make_ulonglong2(P.pos_base + a + i, (unsigned long long)(j - i));
+                }
+                Aw &= ~(mask_lt(j - w * 32) & ~mask_lt(i - w * 32));
+            }
+            if (open_tail && tail_mixed && lane == 0) {
+                const unsigned long long slot = atomicAdd(P.long_count, 1ull);
+                if (slot < P.long_cap)
+                    *reinterpret_cast<ulonglong2 *>(&P.long_list[slot]) = make_ulonglong2(P.pos_base + a + hl, tail_len);
+            }
+        } else if (!EMIT) {
+            // (not instantiated: detection without records or scores)
+        }
+        if (!SCORE) continue;
+        if (P.dbg & 8u) continue;
+
+        // ---- phase C: compact the active positions into the warp's stream ------------------------------
+        int n_act;
+        {
+            const unsigned cnt = (unsigned)__popc(Aw);
+            unsigned incl = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned n = __shfl_up_sync(FULL, incl, o);
+                if (lane >= (unsigned)o) incl += n;
+            }
+            n_act = (int)__shfl_sync(FULL, incl, 31);
+            ws.info[w] = make_uint4(Aw, H, incl - cnt, 0u);
+        }
+        if (n_act == 0) continue;                                         // warp-uniform
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 32; k++) {
+            const uint4 inf = ws.info[k];
+            if (inf.x == 0u) continue;                                    // warp-uniform
+            if ((inf.x >> lane) & 1u) {
+                const uint32_t o = inf.z + __popc(inf.x & lt_mask);
+                const uint32_t sym = EBWT ? ((Eb[k >> 2] >> (8 * (k & 3))) & 0xffu) : 0u;
+                ws.cid[o] = D[k];
+                ws.cmeta[o] = (uint16_t)(sym | (((inf.y >> lane) & 1u) << 8));
+            }
+        }
+        ws.cid[n_act + lane] = 0xffffffffu;                               // one window of padding: lone starts
+        ws.cmeta[n_act + lane] = 0x100u;
+        __syncwarp();
+        if (P.dbg & 4u) continue;
+
+        // ---- phase D: score the clusters of the stream, 32-lane windows --------------------------------
+        unsigned longest = 0;                                             // warp-uniform
+        for (int i = 0; i < n_act;) {
+            uint32_t id = ws.cid[i + lane];
+            const uint32_t meta = ws.cmeta[i + lane];
+            uint32_t sb = __ballot_sync(FULL, (meta & 0x100u) != 0);      // bit 0 is set: i is a start
+            if (!(ws.cmeta[i + 32] & 0x100u)) {
+                // the last cluster of the window is cut: leave it to the next window (turn its lanes
+                // into lone starts; a cluster has at most 32 positions, so it does not start at lane 0)
+                const int ls = 31 - __clz(sb);
+                sb |= 0xffffffffu << ls;
+                if ((int)lane >= ls) id = 0xffffffffu;
+                i += ls;
+            } else {
+                i += 32;
+            }
+            const uint32_t le_mask = lt_mask | (1u << lane);
+            const uint32_t start_bit = 0x80000000u >> __clz(sb & le_mask);     // first lane of my cluster
+            const uint32_t later = sb & ~le_mask;
+            const uint32_t upper = (later & (0u - later)) - 1u;                // lanes below the next start (all if none)
+            const uint32_t cm = upper & ~(start_bit - 1u);                     // lanes of my cluster
+            const bool is_read = id < P.n_reads;
+            const unsigned mm = __match_any_sync(FULL, id) & cm;               // lanes with my id in my cluster
+            const bool leader = (mm & lt_mask) == 0;
+            longest = max(longest, __reduce_max_sync(FULL, (unsigned)__popc(cm)));
+
+            // per-class counts of my id: popc(my group & lanes of that class)
+            uint4 vec = make_uint4(0, 0, 0, 0);
+            bool wide = false, iupac = false;
+            if (!EBWT) {
+                vec.x = (unsigned)__popc(mm);
+            } else {
+                const uint32_t cls = sm.cls[meta & 0xffu];
+                const unsigned c0 = __ballot_sync(FULL, (cls & 1u) != 0), c1 = __ballot_sync(FULL, (cls & 2u) != 0);
+                const unsigned rest = __ballot_sync(FULL, cls >= 4u && id != 0xffffffffu);
+                vec.x = (unsigned)__popc(mm & ~c1 & ~c0) | ((unsigned)__popc(mm & ~c1 & c0) << 8) |
+                        ((unsigned)__popc(mm & c1 & ~c0) << 16) | ((unsigned)__popc(mm & c1 & c0) << 24);
+                wide = rest != 0;                                              // a class beyond A,C,G,T
+                if (wide) {
+                    // exact per-class counts for every class present in the window
+                    const bool real = id != 0xffffffffu;
+                    unsigned present = __reduce_or_sync(FULL, real ? (1u << cls) : 0u);
+                    iupac = (present & 0x7ff0u) != 0;
+                    vec = make_uint4(0, 0, 0, 0);
+                    while (present) {
+                        const int cc = __ffs(present) - 1;
+                        present &= present - 1;
+                        const unsigned b = __ballot_sync(FULL, real && cls == (uint32_t)cc);
+                        const unsigned v = (unsigned)__popc(mm & b) << ((cc & 3) * 8);
+                        if ((cc >> 2) == 0) vec.x |= v; else if ((cc >> 2) == 1) vec.y |= v;
+                        else if ((cc >> 2) == 2) vec.z |= v; else vec.w |= v;
+                    }
+                }
+            }
+            // reads wrap at 256 (:123,206), genomes saturate at 255 (:96-97,222-223): counts <= 32 here
+
+            // every read leader against every genome leader of its cluster
+            unsigned gl = __ballot_sync(FULL, leader && !is_read) & cm;
+            if (!(leader && is_read)) gl = 0;
+            while (__any_sync(FULL, gl != 0)) {
+                const int src = gl ? 31 - __clz(gl) : 0;
+                const uint32_t Gx = __shfl_sync(FULL, vec.x, src);
+                const uint32_t gid = __shfl_sync(FULL, id, src);
+                uint32_t t;
+                if (!EBWT) t = min(vec.x, Gx);
+                else if (!wide) t = score_acgt(vec.x, Gx);
+                else {
+                    uint4 Gv;
+                    Gv.x = Gx;
+                    Gv.y = __shfl_sync(FULL, vec.y, src); Gv.z = __shfl_sync(FULL, vec.z, src);
+                    Gv.w = __shfl_sync(FULL, vec.w, src);
+                    t = (iupac ? score_iupac(vec, Gv) : score_plain(vec, Gv)) & 0xffu;
+                }
+                if (gl == 0) t = 0;
+                else gl ^= 1u << src;
+                if (qn + 32 > QCAP) drain();
+                const unsigned pm = __ballot_sync(FULL, t != 0);
+                if (t) q[qn + __popc(pm & lt_mask)] = make_uint2(id, ((gid - P.n_reads) << 8) | t);
+                qn += __popc(pm);
+            }
+        }
+        max_len = max(max_len, (unsigned long long)longest);
+    }
+    drain();
+
+    // ---- totals of this warp: one atomic per warp and scalar -------------------------------------------
+    {
+        unsigned c2 = cl_count;
+        unsigned long long mx = max_len;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            c2 += __shfl_xor_sync(FULL, c2, o);
+            mx = max(mx, __shfl_xor_sync(FULL, mx, o));
+        }
+        if (lane == 0 && !(P.dbg & 1u)) {
+            if (!EMIT && c2) atomicAdd(P.n_clusters, (unsigned long long)c2);
+            if (mx) atomicMax(P.max_len, mx);
+            if (SCORE && updates) atomicAdd(P.n_updates, updates);
+        }
+    }
+}
+
+} // namespace k12s
+
+uint64_t k12s_num_chunks(uint64_t n_own) { return (n_own + k12s::OWN - 1) / k12s::OWN; }
+
+template <bool SC, bool EM, bool EB, bool EX>
+static cudaError_t launch_variant(const K12Args &a, cudaStream_t s)
+{
+    // persistent grid: every CTA is resident (the look-back of EMIT relies on it), warps stride over chunks
+    static int ctas_per_sm = 0, sms = 0;
+    if (!ctas_per_sm) {
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, k12s::stream_kernel<SC, EM, EB, EX>, k12s::THREADS, 0);
+        if (e != cudaSuccess) return e;
+        if (ctas_per_sm < 1) ctas_per_sm = 1;
+    }
+    const uint64_t chunks = k12s_num_chunks(a.n_own);
+    const uint64_t want = (chunks + k12s::WARPS - 1) / k12s::WARPS;
+    const unsigned grid = (unsigned)std::min<uint64_t>(want, (uint64_t)sms * ctas_per_sm);
+    k12s::stream_kernel<SC, EM, EB, EX><<<grid, k12s::THREADS, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_k12s(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s)
+{
+    if (a.n_own == 0) return cudaSuccess;
+    const bool ebwt = a.ebwt != nullptr;
+    if (!score)                        return launch_variant<false, true, false, false>(a, s);
+    if (emit) {
+        if (ebwt && !exact32)          return launch_variant<true, true, true, false>(a, s);
+        if (ebwt && exact32)           return launch_variant<true, true, true, true>(a, s);
+        if (!ebwt && !exact32)         return launch_variant<true, true, false, false>(a, s);
+        return launch_variant<true, true, false, true>(a, s);
+    }
+    if (ebwt && !exact32)              return launch_variant<true, false, true, false>(a, s);
+    if (ebwt && exact32)               return launch_variant<true, false, true, true>(a, s);
+    if (!ebwt && !exact32)             return launch_variant<true, false, false, false>(a, s);
+    return launch_variant<true, false, false, true>(a, s);
+}
+
+} // namespace lime
