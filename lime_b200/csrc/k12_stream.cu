@@ -4,9 +4,9 @@
 //
 // A position i with lcp[i] < alpha is a "head"; a segment is [head, next head); a segment with at
 // least one da < n_reads and one da >= n_reads is an alpha-cluster.  The kernel is persistent: every
-// WARP walks over chunks of 1024 positions (32 words of 32) with a stride of 896, owns the segments
-// whose head lies in the first 896 positions (the chunk ownership rule of ClusterLCP.cpp:150-202,
-// the remaining 128 positions are look-ahead) and never synchronises with another warp:
+// WARP walks over chunks of 512 positions (16 words of 32) with a stride of 480, owns the segments
+// whose head lies in the first 480 positions (the chunk ownership rule of ClusterLCP.cpp:150-202,
+// the last word is look-ahead) and never synchronises with another warp:
 //
 //   phase A  lane = position inside a word: 32 coalesced loads of lcp and da, two ballots per word
 //            give the head word (lcp < alpha) and the read word (da < n_reads); lane k keeps word k.
@@ -33,11 +33,13 @@ namespace k12s {
 
 constexpr int WARPS = 4;                  // per CTA; warps share nothing but the class table
 constexpr int THREADS = WARPS * 32;
-constexpr int CH = 1024;                  // positions held per warp and chunk (32 words)
-constexpr int OWN = 896;                  // owned positions per chunk (28 words); 128 look-ahead
+constexpr int WORDS = 16;                 // 32-position words per chunk
+constexpr int CH = WORDS * 32;            // positions held per warp and chunk
+constexpr int OWN = CH - 32;              // owned positions per chunk; one word of look-ahead is enough
+                                          // for every cluster the window path takes (<= 32 positions)
 constexpr int NONE = 1 << 30;
 constexpr int MAXFAST = 32;               // longest cluster the window path takes
-constexpr int QCAP = 128;                 // queued similarity updates per warp
+constexpr int QCAP = 96;                  // queued similarity updates per warp
 constexpr int SCAP = CH + 32;             // stream capacity incl. one window of padding
 
 // x_i |= x_{i-1} while c_i (position i continues the run of i-1); Kogge-Stone, 5 steps
@@ -66,7 +68,10 @@ __device__ __forceinline__ uint32_t mask_lt(int k)   // bits [0, k), k may be <=
 }
 
 struct WarpSmem {
-    uint4    info[32];            // per word: active, head, exclusive prefix of popc(active), -
+    uint32_t lcp[CH];             // stage of the next chunk, filled by cp.async while this one is scored
+    uint32_t da[CH];
+    uint8_t  eb[CH];
+    uint4    info[WORDS];         // per word: active, head, exclusive prefix of popc(active), -
     uint32_t cid[SCAP];           // compacted document ids
     uint16_t cmeta[SCAP];         // compacted symbol | start << 8
     uint2    q[QCAP];             // queue of updates {read, genome << 8 | t}
@@ -76,9 +81,15 @@ struct Smem {
     uint8_t  cls[256];            // symbol -> class
 };
 
-__device__ __forceinline__ void prefetch_l2(const void *p)
+// 16-byte asynchronous global -> shared copy (LDGSTS), L1 bypassed
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
 {
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all()
+{
+    asm volatile("cp.async.wait_all;" ::: "memory");
 }
 
 template <bool SCORE, bool EMIT, bool EBWT, bool EXACT32>
@@ -110,18 +121,18 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
     auto drain = [&]() {
         __syncwarp();
         if (P.dbg & 2u) { qn = 0; return; }
-        for (int k = (int)lane; k < qn; k += 128) {
-            uint2 e[4];
-            bool on[4];
+        for (int k = (int)lane; k < qn; k += QCAP) {
+            uint2 e[QCAP / 32];
+            bool on[QCAP / 32];
 #pragma unroll
-            for (int u = 0; u < 4; u++) { on[u] = k + 32 * u < qn; if (on[u]) e[u] = q[k + 32 * u]; }
+            for (int u = 0; u < QCAP / 32; u++) { on[u] = k + 32 * u < qn; if (on[u]) e[u] = q[k + 32 * u]; }
             if (EXACT32) {
 #pragma unroll
-                for (int u = 0; u < 4; u++) if (on[u]) sim_add<true>(acc, e[u].x, e[u].y >> 8, e[u].y & 0xffu);
+                for (int u = 0; u < QCAP / 32; u++) if (on[u]) sim_add<true>(acc, e[u].x, e[u].y >> 8, e[u].y & 0xffu);
             } else {
-                unsigned old[4];
+                unsigned old[QCAP / 32];
 #pragma unroll
-                for (int u = 0; u < 4; u++) {
+                for (int u = 0; u < QCAP / 32; u++) {
                     if (on[u]) {
                         const uint32_t g = e[u].y >> 8;
                         unsigned *wp = reinterpret_cast<unsigned *>(acc.sim8 + (size_t)e[u].x * acc.pitch8) + (g >> 2);
@@ -130,7 +141,7 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
                 }
                 bool carry = false;
 #pragma unroll
-                for (int u = 0; u < 4; u++)
+                for (int u = 0; u < QCAP / 32; u++)
                     if (on[u]) carry |= ((old[u] >> (((e[u].y >> 8) & 3u) * 8u)) & 0xffu) + (e[u].y & 0xffu) > 0xffu;
                 if (carry) *acc.carry = 1u;
             }
@@ -140,59 +151,75 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
         __syncwarp();
     };
 
-    for (uint64_t c = (uint64_t)blockIdx.x * WARPS + warp; c < n_chunks; c += stride) {
+    // Stage pipeline: the chunk after the current one is copied global -> shared asynchronously
+    // (16 bytes per lane and copy) while the current one is scored; whole chunks only, the tail of
+    // the buffer and unaligned buffers are loaded synchronously.
+    const bool aligned = ((reinterpret_cast<uintptr_t>(P.lcp) | reinterpret_cast<uintptr_t>(P.da) |
+                           (SCORE && EBWT ? reinterpret_cast<uintptr_t>(P.ebwt) : 0)) & 15u) == 0;
+    auto stage_issue = [&](uint64_t cc) -> bool {
+        if (cc >= n_chunks) return false;
+        const uint64_t aa = cc * OWN;
+        if (!aligned || aa + CH > P.n_total) return false;
+#pragma unroll
+        for (int k = 0; k < CH / 128; k++) {
+            cp_async16(&ws.lcp[128 * k + 4 * lane], P.lcp + aa + 128 * k + 4 * lane);
+            cp_async16(&ws.da[128 * k + 4 * lane], P.da + aa + 128 * k + 4 * lane);
+        }
+        if (SCORE && EBWT) {
+#pragma unroll
+            for (int k = 0; k < CH / 512; k++) cp_async16(&ws.eb[512 * k + 16 * lane], P.ebwt + aa + 512 * k + 16 * lane);
+        }
+        return true;
+    };
+    const uint64_t c_first = (uint64_t)blockIdx.x * WARPS + warp;
+    bool staged = stage_issue(c_first);
+
+    for (uint64_t c = c_first; c < n_chunks; c += stride) {
         const uint64_t a = c * OWN;                                  // buffer-local start of the chunk
         const int Lt = (int)min((uint64_t)OWN, P.n_own - a);         // owned positions
         const int Lext = (int)min((uint64_t)CH, P.n_total - a);      // real positions in the chunk
 
-        // ---- phase A: load, head / read words ------------------------------------------------------
-        uint32_t D[32];
-        uint32_t Eb[8];
-        uint32_t H = 0, R = 0;
-        {
-            const uint32_t *pl = P.lcp + a + lane, *pd = P.da + a + lane;
-            const uint8_t *pe = P.ebwt + a + lane;
-            // pull the next chunk of this warp into L2 while this one is processed
-            if (c + stride < n_chunks) {
-                const uint64_t an = a + stride * OWN;
-                if (an + 32ull * lane < P.n_total) {
-                    prefetch_l2(P.lcp + an + 32ull * lane);
-                    prefetch_l2(P.da + an + 32ull * lane);
-                    if (SCORE && EBWT && lane < 8 && an + 128ull * lane < P.n_total) prefetch_l2(P.ebwt + an + 128ull * lane);
+        // ---- phase A: head / read words, da and ebwt to registers ------------------------------------
+        uint32_t D[WORDS];
+        uint32_t Eb[WORDS / 4];
+        uint32_t H = 0xffffffffu, R = 0;                             // lanes >= WORDS: beyond the chunk
+        if (staged) {
+            cp_async_wait_all();
+            __syncwarp();
+#pragma unroll
+            for (int k = 0; k < WORDS; k++) {
+                const uint32_t l = ws.lcp[32 * k + lane];
+                D[k] = ws.da[32 * k + lane];
+                const uint32_t hk = __ballot_sync(FULL, l < P.alpha);
+                const uint32_t rk = __ballot_sync(FULL, D[k] < P.n_reads);
+                if (w == k) { H = hk; R = rk; }
+            }
+            if (SCORE && EBWT) {
+#pragma unroll
+                for (int k = 0; k < WORDS; k++) {
+                    const uint32_t e = ws.eb[32 * k + lane];
+                    if ((k & 3) == 0) Eb[k >> 2] = e; else Eb[k >> 2] |= e << (8 * (k & 3));
                 }
             }
-            if (Lext == CH) {
+            __syncwarp();
+        } else {
+            const uint32_t *pl = P.lcp + a + lane, *pd = P.da + a + lane;
+            const uint8_t *pe = P.ebwt + a + lane;
 #pragma unroll
-                for (int k = 0; k < 32; k++) {
-                    const uint32_t l = __ldcs(pl + 32 * k);
-                    D[k] = __ldcs(pd + 32 * k);
-                    const uint32_t hk = __ballot_sync(FULL, l < P.alpha);
-                    const uint32_t rk = __ballot_sync(FULL, D[k] < P.n_reads);
-                    if (w == k) { H = hk; R = rk; }
-                }
+            for (int k = 0; k < WORDS; k++) {
+                const bool ok = 32 * k + (int)lane < Lext;
+                const uint32_t l = ok ? __ldcs(pl + 32 * k) : 0u;              // virtual head
+                D[k] = ok ? __ldcs(pd + 32 * k) : 0xffffffffu;                 // neither read nor real
+                const uint32_t hk = __ballot_sync(FULL, l < P.alpha);
+                const uint32_t rk = __ballot_sync(FULL, D[k] < P.n_reads);
+                if (w == k) { H = hk; R = rk; }
                 if (SCORE && EBWT) {
-#pragma unroll
-                    for (int k = 0; k < 32; k++) {
-                        const uint32_t e = __ldcs(pe + 32 * k);
-                        if ((k & 3) == 0) Eb[k >> 2] = e; else Eb[k >> 2] |= e << (8 * (k & 3));
-                    }
-                }
-            } else {
-#pragma unroll
-                for (int k = 0; k < 32; k++) {
-                    const bool ok = 32 * k + (int)lane < Lext;
-                    const uint32_t l = ok ? __ldcs(pl + 32 * k) : 0u;              // virtual head
-                    D[k] = ok ? __ldcs(pd + 32 * k) : 0xffffffffu;                 // neither read nor real
-                    const uint32_t hk = __ballot_sync(FULL, l < P.alpha);
-                    const uint32_t rk = __ballot_sync(FULL, D[k] < P.n_reads);
-                    if (w == k) { H = hk; R = rk; }
-                    if (SCORE && EBWT) {
-                        const uint32_t e = ok ? (uint32_t)__ldcs(pe + 32 * k) : 0u;
-                        if ((k & 3) == 0) Eb[k >> 2] = e; else Eb[k >> 2] |= e << (8 * (k & 3));
-                    }
+                    const uint32_t e = ok ? (uint32_t)__ldcs(pe + 32 * k) : 0u;
+                    if ((k & 3) == 0) Eb[k >> 2] = e; else Eb[k >> 2] |= e << (8 * (k & 3));
                 }
             }
         }
+        staged = stage_issue(c + stride);                            // lands while this chunk is scored
 
         // ---- phase B: per-word segment flags (lane w owns word w) -------------------------------------
         // A segment holds a read and a genome iff two neighbours inside it differ in kind:
@@ -220,7 +247,7 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
         int E = NONE, hl = -1;
         {
             const uint32_t below_lt = mask_lt(Lt - w * 32);
-            const uint32_t he = H & ~below_lt, hb = H & below_lt;
+            const uint32_t he = w < WORDS ? (H & ~below_lt) : 0u, hb = H & below_lt;   // lanes >= WORDS own no word
             const uint32_t Em = __ballot_sync(FULL, he != 0), Bm = __ballot_sync(FULL, hb != 0);
             if (Em) {
                 const int src = __ffs(Em) - 1;
@@ -378,12 +405,12 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
                 if (lane >= (unsigned)o) incl += n;
             }
             n_act = (int)__shfl_sync(FULL, incl, 31);
-            ws.info[w] = make_uint4(Aw, H, incl - cnt, 0u);
+            if (w < WORDS) ws.info[w] = make_uint4(Aw, H, incl - cnt, 0u);
         }
         if (n_act == 0) continue;                                         // warp-uniform
         __syncwarp();
 #pragma unroll
-        for (int k = 0; k < 32; k++) {
+        for (int k = 0; k < WORDS; k++) {
             const uint4 inf = ws.info[k];
             if (inf.x == 0u) continue;                                    // warp-uniform
             if ((inf.x >> lane) & 1u) {

@@ -18,7 +18,7 @@ for i, l in enumerate(dis):
     m = re.match(r"\s*\.section\s+\.text\.(\S+?),", l)
     if m:
         name = m.group(1)
-        if start is None and sub in name and "fused_kernel" in name:
+        if start is None and sub in name :
             start = i
         elif start is not None and i > start:
             end = i
@@ -32,7 +32,7 @@ for l in dis[start:end]:
     if m:
         cur = (m.group(1).split("/")[-1], int(m.group(2)))
         continue
-    if re.match(r"\s+/\*[0-9a-f]{4}\*/", l):
+    if re.match(r"\s+/\*[0-9a-f]{4,}\*/", l):
         lines.append(cur)
 print("sass rows", len(sass), "disasm instrs", len(lines), file=sys.stderr)
 agg = collections.defaultdict(lambda: [0, 0, 0])
@@ -55,7 +55,7 @@ if len(sys.argv) > 5:
     last = None
     for k in range(n):
         f, ln = lines[k] if lines[k] else ("?", 0)
-        if f == "k12_fused.cu":
+        if f.startswith("k12_"):
             last = ln
         name = "other"
         for nm, lo, hi in ranges:
