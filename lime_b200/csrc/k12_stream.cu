@@ -39,7 +39,10 @@ constexpr int OWN = CH - 32;              // owned positions per chunk; one word
                                           // for every cluster the window path takes (<= 32 positions)
 constexpr int NONE = 1 << 30;
 constexpr int MAXFAST = 32;               // longest cluster the window path takes
-constexpr int QCAP = 96;                  // queued similarity updates per warp
+constexpr int NBMAX = 8;                  // read-range buckets of the two-pass scatter
+constexpr int UBLK = 16;                  // entries per append block (128 bytes)
+constexpr unsigned OVF = 0xffffffffu;     // cursor value: region full, add to the matrix directly
+constexpr unsigned NEED = 0xfffffffeu;    // cursor value: no open block, take one at the next update
 constexpr int SCAP = CH + 32;             // stream capacity incl. one window of padding
 
 // x_i |= x_{i-1} while c_i (position i continues the run of i-1); Kogge-Stone, 5 steps
@@ -74,7 +77,8 @@ struct WarpSmem {
     uint4    info[WORDS];         // per word: active, head, exclusive prefix of popc(active), -
     uint32_t cid[SCAP];           // compacted document ids
     uint16_t cmeta[SCAP];         // compacted symbol | start << 8
-    uint2    q[QCAP];             // queue of updates {read, genome << 8 | t}
+    uint32_t cur[NBMAX][32];      // per bucket and lane: next entry of the lane's open append block
+    uint32_t blk_next[NBMAX];     // per bucket: next free block of the warp's region
 };
 struct Smem {
     WarpSmem w[WARPS];
@@ -109,46 +113,42 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
     const uint64_t stride = (uint64_t)gridDim.x * WARPS;
     unsigned cl_count = 0;                                    // clusters counted by this lane
     unsigned long long max_len = 0;                           // longest cluster seen by this lane
-    unsigned long long updates = 0;                           // warp-uniform
+    unsigned long long updates = 0;                           // updates issued by this lane
 
     SimAcc acc;
     acc.sim8 = P.sim8; acc.pitch8 = P.pitch8; acc.sim32 = P.sim32; acc.lo = P.lo; acc.hi = P.hi;
     acc.n_refs = P.n_refs; acc.carry = P.carry;
-    uint2 *q = ws.q;
-    int qn = 0;
-    // Updates are queued per warp and applied in bulk so that many atomics are in flight per lane
-    // and their return values (needed for the carry check) are not waited for one by one.
-    auto drain = [&]() {
+    // Two-pass scatter: a lane appends its update {read, genome << 8 | t} to a private 128-byte block
+    // of the warp's region of bucket read >> upd_shift; k12s::apply_kernel adds the regions to the
+    // matrix bucket after bucket, so the slab being updated stays in L2 instead of taking one DRAM
+    // sector read + write-back per update.  A lane whose region is full adds to the matrix directly.
+    const unsigned gw = blockIdx.x * WARPS + warp;
+    const bool append = SCORE && !EXACT32 && P.upd != nullptr;
+    if (append) {
+        for (unsigned b = 0; b < P.upd_nb; b++) ws.cur[b][lane] = NEED;
+        if (lane < P.upd_nb) ws.blk_next[lane] = 0u;
         __syncwarp();
-        if (P.dbg & 2u) { qn = 0; return; }
-        for (int k = (int)lane; k < qn; k += QCAP) {
-            uint2 e[QCAP / 32];
-            bool on[QCAP / 32];
-#pragma unroll
-            for (int u = 0; u < QCAP / 32; u++) { on[u] = k + 32 * u < qn; if (on[u]) e[u] = q[k + 32 * u]; }
-            if (EXACT32) {
-#pragma unroll
-                for (int u = 0; u < QCAP / 32; u++) if (on[u]) sim_add<true>(acc, e[u].x, e[u].y >> 8, e[u].y & 0xffu);
-            } else {
-                unsigned old[QCAP / 32];
-#pragma unroll
-                for (int u = 0; u < QCAP / 32; u++) {
-                    if (on[u]) {
-                        const uint32_t g = e[u].y >> 8;
-                        unsigned *wp = reinterpret_cast<unsigned *>(acc.sim8 + (size_t)e[u].x * acc.pitch8) + (g >> 2);
-                        old[u] = atomicAdd(wp, (e[u].y & 0xffu) << ((g & 3u) * 8u));
-                    }
-                }
-                bool carry = false;
-#pragma unroll
-                for (int u = 0; u < QCAP / 32; u++)
-                    if (on[u]) carry |= ((old[u] >> (((e[u].y >> 8) & 3u) * 8u)) & 0xffu) + (e[u].y & 0xffu) > 0xffu;
-                if (carry) *acc.carry = 1u;
+    }
+    auto add_update = [&](uint32_t r, uint32_t g, uint32_t t) {
+        updates++;
+        if (P.dbg & 2u) return;
+        if (EXACT32) { sim_add<true>(acc, r, g, t); return; }
+        if (append) {
+            const unsigned b = r >> P.upd_shift;
+            unsigned cu = ws.cur[b][lane];
+            if (cu == NEED) {
+                const unsigned nb = atomicAdd(&ws.blk_next[b], 1u);
+                cu = nb < P.upd_region / UBLK ? nb * UBLK : OVF;
+                if (cu == OVF) ws.cur[b][lane] = OVF;
+            }
+            if (cu != OVF) {
+                P.upd[((size_t)b * P.upd_nw + gw) * P.upd_region + cu] = make_uint2(r, (g << 8) | t);
+                cu++;
+                ws.cur[b][lane] = (cu & (UBLK - 1)) ? cu : NEED;
+                return;
             }
         }
-        updates += (unsigned long long)qn;
-        qn = 0;
-        __syncwarp();
+        sim_add<false>(acc, r, g, t);
     };
 
     // Stage pipeline: the chunk after the current one is copied global -> shared asynchronously
@@ -500,15 +500,23 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
                 }
                 if (gl == 0) t = 0;
                 else gl ^= 1u << src;
-                if (qn + 32 > QCAP) drain();
-                const unsigned pm = __ballot_sync(FULL, t != 0);
-                if (t) q[qn + __popc(pm & lt_mask)] = make_uint2(id, ((gid - P.n_reads) << 8) | t);
-                qn += __popc(pm);
+                if (t) add_update(id, gid - P.n_reads, t);
             }
         }
         max_len = max(max_len, (unsigned long long)longest);
     }
-    drain();
+    if (append) {
+        // close the open blocks with empty entries (t = 0) and publish the blocks used per region
+        __syncwarp();
+        for (unsigned b = 0; b < P.upd_nb; b++) {
+            unsigned cu = ws.cur[b][lane];
+            if (cu == OVF || cu == NEED) continue;
+            uint2 *reg = P.upd + ((size_t)b * P.upd_nw + gw) * P.upd_region;
+            while (cu & (UBLK - 1)) reg[cu++] = make_uint2(0u, 0u);
+        }
+        if (lane < P.upd_nb)
+            P.upd_fill[(size_t)lane * P.upd_nw + gw] = min(ws.blk_next[lane], P.upd_region / UBLK);
+    }
 
     // ---- totals of this warp: one atomic per warp and scalar -------------------------------------------
     {
@@ -518,6 +526,7 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
         for (int o = 16; o > 0; o >>= 1) {
             c2 += __shfl_xor_sync(FULL, c2, o);
             mx = max(mx, __shfl_xor_sync(FULL, mx, o));
+            updates += __shfl_xor_sync(FULL, updates, o);
         }
         if (lane == 0 && !(P.dbg & 1u)) {
             if (!EMIT && c2) atomicAdd(P.n_clusters, (unsigned long long)c2);
@@ -527,47 +536,122 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
     }
 }
 
+// ---- second pass of the scatter: add the appended updates to the matrix, bucket after bucket --------
+// Every warp of a persistent grid walks the buckets in the same order and takes whole regions of the
+// current bucket, so at any time the atomics of the whole GPU fall into one slab of the matrix
+// (n_reads >> upd_shift rows) that fits in L2.  Entries are read once, coalesced, evict-first.
+constexpr int APPLY_THREADS = 256;
+constexpr int APPLY_UNROLL = 4;
+__global__ void __launch_bounds__(APPLY_THREADS) apply_kernel(ApplyArgs P)
+{
+    const unsigned lane = lane_id();
+    const unsigned gw = (blockIdx.x * APPLY_THREADS + threadIdx.x) >> 5;
+    const unsigned n_warps = (gridDim.x * APPLY_THREADS) >> 5;
+    bool carry = false;
+    for (unsigned b = 0; b < P.upd_nb; b++) {
+        for (unsigned r = gw; r < P.upd_nw; r += n_warps) {
+            const unsigned n = P.upd_fill[(size_t)b * P.upd_nw + r] * UBLK;
+            const uint2 *reg = P.upd + ((size_t)b * P.upd_nw + r) * P.upd_region;
+            for (unsigned k = lane; k < n; k += 32 * APPLY_UNROLL) {
+                uint2 e[APPLY_UNROLL];
+                unsigned old[APPLY_UNROLL];
+#pragma unroll
+                for (int u = 0; u < APPLY_UNROLL; u++)
+                    e[u] = k + 32 * u < n ? __ldcs(reg + k + 32 * u) : make_uint2(0u, 0u);
+#pragma unroll
+                for (int u = 0; u < APPLY_UNROLL; u++) {
+                    const uint32_t t = e[u].y & 0xffu, g = e[u].y >> 8;
+                    if (t) {
+                        unsigned *wp = reinterpret_cast<unsigned *>(P.sim8 + (size_t)e[u].x * P.pitch8) + (g >> 2);
+                        old[u] = atomicAdd(wp, t << ((g & 3u) * 8u));
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < APPLY_UNROLL; u++) {
+                    const uint32_t t = e[u].y & 0xffu, g = e[u].y >> 8;
+                    if (t) carry |= ((old[u] >> ((g & 3u) * 8u)) & 0xffu) + t > 0xffu;
+                }
+            }
+        }
+    }
+    if (carry) *P.carry = 1u;
+}
+
 } // namespace k12s
 
-uint64_t k12s_num_chunks(uint64_t n_own) { return (n_own + k12s::OWN - 1) / k12s::OWN; }
-
-template <bool SC, bool EM, bool EB, bool EX>
-static cudaError_t launch_variant(const K12Args &a, cudaStream_t s)
+cudaError_t launch_k12_apply(const ApplyArgs &a, cudaStream_t s)
 {
-    // persistent grid: every CTA is resident (the look-back of EMIT relies on it), warps stride over chunks
-    static int ctas_per_sm = 0, sms = 0;
-    if (!ctas_per_sm) {
+    static int sms = 0;
+    if (!sms) {
         int dev = 0;
         cudaError_t e = cudaGetDevice(&dev);
         if (e != cudaSuccess) return e;
         e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, k12s::stream_kernel<SC, EM, EB, EX>, k12s::THREADS, 0);
-        if (e != cudaSuccess) return e;
+    }
+    const unsigned warps_per_cta = k12s::APPLY_THREADS / 32;
+    const unsigned want = (a.upd_nw + warps_per_cta - 1) / warps_per_cta;
+    const unsigned grid = std::max(1u, std::min(want, (unsigned)sms * 8u));
+    k12s::apply_kernel<<<grid, k12s::APPLY_THREADS, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+uint64_t k12s_num_chunks(uint64_t n_own) { return (n_own + k12s::OWN - 1) / k12s::OWN; }
+
+template <bool SC, bool EM, bool EB, bool EX>
+static unsigned grid_of(uint64_t n_own)
+{
+    static int ctas_per_sm = 0, sms = 0;
+    if (!ctas_per_sm) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, k12s::stream_kernel<SC, EM, EB, EX>, k12s::THREADS, 0) != cudaSuccess) return 0;
         if (ctas_per_sm < 1) ctas_per_sm = 1;
     }
-    const uint64_t chunks = k12s_num_chunks(a.n_own);
+    const uint64_t chunks = k12s_num_chunks(n_own);
     const uint64_t want = (chunks + k12s::WARPS - 1) / k12s::WARPS;
-    const unsigned grid = (unsigned)std::min<uint64_t>(want, (uint64_t)sms * ctas_per_sm);
+    return (unsigned)std::min<uint64_t>(want, (uint64_t)sms * ctas_per_sm);
+}
+
+template <bool SC, bool EM, bool EB, bool EX>
+static cudaError_t launch_variant(const K12Args &a, cudaStream_t s)
+{
+    // persistent grid: every CTA is resident (the look-back of EMIT relies on it), warps stride over chunks
+    const unsigned grid = grid_of<SC, EM, EB, EX>(a.n_own);
+    if (!grid) return cudaErrorUnknown;
+    if (a.upd && a.upd_nw != grid * k12s::WARPS) return cudaErrorInvalidValue;
     k12s::stream_kernel<SC, EM, EB, EX><<<grid, k12s::THREADS, 0, s>>>(a);
     return cudaGetLastError();
+}
+
+#define LIME_K12S_DISPATCH(CALL)                                                              \
+    if (!score)                        return CALL(false, true, false, false);               \
+    if (emit) {                                                                               \
+        if (ebwt && !exact32)          return CALL(true, true, true, false);                 \
+        if (ebwt && exact32)           return CALL(true, true, true, true);                  \
+        if (!ebwt && !exact32)         return CALL(true, true, false, false);                \
+        return CALL(true, true, false, true);                                                 \
+    }                                                                                         \
+    if (ebwt && !exact32)              return CALL(true, false, true, false);                \
+    if (ebwt && exact32)               return CALL(true, false, true, true);                 \
+    if (!ebwt && !exact32)             return CALL(true, false, false, false);               \
+    return CALL(true, false, false, true);
+
+unsigned k12s_grid_warps(bool score, bool emit, bool ebwt, bool exact32, uint64_t n_own)
+{
+#define LIME_GW(SC, EM, EB, EX) (grid_of<SC, EM, EB, EX>(n_own) * (unsigned)k12s::WARPS)
+    LIME_K12S_DISPATCH(LIME_GW)
+#undef LIME_GW
 }
 
 cudaError_t launch_k12s(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s)
 {
     if (a.n_own == 0) return cudaSuccess;
     const bool ebwt = a.ebwt != nullptr;
-    if (!score)                        return launch_variant<false, true, false, false>(a, s);
-    if (emit) {
-        if (ebwt && !exact32)          return launch_variant<true, true, true, false>(a, s);
-        if (ebwt && exact32)           return launch_variant<true, true, true, true>(a, s);
-        if (!ebwt && !exact32)         return launch_variant<true, true, false, false>(a, s);
-        return launch_variant<true, true, false, true>(a, s);
-    }
-    if (ebwt && !exact32)              return launch_variant<true, false, true, false>(a, s);
-    if (ebwt && exact32)               return launch_variant<true, false, true, true>(a, s);
-    if (!ebwt && !exact32)             return launch_variant<true, false, false, false>(a, s);
-    return launch_variant<true, false, false, true>(a, s);
+#define LIME_LV(SC, EM, EB, EX) launch_variant<SC, EM, EB, EX>(a, s)
+    LIME_K12S_DISPATCH(LIME_LV)
+#undef LIME_LV
 }
 
 } // namespace lime

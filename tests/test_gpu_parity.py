@@ -116,6 +116,45 @@ def test_fused_adversarial_layouts(ctx, oracle):
         _check_case(ctx, oracle, case, 16, 0, beta=0.0, fused=True, keep=False)
 
 
+def test_stream_chunk_boundaries(ctx, oracle):
+    """Head patterns around the stream kernel's chunk geometry: chunks start every 480 positions,
+    hold 512 (one word of look-ahead); clusters of 28..40 positions straddle every boundary."""
+    rng = np.random.default_rng(17)
+    n, n_reads, n_refs = 40 * 480 + 123, 60, 5
+    for trial in range(10):
+        lcp = np.full(n, 20, np.uint32)
+        heads = set([0])
+        for c in range(1, 40):
+            for off in rng.integers(-40, 40, size=3):
+                heads.add(int(min(max(480 * c + off, 0), n - 1)))
+            if trial % 2:
+                heads |= {480 * c - 1, 480 * c, 480 * c + 31, 480 * c + 32}
+        for h in rng.integers(0, n, size=[0, 100, 1500][trial % 3]):
+            heads.add(int(h))
+        lcp[sorted(heads)] = 3
+        da = rng.integers(0, n_reads + n_refs, size=n).astype(np.uint32)
+        if trial % 3 == 1:
+            da[rng.random(n) < 0.95] = 1
+        ebwt = np.frombuffer(bytes(rng.choice(list(b"ACGTN\0R$"), size=n).tolist()), dtype=np.uint8).copy()
+        case = dict(name=f"chunk{trial}", lcp=lcp, da=da, ebwt=ebwt, n_reads=n_reads, n_refs=n_refs, read_len=100)
+        _check_case(ctx, oracle, case, 16, 1, beta=0.0, fused=True)
+        _check_case(ctx, oracle, case, 16, 0, beta=0.0, fused=True, keep=False)
+
+
+@pytest.mark.parametrize("region", [0, 64])
+def test_two_pass_scatter_forced(ctx, oracle, corpus, monkeypatch, region):
+    """The append + apply scatter (taken by default only for matrices larger than L2) forced on small
+    inputs; region=64 makes the per-warp regions overflow so the direct-add fallback runs too."""
+    monkeypatch.setenv("LIME_APPEND", "1")
+    if region:
+        monkeypatch.setenv("LIME_APPEND_REGION", str(region))
+    for case in corpus:
+        _check_case(ctx, oracle, case, 16, 1, beta=0.0 if case["name"] == "wrap" else 0.25, fused=True, keep=False)
+    case = C.synth_case("synth_medium", 3_000_000, 30_000, 40, seed=33, p_long=2e-5, max_seg=60000)
+    _check_case(ctx, oracle, case, 16, 1, fused=True, keep=False)
+    _check_case(ctx, oracle, case, 12, 0, fused=True, keep=True)
+
+
 def test_sharded_loads_union_equals_whole(ctx, oracle):
     """Position shards with a halo (lime_load n_own / n_halo / pos_base / is_last): the clusters of
     the shards are a partition of the whole array's clusters and the matrices add up mod 256."""
