@@ -7,7 +7,7 @@ using namespace lime;
 
 
 static const char *const kKernelNames[KID_COUNT] = {
-    "k12_fused", "k12_apply", "k1_detect", "k2_warp", "k2_block", "k2_narrow", "k3_choose", "k3_export", "k3_import", "k3_count", "k3_emit", "k3_classify"};
+    "k12_fused", "k12_check", "k1_detect", "k2_warp", "k2_block", "k2_narrow", "k3_choose", "k3_export", "k3_import", "k3_count", "k3_emit", "k3_classify"};
 
 // device scalar block layout (u64 slots)
 enum {
@@ -15,6 +15,7 @@ enum {
     SC_TILE_COUNTER,   // u32 used
     SC_ERR,            // u32 used
     SC_CARRY,          // u32 used
+    SC_SUMT, SC_BYTESUM,
     SC_COUNT
 };
 

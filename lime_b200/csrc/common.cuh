@@ -100,7 +100,7 @@ struct DevBuf {
 
 enum KernelId {
     KID_K12_FUSED = 0,
-    KID_K12_APPLY,
+    KID_K12_CHECK,
     KID_K1_DETECT,
     KID_K2_WARP,
     KID_K2_BLOCK,
@@ -157,7 +157,6 @@ struct lime_ctx {
     lime::DevBuf sim32;             // exact pass scratch
     lime::DevBuf large_list;        // u64 cluster indices for the block path
     lime::DevBuf long_recs;         // fused path: records of the clusters left to the block path
-    lime::DevBuf upd, upd_fill;     // fused path: appended updates of the two-pass scatter, blocks used per region
     lime::DevBuf k2_scratch;        // block-path hash tables
     uint64_t sim_stats[4] = {0, 0, 0, 0};
 
@@ -190,6 +189,7 @@ struct K2Args {
     // exact 32-bit accumulator for reads [lo, hi)
     uint32_t *sim32; uint32_t lo, hi;
     unsigned int *carry;              // set to 1 when a packed add carried out of its byte
+    unsigned long long *sum_t;        // when non-null: total of all t added (see K12Args::sum_t)
     unsigned long long *large_count;  // block-path work list
     unsigned long long *large_list;   // indices into cl (cluster-list path) ...
     const lime_cluster *long_recs;    // ... or, when non-null, the records themselves (fused path)
@@ -226,21 +226,11 @@ struct K12Args {
     unsigned int *carry;
     unsigned long long *n_updates;
     unsigned dbg;                     // experiment switches (LIME_DEBUG env), 0 in production
-    // two-pass scatter (k12_stream.cu): updates are appended to per-(bucket, warp) regions, bucket =
-    // read >> upd_shift, and applied bucket after bucket so that the matrix slab stays in L2
-    uint2 *upd;                       // null: add to the matrix directly
-    unsigned int *upd_fill;           // [upd_nb][upd_nw] blocks used per region
-    uint32_t upd_region;              // entries per region (multiple of 512)
-    uint32_t upd_shift, upd_nb, upd_nw;
+    // stream kernel: fire-and-forget adds; sum_t receives the total of all t added to the matrix so
+    // that the host can prove the absence of byte carries (bytesum of the matrix == sum_t)
+    unsigned long long *sum_t;        // null: every add inspects the returned word instead
 };
-struct ApplyArgs {
-    const uint2 *upd; const unsigned int *upd_fill;
-    uint32_t upd_region, upd_nb, upd_nw;
-    uint8_t *sim8; uint64_t pitch8;
-    unsigned int *carry;
-};
-cudaError_t launch_k12_apply(const ApplyArgs &a, cudaStream_t s);
-unsigned k12s_grid_warps(bool score, bool emit, bool ebwt, bool exact32, uint64_t n_own);   // warps of the launch
+cudaError_t launch_bytesum(const uint8_t *p, uint64_t bytes, unsigned long long *out, cudaStream_t s);
 cudaError_t launch_k12(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s);
 uint64_t k12_num_tiles(uint64_t n_own);
 cudaError_t launch_k12s(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s);   // k12_stream.cu

@@ -442,7 +442,7 @@ __global__ void __launch_bounds__(THREADS, 4) fused_kernel(K12Args P)
     }
     SimAcc acc;
     acc.sim8 = P.sim8; acc.pitch8 = P.pitch8; acc.sim32 = P.sim32; acc.lo = P.lo; acc.hi = P.hi;
-    acc.n_refs = P.n_refs; acc.carry = P.carry;
+    acc.n_refs = P.n_refs; acc.carry = P.carry; acc.sum_t = nullptr;
     unsigned long long updates = 0;
     unsigned longest = 0;                        // longest cluster this warp scored (warp-uniform)
 

@@ -39,10 +39,6 @@ constexpr int OWN = CH - 32;              // owned positions per chunk; one word
                                           // for every cluster the window path takes (<= 32 positions)
 constexpr int NONE = 1 << 30;
 constexpr int MAXFAST = 32;               // longest cluster the window path takes
-constexpr int NBMAX = 8;                  // read-range buckets of the two-pass scatter
-constexpr int UBLK = 16;                  // entries per append block (128 bytes)
-constexpr unsigned OVF = 0xffffffffu;     // cursor value: region full, add to the matrix directly
-constexpr unsigned NEED = 0xfffffffeu;    // cursor value: no open block, take one at the next update
 constexpr int SCAP = CH + 32;             // stream capacity incl. one window of padding
 
 // x_i |= x_{i-1} while c_i (position i continues the run of i-1); Kogge-Stone, 5 steps
@@ -77,8 +73,6 @@ struct WarpSmem {
     uint4    info[WORDS];         // per word: active, head, exclusive prefix of popc(active), -
     uint32_t cid[SCAP];           // compacted document ids
     uint16_t cmeta[SCAP];         // compacted symbol | start << 8
-    uint32_t cur[NBMAX][32];      // per bucket and lane: next entry of the lane's open append block
-    uint32_t blk_next[NBMAX];     // per bucket: next free block of the warp's region
 };
 struct Smem {
     WarpSmem w[WARPS];
@@ -117,37 +111,24 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
 
     SimAcc acc;
     acc.sim8 = P.sim8; acc.pitch8 = P.pitch8; acc.sim32 = P.sim32; acc.lo = P.lo; acc.hi = P.hi;
-    acc.n_refs = P.n_refs; acc.carry = P.carry;
-    // Two-pass scatter: a lane appends its update {read, genome << 8 | t} to a private 128-byte block
-    // of the warp's region of bucket read >> upd_shift; k12s::apply_kernel adds the regions to the
-    // matrix bucket after bucket, so the slab being updated stays in L2 instead of taking one DRAM
-    // sector read + write-back per update.  A lane whose region is full adds to the matrix directly.
-    const unsigned gw = blockIdx.x * WARPS + warp;
-    const bool append = SCORE && !EXACT32 && P.upd != nullptr;
-    if (append) {
-        for (unsigned b = 0; b < P.upd_nb; b++) ws.cur[b][lane] = NEED;
-        if (lane < P.upd_nb) ws.blk_next[lane] = 0u;
-        __syncwarp();
-    }
+    acc.n_refs = P.n_refs; acc.carry = P.carry; acc.sum_t = P.sum_t;
+    // Matrix updates are fire-and-forget adds of t << 8*(g&3) to the 32-bit word that holds the uint8
+    // cell: no return value to wait for.  A carry out of a byte (true cell sum > 255, where the
+    // reference wraps, ClusterBWT_DA.cpp:183,247) lowers the byte sum of the matrix by 255 or 256, so
+    // the host proves their absence afterwards by comparing the byte sum of the matrix with the
+    // total of all t (sum_t) and otherwise reruns the pass into exact 32-bit cells.
+    const bool red_mode = P.sum_t != nullptr;
+    unsigned long long t_total = 0;                           // sum of t added by this lane
     auto add_update = [&](uint32_t r, uint32_t g, uint32_t t) {
         updates++;
         if (P.dbg & 2u) return;
         if (EXACT32) { sim_add<true>(acc, r, g, t); return; }
-        if (append) {
-            const unsigned b = r >> P.upd_shift;
-            unsigned cu = ws.cur[b][lane];
-            if (cu == NEED) {
-                const unsigned nb = atomicAdd(&ws.blk_next[b], 1u);
-                cu = nb < P.upd_region / UBLK ? nb * UBLK : OVF;
-                if (cu == OVF) ws.cur[b][lane] = OVF;
-            }
-            if (cu != OVF) {
-                P.upd[((size_t)b * P.upd_nw + gw) * P.upd_region + cu] = make_uint2(r, (g << 8) | t);
-                cu++;
-                ws.cur[b][lane] = (cu & (UBLK - 1)) ? cu : NEED;
-                return;
-            }
+        if (red_mode) {
+            atomicAdd(reinterpret_cast<unsigned *>(acc.sim8 + (size_t)r * acc.pitch8) + (g >> 2), t << ((g & 3u) * 8u));
+            t_total += t;
+            return;
         }
+        acc.sum_t = nullptr;
         sim_add<false>(acc, r, g, t);
     };
 
@@ -505,19 +486,6 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
         }
         max_len = max(max_len, (unsigned long long)longest);
     }
-    if (append) {
-        // close the open blocks with empty entries (t = 0) and publish the blocks used per region
-        __syncwarp();
-        for (unsigned b = 0; b < P.upd_nb; b++) {
-            unsigned cu = ws.cur[b][lane];
-            if (cu == OVF || cu == NEED) continue;
-            uint2 *reg = P.upd + ((size_t)b * P.upd_nw + gw) * P.upd_region;
-            while (cu & (UBLK - 1)) reg[cu++] = make_uint2(0u, 0u);
-        }
-        if (lane < P.upd_nb)
-            P.upd_fill[(size_t)lane * P.upd_nw + gw] = min(ws.blk_next[lane], P.upd_region / UBLK);
-    }
-
     // ---- totals of this warp: one atomic per warp and scalar -------------------------------------------
     {
         unsigned c2 = cl_count;
@@ -527,72 +495,51 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
             c2 += __shfl_xor_sync(FULL, c2, o);
             mx = max(mx, __shfl_xor_sync(FULL, mx, o));
             updates += __shfl_xor_sync(FULL, updates, o);
+            t_total += __shfl_xor_sync(FULL, t_total, o);
         }
         if (lane == 0 && !(P.dbg & 1u)) {
             if (!EMIT && c2) atomicAdd(P.n_clusters, (unsigned long long)c2);
             if (mx) atomicMax(P.max_len, mx);
             if (SCORE && updates) atomicAdd(P.n_updates, updates);
+            if (SCORE && t_total) atomicAdd(P.sum_t, t_total);
         }
     }
 }
 
-// ---- second pass of the scatter: add the appended updates to the matrix, bucket after bucket --------
-// Every warp of a persistent grid walks the buckets in the same order and takes whole regions of the
-// current bucket, so at any time the atomics of the whole GPU fall into one slab of the matrix
-// (n_reads >> upd_shift rows) that fits in L2.  Entries are read once, coalesced, evict-first.
-constexpr int APPLY_THREADS = 256;
-constexpr int APPLY_UNROLL = 4;
-__global__ void __launch_bounds__(APPLY_THREADS) apply_kernel(ApplyArgs P)
+// ---- byte sum of the matrix (carry check of the fire-and-forget adds) -------------------------------
+constexpr int SUM_THREADS = 256;
+__global__ void __launch_bounds__(SUM_THREADS) bytesum_kernel(const uint4 *p, uint64_t n16, unsigned long long *out)
 {
-    const unsigned lane = lane_id();
-    const unsigned gw = (blockIdx.x * APPLY_THREADS + threadIdx.x) >> 5;
-    const unsigned n_warps = (gridDim.x * APPLY_THREADS) >> 5;
-    bool carry = false;
-    for (unsigned b = 0; b < P.upd_nb; b++) {
-        for (unsigned r = gw; r < P.upd_nw; r += n_warps) {
-            const unsigned n = P.upd_fill[(size_t)b * P.upd_nw + r] * UBLK;
-            const uint2 *reg = P.upd + ((size_t)b * P.upd_nw + r) * P.upd_region;
-            for (unsigned k = lane; k < n; k += 32 * APPLY_UNROLL) {
-                uint2 e[APPLY_UNROLL];
-                unsigned old[APPLY_UNROLL];
-#pragma unroll
-                for (int u = 0; u < APPLY_UNROLL; u++)
-                    e[u] = k + 32 * u < n ? __ldcs(reg + k + 32 * u) : make_uint2(0u, 0u);
-#pragma unroll
-                for (int u = 0; u < APPLY_UNROLL; u++) {
-                    const uint32_t t = e[u].y & 0xffu, g = e[u].y >> 8;
-                    if (t) {
-                        unsigned *wp = reinterpret_cast<unsigned *>(P.sim8 + (size_t)e[u].x * P.pitch8) + (g >> 2);
-                        old[u] = atomicAdd(wp, t << ((g & 3u) * 8u));
-                    }
-                }
-#pragma unroll
-                for (int u = 0; u < APPLY_UNROLL; u++) {
-                    const uint32_t t = e[u].y & 0xffu, g = e[u].y >> 8;
-                    if (t) carry |= ((old[u] >> ((g & 3u) * 8u)) & 0xffu) + t > 0xffu;
-                }
-            }
-        }
+    unsigned acc4 = 0;                                          // <= 2^32 / 1020 vectors per thread
+    unsigned long long total = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * SUM_THREADS + threadIdx.x; i < n16; i += (uint64_t)gridDim.x * SUM_THREADS) {
+        const uint4 v = __ldcs(p + i);
+        acc4 = __dp4a(v.x, 0x01010101u, acc4); acc4 = __dp4a(v.y, 0x01010101u, acc4);
+        acc4 = __dp4a(v.z, 0x01010101u, acc4); acc4 = __dp4a(v.w, 0x01010101u, acc4);
+        if (acc4 > 0xf0000000u) { total += acc4; acc4 = 0; }
     }
-    if (carry) *P.carry = 1u;
+    total += acc4;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(FULL, total, o);
+    __shared__ unsigned long long part[SUM_THREADS / 32];
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = total;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long t = 0;
+        for (int k = 0; k < SUM_THREADS / 32; k++) t += part[k];
+        if (t) atomicAdd(out, t);
+    }
 }
 
 } // namespace k12s
 
-cudaError_t launch_k12_apply(const ApplyArgs &a, cudaStream_t s)
+// bytes must be a multiple of 16 and p 16-byte aligned (the matrix pitch is)
+cudaError_t launch_bytesum(const uint8_t *p, uint64_t bytes, unsigned long long *out, cudaStream_t s)
 {
-    static int sms = 0;
-    if (!sms) {
-        int dev = 0;
-        cudaError_t e = cudaGetDevice(&dev);
-        if (e != cudaSuccess) return e;
-        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (e != cudaSuccess) return e;
-    }
-    const unsigned warps_per_cta = k12s::APPLY_THREADS / 32;
-    const unsigned want = (a.upd_nw + warps_per_cta - 1) / warps_per_cta;
-    const unsigned grid = std::max(1u, std::min(want, (unsigned)sms * 8u));
-    k12s::apply_kernel<<<grid, k12s::APPLY_THREADS, 0, s>>>(a);
+    const uint64_t n16 = bytes / 16;
+    if (!n16) return cudaSuccess;
+    const unsigned grid = (unsigned)std::min<uint64_t>((n16 + k12s::SUM_THREADS - 1) / k12s::SUM_THREADS, 148ull * 16);
+    k12s::bytesum_kernel<<<grid, k12s::SUM_THREADS, 0, s>>>(reinterpret_cast<const uint4 *>(p), n16, out);
     return cudaGetLastError();
 }
 
@@ -620,7 +567,6 @@ static cudaError_t launch_variant(const K12Args &a, cudaStream_t s)
     // persistent grid: every CTA is resident (the look-back of EMIT relies on it), warps stride over chunks
     const unsigned grid = grid_of<SC, EM, EB, EX>(a.n_own);
     if (!grid) return cudaErrorUnknown;
-    if (a.upd && a.upd_nw != grid * k12s::WARPS) return cudaErrorInvalidValue;
     k12s::stream_kernel<SC, EM, EB, EX><<<grid, k12s::THREADS, 0, s>>>(a);
     return cudaGetLastError();
 }
@@ -637,13 +583,6 @@ static cudaError_t launch_variant(const K12Args &a, cudaStream_t s)
     if (ebwt && exact32)               return CALL(true, false, true, true);                 \
     if (!ebwt && !exact32)             return CALL(true, false, false, false);               \
     return CALL(true, false, false, true);
-
-unsigned k12s_grid_warps(bool score, bool emit, bool ebwt, bool exact32, uint64_t n_own)
-{
-#define LIME_GW(SC, EM, EB, EX) (grid_of<SC, EM, EB, EX>(n_own) * (unsigned)k12s::WARPS)
-    LIME_K12S_DISPATCH(LIME_GW)
-#undef LIME_GW
-}
 
 cudaError_t launch_k12s(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s)
 {

@@ -44,7 +44,7 @@ void lime_destroy(lime_ctx *ctx)
     for (auto &p : ctx->prof_events) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     DevBuf *bufs[] = {&ctx->in_lcp, &ctx->in_da, &ctx->in_ebwt, &ctx->clusters, &ctx->tile_state,
                       &ctx->scalars, &ctx->sim_own, &ctx->sim32, &ctx->large_list, &ctx->long_recs, &ctx->k2_scratch,
-                      &ctx->row_counts, &ctx->cls_out, &ctx->tax_tables, &ctx->upd, &ctx->upd_fill};
+                      &ctx->row_counts, &ctx->cls_out, &ctx->tax_tables};
     for (DevBuf *b : bufs) b->release();
     for (auto &s : ctx->slots) { s.bin.release(); s.pos.release(); }
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);

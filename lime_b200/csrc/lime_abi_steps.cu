@@ -12,7 +12,7 @@ static int run_k2_pass(lime_ctx *ctx, bool ebwt, bool exact32, uint32_t lo, uint
     a.pos_base = ctx->pos_base; a.n_reads = ctx->n_reads; a.n_refs = ctx->n_refs;
     a.sim8 = ctx->d_sim; a.pitch8 = ctx->sim_pitch;
     a.sim32 = ctx->sim32.as<uint32_t>(); a.lo = lo; a.hi = hi;
-    a.carry = scalar<unsigned int>(ctx, SC_CARRY);
+    a.carry = scalar<unsigned int>(ctx, SC_CARRY); a.sum_t = nullptr;
     a.large_count = scalar<unsigned long long>(ctx, SC_LARGE_COUNT);
     a.large_next = scalar<unsigned long long>(ctx, SC_LARGE_NEXT);
     a.n_updates = scalar<unsigned long long>(ctx, SC_NUPDATES);
@@ -54,34 +54,11 @@ static int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, boo
     a.carry = scalar<unsigned int>(ctx, SC_CARRY);
     a.n_updates = scalar<unsigned long long>(ctx, SC_NUPDATES);
     { const char *e = getenv("LIME_DEBUG"); a.dbg = e ? (unsigned)atoi(e) : 0u; }
-    // Two-pass scatter when the matrix is larger than what stays in L2 next to the input stream:
-    // read-range buckets of at most NB slabs, one region per (bucket, warp).  LIME_APPEND=0/1 forces it.
-    a.upd = nullptr; a.upd_fill = nullptr; a.upd_region = 0; a.upd_shift = 31; a.upd_nb = 1; a.upd_nw = 0;
+    // stream kernel: fire-and-forget adds, carries ruled out afterwards by the byte sum (see below)
     {
-        const char *e = getenv("LIME_APPEND"), *k = getenv("LIME_K12");
-        const uint64_t sim_bytes = ctx->sim_rows * ctx->sim_pitch;
-        const bool eligible = !exact32 && !(k && k[0] == 't') && ctx->n_reads && ctx->n_reads < (1u << 31);
-        const bool big = sim_bytes > (48ull << 20), force = e && e[0] == '1', forbid = e && e[0] == '0';
-        const bool use = eligible && !forbid && (big || force);
-        const unsigned nw = use ? k12s_grid_warps(true, emit, ebwt, exact32, ctx->n_own) : 0;
-        if (use && nw) {
-            unsigned sh = 31, nb = 1;
-            if (big || force) {
-                sh = 0;
-                while ((((uint64_t)ctx->n_reads - 1) >> sh) + 1 > 8) sh++;
-                nb = (unsigned)((((uint64_t)ctx->n_reads - 1) >> sh) + 1);
-            }
-            uint64_t region = (uint64_t)((double)n_total * 0.35 / ((double)nw * nb)) + 1;
-            region = std::max<uint64_t>(256, (region + 255) / 256 * 256);
-            const uint64_t cap_bytes = 4ull << 30;
-            while (region > 256 && region * nw * nb * 8 > cap_bytes) region -= 256;
-            if (force && getenv("LIME_APPEND_REGION")) region = std::max(16, atoi(getenv("LIME_APPEND_REGION")) / 16 * 16);
-            CK(ctx->upd.reserve(region * nw * nb * 8), "cudaMalloc update regions");
-            CK(ctx->upd_fill.reserve((uint64_t)nw * nb * 4), "cudaMalloc region fill");
-            CK(cudaMemsetAsync(ctx->upd_fill.p, 0, (uint64_t)nw * nb * 4, ctx->stream), "memset region fill");
-            a.upd = ctx->upd.as<uint2>(); a.upd_fill = ctx->upd_fill.as<unsigned int>();
-            a.upd_region = (uint32_t)region; a.upd_shift = sh; a.upd_nb = nb; a.upd_nw = nw;
-        }
+        const char *k = getenv("LIME_K12");
+        const bool tile_kernel = k && k[0] == 't';
+        a.sum_t = (!exact32 && !tile_kernel) ? scalar<unsigned long long>(ctx, SC_SUMT) : nullptr;
     }
     const uint64_t tiles = k12_num_tiles(ctx->n_own);
     CK(cudaMemsetAsync(ctx->scalars.p, 0, sizeof(unsigned long long) * SC_COUNT, ctx->stream), "memset scalars");
@@ -89,13 +66,6 @@ static int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, boo
     if (tiles) {
         LaunchScope ls(ctx, KID_K12_FUSED);
         CK(launch_k12(a, true, emit, exact32, ctx->stream), "k12_fused launch");
-    }
-    if (tiles && a.upd) {
-        ApplyArgs ap;
-        ap.upd = a.upd; ap.upd_fill = a.upd_fill; ap.upd_region = a.upd_region; ap.upd_nb = a.upd_nb; ap.upd_nw = a.upd_nw;
-        ap.sim8 = a.sim8; ap.pitch8 = a.pitch8; ap.carry = a.carry;
-        LaunchScope ls(ctx, KID_K12_APPLY);
-        CK(launch_k12_apply(ap, ctx->stream), "k12_apply launch");
     }
     CK(cudaMemcpyAsync(sc, ctx->scalars.p, sizeof(unsigned long long) * SC_COUNT, cudaMemcpyDeviceToHost, ctx->stream), "D2H scalars");
     CK(cudaStreamSynchronize(ctx->stream), "k12_fused");
@@ -110,7 +80,7 @@ static int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, boo
         b.cl = nullptr; b.n_cl = 0; b.da = ctx->d_da; b.ebwt = a.ebwt;
         b.pos_base = ctx->pos_base; b.n_reads = ctx->n_reads; b.n_refs = ctx->n_refs;
         b.sim8 = a.sim8; b.pitch8 = a.pitch8; b.sim32 = a.sim32; b.lo = lo; b.hi = hi;
-        b.carry = a.carry; b.large_count = a.long_count; b.large_list = nullptr; b.long_recs = a.long_list;
+        b.carry = a.carry; b.sum_t = a.sum_t; b.large_count = a.long_count; b.large_list = nullptr; b.long_recs = a.long_list;
         b.large_next = scalar<unsigned long long>(ctx, SC_LARGE_NEXT);
         b.n_updates = a.n_updates;
         b.scratch = ctx->k2_scratch.as<uint8_t>(); b.scratch_per_cta = k2_block_scratch_bytes();
@@ -122,6 +92,20 @@ static int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, boo
         CK(cudaMemcpyAsync(sc2, ctx->scalars.p, sizeof(sc2), cudaMemcpyDeviceToHost, ctx->stream), "D2H scalars");
         CK(cudaStreamSynchronize(ctx->stream), "k2_block");
         sc[SC_CARRY] = sc2[SC_CARRY]; sc[SC_NUPDATES] = sc2[SC_NUPDATES];
+    }
+    if (a.sum_t && tiles && ctx->sim_rows * ctx->sim_pitch) {
+        // The matrix was zero before this pass (lime_load) and every add is t << 8k on a 32-bit word:
+        // a carry out of a byte lowers the byte sum by 255 (256 out of the top byte), so
+        // byte sum == total of t  <=>  no cell exceeded 255.
+        unsigned long long chk[2];
+        {
+            LaunchScope ls(ctx, KID_K12_CHECK);
+            CK(launch_bytesum(ctx->d_sim, ctx->sim_rows * ctx->sim_pitch, scalar<unsigned long long>(ctx, SC_BYTESUM), ctx->stream),
+               "k12_check launch");
+        }
+        CK(cudaMemcpyAsync(chk, scalar<unsigned long long>(ctx, SC_SUMT), sizeof(chk), cudaMemcpyDeviceToHost, ctx->stream), "D2H checksum");
+        CK(cudaStreamSynchronize(ctx->stream), "k12_check");
+        if (chk[0] != chk[1]) sc[SC_CARRY] = 1;
     }
     return LIME_OK;
 }

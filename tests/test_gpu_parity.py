@@ -141,20 +141,6 @@ def test_stream_chunk_boundaries(ctx, oracle):
         _check_case(ctx, oracle, case, 16, 0, beta=0.0, fused=True, keep=False)
 
 
-@pytest.mark.parametrize("region", [0, 64])
-def test_two_pass_scatter_forced(ctx, oracle, corpus, monkeypatch, region):
-    """The append + apply scatter (taken by default only for matrices larger than L2) forced on small
-    inputs; region=64 makes the per-warp regions overflow so the direct-add fallback runs too."""
-    monkeypatch.setenv("LIME_APPEND", "1")
-    if region:
-        monkeypatch.setenv("LIME_APPEND_REGION", str(region))
-    for case in corpus:
-        _check_case(ctx, oracle, case, 16, 1, beta=0.0 if case["name"] == "wrap" else 0.25, fused=True, keep=False)
-    case = C.synth_case("synth_medium", 3_000_000, 30_000, 40, seed=33, p_long=2e-5, max_seg=60000)
-    _check_case(ctx, oracle, case, 16, 1, fused=True, keep=False)
-    _check_case(ctx, oracle, case, 12, 0, fused=True, keep=True)
-
-
 def test_sharded_loads_union_equals_whole(ctx, oracle):
     """Position shards with a halo (lime_load n_own / n_halo / pos_base / is_last): the clusters of
     the shards are a partition of the whole array's clusters and the matrices add up mod 256."""
