@@ -193,6 +193,7 @@ struct K2Args {
     unsigned long long *large_count;  // block-path work list
     unsigned long long *large_list;   // indices into cl (cluster-list path) ...
     const lime_cluster *long_recs;    // ... or, when non-null, the records themselves (fused path)
+    uint64_t large_cap;               // entries the work list can hold
     unsigned long long *large_next;   // ticket for the block path
     unsigned long long *n_updates;    // statistics
     uint8_t *scratch; uint64_t scratch_per_cta;

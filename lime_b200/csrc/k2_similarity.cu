@@ -173,7 +173,9 @@ __global__ void __launch_bounds__(BLOCK_THREADS) block_kernel(K2Args P)
     uint32_t *glist = rlist + LIME_SIZE_MAX_BUF;
     const int tid = threadIdx.x;
     const unsigned lane = lane_id(), warp = tid >> 5;
-    const unsigned long long n_large = *P.large_count;
+    // the list may have overflowed (count > cap) and a cluster may exceed the buffers: the host
+    // reports both as errors after the pass, the kernel just stays inside its arrays
+    const unsigned long long n_large = min(*P.large_count, (unsigned long long)P.large_cap);
     unsigned long long updates = 0;
 
     while (true) {
@@ -183,7 +185,8 @@ __global__ void __launch_bounds__(BLOCK_THREADS) block_kernel(K2Args P)
         if (item >= n_large) break;
         const lime_cluster c = P.long_recs ? P.long_recs[item] : P.cl[P.large_list[item]];
         const uint64_t start = c.pStart - P.pos_base;
-        const uint32_t len = (uint32_t)c.len;          // <= 65536, checked by the host
+        if (c.len > LIME_SIZE_MAX_BUF) { __syncthreads(); continue; }    // LIME_ERR_MAXLEN on the host
+        const uint32_t len = (uint32_t)c.len;
         uint32_t cap = 64;
         while (cap < 2 * len) cap <<= 1;
         const uint32_t mask = cap - 1;

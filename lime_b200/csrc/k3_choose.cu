@@ -189,11 +189,14 @@ __device__ __forceinline__ void row_stats(const uint8_t *row, uint32_t chunks, u
 
 // TRIPLES: instead of .res records, export every non-zero cell of the rows as a triple
 // {read id, genome << 8 | count} (no header, no beta test) -- the multi-GPU exchange format.
-template <int LPR, bool TRIPLES>
+// REGS (rows of at most 16 * LPR bytes, LPR <= 8): the CTA's 256 rows are loaded once, all loads of a
+// thread in flight together, and staged in shared memory for the count and the emit step.
+template <int LPR, bool TRIPLES, bool REGS>
 __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
 {
     constexpr unsigned HDR = TRIPLES ? 0u : 1u;
     constexpr int RPW = 32 / LPR;                    // rows a warp handles per step
+    constexpr int STEPS = ROWS_PER_WARP / RPW;
     __shared__ uint32_t s_cnt[TILE_READS];
     __shared__ uint32_t s_off[TILE_READS];
     __shared__ uint32_t s_warp_sum[WARPS];
@@ -212,9 +215,34 @@ __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
     if (!TRIPLES && tile == 0 && tid == 0 && P.bin_cap) { P.bin[0].sim = 0.0f; P.bin[0].idRef = 0; }   // sentinel (:376-382)
 
     // ---- count ----
+    __shared__ uint4 s_rows[REGS ? TILE_READS * LPR : 1];
+    if (REGS) {
+        uint4 held[STEPS];
+#pragma unroll
+        for (int st = 0; st < STEPS; st++) {
+            const uint32_t lr = r0 + warp * ROWS_PER_WARP + st * RPW + grp;
+            held[st] = make_uint4(0, 0, 0, 0);
+            if (lr < n && sub < chunks)
+                held[st] = __ldcs(reinterpret_cast<const uint4 *>(P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8) + sub);
+        }
+#pragma unroll
+        for (int st = 0; st < STEPS; st++) s_rows[(warp * ROWS_PER_WARP + st * RPW + grp) * LPR + sub] = held[st];
+        __syncwarp();
+    }
     for (int k = 0; k < ROWS_PER_WARP; k += RPW) {
         const uint32_t lr = r0 + warp * ROWS_PER_WARP + k + grp;
         uint32_t mx = 0, nnz = 0;
+        if (REGS) {
+            const uint4 v = s_rows[(warp * ROWS_PER_WARP + k + grp) * LPR + sub];
+            const uint32_t m = __vmaxu4(__vmaxu4(v.x, v.y), __vmaxu4(v.z, v.w));
+            mx = max(max(m & 0xff, (m >> 8) & 0xff), max((m >> 16) & 0xff, m >> 24));
+            nnz = __popc(nz_bytes(v.x)) + __popc(nz_bytes(v.y)) + __popc(nz_bytes(v.z)) + __popc(nz_bytes(v.w));
+#pragma unroll
+            for (int o = LPR / 2; o > 0; o >>= 1) {
+                mx = max(mx, __shfl_xor_sync(FULL, mx, o));
+                nnz += __shfl_xor_sync(FULL, nnz, o);
+            }
+        } else
         row_stats<LPR>(P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8, chunks, sub, lr < n, mx, nnz);
         if (sub == 0) {
             const float ns = __fdiv_rn((float)mx, normf);
@@ -266,7 +294,8 @@ __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
         for (uint32_t c0 = 0; c0 < chunks; c0 += LPR) {
             const uint32_t ch = c0 + sub;
             uint4 v = make_uint4(0, 0, 0, 0);
-            if (on && ch < chunks) v = __ldg(reinterpret_cast<const uint4 *>(row) + ch);
+            if (REGS) { if (on) v = s_rows[slot * LPR + sub]; }
+            else if (on && ch < chunks) v = __ldg(reinterpret_cast<const uint4 *>(row) + ch);
             const uint32_t wv[4] = {v.x, v.y, v.z, v.w};
             uint32_t mine = 0;
 #pragma unroll
@@ -334,12 +363,12 @@ static cudaError_t launch_choose_t(const K3Args &a, cudaStream_t s)
     if (tiles == 0) return cudaSuccess;
     const uint64_t chunks = a.pitch8 / 16;
     const unsigned g = (unsigned)tiles;
-    if (chunks <= 1)       k3::choose_kernel<1, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 2)  k3::choose_kernel<2, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 4)  k3::choose_kernel<4, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 8)  k3::choose_kernel<8, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 16) k3::choose_kernel<16, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
-    else                   k3::choose_kernel<32, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
+    if (chunks <= 1)       k3::choose_kernel<1, TRIPLES, true><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 2)  k3::choose_kernel<2, TRIPLES, true><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 4)  k3::choose_kernel<4, TRIPLES, true><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 8)  k3::choose_kernel<8, TRIPLES, true><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 16) k3::choose_kernel<16, TRIPLES, false><<<g, k3::THREADS, 0, s>>>(a);
+    else                   k3::choose_kernel<32, TRIPLES, false><<<g, k3::THREADS, 0, s>>>(a);
     return cudaGetLastError();
 }
 cudaError_t launch_k3_choose(const K3Args &a, cudaStream_t s) { return launch_choose_t<false>(a, s); }

@@ -16,7 +16,7 @@ static int run_k2_pass(lime_ctx *ctx, bool ebwt, bool exact32, uint32_t lo, uint
     a.large_count = scalar<unsigned long long>(ctx, SC_LARGE_COUNT);
     a.large_next = scalar<unsigned long long>(ctx, SC_LARGE_NEXT);
     a.n_updates = scalar<unsigned long long>(ctx, SC_NUPDATES);
-    a.large_list = ctx->large_list.as<unsigned long long>();
+    a.large_list = ctx->large_list.as<unsigned long long>(); a.large_cap = ctx->large_list.cap / 8;
     a.long_recs = nullptr;
     a.scratch = ctx->k2_scratch.as<uint8_t>(); a.scratch_per_cta = k2_block_scratch_bytes();
     CK(cudaMemsetAsync(ctx->scalars.p, 0, sizeof(unsigned long long) * SC_COUNT, ctx->stream), "memset scalars");
@@ -67,6 +67,31 @@ static int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, boo
         LaunchScope ls(ctx, KID_K12_FUSED);
         CK(launch_k12(a, true, emit, exact32, ctx->stream), "k12_fused launch");
     }
+    // the block path over the clusters set aside (it reads their count on the device), the carry
+    // check, then ONE synchronisation for the whole pass
+    if (tiles) {
+        K2Args b;
+        b.cl = nullptr; b.n_cl = 0; b.da = ctx->d_da; b.ebwt = a.ebwt;
+        b.pos_base = ctx->pos_base; b.n_reads = ctx->n_reads; b.n_refs = ctx->n_refs;
+        b.sim8 = a.sim8; b.pitch8 = a.pitch8; b.sim32 = a.sim32; b.lo = lo; b.hi = hi;
+        b.carry = a.carry; b.sum_t = a.sum_t; b.large_count = a.long_count; b.large_list = nullptr; b.long_recs = a.long_list;
+        b.large_cap = a.long_cap;
+        b.large_next = scalar<unsigned long long>(ctx, SC_LARGE_NEXT);
+        b.n_updates = a.n_updates;
+        b.scratch = ctx->k2_scratch.as<uint8_t>(); b.scratch_per_cta = k2_block_scratch_bytes();
+        {
+            LaunchScope ls(ctx, KID_K2_BLOCK);
+            CK(launch_k2_block(b, exact32, ctx->stream, k2_block_grid()), "k2_block launch");
+        }
+        if (a.sum_t && ctx->sim_rows * ctx->sim_pitch) {
+            // The matrix was zero before this pass (lime_load) and every add is t << 8k on a 32-bit
+            // word: a carry out of a byte lowers the byte sum by 255 (256 out of the top byte), so
+            // byte sum == total of t  <=>  no cell exceeded 255.
+            LaunchScope ls(ctx, KID_K12_CHECK);
+            CK(launch_bytesum(ctx->d_sim, ctx->sim_rows * ctx->sim_pitch, scalar<unsigned long long>(ctx, SC_BYTESUM), ctx->stream),
+               "k12_check launch");
+        }
+    }
     CK(cudaMemcpyAsync(sc, ctx->scalars.p, sizeof(unsigned long long) * SC_COUNT, cudaMemcpyDeviceToHost, ctx->stream), "D2H scalars");
     CK(cudaStreamSynchronize(ctx->stream), "k12_fused");
     if ((unsigned)sc[SC_ERR] & 1u)
@@ -75,38 +100,7 @@ static int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, boo
         return fail(ctx, LIME_ERR_MAXLEN, "maximum cluster size is greater than sizeMaxBuf");
     if (sc[SC_LARGE_COUNT] > a.long_cap)
         return fail(ctx, LIME_ERR_NOMEM, "lime_cluster_similarity: long-cluster list overflow");
-    if (sc[SC_LARGE_COUNT]) {
-        K2Args b;
-        b.cl = nullptr; b.n_cl = 0; b.da = ctx->d_da; b.ebwt = a.ebwt;
-        b.pos_base = ctx->pos_base; b.n_reads = ctx->n_reads; b.n_refs = ctx->n_refs;
-        b.sim8 = a.sim8; b.pitch8 = a.pitch8; b.sim32 = a.sim32; b.lo = lo; b.hi = hi;
-        b.carry = a.carry; b.sum_t = a.sum_t; b.large_count = a.long_count; b.large_list = nullptr; b.long_recs = a.long_list;
-        b.large_next = scalar<unsigned long long>(ctx, SC_LARGE_NEXT);
-        b.n_updates = a.n_updates;
-        b.scratch = ctx->k2_scratch.as<uint8_t>(); b.scratch_per_cta = k2_block_scratch_bytes();
-        {
-            LaunchScope ls(ctx, KID_K2_BLOCK);
-            CK(launch_k2_block(b, exact32, ctx->stream, k2_block_grid()), "k2_block launch");
-        }
-        unsigned long long sc2[SC_COUNT];
-        CK(cudaMemcpyAsync(sc2, ctx->scalars.p, sizeof(sc2), cudaMemcpyDeviceToHost, ctx->stream), "D2H scalars");
-        CK(cudaStreamSynchronize(ctx->stream), "k2_block");
-        sc[SC_CARRY] = sc2[SC_CARRY]; sc[SC_NUPDATES] = sc2[SC_NUPDATES];
-    }
-    if (a.sum_t && tiles && ctx->sim_rows * ctx->sim_pitch) {
-        // The matrix was zero before this pass (lime_load) and every add is t << 8k on a 32-bit word:
-        // a carry out of a byte lowers the byte sum by 255 (256 out of the top byte), so
-        // byte sum == total of t  <=>  no cell exceeded 255.
-        unsigned long long chk[2];
-        {
-            LaunchScope ls(ctx, KID_K12_CHECK);
-            CK(launch_bytesum(ctx->d_sim, ctx->sim_rows * ctx->sim_pitch, scalar<unsigned long long>(ctx, SC_BYTESUM), ctx->stream),
-               "k12_check launch");
-        }
-        CK(cudaMemcpyAsync(chk, scalar<unsigned long long>(ctx, SC_SUMT), sizeof(chk), cudaMemcpyDeviceToHost, ctx->stream), "D2H checksum");
-        CK(cudaStreamSynchronize(ctx->stream), "k12_check");
-        if (chk[0] != chk[1]) sc[SC_CARRY] = 1;
-    }
+    if (a.sum_t && sc[SC_SUMT] != sc[SC_BYTESUM]) sc[SC_CARRY] = 1;
     return LIME_OK;
 }
 
