@@ -8,18 +8,20 @@
 // whose head lies in the first 480 positions (the chunk ownership rule of ClusterLCP.cpp:150-202,
 // the last word is look-ahead) and never synchronises with another warp:
 //
-//   phase A  lane = position inside a word: 32 coalesced loads of lcp and da, two ballots per word
-//            give the head word (lcp < alpha) and the read word (da < n_reads); lane k keeps word k.
-//            da / ebwt stay in registers.
+//   stage    the next chunk of lcp / da / ebwt is copied global -> shared with cp.async while the
+//            current chunk is scored (the warp's only DRAM reads: no load latency on the critical path).
+//   phase A  lane = position inside a word: two ballots per word give the head word (lcp < alpha)
+//            and the read word (da < n_reads); lane k keeps word k.
 //   phase B  lane = word: bit-parallel segmented OR-fills (Kogge-Stone inside the word, the same
 //            routine over the 32 words through ballots) decide which positions lie in a segment
 //            that holds both a read and a genome: the "active" word.  No per-cluster loop.
-//   phase C  active positions (about a fifth of the input) are compacted from registers into the
-//            warp's shared-memory stream (id, symbol | cluster-start flag).
+//   phase C  active positions (about a fifth of the input) are compacted from the stage into the
+//            warp's shared-memory stream (id, symbol | cluster-start flag), two lanes per word walking
+//            the set bits of the active word.
 //   phase D  32-lane windows slide over the stream, one lane per position: equal ids are grouped
 //            with __match_any_sync, symbol classes counted with ballots, every read leader meets
-//            every genome leader of its cluster by shuffle; updates (read, genome, t) are queued per
-//            warp and applied to the similarity matrix in bulk.
+//            every genome leader of its cluster by shuffle; updates (read, genome, t) are fire-and-forget
+//            adds to the similarity matrix (carries ruled out afterwards, see add_update).
 //   Clusters longer than 32 positions or running past the look-ahead are rare; they are appended
 //   to a list that the block-path kernel of k2_similarity.cu consumes afterwards.
 //
@@ -70,7 +72,6 @@ struct WarpSmem {
     uint32_t lcp[CH];             // stage of the next chunk, filled by cp.async while this one is scored
     uint32_t da[CH];
     uint8_t  eb[CH];
-    uint4    info[WORDS];         // per word: active, head, exclusive prefix of popc(active), -
     uint32_t cid[SCAP];           // compacted document ids
     uint16_t cmeta[SCAP];         // compacted symbol | start << 8
 };
@@ -91,7 +92,7 @@ __device__ __forceinline__ void cp_async_wait_all()
 }
 
 template <bool SCORE, bool EMIT, bool EBWT, bool EXACT32>
-__global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
+__global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
 {
     __shared__ Smem sm;
     const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
@@ -160,9 +161,7 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
         const int Lt = (int)min((uint64_t)OWN, P.n_own - a);         // owned positions
         const int Lext = (int)min((uint64_t)CH, P.n_total - a);      // real positions in the chunk
 
-        // ---- phase A: head / read words, da and ebwt to registers ------------------------------------
-        uint32_t D[WORDS];
-        uint32_t Eb[WORDS / 4];
+        // ---- phase A: head / read words (lane = position inside a word) ------------------------------
         uint32_t H = 0xffffffffu, R = 0;                             // lanes >= WORDS: beyond the chunk
         if (staged) {
             cp_async_wait_all();
@@ -170,37 +169,37 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
 #pragma unroll
             for (int k = 0; k < WORDS; k++) {
                 const uint32_t l = ws.lcp[32 * k + lane];
-                D[k] = ws.da[32 * k + lane];
+                const uint32_t d = ws.da[32 * k + lane];
                 const uint32_t hk = __ballot_sync(FULL, l < P.alpha);
-                const uint32_t rk = __ballot_sync(FULL, D[k] < P.n_reads);
+                const uint32_t rk = __ballot_sync(FULL, d < P.n_reads);
                 if (w == k) { H = hk; R = rk; }
             }
-            if (SCORE && EBWT) {
-#pragma unroll
-                for (int k = 0; k < WORDS; k++) {
-                    const uint32_t e = ws.eb[32 * k + lane];
-                    if ((k & 3) == 0) Eb[k >> 2] = e; else Eb[k >> 2] |= e << (8 * (k & 3));
-                }
-            }
-            __syncwarp();
         } else {
+            // tail of the buffer (or unaligned buffers): guarded loads, da / ebwt put into the stage
             const uint32_t *pl = P.lcp + a + lane, *pd = P.da + a + lane;
             const uint8_t *pe = P.ebwt + a + lane;
 #pragma unroll
             for (int k = 0; k < WORDS; k++) {
                 const bool ok = 32 * k + (int)lane < Lext;
                 const uint32_t l = ok ? __ldcs(pl + 32 * k) : 0u;              // virtual head
-                D[k] = ok ? __ldcs(pd + 32 * k) : 0xffffffffu;                 // neither read nor real
+                const uint32_t d = ok ? __ldcs(pd + 32 * k) : 0xffffffffu;     // neither read nor real
                 const uint32_t hk = __ballot_sync(FULL, l < P.alpha);
-                const uint32_t rk = __ballot_sync(FULL, D[k] < P.n_reads);
+                const uint32_t rk = __ballot_sync(FULL, d < P.n_reads);
                 if (w == k) { H = hk; R = rk; }
-                if (SCORE && EBWT) {
-                    const uint32_t e = ok ? (uint32_t)__ldcs(pe + 32 * k) : 0u;
-                    if ((k & 3) == 0) Eb[k >> 2] = e; else Eb[k >> 2] |= e << (8 * (k & 3));
+                if (SCORE) {
+                    ws.da[32 * k + lane] = d;
+                    if (EBWT) ws.eb[32 * k + lane] = ok ? __ldcs(pe + 32 * k) : (uint8_t)0;
                 }
             }
+            __syncwarp();
         }
-        staged = stage_issue(c + stride);                            // lands while this chunk is scored
+        // the stage is free once da / ebwt of the active positions are compacted (phase C); without
+        // scoring right away.  The copy lands while this chunk is scored.
+        bool issued = false;
+        auto issue_next = [&]() {
+            if (!issued) { __syncwarp(); staged = stage_issue(c + stride); issued = true; }
+        };
+        if (!SCORE) issue_next();
 
         // ---- phase B: per-word segment flags (lane w owns word w) -------------------------------------
         // A segment holds a read and a genome iff two neighbours inside it differ in kind:
@@ -373,9 +372,11 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
             // (not instantiated: detection without records or scores)
         }
         if (!SCORE) continue;
-        if (P.dbg & 8u) continue;
+        if (P.dbg & 8u) { issue_next(); continue; }
 
         // ---- phase C: compact the active positions into the warp's stream ------------------------------
+        // two lanes per word (16 positions each) walk the set bits of the active word and copy
+        // id / symbol / start flag from the stage: work proportional to the active positions
         int n_act;
         {
             const unsigned cnt = (unsigned)__popc(Aw);
@@ -386,21 +387,22 @@ __global__ void __launch_bounds__(THREADS, 6) stream_kernel(K12Args P)
                 if (lane >= (unsigned)o) incl += n;
             }
             n_act = (int)__shfl_sync(FULL, incl, 31);
-            if (w < WORDS) ws.info[w] = make_uint4(Aw, H, incl - cnt, 0u);
-        }
-        if (n_act == 0) continue;                                         // warp-uniform
-        __syncwarp();
-#pragma unroll
-        for (int k = 0; k < WORDS; k++) {
-            const uint4 inf = ws.info[k];
-            if (inf.x == 0u) continue;                                    // warp-uniform
-            if ((inf.x >> lane) & 1u) {
-                const uint32_t o = inf.z + __popc(inf.x & lt_mask);
-                const uint32_t sym = EBWT ? ((Eb[k >> 2] >> (8 * (k & 3))) & 0xffu) : 0u;
-                ws.cid[o] = D[k];
-                ws.cmeta[o] = (uint16_t)(sym | (((inf.y >> lane) & 1u) << 8));
+            const int ww = lane >> 1, hf = lane & 1;
+            const uint32_t Aq = __shfl_sync(FULL, Aw, ww), Hq = __shfl_sync(FULL, H, ww);
+            uint32_t o = __shfl_sync(FULL, incl - cnt, ww);
+            uint32_t bits = Aq & 0xffffu, hh = Hq & 0xffffu;
+            if (hf) { o += __popc(bits); bits = Aq >> 16; hh = Hq >> 16; }
+            const int p0 = ww * 32 + hf * 16;
+            while (bits) {
+                const int b = __ffs(bits) - 1;
+                bits &= bits - 1;
+                ws.cid[o] = ws.da[p0 + b];
+                ws.cmeta[o] = (uint16_t)((EBWT ? (uint32_t)ws.eb[p0 + b] : 0u) | (((hh >> b) & 1u) << 8));
+                o++;
             }
         }
+        issue_next();                                                     // includes the __syncwarp
+        if (n_act == 0) continue;                                         // warp-uniform
         ws.cid[n_act + lane] = 0xffffffffu;                               // one window of padding: lone starts
         ws.cmeta[n_act + lane] = 0x100u;
         __syncwarp();

@@ -344,6 +344,157 @@ __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
     }
 }
 
+// ---- single pass for rows of at most 128 bytes (n_refs <= 128): sparse-aware ----------------------
+// The CTA's 256 rows are loaded once (all loads of a thread in flight together) into shared memory;
+// a lane turns its 16 cells into a 16-bit non-zero mask and only walks the set bits, so the work is
+// proportional to the non-zero cells (a few per row) instead of n_refs.
+__device__ __forceinline__ uint32_t nz_nibble(uint32_t w)      // bit b: byte b of w is non-zero
+{
+    const uint32_t h = (((w & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w) & 0x80808080u;
+    return ((h >> 7) * 0x01020408u) >> 24;
+}
+__device__ __forceinline__ uint32_t nz_mask16(const uint4 &v)
+{
+    return nz_nibble(v.x) | (nz_nibble(v.y) << 4) | (nz_nibble(v.z) << 8) | (nz_nibble(v.w) << 12);
+}
+
+template <int LPR, bool TRIPLES>
+__global__ void __launch_bounds__(THREADS) choose_sparse_kernel(K3Args P)
+{
+    constexpr unsigned HDR = TRIPLES ? 0u : 1u;
+    constexpr int RPW = 32 / LPR;                    // rows a warp handles per step
+    constexpr int STEPS = ROWS_PER_WARP / RPW;
+    __shared__ uint4 s_rows[TILE_READS * LPR];
+    __shared__ uint32_t s_cnt[TILE_READS];
+    __shared__ uint32_t s_off[TILE_READS];
+    __shared__ uint32_t s_max[TILE_READS];
+    __shared__ uint32_t s_warp_sum[WARPS];
+    __shared__ unsigned s_tile;
+    __shared__ unsigned long long s_excl;
+    const int tid = threadIdx.x;
+    const unsigned lane = lane_id(), warp = tid >> 5;
+    const unsigned sub = lane % LPR, grp = lane / LPR;
+    if (tid == 0) s_tile = atomicAdd(P.tile_counter, 1u);
+    __syncthreads();
+    const unsigned tile = s_tile;
+    const uint32_t n = P.read_end - P.read_begin;
+    const uint32_t r0 = tile * TILE_READS;
+    const uint32_t chunks = (uint32_t)(P.pitch8 / 16);           // <= LPR
+    const float normf = (float)P.norm;
+    const uint8_t *s_bytes = reinterpret_cast<const uint8_t *>(s_rows);
+    if (!TRIPLES && tile == 0 && tid == 0 && P.bin_cap) { P.bin[0].sim = 0.0f; P.bin[0].idRef = 0; }   // sentinel (:376-382)
+
+    // ---- load ----
+    {
+        uint4 held[STEPS];
+#pragma unroll
+        for (int st = 0; st < STEPS; st++) {
+            const uint32_t lr = r0 + warp * ROWS_PER_WARP + st * RPW + grp;
+            held[st] = make_uint4(0, 0, 0, 0);
+            if (lr < n && sub < chunks)
+                held[st] = __ldcs(reinterpret_cast<const uint4 *>(P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8) + sub);
+        }
+#pragma unroll
+        for (int st = 0; st < STEPS; st++) s_rows[(warp * ROWS_PER_WARP + st * RPW + grp) * LPR + sub] = held[st];
+        __syncwarp();
+    }
+    // ---- count ----
+    for (int k = 0; k < ROWS_PER_WARP; k += RPW) {
+        const int slot = warp * ROWS_PER_WARP + k + grp;
+        const uint32_t lr = r0 + slot;
+        uint32_t m16 = nz_mask16(s_rows[slot * LPR + sub]);
+        uint32_t nnz = __popc(m16), mx = 0;
+        while (m16) {
+            const int i = __ffs(m16) - 1;
+            m16 &= m16 - 1;
+            mx = max(mx, (uint32_t)s_bytes[(slot * LPR + sub) * 16 + i]);
+        }
+#pragma unroll
+        for (int o = LPR / 2; o > 0; o >>= 1) {
+            mx = max(mx, __shfl_xor_sync(FULL, mx, o));
+            nnz += __shfl_xor_sync(FULL, nnz, o);
+        }
+        if (sub == 0) {
+            const float ns = __fdiv_rn((float)mx, normf);
+            const bool pass = TRIPLES ? (nnz != 0) : (ns > P.beta);
+            s_cnt[slot] = (lr < n && pass) ? HDR + nnz : 0u;
+            s_max[slot] = mx;
+        }
+    }
+    __syncthreads();
+    // ---- offsets ----
+    const uint32_t c = s_cnt[tid];
+    uint32_t incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(FULL, incl, o);
+        if (lane >= (unsigned)o) incl += v;
+    }
+    if (lane == 31) s_warp_sum[warp] = incl;
+    __syncthreads();
+    uint32_t warp_off = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < WARPS; w++) {
+        const uint32_t x = s_warp_sum[w];
+        if (w < (int)warp) warp_off += x;
+        total += x;
+    }
+    if (warp == 0) {
+        const unsigned long long e = lookback_exclusive(P.tile_state, tile, total);
+        if (lane == 0) {
+            s_excl = e;
+            if (tile == gridDim.x - 1) *P.n_records = HDR + e + total;
+        }
+    }
+    s_off[tid] = warp_off + (incl - c);
+    __syncthreads();
+    const unsigned long long tile_base = HDR + s_excl;
+    if (!TRIPLES) {
+        const uint32_t lr = r0 + tid;
+        if (lr < n) P.pos[lr] = c ? tile_base + s_off[tid] : 0ull;
+    }
+    // ---- emit ----
+    for (int k = 0; k < ROWS_PER_WARP; k += RPW) {
+        const int slot = warp * ROWS_PER_WARP + k + grp;
+        const uint32_t lr = r0 + slot;
+        const bool on = s_cnt[slot] != 0;                       // implies lr < n
+        if (!__any_sync(FULL, on)) continue;
+        const unsigned long long o = tile_base + s_off[slot];
+        uint32_t m16 = on ? nz_mask16(s_rows[slot * LPR + sub]) : 0u;
+        const uint32_t mine = __popc(m16);
+        uint32_t inc2 = mine;
+#pragma unroll
+        for (int x = 1; x < LPR; x <<= 1) {
+            const uint32_t y = __shfl_up_sync(FULL, inc2, x, LPR);
+            if (sub >= (unsigned)x) inc2 += y;
+        }
+        unsigned long long dst = o + HDR + (inc2 - mine);
+        while (m16) {
+            const int i = __ffs(m16) - 1;
+            m16 &= m16 - 1;
+            const uint32_t cell = s_bytes[(slot * LPR + sub) * 16 + i];
+            if (dst < P.bin_cap) {
+                lime_pair_sim rec;
+                if (TRIPLES) {
+                    rec.sim = __uint_as_float(P.read_begin + lr);
+                    rec.idRef = ((16 * sub + i) << 8) | cell;
+                } else {
+                    rec.sim = __fdiv_rn((float)cell, normf);
+                    rec.idRef = 16 * sub + i;
+                }
+                P.bin[dst] = rec;
+            }
+            dst++;
+        }
+        if (!TRIPLES && on && sub == 0 && o < P.bin_cap) {
+            lime_pair_sim h;
+            h.sim = __fdiv_rn((float)s_max[slot], normf);
+            h.idRef = s_cnt[slot] - HDR;
+            P.bin[o] = h;
+        }
+    }
+}
+
 } // namespace k3
 
 uint64_t k3_num_tiles(uint32_t n_reads) { return ((uint64_t)n_reads + k3::TILE_READS - 1) / k3::TILE_READS; }
@@ -363,10 +514,10 @@ static cudaError_t launch_choose_t(const K3Args &a, cudaStream_t s)
     if (tiles == 0) return cudaSuccess;
     const uint64_t chunks = a.pitch8 / 16;
     const unsigned g = (unsigned)tiles;
-    if (chunks <= 1)       k3::choose_kernel<1, TRIPLES, true><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 2)  k3::choose_kernel<2, TRIPLES, true><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 4)  k3::choose_kernel<4, TRIPLES, true><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 8)  k3::choose_kernel<8, TRIPLES, true><<<g, k3::THREADS, 0, s>>>(a);
+    if (chunks <= 1)       k3::choose_sparse_kernel<1, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 2)  k3::choose_sparse_kernel<2, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 4)  k3::choose_sparse_kernel<4, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 8)  k3::choose_sparse_kernel<8, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
     else if (chunks <= 16) k3::choose_kernel<16, TRIPLES, false><<<g, k3::THREADS, 0, s>>>(a);
     else                   k3::choose_kernel<32, TRIPLES, false><<<g, k3::THREADS, 0, s>>>(a);
     return cudaGetLastError();
