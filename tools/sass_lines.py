@@ -9,7 +9,7 @@ rows = list(csv.reader(out.splitlines()))
 hdr = rows[1]
 ix = {h: i for i, h in enumerate(hdr)}
 sass = rows[2:]
-dis = subprocess.run(["nvdisasm", "-g", "-c", cubin], capture_output=True, text=True).stdout.splitlines()
+dis = subprocess.run(["nvdisasm", "-gi", "-c", cubin], capture_output=True, text=True).stdout.splitlines()
 # locate the function
 start = None
 for i, l in enumerate(dis):
@@ -30,6 +30,7 @@ lines = []
 for l in dis[start:end]:
     m = re.search(r'//## File "([^"]+)", line (\d+)', l)
     if m:
+        # consecutive marker lines form an inline chain; the last one is the outermost frame
         cur = (m.group(1).split("/")[-1], int(m.group(2)))
         continue
     if re.match(r"\s+/\*[0-9a-f]{4,}\*/", l):
