@@ -42,7 +42,7 @@ def main():
     tpath = os.path.join(prof, "traffic.json")
     if os.path.exists(tpath):
         traffic = json.load(open(tpath))
-    names = {"fused_kernel": "k12_fused", "choose_kernel": "k3_choose", "count_kernel": "k3_count",
+    names = {"fused_kernel": "k12_fused", "stream_kernel": "k12_fused", "choose_sparse_kernel": "k3_choose", "bytesum_kernel": "k12_check", "choose_kernel": "k3_choose", "count_kernel": "k3_count",
              "emit_kernel": "k3_emit", "classify_kernel": "k3_classify", "block_kernel": "k2_block",
              "warp_kernel": "k2_warp"}
     for f in sorted(os.listdir(go)):
