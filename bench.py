@@ -520,11 +520,11 @@ def run_ours_multi(args, w, world, rank, local):
         job.stats = []
         for s, sh in enumerate(shards):
             job.run_strand(s, sh, w["alpha"], w["beta"], w["ebwt"], w["read_len"])
-        return job.finish(v, None, w["tax_rank"], False, gather=gather)
+        return job.finish(v, None, w["tax_rank"], False, gather="root" if gather else False)
 
     for _ in range(max(args.warmup, 1)):
         out = step()
-    kinds = {chr(t): int((out[0] == t).sum()) for t in np.unique(out[0])}
+    kinds = {chr(t): int((out[0] == t).sum()) for t in np.unique(out[0])} if rank == 0 else None
     stats = list(job.stats)
 
     clocks = ClockSampler(local)
@@ -564,7 +564,7 @@ def run_ours_multi(args, w, world, rank, local):
     step()
     job.timer = lambda name: multi._NoTimer()
     sent = sum(st["triples_sent"] for st in job.stats) * 8
-    phases = torch.tensor([tm.ms.get(k, 0.0) for k in ("compute", "export", "all_to_all", "import", "choose", "scalars", "classify", "gather")],
+    phases = torch.tensor([tm.ms.get(k, 0.0) for k in ("compute", "export", "counts", "all_to_all", "import", "choose", "scalars", "classify", "gather")],
                           device=dev, dtype=torch.float64)
     dist.all_reduce(phases, op=dist.ReduceOp.MAX)
     sent_t = torch.tensor([sent], device=dev, dtype=torch.int64)
@@ -583,7 +583,7 @@ def run_ours_multi(args, w, world, rank, local):
         alg_per_launch = (8 + w["ebwt"]) * (S + 0)
         avg_ms = kern[top]["ms"] / kern[top]["launches"]
         achieved = alg_per_launch / (avg_ms * 1e-3) / 1e9 if top == "k12_fused" else None
-        ph = dict(zip(("compute", "export", "all_to_all", "import", "choose", "scalars", "classify", "gather"), [float(x) for x in phases.tolist()]))
+        ph = dict(zip(("compute", "export", "counts", "all_to_all", "import", "choose", "scalars", "classify", "gather"), [float(x) for x in phases.tolist()]))
         a2a_ms = ph["all_to_all"]
         line = {
             "metric": METRIC, "value": symbols / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -611,6 +611,8 @@ def run_ours_multi(args, w, world, rank, local):
 
 
 def main():
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "WARN"):
+        os.environ["NCCL_DEBUG"] = "NONE"          # NCCL would print its version banner on stdout next to the JSON line
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)

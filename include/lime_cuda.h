@@ -53,7 +53,8 @@ const char *lime_last_error(const lime_ctx *ctx);      /* ctx may be NULL: last 
 const char *lime_version(void);
 
 /* Launch all work of this ctx on an existing cudaStream_t (passed as void*), e.g. the caller's
- * current stream so that its CUDA events bracket our kernels.  NULL restores the ctx's own stream. */
+ * current stream so that its CUDA events bracket our kernels.  NULL restores the ctx's own stream;
+ * pass cudaStreamLegacy ((void*)0x1) for the default stream. */
 int  lime_set_stream(lime_ctx *ctx, void *cuda_stream);
 
 /* Page-locked host memory for buffers handed to lime_load / lime_classify / the copy functions:
@@ -159,12 +160,17 @@ int  lime_sim_import(lime_ctx *ctx, const void *dev_triples, uint64_t n_triples)
  *   v_corRef  [n_refs]     genome -> taxid at tax_rank (FixRank, Classify.cpp:33-89)
  *   m_corRef  [6][n_refs]  genome -> taxid per rank, or NULL      (HIGHER=1, :61-67)
  *   higher    0/1          the HIGHER build variant (:262-302, 672-677)
- * Outputs (host, one per read of the slot range): type 'C'/'U'/'A'/'H', taxid, sim
+ * Outputs (host, one per read of the slot range; NULL: not copied): type 'C'/'U'/'A'/'H', taxid, sim
  * (typeOutput, Tools.h:100-104; Assign, Classify.cpp:157-162).
  */
 int  lime_classify(lime_ctx *ctx, int n_files, uint32_t n_refs,
                    const uint32_t *v_corRef, const uint32_t *m_corRef, int tax_rank, int higher,
                    uint8_t *out_type, uint32_t *out_tax, float *out_sim);
+
+/* The results of the last lime_classify again, into host (LIME_MEM_HOST) or device (LIME_MEM_DEVICE)
+ * buffers of the caller; NULL pointers are skipped.  With lime_classify(..., NULL, NULL, NULL) this
+ * keeps the assignments on the device, e.g. for a gather over NVLink in a multi-GPU job. */
+int  lime_classify_result(lime_ctx *ctx, uint8_t *type, uint32_t *tax, float *sim, int mem);
 
 /* ---- instrumentation ---------------------------------------------------------------------- */
 

@@ -51,6 +51,7 @@ SIGNATURES = {
     "lime_choose_copy": (C.c_int, [vp, C.c_int, vp, vp]),
     "lime_slot_set": (C.c_int, [vp, C.c_int, vp, C.c_uint64, vp, C.c_uint32]),
     "lime_classify": (C.c_int, [vp, C.c_int, C.c_uint32, vp, vp, C.c_int, C.c_int, vp, vp, vp]),
+    "lime_classify_result": (C.c_int, [vp, vp, vp, vp, C.c_int]),
     "lime_launch_count": (C.c_uint64, [vp]),
     "lime_prof_enable": (C.c_int, [vp, C.c_int]),
     "lime_prof_kernels": (C.c_int, []),

@@ -69,7 +69,14 @@ class LimeContext:
 
     # ---- plumbing -----------------------------------------------------------------------
     def set_stream(self, stream_ptr):
-        self._ck(self.lib.lime_set_stream(self.h, C.c_void_p(stream_ptr) if stream_ptr else None))
+        """Run this context's work on a caller stream.  A raw handle of 0 is CUDA's default stream
+        (what torch.cuda.current_stream().cuda_stream returns unless a side stream is current): it is
+        passed as cudaStreamLegacy (0x1) so that our kernels are ordered with the caller's work on it
+        (events, NCCL collectives waited for on it).  None restores the context's own stream."""
+        if stream_ptr is None:
+            self._ck(self.lib.lime_set_stream(self.h, None))
+        else:
+            self._ck(self.lib.lime_set_stream(self.h, C.c_void_p(stream_ptr if stream_ptr else 1)))
 
     def launch_count(self):
         return int(self.lib.lime_launch_count(self.h))
@@ -189,6 +196,18 @@ class LimeContext:
         self._slot_shape[slot] = (bin_.shape[0], pos.shape[0])
 
     # ---- step 3 ---------------------------------------------------------------------------
+    def classify_on_device(self, n_files, n_refs, v_corRef, m_corRef=None, tax_rank=1, higher=False):
+        """lime_classify without the copy to the host; fetch with classify_result_to_device()."""
+        v = np.ascontiguousarray(v_corRef, dtype=np.uint32)
+        m = None if m_corRef is None else np.ascontiguousarray(m_corRef, dtype=np.uint32)
+        self._ck(self.lib.lime_classify(self.h, n_files, n_refs, _ptr(v), _ptr(m), tax_rank,
+                                        1 if higher else 0, None, None, None))
+        return self._slot_shape[0][1]
+
+    def classify_result_to_device(self, type_ptr, tax_ptr, sim_ptr):
+        """Device-to-device copy of the last classification (u8 / u32 / f32 arrays of the slot's reads)."""
+        self._ck(self.lib.lime_classify_result(self.h, C.c_void_p(type_ptr), C.c_void_p(tax_ptr), C.c_void_p(sim_ptr), MEM_DEVICE))
+
     def classify(self, n_files, n_refs, v_corRef, m_corRef=None, tax_rank=1, higher=False):
         n_reads = self._slot_shape[0][1]
         v = np.ascontiguousarray(v_corRef, dtype=np.uint32)

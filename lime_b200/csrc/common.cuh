@@ -164,6 +164,7 @@ struct lime_ctx {
     lime::Slot slots[LIME_MAXFILES];
     lime::DevBuf row_counts;
     lime::DevBuf cls_out;           // classify outputs
+    uint64_t cls_n = 0; bool cls_n_valid = false;
     lime::DevBuf tax_tables;        // v_corRef + m_corRef on device
 
     // instrumentation

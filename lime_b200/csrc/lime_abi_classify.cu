@@ -74,7 +74,25 @@ int lime_classify(lime_ctx *ctx, int n_files, uint32_t n_refs,
         if (out_type) CK(cudaMemcpyAsync(out_type, a.out_type, n_reads, cudaMemcpyDeviceToHost, ctx->stream), "D2H type");
     }
     CK(cudaStreamSynchronize(ctx->stream), "k3_classify");
+    ctx->cls_n = n_reads; ctx->cls_n_valid = !(err & 1u);
     if (err & 1u) return fail(ctx, LIME_ERR_ROWS, "lime_classify: a .res row is not strictly ascending in genome id (or out of range)");
+    return LIME_OK;
+}
+
+int lime_classify_result(lime_ctx *ctx, uint8_t *type, uint32_t *tax, float *sim, int mem)
+{
+    if (!ctx) return LIME_ERR_ARG;
+    if (!ctx->cls_n_valid) return fail(ctx, LIME_ERR_STATE, "lime_classify_result: no classification to return");
+    CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+    const uint64_t n = ctx->cls_n, n16 = (n + 15) / 16 * 16;
+    const uint8_t *base = ctx->cls_out.as<uint8_t>();
+    const cudaMemcpyKind kind = mem == LIME_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+    if (n) {
+        if (tax) CK(cudaMemcpyAsync(tax, base, n * 4, kind, ctx->stream), "copy tax");
+        if (sim) CK(cudaMemcpyAsync(sim, base + n16 * 4, n * 4, kind, ctx->stream), "copy sim");
+        if (type) CK(cudaMemcpyAsync(type, base + n16 * 8, n, kind, ctx->stream), "copy type");
+    }
+    if (mem != LIME_MEM_DEVICE) CK(cudaStreamSynchronize(ctx->stream), "lime_classify_result");
     return LIME_OK;
 }
 

@@ -141,6 +141,34 @@ def test_stream_chunk_boundaries(ctx, oracle):
         _check_case(ctx, oracle, case, 16, 0, beta=0.0, fused=True, keep=False)
 
 
+@pytest.mark.parametrize("n_refs,ebwt_mode,alpha", [(40, 1, 16), (9, 0, 12), (100, 1, 16), (300, 0, 14)])
+def test_export_import_roundtrip(ctx, oracle, n_refs, ebwt_mode, alpha):
+    """lime_sim_export / lime_sim_import (the multi-GPU exchange): the triples of a row range are
+    exactly the non-zero cells of the oracle's matrix, and importing them into a freshly loaded
+    (zero) matrix restores those rows."""
+    import torch
+    case = C.synth_case(f"synth_x{n_refs}", 1_200_000, 12_000, n_refs, seed=51 + n_refs, p_long=2e-5, max_seg=60000)
+    ebwt = case["ebwt"] if ebwt_mode else None
+    ctx.load(case["lcp"], case["da"], ebwt, case["n_reads"], n_refs)
+    ctx.cluster_similarity(alpha, ebwt_mode, False)
+    cl, _ = oracle.cluster_detect(case["lcp"], case["da"], case["n_reads"], alpha)
+    sim_o = oracle.similarity(cl, case["da"], ebwt, case["n_reads"], n_refs)
+    assert np.array_equal(ctx.sim_matrix(), sim_o)
+    lo, hi = 3000, 9500
+    buf = torch.empty(int(np.count_nonzero(sim_o)) + 8, dtype=torch.int64, device="cuda:0")
+    n = ctx.sim_export(lo, hi, buf.data_ptr(), buf.numel())
+    tr = buf[:n].cpu().numpy().view(np.uint32).reshape(-1, 2)
+    r, g, c = tr[:, 0], tr[:, 1] >> 8, tr[:, 1] & 0xFF
+    rr, gg = np.nonzero(sim_o[lo:hi])
+    assert n == rr.shape[0]
+    assert np.array_equal(r, rr + lo) and np.array_equal(g, gg) and np.array_equal(c, sim_o[lo:hi][rr, gg])
+    ctx.load(case["lcp"], case["da"], ebwt, case["n_reads"], n_refs)          # zero matrix
+    ctx.sim_import(buf.data_ptr(), n)
+    want = np.zeros_like(sim_o)
+    want[lo:hi] = sim_o[lo:hi]
+    assert np.array_equal(ctx.sim_matrix(), want)
+
+
 def test_sharded_loads_union_equals_whole(ctx, oracle):
     """Position shards with a halo (lime_load n_own / n_halo / pos_base / is_last): the clusters of
     the shards are a partition of the whole array's clusters and the matrices add up mod 256."""
