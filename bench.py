@@ -477,6 +477,25 @@ class _SyncTimer:
         return T()
 
 
+class _HostTimer:
+    """Per-phase host wall time WITHOUT device synchronisation (where the host thread spends a step)."""
+
+    def __init__(self):
+        self.ms = {}
+
+    def __call__(self, name):
+        outer = self
+
+        class T:
+            def __enter__(self_inner):
+                self_inner.t = time.perf_counter()
+
+            def __exit__(self_inner, *a):
+                outer.ms[name] = outer.ms.get(name, 0.0) + (time.perf_counter() - self_inner.t) * 1e3
+                return False
+        return T()
+
+
 def run_ours_multi(args, w, world, rank, local):
     """N > 1: weak scaling.  Every rank holds one 402 M-position shard of every strand of an
     N x 402 M-position job with N x 2 M reads; see lime_b200/multi.py for the exchange."""
@@ -558,6 +577,16 @@ def run_ours_multi(args, w, world, rank, local):
         clk["window"] = "timed region + untimed repeats of the same step up to 0.7 s (nvidia-smi -lms 50)"
         clocks.stop()
 
+    if os.environ.get("LIME_TRACE"):
+        ht = _HostTimer()
+        job.timer = ht
+        dist.barrier(); torch.cuda.synchronize()
+        t_h = time.perf_counter()
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize()
+        print(f"[trace] rank {rank}: 3 steps {1e3 * (time.perf_counter() - t_h):.2f} ms, host ms per phase (3 steps): "
+              + ", ".join(f"{k}={v:.2f}" for k, v in ht.ms.items()), file=sys.stderr, flush=True)
     # one diagnostic step with synchronising per-phase timers (not part of the timed region)
     tm = _SyncTimer(torch)
     job.timer = tm

@@ -117,6 +117,7 @@ class ShardedJob:
         self.lo, self.hi = self.ranges[rank]
         self.timer = timer or (lambda name: _NoTimer())
         self.sendbuf = self.recvbuf = None
+        self._pinned = {}
         self.stats = []
         self.n_strands = 0
 
@@ -210,7 +211,10 @@ class ShardedJob:
                 if fetch:
                     whole = torch.cat(parts)[:self.n_reads]
                     if whole.is_cuda:
-                        host = torch.empty(whole.shape, dtype=whole.dtype, pin_memory=True)
+                        key = (len(outs), whole.shape[0], whole.dtype)
+                        host = self._pinned.get(key)
+                        if host is None:              # page-locked once, reused by every later job step
+                            host = self._pinned[key] = torch.empty(whole.shape, dtype=whole.dtype, pin_memory=True)
                         host.copy_(whole, non_blocking=True)
                         outs.append(host)
                     else:
@@ -219,7 +223,8 @@ class ShardedJob:
                 torch.cuda.synchronize()
         if not fetch:
             return None, None, None
-        return outs[0].numpy().copy(), outs[1].numpy().view(np.uint32).copy(), outs[2].numpy().view(np.float32).copy()
+        # views of job-owned (page-locked) buffers on CUDA: valid until the next finish()
+        return outs[0].numpy(), outs[1].numpy().view(np.uint32), outs[2].numpy().view(np.float32)
 
 
 class _NoTimer:
