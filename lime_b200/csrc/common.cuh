@@ -206,7 +206,7 @@ int k2_block_grid();
 cudaError_t launch_k2_narrow(const uint32_t *sim32, uint32_t lo, uint32_t hi, uint32_t n_refs,
                              uint8_t *sim8, uint64_t pitch8, cudaStream_t s);
 
-// fused steps 1 + 2a (k12_fused.cu)
+// fused steps 1 + 2a (k12_stream.cu)
 struct K12Args {
     const uint32_t *lcp, *da;
     const uint8_t *ebwt;              // null in DA-only mode
@@ -216,7 +216,6 @@ struct K12Args {
     lime_cluster *out;                // EMIT: records in ascending pStart order
     uint64_t out_cap;
     unsigned long long *tile_state;   // EMIT: look-back descriptors
-    unsigned int *tile_counter;       // EMIT: tile tickets
     unsigned long long *n_clusters;   // device scalars
     unsigned long long *max_len;
     unsigned int *err;                // bit0: halo exhausted
@@ -235,7 +234,6 @@ struct K12Args {
 cudaError_t launch_bytesum(const uint8_t *p, uint64_t bytes, unsigned long long *out, cudaStream_t s);
 cudaError_t launch_k12(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s);
 uint64_t k12_num_tiles(uint64_t n_own);
-cudaError_t launch_k12s(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s);   // k12_stream.cu
 uint64_t k12s_num_chunks(uint64_t n_own);
 uint64_t k12_long_cap(uint64_t n_total);
 

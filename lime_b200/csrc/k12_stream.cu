@@ -586,7 +586,12 @@ static cudaError_t launch_variant(const K12Args &a, cudaStream_t s)
     if (!ebwt && !exact32)             return CALL(true, false, false, false);               \
     return CALL(true, false, false, true);
 
-cudaError_t launch_k12s(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s)
+// look-back descriptors (EMIT) are per chunk; the long-cluster list holds at most one record per
+// 33 positions plus one open tail per chunk
+uint64_t k12_num_tiles(uint64_t n_own) { return k12s_num_chunks(n_own); }
+uint64_t k12_long_cap(uint64_t n_total) { return n_total / (k12s::MAXFAST + 1) + k12_num_tiles(n_total) + 16; }
+
+cudaError_t launch_k12(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s)
 {
     if (a.n_own == 0) return cudaSuccess;
     const bool ebwt = a.ebwt != nullptr;

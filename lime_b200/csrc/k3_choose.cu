@@ -12,6 +12,7 @@
 //                read its record offset in one pass over the matrix; writes pos[].
 // emit_kernel  : re-reads the rows (L2 resident for typical sizes) and writes the records.
 #include "common.cuh"
+#include <algorithm>
 
 namespace lime {
 namespace k3 {
@@ -189,14 +190,12 @@ __device__ __forceinline__ void row_stats(const uint8_t *row, uint32_t chunks, u
 
 // TRIPLES: instead of .res records, export every non-zero cell of the rows as a triple
 // {read id, genome << 8 | count} (no header, no beta test) -- the multi-GPU exchange format.
-// REGS (rows of at most 16 * LPR bytes, LPR <= 8): the CTA's 256 rows are loaded once, all loads of a
-// thread in flight together, and staged in shared memory for the count and the emit step.
-template <int LPR, bool TRIPLES, bool REGS>
+template <int LPR>
 __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
 {
+    constexpr bool TRIPLES = false;      // (triples are exported by export_kernel)
     constexpr unsigned HDR = TRIPLES ? 0u : 1u;
     constexpr int RPW = 32 / LPR;                    // rows a warp handles per step
-    constexpr int STEPS = ROWS_PER_WARP / RPW;
     __shared__ uint32_t s_cnt[TILE_READS];
     __shared__ uint32_t s_off[TILE_READS];
     __shared__ uint32_t s_warp_sum[WARPS];
@@ -215,34 +214,9 @@ __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
     if (!TRIPLES && tile == 0 && tid == 0 && P.bin_cap) { P.bin[0].sim = 0.0f; P.bin[0].idRef = 0; }   // sentinel (:376-382)
 
     // ---- count ----
-    __shared__ uint4 s_rows[REGS ? TILE_READS * LPR : 1];
-    if (REGS) {
-        uint4 held[STEPS];
-#pragma unroll
-        for (int st = 0; st < STEPS; st++) {
-            const uint32_t lr = r0 + warp * ROWS_PER_WARP + st * RPW + grp;
-            held[st] = make_uint4(0, 0, 0, 0);
-            if (lr < n && sub < chunks)
-                held[st] = __ldcs(reinterpret_cast<const uint4 *>(P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8) + sub);
-        }
-#pragma unroll
-        for (int st = 0; st < STEPS; st++) s_rows[(warp * ROWS_PER_WARP + st * RPW + grp) * LPR + sub] = held[st];
-        __syncwarp();
-    }
     for (int k = 0; k < ROWS_PER_WARP; k += RPW) {
         const uint32_t lr = r0 + warp * ROWS_PER_WARP + k + grp;
         uint32_t mx = 0, nnz = 0;
-        if (REGS) {
-            const uint4 v = s_rows[(warp * ROWS_PER_WARP + k + grp) * LPR + sub];
-            const uint32_t m = __vmaxu4(__vmaxu4(v.x, v.y), __vmaxu4(v.z, v.w));
-            mx = max(max(m & 0xff, (m >> 8) & 0xff), max((m >> 16) & 0xff, m >> 24));
-            nnz = __popc(nz_bytes(v.x)) + __popc(nz_bytes(v.y)) + __popc(nz_bytes(v.z)) + __popc(nz_bytes(v.w));
-#pragma unroll
-            for (int o = LPR / 2; o > 0; o >>= 1) {
-                mx = max(mx, __shfl_xor_sync(FULL, mx, o));
-                nnz += __shfl_xor_sync(FULL, nnz, o);
-            }
-        } else
         row_stats<LPR>(P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8, chunks, sub, lr < n, mx, nnz);
         if (sub == 0) {
             const float ns = __fdiv_rn((float)mx, normf);
@@ -294,8 +268,7 @@ __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
         for (uint32_t c0 = 0; c0 < chunks; c0 += LPR) {
             const uint32_t ch = c0 + sub;
             uint4 v = make_uint4(0, 0, 0, 0);
-            if (REGS) { if (on) v = s_rows[slot * LPR + sub]; }
-            else if (on && ch < chunks) v = __ldg(reinterpret_cast<const uint4 *>(row) + ch);
+            if (on && ch < chunks) v = __ldg(reinterpret_cast<const uint4 *>(row) + ch);
             const uint32_t wv[4] = {v.x, v.y, v.z, v.w};
             uint32_t mine = 0;
 #pragma unroll
@@ -358,9 +331,10 @@ __device__ __forceinline__ uint32_t nz_mask16(const uint4 &v)
     return nz_nibble(v.x) | (nz_nibble(v.y) << 4) | (nz_nibble(v.z) << 8) | (nz_nibble(v.w) << 12);
 }
 
-template <int LPR, bool TRIPLES>
+template <int LPR>
 __global__ void __launch_bounds__(THREADS) choose_sparse_kernel(K3Args P)
 {
+    constexpr bool TRIPLES = false;      // (triples are exported by export_kernel)
     constexpr unsigned HDR = TRIPLES ? 0u : 1u;
     constexpr int RPW = 32 / LPR;                    // rows a warp handles per step
     constexpr int STEPS = ROWS_PER_WARP / RPW;
@@ -495,6 +469,52 @@ __global__ void __launch_bounds__(THREADS) choose_sparse_kernel(K3Args P)
     }
 }
 
+// ---- export of the non-zero cells of a row range as triples, in no particular order ----------------
+// (the multi-GPU exchange format {read id, genome << 8 | count}; the importer adds them in any order).
+// A pure streaming pass: one 16-cell chunk per lane, warp-aggregated append with one atomic per warp.
+__global__ void __launch_bounds__(THREADS) export_kernel(K3Args P)
+{
+    const unsigned lane = lane_id();
+    const uint64_t chunks = P.pitch8 / 16;
+    const uint64_t items = (uint64_t)(P.read_end - P.read_begin) * chunks;
+    const uint64_t stride = (uint64_t)gridDim.x * THREADS;
+    const uint64_t rounds = (items + stride - 1) / stride;
+    uint64_t i = (uint64_t)blockIdx.x * THREADS + threadIdx.x;
+    for (uint64_t it = 0; it < rounds; it++, i += stride) {          // whole warps stay in the loop together
+        uint4 v = make_uint4(0, 0, 0, 0);
+        uint32_t row = 0, ch = 0;
+        if (i < items) {
+            row = (uint32_t)(i / chunks); ch = (uint32_t)(i % chunks);
+            v = __ldcs(reinterpret_cast<const uint4 *>(P.sim8 + (size_t)(P.read_begin + row) * P.pitch8) + ch);
+        }
+        uint32_t m16 = nz_mask16(v);
+        const uint32_t cnt = __popc(m16);
+        if (!__any_sync(FULL, cnt != 0)) continue;
+        uint32_t incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(FULL, incl, o);
+            if (lane >= (unsigned)o) incl += y;
+        }
+        unsigned long long base = 0;
+        if (lane == 31) base = atomicAdd(P.n_records, (unsigned long long)incl);
+        base = __shfl_sync(FULL, base, 31) + (incl - cnt);
+        const uint32_t wv[4] = {v.x, v.y, v.z, v.w};
+        while (m16) {
+            const int b = __ffs(m16) - 1;
+            m16 &= m16 - 1;
+            const uint32_t cell = (wv[b >> 2] >> ((b & 3) * 8)) & 0xffu;
+            if (base < P.bin_cap) {
+                lime_pair_sim rec;
+                rec.sim = __uint_as_float(P.read_begin + row);
+                rec.idRef = ((16 * ch + b) << 8) | cell;
+                P.bin[base] = rec;
+            }
+            base++;
+        }
+    }
+}
+
 } // namespace k3
 
 uint64_t k3_num_tiles(uint32_t n_reads) { return ((uint64_t)n_reads + k3::TILE_READS - 1) / k3::TILE_READS; }
@@ -507,23 +527,28 @@ cudaError_t launch_k3_count(const K3Args &a, cudaStream_t s)
     return cudaGetLastError();
 }
 
-template <bool TRIPLES>
-static cudaError_t launch_choose_t(const K3Args &a, cudaStream_t s)
+cudaError_t launch_k3_choose(const K3Args &a, cudaStream_t s)
 {
     const uint64_t tiles = k3_num_tiles(a.read_end - a.read_begin);
     if (tiles == 0) return cudaSuccess;
     const uint64_t chunks = a.pitch8 / 16;
     const unsigned g = (unsigned)tiles;
-    if (chunks <= 1)       k3::choose_sparse_kernel<1, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 2)  k3::choose_sparse_kernel<2, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 4)  k3::choose_sparse_kernel<4, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 8)  k3::choose_sparse_kernel<8, TRIPLES><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 16) k3::choose_kernel<16, TRIPLES, false><<<g, k3::THREADS, 0, s>>>(a);
-    else                   k3::choose_kernel<32, TRIPLES, false><<<g, k3::THREADS, 0, s>>>(a);
+    if (chunks <= 1)       k3::choose_sparse_kernel<1><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 2)  k3::choose_sparse_kernel<2><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 4)  k3::choose_sparse_kernel<4><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 8)  k3::choose_sparse_kernel<8><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 16) k3::choose_kernel<16><<<g, k3::THREADS, 0, s>>>(a);
+    else                   k3::choose_kernel<32><<<g, k3::THREADS, 0, s>>>(a);
     return cudaGetLastError();
 }
-cudaError_t launch_k3_choose(const K3Args &a, cudaStream_t s) { return launch_choose_t<false>(a, s); }
-cudaError_t launch_k3_export(const K3Args &a, cudaStream_t s) { return launch_choose_t<true>(a, s); }
+cudaError_t launch_k3_export(const K3Args &a, cudaStream_t s)
+{
+    const uint64_t items = (uint64_t)(a.read_end - a.read_begin) * (a.pitch8 / 16);
+    if (items == 0) return cudaSuccess;
+    const uint64_t want = (items + k3::THREADS - 1) / k3::THREADS;
+    k3::export_kernel<<<(unsigned)std::min<uint64_t>(want, 148ull * 8), k3::THREADS, 0, s>>>(a);
+    return cudaGetLastError();
+}
 
 // adds triples {read, genome << 8 | count} into uint8 cells (wrapping); keys unique within one call
 cudaError_t launch_k3_import(const lime_pair_sim *tr, uint64_t n, uint8_t *sim8, uint64_t pitch8, uint32_t n_reads,

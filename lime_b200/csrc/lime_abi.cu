@@ -152,7 +152,6 @@ int lime_cluster_detect(lime_ctx *ctx, uint32_t alpha, uint64_t *n_clusters, uin
         a.alpha = alpha; a.n_reads = ctx->n_reads; a.n_refs = ctx->n_refs;
         a.out = ctx->clusters.as<lime_cluster>(); a.out_cap = ctx->cl_cap;
         a.tile_state = ctx->tile_state.as<unsigned long long>();
-        a.tile_counter = scalar<unsigned int>(ctx, SC_TILE_COUNTER);
         a.n_clusters = scalar<unsigned long long>(ctx, SC_NCLUSTERS);
         a.max_len = scalar<unsigned long long>(ctx, SC_MAXLEN);
         a.err = scalar<unsigned int>(ctx, SC_ERR);

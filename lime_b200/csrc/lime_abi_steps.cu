@@ -42,7 +42,6 @@ static int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, boo
     a.alpha = alpha; a.n_reads = ctx->n_reads; a.n_refs = ctx->n_refs;
     a.out = ctx->clusters.as<lime_cluster>(); a.out_cap = emit ? ctx->cl_cap : 0;
     a.tile_state = ctx->tile_state.as<unsigned long long>();
-    a.tile_counter = scalar<unsigned int>(ctx, SC_TILE_COUNTER);
     a.n_clusters = scalar<unsigned long long>(ctx, SC_NCLUSTERS);
     a.max_len = scalar<unsigned long long>(ctx, SC_MAXLEN);
     a.err = scalar<unsigned int>(ctx, SC_ERR);
@@ -54,12 +53,8 @@ static int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, boo
     a.carry = scalar<unsigned int>(ctx, SC_CARRY);
     a.n_updates = scalar<unsigned long long>(ctx, SC_NUPDATES);
     { const char *e = getenv("LIME_DEBUG"); a.dbg = e ? (unsigned)atoi(e) : 0u; }
-    // stream kernel: fire-and-forget adds, carries ruled out afterwards by the byte sum (see below)
-    {
-        const char *k = getenv("LIME_K12");
-        const bool tile_kernel = k && k[0] == 't';
-        a.sum_t = (!exact32 && !tile_kernel) ? scalar<unsigned long long>(ctx, SC_SUMT) : nullptr;
-    }
+    // fire-and-forget adds; carries are ruled out after the pass by the byte sum (see below)
+    a.sum_t = !exact32 ? scalar<unsigned long long>(ctx, SC_SUMT) : nullptr;
     const uint64_t tiles = k12_num_tiles(ctx->n_own);
     CK(cudaMemsetAsync(ctx->scalars.p, 0, sizeof(unsigned long long) * SC_COUNT, ctx->stream), "memset scalars");
     if (emit) CK(cudaMemsetAsync(ctx->tile_state.p, 0, std::max<uint64_t>(tiles, 1) * 8, ctx->stream), "memset tile state");
