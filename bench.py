@@ -539,11 +539,14 @@ def run_ours_multi(args, w, world, rank, local):
         job.stats = []
         for s, sh in enumerate(shards):
             job.run_strand(s, sh, w["alpha"], w["beta"], w["ebwt"], w["read_len"])
-        return job.finish(v, None, w["tax_rank"], False, gather="root" if gather else False)
+        # every rank fetches the assignments of the reads it owns (9 B per read, as at N = 1)
+        return job.finish(v, None, w["tax_rank"], False, gather=False)
 
     for _ in range(max(args.warmup, 1)):
         out = step()
-    kinds = {chr(t): int((out[0] == t).sum()) for t in np.unique(out[0])} if rank == 0 else None
+    cnt = torch.tensor([int((out[0] == ord(c)).sum()) for c in "CUAH"], device=dev, dtype=torch.int64)
+    dist.all_reduce(cnt)
+    kinds = {c: int(x) for c, x in zip("CUAH", cnt.tolist()) if x}
     stats = list(job.stats)
 
     clocks = ClockSampler(local)
@@ -620,7 +623,7 @@ def run_ours_multi(args, w, world, rank, local):
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": w["name"] + f"; x{world} weak scaling: {world} position shards of {S} symbols per strand, {n_reads} reads",
                        "l2": "inputs (3.6 GB per strand and GPU) are larger than L2; no flush needed",
-                       "parallelism": f"position-sharded x{world}, halo {HALO}, triples all-to-all by read owner",
+                       "parallelism": f"position-sharded x{world}, halo {HALO}, triples all-to-all by read owner; every rank copies the assignments of its own read range to its host",
                        "symbols_per_step": symbols, "reads_per_step": n_reads, "strand_stats": stats, "assignments": kinds},
             "reads_per_s": n_reads / (ms_step * 1e-3),
             "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",

@@ -16,8 +16,7 @@
 //            routine over the 32 words through ballots) decide which positions lie in a segment
 //            that holds both a read and a genome: the "active" word.  No per-cluster loop.
 //   phase C  active positions (about a fifth of the input) are compacted from the stage into the
-//            warp's shared-memory stream (id, symbol | cluster-start flag), two lanes per word walking
-//            the set bits of the active word.
+//            warp's shared-memory stream (id, symbol | cluster-start flag), word by word.
 //   phase D  32-lane windows slide over the stream, one lane per position: equal ids are grouped
 //            with __match_any_sync, symbol classes counted with ballots, every read leader meets
 //            every genome leader of its cluster by shuffle; updates (read, genome, t) are fire-and-forget
@@ -68,8 +67,9 @@ __device__ __forceinline__ uint32_t mask_lt(int k)   // bits [0, k), k may be <=
     return k <= 0 ? 0u : (k >= 32 ? 0xffffffffu : ((1u << k) - 1u));
 }
 
-struct WarpSmem {
+struct alignas(16) WarpSmem {
     uint32_t lcp[CH];             // stage of the next chunk, filled by cp.async while this one is scored
+                                  // (dead after phase A: phase C keeps its per-word broadcast there)
     uint32_t da[CH];
     uint8_t  eb[CH];
     uint32_t cid[SCAP];           // compacted document ids
@@ -375,8 +375,9 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
         if (P.dbg & 8u) { issue_next(); continue; }
 
         // ---- phase C: compact the active positions into the warp's stream ------------------------------
-        // two lanes per word (16 positions each) walk the set bits of the active word and copy
-        // id / symbol / start flag from the stage: work proportional to the active positions
+        // lane = position inside a word again: per word one broadcast of (active, head, offset), the
+        // active lanes copy id / symbol / start flag from the stage; words without active positions
+        // are skipped (warp-uniform)
         int n_act;
         {
             const unsigned cnt = (unsigned)__popc(Aw);
@@ -387,18 +388,20 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
                 if (lane >= (unsigned)o) incl += n;
             }
             n_act = (int)__shfl_sync(FULL, incl, 31);
-            const int ww = lane >> 1, hf = lane & 1;
-            const uint32_t Aq = __shfl_sync(FULL, Aw, ww), Hq = __shfl_sync(FULL, H, ww);
-            uint32_t o = __shfl_sync(FULL, incl - cnt, ww);
-            uint32_t bits = Aq & 0xffffu, hh = Hq & 0xffffu;
-            if (hf) { o += __popc(bits); bits = Aq >> 16; hh = Hq >> 16; }
-            const int p0 = ww * 32 + hf * 16;
-            while (bits) {
-                const int b = __ffs(bits) - 1;
-                bits &= bits - 1;
-                ws.cid[o] = ws.da[p0 + b];
-                ws.cmeta[o] = (uint16_t)((EBWT ? (uint32_t)ws.eb[p0 + b] : 0u) | (((hh >> b) & 1u) << 8));
-                o++;
+            uint4 *info = reinterpret_cast<uint4 *>(ws.lcp);      // per word: active, head, exclusive prefix, -
+            if (w < WORDS) info[w] = make_uint4(Aw, H, incl - cnt, 0u);
+            __syncwarp();
+            if (n_act) {
+#pragma unroll
+                for (int k = 0; k < WORDS; k++) {
+                    const uint4 inf = info[k];
+                    if (inf.x == 0u) continue;
+                    if ((inf.x >> lane) & 1u) {
+                        const uint32_t o = inf.z + __popc(inf.x & lt_mask);
+                        ws.cid[o] = ws.da[32 * k + lane];
+                        ws.cmeta[o] = (uint16_t)((EBWT ? (uint32_t)ws.eb[32 * k + lane] : 0u) | (((inf.y >> lane) & 1u) << 8));
+                    }
+                }
             }
         }
         issue_next();                                                     // includes the __syncwarp
