@@ -472,23 +472,28 @@ __global__ void __launch_bounds__(THREADS) choose_sparse_kernel(K3Args P)
 // ---- export of the non-zero cells of a row range as triples, in no particular order ----------------
 // (the multi-GPU exchange format {read id, genome << 8 | count}; the importer adds them in any order).
 // A pure streaming pass: one 16-cell chunk per lane, warp-aggregated append with one atomic per warp.
+constexpr int EXPORT_UNROLL = 8;          // chunks per lane and round: one append atomic per 4 KB of matrix
 __global__ void __launch_bounds__(THREADS) export_kernel(K3Args P)
 {
     const unsigned lane = lane_id();
     const uint64_t chunks = P.pitch8 / 16;
     const uint64_t items = (uint64_t)(P.read_end - P.read_begin) * chunks;
-    const uint64_t stride = (uint64_t)gridDim.x * THREADS;
-    const uint64_t rounds = (items + stride - 1) / stride;
-    uint64_t i = (uint64_t)blockIdx.x * THREADS + threadIdx.x;
-    for (uint64_t it = 0; it < rounds; it++, i += stride) {          // whole warps stay in the loop together
-        uint4 v = make_uint4(0, 0, 0, 0);
-        uint32_t row = 0, ch = 0;
-        if (i < items) {
-            row = (uint32_t)(i / chunks); ch = (uint32_t)(i % chunks);
-            v = __ldcs(reinterpret_cast<const uint4 *>(P.sim8 + (size_t)(P.read_begin + row) * P.pitch8) + ch);
+    const uint64_t per_warp = 32ull * EXPORT_UNROLL;
+    const uint64_t n_groups = (items + per_warp - 1) / per_warp;
+    const uint64_t warp_global = ((uint64_t)blockIdx.x * THREADS + threadIdx.x) >> 5;
+    const uint64_t warp_stride = ((uint64_t)gridDim.x * THREADS) >> 5;
+    const uint4 *base16 = reinterpret_cast<const uint4 *>(P.sim8 + (size_t)P.read_begin * P.pitch8);   // rows are contiguous
+    for (uint64_t grp = warp_global; grp < n_groups; grp += warp_stride) {
+        uint4 v[EXPORT_UNROLL];
+        uint32_t m[EXPORT_UNROLL];
+        uint32_t cnt = 0;
+#pragma unroll
+        for (int u = 0; u < EXPORT_UNROLL; u++) {
+            const uint64_t i = grp * per_warp + 32ull * u + lane;
+            v[u] = i < items ? __ldcs(base16 + i) : make_uint4(0, 0, 0, 0);
         }
-        uint32_t m16 = nz_mask16(v);
-        const uint32_t cnt = __popc(m16);
+#pragma unroll
+        for (int u = 0; u < EXPORT_UNROLL; u++) { m[u] = nz_mask16(v[u]); cnt += __popc(m[u]); }
         if (!__any_sync(FULL, cnt != 0)) continue;
         uint32_t incl = cnt;
 #pragma unroll
@@ -496,21 +501,28 @@ __global__ void __launch_bounds__(THREADS) export_kernel(K3Args P)
             const uint32_t y = __shfl_up_sync(FULL, incl, o);
             if (lane >= (unsigned)o) incl += y;
         }
-        unsigned long long base = 0;
-        if (lane == 31) base = atomicAdd(P.n_records, (unsigned long long)incl);
-        base = __shfl_sync(FULL, base, 31) + (incl - cnt);
-        const uint32_t wv[4] = {v.x, v.y, v.z, v.w};
-        while (m16) {
-            const int b = __ffs(m16) - 1;
-            m16 &= m16 - 1;
-            const uint32_t cell = (wv[b >> 2] >> ((b & 3) * 8)) & 0xffu;
-            if (base < P.bin_cap) {
-                lime_pair_sim rec;
-                rec.sim = __uint_as_float(P.read_begin + row);
-                rec.idRef = ((16 * ch + b) << 8) | cell;
-                P.bin[base] = rec;
+        unsigned long long dst = 0;
+        if (lane == 31) dst = atomicAdd(P.n_records, (unsigned long long)incl);
+        dst = __shfl_sync(FULL, dst, 31) + (incl - cnt);
+#pragma unroll
+        for (int u = 0; u < EXPORT_UNROLL; u++) {
+            if (!m[u]) continue;
+            const uint64_t i = grp * per_warp + 32ull * u + lane;
+            const uint32_t row = (uint32_t)(i / chunks), ch = (uint32_t)(i % chunks);
+            const uint32_t wv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+            uint32_t mm = m[u];
+            while (mm) {
+                const int b = __ffs(mm) - 1;
+                mm &= mm - 1;
+                const uint32_t cell = (wv[b >> 2] >> ((b & 3) * 8)) & 0xffu;
+                if (dst < P.bin_cap) {
+                    lime_pair_sim rec;
+                    rec.sim = __uint_as_float(P.read_begin + row);
+                    rec.idRef = ((16 * ch + b) << 8) | cell;
+                    P.bin[dst] = rec;
+                }
+                dst++;
             }
-            base++;
         }
     }
 }
@@ -545,7 +557,7 @@ cudaError_t launch_k3_export(const K3Args &a, cudaStream_t s)
 {
     const uint64_t items = (uint64_t)(a.read_end - a.read_begin) * (a.pitch8 / 16);
     if (items == 0) return cudaSuccess;
-    const uint64_t want = (items + k3::THREADS - 1) / k3::THREADS;
+    const uint64_t want = (items + (uint64_t)k3::THREADS * k3::EXPORT_UNROLL - 1) / ((uint64_t)k3::THREADS * k3::EXPORT_UNROLL);
     k3::export_kernel<<<(unsigned)std::min<uint64_t>(want, 148ull * 8), k3::THREADS, 0, s>>>(a);
     return cudaGetLastError();
 }

@@ -193,7 +193,7 @@ class ShardedJob:
             else:
                 typ, tax, sim = self.be.classify(self.n_strands, self.n_refs, v, m, tax_rank, higher)
         if not gather or self.world == 1:
-            return np.array(typ), np.array(tax), np.array(sim)
+            return typ, tax, sim          # the backend's (page-locked, context-owned) arrays: valid until the next classify
         with self.timer("gather"):
             # three contiguous all-gathers (type u8, taxid u32, sim f32 bits); every rank owns `per`
             # reads except possibly the last ones, so the padded concatenation IS the read order
