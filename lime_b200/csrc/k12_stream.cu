@@ -16,7 +16,7 @@
 //            routine over the 32 words through ballots) decide which positions lie in a segment
 //            that holds both a read and a genome: the "active" word.  No per-cluster loop.
 //   phase C  active positions (about a fifth of the input) are compacted from the stage into the
-//            warp's shared-memory stream (id, symbol | cluster-start flag), word by word.
+//            warp's shared-memory stream (id, symbol class | cluster-start flag), word by word.
 //   phase D  32-lane windows slide over the stream, one lane per position: equal ids are grouped
 //            with __match_any_sync, symbol classes counted with ballots, every read leader meets
 //            every genome leader of its cluster by shuffle; updates (read, genome, t) are fire-and-forget
@@ -73,7 +73,7 @@ struct alignas(16) WarpSmem {
     uint32_t da[CH];
     uint8_t  eb[CH];
     uint32_t cid[SCAP];           // compacted document ids
-    uint16_t cmeta[SCAP];         // compacted symbol | start << 8
+    uint16_t cmeta[SCAP];         // compacted symbol class | start << 8
 };
 struct Smem {
     WarpSmem w[WARPS];
@@ -81,10 +81,9 @@ struct Smem {
 };
 
 // 16-byte asynchronous global -> shared copy (LDGSTS), L1 bypassed
-__device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
+__device__ __forceinline__ void cp_async16(unsigned smem_addr, const void *gmem)
 {
-    const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gmem) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all()
 {
@@ -108,7 +107,7 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
     const uint64_t stride = (uint64_t)gridDim.x * WARPS;
     unsigned cl_count = 0;                                    // clusters counted by this lane
     unsigned long long max_len = 0;                           // longest cluster seen by this lane
-    unsigned long long updates = 0;                           // updates issued by this lane
+    unsigned updates = 0;                                     // updates issued by this lane (a lane sees < 2^32 pairs)
 
     SimAcc acc;
     acc.sim8 = P.sim8; acc.pitch8 = P.pitch8; acc.sim32 = P.sim32; acc.lo = P.lo; acc.hi = P.hi;
@@ -138,21 +137,34 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
     // the buffer and unaligned buffers are loaded synchronously.
     const bool aligned = ((reinterpret_cast<uintptr_t>(P.lcp) | reinterpret_cast<uintptr_t>(P.da) |
                            (SCORE && EBWT ? reinterpret_cast<uintptr_t>(P.ebwt) : 0)) & 15u) == 0;
+    // per-lane source / destination of its 16-byte pieces (piece k of lcp / da is 512 bytes further)
+    const char *g_lcp = reinterpret_cast<const char *>(P.lcp) + 16 * lane;
+    const char *g_da = reinterpret_cast<const char *>(P.da) + 16 * lane;
+    const char *g_eb = reinterpret_cast<const char *>(P.ebwt) + 16 * lane;
+    const unsigned s_lcp = (unsigned)__cvta_generic_to_shared(&ws.lcp[4 * lane]);
+    const unsigned s_da = (unsigned)__cvta_generic_to_shared(&ws.da[4 * lane]);
+    const unsigned s_eb = (unsigned)__cvta_generic_to_shared(&ws.eb[16 * lane]);
     auto stage_issue = [&](uint64_t cc) -> bool {
         if (cc >= n_chunks) return false;
         const uint64_t aa = cc * OWN;
         if (!aligned || aa + CH > P.n_total) return false;
+        const char *pl = g_lcp + 4 * aa, *pd = g_da + 4 * aa;
 #pragma unroll
         for (int k = 0; k < CH / 128; k++) {
-            cp_async16(&ws.lcp[128 * k + 4 * lane], P.lcp + aa + 128 * k + 4 * lane);
-            cp_async16(&ws.da[128 * k + 4 * lane], P.da + aa + 128 * k + 4 * lane);
+            cp_async16(s_lcp + 512 * k, pl + 512 * k);
+            cp_async16(s_da + 512 * k, pd + 512 * k);
         }
         if (SCORE && EBWT) {
+            const char *pe = g_eb + aa;
 #pragma unroll
-            for (int k = 0; k < CH / 512; k++) cp_async16(&ws.eb[512 * k + 16 * lane], P.ebwt + aa + 512 * k + 16 * lane);
+            for (int k = 0; k < CH / 512; k++) cp_async16(s_eb + 512 * k, pe + 512 * k);
         }
         return true;
     };
+    // masks of a whole chunk (every chunk but the last ones of the buffer)
+    const uint32_t V_full = w < WORDS ? 0xffffffffu : 0u;
+    const uint32_t XM_full = w < WORDS - 1 ? 0xffffffffu : (w == WORDS - 1 ? 0x7fffffffu : 0u);
+    const uint32_t BL_full = mask_lt(OWN - w * 32);
     const uint64_t c_first = (uint64_t)blockIdx.x * WARPS + warp;
     bool staged = stage_issue(c_first);
 
@@ -204,10 +216,11 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
         // ---- phase B: per-word segment flags (lane w owns word w) -------------------------------------
         // A segment holds a read and a genome iff two neighbours inside it differ in kind:
         // X_i = (read_i != read_{i+1}) and i+1 is not a head.  One flag to spread over the segment.
-        const uint32_t V = mask_lt(Lext - w * 32);
+        const bool whole = Lext == CH && Lt == OWN;                       // warp-uniform
+        const uint32_t V = whole ? V_full : mask_lt(Lext - w * 32);
         const uint32_t Hup = __shfl_down_sync(FULL, H, 1), Rup = __shfl_down_sync(FULL, R, 1);
         const uint32_t Hn = (H >> 1) | (Hup << 31), Rn = (R >> 1) | (Rup << 31);
-        const uint32_t X = (R ^ Rn) & ~Hn & mask_lt(Lext - w * 32 - 1);   // the last position has no neighbour
+        const uint32_t X = (R ^ Rn) & ~Hn & (whole ? XM_full : mask_lt(Lext - w * 32 - 1));   // the last position has no neighbour
         const bool hasHead = H != 0;
         const uint32_t lowmask = hasHead ? ((H & (0u - H)) - 1u) : 0xffffffffu;           // below the first head
         const uint32_t himask = hasHead ? (0xffffffffu << (31 - __clz(H))) : 0xffffffffu; // at / above the last head
@@ -226,7 +239,7 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
         // first head at or after Lt (E), last head before Lt (hl)
         int E = NONE, hl = -1;
         {
-            const uint32_t below_lt = mask_lt(Lt - w * 32);
+            const uint32_t below_lt = whole ? BL_full : mask_lt(Lt - w * 32);
             const uint32_t he = w < WORDS ? (H & ~below_lt) : 0u, hb = H & below_lt;   // lanes >= WORDS own no word
             const uint32_t Em = __ballot_sync(FULL, he != 0), Bm = __ballot_sync(FULL, hb != 0);
             if (Em) {
@@ -399,7 +412,7 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
                     if ((inf.x >> lane) & 1u) {
                         const uint32_t o = inf.z + __popc(inf.x & lt_mask);
                         ws.cid[o] = ws.da[32 * k + lane];
-                        ws.cmeta[o] = (uint16_t)((EBWT ? (uint32_t)ws.eb[32 * k + lane] : 0u) | (((inf.y >> lane) & 1u) << 8));
+                        ws.cmeta[o] = (uint16_t)((EBWT ? (uint32_t)sm.cls[ws.eb[32 * k + lane]] : 0u) | (((inf.y >> lane) & 1u) << 8));
                     }
                 }
             }
@@ -443,7 +456,7 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
             if (!EBWT) {
                 vec.x = (unsigned)__popc(mm);
             } else {
-                const uint32_t cls = sm.cls[meta & 0xffu];
+                const uint32_t cls = meta & 0xffu;
                 const unsigned c0 = __ballot_sync(FULL, (cls & 1u) != 0), c1 = __ballot_sync(FULL, (cls & 2u) != 0);
                 const unsigned rest = __ballot_sync(FULL, cls >= 4u && id != 0xffffffffu);
                 vec.x = (unsigned)__popc(mm & ~c1 & ~c0) | ((unsigned)__popc(mm & ~c1 & c0) << 8) |
@@ -494,19 +507,19 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
     // ---- totals of this warp: one atomic per warp and scalar -------------------------------------------
     {
         unsigned c2 = cl_count;
-        unsigned long long mx = max_len;
+        unsigned long long mx = max_len, up = updates, tt = t_total;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             c2 += __shfl_xor_sync(FULL, c2, o);
             mx = max(mx, __shfl_xor_sync(FULL, mx, o));
-            updates += __shfl_xor_sync(FULL, updates, o);
-            t_total += __shfl_xor_sync(FULL, t_total, o);
+            up += __shfl_xor_sync(FULL, up, o);
+            tt += __shfl_xor_sync(FULL, tt, o);
         }
         if (lane == 0 && !(P.dbg & 1u)) {
             if (!EMIT && c2) atomicAdd(P.n_clusters, (unsigned long long)c2);
             if (mx) atomicMax(P.max_len, mx);
-            if (SCORE && updates) atomicAdd(P.n_updates, updates);
-            if (SCORE && t_total) atomicAdd(P.sum_t, t_total);
+            if (SCORE && up) atomicAdd(P.n_updates, up);
+            if (SCORE && tt) atomicAdd(P.sum_t, tt);
         }
     }
 }

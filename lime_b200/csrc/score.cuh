@@ -51,7 +51,7 @@ __device__ __forceinline__ constexpr unsigned compat_bits(int a)
 // full matcher incl. the IUPAC cross loop (:146-177).  In the "genome IUPAC vs read base" branch
 // the reference zeroes one operand before subtracting it from the other (:153-154, :158-159), so
 // the other operand keeps its value; t wraps as uint8 (:131), taken mod 256 by the caller.
-static __device__ __noinline__ uint32_t score_iupac(const uint4 &R, const uint4 &G)
+static __device__ __noinline__ uint32_t score_iupac(const uint4 R, const uint4 G)
 {
     uint32_t rr[16], gg[16], t = 0;
 #pragma unroll
