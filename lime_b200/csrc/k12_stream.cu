@@ -324,6 +324,12 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
         cl_count += count;
         if (own_tail) max_len = max(max_len, tail_len);
 
+        if (!SCORE && !EMIT) {
+            // counting pass of the two-pass record emission: clusters owned by this chunk
+            const unsigned total = __reduce_add_sync(FULL, count);
+            if (lane == 0) P.tile_state[c] = total;
+            continue;
+        }
         unsigned long long rec_base = 0;
         if (EMIT) {
             unsigned incl = count;
@@ -333,8 +339,7 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
                 if (lane >= (unsigned)o) incl += n;
             }
             const unsigned total = __shfl_sync(FULL, incl, 31);
-            const unsigned long long e = lookback_exclusive(P.tile_state, (unsigned)c, total);
-            const unsigned long long e0 = __shfl_sync(FULL, e, 0);
+            const unsigned long long e0 = P.tile_state[c];                // exclusive prefix of the counting pass
             if (lane == 0 && c == n_chunks - 1) *P.n_clusters = e0 + total;
             rec_base = e0 + (incl - count);
             // every owned head: length to the next head, record in ascending pStart order
@@ -381,8 +386,6 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
                 if (slot < P.long_cap)
                     *reinterpret_cast<ulonglong2 *>(&P.long_list[slot]) = make_ulonglong2(P.pos_base + a + hl, tail_len);
             }
-        } else if (!EMIT) {
-            // (not instantiated: detection without records or scores)
         }
         if (!SCORE) continue;
         if (P.dbg & 8u) { issue_next(); continue; }
@@ -524,6 +527,28 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
     }
 }
 
+// ---- exclusive prefix over the per-chunk cluster counts (between the counting and the emitting pass) ----
+constexpr int SCAN_THREADS = 1024;
+__global__ void __launch_bounds__(SCAN_THREADS) chunk_scan_kernel(unsigned long long *a, uint64_t n, unsigned long long *total)
+{
+    __shared__ unsigned long long part[SCAN_THREADS];
+    const uint64_t per = (n + SCAN_THREADS - 1) / SCAN_THREADS;
+    const uint64_t lo = min(n, per * threadIdx.x), hi = min(n, lo + per);
+    unsigned long long sum = 0;
+    for (uint64_t i = lo; i < hi; i++) sum += a[i];
+    part[threadIdx.x] = sum;
+    __syncthreads();
+    for (int o = 1; o < SCAN_THREADS; o <<= 1) {                 // Hillis-Steele over the 1024 partial sums
+        const unsigned long long v = threadIdx.x >= (unsigned)o ? part[threadIdx.x - o] : 0ull;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    unsigned long long run = part[threadIdx.x] - sum;
+    for (uint64_t i = lo; i < hi; i++) { const unsigned long long v = a[i]; a[i] = run; run += v; }
+    if (threadIdx.x == SCAN_THREADS - 1 && total) *total = part[threadIdx.x];
+}
+
 // ---- byte sum of the matrix (carry check of the fire-and-forget adds) -------------------------------
 constexpr int SUM_THREADS = 256;
 __global__ void __launch_bounds__(SUM_THREADS) bytesum_kernel(const uint4 *p, uint64_t n16, unsigned long long *out)
@@ -582,7 +607,7 @@ static unsigned grid_of(uint64_t n_own)
 template <bool SC, bool EM, bool EB, bool EX>
 static cudaError_t launch_variant(const K12Args &a, cudaStream_t s)
 {
-    // persistent grid: every CTA is resident (the look-back of EMIT relies on it), warps stride over chunks
+    // persistent grid, warps stride over chunks
     const unsigned grid = grid_of<SC, EM, EB, EX>(a.n_own);
     if (!grid) return cudaErrorUnknown;
     k12s::stream_kernel<SC, EM, EB, EX><<<grid, k12s::THREADS, 0, s>>>(a);
@@ -590,7 +615,7 @@ static cudaError_t launch_variant(const K12Args &a, cudaStream_t s)
 }
 
 #define LIME_K12S_DISPATCH(CALL)                                                              \
-    if (!score)                        return CALL(false, true, false, false);               \
+    if (!score)                        return emit ? CALL(false, true, false, false) : CALL(false, false, false, false); \
     if (emit) {                                                                               \
         if (ebwt && !exact32)          return CALL(true, true, true, false);                 \
         if (ebwt && exact32)           return CALL(true, true, true, true);                  \
@@ -607,9 +632,21 @@ static cudaError_t launch_variant(const K12Args &a, cudaStream_t s)
 uint64_t k12_num_tiles(uint64_t n_own) { return k12s_num_chunks(n_own); }
 uint64_t k12_long_cap(uint64_t n_total) { return n_total / (k12s::MAXFAST + 1) + k12_num_tiles(n_total) + 16; }
 
+// Records (.clrs) are emitted in two passes: a counting pass (phases A + B only) leaves the number of
+// clusters of every chunk in tile_state, an exclusive scan turns it into record offsets, and the
+// emitting pass (with or without scoring) reads its offset there -- no look-back between warps.
 cudaError_t launch_k12(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s)
 {
     if (a.n_own == 0) return cudaSuccess;
+    if (emit) {
+        cudaError_t e = launch_variant<false, false, false, false>(a, s);
+        if (e != cudaSuccess) return e;
+        k12s::chunk_scan_kernel<<<1, k12s::SCAN_THREADS, 0, s>>>(a.tile_state, k12s_num_chunks(a.n_own), nullptr);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+        e = cudaMemsetAsync(a.n_clusters, 0, sizeof(unsigned long long), s);      // the counting pass added its total
+        if (e != cudaSuccess) return e;
+    }
     const bool ebwt = a.ebwt != nullptr;
 #define LIME_LV(SC, EM, EB, EX) launch_variant<SC, EM, EB, EX>(a, s)
     LIME_K12S_DISPATCH(LIME_LV)
