@@ -36,7 +36,7 @@ WORKLOAD = dict(name="cfg2 single-end synthetic: 2M reads x 100bp + 100 genomes,
                      "2 strands (F,RC), EBWT=1, alpha=16, beta=0.25, TaxRank=1",
                 n=402_000_000, n_reads=2_000_000, n_refs=100, read_len=100, alpha=16, beta=0.25,
                 ebwt=1, n_strands=2, tax_rank=1, seed=20261104 + 2)
-CPU_SAMPLE_N = 1 << 27          # positions per strand of the CPU-timed prefix sample (~5 s per run on 16 cores)
+CPU_SAMPLE_N = 1 << 28          # positions per strand of the CPU-timed prefix sample (~4.5 s per run on 16 cores)
 METRIC = "ebwt_symbols_per_s"
 UNIT = "symbols/s"
 
