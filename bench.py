@@ -533,10 +533,21 @@ def run_ours_multi(args, w, world, rank, local):
                            is_last=rank == world - 1))
     torch.cuda.synchronize()
     be = multi.CudaBackend(ctx, torch, dev)
-    job = multi.ShardedJob(dist, torch, be, rank, world, n_reads, w["n_refs"])
+    # LIME_MULTI=peer: updates go straight to the read owner's slab over NVLink (PeerJob); =exchange: partial
+    # matrices + triples all-to-all (ShardedJob, also the exact fallback).  Default: whichever was measured
+    # faster on this pool (profiles/README.md): peer adds on 2 GPUs, the exchange beyond (remote adds over
+    # a footprint of several owners collapse to 0.3 G adds/s on 8 GPUs)
+    mode = os.environ.get("LIME_MULTI", "auto")
+    peer = mode == "peer" or (mode == "auto" and world <= 2)
+    if peer:
+        job = multi.PeerJob(dist, torch, be, rank, world, n_reads, w["n_refs"], w["n_strands"])
+    else:
+        job = multi.ShardedJob(dist, torch, be, rank, world, n_reads, w["n_refs"])
 
     def step(gather=True):
         job.stats = []
+        if peer:
+            job.begin()
         for s, sh in enumerate(shards):
             job.run_strand(s, sh, w["alpha"], w["beta"], w["ebwt"], w["read_len"])
         # every rank fetches the assignments of the reads it owns (9 B per read, as at N = 1)
@@ -570,6 +581,9 @@ def run_ours_multi(args, w, world, rank, local):
     launches = torch.tensor([ctx.launch_count() - l0], device=dev, dtype=torch.int64)
     dist.all_reduce(launches, op=dist.ReduceOp.SUM)
     prof = ctx.prof(); ctx.prof_enable(False)
+    k12_all = torch.zeros(world, device=dev, dtype=torch.float64)
+    k12_all[rank] = prof.get("k12_fused", {}).get("ms", 0.0) / max(prof.get("k12_fused", {}).get("launches", 1), 1)
+    dist.all_reduce(k12_all)
     n_ext = torch.tensor([max(0, int(0.7 / max(ms_step * 1e-3, 1e-4)) - args.steps)], device=dev, dtype=torch.int64)
     dist.broadcast(n_ext, 0)                                       # same number of extra steps on every rank
     for _ in range(int(n_ext.item())):
@@ -595,9 +609,9 @@ def run_ours_multi(args, w, world, rank, local):
     job.timer = tm
     step()
     job.timer = lambda name: multi._NoTimer()
-    sent = sum(st["triples_sent"] for st in job.stats) * 8
-    phases = torch.tensor([tm.ms.get(k, 0.0) for k in ("compute", "export", "counts", "all_to_all", "import", "choose", "scalars", "classify", "gather")],
-                          device=dev, dtype=torch.float64)
+    sent = sum(st.get("triples_sent", 0) for st in job.stats) * 8
+    PH = ("zero", "compute", "export", "counts", "all_to_all", "import", "choose", "scalars", "classify", "gather", "check")
+    phases = torch.tensor([tm.ms.get(k, 0.0) for k in PH], device=dev, dtype=torch.float64)
     dist.all_reduce(phases, op=dist.ReduceOp.MAX)
     sent_t = torch.tensor([sent], device=dev, dtype=torch.int64)
     dist.all_reduce(sent_t, op=dist.ReduceOp.MAX)
@@ -615,29 +629,37 @@ def run_ours_multi(args, w, world, rank, local):
         alg_per_launch = (8 + w["ebwt"]) * (S + 0)
         avg_ms = kern[top]["ms"] / kern[top]["launches"]
         achieved = alg_per_launch / (avg_ms * 1e-3) / 1e9 if top == "k12_fused" else None
-        ph = dict(zip(("compute", "export", "counts", "all_to_all", "import", "choose", "scalars", "classify", "gather"), [float(x) for x in phases.tolist()]))
-        a2a_ms = ph["all_to_all"]
+        ph = {k: float(x) for k, x in zip(PH, phases.tolist()) if x > 0}
+        a2a_ms = ph.get("all_to_all", 0.0)
+        par = (f"position-sharded x{world}, halo {HALO}; similarity rows live on the read owner's GPU and every update is a "
+               "red.add over NVLink / NVSwitch peer memory issued by the fused kernel (no partial matrix, no all-to-all)" if peer else
+               f"position-sharded x{world}, halo {HALO}, triples all-to-all by read owner")
         line = {
             "metric": METRIC, "value": symbols / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 1), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": w["name"] + f"; x{world} weak scaling: {world} position shards of {S} symbols per strand, {n_reads} reads",
                        "l2": "inputs (3.6 GB per strand and GPU) are larger than L2; no flush needed",
-                       "parallelism": f"position-sharded x{world}, halo {HALO}, triples all-to-all by read owner; every rank copies the assignments of its own read range to its host",
+                       "parallelism": par + "; every rank copies the assignments of its own read range to its host",
                        "symbols_per_step": symbols, "reads_per_step": n_reads, "strand_stats": stats, "assignments": kinds},
             "reads_per_s": n_reads / (ms_step * 1e-3),
             "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
                          "frac": (achieved / peak_gbs) if achieved else None, "traffic": None, "peak_source": peak_src,
                          "alg_bytes_per_launch": alg_per_launch, "avg_launch_ms": avg_ms,
                          "kernels_ms_per_step_rank0": {k: x["ms"] / args.steps for k, x in kern.items()},
+                         "k12_ms_per_launch_by_rank": [round(float(x), 3) for x in k12_all.tolist()],
                          "job_frac_of_aggregate_peak": (8 + w["ebwt"]) * symbols / (ms_step * 1e-3) / 1e9 / (peak_gbs * world)},
-            "exchange": {"phases_ms_max_over_ranks": ph, "all_to_all_bytes_sent_per_rank_max": int(sent_t.item()),
+            "exchange": {"mode": "peer-memory adds" if peer else "triples all-to-all", "phases_ms_max_over_ranks": ph,
+                         "all_to_all_bytes_sent_per_rank_max": int(sent_t.item()),
                          "all_to_all_GBps_per_rank": (int(sent_t.item()) / (a2a_ms * 1e-3) / 1e9) if a2a_ms > 0 else None,
+                         "remote_updates_per_rank_and_step": (sum(st.get("updates", 0) for st in stats) // world * (world - 1) // world) if peer else None,
                          "nvlink_peak_GBps_per_direction": 900, "note": "phase times from one extra synchronised step"},
             "cpu_baseline": None, "e2e": None, "gpu_launches": int(launches.item()), "clocks": clk,
         }
         print(json.dumps(line), flush=True)
     dist.barrier()
+    if peer:
+        job.close()
     ctx.close()
     dist.destroy_process_group()
 

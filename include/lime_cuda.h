@@ -153,6 +153,41 @@ int  lime_sim_export(lime_ctx *ctx, uint32_t read_begin, uint32_t read_end, void
                      uint64_t cap, uint64_t *n_triples);
 int  lime_sim_import(lime_ctx *ctx, const void *dev_triples, uint64_t n_triples);
 
+/* ---- multi-GPU accumulation over peer memory (one NVLink / NVSwitch node) ---------------------- */
+
+/*
+ * The alternative to export / all-to-all / import: every GPU holds only the rows of the reads it owns
+ * (rank k owns reads [k * reads_per_rank, (k+1) * reads_per_rank)), one slab of `rows` x pitch uint8
+ * per strand, and maps the slabs of all other GPUs (CUDA IPC).  lime_peer_accumulate is
+ * lime_cluster_similarity with every update added directly to the owner's slab over NVLink: the
+ * reference's `SimArray_[read][genome] += t` (ClusterBWT_DA.cpp:183,247) on a matrix that is spread
+ * over the node.  Call order on every rank (collectives are the caller's, e.g. NCCL):
+ *   lime_peer_alloc -> all-gather the 64-byte handles -> lime_peer_open            (once)
+ *   lime_peer_zero -> BARRIER -> per strand: lime_load, lime_peer_accumulate(slab) -> BARRIER ->
+ *   per strand: lime_peer_select(slab) + lime_choose(slot, ..., 0, own reads) -> lime_classify.
+ * out[4] of lime_peer_accumulate = this shard's nClusters, maxLen, updates, sum of all t added.
+ * lime_peer_select makes slab `slab` the matrix lime_choose reads (row 0 = first owned read);
+ * total_updates (sum over all ranks) bounds its records; byte_sum (optional, DEVICE memory, written
+ * asynchronously on the ctx stream) receives the byte sum of the slab: the sum over ranks of the
+ * byte sums must equal the sum over ranks of out[3], otherwise a cell exceeded 255 and the job has
+ * to be redone through the exact path (lime_sim_export route).
+ * lime_peer_zero_slab clears one slab once lime_choose has read it, so that the collective which
+ * carries the byte sums is also the "all slabs are zero" barrier of the next job (no lime_peer_zero).
+ */
+#define LIME_IPC_HANDLE_BYTES 64
+#define LIME_PEER_MAX         16
+int  lime_peer_alloc(lime_ctx *ctx, uint64_t rows, uint32_t n_refs, int n_slabs, uint8_t *ipc_handle);
+int  lime_peer_open(lime_ctx *ctx, int world, int rank, const uint8_t *ipc_handles, uint32_t reads_per_rank);
+int  lime_peer_close(lime_ctx *ctx);
+int  lime_peer_zero(lime_ctx *ctx);
+int  lime_peer_accumulate(lime_ctx *ctx, uint32_t alpha, int ebwt_mode, int slab, uint64_t out[4]);
+int  lime_peer_select(lime_ctx *ctx, int slab, uint64_t total_updates, uint64_t *byte_sum);
+int  lime_peer_zero_slab(lime_ctx *ctx, int slab);
+/* Instrumentation: n_adds adds of 0 to random cells of the first span_rows rows of the slabs of owners
+ * [first_owner, first_owner + n_owners); mode 0 red, 1 atom (returned), 2 store.  *ms = device time. */
+int  lime_peer_probe(lime_ctx *ctx, int slab, int first_owner, int n_owners, uint32_t span_rows, uint64_t n_adds,
+                     int mode, double *ms);
+
 /* ---- step 3 : Classify.cpp:474-702 -------------------------------------------------------- */
 
 /*

@@ -27,6 +27,7 @@ u8p, u32p, u64p, f32p = (C.POINTER(C.c_uint8), C.POINTER(C.c_uint32), C.POINTER(
 vp = C.c_void_p
 
 # name -> (restype, argtypes); must list every symbol include/lime_cuda.h declares
+IPC_HANDLE_BYTES = 64       # LIME_IPC_HANDLE_BYTES
 SIGNATURES = {
     "lime_init": (C.c_int, [C.POINTER(vp), C.c_int]),
     "lime_destroy": (None, [vp]),
@@ -52,6 +53,14 @@ SIGNATURES = {
     "lime_slot_set": (C.c_int, [vp, C.c_int, vp, C.c_uint64, vp, C.c_uint32]),
     "lime_classify": (C.c_int, [vp, C.c_int, C.c_uint32, vp, vp, C.c_int, C.c_int, vp, vp, vp]),
     "lime_classify_result": (C.c_int, [vp, vp, vp, vp, C.c_int]),
+    "lime_peer_alloc": (C.c_int, [vp, C.c_uint64, C.c_uint32, C.c_int, vp]),
+    "lime_peer_open": (C.c_int, [vp, C.c_int, C.c_int, vp, C.c_uint32]),
+    "lime_peer_close": (C.c_int, [vp]),
+    "lime_peer_zero": (C.c_int, [vp]),
+    "lime_peer_accumulate": (C.c_int, [vp, C.c_uint32, C.c_int, C.c_int, u64p]),
+    "lime_peer_select": (C.c_int, [vp, C.c_int, C.c_uint64, vp]),
+    "lime_peer_zero_slab": (C.c_int, [vp, C.c_int]),
+    "lime_peer_probe": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint64, C.c_int, C.POINTER(C.c_double)]),
     "lime_launch_count": (C.c_uint64, [vp]),
     "lime_prof_enable": (C.c_int, [vp, C.c_int]),
     "lime_prof_kernels": (C.c_int, []),

@@ -172,6 +172,43 @@ class LimeContext:
     def sim_import(self, dev_ptr, n):
         self._ck(self.lib.lime_sim_import(self.h, C.c_void_p(dev_ptr) if dev_ptr else None, n))
 
+    # ---- multi-GPU accumulation over peer memory ----------------------------------------------
+    def peer_alloc(self, rows, n_refs, n_slabs):
+        """Allocate this rank's slabs; returns the 64-byte CUDA IPC handle to all-gather."""
+        h = np.zeros(_lib.IPC_HANDLE_BYTES, dtype=np.uint8)
+        self._ck(self.lib.lime_peer_alloc(self.h, rows, n_refs, n_slabs, _ptr(h)))
+        return h
+
+    def peer_open(self, world, rank, handles, reads_per_rank):
+        handles = np.ascontiguousarray(handles, dtype=np.uint8).reshape(world * _lib.IPC_HANDLE_BYTES)
+        self._ck(self.lib.lime_peer_open(self.h, world, rank, _ptr(handles), reads_per_rank))
+
+    def peer_close(self):
+        self._ck(self.lib.lime_peer_close(self.h))
+
+    def peer_zero(self):
+        self._ck(self.lib.lime_peer_zero(self.h))
+
+    def peer_accumulate(self, alpha, ebwt_mode, slab):
+        """-> (n_clusters, max_len, updates, sum_t) of this shard."""
+        out = (C.c_uint64 * 4)()
+        self._ck(self.lib.lime_peer_accumulate(self.h, alpha, 1 if ebwt_mode else 0, slab, out))
+        return tuple(int(x) for x in out)
+
+    def peer_select(self, slab, total_updates, byte_sum_dev_ptr=None):
+        """byte_sum_dev_ptr: device address of a uint64 that receives the slab's byte sum (async)."""
+        self._ck(self.lib.lime_peer_select(self.h, slab, total_updates,
+                                           C.c_void_p(byte_sum_dev_ptr) if byte_sum_dev_ptr else None))
+
+    def peer_probe(self, slab, first_owner, n_owners, span_rows, n_adds, mode=0):
+        """Device milliseconds of n_adds random adds of 0 into the slabs (instrumentation)."""
+        ms = C.c_double()
+        self._ck(self.lib.lime_peer_probe(self.h, slab, first_owner, n_owners, span_rows, n_adds, mode, C.byref(ms)))
+        return float(ms.value)
+
+    def peer_zero_slab(self, slab):
+        self._ck(self.lib.lime_peer_zero_slab(self.h, slab))
+
     def choose(self, slot, norm, beta, read_begin=0, read_end=None):
         if read_end is None:
             read_end = self.n_reads

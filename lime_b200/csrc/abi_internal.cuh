@@ -37,6 +37,12 @@ template <class T> static T *scalar(lime_ctx *c, int slot)
     return reinterpret_cast<T *>(c->scalars.as<unsigned long long>() + slot);
 }
 
+// lime_abi_steps.cu / lime_abi_peer.cu
+int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, bool exact32, uint32_t lo, uint32_t hi,
+                 unsigned long long sc[SC_COUNT], int peer_slab);
+lime::PeerTable peer_table(const lime_ctx *ctx, int slab);
+void peer_release(lime_ctx *ctx);
+
 // bracket one kernel launch with events when profiling
 struct LaunchScope {
     lime_ctx *c; int kid; cudaEvent_t a = nullptr, b = nullptr;

@@ -79,6 +79,24 @@ __device__ __forceinline__ unsigned long long lookback_exclusive(unsigned long l
     return excl;
 }
 
+// ---- similarity rows spread over the GPUs of one NVSwitch node (peer memory) -------------------
+// Reads are owned by contiguous ranges of `per` reads; base[k] is owner k's slab ([per][pitch] uint8,
+// its own cudaMalloc, mapped here through CUDA IPC).  Adds go straight to the owner over NVLink.
+constexpr int PEER_MAX = 16;
+struct PeerTable {
+    uint8_t *base[PEER_MAX];
+    uint32_t per;                 // reads per owner
+    uint32_t magic;               // min(floor(2^32 / per), 2^32 - 1)
+};
+// row of global read r in its owner's slab
+__device__ __forceinline__ uint8_t *peer_row(const PeerTable &T, uint64_t pitch, uint32_t r)
+{
+    uint32_t q = __umulhi(r, T.magic);            // quotient or quotient - 1
+    uint32_t rem = r - q * T.per;
+    if (rem >= T.per) { q++; rem -= T.per; }
+    return T.base[q] + (size_t)rem * pitch;
+}
+
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
@@ -123,6 +141,17 @@ struct Slot {
 
 struct ProfEvent { int kid; cudaEvent_t a, b; };
 
+// peer-memory accumulation (lime_abi_peer.cu)
+struct PeerState {
+    bool active = false;
+    int world = 0, rank = 0, n_slabs = 0;
+    uint64_t rows = 0, pitch = 0;          // per slab
+    uint32_t per = 0;
+    void *own = nullptr;                   // n_slabs slabs, one cudaMalloc
+    void *mapped[PEER_MAX] = {nullptr};    // every owner's allocation in this process (own included)
+    DevBuf tables;                         // PeerTable[n_slabs] on the device (block path)
+};
+
 } // namespace lime
 
 struct lime_ctx {
@@ -166,6 +195,7 @@ struct lime_ctx {
     lime::DevBuf cls_out;           // classify outputs
     uint64_t cls_n = 0; bool cls_n_valid = false;
     lime::DevBuf tax_tables;        // v_corRef + m_corRef on device
+    lime::PeerState peer;
 
     // instrumentation
     uint64_t launches = 0;
@@ -198,6 +228,7 @@ struct K2Args {
     unsigned long long *large_next;   // ticket for the block path
     unsigned long long *n_updates;    // statistics
     uint8_t *scratch; uint64_t scratch_per_cta;
+    const PeerTable *peer = nullptr;  // device pointer; non-null: rows live in the owners' slabs
 };
 cudaError_t launch_k2_warp(const K2Args &a, bool exact32, cudaStream_t s);
 cudaError_t launch_k2_block(const K2Args &a, bool exact32, cudaStream_t s, int grid);
@@ -230,6 +261,11 @@ struct K12Args {
     // stream kernel: fire-and-forget adds; sum_t receives the total of all t added to the matrix so
     // that the host can prove the absence of byte carries (bytesum of the matrix == sum_t)
     unsigned long long *sum_t;        // null: every add inspects the returned word instead
+    // peer mode (multi-GPU): read rows live in the owners' slabs; sim8 is unused
+    int peer_on = 0;
+    uint32_t peer_self = 0, peer_world = 1;
+    PeerTable peer;
+    const PeerTable *peer_dev = nullptr;
 };
 cudaError_t launch_bytesum(const uint8_t *p, uint64_t bytes, unsigned long long *out, cudaStream_t s);
 cudaError_t launch_k12(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s);

@@ -90,8 +90,10 @@ __device__ __forceinline__ void cp_async_wait_all()
     asm volatile("cp.async.wait_all;" ::: "memory");
 }
 
-template <bool SCORE, bool EMIT, bool EBWT, bool EXACT32>
-__global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
+// PEER: the rows of the similarity matrix live in their owners' slabs (one GPU per read range, mapped
+// peer memory); every update is a fire-and-forget add that travels over NVLink / NVSwitch to the owner.
+template <bool SCORE, bool EMIT, bool EBWT, bool EXACT32, bool PEER = false>
+__global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constant__ K12Args P)
 {
     __shared__ Smem sm;
     const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
@@ -112,6 +114,7 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
     SimAcc acc;
     acc.sim8 = P.sim8; acc.pitch8 = P.pitch8; acc.sim32 = P.sim32; acc.lo = P.lo; acc.hi = P.hi;
     acc.n_refs = P.n_refs; acc.carry = P.carry; acc.sum_t = P.sum_t;
+    acc.peer = PEER ? P.peer_dev : nullptr;
     // Matrix updates are fire-and-forget adds of t << 8*(g&3) to the 32-bit word that holds the uint8
     // cell: no return value to wait for.  A carry out of a byte (true cell sum > 255, where the
     // reference wraps, ClusterBWT_DA.cpp:183,247) lowers the byte sum of the matrix by 255 or 256, so
@@ -123,6 +126,22 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(K12Args P)
         updates++;
         if (P.dbg & 2u) return;
         if (EXACT32) { sim_add<true>(acc, r, g, t); return; }
+        if (PEER) {
+            uint8_t *row = peer_row(P.peer, P.pitch8, r);
+            if (P.dbg & 0x3f0u) {                   // experiments: where do the adds go
+                const uint32_t q = r / P.peer.per;
+                uint32_t rem = r - q * P.peer.per;
+                uint32_t dst = q;
+                if (P.dbg & 16u) dst = P.peer_self;                                  // all local
+                if (P.dbg & 64u) dst = (P.peer_self + 1u) % P.peer_world;            // all to the next rank
+                if (P.dbg & 128u) dst = (P.peer_self + 1u + q % 3u) % P.peer_world;  // three peers
+                if (P.dbg & 256u) rem &= 0x3ffffu;                                   // 28 MB per owner
+                row = P.peer.base[dst] + (size_t)rem * P.pitch8;
+            }
+            atomicAdd(reinterpret_cast<unsigned *>(row) + (g >> 2), t << ((g & 3u) * 8u));
+            t_total += t;
+            return;
+        }
         if (red_mode) {
             atomicAdd(reinterpret_cast<unsigned *>(acc.sim8 + (size_t)r * acc.pitch8) + (g >> 2), t << ((g & 3u) * 8u));
             t_total += t;
@@ -588,7 +607,7 @@ cudaError_t launch_bytesum(const uint8_t *p, uint64_t bytes, unsigned long long 
 
 uint64_t k12s_num_chunks(uint64_t n_own) { return (n_own + k12s::OWN - 1) / k12s::OWN; }
 
-template <bool SC, bool EM, bool EB, bool EX>
+template <bool SC, bool EM, bool EB, bool EX, bool PE = false>
 static unsigned grid_of(uint64_t n_own)
 {
     static int ctas_per_sm = 0, sms = 0;
@@ -596,7 +615,7 @@ static unsigned grid_of(uint64_t n_own)
         int dev = 0;
         if (cudaGetDevice(&dev) != cudaSuccess) return 0;
         if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, k12s::stream_kernel<SC, EM, EB, EX>, k12s::THREADS, 0) != cudaSuccess) return 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, k12s::stream_kernel<SC, EM, EB, EX, PE>, k12s::THREADS, 0) != cudaSuccess) return 0;
         if (ctas_per_sm < 1) ctas_per_sm = 1;
     }
     const uint64_t chunks = k12s_num_chunks(n_own);
@@ -604,13 +623,13 @@ static unsigned grid_of(uint64_t n_own)
     return (unsigned)std::min<uint64_t>(want, (uint64_t)sms * ctas_per_sm);
 }
 
-template <bool SC, bool EM, bool EB, bool EX>
+template <bool SC, bool EM, bool EB, bool EX, bool PE = false>
 static cudaError_t launch_variant(const K12Args &a, cudaStream_t s)
 {
     // persistent grid, warps stride over chunks
-    const unsigned grid = grid_of<SC, EM, EB, EX>(a.n_own);
+    const unsigned grid = grid_of<SC, EM, EB, EX, PE>(a.n_own);
     if (!grid) return cudaErrorUnknown;
-    k12s::stream_kernel<SC, EM, EB, EX><<<grid, k12s::THREADS, 0, s>>>(a);
+    k12s::stream_kernel<SC, EM, EB, EX, PE><<<grid, k12s::THREADS, 0, s>>>(a);
     return cudaGetLastError();
 }
 
@@ -638,6 +657,12 @@ uint64_t k12_long_cap(uint64_t n_total) { return n_total / (k12s::MAXFAST + 1) +
 cudaError_t launch_k12(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s)
 {
     if (a.n_own == 0) return cudaSuccess;
+    if (a.peer_on) {
+        // multi-GPU peer mode: scoring only, fire-and-forget adds into the owners' slabs
+        if (!score || emit || exact32 || !a.sum_t) return cudaErrorInvalidValue;
+        return a.ebwt ? launch_variant<true, false, true, false, true>(a, s)
+                      : launch_variant<true, false, false, false, true>(a, s);
+    }
     if (emit) {
         cudaError_t e = launch_variant<false, false, false, false>(a, s);
         if (e != cudaSuccess) return e;

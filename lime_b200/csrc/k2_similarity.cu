@@ -27,7 +27,7 @@ __device__ __forceinline__ void sim_add(const K2Args &P, uint32_t r, uint32_t g,
 {
     SimAcc acc;
     acc.sim8 = P.sim8; acc.pitch8 = P.pitch8; acc.sim32 = P.sim32; acc.lo = P.lo; acc.hi = P.hi;
-    acc.n_refs = P.n_refs; acc.carry = P.carry; acc.sum_t = P.sum_t;
+    acc.n_refs = P.n_refs; acc.carry = P.carry; acc.sum_t = P.sum_t; acc.peer = P.peer;
     lime::sim_add<EXACT32>(acc, r, g, t);
 }
 

@@ -42,6 +42,7 @@ void lime_destroy(lime_ctx *ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     for (auto &p : ctx->prof_events) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    peer_release(ctx);
     DevBuf *bufs[] = {&ctx->in_lcp, &ctx->in_da, &ctx->in_ebwt, &ctx->clusters, &ctx->tile_state,
                       &ctx->scalars, &ctx->sim_own, &ctx->sim32, &ctx->large_list, &ctx->long_recs, &ctx->k2_scratch,
                       &ctx->row_counts, &ctx->cls_out, &ctx->tax_tables};
@@ -115,6 +116,11 @@ int lime_load(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint
     ctx->n_own = n_own; ctx->n_halo = n_halo; ctx->pos_base = pos_base; ctx->is_last = is_last;
     ctx->n_reads = n_reads; ctx->n_refs = n_refs;
     // similarity accumulator: dense uint8 [n_reads][pitch], zeroed
+    if (ctx->peer.active) {
+        // peer mode: the rows live in the owners' slabs, zeroed by lime_peer_zero
+        ctx->loaded = true;
+        return LIME_OK;
+    }
     if (!ctx->sim_bound) {
         ctx->sim_pitch = lime_sim_pitch(n_refs);
         ctx->sim_rows = n_reads;

@@ -31,9 +31,11 @@ static int run_k2_pass(lime_ctx *ctx, bool ebwt, bool exact32, uint32_t lo, uint
     return LIME_OK;
 }
 
-// one fused pass (steps 1 + 2a) plus the block path over the clusters it set aside
-static int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, bool exact32, uint32_t lo, uint32_t hi,
-                        unsigned long long sc[SC_COUNT])
+// one fused pass (steps 1 + 2a) plus the block path over the clusters it set aside;
+// peer_slab >= 0: the adds go to the owners' slabs of that index (lime_abi_peer.cu) and the carry
+// check is left to the caller (it needs every GPU's adds to have landed)
+int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, bool exact32, uint32_t lo, uint32_t hi,
+                 unsigned long long sc[SC_COUNT], int peer_slab)
 {
     const uint64_t n_total = ctx->n_own + ctx->n_halo;
     K12Args a;
@@ -55,6 +57,13 @@ static int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, boo
     { const char *e = getenv("LIME_DEBUG"); a.dbg = e ? (unsigned)atoi(e) : 0u; }
     // fire-and-forget adds; carries are ruled out after the pass by the byte sum (see below)
     a.sum_t = !exact32 ? scalar<unsigned long long>(ctx, SC_SUMT) : nullptr;
+    const bool peer = peer_slab >= 0;
+    if (peer) {
+        a.peer_on = 1; a.peer_self = (uint32_t)ctx->peer.rank; a.peer_world = (uint32_t)ctx->peer.world;
+        a.peer = peer_table(ctx, peer_slab);
+        a.peer_dev = ctx->peer.tables.as<PeerTable>() + peer_slab;
+        a.sim8 = nullptr; a.pitch8 = ctx->peer.pitch;
+    }
     const uint64_t tiles = k12_num_tiles(ctx->n_own);
     CK(cudaMemsetAsync(ctx->scalars.p, 0, sizeof(unsigned long long) * SC_COUNT, ctx->stream), "memset scalars");
     if (emit) CK(cudaMemsetAsync(ctx->tile_state.p, 0, std::max<uint64_t>(tiles, 1) * 8, ctx->stream), "memset tile state");
@@ -69,6 +78,7 @@ static int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, boo
         b.cl = nullptr; b.n_cl = 0; b.da = ctx->d_da; b.ebwt = a.ebwt;
         b.pos_base = ctx->pos_base; b.n_reads = ctx->n_reads; b.n_refs = ctx->n_refs;
         b.sim8 = a.sim8; b.pitch8 = a.pitch8; b.sim32 = a.sim32; b.lo = lo; b.hi = hi;
+        b.peer = peer ? a.peer_dev : nullptr;
         b.carry = a.carry; b.sum_t = a.sum_t; b.large_count = a.long_count; b.large_list = nullptr; b.long_recs = a.long_list;
         b.large_cap = a.long_cap;
         b.large_next = scalar<unsigned long long>(ctx, SC_LARGE_NEXT);
@@ -78,7 +88,7 @@ static int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, boo
             LaunchScope ls(ctx, KID_K2_BLOCK);
             CK(launch_k2_block(b, exact32, ctx->stream, k2_block_grid()), "k2_block launch");
         }
-        if (a.sum_t && ctx->sim_rows * ctx->sim_pitch) {
+        if (a.sum_t && !peer && ctx->sim_rows * ctx->sim_pitch) {
             // The matrix was zero before this pass (lime_load) and every add is t << 8k on a 32-bit
             // word: a carry out of a byte lowers the byte sum by 255 (256 out of the top byte), so
             // byte sum == total of t  <=>  no cell exceeded 255.
@@ -95,7 +105,7 @@ static int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, boo
         return fail(ctx, LIME_ERR_MAXLEN, "maximum cluster size is greater than sizeMaxBuf");
     if (sc[SC_LARGE_COUNT] > a.long_cap)
         return fail(ctx, LIME_ERR_NOMEM, "lime_cluster_similarity: long-cluster list overflow");
-    if (a.sum_t && sc[SC_SUMT] != sc[SC_BYTESUM]) sc[SC_CARRY] = 1;
+    if (a.sum_t && !peer && sc[SC_SUMT] != sc[SC_BYTESUM]) sc[SC_CARRY] = 1;
     return LIME_OK;
 }
 
@@ -123,7 +133,7 @@ extern "C" int lime_cluster_similarity(lime_ctx *ctx, uint32_t alpha, int ebwt_m
     }
     unsigned long long sc[SC_COUNT];
     ctx->sim_done = true;
-    int rc = run_k12_pass(ctx, alpha, ebwt_mode != 0, emit, false, 0, 0, sc);
+    int rc = run_k12_pass(ctx, alpha, ebwt_mode != 0, emit, false, 0, 0, sc, -1);
     if (rc) return rc;
     const uint64_t n_cl = sc[SC_NCLUSTERS], mx = sc[SC_MAXLEN];
     ctx->sim_stats[1] = sc[SC_LARGE_COUNT];
@@ -155,7 +165,7 @@ extern "C" int lime_cluster_similarity(lime_ctx *ctx, uint32_t alpha, int ebwt_m
     for (uint64_t lo = 0; lo < ctx->n_reads; lo += band) {
         const uint64_t hi = std::min<uint64_t>(lo + band, ctx->n_reads);
         CK(cudaMemsetAsync(ctx->sim32.p, 0, (hi - lo) * ctx->n_refs * 4, ctx->stream), "memset exact accumulator");
-        rc = run_k12_pass(ctx, alpha, ebwt_mode != 0, false, true, (uint32_t)lo, (uint32_t)hi, sc);
+        rc = run_k12_pass(ctx, alpha, ebwt_mode != 0, false, true, (uint32_t)lo, (uint32_t)hi, sc, -1);
         if (rc) return rc;
         {
             LaunchScope ls(ctx, KID_K2_NARROW);

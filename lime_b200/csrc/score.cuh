@@ -88,6 +88,7 @@ struct SimAcc {
     uint32_t *sim32; uint32_t lo, hi, n_refs;
     unsigned int *carry;
     unsigned long long *sum_t;        // optional: total of t added through the checked path
+    const PeerTable *peer = nullptr;  // optional: rows live in the owners' slabs (peer memory)
 };
 
 template <bool EXACT32>
@@ -96,7 +97,8 @@ __device__ __forceinline__ void sim_add(const SimAcc &P, uint32_t r, uint32_t g,
     if (EXACT32) {
         if (r >= P.lo && r < P.hi) atomicAdd(&P.sim32[(size_t)(r - P.lo) * P.n_refs + g], t);
     } else {
-        unsigned *w = reinterpret_cast<unsigned *>(P.sim8 + (size_t)r * P.pitch8) + (g >> 2);
+        uint8_t *row = P.peer ? peer_row(*P.peer, P.pitch8, r) : P.sim8 + (size_t)r * P.pitch8;
+        unsigned *w = reinterpret_cast<unsigned *>(row) + (g >> 2);
         const unsigned sh = (g & 3u) * 8u;
         const unsigned old = atomicAdd(w, t << sh);
         if (((old >> sh) & 0xffu) + t > 0xffu) *P.carry = 1u;

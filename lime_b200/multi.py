@@ -19,6 +19,8 @@ all-reduce each.
 The compute goes through a small backend object so that the same host logic runs on CUDA
 (`CudaBackend`, the C ABI) and, in the CPU tests (gloo, world size 2), on a checker backend.
 """
+import os
+
 import numpy as np
 
 from .pipeline import norm_of
@@ -225,6 +227,104 @@ class ShardedJob:
             return None, None, None
         # views of job-owned (page-locked) buffers on CUDA: valid until the next finish()
         return outs[0].numpy(), outs[1].numpy().view(np.uint32), outs[2].numpy().view(np.float32)
+
+
+class CarryDetected(RuntimeError):
+    """A similarity cell exceeded 255 during a peer-memory job: redo it with ShardedJob, whose
+    backend reruns the pass into exact 32-bit cells (the uint8 wrap of SimArray_, Tools.h:68)."""
+
+
+class PeerJob:
+    """The same job as ShardedJob with the exchange folded into the compute kernel: every rank holds
+    only the similarity rows of the reads it owns (one slab per strand) and maps the slabs of all other
+    ranks (CUDA IPC over NVLink / NVSwitch); the fused kernel adds every (read, genome, t) straight
+    into the owner's slab (lime_peer_accumulate).  No partial matrices, no triples, no all-to-all:
+    the collectives left are three tiny all-gathers per job that double as the barriers
+      zeroed slabs -> [adds of all strands] -> scalars -> [choose, classify] -> byte sums (carry check).
+
+        job = PeerJob(dist, torch, backend, rank, world, n_reads, n_refs, n_strands)
+        job.begin()
+        for s, shard in enumerate(strands): job.run_strand(s, shard, alpha, beta, ebwt_mode, read_len)
+        typ, tax, sim = job.finish(v, m, tax_rank, higher)
+    """
+
+    def __init__(self, dist, torch, backend, rank, world, n_reads, n_refs, n_strands, timer=None):
+        self.dist, self.torch, self.be = dist, torch, backend
+        self.rank, self.world = rank, world
+        self.n_reads, self.n_refs, self.n_strands = n_reads, n_refs, n_strands
+        self.ranges = read_ranges(n_reads, world)
+        self.lo, self.hi = self.ranges[rank]
+        self.per = max(self.ranges[0][1] - self.ranges[0][0], 1)
+        self.timer = timer or (lambda name: _NoTimer())
+        self.stats, self._local, self._pending = [], [], []
+        self._inner = ShardedJob(dist, torch, backend, rank, world, n_reads, n_refs)   # finish() = classify + gather
+        ctx, dev = backend.ctx, backend.device
+        handle = ctx.peer_alloc(self.per, n_refs, n_strands)
+        mine = torch.from_numpy(handle.copy()).to(dev)
+        parts = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(parts, mine)
+        ctx.peer_open(world, rank, torch.stack(parts).cpu().numpy(), self.per)
+        dist.barrier()                       # every rank has mapped every slab
+        self._dirty = False
+        self._bs = torch.zeros(n_strands, dtype=torch.int64, device=dev)
+
+    def _all_gather_i64(self, values):
+        """Every rank's vector of integers, as a (world, len) int64 numpy array; also a barrier."""
+        torch, dist = self.torch, self.dist
+        t = torch.tensor(values, dtype=torch.int64).to(self.be.device)
+        out = torch.empty(self.world * t.numel(), dtype=torch.int64, device=self.be.device)
+        dist.all_gather_into_tensor(out, t)
+        return out.cpu().numpy().reshape(self.world, -1)
+
+    def begin(self):
+        """Nobody may add before every rank's slabs are zero: true after the constructor (fresh slabs,
+        then the handle all-gather) and after every finish() (slabs cleared before its last all-gather);
+        an abandoned job needs the explicit zero + barrier."""
+        if self._dirty:
+            with self.timer("zero"):
+                self.be.ctx.peer_zero()
+                self.dist.barrier()
+        self._dirty = True
+        self.stats, self._local, self._pending = [], [], []
+
+    def run_strand(self, slot, shard, alpha, beta, ebwt_mode, read_len):
+        be = self.be
+        with self.timer("compute"):
+            be.load(shard["lcp"], shard["da"], shard["ebwt"] if ebwt_mode else None, shard["n_own"], shard["n_halo"],
+                    shard["pos_base"], shard["is_last"], self.n_reads, self.n_refs)
+            n_cl, max_len, updates, sum_t = be.ctx.peer_accumulate(alpha, ebwt_mode, slot)
+        self._local += [n_cl, max_len, updates, sum_t]
+        self._pending.append((slot, norm_of(read_len, alpha), beta))
+
+    def finish(self, v, m=None, tax_rank=1, higher=False, gather=True):
+        be = self.be
+        with self.timer("scalars"):
+            # every rank's (nClusters, maxLen, updates, sum_t) per strand; completing it means every
+            # rank's adds have landed (each rank synchronised its kernels before contributing)
+            sc = self._all_gather_i64(self._local).reshape(self.world, len(self._pending), 4)
+        with self.timer("choose"):
+            for k, (slot, norm, beta) in enumerate(self._pending):
+                be.ctx.peer_select(slot, int(sc[:, k, 2].sum()), self._bs.data_ptr() + 8 * k)
+                n_rec = be.choose(slot, norm, beta, 0, self.hi - self.lo)
+                be.ctx.peer_zero_slab(slot)               # ready for the next job once `check` has completed
+                self.stats.append({"n_clusters": int(sc[:, k, 0].sum()), "max_len": int(sc[:, k, 1].max()),
+                                   "n_records_local": int(n_rec), "updates": int(sc[:, k, 2].sum())})
+        inner = self._inner
+        inner.timer, inner.n_strands = self.timer, len(self._pending)
+        out = inner.finish(v, m, tax_rank, higher, gather=gather)
+        with self.timer("check"):
+            allbs = self.torch.empty(self.world * self._bs.numel(), dtype=self.torch.int64, device=be.device)
+            self.dist.all_gather_into_tensor(allbs, self._bs)
+            bs = allbs.cpu().numpy().reshape(self.world, -1)
+            self._dirty = False
+            for k in range(len(self._pending)):
+                if int(bs[:, k].sum()) != int(sc[:, k, 3].sum()) and not os.environ.get("LIME_DEBUG"):
+                    raise CarryDetected(f"strand {k}: byte sum {int(bs[:, k].sum())} != total added {int(sc[:, k, 3].sum())}")
+        return out
+
+    def close(self):
+        self.dist.barrier()
+        self.be.ctx.peer_close()
 
 
 class _NoTimer:

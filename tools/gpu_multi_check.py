@@ -75,15 +75,26 @@ def main():
         for s, sh in enumerate(shards):
             job.run_strand(s, sh, alpha, 0.25, ebwt_mode, 100)
         got = job.finish(v, m, 1, True)
+        # the same job with the exchange folded into the kernel (adds over peer memory)
+        pj = multi.PeerJob(dist, torch, be, rank, world, n_reads, n_refs, n_strands)
+        got_p = None
+        for rep in range(2):                       # twice: the slabs are reused
+            pj.begin()
+            for s, sh in enumerate(shards):
+                pj.run_strand(s, sh, alpha, 0.25, ebwt_mode, 100)
+            got_p = [np.array(a) for a in pj.finish(v, m, 1, True)]
+        pj.close()
         # single-GPU job on the whole arrays (every rank computes it, cheap at this size)
         strands = [{"ebwt": e.data_ptr(), "lcp": l.data_ptr(), "da": d.data_ptr(), "n": n} for (e, l, d) in whole]
         exp, stats = run_job(ctx, strands, n_reads, n_refs, 100, alpha, 0.25, ebwt_mode, v, m, 1, True, mem=MEM_DEVICE)
         same = all(np.array_equal(np.asarray(a).view(np.uint8), np.asarray(b).view(np.uint8)) for a, b in zip(got, exp))
+        same_p = all(np.array_equal(np.asarray(a).view(np.uint8), np.asarray(b).view(np.uint8)) for a, b in zip(got_p, exp))
         sc = all(js["n_clusters"] == st[0] and js["max_len"] == st[1] for js, st in zip(job.stats, stats))
+        sc = sc and all(js["n_clusters"] == st[0] and js["max_len"] == st[1] for js, st in zip(pj.stats, stats))
         kinds = {chr(t): int((got[0] == t).sum()) for t in np.unique(got[0])}
-        print(f"rank {rank}/{world}: n={n} strands={n_strands} ebwt={ebwt_mode} alpha={alpha}: assignments equal={same} "
+        print(f"rank {rank}/{world}: n={n} strands={n_strands} ebwt={ebwt_mode} alpha={alpha}: assignments equal={same} peer-memory job equal={same_p} "
               f"scalars equal={sc} {kinds} triples sent={[js['triples_sent'] for js in job.stats]}", flush=True)
-        ok = ok and same and sc
+        ok = ok and same and same_p and sc
     flag = torch.tensor([0 if ok else 1], device=dev)
     dist.all_reduce(flag)
     dist.barrier()
