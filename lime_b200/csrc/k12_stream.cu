@@ -85,6 +85,27 @@ __device__ __forceinline__ void cp_async16(unsigned smem_addr, const void *gmem)
 {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gmem) : "memory");
 }
+// the same with an L2 eviction policy (createpolicy): the inputs are read once and should not push the
+// similarity matrix out of L2
+__device__ __forceinline__ void cp_async16_hint(unsigned smem_addr, const void *gmem, uint64_t pol)
+{
+    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(smem_addr), "l"(gmem), "l"(pol) : "memory");
+}
+// 0 evict_normal, 1 evict_first, 2 evict_last, 3 / 4 evict_last for one half / one quarter of the lines
+__device__ __forceinline__ uint64_t l2_policy(int kind)
+{
+    uint64_t p;
+    if (kind == 1) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    else if (kind == 2) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    else if (kind == 3) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 0.5;" : "=l"(p));
+    else if (kind == 4) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 0.25;" : "=l"(p));
+    else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ void red_add_hint(unsigned *addr, unsigned v, uint64_t pol)
+{
+    asm volatile("red.relaxed.gpu.global.add.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(addr), "r"(v), "l"(pol) : "memory");
+}
 __device__ __forceinline__ void cp_async_wait_all()
 {
     asm volatile("cp.async.wait_all;" ::: "memory");
@@ -120,6 +141,12 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
     // reference wraps, ClusterBWT_DA.cpp:183,247) lowers the byte sum of the matrix by 255 or 256, so
     // the host proves their absence afterwards by comparing the byte sum of the matrix with the
     // total of all t (sum_t) and otherwise reruns the pass into exact 32-bit cells.
+    // L2 policies: the inputs are read once (evict_first), the lines of the similarity matrix should stay
+    // (evict_last); together 4.23 -> 3.67 ms per step on the BASELINE workload.  Experiment switches:
+    // dbg 1024 = inputs evict_normal, 2048 = adds without a policy, 4096 / 8192 = evict_last for 1/2, 1/4 of the lines
+    const uint64_t pol_in = l2_policy((P.dbg & 1024u) ? 0 : 1);
+    const uint64_t pol_mat = l2_policy((P.dbg & 4096u) ? 3 : (P.dbg & 8192u) ? 4 : 2);
+
     const bool red_mode = P.sum_t != nullptr;
     unsigned long long t_total = 0;                           // sum of t added by this lane
     auto add_update = [&](uint32_t r, uint32_t g, uint32_t t) {
@@ -143,7 +170,9 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
             return;
         }
         if (red_mode) {
-            atomicAdd(reinterpret_cast<unsigned *>(acc.sim8 + (size_t)r * acc.pitch8) + (g >> 2), t << ((g & 3u) * 8u));
+            unsigned *wp = reinterpret_cast<unsigned *>(acc.sim8 + (size_t)r * acc.pitch8) + (g >> 2);
+            if (P.dbg & 2048u) atomicAdd(wp, t << ((g & 3u) * 8u));
+            else red_add_hint(wp, t << ((g & 3u) * 8u), pol_mat);
             t_total += t;
             return;
         }
@@ -170,13 +199,13 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
         const char *pl = g_lcp + 4 * aa, *pd = g_da + 4 * aa;
 #pragma unroll
         for (int k = 0; k < CH / 128; k++) {
-            cp_async16(s_lcp + 512 * k, pl + 512 * k);
-            cp_async16(s_da + 512 * k, pd + 512 * k);
+            cp_async16_hint(s_lcp + 512 * k, pl + 512 * k, pol_in);
+            cp_async16_hint(s_da + 512 * k, pd + 512 * k, pol_in);
         }
         if (SCORE && EBWT) {
             const char *pe = g_eb + aa;
 #pragma unroll
-            for (int k = 0; k < CH / 512; k++) cp_async16(s_eb + 512 * k, pe + 512 * k);
+            for (int k = 0; k < CH / 512; k++) cp_async16_hint(s_eb + 512 * k, pe + 512 * k, pol_in);
         }
         return true;
     };
