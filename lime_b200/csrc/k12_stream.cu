@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
                 if (P.dbg & 256u) rem &= 0x3ffffu;                                   // 28 MB per owner
                 row = P.peer.base[dst] + (size_t)rem * P.pitch8;
             }
-            atomicAdd(reinterpret_cast<unsigned *>(row) + (g >> 2), t << ((g & 3u) * 8u));
+            red_add_hint(reinterpret_cast<unsigned *>(row) + (g >> 2), t << ((g & 3u) * 8u), pol_mat);
             t_total += t;
             return;
         }

@@ -89,6 +89,32 @@ class CudaBackend:
     def classify(self, n_files, n_refs, v, m, tax_rank, higher):
         return self.ctx.classify(n_files, n_refs, v, m, tax_rank, higher)
 
+    # ---- peer-memory accumulation (PeerJob) -------------------------------------------------------
+    def peer_setup(self, dist, world, rank, rows, n_refs, n_slabs):
+        """Allocate this rank's slabs, all-gather the CUDA IPC handles, map every owner's slabs."""
+        torch = self.torch
+        mine = torch.from_numpy(self.ctx.peer_alloc(rows, n_refs, n_slabs).copy()).to(self.device)
+        parts = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(parts, mine)
+        self.ctx.peer_open(world, rank, torch.stack(parts).cpu().numpy(), rows)
+        dist.barrier()                       # every rank has mapped every slab
+
+    def peer_zero(self):
+        self.ctx.peer_zero()
+
+    def peer_accumulate(self, alpha, ebwt_mode, slab):
+        return self.ctx.peer_accumulate(alpha, ebwt_mode, slab)
+
+    def peer_select(self, slab, total_updates, byte_sums, k):
+        """byte_sums: int64 tensor of the job; element k receives the slab's byte sum (asynchronously)."""
+        self.ctx.peer_select(slab, total_updates, byte_sums.data_ptr() + 8 * k)
+
+    def peer_zero_slab(self, slab):
+        self.ctx.peer_zero_slab(slab)
+
+    def peer_close(self):
+        self.ctx.peer_close()
+
     def classify_tensors(self, n_files, n_refs, v, m, tax_rank, higher, pad_to):
         """Classify and leave the assignments on the device: (type u8, taxid i32, sim-bits i32) tensors
         of pad_to elements (zero beyond this rank's reads), ready for an all-gather over NVLink."""
@@ -258,23 +284,19 @@ class PeerJob:
         self.timer = timer or (lambda name: _NoTimer())
         self.stats, self._local, self._pending = [], [], []
         self._inner = ShardedJob(dist, torch, backend, rank, world, n_reads, n_refs)   # finish() = classify + gather
-        ctx, dev = backend.ctx, backend.device
-        handle = ctx.peer_alloc(self.per, n_refs, n_strands)
-        mine = torch.from_numpy(handle.copy()).to(dev)
-        parts = [torch.empty_like(mine) for _ in range(world)]
-        dist.all_gather(parts, mine)
-        ctx.peer_open(world, rank, torch.stack(parts).cpu().numpy(), self.per)
-        dist.barrier()                       # every rank has mapped every slab
+        backend.peer_setup(dist, world, rank, self.per, n_refs, n_strands)
         self._dirty = False
-        self._bs = torch.zeros(n_strands, dtype=torch.int64, device=dev)
+        self._bs = torch.zeros(n_strands, dtype=torch.int64)
+        if getattr(backend, "device", None) is not None:
+            self._bs = self._bs.to(backend.device)
 
     def _all_gather_i64(self, values):
         """Every rank's vector of integers, as a (world, len) int64 numpy array; also a barrier."""
         torch, dist = self.torch, self.dist
-        t = torch.tensor(values, dtype=torch.int64).to(self.be.device)
-        out = torch.empty(self.world * t.numel(), dtype=torch.int64, device=self.be.device)
-        dist.all_gather_into_tensor(out, t)
-        return out.cpu().numpy().reshape(self.world, -1)
+        t = self._inner._cpu_or_dev(values)
+        parts = [torch.empty_like(t) for _ in range(self.world)]
+        dist.all_gather(parts, t)
+        return torch.stack(parts).cpu().numpy().reshape(self.world, -1)
 
     def begin(self):
         """Nobody may add before every rank's slabs are zero: true after the constructor (fresh slabs,
@@ -282,7 +304,7 @@ class PeerJob:
         an abandoned job needs the explicit zero + barrier."""
         if self._dirty:
             with self.timer("zero"):
-                self.be.ctx.peer_zero()
+                self.be.peer_zero()
                 self.dist.barrier()
         self._dirty = True
         self.stats, self._local, self._pending = [], [], []
@@ -292,7 +314,7 @@ class PeerJob:
         with self.timer("compute"):
             be.load(shard["lcp"], shard["da"], shard["ebwt"] if ebwt_mode else None, shard["n_own"], shard["n_halo"],
                     shard["pos_base"], shard["is_last"], self.n_reads, self.n_refs)
-            n_cl, max_len, updates, sum_t = be.ctx.peer_accumulate(alpha, ebwt_mode, slot)
+            n_cl, max_len, updates, sum_t = be.peer_accumulate(alpha, ebwt_mode, slot)
         self._local += [n_cl, max_len, updates, sum_t]
         self._pending.append((slot, norm_of(read_len, alpha), beta))
 
@@ -304,18 +326,18 @@ class PeerJob:
             sc = self._all_gather_i64(self._local).reshape(self.world, len(self._pending), 4)
         with self.timer("choose"):
             for k, (slot, norm, beta) in enumerate(self._pending):
-                be.ctx.peer_select(slot, int(sc[:, k, 2].sum()), self._bs.data_ptr() + 8 * k)
+                be.peer_select(slot, int(sc[:, k, 2].sum()), self._bs, k)
                 n_rec = be.choose(slot, norm, beta, 0, self.hi - self.lo)
-                be.ctx.peer_zero_slab(slot)               # ready for the next job once `check` has completed
+                be.peer_zero_slab(slot)                   # ready for the next job once `check` has completed
                 self.stats.append({"n_clusters": int(sc[:, k, 0].sum()), "max_len": int(sc[:, k, 1].max()),
                                    "n_records_local": int(n_rec), "updates": int(sc[:, k, 2].sum())})
         inner = self._inner
         inner.timer, inner.n_strands = self.timer, len(self._pending)
         out = inner.finish(v, m, tax_rank, higher, gather=gather)
         with self.timer("check"):
-            allbs = self.torch.empty(self.world * self._bs.numel(), dtype=self.torch.int64, device=be.device)
-            self.dist.all_gather_into_tensor(allbs, self._bs)
-            bs = allbs.cpu().numpy().reshape(self.world, -1)
+            parts = [self.torch.empty_like(self._bs) for _ in range(self.world)]
+            self.dist.all_gather(parts, self._bs)
+            bs = self.torch.stack(parts).cpu().numpy().reshape(self.world, -1)
             self._dirty = False
             for k in range(len(self._pending)):
                 if int(bs[:, k].sum()) != int(sc[:, k, 3].sum()) and not os.environ.get("LIME_DEBUG"):
@@ -324,7 +346,7 @@ class PeerJob:
 
     def close(self):
         self.dist.barrier()
-        self.be.ctx.peer_close()
+        self.be.peer_close()
 
 
 class _NoTimer:

@@ -66,6 +66,44 @@ class OracleBackend:
         return self.o.classify(bins, poss, n_refs, v, m, tax_rank, higher)
 
 
+    # ---- peer-memory emulation (PeerJob): every owner's slabs are one shared file; the ranks add in turn,
+    # which plays the role of the kernel's atomic adds into the owner's memory
+    def peer_setup(self, dist, world, rank, rows, n_refs, n_slabs):
+        self.pd = (dist, world, rank, rows)
+        path = lambda r: os.path.join(self.shm_dir, f"slab{r}.u8")
+        mine = np.memmap(path(rank), dtype=np.uint8, mode="w+", shape=(n_slabs, rows, n_refs))
+        mine[:] = 0
+        mine.flush()
+        dist.barrier()
+        self.slabs = [np.memmap(path(r), dtype=np.uint8, mode="r+", shape=(n_slabs, rows, n_refs)) for r in range(world)]
+
+    def peer_zero(self):
+        self.slabs[self.pd[2]][:] = 0
+
+    def peer_accumulate(self, alpha, ebwt_mode, slab):
+        dist, world, rank, rows = self.pd
+        n_cl, mx = self.cluster_similarity(alpha, ebwt_mode)
+        for turn in range(world):
+            if turn == rank:
+                for k in range(world):
+                    lo, hi = k * rows, min((k + 1) * rows, self.n_reads)
+                    if hi > lo:
+                        self.slabs[k][slab, :hi - lo] += self.sim[lo:hi]            # uint8 wrap, as the cell
+                        self.slabs[k].flush()
+            dist.barrier()
+        return n_cl, mx, int(np.count_nonzero(self.sim)), int(self.sim.astype(np.int64).sum())
+
+    def peer_select(self, slab, total_updates, byte_sums, k):
+        self.sim = np.array(self.slabs[self.pd[2]][slab])
+        byte_sums[k] = int(self.sim.astype(np.int64).sum())
+
+    def peer_zero_slab(self, slab):
+        self.slabs[self.pd[2]][slab] = 0
+
+    def peer_close(self):
+        self.slabs = None
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -74,7 +112,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, strands, n_reads, n_refs, read_len, alpha, beta, halo, v, m, q):
+def _worker(rank, world, port, strands, n_reads, n_refs, read_len, alpha, beta, halo, v, m, q, peer_dir=None):
     import torch
     import torch.distributed as dist
     from oracle.oracle import Oracle
@@ -82,7 +120,13 @@ def _worker(rank, world, port, strands, n_reads, n_refs, read_len, alpha, beta, 
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     be = OracleBackend(Oracle(), torch)
-    job = multi.ShardedJob(dist, torch, be, rank, world, n_reads, n_refs)
+    if peer_dir:
+        be.shm_dir = peer_dir
+        job = multi.PeerJob(dist, torch, be, rank, world, n_reads, n_refs, len(strands))
+        job.begin()
+    else:
+        job = multi.ShardedJob(dist, torch, be, rank, world, n_reads, n_refs)
+    job_shards = []
     for s, (ebwt, lcp, da) in enumerate(strands):
         n = lcp.shape[0]
         a, b = multi.shard_ranges(n, world)[rank]
@@ -93,16 +137,25 @@ def _worker(rank, world, port, strands, n_reads, n_refs, read_len, alpha, beta, 
         t[2][:b - a] = torch.from_numpy(ebwt[a:b])
         got = multi.exchange_halo(dist, rank, world, t, b - a, halo)
         assert got == h
-        st = job.run_strand(s, dict(lcp=t[0], da=t[1], ebwt=t[2], n_own=b - a, n_halo=h, pos_base=a,
-                                    is_last=rank == world - 1), alpha, beta, 1, read_len)
+        job_shards.append(dict(lcp=t[0], da=t[1], ebwt=t[2], n_own=b - a, n_halo=h, pos_base=a, is_last=rank == world - 1))
+        job.run_strand(s, job_shards[-1], alpha, beta, 1, read_len)
     typ, tax, sim = job.finish(v, m, 1, m is not None)
+    if peer_dir:
+        # the slabs are reused by the next job without an explicit zero + barrier
+        first = [np.array(x) for x in (typ, tax, sim)]
+        job.begin()
+        for s, sh in enumerate(job_shards):
+            job.run_strand(s, sh, alpha, beta, 1, read_len)
+        typ, tax, sim = job.finish(v, m, 1, m is not None)
+        assert all(a.tobytes() == np.asarray(b).tobytes() for a, b in zip(first, (typ, tax, sim)))
+        job.close()
     q.put((rank, typ, tax, sim, job.stats))
     dist.barrier()
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_sharded_job_equals_single_process(oracle, world):
+@pytest.mark.parametrize("world,peer", [(2, False), (3, False), (2, True), (3, True)])
+def test_sharded_job_equals_single_process(oracle, world, peer, tmp_path):
     import torch.multiprocessing as mp
     n_reads, n_refs, read_len, alpha, beta = 1201, 9, 100, 14, 0.25
     strands = []
@@ -122,7 +175,8 @@ def test_sharded_job_equals_single_process(oracle, world):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, strands, n_reads, n_refs, read_len, alpha, beta, 2048, v, m, q))
+    procs = [ctx.Process(target=_worker, args=(r, world, port, strands, n_reads, n_refs, read_len, alpha, beta, 2048, v, m, q,
+                                               str(tmp_path) if peer else None))
              for r in range(world)]
     for p in procs:
         p.start()
@@ -134,5 +188,5 @@ def test_sharded_job_equals_single_process(oracle, world):
         assert typ.tobytes() == exp[0].tobytes() and tax.tobytes() == exp[1].tobytes() and sim.tobytes() == exp[2].tobytes()
         for s in range(2):
             assert (stats[s]["n_clusters"], stats[s]["max_len"]) == scal[s]
-        assert stats[0]["triples_sent"] > 0
+        assert peer or stats[0]["triples_sent"] > 0
     assert set(chr(t) for t in exp[0]) >= {"C", "U"}
