@@ -170,6 +170,45 @@ def test_export_import_roundtrip(ctx, oracle, n_refs, ebwt_mode, alpha):
     assert np.array_equal(ctx.sim_matrix(), want)
 
 
+@pytest.mark.parametrize("ebwt_mode,alpha", [(1, 16), (0, 12)])
+def test_peer_slab_accumulation(oracle, ebwt_mode, alpha):
+    """lime_peer_*: the fused kernel adding into owner slabs (K12<PEER>), here with one owner in one
+    process (CUDA IPC cannot map a process's own allocation twice; 2 and 8 owners are checked under
+    torchrun by tools/gpu_multi_check.py).  Slab contents, byte-sum carry proof, choose on the slab,
+    slab reuse after lime_peer_zero_slab."""
+    import torch
+    from lime_b200.api import LimeContext
+    case = C.synth_case(f"synth_peer{ebwt_mode}", 1_500_000, 15_000, 37, seed=91 + ebwt_mode, p_long=2e-5, max_seg=60000)
+    ebwt = case["ebwt"] if ebwt_mode else None
+    cl, mx = oracle.cluster_detect(case["lcp"], case["da"], case["n_reads"], alpha)
+    sim_o = oracle.similarity(cl, case["da"], ebwt, case["n_reads"], case["n_refs"])
+    norm = (case["read_len"] + 1 - alpha) & 0xFFFFFFFF
+    bin_o, pos_o = oracle.choose(sim_o, norm, np.float32(0.25))
+    c = LimeContext(0)
+    try:
+        handle = c.peer_alloc(case["n_reads"], case["n_refs"], 2)
+        c.peer_open(1, 0, handle, case["n_reads"])
+        bs = torch.zeros(2, dtype=torch.int64, device="cuda:0")
+        for rep in range(2):                                    # second round: reused slabs
+            for slab in (0, 1):
+                c.load(case["lcp"], case["da"], ebwt, case["n_reads"], case["n_refs"])
+                n_cl, max_len, updates, sum_t = c.peer_accumulate(alpha, ebwt_mode, slab)
+                assert (n_cl, max_len) == (cl.shape[0], mx)
+                assert sum_t == int(sim_o.astype(np.int64).sum()) and updates >= np.count_nonzero(sim_o)
+            for slab in (0, 1):
+                c.peer_select(slab, updates, bs.data_ptr() + 8 * slab)
+                assert np.array_equal(c.sim_matrix(), sim_o)
+                n_rec = c.choose(slab, norm, 0.25, 0, case["n_reads"])
+                bin_g, pos_g = c.choose_result(slab)
+                assert n_rec == bin_o.shape[0] and bin_g.tobytes() == bin_o.tobytes() and pos_g.tobytes() == pos_o.tobytes()
+                c.peer_zero_slab(slab)
+            torch.cuda.synchronize()
+            assert bs.tolist() == [sum_t, sum_t]
+        c.peer_close()
+    finally:
+        c.close()
+
+
 def test_sharded_loads_union_equals_whole(ctx, oracle):
     """Position shards with a halo (lime_load n_own / n_halo / pos_base / is_last): the clusters of
     the shards are a partition of the whole array's clusters and the matrices add up mod 256."""
