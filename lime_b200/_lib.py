@@ -70,6 +70,9 @@ SIGNATURES = {
     # host-side helpers (lime_host.h)
     "lime_host_fix_rank": (C.c_int64, [C.c_char_p, C.c_int, C.c_uint32, vp, C.c_uint64, vp]),
     "lime_host_write_csv": (C.c_int, [C.c_char_p, C.c_uint32, vp, vp, vp]),
+    "lime_host_read_gesa": (C.c_int64, [C.c_char_p, vp, vp, vp, C.c_uint64]),
+    "lime_host_write_res_txt": (C.c_int, [C.c_char_p, vp, C.c_uint64, vp, C.c_uint32]),
+    "lime_host_read_res_txt": (C.c_int64, [C.c_char_p, C.c_uint32, vp, C.c_uint64, vp]),
 }
 
 _lib = None

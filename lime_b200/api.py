@@ -270,6 +270,39 @@ def fix_rank(path, tax_rank, n_refs, higher=False):
     return (v[:n_refs] if found == n_refs else None), (m[:, :n_refs].copy() if m is not None else None), int(found)
 
 
+def read_gesa(path):
+    """<fasta>.<numSeq>.gesa (egsa) -> (ebwt u8, lcp u32, da u32), EGSAtoBCR.cpp:72-91."""
+    lib = _lib.load()
+    n = lib.lime_host_read_gesa(path.encode(), None, None, None, 0)
+    if n < 0:
+        raise FileNotFoundError(path)
+    ebwt, lcp, da = np.empty(n, np.uint8), np.empty(n, np.uint32), np.empty(n, np.uint32)
+    lib.lime_host_read_gesa(path.encode(), _ptr(ebwt), _ptr(lcp), _ptr(da), n)
+    return ebwt, lcp, da
+
+
+def write_res_txt(path, bin_, pos):
+    """BIN=0 text form of the .res.bin / .res.pos images (ClusterBWT_DA.cpp:414,424,440)."""
+    lib = _lib.load()
+    bin_ = np.ascontiguousarray(bin_, dtype=PAIR_SIM_DT)
+    pos = np.ascontiguousarray(pos, dtype=np.uint64)
+    rc = lib.lime_host_write_res_txt(path.encode(), _ptr(bin_), bin_.shape[0], _ptr(pos), pos.shape[0])
+    if rc != 0:
+        raise OSError(f"cannot write {path} ({rc})")
+
+
+def read_res_txt(path, n_reads):
+    """<fasta>.res.txt -> (.res.bin image, .res.pos image) holding the values of the text."""
+    lib = _lib.load()
+    pos = np.zeros(max(n_reads, 1), dtype=np.uint64)
+    n = lib.lime_host_read_res_txt(path.encode(), n_reads, None, 0, _ptr(pos))
+    if n < 0:
+        raise OSError(f"cannot read {path} ({n})")
+    bin_ = np.zeros(n, dtype=PAIR_SIM_DT)
+    lib.lime_host_read_res_txt(path.encode(), n_reads, _ptr(bin_), n, _ptr(pos))
+    return bin_, pos[:n_reads]
+
+
 def write_csv(path, typ, tax, sim):
     lib = _lib.load()
     typ = np.ascontiguousarray(typ, dtype=np.uint8)

@@ -10,6 +10,9 @@ using namespace limehost;
 #ifndef HIGHER
 #define HIGHER 0
 #endif
+#ifndef BIN
+#define BIN 1          // 0: text inputs <in_i>.txt (reference Makefile:12, Classify.cpp:430-444)
+#endif
 
 static const char *USAGE = " N fileInput1 fileInput2 ... fileInputN numReads numGenomes fileOutput fileTaxo taxRank numThreads";
 
@@ -68,6 +71,7 @@ int main(int argc, char **argv)
     if (rc) die_lime(nullptr, "lime_init", rc);
     std::cout << "Reading files:";                                                                  // :401-445
     for (unsigned i = 0; i < numFile; i++) {
+#if BIN
         const std::string sFileBin = fileInput[i] + ".bin", sFilePos = fileInput[i] + ".pos";
         std::cout << "\n\t" << sFileBin;
         std::cout << "\n\t" << sFilePos;
@@ -79,6 +83,20 @@ int main(int argc, char **argv)
         if (rc) die_lime(ctx, "lime_slot_set", rc);
         lime_pinned_free(bin);
         lime_pinned_free(pos);
+#else
+        // one text line per read; the same tokens the reference parses (Classify.cpp:128-153) become
+        // the record images the classification kernel reads
+        const std::string sFileTxt = fileInput[i] + ".txt";
+        std::cout << "\n\t" << sFileTxt;
+        std::vector<uint64_t> pos(numReads ? numReads : 1);
+        const int64_t nRec = lime_host_read_res_txt(sFileTxt.c_str(), numReads, nullptr, 0, pos.data());
+        if (nRec == -1) { std::cerr << "Error opening " << sFileTxt << std::endl; exit(1); }     // :439-442
+        if (nRec < 0) { std::cerr << "\nError: " << sFileTxt << " holds fewer than numReads lines." << std::endl; exit(EXIT_FAILURE); }
+        std::vector<lime_pair_sim> bin((size_t)nRec);
+        lime_host_read_res_txt(sFileTxt.c_str(), numReads, bin.data(), (uint64_t)nRec, pos.data());
+        rc = lime_slot_set(ctx, (int)i, bin.data(), (uint64_t)nRec, pos.data(), numReads);
+        if (rc) die_lime(ctx, "lime_slot_set", rc);
+#endif
     }
     std::cout << std::endl;
 

@@ -9,6 +9,9 @@ using namespace limehost;
 #ifndef EBWT
 #define EBWT 1
 #endif
+#ifndef BIN
+#define BIN 1          // 0: text output <fasta>.res.txt (reference Makefile:12, ClusterBWT_DA.cpp:715-726)
+#endif
 
 int main(int argc, char **argv)
 {
@@ -75,6 +78,7 @@ int main(int argc, char **argv)
     fprintf(stderr, "TIME clusterAnalyze: %.6lf\n", t_an.seconds());           // :683-687
 
     const std::string fnF = fileFasta + ".res";                                // :701-714
+#if BIN
     const std::string sResultPos = fnF + ".pos", sResultBin = fnF + ".bin";
     FILE *fdPos = fopen(sResultPos.c_str(), "wb");
     std::cerr << "Writing " << sResultPos << std::endl;
@@ -82,19 +86,32 @@ int main(int argc, char **argv)
     std::cerr << "Writing " << sResultBin << std::endl;
     if (!fdPos) die_open(sResultPos);
     if (!fdBin) die_open(sResultBin);
+#else
+    const std::string sResultTxt = fnF + ".txt";
+    {
+        FILE *probe = fopen(sResultTxt.c_str(), "w");
+        if (!probe) die_open(sResultTxt);
+        fclose(probe);
+    }
+    std::cerr << "Writing " << sResultTxt << std::endl;
+#endif
     Timer t_ch;
     uint64_t nRecords = 0;
     rc = lime_choose(ctx, 0, norm, beta, 0, numRead, &nRecords);
     if (rc) die_lime(ctx, "lime_choose", rc);
     std::vector<lime_pair_sim> bin(nRecords);
-    std::vector<uint64_t> pos(numRead);
+    std::vector<uint64_t> pos(numRead ? numRead : 1);
     rc = lime_choose_copy(ctx, 0, bin.data(), pos.data());
     if (rc) die_lime(ctx, "lime_choose_copy", rc);
+#if BIN
     fwrite(bin.data(), sizeof(lime_pair_sim), nRecords, fdBin);
     if (numRead) fwrite(pos.data(), sizeof(uint64_t), numRead, fdPos);
     fclose(fdBin);
     fclose(fdPos);
     std::cout << "Output (in bytes): " << nRecords << "\t" << sizeof(lime_pair_sim) << std::endl;  // :446
+#else
+    if (lime_host_write_res_txt(sResultTxt.c_str(), bin.data(), nRecords, pos.data(), numRead) != 0) die_open(sResultTxt);
+#endif
     fprintf(stdout, "Time: %.6lf\n", t_ch.seconds());                          // :744
 
     std::cout << "Cluster analysis completed with beta=" << beta << "." << std::endl;      // :757-758

@@ -68,3 +68,75 @@ extern "C" int lime_host_write_csv(const char *path, uint32_t n_reads,
     out.write(buf.data(), (std::streamsize)buf.size());
     return out.good() ? 0 : -1;
 }
+
+// ---- .gesa (egsa output) -> ebwt / lcp / da, EGSAtoBCR.cpp:9-15,72-91 --------------------------------
+// record = { u32 text (document id), u32 suff, u32 lcp, u8 bwt }, 13 bytes, no padding, no header
+extern "C" int64_t lime_host_read_gesa(const char *path, uint8_t *ebwt, uint32_t *lcp, uint32_t *da, uint64_t cap)
+{
+    FILE *f = std::fopen(path, "rb");
+    if (!f) return -1;
+    constexpr size_t REC = 13, BATCH = 1 << 16;
+    std::string buf(REC * BATCH, '\0');
+    uint64_t n = 0;
+    size_t got;
+    while ((got = std::fread(&buf[0], 1, REC * BATCH, f)) >= REC) {
+        const size_t recs = got / REC;          // a truncated last record is dropped, as by the reference loop
+        for (size_t i = 0; i < recs; i++, n++) {
+            if (n >= cap) continue;             // keep counting: the caller sizes its arrays from the result
+            const unsigned char *p = reinterpret_cast<const unsigned char *>(&buf[i * REC]);
+            std::memcpy(&da[n], p, 4);
+            std::memcpy(&lcp[n], p + 8, 4);
+            ebwt[n] = p[12];
+        }
+        if (got % REC) break;
+    }
+    std::fclose(f);
+    return (int64_t)n;
+}
+
+// ---- BIN=0: <fasta>.res.txt, one line per read (ClusterBWT_DA.cpp:414,424,440) -------------------------
+extern "C" int lime_host_write_res_txt(const char *path, const lime_pair_sim *bin, uint64_t n_records,
+                                       const uint64_t *pos, uint32_t n_reads)
+{
+    FILE *f = std::fopen(path, "w");
+    if (!f) return -1;
+    for (uint32_t r = 0; r < n_reads; r++) {
+        const uint64_t h = pos[r];
+        if (h) {
+            if (h >= n_records || h + bin[h].idRef >= n_records) { std::fclose(f); return -2; }
+            std::fprintf(f, "%.5f", bin[h].sim);
+            for (uint32_t j = 1; j <= bin[h].idRef; j++) std::fprintf(f, "\t%u\t%.5f", bin[h + j].idRef, bin[h + j].sim);
+        }
+        std::fputc('\n', f);
+    }
+    return std::fclose(f) == 0 ? 0 : -1;
+}
+
+// The reverse (Classify.cpp:128-153 reads the same tokens with operator>>): images of .res.bin / .res.pos
+// with the values the text holds.  Returns the number of records incl. the sentinel (it may exceed
+// bin_cap: nothing is written past it), -1 if the file cannot be opened, -2 on fewer than n_reads lines.
+extern "C" int64_t lime_host_read_res_txt(const char *path, uint32_t n_reads, lime_pair_sim *bin, uint64_t bin_cap,
+                                          uint64_t *pos)
+{
+    std::ifstream in(path);
+    if (!in.is_open()) return -1;
+    uint64_t total = 1;
+    if (bin_cap) { bin[0].sim = 0.0f; bin[0].idRef = 0; }
+    std::string line;
+    for (uint32_t r = 0; r < n_reads; r++) {
+        if (!std::getline(in, line)) return -2;
+        std::istringstream is(line);
+        float mx;
+        if (!(is >> mx)) { pos[r] = 0; continue; }
+        const uint64_t h = total++;
+        uint32_t count = 0, id;
+        float s;
+        while ((is >> id) && (is >> s)) {
+            if (total < bin_cap) { bin[total].sim = s; bin[total].idRef = id; }
+            total++; count++;
+        }
+        if (h < bin_cap) { bin[h].sim = mx; bin[h].idRef = count; }
+        pos[r] = h;
+    }
+    return (int64_t)total;
+}

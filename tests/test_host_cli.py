@@ -26,7 +26,8 @@ def test_executables_are_built_and_print_the_reference_usage():
                    ("Classify", "N fileInput1 fileInput2 ... fileInputN numReads numGenomes fileOutput fileTaxo taxRank numThreads"),
                    ("Classify_higher1", "N fileInput1"),
                    ("LiME_fused", "N File_1 ... File_N output numReads numGenomes LineageFile readLen threads"),
-                   ("LiME_fused_ebwt0", "N File_1"), ("LiME_fused_higher1", "N File_1")):
+                   ("LiME_fused_ebwt0", "N File_1"), ("LiME_fused_higher1", "N File_1"),
+                   ("ClusterBWT_DA_bin0", "fileFasta readLen beta threads"), ("Classify_bin0", "N fileInput1")):
         r = _run(exe, [], ROOT)
         assert r.returncode == 1 and "Error usage" in r.stderr and n in r.stderr, (exe, r.stderr)
     r = _run("Classify", [3, "a", "b", "c", 1, 1, "o", "t", 1, 1], ROOT)
@@ -167,3 +168,40 @@ def test_fused_driver_equals_the_three_steps(tmp_path, oracle, n_files, exe, ebw
              str(tmp_path))
     assert r.returncode == 0, r.stderr
     assert open(out3, "rb").read() == open(exp, "rb").read()
+
+
+@pytest.mark.gpu
+def test_bin0_text_variants(tmp_path, oracle):
+    """BIN=0 builds: ClusterBWT_DA_bin0 writes <fasta>.res.txt, Classify_bin0 reads <in>.txt
+    (the text format itself is pinned against the reference in tests/test_formats.py)."""
+    from lime_b200 import api
+    alpha, beta, read_len, n_reads, n_refs, tax_rank = 16, 0.25, 100, 2500, 12, 1
+    lin = str(tmp_path / "lineage.csv")
+    with open(lin, "w", newline="") as f:
+        f.write(C.lineage_text(C.default_lineage(n_refs, holes=False, seed=5)))
+    stems, bins, poss = [], [], []
+    for i in range(2):
+        case = C.synth_case(f"tx{i}", 300_000 + 11 * i, n_reads, n_refs, seed=400 + i, p_long=2e-4, max_seg=3000)
+        fasta = str(tmp_path / f"m{i}+Refs.fasta")
+        datagen.write_strand(fasta, case["ebwt"], case["lcp"], case["da"])
+        assert _run("ClusterLCP", [fasta, n_reads, n_refs, alpha, 4], str(tmp_path)).returncode == 0
+        r = _run("ClusterBWT_DA_bin0", [fasta, read_len, beta, 4], str(tmp_path))
+        assert r.returncode == 0, r.stderr
+        assert not os.path.exists(fasta + ".res.bin")
+        cl, _ = oracle.cluster_detect(case["lcp"], case["da"], n_reads, alpha)
+        b, p = oracle.choose(oracle.similarity(cl, case["da"], case["ebwt"], n_reads, n_refs), read_len + 1 - alpha, np.float32(beta))
+        exp_txt = str(tmp_path / f"exp{i}.txt")
+        api.write_res_txt(exp_txt, b, p)
+        assert open(fasta + ".res.txt", "rb").read() == open(exp_txt, "rb").read()
+        b5, p5 = api.read_res_txt(exp_txt, n_reads)
+        stems.append(fasta + ".res"); bins.append(b5); poss.append(p5)
+    out = str(tmp_path / "ours.csv")
+    r = _run("Classify_bin0", [2] + stems + [n_reads, n_refs, out, lin, tax_rank, 2], str(tmp_path))
+    assert r.returncode == 0, r.stderr
+    v, m, _ = oracle.fix_rank(lin, tax_rank, n_refs, False)
+    typ, tax, sim = oracle.classify(bins, poss, n_refs, v, None, tax_rank, False)
+    exp = str(tmp_path / "oracle.csv")
+    oracle.write_csv(exp, typ, tax, sim)
+    assert open(out, "rb").read() == open(exp, "rb").read()
+    r = _run("Classify_bin0", [2, str(tmp_path / "nope"), stems[1], n_reads, n_refs, out, lin, tax_rank, 2], str(tmp_path))
+    assert r.returncode == 1 and "Error opening" in r.stderr
