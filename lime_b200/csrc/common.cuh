@@ -246,7 +246,7 @@ struct K12Args {
     uint32_t alpha, n_reads, n_refs;
     lime_cluster *out;                // EMIT: records in ascending pStart order
     uint64_t out_cap;
-    unsigned long long *tile_state;   // EMIT: look-back descriptors
+    unsigned long long *tile_state;   // EMIT: per-chunk cluster counts, turned into record offsets by a scan
     unsigned long long *n_clusters;   // device scalars
     unsigned long long *max_len;
     unsigned int *err;                // bit0: halo exhausted

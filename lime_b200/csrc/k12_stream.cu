@@ -675,7 +675,7 @@ static cudaError_t launch_variant(const K12Args &a, cudaStream_t s)
     if (!ebwt && !exact32)             return CALL(true, false, false, false);               \
     return CALL(true, false, false, true);
 
-// look-back descriptors (EMIT) are per chunk; the long-cluster list holds at most one record per
+// per-chunk cluster counts / record offsets (EMIT) are per chunk; the long-cluster list holds at most one record per
 // 33 positions plus one open tail per chunk
 uint64_t k12_num_tiles(uint64_t n_own) { return k12s_num_chunks(n_own); }
 uint64_t k12_long_cap(uint64_t n_total) { return n_total / (k12s::MAXFAST + 1) + k12_num_tiles(n_total) + 16; }
