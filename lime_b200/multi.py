@@ -349,6 +349,26 @@ class PeerJob:
         self.be.peer_close()
 
 
+def run_sharded(dist, torch, backend, rank, world, n_reads, n_refs, shards, alpha, beta, ebwt_mode, read_len,
+                v, m=None, tax_rank=1, higher=False, gather=True, peer_job=None):
+    """One classification job over `world` ranks: through `peer_job` (a PeerJob, reused between calls)
+    when given, and again through the exchange route when that one reports a cell above 255 -- every rank
+    sees the same all-gathered sums, so all ranks take the same branch.  shards: this rank's shard of
+    every strand (dicts as for run_strand).  Returns (assignments, per-strand stats, route)."""
+    if peer_job is not None:
+        try:
+            peer_job.begin()
+            for s, sh in enumerate(shards):
+                peer_job.run_strand(s, sh, alpha, beta, ebwt_mode, read_len)
+            return peer_job.finish(v, m, tax_rank, higher, gather=gather), list(peer_job.stats), "peer"
+        except CarryDetected:
+            pass
+    job = ShardedJob(dist, torch, backend, rank, world, n_reads, n_refs)
+    for s, sh in enumerate(shards):
+        job.run_strand(s, sh, alpha, beta, ebwt_mode, read_len)
+    return job.finish(v, m, tax_rank, higher, gather=gather), list(job.stats), "exchange"
+
+
 class _NoTimer:
     def __enter__(self):
         return self

@@ -190,3 +190,57 @@ def test_sharded_job_equals_single_process(oracle, world, peer, tmp_path):
             assert (stats[s]["n_clusters"], stats[s]["max_len"]) == scal[s]
         assert peer or stats[0]["triples_sent"] > 0
     assert set(chr(t) for t in exp[0]) >= {"C", "U"}
+
+
+def _worker_fallback(rank, world, port, case, alpha, beta, halo, v, q, peer_dir):
+    import torch
+    import torch.distributed as dist
+    from oracle.oracle import Oracle
+    from lime_b200 import multi
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    be = OracleBackend(Oracle(), torch)
+    be.shm_dir = peer_dir
+    n = case["lcp"].shape[0]
+    a, b = multi.shard_ranges(n, world)[rank]
+    t = [torch.zeros(b - a + halo, dtype=torch.int32) for _ in range(2)] + [torch.zeros(b - a + halo, dtype=torch.uint8)]
+    t[0][:b - a] = torch.from_numpy(case["lcp"][a:b].view(np.int32))
+    t[1][:b - a] = torch.from_numpy(case["da"][a:b].view(np.int32))
+    t[2][:b - a] = torch.from_numpy(case["ebwt"][a:b])
+    h = multi.exchange_halo(dist, rank, world, t, b - a, halo)
+    shard = dict(lcp=t[0], da=t[1], ebwt=t[2], n_own=b - a, n_halo=h, pos_base=a, is_last=rank == world - 1)
+    pj = multi.PeerJob(dist, torch, be, rank, world, case["n_reads"], case["n_refs"], 2)
+    out, stats, route = multi.run_sharded(dist, torch, be, rank, world, case["n_reads"], case["n_refs"], [shard, shard],
+                                          alpha, beta, 1, case["read_len"], v, peer_job=pj)
+    pj.close()
+    q.put((rank, out, stats, route))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_peer_job_falls_back_when_a_cell_exceeds_255(oracle, tmp_path):
+    """Cell sums above 255 (the uint8 wrap of SimArray_): the byte-sum proof of the peer-memory job fails on
+    every rank and run_sharded redoes the job through the exchange route, whose result wraps like the reference."""
+    import torch.multiprocessing as mp
+    case = C.wrap_case(n=30000)
+    alpha, beta, world = 16, 0.0, 2
+    v = np.arange(case["n_refs"], dtype=np.uint32) + 7
+    cl, mx = oracle.cluster_detect(case["lcp"], case["da"], case["n_reads"], alpha)
+    sim = oracle.similarity(cl, case["da"], case["ebwt"], case["n_reads"], case["n_refs"])
+    b, p = oracle.choose(sim, case["read_len"] + 1 - alpha, np.float32(beta))
+    exp = oracle.classify([b, b], [p, p], case["n_refs"], v, None, 1, False)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_fallback, args=(r, world, port, case, alpha, beta, int(mx) + 8, v, q, str(tmp_path)))
+             for r in range(world)]
+    for pr in procs:
+        pr.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for pr in procs:
+        pr.join(timeout=60)
+        assert pr.exitcode == 0
+    for rank, out, stats, route in res:
+        assert route == "exchange"
+        assert all(np.asarray(g).tobytes() == e.tobytes() for g, e in zip(out, exp))
+        assert (stats[0]["n_clusters"], stats[0]["max_len"]) == (cl.shape[0], mx)
