@@ -285,7 +285,7 @@ class PeerJob:
         self.stats, self._local, self._pending = [], [], []
         self._inner = ShardedJob(dist, torch, backend, rank, world, n_reads, n_refs)   # finish() = classify + gather
         backend.peer_setup(dist, world, rank, self.per, n_refs, n_strands)
-        self._dirty = False
+        self._dirty, self.closed = False, False
         self._bs = torch.zeros(n_strands, dtype=torch.int64)
         if getattr(backend, "device", None) is not None:
             self._bs = self._bs.to(backend.device)
@@ -302,6 +302,8 @@ class PeerJob:
         """Nobody may add before every rank's slabs are zero: true after the constructor (fresh slabs,
         then the handle all-gather) and after every finish() (slabs cleared before its last all-gather);
         an abandoned job needs the explicit zero + barrier."""
+        if self.closed:
+            raise RuntimeError("PeerJob is closed")
         if self._dirty:
             with self.timer("zero"):
                 self.be.peer_zero()
@@ -345,6 +347,10 @@ class PeerJob:
         return out
 
     def close(self):
+        """Collective: unmaps and frees the slabs; the backend then allocates whole matrices again."""
+        if self.closed:
+            return
+        self.closed = True
         self.dist.barrier()
         self.be.peer_close()
 
@@ -353,16 +359,17 @@ def run_sharded(dist, torch, backend, rank, world, n_reads, n_refs, shards, alph
                 v, m=None, tax_rank=1, higher=False, gather=True, peer_job=None):
     """One classification job over `world` ranks: through `peer_job` (a PeerJob, reused between calls)
     when given, and again through the exchange route when that one reports a cell above 255 -- every rank
-    sees the same all-gathered sums, so all ranks take the same branch.  shards: this rank's shard of
-    every strand (dicts as for run_strand).  Returns (assignments, per-strand stats, route)."""
-    if peer_job is not None:
+    sees the same all-gathered sums, so all ranks take the same branch; the peer job is closed then (its
+    slabs are released so that the backend allocates whole matrices again).  shards: this rank's shard
+    of every strand (dicts as for run_strand).  Returns (assignments, per-strand stats, route)."""
+    if peer_job is not None and not peer_job.closed:
         try:
             peer_job.begin()
             for s, sh in enumerate(shards):
                 peer_job.run_strand(s, sh, alpha, beta, ebwt_mode, read_len)
             return peer_job.finish(v, m, tax_rank, higher, gather=gather), list(peer_job.stats), "peer"
         except CarryDetected:
-            pass
+            peer_job.close()
     job = ShardedJob(dist, torch, backend, rank, world, n_reads, n_refs)
     for s, sh in enumerate(shards):
         job.run_strand(s, sh, alpha, beta, ebwt_mode, read_len)
