@@ -334,3 +334,37 @@ def test_full_paired_pipeline_exact(ctx, oracle, tmp_path):
         for g, e in zip(got, exp):
             assert g.tobytes() == e.tobytes()
     assert set(chr(t) for t in exp[0]) >= {"C"}
+
+
+def _expected_job(oracle, cases, n_reads, n_refs, read_len, alpha, beta, ebwt_mode, v, m, tax_rank, higher):
+    bins, poss, scal = [], [], []
+    for c in cases:
+        cl, mx = oracle.cluster_detect(c["lcp"], c["da"], n_reads, alpha)
+        sim = oracle.similarity(cl, c["da"], c["ebwt"] if ebwt_mode else None, n_reads, n_refs)
+        b, p = oracle.choose(sim, (read_len + 1 - alpha) & 0xFFFFFFFF, np.float32(beta))
+        bins.append(b); poss.append(p); scal.append((cl.shape[0], mx, b.shape[0]))
+    return oracle.classify(bins, poss, n_refs, v, m, tax_rank, higher), scal
+
+
+@pytest.mark.parametrize("shape", ["cfg3_ebwt0_4strands", "cfg4_higher_len150_trlcp32", "cfg5_alpha12", "cfg5_alpha20", "cfg5_alpha24"])
+def test_baseline_config_shapes(ctx, oracle, shape):
+    """Reduced-size versions of BASELINE.json configs 3-5 (config 2 is the bench workload, config 1 the exact
+    paired-end test above): whole jobs through the fused path, assignments and per-strand scalars bit-exact."""
+    from lime_b200.pipeline import run_job, synthetic_lineage
+    if shape == "cfg3_ebwt0_4strands":
+        n, n_reads, n_refs, read_len, alpha, ebwt_mode, higher, n_str, kw = 600_000, 20_000, 93, 100, 16, 0, False, 4, {}
+    elif shape == "cfg4_higher_len150_trlcp32":
+        n, n_reads, n_refs, read_len, alpha, ebwt_mode, higher, n_str, kw = 700_000, 12_000, 100, 150, 16, 1, True, 4, {"trlcp": 32}
+    else:
+        n, n_reads, n_refs, read_len, alpha, ebwt_mode, higher, n_str, kw = 500_000, 15_000, 50, 100, int(shape[10:]), 1, False, 2, {}
+    rows, v, m = synthetic_lineage(n_refs)
+    cases = [C.synth_case(f"{shape}_{s}", n + 13 * s, n_reads, n_refs, read_len=read_len, seed=700 + s, p_long=2e-5, max_seg=20000, **kw)
+             for s in range(n_str)]
+    exp, scal = _expected_job(oracle, cases, n_reads, n_refs, read_len, alpha, 0.25, ebwt_mode, v, m if higher else None, 1, higher)
+    strands = [{"ebwt": c["ebwt"], "lcp": c["lcp"], "da": c["da"], "n": c["lcp"].shape[0]} for c in cases]
+    got, stats = run_job(ctx, strands, n_reads, n_refs, read_len, alpha, 0.25, ebwt_mode, v, m if higher else None, 1, higher)
+    assert [tuple(int(x) for x in st) for st in stats] == [tuple(int(x) for x in sc) for sc in scal]
+    for g, e in zip(got, exp):
+        assert np.asarray(g).tobytes() == e.tobytes()
+    if alpha <= 16:
+        assert int((exp[0] == ord("C")).sum()) > 0
