@@ -244,3 +244,27 @@ def test_peer_job_falls_back_when_a_cell_exceeds_255(oracle, tmp_path):
         assert route == "exchange"
         assert all(np.asarray(g).tobytes() == e.tobytes() for g, e in zip(out, exp))
         assert (stats[0]["n_clusters"], stats[0]["max_len"]) == (cl.shape[0], mx)
+
+
+def test_owner_division_by_multiply_high():
+    """peer_row() of csrc/common.cuh finds a read's owner with q = umulhi(r, magic), magic =
+    min(floor(2^32 / per), 2^32 - 1), and one correction step; restated here and checked against
+    integer division over the whole 32-bit range of read ids for awkward divisors."""
+    rng = np.random.default_rng(11)
+    pers = [1, 2, 3, 5, 7, 255, 256, 257, 65535, 65536, 65537, 1_000_003, 2_000_000, 2 ** 31 - 1, 2 ** 31, 2 ** 32 - 1]
+    pers += [int(x) for x in rng.integers(1, 2 ** 32, size=40)]
+    for per in pers:
+        magic = min((1 << 32) // per, (1 << 32) - 1)
+        r = np.concatenate([rng.integers(0, 1 << 32, size=20000, dtype=np.uint64),
+                            np.arange(0, min(4 * per, 1 << 32), max(per // 3, 1), dtype=np.uint64)[:20000],
+                            np.array([0, per - 1, per, per + 1 if per + 1 < (1 << 32) else 0, (1 << 32) - 1], dtype=np.uint64)])
+        for edge in (per, 2 * per, 3 * per):
+            if edge < (1 << 32):
+                r = np.concatenate([r, np.array([edge - 1, edge], dtype=np.uint64)])
+        q = (r * np.uint64(magic)) >> np.uint64(32)
+        rem = (r - q * np.uint64(per)) & np.uint64(0xFFFFFFFF)            # 32-bit arithmetic of the kernel
+        fix = rem >= np.uint64(per)
+        q = q + fix.astype(np.uint64)
+        rem = np.where(fix, rem - np.uint64(per), rem)
+        assert np.array_equal(q, r // np.uint64(per)), per
+        assert np.array_equal(rem, r % np.uint64(per)), per
