@@ -29,6 +29,12 @@
 #include "score.cuh"
 #include <algorithm>
 
+// compile-time experiment switches for the next round of tuning (bit 0: row address per read leader,
+// bit 1: arithmetic A/C/G/T classes); 0 in every shipped build -- the default code is unchanged
+#ifndef LIME_K12_EXP
+#define LIME_K12_EXP 0
+#endif
+
 namespace lime {
 namespace k12s {
 
@@ -463,7 +469,18 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
                     if ((inf.x >> lane) & 1u) {
                         const uint32_t o = inf.z + __popc(inf.x & lt_mask);
                         ws.cid[o] = ws.da[32 * k + lane];
+#if LIME_K12_EXP & 2
+                        // experiment (not built by default): A,C,G,T mapped arithmetically, the table only for the rest
+                        uint32_t cl0 = 0u;
+                        if (EBWT) {
+                            const uint32_t sy = ws.eb[32 * k + lane], d = sy - 0x41u;
+                            const uint32_t x = (sy >> 1) & 3u;
+                            cl0 = (d < 20u && ((0x80045u >> d) & 1u)) ? (x ^ (x >> 1)) : (uint32_t)sm.cls[sy];
+                        }
+                        ws.cmeta[o] = (uint16_t)(cl0 | (((inf.y >> lane) & 1u) << 8));
+#else
                         ws.cmeta[o] = (uint16_t)((EBWT ? (uint32_t)sm.cls[ws.eb[32 * k + lane]] : 0u) | (((inf.y >> lane) & 1u) << 8));
+#endif
                     }
                 }
             }
@@ -534,6 +551,10 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
             // every read leader against every genome leader of its cluster
             unsigned gl = __ballot_sync(FULL, leader && !is_read) & cm;
             if (!(leader && is_read)) gl = 0;
+#if LIME_K12_EXP & 1
+            // experiment (not built by default): the row address once per read leader instead of once per pair
+            unsigned *row_w = reinterpret_cast<unsigned *>(acc.sim8 + (size_t)(gl ? id : 0u) * acc.pitch8);
+#endif
             while (__any_sync(FULL, gl != 0)) {
                 const int src = gl ? 31 - __clz(gl) : 0;
                 const uint32_t Gx = __shfl_sync(FULL, vec.x, src);
@@ -550,7 +571,18 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
                 }
                 if (gl == 0) t = 0;
                 else gl ^= 1u << src;
+#if LIME_K12_EXP & 1
+                if (t) {
+                    if (!PEER && !EXACT32 && red_mode && !(P.dbg & 0x802u)) {
+                        const uint32_t g = gid - P.n_reads;
+                        updates++;
+                        red_add_hint(row_w + (g >> 2), t << ((g & 3u) * 8u), pol_mat);
+                        t_total += t;
+                    } else add_update(id, gid - P.n_reads, t);
+                }
+#else
                 if (t) add_update(id, gid - P.n_reads, t);
+#endif
             }
         }
         max_len = max(max_len, (unsigned long long)longest);
