@@ -80,6 +80,25 @@ int  lime_load(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uin
                uint64_t n_own, uint64_t n_halo, uint64_t pos_base, int is_last,
                uint32_t n_reads, uint32_t n_refs, int mem);
 
+/*
+ * Narrowed lcp transfer.  Every step reads lcp only through `lcp[i] < alpha` (ClusterLCP.cpp:150-202,
+ * :246-264), so for alpha <= 255 the byte min(lcp, 255) decides every test as the 32-bit value does.
+ * lime_set_alpha_limit declares the largest alpha the caller will use on the strands it loads from now
+ * on (the drop-in executables know it from their command line before they read a file); 0 = no promise
+ * (default).  With 1 <= max_alpha <= 255, lime_load(LIME_MEM_HOST) narrows lcp on host threads, chunk by
+ * chunk into page-locked stage buffers while the previous chunks are on the bus, sends 1 + 4 (+1) instead
+ * of 4 + 4 (+1) bytes per position over PCIe and widens on the device; results are identical.  A step
+ * called with alpha > 255 on a strand loaded that way fails with LIME_ERR_STATE.
+ */
+int  lime_set_alpha_limit(lime_ctx *ctx, uint32_t max_alpha);
+/* The host half on its own (no CUDA): out[i] = min(lcp[i], 255) with `threads` host threads (<= 0:
+ * lime_host_threads()), and the same through the chunk ring lime_load uses (slots stage buffers of
+ * `chunk` positions).  Exposed for the CPU tests and for callers that narrow while they read a file. */
+int  lime_host_threads(void);     /* LIME_HOST_THREADS or min(hardware threads, 16) */
+int  lime_host_narrow_lcp(const uint32_t *lcp, uint8_t *out, uint64_t n, int threads);
+int  lime_host_narrow_lcp_pipelined(const uint32_t *lcp, uint8_t *out, uint64_t n, uint64_t chunk,
+                                    int threads, int slots);
+
 /* ---- step 1 : ClusterLCP.cpp:139-283 ------------------------------------------------------ */
 
 /* Detect the alpha-clusters owned by this shard.  n_clusters / max_len are the shard's values of

@@ -96,6 +96,11 @@ class LimeContext:
         return out
 
     # ---- inputs -------------------------------------------------------------------------
+    def set_alpha_limit(self, max_alpha):
+        """lime_set_alpha_limit: promise alpha <= max_alpha for the strands loaded from now on; with
+        1..255 host-mode loads ship lcp as min(lcp, 255) bytes (identical results).  0 = no promise."""
+        self._ck(self.lib.lime_set_alpha_limit(self.h, int(max_alpha)))
+
     def load(self, lcp, da, ebwt, n_reads, n_refs, n_own=None, n_halo=0, pos_base=0, is_last=True,
              mem=MEM_HOST, n_total=None):
         """lime_load.  Host mode takes numpy arrays; device mode takes pointers + n_total."""

@@ -7,7 +7,7 @@ using namespace lime;
 
 
 static const char *const kKernelNames[KID_COUNT] = {
-    "k12_fused", "k12_check", "k1_detect", "k2_warp", "k2_block", "k2_narrow", "k3_choose", "k3_export", "k3_import", "k3_count", "k3_emit", "k3_classify"};
+    "k12_fused", "k12_check", "k1_detect", "k2_warp", "k2_block", "k2_narrow", "k3_choose", "k3_export", "k3_import", "k3_count", "k3_emit", "k3_classify", "load_widen"};
 
 // device scalar block layout (u64 slots)
 enum {
@@ -42,6 +42,9 @@ int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, bool exact
                  unsigned long long sc[SC_COUNT], int peer_slab);
 lime::PeerTable peer_table(const lime_ctx *ctx, int slab);
 void peer_release(lime_ctx *ctx);
+// lime_abi_load.cu
+int load_host_narrow(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint8_t *ebwt, uint64_t n);
+void load_release(lime_ctx *ctx);
 
 // bracket one kernel launch with events when profiling
 struct LaunchScope {

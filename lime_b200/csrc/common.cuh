@@ -100,6 +100,9 @@ __device__ __forceinline__ uint8_t *peer_row(const PeerTable &T, uint64_t pitch,
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
+constexpr int LIME_STAGE_SLOTS = 3;
+constexpr uint64_t LIME_STAGE_CHUNK = 8ull << 20;   // positions per chunk of the narrowed lcp transfer
+
 struct DevBuf {
     void *p = nullptr;
     size_t cap = 0;
@@ -129,6 +132,7 @@ enum KernelId {
     KID_K3_COUNT,
     KID_K3_EMIT,
     KID_K3_CLASSIFY,
+    KID_LOAD_WIDEN,
     KID_COUNT
 };
 
@@ -167,6 +171,14 @@ struct lime_ctx {
     int is_last = 1;
     uint32_t n_reads = 0, n_refs = 0;
     bool loaded = false;
+    // narrowed lcp transfer (lime_abi_load.cu): alpha_limit is the caller's promise (lime_set_alpha_limit),
+    // lcp_clamped says the resident lcp holds min(lcp, 255)
+    uint32_t alpha_limit = 0;
+    bool lcp_clamped = false;
+    lime::DevBuf in_lcp8;
+    uint8_t *stage[lime::LIME_STAGE_SLOTS] = {nullptr};
+    cudaEvent_t stage_ev[lime::LIME_STAGE_SLOTS] = {nullptr};
+    bool stage_busy = false;
 
     // clusters
     lime::DevBuf clusters;          // lime_cluster[cl_cap]
@@ -267,6 +279,8 @@ struct K12Args {
     PeerTable peer;
     const PeerTable *peer_dev = nullptr;
 };
+// lime_abi_load.cu: out[i] = in[i] for a chunk of the narrowed lcp (both 16-byte aligned)
+cudaError_t launch_widen(const uint8_t *in, uint32_t *out, uint64_t n, cudaStream_t s);
 cudaError_t launch_bytesum(const uint8_t *p, uint64_t bytes, unsigned long long *out, cudaStream_t s);
 cudaError_t launch_k12(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s);
 uint64_t k12_num_tiles(uint64_t n_own);

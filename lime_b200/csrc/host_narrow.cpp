@@ -1,0 +1,133 @@
+// host_narrow.cpp -- host half of the narrowed lcp transfer of lime_load(LIME_MEM_HOST).
+//
+// Every step of the path reads lcp only through `lcp[i] < alpha` (ClusterLCP.cpp:150-202, :246-264),
+// so for alpha <= 255 the byte min(lcp, 255) decides every test exactly as the 32-bit value does.
+// Shipping that byte takes 1 instead of 4 of the 9 bytes per position over PCIe.  No CUDA in here:
+// plain C++ (g++, AVX2 clone picked at load time), tested on the CPU (tests/test_narrow_lcp.py).
+#include <algorithm>
+#include <atomic>
+#include <cstdint>
+#include <cstdlib>
+#include <thread>
+#include <sched.h>
+#include <vector>
+#include "../../include/lime_cuda.h"
+
+namespace {
+
+__attribute__((target_clones("avx2", "default")))
+void narrow_range(const uint32_t *__restrict__ src, uint8_t *__restrict__ dst, uint64_t n)
+{
+    for (uint64_t i = 0; i < n; i++) {
+        const uint32_t v = src[i];
+        dst[i] = (uint8_t)(v < 255u ? v : 255u);
+    }
+}
+
+} // namespace
+
+extern "C" int lime_host_threads(void)
+{
+    if (const char *e = getenv("LIME_HOST_THREADS")) {
+        const int t = atoi(e);
+        if (t >= 1) return std::min(t, 256);
+    }
+    // the cores this process may run on (a container's cpuset), not the machine's
+    unsigned hc = std::thread::hardware_concurrency();
+    cpu_set_t set;
+    if (sched_getaffinity(0, sizeof(set), &set) == 0 && CPU_COUNT(&set) > 0) hc = (unsigned)CPU_COUNT(&set);
+    return (int)std::max(1u, std::min(hc ? hc : 1u, 16u));
+}
+
+extern "C" int lime_host_narrow_lcp(const uint32_t *lcp, uint8_t *out, uint64_t n, int threads)
+{
+    if ((!lcp || !out) && n) return LIME_ERR_ARG;
+    if (threads <= 0) threads = lime_host_threads();
+    // below a few MB one thread is faster than starting the others
+    const uint64_t per = std::max<uint64_t>((n + threads - 1) / threads, 1u << 20);
+    std::vector<std::thread> pool;
+    for (uint64_t a = per; a < n; a += per)
+        pool.emplace_back(narrow_range, lcp + a, out + a, std::min(per, n - a));
+    narrow_range(lcp, out, std::min(per, n));
+    for (auto &t : pool) t.join();
+    return LIME_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// The chunk pipeline of lime_load: `threads` workers narrow chunk after chunk into a ring of
+// `slots` page-locked stage buffers; the calling thread (lime_abi_load.cu) takes each finished chunk,
+// queues its copy and gives the slot back once the copy's event has completed.  Workers only touch
+// host memory; all CUDA calls stay on the calling thread.
+// ---------------------------------------------------------------------------------------------
+namespace lime {
+
+struct NarrowPipe {
+    const uint32_t *src = nullptr;
+    uint64_t n = 0, chunk = 0, n_chunks = 0;
+    int threads = 0, slots = 0;
+    uint8_t *const *stage = nullptr;                 // [slots] buffers of `chunk` bytes
+    std::vector<std::atomic<int>> done;              // per chunk: workers that finished their slice
+    std::atomic<uint64_t> free_upto{0};              // chunks < free_upto own a free slot
+    std::vector<std::thread> pool;
+
+    NarrowPipe(const uint32_t *src_, uint64_t n_, uint64_t chunk_, int threads_, int slots_, uint8_t *const *stage_)
+        : src(src_), n(n_), chunk(chunk_), n_chunks((n_ + chunk_ - 1) / chunk_), threads(threads_), slots(slots_),
+          stage(stage_), done((n_ + chunk_ - 1) / chunk_)
+    {
+        for (auto &d : done) d.store(0, std::memory_order_relaxed);
+        free_upto.store((uint64_t)slots, std::memory_order_release);
+        for (int t = 0; t < threads; t++) pool.emplace_back([this, t] { work(t); });
+    }
+    ~NarrowPipe()
+    {
+        free_upto.store(~0ull, std::memory_order_release);      // an aborted load must not strand the workers
+        for (auto &t : pool) t.join();
+    }
+    void work(int t)
+    {
+        for (uint64_t c = 0; c < n_chunks; c++) {
+            while (c >= free_upto.load(std::memory_order_acquire)) std::this_thread::yield();
+            const uint64_t base = c * chunk, len = std::min(chunk, n - base);
+            // slices on 64-byte boundaries of the output
+            const uint64_t per = ((len + threads - 1) / threads + 63) / 64 * 64;
+            const uint64_t a = std::min(len, per * (uint64_t)t), b = std::min(len, a + per);
+            if (b > a) narrow_range(src + base + a, stage[c % slots] + a, b - a);
+            done[c].fetch_add(1, std::memory_order_release);
+        }
+    }
+    bool ready(uint64_t c) const { return done[c].load(std::memory_order_acquire) == threads; }
+    // the copies of chunks < k have completed: chunks < k + slots may be narrowed
+    void released(uint64_t k) { free_upto.store(k + (uint64_t)slots, std::memory_order_release); }
+};
+
+NarrowPipe *narrow_pipe_open(const uint32_t *src, uint64_t n, uint64_t chunk, int threads, int slots, uint8_t *const *stage)
+{
+    return new NarrowPipe(src, n, chunk, threads, slots, stage);
+}
+bool narrow_pipe_ready(const NarrowPipe *p, uint64_t c) { return p->ready(c); }
+void narrow_pipe_released(NarrowPipe *p, uint64_t k) { p->released(k); }
+void narrow_pipe_close(NarrowPipe *p) { delete p; }
+
+} // namespace lime
+
+// CPU test hook of the pipeline: the same ring, with memcpy standing in for the asynchronous copy
+// (a slot is handed back right after its chunk was taken).
+extern "C" int lime_host_narrow_lcp_pipelined(const uint32_t *lcp, uint8_t *out, uint64_t n, uint64_t chunk,
+                                              int threads, int slots)
+{
+    if ((!lcp || !out) && n) return LIME_ERR_ARG;
+    if (chunk == 0 || slots < 1 || slots > 8) return LIME_ERR_ARG;
+    if (threads <= 0) threads = lime_host_threads();
+    if (n == 0) return LIME_OK;
+    std::vector<std::vector<uint8_t>> bufs(slots, std::vector<uint8_t>(chunk));
+    std::vector<uint8_t *> stage;
+    for (auto &b : bufs) stage.push_back(b.data());
+    lime::NarrowPipe pipe(lcp, n, chunk, threads, slots, stage.data());
+    for (uint64_t c = 0; c < pipe.n_chunks; c++) {
+        while (!pipe.ready(c)) std::this_thread::yield();
+        const uint64_t base = c * chunk, len = std::min(chunk, n - base);
+        std::copy(stage[c % slots], stage[c % slots] + len, out + base);
+        pipe.released(c + 1);
+    }
+    return LIME_OK;
+}

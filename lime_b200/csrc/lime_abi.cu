@@ -43,6 +43,7 @@ void lime_destroy(lime_ctx *ctx)
     cudaStreamSynchronize(ctx->stream);
     for (auto &p : ctx->prof_events) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     peer_release(ctx);
+    load_release(ctx);
     DevBuf *bufs[] = {&ctx->in_lcp, &ctx->in_da, &ctx->in_ebwt, &ctx->clusters, &ctx->tile_state,
                       &ctx->scalars, &ctx->sim_own, &ctx->sim32, &ctx->large_list, &ctx->long_recs, &ctx->k2_scratch,
                       &ctx->row_counts, &ctx->cls_out, &ctx->tax_tables};
@@ -98,20 +99,24 @@ int lime_load(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint
             (reinterpret_cast<uintptr_t>(ebwt) & 3))
             return fail(ctx, LIME_ERR_ARG, "lime_load: device lcp/da must be 16-byte aligned, ebwt 4-byte aligned");
         ctx->d_lcp = lcp; ctx->d_da = da; ctx->d_ebwt = ebwt;
+        ctx->lcp_clamped = false;
     } else {
+        // narrowed lcp transfer (lime_abi_load.cu) when the caller has promised alpha <= 255
+        const bool narrow = lcp && ctx->alpha_limit >= 1 && ctx->alpha_limit <= 255 && n >= (1ull << 16);
         if (lcp || n == 0) CK(ctx->in_lcp.reserve(std::max<uint64_t>(n, 4) * 4), "cudaMalloc lcp");
         CK(ctx->in_da.reserve(std::max<uint64_t>(n, 4) * 4), "cudaMalloc da");
-        if (n) {
+        if (ebwt) CK(ctx->in_ebwt.reserve(std::max<uint64_t>(n, 16)), "cudaMalloc ebwt");
+        if (narrow) {
+            const int rc = load_host_narrow(ctx, lcp, da, ebwt, n);
+            if (rc != LIME_OK) return rc;
+        } else if (n) {
             if (lcp) CK(cudaMemcpyAsync(ctx->in_lcp.p, lcp, n * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D lcp");
             CK(cudaMemcpyAsync(ctx->in_da.p, da, n * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D da");
+            if (ebwt) CK(cudaMemcpyAsync(ctx->in_ebwt.p, ebwt, n, cudaMemcpyHostToDevice, ctx->stream), "H2D ebwt");
         }
+        ctx->lcp_clamped = narrow;
         ctx->d_lcp = (lcp || n == 0) ? ctx->in_lcp.as<uint32_t>() : nullptr; ctx->d_da = ctx->in_da.as<uint32_t>();
-        ctx->d_ebwt = nullptr;
-        if (ebwt) {
-            CK(ctx->in_ebwt.reserve(std::max<uint64_t>(n, 16)), "cudaMalloc ebwt");
-            if (n) CK(cudaMemcpyAsync(ctx->in_ebwt.p, ebwt, n, cudaMemcpyHostToDevice, ctx->stream), "H2D ebwt");
-            ctx->d_ebwt = ctx->in_ebwt.as<uint8_t>();
-        }
+        ctx->d_ebwt = ebwt ? ctx->in_ebwt.as<uint8_t>() : nullptr;
     }
     ctx->n_own = n_own; ctx->n_halo = n_halo; ctx->pos_base = pos_base; ctx->is_last = is_last;
     ctx->n_reads = n_reads; ctx->n_refs = n_refs;
@@ -140,6 +145,8 @@ int lime_cluster_detect(lime_ctx *ctx, uint32_t alpha, uint64_t *n_clusters, uin
     if (!ctx) return LIME_ERR_ARG;
     if (!ctx->loaded) return fail(ctx, LIME_ERR_STATE, "lime_cluster_detect: nothing loaded");
     if (!ctx->d_lcp && ctx->n_own) return fail(ctx, LIME_ERR_STATE, "lime_cluster_detect: loaded without lcp");
+    if (ctx->lcp_clamped && alpha > 255)
+        return fail(ctx, LIME_ERR_STATE, "lime_cluster_detect: lcp was loaded narrowed (lime_set_alpha_limit <= 255), alpha > 255 needs a reload");
     CK(cudaSetDevice(ctx->device), "cudaSetDevice");
     const uint64_t n_total = ctx->n_own + ctx->n_halo;
     const uint64_t tiles = k12_num_tiles(ctx->n_own);

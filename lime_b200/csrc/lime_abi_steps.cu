@@ -37,6 +37,8 @@ static int run_k2_pass(lime_ctx *ctx, bool ebwt, bool exact32, uint32_t lo, uint
 int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, bool exact32, uint32_t lo, uint32_t hi,
                  unsigned long long sc[SC_COUNT], int peer_slab)
 {
+    if (ctx->lcp_clamped && alpha > 255)
+        return fail(ctx, LIME_ERR_STATE, "lcp was loaded narrowed (lime_set_alpha_limit <= 255), alpha > 255 needs a reload");
     const uint64_t n_total = ctx->n_own + ctx->n_halo;
     K12Args a;
     a.lcp = ctx->d_lcp; a.da = ctx->d_da; a.ebwt = ebwt ? ctx->d_ebwt : nullptr;

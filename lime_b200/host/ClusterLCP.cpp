@@ -40,6 +40,7 @@ int main(int argc, char **argv)
     lime_ctx *ctx = nullptr;
     int rc = lime_init(&ctx, device_from_env());
     if (rc) die_lime(nullptr, "lime_init", rc);
+    alpha_limit_from_env(ctx, alpha);
     rc = lime_load(ctx, lcp, da, nullptr, n, 0, 0, 1, numReads, numGenomes, LIME_MEM_HOST);
     if (rc) die_lime(ctx, "lime_load", rc);
     uint64_t nClusters = 0, maxLen = 0;

@@ -122,6 +122,7 @@ int main(int argc, char **argv)
     lime_ctx *ctx = nullptr;
     int rc = lime_init(&ctx, device_from_env());
     if (rc) die_lime(nullptr, "lime_init", rc);
+    alpha_limit_from_env(ctx, alpha);
     const uint32_t norm = (uint32_t)((int)readLen + 1 - (int)alpha);          // ClusterBWT_DA.cpp:555
 
     // ---- steps 1 + 2 per strand; the next strand's files are read while the GPU works ----------------

@@ -75,4 +75,12 @@ inline int device_from_env()
     return e ? atoi(e) : 0;
 }
 
+// LIME_NARROW_LCP=1: tell the library the alpha of this run, so that lime_load ships lcp as bytes when
+// alpha <= 255 (lime_set_alpha_limit).  Opt-in until the transfer has been measured on the target box.
+inline void alpha_limit_from_env(lime_ctx *ctx, uint32_t alpha)
+{
+    const char *e = getenv("LIME_NARROW_LCP");
+    if (e && atoi(e) > 0) lime_set_alpha_limit(ctx, alpha);
+}
+
 } // namespace limehost

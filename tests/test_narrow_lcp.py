@@ -1,0 +1,68 @@
+"""CPU tests of the host half of the narrowed lcp transfer (lime_b200/csrc/host_narrow.cpp):
+out[i] = min(lcp[i], 255), plain and through the chunk ring lime_load(LIME_MEM_HOST) uses, and the
+claim it rests on: for alpha <= 255, `min(lcp, 255) < alpha` is `lcp < alpha` (ClusterLCP.cpp:150-202
+only ever compares lcp with alpha)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from lime_b200 import _lib
+
+
+def _lcp(n, seed):
+    rng = np.random.default_rng(seed)
+    a = rng.integers(0, 300, n, dtype=np.uint32)
+    if n:
+        k = max(1, n // 16)
+        a[rng.integers(0, n, k)] = rng.integers(0, 2**32, k, dtype=np.uint64).astype(np.uint32)
+        a[rng.integers(0, n, 4)] = np.array([0, 254, 255, 256], dtype=np.uint32)[: min(4, n)] if n >= 4 else a[:1]
+        a[-1] = 0xFFFFFFFF
+    return a
+
+
+def _ptr(a):
+    return C.c_void_p(a.ctypes.data)
+
+
+@pytest.mark.parametrize("n", [0, 1, 15, 16, 17, 63, 64, 65, 4097, (1 << 20) + 3, 3 * (1 << 20) + 77])
+@pytest.mark.parametrize("threads", [1, 3, 8])
+def test_narrow_plain(n, threads):
+    lib = _lib.load()
+    lcp = _lcp(n, 7 + n)
+    out = np.full(n + 8, 0xAB, dtype=np.uint8)
+    assert lib.lime_host_narrow_lcp(_ptr(lcp), _ptr(out), n, threads) == 0
+    assert np.array_equal(out[:n], np.minimum(lcp, 255).astype(np.uint8))
+    assert (out[n:] == 0xAB).all()           # nothing written past the end
+
+
+@pytest.mark.parametrize("n,chunk,threads,slots", [
+    (1, 64, 2, 1), (64, 64, 3, 2), (65, 64, 3, 3), (1000, 64, 5, 3), (100003, 4096, 7, 3),
+    (100003, 4096, 1, 1), (1 << 20, 1 << 16, 4, 2), ((1 << 21) + 11, 100000, 15, 3), (5, 1 << 20, 16, 3)])
+def test_narrow_pipelined(n, chunk, threads, slots):
+    lib = _lib.load()
+    lcp = _lcp(n, 11 + n)
+    out = np.full(n + 8, 0xCD, dtype=np.uint8)
+    assert lib.lime_host_narrow_lcp_pipelined(_ptr(lcp), _ptr(out), n, chunk, threads, slots) == 0
+    assert np.array_equal(out[:n], np.minimum(lcp, 255).astype(np.uint8))
+    assert (out[n:] == 0xCD).all()
+
+
+def test_narrow_pipelined_rejects_bad_arguments():
+    lib = _lib.load()
+    lcp = _lcp(10, 1)
+    out = np.zeros(10, dtype=np.uint8)
+    assert lib.lime_host_narrow_lcp_pipelined(_ptr(lcp), _ptr(out), 10, 0, 1, 1) != 0
+    assert lib.lime_host_narrow_lcp_pipelined(_ptr(lcp), _ptr(out), 10, 4, 1, 0) != 0
+    assert lib.lime_host_narrow_lcp(None, _ptr(out), 10, 1) != 0
+    assert lib.lime_host_threads() >= 1
+
+
+def test_clamped_lcp_decides_every_head_test_for_alpha_up_to_255():
+    lcp = _lcp(1 << 16, 3)
+    lcp[:600] = np.arange(600, dtype=np.uint32)          # every value around the clamp
+    nar = np.minimum(lcp, 255).astype(np.uint8)
+    for alpha in (1, 2, 12, 16, 24, 32, 254, 255):
+        assert np.array_equal(lcp < alpha, nar < alpha)
+    # and the limit is tight: alpha = 256 is not decided by the byte
+    assert not np.array_equal(lcp < 256, nar.astype(np.uint32) < 256)
