@@ -577,11 +577,11 @@ def run_ours_multi(args, w, world, rank, local):
     else:
         job = multi.ShardedJob(dist, torch, be, rank, world, n_reads, w["n_refs"])
 
-    def step(gather=True):
+    def step(gather=True, src=None):
         job.stats = []
         if peer:
             job.begin()
-        for s, sh in enumerate(shards):
+        for s, sh in enumerate(src or shards):
             job.run_strand(s, sh, w["alpha"], w["beta"], w["ebwt"], w["read_len"])
         # every rank fetches the assignments of the reads it owns (9 B per read, as at N = 1)
         return job.finish(v, None, w["tax_rank"], False, gather=False)
@@ -649,6 +649,64 @@ def run_ours_multi(args, w, world, rank, local):
     sent_t = torch.tensor([sent], device=dev, dtype=torch.int64)
     dist.all_reduce(sent_t, op=dist.ReduceOp.MAX)
 
+    # ---- e2e: the same step with every rank's shards in page-locked HOST memory (lime_load(LIME_MEM_HOST) per
+    # strand inside the timed region) and each rank's assignments copied back to its host, max over ranks.
+    # Every rank first proves, without collectives, that it can load its host shards; the leg runs only
+    # if all ranks can (a rank dropping out of a step would leave the others in a collective).
+    e2e = None
+    if not args.no_e2e and os.environ.get("LIME_BENCH_MULTI_E2E", "1") != "0":
+        ok, why, host_shards = 1, "", []
+        try:
+            for sh in shards:
+                hs = dict(sh)
+                for k in ("ebwt", "lcp", "da"):
+                    t = torch.empty(sh[k].shape, dtype=sh[k].dtype, pin_memory=True)
+                    t.copy_(sh[k])
+                    hs[k] = t
+                host_shards.append(hs)
+            torch.cuda.synchronize()
+            for hs in host_shards:
+                be.load(hs["lcp"], hs["da"], hs["ebwt"] if w["ebwt"] else None, hs["n_own"], hs["n_halo"],
+                        hs["pos_base"], hs["is_last"], n_reads, w["n_refs"])
+            torch.cuda.synchronize()
+        except BaseException as ex:                      # noqa: BLE001
+            ok, why = 0, "%s: %s" % (type(ex).__name__, ex)
+        flag = torch.tensor([ok], device=dev, dtype=torch.int64)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 1:
+            out_d = tuple(np.array(x, copy=True) for x in step())
+            out_h = tuple(np.array(x, copy=True) for x in step(src=host_shards))
+            same = torch.tensor([int(all(a.tobytes() == b.tobytes() for a, b in zip(out_d, out_h)))], device=dev,
+                                dtype=torch.int64)
+            dist.all_reduce(same, op=dist.ReduceOp.MIN)
+            e2e_steps = max(1, min(args.steps, 5))
+            dist.barrier(); torch.cuda.synchronize()
+            ev0.record(stream)
+            tw0 = time.perf_counter()
+            for _ in range(e2e_steps):
+                step(src=host_shards)
+            ev1.record(stream)
+            torch.cuda.synchronize()
+            tw1 = time.perf_counter()
+            dist.barrier()
+            e_ms = torch.tensor([max(ev0.elapsed_time(ev1), (tw1 - tw0) * 1e3)], device=dev, dtype=torch.float64)
+            dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
+            e_ms = float(e_ms.item()) / e2e_steps
+            h2d = sum((8 + w["ebwt"]) * (hs["n_own"] + hs["n_halo"]) for hs in host_shards)
+            h2d_t = torch.tensor([h2d], device=dev, dtype=torch.int64)
+            dist.all_reduce(h2d_t)
+            if int(same.item()) == 1:
+                e2e = {"value": S * w["n_strands"] * world / (e_ms * 1e-3), "unit": UNIT,
+                       "h2d_bytes_per_step": int(h2d_t.item()), "d2h_bytes_per_step": 9 * n_reads,
+                       "ms_per_step": e_ms, "steps": e2e_steps, "reads_per_s": n_reads / (e_ms * 1e-3),
+                       "note": "every rank: lime_load(LIME_MEM_HOST) of its shard of each strand from page-locked host "
+                               "arrays + its assignments copied back; max over ranks; results equal to the resident step"}
+            else:
+                e2e = {"error": "host-buffer step disagrees with the resident step"}
+        else:
+            e2e = {"error": "host-shard pre-flight failed on some rank" + (": " + why if why else "")}
+        del host_shards
+
     if rank == 0:
         symbols = S * w["n_strands"] * world
         peaks = {}
@@ -687,7 +745,7 @@ def run_ours_multi(args, w, world, rank, local):
                          "all_to_all_GBps_per_rank": (int(sent_t.item()) / (a2a_ms * 1e-3) / 1e9) if a2a_ms > 0 else None,
                          "remote_updates_per_rank_and_step": (sum(st.get("updates", 0) for st in stats) // world * (world - 1) // world) if peer else None,
                          "nvlink_peak_GBps_per_direction": 900, "note": "phase times from one extra synchronised step"},
-            "cpu_baseline": None, "e2e": None, "gpu_launches": int(launches.item()), "clocks": clk,
+            "cpu_baseline": None, "e2e": e2e, "gpu_launches": int(launches.item()), "clocks": clk,
         }
         print(json.dumps(line), flush=True)
     dist.barrier()

@@ -62,11 +62,19 @@ class CudaBackend:
         self.ctx, self.torch, self.device = ctx, torch, device
 
     def load(self, lcp, da, ebwt, n_own, n_halo, pos_base, is_last, n_reads, n_refs):
-        from ._lib import MEM_DEVICE
+        """CUDA tensors are borrowed (LIME_MEM_DEVICE); CPU tensors (page-locked for full PCIe rate) are
+        copied in by lime_load(LIME_MEM_HOST) -- the end-to-end leg of the bench."""
+        from ._lib import MEM_DEVICE, MEM_HOST
         self._keep = (lcp, da, ebwt)
+        n = n_own + n_halo
+        if lcp.device.type == "cpu":
+            self.ctx.load(lcp[:n].numpy().view(np.uint32), da[:n].numpy().view(np.uint32),
+                          ebwt[:n].numpy() if ebwt is not None else None, n_reads, n_refs,
+                          n_own=n_own, n_halo=n_halo, pos_base=pos_base, is_last=is_last, mem=MEM_HOST)
+            return
         self.ctx.load(lcp.data_ptr(), da.data_ptr(), ebwt.data_ptr() if ebwt is not None else None, n_reads, n_refs,
                       n_own=n_own, n_halo=n_halo, pos_base=pos_base, is_last=is_last, mem=MEM_DEVICE,
-                      n_total=n_own + n_halo)
+                      n_total=n)
 
     def cluster_similarity(self, alpha, ebwt_mode):
         return self.ctx.cluster_similarity(alpha, ebwt_mode, False)
