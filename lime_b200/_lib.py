@@ -41,7 +41,7 @@ SIGNATURES = {
     "lime_set_alpha_limit": (C.c_int, [vp, C.c_uint32]),
     "lime_host_threads": (C.c_int, []),
     "lime_host_narrow_lcp": (C.c_int, [vp, vp, C.c_uint64, C.c_int]),
-    "lime_host_narrow_lcp_pipelined": (C.c_int, [vp, vp, C.c_uint64, C.c_uint64, C.c_int, C.c_int]),
+    "lime_host_narrow_lcp_pipelined": (C.c_int, [vp, vp, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int]),
     "lime_cluster_detect": (C.c_int, [vp, C.c_uint32, u64p, u64p]),
     "lime_clusters_copy": (C.c_int, [vp, vp, C.c_uint64]),
     "lime_clusters_set": (C.c_int, [vp, vp, C.c_uint64, C.c_uint64]),

@@ -8,10 +8,14 @@
 #include <atomic>
 #include <cstdint>
 #include <cstdlib>
+#include <chrono>
+#include <deque>
+#include <mutex>
 #include <thread>
 #include <sched.h>
 #include <vector>
 #include "../../include/lime_cuda.h"
+#include "narrow_loop.h"
 
 namespace {
 
@@ -110,10 +114,68 @@ void narrow_pipe_close(NarrowPipe *p) { delete p; }
 
 } // namespace lime
 
-// CPU test hook of the pipeline: the same ring, with memcpy standing in for the asynchronous copy
-// (a slot is handed back right after its chunk was taken).
+// CPU test hook: narrow_transfer (narrow_loop.h, the loop lime_load runs) over a simulated copy queue -- an
+// in-order worker that performs each queued copy `copy_delay_us` after taking it, so a stage slot that
+// is rewritten before its copy has run shows up as wrong output.
+namespace {
+
+struct SimQueue {
+    struct Job { int slot; uint64_t base, len, seq; };
+    uint8_t *out; uint8_t *const *stage; int delay_us;
+    std::mutex mu; std::deque<Job> jobs; bool stop = false;
+    std::atomic<uint64_t> recorded[8], completed[8];
+    std::thread worker;
+    SimQueue(uint8_t *out_, uint8_t *const *stage_, int delay_us_) : out(out_), stage(stage_), delay_us(delay_us_)
+    {
+        for (int s = 0; s < 8; s++) { recorded[s].store(0); completed[s].store(0); }
+        worker = std::thread([this] { run(); });
+    }
+    ~SimQueue()
+    {
+        { std::lock_guard<std::mutex> g(mu); stop = true; }
+        worker.join();
+    }
+    void run()
+    {
+        for (;;) {
+            Job j;
+            {
+                std::lock_guard<std::mutex> g(mu);
+                if (jobs.empty()) { if (stop) return; j.slot = -1; }
+                else { j = jobs.front(); jobs.pop_front(); }
+            }
+            if (j.slot < 0) { std::this_thread::yield(); continue; }
+            if (delay_us > 0) std::this_thread::sleep_for(std::chrono::microseconds(delay_us));
+            std::copy(stage[j.slot], stage[j.slot] + j.len, out + j.base);
+            completed[j.slot].store(j.seq, std::memory_order_release);
+        }
+    }
+    int stage_copy(int slot, uint64_t base, uint64_t len)
+    {
+        const uint64_t seq = recorded[slot].load(std::memory_order_relaxed) + 1;
+        recorded[slot].store(seq, std::memory_order_relaxed);
+        std::lock_guard<std::mutex> g(mu);
+        jobs.push_back({slot, base, len, seq});
+        return 0;
+    }
+    int slot_state(int slot)
+    {
+        return completed[slot].load(std::memory_order_acquire) == recorded[slot].load(std::memory_order_relaxed) ? 0 : 1;
+    }
+    int rest(uint64_t, uint64_t) { return 0; }
+    void drain()
+    {
+        for (;;) {
+            { std::lock_guard<std::mutex> g(mu); if (jobs.empty()) break; }
+            std::this_thread::yield();
+        }
+    }
+};
+
+} // namespace
+
 extern "C" int lime_host_narrow_lcp_pipelined(const uint32_t *lcp, uint8_t *out, uint64_t n, uint64_t chunk,
-                                              int threads, int slots)
+                                              int threads, int slots, int copy_delay_us)
 {
     if ((!lcp || !out) && n) return LIME_ERR_ARG;
     if (chunk == 0 || slots < 1 || slots > 8) return LIME_ERR_ARG;
@@ -122,12 +184,11 @@ extern "C" int lime_host_narrow_lcp_pipelined(const uint32_t *lcp, uint8_t *out,
     std::vector<std::vector<uint8_t>> bufs(slots, std::vector<uint8_t>(chunk));
     std::vector<uint8_t *> stage;
     for (auto &b : bufs) stage.push_back(b.data());
-    lime::NarrowPipe pipe(lcp, n, chunk, threads, slots, stage.data());
-    for (uint64_t c = 0; c < pipe.n_chunks; c++) {
-        while (!pipe.ready(c)) std::this_thread::yield();
-        const uint64_t base = c * chunk, len = std::min(chunk, n - base);
-        std::copy(stage[c % slots], stage[c % slots] + len, out + base);
-        pipe.released(c + 1);
-    }
-    return LIME_OK;
+    int rc;
+    {
+        SimQueue q(out, stage.data(), copy_delay_us);
+        rc = lime::narrow_transfer(q, lcp, n, chunk, threads, slots, stage.data());
+        q.drain();
+    }                                                      // joins the worker: every queued copy has run
+    return rc ? LIME_ERR_CUDA : LIME_OK;
 }

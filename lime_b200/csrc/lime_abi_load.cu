@@ -6,16 +6,10 @@
 // of page-locked stage buffers (host_narrow.cpp) while the previous chunks are on the bus; on the device
 // widen_kernel writes the 32-bit array the step kernels read, so nothing downstream changes.
 #include "abi_internal.cuh"
+#include "narrow_loop.h"
 #include <algorithm>
-#include <thread>
 
 namespace lime {
-
-struct NarrowPipe;
-NarrowPipe *narrow_pipe_open(const uint32_t *src, uint64_t n, uint64_t chunk, int threads, int slots, uint8_t *const *stage);
-bool narrow_pipe_ready(const NarrowPipe *p, uint64_t c);
-void narrow_pipe_released(NarrowPipe *p, uint64_t k);
-void narrow_pipe_close(NarrowPipe *p);
 
 // 16 narrowed positions per thread and iteration: one 16-byte load, four 16-byte stores
 __global__ void __launch_bounds__(256) widen_kernel(const uint8_t *__restrict__ in, uint32_t *__restrict__ out, uint64_t n)
@@ -54,6 +48,50 @@ void load_release(lime_ctx *ctx)
     ctx->in_lcp8.release();
 }
 
+namespace {
+
+// the copy queue of narrow_transfer (narrow_loop.h) on the context's stream
+struct CudaQueue {
+    lime_ctx *ctx;
+    const uint32_t *da; const uint8_t *ebwt;
+    uint8_t *d8; uint32_t *d32;
+    int error(cudaError_t e, const char *what) { fail_cuda(ctx, e, what); return e == cudaErrorMemoryAllocation ? LIME_ERR_NOMEM : LIME_ERR_CUDA; }
+    int stage_copy(int slot, uint64_t base, uint64_t len)
+    {
+        ctx->stage_busy = true;
+        cudaError_t e = cudaMemcpyAsync(d8 + base, ctx->stage[slot], len, cudaMemcpyHostToDevice, ctx->stream);
+        if (e != cudaSuccess) return error(e, "H2D lcp (narrowed)");
+        e = cudaEventRecord(ctx->stage_ev[slot], ctx->stream);
+        if (e != cudaSuccess) return error(e, "cudaEventRecord");
+        return 0;
+    }
+    int slot_state(int slot)
+    {
+        const cudaError_t e = cudaEventQuery(ctx->stage_ev[slot]);
+        if (e == cudaSuccess) return 0;
+        if (e == cudaErrorNotReady) { cudaGetLastError(); return 1; }
+        return error(e, "H2D lcp (narrowed)");
+    }
+    int rest(uint64_t base, uint64_t len)
+    {
+        cudaError_t e;
+        {
+            LaunchScope ls(ctx, KID_LOAD_WIDEN);
+            e = launch_widen(d8 + base, d32 + base, len, ctx->stream);
+        }
+        if (e != cudaSuccess) return error(e, "load_widen launch");
+        e = cudaMemcpyAsync(ctx->in_da.as<uint32_t>() + base, da + base, len * 4, cudaMemcpyHostToDevice, ctx->stream);
+        if (e != cudaSuccess) return error(e, "H2D da");
+        if (ebwt) {
+            e = cudaMemcpyAsync(ctx->in_ebwt.as<uint8_t>() + base, ebwt + base, len, cudaMemcpyHostToDevice, ctx->stream);
+            if (e != cudaSuccess) return error(e, "H2D ebwt");
+        }
+        return 0;
+    }
+};
+
+} // namespace
+
 // lcp, da (and ebwt) of n positions: host -> device, lcp narrowed.  The device arrays are reserved by the caller.
 int load_host_narrow(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint8_t *ebwt, uint64_t n)
 {
@@ -65,46 +103,10 @@ int load_host_narrow(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, con
         else if (ctx->stage_busy) CK(cudaEventSynchronize(ctx->stage_ev[s]), "lcp stage of the previous load");
     }
     ctx->stage_busy = false;
-    const uint64_t n_chunks = (n + chunk - 1) / chunk;
-    // the calling thread only queues copies; it yields while it waits
+    // the calling thread only queues copies (it yields while it waits): one core is left to it
     const int threads = std::max(1, lime_host_threads() - 1);
-    NarrowPipe *pipe = narrow_pipe_open(lcp, n, chunk, threads, LIME_STAGE_SLOTS, ctx->stage);
-    struct Closer { NarrowPipe *p; ~Closer() { narrow_pipe_close(p); } } closer{pipe};
-    uint8_t *d8 = ctx->in_lcp8.as<uint8_t>();
-    uint32_t *d32 = ctx->in_lcp.as<uint32_t>();
-    uint64_t queued = 0, released = 0;
-    cudaError_t bad = cudaSuccess;
-    auto poll = [&]() {
-        while (released < queued) {
-            const cudaError_t q = cudaEventQuery(ctx->stage_ev[released % LIME_STAGE_SLOTS]);
-            if (q == cudaErrorNotReady) { cudaGetLastError(); break; }
-            if (q != cudaSuccess) { bad = q; break; }
-            released++;
-        }
-        narrow_pipe_released(pipe, released);
-    };
-    for (uint64_t c = 0; c < n_chunks; c++) {
-        while (!narrow_pipe_ready(pipe, c)) {
-            poll();
-            if (bad != cudaSuccess) return fail_cuda(ctx, bad, "H2D lcp (narrowed)");
-            std::this_thread::yield();
-        }
-        const uint64_t base = c * chunk, len = std::min(chunk, n - base);
-        const int s = (int)(c % LIME_STAGE_SLOTS);
-        ctx->stage_busy = true;
-        CK(cudaMemcpyAsync(d8 + base, ctx->stage[s], len, cudaMemcpyHostToDevice, ctx->stream), "H2D lcp (narrowed)");
-        CK(cudaEventRecord(ctx->stage_ev[s], ctx->stream), "cudaEventRecord");
-        queued = c + 1;
-        {
-            LaunchScope ls(ctx, KID_LOAD_WIDEN);
-            CK(launch_widen(d8 + base, d32 + base, len, ctx->stream), "load_widen launch");
-        }
-        CK(cudaMemcpyAsync(ctx->in_da.as<uint32_t>() + base, da + base, len * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D da");
-        if (ebwt) CK(cudaMemcpyAsync(ctx->in_ebwt.as<uint8_t>() + base, ebwt + base, len, cudaMemcpyHostToDevice, ctx->stream), "H2D ebwt");
-        poll();
-        if (bad != cudaSuccess) return fail_cuda(ctx, bad, "H2D lcp (narrowed)");
-    }
-    return LIME_OK;
+    CudaQueue q{ctx, da, ebwt, ctx->in_lcp8.as<uint8_t>(), ctx->in_lcp.as<uint32_t>()};
+    return narrow_transfer(q, lcp, n, chunk, threads, LIME_STAGE_SLOTS, ctx->stage);
 }
 
 extern "C" int lime_set_alpha_limit(lime_ctx *ctx, uint32_t max_alpha)

@@ -36,14 +36,17 @@ def test_narrow_plain(n, threads):
     assert (out[n:] == 0xAB).all()           # nothing written past the end
 
 
+@pytest.mark.parametrize("delay_us", [0, 50])
 @pytest.mark.parametrize("n,chunk,threads,slots", [
     (1, 64, 2, 1), (64, 64, 3, 2), (65, 64, 3, 3), (1000, 64, 5, 3), (100003, 4096, 7, 3),
     (100003, 4096, 1, 1), (1 << 20, 1 << 16, 4, 2), ((1 << 21) + 11, 100000, 15, 3), (5, 1 << 20, 16, 3)])
-def test_narrow_pipelined(n, chunk, threads, slots):
+def test_narrow_pipelined(n, chunk, threads, slots, delay_us):
+    """narrow_transfer (the loop lime_load runs) over a simulated in-order asynchronous copy queue: a stage
+    slot rewritten before its (delayed) copy has run would corrupt the output."""
     lib = _lib.load()
     lcp = _lcp(n, 11 + n)
     out = np.full(n + 8, 0xCD, dtype=np.uint8)
-    assert lib.lime_host_narrow_lcp_pipelined(_ptr(lcp), _ptr(out), n, chunk, threads, slots) == 0
+    assert lib.lime_host_narrow_lcp_pipelined(_ptr(lcp), _ptr(out), n, chunk, threads, slots, delay_us) == 0
     assert np.array_equal(out[:n], np.minimum(lcp, 255).astype(np.uint8))
     assert (out[n:] == 0xCD).all()
 
@@ -52,8 +55,8 @@ def test_narrow_pipelined_rejects_bad_arguments():
     lib = _lib.load()
     lcp = _lcp(10, 1)
     out = np.zeros(10, dtype=np.uint8)
-    assert lib.lime_host_narrow_lcp_pipelined(_ptr(lcp), _ptr(out), 10, 0, 1, 1) != 0
-    assert lib.lime_host_narrow_lcp_pipelined(_ptr(lcp), _ptr(out), 10, 4, 1, 0) != 0
+    assert lib.lime_host_narrow_lcp_pipelined(_ptr(lcp), _ptr(out), 10, 0, 1, 1, 0) != 0
+    assert lib.lime_host_narrow_lcp_pipelined(_ptr(lcp), _ptr(out), 10, 4, 1, 0, 0) != 0
     assert lib.lime_host_narrow_lcp(None, _ptr(out), 10, 1) != 0
     assert lib.lime_host_threads() >= 1
 
