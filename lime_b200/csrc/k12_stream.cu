@@ -29,8 +29,9 @@
 #include "score.cuh"
 #include <algorithm>
 
-// compile-time experiment switches for the next round of tuning (bit 0: row address per read leader,
-// bit 1: arithmetic A/C/G/T classes); 0 in every shipped build -- the default code is unchanged
+// compile-time experiment switches for the next round of tuning (value 1: row address per read leader,
+// 2: arithmetic A/C/G/T classes, 4: packed 32-bit stream element); 0 in every shipped build -- the SASS
+// of the default build is byte-identical with and without these blocks
 #ifndef LIME_K12_EXP
 #define LIME_K12_EXP 0
 #endif
@@ -468,7 +469,9 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
                     if (inf.x == 0u) continue;
                     if ((inf.x >> lane) & 1u) {
                         const uint32_t o = inf.z + __popc(inf.x & lt_mask);
+#if !(LIME_K12_EXP & 4)
                         ws.cid[o] = ws.da[32 * k + lane];
+#endif
 #if LIME_K12_EXP & 2
                         // experiment (not built by default): A,C,G,T mapped arithmetically, the table only for the rest
                         uint32_t cl0 = 0u;
@@ -477,9 +480,15 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
                             const uint32_t x = (sy >> 1) & 3u;
                             cl0 = (d < 20u && ((0x80045u >> d) & 1u)) ? (x ^ (x >> 1)) : (uint32_t)sm.cls[sy];
                         }
-                        ws.cmeta[o] = (uint16_t)(cl0 | (((inf.y >> lane) & 1u) << 8));
 #else
-                        ws.cmeta[o] = (uint16_t)((EBWT ? (uint32_t)sm.cls[ws.eb[32 * k + lane]] : 0u) | (((inf.y >> lane) & 1u) << 8));
+                        const uint32_t cl0 = EBWT ? (uint32_t)sm.cls[ws.eb[32 * k + lane]] : 0u;
+#endif
+#if LIME_K12_EXP & 4
+                        // experiment (not built by default): one packed element id | class << 27 | start << 31
+                        // (ids < 2^27 - 1, checked by the launcher): one store here, one load in phase D
+                        ws.cid[o] = ws.da[32 * k + lane] | (cl0 << 27) | (((inf.y >> lane) & 1u) << 31);
+#else
+                        ws.cmeta[o] = (uint16_t)(cl0 | (((inf.y >> lane) & 1u) << 8));
 #endif
                     }
                 }
@@ -488,17 +497,28 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
         issue_next();                                                     // includes the __syncwarp
         if (n_act == 0) continue;                                         // warp-uniform
         ws.cid[n_act + lane] = 0xffffffffu;                               // one window of padding: lone starts
+#if !(LIME_K12_EXP & 4)
         ws.cmeta[n_act + lane] = 0x100u;
+#endif
         __syncwarp();
         if (P.dbg & 4u) continue;
 
         // ---- phase D: score the clusters of the stream, 32-lane windows --------------------------------
         unsigned longest = 0;                                             // warp-uniform
         for (int i = 0; i < n_act;) {
+#if LIME_K12_EXP & 4
+            const uint32_t pk = ws.cid[i + lane];
+            uint32_t id = pk & 0x07ffffffu;
+            if (id == 0x07ffffffu) id = 0xffffffffu;                      // padding
+            const uint32_t meta = ((pk >> 27) & 15u) | ((pk >> 31) << 8);
+#define K12_NEXT_IS_START ((ws.cid[i + 32] >> 31) != 0u)
+#else
             uint32_t id = ws.cid[i + lane];
             const uint32_t meta = ws.cmeta[i + lane];
+#define K12_NEXT_IS_START (ws.cmeta[i + 32] & 0x100u)
+#endif
             uint32_t sb = __ballot_sync(FULL, (meta & 0x100u) != 0);      // bit 0 is set: i is a start
-            if (!(ws.cmeta[i + 32] & 0x100u)) {
+            if (!K12_NEXT_IS_START) {
                 // the last cluster of the window is cut: leave it to the next window (turn its lanes
                 // into lone starts; a cluster has at most 32 positions, so it does not start at lane 0)
                 const int ls = 31 - __clz(sb);
@@ -718,6 +738,9 @@ uint64_t k12_long_cap(uint64_t n_total) { return n_total / (k12s::MAXFAST + 1) +
 cudaError_t launch_k12(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s)
 {
     if (a.n_own == 0) return cudaSuccess;
+#if LIME_K12_EXP & 4
+    if ((uint64_t)a.n_reads + a.n_refs >= 0x07ffffffull) return cudaErrorInvalidValue;   // packed stream elements
+#endif
     if (a.peer_on) {
         // multi-GPU peer mode: scoring only, fire-and-forget adds into the owners' slabs
         if (!score || emit || exact32 || !a.sum_t) return cudaErrorInvalidValue;
