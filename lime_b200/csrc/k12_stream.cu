@@ -30,7 +30,8 @@
 #include <algorithm>
 
 // compile-time experiment switches for the next round of tuning (value 1: row address per read leader,
-// 2: arithmetic A/C/G/T classes, 4: packed 32-bit stream element); 0 in every shipped build -- the SASS
+// 2: arithmetic A/C/G/T classes, 4: packed 32-bit stream element, 8: phase C visits only the non-empty
+// words); 0 in every shipped build -- the SASS
 // of the default build is byte-identical with and without these blocks
 #ifndef LIME_K12_EXP
 #define LIME_K12_EXP 0
@@ -463,10 +464,17 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
             if (w < WORDS) info[w] = make_uint4(Aw, H, incl - cnt, 0u);
             __syncwarp();
             if (n_act) {
+#if LIME_K12_EXP & 8
+                // experiment (not built by default): visit only the words that hold active positions
+                for (unsigned nzw = __ballot_sync(FULL, w < WORDS && Aw != 0u); nzw; nzw &= nzw - 1u) {
+                    const int k = __ffs(nzw) - 1;
+                    const uint4 inf = info[k];
+#else
 #pragma unroll
                 for (int k = 0; k < WORDS; k++) {
                     const uint4 inf = info[k];
                     if (inf.x == 0u) continue;
+#endif
                     if ((inf.x >> lane) & 1u) {
                         const uint32_t o = inf.z + __popc(inf.x & lt_mask);
 #if !(LIME_K12_EXP & 4)

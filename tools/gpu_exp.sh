@@ -1,9 +1,9 @@
 #!/bin/bash
 # compile-time experiments of the stream kernel (LIME_K12_EXP bits, see k12_stream.cu): rebuilds the
 # library on the GPU box per variant, runs the parity tests of the fused path and a short bench, and
-# puts the default build back.  usage: gpu_exp.sh 1 2 4 7   (bit 1: row address per read leader, 2: arithmetic A,C,G,T class, 4: packed stream element)
+# puts the default build back.  usage: gpu_exp.sh 1 2 4 8 12 15   (1: row address per read leader, 2: arithmetic A,C,G,T class, 4: packed stream element, 8: phase C visits non-empty words only; sums combine)
 mkdir -p gpurun_out
-for v in ${@:-1 2 4 7} 0; do
+for v in ${@:-1 2 4 8 12 15} 0; do
   touch lime_b200/csrc/k12_stream.cu
   make -s -C lime_b200/csrc EXTRA=-DLIME_K12_EXP=$v || { echo "build $v failed"; continue; }
   if [ "$v" != 0 ]; then

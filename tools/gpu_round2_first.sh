@@ -17,4 +17,4 @@ except Exception as e:
     print('bench line unreadable:', e)
 PY
 LIME_NARROW_LCP=1 python -m pytest tests/test_host_cli.py -m gpu -x -q > gpurun_out/r2_cli_narrow.log 2>&1; echo "cli (LIME_NARROW_LCP=1) rc=$?"; tail -2 gpurun_out/r2_cli_narrow.log
-bash tools/gpu_exp.sh 1 2 4 7
+bash tools/gpu_exp.sh 1 2 4 8 12 15
