@@ -95,7 +95,7 @@ int  lime_set_alpha_limit(lime_ctx *ctx, uint32_t max_alpha);
  * lime_host_threads()), and the same through the chunk loop lime_load runs (slots stage buffers of
  * `chunk` positions) over a simulated in-order copy queue that performs each copy copy_delay_us after
  * taking it.  Exposed for the CPU tests and for callers that narrow while they read a file. */
-int  lime_host_threads(void);     /* LIME_HOST_THREADS or min(hardware threads, 16) */
+int  lime_host_threads(void);     /* LIME_HOST_THREADS, else min(cores in the affinity mask, 16) */
 int  lime_host_narrow_lcp(const uint32_t *lcp, uint8_t *out, uint64_t n, int threads);
 int  lime_host_narrow_lcp_pipelined(const uint32_t *lcp, uint8_t *out, uint64_t n, uint64_t chunk,
                                     int threads, int slots, int copy_delay_us);
