@@ -38,6 +38,8 @@ extern "C" {
 #define LIME_ERR_STATE    -5   /* call order violated (e.g. similarity before cluster_detect)    */
 #define LIME_ERR_NOMEM    -6   /* device or host allocation failed                               */
 #define LIME_ERR_ROWS     -7   /* .res rows not strictly ascending in genome id                  */
+#define LIME_ERR_RETRY    -8   /* a strand run without synchronisation must be redone with the   */
+                               /* synchronising calls (buffer guess too small, or a cell > 255)  */
 
 #define LIME_MEM_HOST      0
 #define LIME_MEM_DEVICE    1
@@ -72,7 +74,10 @@ void  lime_pinned_free(void *p);
  *   n_halo   positions after the owned range that a straddling cluster may run into (:246-264);
  *   is_last  non-zero if element n_own+n_halo-1 is the last position of the whole array (:244-245).
  * Single GPU: n_halo = 0, pos_base = 0, is_last = 1.
- * mem = LIME_MEM_HOST copies (pageable or pinned) host arrays to the device;
+ * mem = LIME_MEM_HOST copies (pageable or pinned) host arrays to the device.  From page-locked memory the
+ * copies are asynchronous: lime_load may return while they are in flight, so the arrays must not be modified
+ * or freed before the next synchronising call on this ctx (lime_cluster_detect, lime_cluster_similarity,
+ * lime_similarity, lime_choose, lime_classify, any *_copy) has returned;
  * mem = LIME_MEM_DEVICE borrows 16-byte aligned device pointers, which must stay valid.
  * Loading resets the clusters and zeroes the similarity accumulator.
  */
@@ -87,7 +92,7 @@ int  lime_load(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uin
  * on (the drop-in executables know it from their command line before they read a file); 0 = no promise
  * (default).  With 1 <= max_alpha <= 255, lime_load(LIME_MEM_HOST) narrows lcp on host threads, chunk by
  * chunk into page-locked stage buffers while the previous chunks are on the bus, sends 1 + 4 (+1) instead
- * of 4 + 4 (+1) bytes per position over PCIe and widens on the device; results are identical.  A step
+ * of 4 + 4 (+1) bytes per position over PCIe and the kernels read the bytes; results are identical.  A step
  * called with alpha > 255 on a strand loaded that way fails with LIME_ERR_STATE.
  */
 int  lime_set_alpha_limit(lime_ctx *ctx, uint32_t max_alpha);
@@ -126,6 +131,19 @@ int  lime_clusters_set(lime_ctx *ctx, const lime_cluster *cl, uint64_t n_cluster
 int  lime_cluster_similarity(lime_ctx *ctx, uint32_t alpha, int ebwt_mode, int keep_clusters,
                              uint64_t *n_clusters, uint64_t *max_len);
 
+/*
+ * One strand of LiME_paired.sh (:44-68: ClusterLCP, then ClusterBWT_DA) without a host synchronisation:
+ * lime_cluster_similarity + lime_choose(slot, norm, beta, all reads) queued on the ctx stream -- fused kernel,
+ * block path, one choose pass that also proves the absence of uint8 carries (byte sum) and leaves the matrix
+ * zero for the next lime_load.  Errors of the strand (halo, maxLen > sizeMaxBuf) and its scalars surface at the
+ * next lime_classify, which returns LIME_ERR_RETRY when the strand has to be redone with the synchronising
+ * calls (record buffer sized from the previous strands too small; a cell above 255).  The first strand of a
+ * context runs synchronously (it sizes the buffers).  lime_strand_status: nClusters, maxLen (the values of
+ * <stem>.out), records incl. sentinel, updates -- valid once the slot has been read back by lime_classify.
+ */
+int  lime_strand_run(lime_ctx *ctx, int slot, uint32_t alpha, int ebwt_mode, uint32_t norm, float beta);
+int  lime_strand_status(lime_ctx *ctx, int slot, uint64_t out[4]);
+
 /* ---- step 2 : ClusterBWT_DA.cpp:256-358, 361-450 ------------------------------------------ */
 
 /* Accumulate t(read, genome) of every resident cluster into the similarity matrix
@@ -140,7 +158,8 @@ int  lime_similarity(lime_ctx *ctx, int ebwt_mode);
 int  lime_sim_bind(lime_ctx *ctx, void *dev_matrix, uint64_t rows, uint64_t pitch);
 /* Row pitch in bytes the ctx uses for n_refs genomes. */
 uint64_t lime_sim_pitch(uint32_t n_refs);
-/* Dense copy of the matrix, [n_reads][n_refs] uint8 (the SMALL=1 dump, ClusterBWT_DA.cpp:672-681). */
+/* Dense copy of the matrix, [n_reads][n_refs] uint8 (the SMALL=1 dump, ClusterBWT_DA.cpp:672-681); in exchange
+ * mode (lime_xchg_*) the selected slab, [reads_per_rank][n_refs]. */
 int  lime_sim_copy(lime_ctx *ctx, uint8_t *out);
 
 /*
@@ -161,7 +180,8 @@ int  lime_slot_set(lime_ctx *ctx, int slot, const lime_pair_sim *bin, uint64_t n
 
 /*
  * With the position range sharded over GPUs every GPU accumulates a PARTIAL similarity matrix over
- * all reads.  Reads are owned by contiguous ranges; before lime_choose the owner needs the sum.
+ * all reads.  Reads are owned by contiguous ranges; before lime_choose the owner needs the sum.  This is the
+ * exact route (a cell above 255 wraps as the reference's does) behind the faster lime_xchg_* calls below.
  * lime_sim_export writes the non-zero cells of rows [read_begin, read_end) as triples
  * {uint32 read, uint32 genome << 8 | count} (ascending read, then genome) to DEVICE memory
  * `dev_triples` (capacity `cap` triples, 8 bytes each) -- what is sent to the owner of that range;
@@ -173,40 +193,43 @@ int  lime_sim_export(lime_ctx *ctx, uint32_t read_begin, uint32_t read_end, void
                      uint64_t cap, uint64_t *n_triples);
 int  lime_sim_import(lime_ctx *ctx, const void *dev_triples, uint64_t n_triples);
 
-/* ---- multi-GPU accumulation over peer memory (one NVLink / NVSwitch node) ---------------------- */
+/* ---- multi-GPU: similarity rows on the read owner, updates routed as records ------------------ */
 
 /*
- * The alternative to export / all-to-all / import: every GPU holds only the rows of the reads it owns
- * (rank k owns reads [k * reads_per_rank, (k+1) * reads_per_rank)), one slab of `rows` x pitch uint8
- * per strand, and maps the slabs of all other GPUs (CUDA IPC).  lime_peer_accumulate is
- * lime_cluster_similarity with every update added directly to the owner's slab over NVLink: the
- * reference's `SimArray_[read][genome] += t` (ClusterBWT_DA.cpp:183,247) on a matrix that is spread
- * over the node.  Call order on every rank (collectives are the caller's, e.g. NCCL):
- *   lime_peer_alloc -> all-gather the 64-byte handles -> lime_peer_open            (once)
- *   lime_peer_zero -> BARRIER -> per strand: lime_load, lime_peer_accumulate(slab) -> BARRIER ->
- *   per strand: lime_peer_select(slab) + lime_choose(slot, ..., 0, own reads) -> lime_classify.
- * out[4] of lime_peer_accumulate = this shard's nClusters, maxLen, updates, sum of all t added.
- * lime_peer_select makes slab `slab` the matrix lime_choose reads (row 0 = first owned read);
- * total_updates (sum over all ranks) bounds its records; byte_sum (optional, DEVICE memory, written
- * asynchronously on the ctx stream) receives the byte sum of the slab: the sum over ranks of the
- * byte sums must equal the sum over ranks of out[3], otherwise a cell exceeded 255 and the job has
- * to be redone through the exact path (lime_sim_export route).
- * lime_peer_zero_slab clears one slab once lime_choose has read it, so that the collective which
- * carries the byte sums is also the "all slabs are zero" barrier of the next job (no lime_peer_zero).
+ * The route of north_star ("partial (read, genome, count) triples are routed to their owning GPU by read id")
+ * without a partial matrix over all reads: rank k owns reads [k * reads_per_rank, (k+1) * reads_per_rank) and
+ * keeps only their rows (one slab of reads_per_rank x pitch uint8 per strand) plus an inbox with one region of
+ * inbox_cap records per source rank and strand, which the other processes map (CUDA IPC).  The reference's
+ * `SimArray_[read][genome] += t` (ClusterBWT_DA.cpp:183,247) becomes a record {read, genome << 8 | t}:
+ *   lime_xchg_accumulate  lime_cluster_similarity with every update appended to a local list (capacity
+ *                         flat_cap records), then sorted by owner and written into this rank's region of each
+ *                         owner's inbox -- bulk stores over NVLink / NVSwitch, nothing remote is read or updated
+ *                         atomically.  dev_sent (DEVICE memory, [world] uint64) receives the records sent to
+ *                         every owner;
+ *   (caller)              all-gather of dev_sent over the ranks -> dev_counts_all [world][world] (source major):
+ *                         the job's only collective per strand, and the barrier "every source has delivered";
+ *   lime_xchg_apply       adds the records of all regions of this rank's inbox to the slab;
+ *   lime_xchg_choose      clusterChoose (ClusterBWT_DA.cpp:361-450) of the owned reads into strand slot `strand`.
+ * None of the three synchronises with the host.  lime_classify then classifies the owned reads and reads the
+ * strands' device state back: LIME_ERR_RETRY means the job must be redone through lime_sim_export / lime_sim_import
+ * (a cell exceeded 255, where the reference wraps, or a list / inbox was too small); the ranks agree on that
+ * by their own collective.  lime_strand_status gives nClusters / maxLen / records / updates of this rank's shard.
+ * Call order on every rank: lime_xchg_alloc -> all-gather the 64-byte handles -> lime_xchg_open (once); per job
+ * and strand: lime_load, lime_xchg_accumulate, all-gather, lime_xchg_apply, lime_xchg_choose; lime_classify.
+ * lime_xchg_open(ctx, NULL) is a loopback for tests on one GPU: all owners' regions are local, rank k applies
+ * region k.  lime_xchg_status synchronises and returns nClusters, maxLen, updates, list slots used, sum of t
+ * applied, byte sum of the slab, records, error bits of one strand.
  */
 #define LIME_IPC_HANDLE_BYTES 64
-#define LIME_PEER_MAX         16
-int  lime_peer_alloc(lime_ctx *ctx, uint64_t rows, uint32_t n_refs, int n_slabs, uint8_t *ipc_handle);
-int  lime_peer_open(lime_ctx *ctx, int world, int rank, const uint8_t *ipc_handles, uint32_t reads_per_rank);
-int  lime_peer_close(lime_ctx *ctx);
-int  lime_peer_zero(lime_ctx *ctx);
-int  lime_peer_accumulate(lime_ctx *ctx, uint32_t alpha, int ebwt_mode, int slab, uint64_t out[4]);
-int  lime_peer_select(lime_ctx *ctx, int slab, uint64_t total_updates, uint64_t *byte_sum);
-int  lime_peer_zero_slab(lime_ctx *ctx, int slab);
-/* Instrumentation: n_adds adds of 0 to random cells of the first span_rows rows of the slabs of owners
- * [first_owner, first_owner + n_owners); mode 0 red, 1 atom (returned), 2 store.  *ms = device time. */
-int  lime_peer_probe(lime_ctx *ctx, int slab, int first_owner, int n_owners, uint32_t span_rows, uint64_t n_adds,
-                     int mode, double *ms);
+#define LIME_XCHG_MAX         16
+int  lime_xchg_alloc(lime_ctx *ctx, int world, int rank, uint32_t reads_per_rank, uint32_t n_refs, int n_strands,
+                     uint64_t flat_cap, uint64_t inbox_cap, uint8_t *ipc_handle);
+int  lime_xchg_open(lime_ctx *ctx, const uint8_t *ipc_handles);
+int  lime_xchg_close(lime_ctx *ctx);
+int  lime_xchg_accumulate(lime_ctx *ctx, uint32_t alpha, int ebwt_mode, int strand, uint64_t *dev_sent);
+int  lime_xchg_apply(lime_ctx *ctx, int strand, const uint64_t *dev_counts_all);
+int  lime_xchg_choose(lime_ctx *ctx, int strand, uint32_t norm, float beta, uint32_t n_own_reads);
+int  lime_xchg_status(lime_ctx *ctx, int strand, uint64_t out[8]);
 
 /* ---- step 3 : Classify.cpp:474-702 -------------------------------------------------------- */
 

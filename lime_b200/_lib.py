@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "liblime_b200.so")
 
 OK = 0
-ERR_ARG, ERR_CUDA, ERR_MAXLEN, ERR_HALO, ERR_STATE, ERR_NOMEM, ERR_ROWS = -1, -2, -3, -4, -5, -6, -7
+ERR_ARG, ERR_CUDA, ERR_MAXLEN, ERR_HALO, ERR_STATE, ERR_NOMEM, ERR_ROWS, ERR_RETRY = -1, -2, -3, -4, -5, -6, -7, -8
 MEM_HOST, MEM_DEVICE = 0, 1
 
 
@@ -57,14 +57,15 @@ SIGNATURES = {
     "lime_slot_set": (C.c_int, [vp, C.c_int, vp, C.c_uint64, vp, C.c_uint32]),
     "lime_classify": (C.c_int, [vp, C.c_int, C.c_uint32, vp, vp, C.c_int, C.c_int, vp, vp, vp]),
     "lime_classify_result": (C.c_int, [vp, vp, vp, vp, C.c_int]),
-    "lime_peer_alloc": (C.c_int, [vp, C.c_uint64, C.c_uint32, C.c_int, vp]),
-    "lime_peer_open": (C.c_int, [vp, C.c_int, C.c_int, vp, C.c_uint32]),
-    "lime_peer_close": (C.c_int, [vp]),
-    "lime_peer_zero": (C.c_int, [vp]),
-    "lime_peer_accumulate": (C.c_int, [vp, C.c_uint32, C.c_int, C.c_int, u64p]),
-    "lime_peer_select": (C.c_int, [vp, C.c_int, C.c_uint64, vp]),
-    "lime_peer_zero_slab": (C.c_int, [vp, C.c_int]),
-    "lime_peer_probe": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint64, C.c_int, C.POINTER(C.c_double)]),
+    "lime_xchg_alloc": (C.c_int, [vp, C.c_int, C.c_int, C.c_uint32, C.c_uint32, C.c_int, C.c_uint64, C.c_uint64, vp]),
+    "lime_xchg_open": (C.c_int, [vp, vp]),
+    "lime_xchg_close": (C.c_int, [vp]),
+    "lime_xchg_accumulate": (C.c_int, [vp, C.c_uint32, C.c_int, C.c_int, vp]),
+    "lime_xchg_apply": (C.c_int, [vp, C.c_int, vp]),
+    "lime_xchg_choose": (C.c_int, [vp, C.c_int, C.c_uint32, C.c_float, C.c_uint32]),
+    "lime_xchg_status": (C.c_int, [vp, C.c_int, u64p]),
+    "lime_strand_run": (C.c_int, [vp, C.c_int, C.c_uint32, C.c_int, C.c_uint32, C.c_float]),
+    "lime_strand_status": (C.c_int, [vp, C.c_int, u64p]),
     "lime_launch_count": (C.c_uint64, [vp]),
     "lime_prof_enable": (C.c_int, [vp, C.c_int]),
     "lime_prof_kernels": (C.c_int, []),

@@ -159,8 +159,9 @@ class LimeContext:
         self._ck(self.lib.lime_sim_stats(self.h, out))
         return {"warp_clusters": out[0], "block_clusters": out[1], "updates": out[2], "exact_pass": out[3]}
 
-    def sim_matrix(self):
-        out = np.empty((self.n_reads, self.n_refs), dtype=np.uint8)
+    def sim_matrix(self, rows=None):
+        """Dense copy of the matrix; rows: the slab height in exchange mode (reads per rank)."""
+        out = np.empty((self.n_reads if rows is None else rows, self.n_refs), dtype=np.uint8)
         self._ck(self.lib.lime_sim_copy(self.h, _ptr(out)))
         return out
 
@@ -177,42 +178,53 @@ class LimeContext:
     def sim_import(self, dev_ptr, n):
         self._ck(self.lib.lime_sim_import(self.h, C.c_void_p(dev_ptr) if dev_ptr else None, n))
 
-    # ---- multi-GPU accumulation over peer memory ----------------------------------------------
-    def peer_alloc(self, rows, n_refs, n_slabs):
-        """Allocate this rank's slabs; returns the 64-byte CUDA IPC handle to all-gather."""
+    # ---- multi-GPU: rows on the read owner, updates routed as records -----------------------------
+    def xchg_alloc(self, world, rank, reads_per_rank, n_refs, n_strands, flat_cap, inbox_cap):
+        """Allocate this rank's slabs / update list / inbox; returns the 64-byte CUDA IPC handle to all-gather."""
         h = np.zeros(_lib.IPC_HANDLE_BYTES, dtype=np.uint8)
-        self._ck(self.lib.lime_peer_alloc(self.h, rows, n_refs, n_slabs, _ptr(h)))
+        self._ck(self.lib.lime_xchg_alloc(self.h, world, rank, reads_per_rank, n_refs, n_strands, flat_cap, inbox_cap, _ptr(h)))
         return h
 
-    def peer_open(self, world, rank, handles, reads_per_rank):
-        handles = np.ascontiguousarray(handles, dtype=np.uint8).reshape(world * _lib.IPC_HANDLE_BYTES)
-        self._ck(self.lib.lime_peer_open(self.h, world, rank, _ptr(handles), reads_per_rank))
+    def xchg_open(self, handles=None):
+        """Map every rank's inbox (handles: (world, 64) uint8); None = loopback on one GPU (tests)."""
+        if handles is not None:
+            handles = np.ascontiguousarray(handles, dtype=np.uint8).reshape(-1)
+        self._ck(self.lib.lime_xchg_open(self.h, _ptr(handles)))
 
-    def peer_close(self):
-        self._ck(self.lib.lime_peer_close(self.h))
+    def xchg_close(self):
+        self._ck(self.lib.lime_xchg_close(self.h))
 
-    def peer_zero(self):
-        self._ck(self.lib.lime_peer_zero(self.h))
+    def xchg_accumulate(self, alpha, ebwt_mode, strand, dev_sent_ptr):
+        self._ck(self.lib.lime_xchg_accumulate(self.h, alpha, 1 if ebwt_mode else 0, strand, C.c_void_p(dev_sent_ptr)))
 
-    def peer_accumulate(self, alpha, ebwt_mode, slab):
-        """-> (n_clusters, max_len, updates, sum_t) of this shard."""
+    def xchg_apply(self, strand, dev_counts_all_ptr):
+        self._ck(self.lib.lime_xchg_apply(self.h, strand, C.c_void_p(dev_counts_all_ptr)))
+
+    def xchg_choose(self, strand, norm, beta, n_own_reads):
+        self._ck(self.lib.lime_xchg_choose(self.h, strand, norm, beta, n_own_reads))
+        self._slot_shape = getattr(self, "_slot_shape", {})
+        self._slot_shape[strand] = (None, n_own_reads)
+
+    def xchg_status(self, strand):
+        out = (C.c_uint64 * 8)()
+        self._ck(self.lib.lime_xchg_status(self.h, strand, out))
+        k = ("n_clusters", "max_len", "updates", "list_slots", "applied_t", "byte_sum", "n_records", "err")
+        return {a: int(b) for a, b in zip(k, out)}
+
+    # ---- one strand without a host synchronisation ------------------------------------------------
+    def strand_run(self, slot, alpha, ebwt_mode, norm, beta):
+        """lime_strand_run: lime_cluster_similarity + lime_choose of all reads, queued; checked at classify()."""
+        self._ck(self.lib.lime_strand_run(self.h, slot, alpha, 1 if ebwt_mode else 0, norm, beta))
+        self._slot_shape = getattr(self, "_slot_shape", {})
+        self._slot_shape[slot] = (None, self.n_reads)
+
+    def strand_status(self, slot):
+        """-> (n_clusters, max_len, n_records, updates) of a slot that lime_classify has read back."""
         out = (C.c_uint64 * 4)()
-        self._ck(self.lib.lime_peer_accumulate(self.h, alpha, 1 if ebwt_mode else 0, slab, out))
+        self._ck(self.lib.lime_strand_status(self.h, slot, out))
+        if slot in getattr(self, "_slot_shape", {}):
+            self._slot_shape[slot] = (int(out[2]), self._slot_shape[slot][1])
         return tuple(int(x) for x in out)
-
-    def peer_select(self, slab, total_updates, byte_sum_dev_ptr=None):
-        """byte_sum_dev_ptr: device address of a uint64 that receives the slab's byte sum (async)."""
-        self._ck(self.lib.lime_peer_select(self.h, slab, total_updates,
-                                           C.c_void_p(byte_sum_dev_ptr) if byte_sum_dev_ptr else None))
-
-    def peer_probe(self, slab, first_owner, n_owners, span_rows, n_adds, mode=0):
-        """Device milliseconds of n_adds random adds of 0 into the slabs (instrumentation)."""
-        ms = C.c_double()
-        self._ck(self.lib.lime_peer_probe(self.h, slab, first_owner, n_owners, span_rows, n_adds, mode, C.byref(ms)))
-        return float(ms.value)
-
-    def peer_zero_slab(self, slab):
-        self._ck(self.lib.lime_peer_zero_slab(self.h, slab))
 
     def choose(self, slot, norm, beta, read_begin=0, read_end=None):
         if read_end is None:
@@ -225,6 +237,8 @@ class LimeContext:
 
     def choose_result(self, slot):
         n_rec, n_reads = self._slot_shape[slot]
+        if n_rec is None:
+            n_rec = self.strand_status(slot)[2]
         bin_ = np.empty(n_rec, dtype=PAIR_SIM_DT)
         pos = np.empty(n_reads, dtype=np.uint64)
         self._ck(self.lib.lime_choose_copy(self.h, slot, _ptr(bin_), _ptr(pos)))

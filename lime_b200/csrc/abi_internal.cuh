@@ -7,7 +7,7 @@ using namespace lime;
 
 
 static const char *const kKernelNames[KID_COUNT] = {
-    "k12_fused", "k12_check", "k1_detect", "k2_warp", "k2_block", "k2_narrow", "k3_choose", "k3_export", "k3_import", "k3_count", "k3_emit", "k3_classify", "load_widen"};
+    "k12_fused", "k12_check", "k1_detect", "k2_warp", "k2_block", "k2_narrow", "k3_choose", "k3_export", "k3_import", "k3_count", "k3_emit", "k3_classify", "x_route", "x_apply"};
 
 // device scalar block layout (u64 slots)
 enum {
@@ -18,6 +18,18 @@ enum {
     SC_SUMT, SC_BYTESUM,
     SC_COUNT
 };
+
+// per-strand device state of the calls that do not synchronise (lime_strand_run, lime_xchg_*): one block of
+// SS_COUNT u64 per strand slot in ctx->strand_state; read back once, by lime_classify / lime_xchg_status
+enum {
+    SS_NCLUSTERS = 0, SS_MAXLEN, SS_LONG_COUNT, SS_LONG_NEXT, SS_NUPDATES, SS_SUMT, SS_BYTESUM, SS_NRECORDS,
+    SS_ERR,            // bit0 halo exhausted, bit2 inbox region overflow, bit3 record out of range
+    SS_TILE_COUNTER,   // u32 used
+    SS_FLAT_COUNT, SS_APPLIED_T, SS_APPLIED_N,
+    SS_SENT = 16,      // [XCHG_MAX] records routed to every owner
+    SS_COUNT = 32
+};
+static_assert(SS_SENT + lime::XCHG_MAX <= SS_COUNT, "strand state block");
 
 static int fail(lime_ctx *c, int code, const std::string &msg)
 {
@@ -37,11 +49,20 @@ template <class T> static T *scalar(lime_ctx *c, int slot)
     return reinterpret_cast<T *>(c->scalars.as<unsigned long long>() + slot);
 }
 
-// lime_abi_steps.cu / lime_abi_peer.cu
-int run_k12_pass(lime_ctx *ctx, uint32_t alpha, bool ebwt, bool emit, bool exact32, uint32_t lo, uint32_t hi,
-                 unsigned long long sc[SC_COUNT], int peer_slab);
-lime::PeerTable peer_table(const lime_ctx *ctx, int slab);
-void peer_release(lime_ctx *ctx);
+template <class T> static T *strand_scalar(lime_ctx *c, int slot, int k)
+{
+    return reinterpret_cast<T *>(c->strand_state.as<unsigned long long>() + (size_t)slot * SS_COUNT + k);
+}
+
+// lime_abi_steps.cu / lime_abi_xchg.cu
+// the fused kernel + the block path over the clusters it sets aside, asynchronous; scalars land in `sc`
+// (a device block laid out as SS_*); flat: records instead of adds into ctx->d_sim
+int queue_k12_score(lime_ctx *ctx, uint32_t alpha, bool ebwt, unsigned long long *sc, const lime::FlatOut &flat);
+int reserve_score_scratch(lime_ctx *ctx);
+int queue_choose_deferred(lime_ctx *ctx, int slot, uint32_t norm, float beta, uint32_t n, uint64_t cap, int kind);
+int detect_into_ctx(lime_ctx *ctx, uint32_t alpha, unsigned long long host_sc[SC_COUNT]);
+void xchg_release(lime_ctx *ctx);
+int strand_readback(lime_ctx *ctx, int slot);
 // lime_abi_load.cu
 int load_host_narrow(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint8_t *ebwt, uint64_t n);
 void load_release(lime_ctx *ctx);

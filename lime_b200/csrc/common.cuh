@@ -79,24 +79,6 @@ __device__ __forceinline__ unsigned long long lookback_exclusive(unsigned long l
     return excl;
 }
 
-// ---- similarity rows spread over the GPUs of one NVSwitch node (peer memory) -------------------
-// Reads are owned by contiguous ranges of `per` reads; base[k] is owner k's slab ([per][pitch] uint8,
-// its own cudaMalloc, mapped here through CUDA IPC).  Adds go straight to the owner over NVLink.
-constexpr int PEER_MAX = 16;
-struct PeerTable {
-    uint8_t *base[PEER_MAX];
-    uint32_t per;                 // reads per owner
-    uint32_t magic;               // min(floor(2^32 / per), 2^32 - 1)
-};
-// row of global read r in its owner's slab
-__device__ __forceinline__ uint8_t *peer_row(const PeerTable &T, uint64_t pitch, uint32_t r)
-{
-    uint32_t q = __umulhi(r, T.magic);            // quotient or quotient - 1
-    uint32_t rem = r - q * T.per;
-    if (rem >= T.per) { q++; rem -= T.per; }
-    return T.base[q] + (size_t)rem * pitch;
-}
-
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
@@ -132,7 +114,8 @@ enum KernelId {
     KID_K3_COUNT,
     KID_K3_EMIT,
     KID_K3_CLASSIFY,
-    KID_LOAD_WIDEN,
+    KID_X_ROUTE,
+    KID_X_APPLY,
     KID_COUNT
 };
 
@@ -141,19 +124,29 @@ struct Slot {
     uint64_t n_records = 0;
     uint32_t read_begin = 0, n_reads = 0;
     bool valid = false;
+    // filled by a call that did not synchronise: n_records lives in the strand's device state until
+    // lime_classify has read it back; status = nClusters, maxLen, records, updates of that strand
+    bool deferred = false;
+    uint64_t bin_cap = 0;
+    uint64_t status[4] = {0, 0, 0, 0};
+    int kind = 0;                   // deferred: 1 = one GPU (carry proof: sum_t), 2 = exchange (applied_t)
 };
 
 struct ProfEvent { int kid; cudaEvent_t a, b; };
 
-// peer-memory accumulation (lime_abi_peer.cu)
-struct PeerState {
-    bool active = false;
-    int world = 0, rank = 0, n_slabs = 0;
+// multi-GPU exchange of similarity updates (lime_abi_xchg.cu): the rows of a read live on its owner only
+constexpr int XCHG_MAX = 16;
+struct XchgState {
+    bool active = false, loopback = false;
+    int world = 0, rank = 0, n_strands = 0;
+    uint32_t per = 0;                      // reads per owner
     uint64_t rows = 0, pitch = 0;          // per slab
-    uint32_t per = 0;
-    void *own = nullptr;                   // n_slabs slabs, one cudaMalloc
-    void *mapped[PEER_MAX] = {nullptr};    // every owner's allocation in this process (own included)
-    DevBuf tables;                         // PeerTable[n_slabs] on the device (block path)
+    uint64_t flat_cap = 0, inbox_cap = 0;  // records
+    DevBuf slabs;                          // [n_strands][rows][pitch] uint8: the similarity rows of the owned reads
+    DevBuf flat;                           // [flat_cap] records {read, genome << 8 | t} of the strand being scored
+    void *inbox_own = nullptr;             // [n_strands][world][inbox_cap] records, plain cudaMalloc (CUDA IPC)
+    void *inbox_map[XCHG_MAX] = {nullptr}; // every rank's inbox in this process (own included)
+    DevBuf state;                          // device scalars, see lime_abi_xchg.cu
 };
 
 } // namespace lime
@@ -164,17 +157,18 @@ struct lime_ctx {
     std::string err;
 
     // resident strand
-    const uint32_t *d_lcp = nullptr, *d_da = nullptr;
+    const void *d_lcp = nullptr;            // uint32 values, or -- lcp8 -- the bytes min(lcp, 255) of a narrowed load
+    bool lcp8 = false;
+    const uint32_t *d_da = nullptr;
     const uint8_t *d_ebwt = nullptr;
     lime::DevBuf in_lcp, in_da, in_ebwt;
     uint64_t n_own = 0, n_halo = 0, pos_base = 0;
     int is_last = 1;
     uint32_t n_reads = 0, n_refs = 0;
     bool loaded = false;
-    // narrowed lcp transfer (lime_abi_load.cu): alpha_limit is the caller's promise (lime_set_alpha_limit),
-    // lcp_clamped says the resident lcp holds min(lcp, 255)
+    // narrowed lcp transfer (lime_abi_load.cu): alpha_limit is the caller's promise (lime_set_alpha_limit);
+    // such a load leaves min(lcp, 255) as bytes on the device (lcp8) and the kernels read those
     uint32_t alpha_limit = 0;
-    bool lcp_clamped = false;
     lime::DevBuf in_lcp8;
     uint8_t *stage[lime::LIME_STAGE_SLOTS] = {nullptr};
     cudaEvent_t stage_ev[lime::LIME_STAGE_SLOTS] = {nullptr};
@@ -189,6 +183,11 @@ struct lime_ctx {
     // step-1 scratch
     lime::DevBuf tile_state;        // u64 per tile
     lime::DevBuf scalars;           // small block of device scalars (see abi)
+    lime::DevBuf strand_state;      // [LIME_MAXFILES][SS_COUNT] u64: scalars of the strands run without a host sync
+    unsigned long long *strand_host = nullptr;   // page-locked mirror of strand_state
+    uint64_t rec_hint = 0;          // records of the largest strand result seen (sizes the next deferred one)
+    bool sim_clean = false;         // the matrix is known to be all zero (left so by the choose pass)
+    const void *sim_clean_ptr = nullptr; uint64_t sim_clean_bytes = 0;
 
     // similarity accumulator
     lime::DevBuf sim_own;
@@ -207,7 +206,7 @@ struct lime_ctx {
     lime::DevBuf cls_out;           // classify outputs
     uint64_t cls_n = 0; bool cls_n_valid = false;
     lime::DevBuf tax_tables;        // v_corRef + m_corRef on device
-    lime::PeerState peer;
+    lime::XchgState xchg;
 
     // instrumentation
     uint64_t launches = 0;
@@ -220,6 +219,15 @@ struct lime_ctx {
 namespace lime {
 
 // launchers implemented in the kernel translation units; all asynchronous on ctx->stream
+
+// records {read, genome << 8 | t} of similarity updates, appended instead of added when the rows of the
+// matrix live on other GPUs (multi-GPU exchange, lime_abi_xchg.cu / xchg.cu)
+struct FlatOut {
+    uint2 *rec = nullptr;                 // null: updates go into the matrix
+    unsigned long long *count = nullptr;  // slots handed out so far (every slot below it holds a record, t = 0: none)
+    uint64_t cap = 0;                     // slots the list can hold; more -> the host reports LIME_ERR_NOMEM
+};
+
 struct K2Args {
     const lime_cluster *cl;
     uint64_t n_cl;
@@ -240,7 +248,7 @@ struct K2Args {
     unsigned long long *large_next;   // ticket for the block path
     unsigned long long *n_updates;    // statistics
     uint8_t *scratch; uint64_t scratch_per_cta;
-    const PeerTable *peer = nullptr;  // device pointer; non-null: rows live in the owners' slabs
+    FlatOut flat;                     // block path only
 };
 cudaError_t launch_k2_warp(const K2Args &a, bool exact32, cudaStream_t s);
 cudaError_t launch_k2_block(const K2Args &a, bool exact32, cudaStream_t s, int grid);
@@ -250,45 +258,61 @@ cudaError_t launch_k2_narrow(const uint32_t *sim32, uint32_t lo, uint32_t hi, ui
                              uint8_t *sim8, uint64_t pitch8, cudaStream_t s);
 
 // fused steps 1 + 2a (k12_stream.cu)
+constexpr uint32_t K12_ID_LIMIT = 0x07ffffffu;   // the stream kernel packs id | class << 27 | start << 31
+constexpr int K12_FLAT_BLK = 256;                // slots a warp takes from the flat list at a time
+enum { K12_COUNT = 0, K12_DETECT = 1, K12_DIRECT = 2, K12_FLAT = 3 };
 struct K12Args {
-    const uint32_t *lcp, *da;
+    const void *lcp;                  // uint32[n_total], or uint8[n_total] = min(lcp, 255) when lcp8
+    int lcp8;
+    const uint32_t *da;
     const uint8_t *ebwt;              // null in DA-only mode
     uint64_t n_own, n_total, pos_base;
     int is_last;
     uint32_t alpha, n_reads, n_refs;
-    lime_cluster *out;                // EMIT: records in ascending pStart order
+    lime_cluster *out;                // K12_DETECT: records in ascending pStart order
     uint64_t out_cap;
-    unsigned long long *tile_state;   // EMIT: per-chunk cluster counts, turned into record offsets by a scan
+    unsigned long long *tile_state;   // K12_DETECT: per-chunk cluster counts, turned into record offsets by a scan
     unsigned long long *n_clusters;   // device scalars
     unsigned long long *max_len;
     unsigned int *err;                // bit0: halo exhausted
     lime_cluster *long_list;          // clusters the window path does not take
     unsigned long long *long_count;
     uint64_t long_cap;
-    uint8_t *sim8; uint64_t pitch8;   // packed uint8 accumulator
-    uint32_t *sim32; uint32_t lo, hi; // exact 32-bit accumulator for reads [lo, hi)
-    unsigned int *carry;
+    uint8_t *sim8; uint64_t pitch8;   // K12_DIRECT: packed uint8 accumulator, updated with fire-and-forget adds
     unsigned long long *n_updates;
-    unsigned dbg;                     // experiment switches (LIME_DEBUG env), 0 in production
-    // stream kernel: fire-and-forget adds; sum_t receives the total of all t added to the matrix so
-    // that the host can prove the absence of byte carries (bytesum of the matrix == sum_t)
-    unsigned long long *sum_t;        // null: every add inspects the returned word instead
-    // peer mode (multi-GPU): read rows live in the owners' slabs; sim8 is unused
-    int peer_on = 0;
-    uint32_t peer_self = 0, peer_world = 1;
-    PeerTable peer;
-    const PeerTable *peer_dev = nullptr;
+    // total of all t issued, so that the absence of byte carries can be proven (byte sum of the matrix == sum_t)
+    unsigned long long *sum_t;
+    uint2 *flat;                      // K12_FLAT: the record list (FlatOut)
+    unsigned long long *flat_count;
+    uint64_t flat_cap;
 };
-// lime_abi_load.cu: out[i] = in[i] for a chunk of the narrowed lcp (both 16-byte aligned)
-cudaError_t launch_widen(const uint8_t *in, uint32_t *out, uint64_t n, cudaStream_t s);
 cudaError_t launch_bytesum(const uint8_t *p, uint64_t bytes, unsigned long long *out, cudaStream_t s);
-cudaError_t launch_k12(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s);
+cudaError_t launch_k12(const K12Args &a, int what, cudaStream_t s);
 uint64_t k12_num_tiles(uint64_t n_own);
 uint64_t k12s_num_chunks(uint64_t n_own);
 uint64_t k12_long_cap(uint64_t n_total);
 
+// multi-GPU routing of the update records (xchg.cu)
+struct XchgRoute {
+    const uint2 *flat; const unsigned long long *flat_count; uint64_t flat_cap;
+    uint32_t world, per, n_refs;
+    uint2 *dst[XCHG_MAX];             // owner o's inbox region for this source and strand (peer or local memory)
+    uint64_t inbox_cap;
+    unsigned long long *sent;         // [world] device counters (local)
+    unsigned long long *err;
+};
+struct XchgApply {
+    const uint2 *src; uint64_t inbox_cap;
+    const unsigned long long *counts_all;   // [world][world], device
+    uint32_t world, rank;
+    uint8_t *slab; uint64_t pitch; uint32_t rows, n_refs;
+    unsigned long long *applied_t, *applied_n, *err;
+};
+cudaError_t launch_xchg_route(const XchgRoute &a, cudaStream_t s);
+cudaError_t launch_xchg_apply(const XchgApply &a, cudaStream_t s);
+
 struct K3Args {
-    const uint8_t *sim8; uint64_t pitch8;
+    uint8_t *sim8; uint64_t pitch8;
     uint32_t n_refs, read_begin, read_end;
     uint32_t norm; float beta;
     unsigned long long *tile_state;
@@ -297,6 +321,10 @@ struct K3Args {
     uint64_t *pos;                    // [read_end-read_begin]
     lime_pair_sim *bin;               // emit only
     uint64_t bin_cap;                 // single-pass kernel: capacity of bin (writes are guarded)
+    // single-pass kernel, optional: add the byte sum of the rows to *byte_sum (carry proof of the fire-and-forget
+    // adds, one pass over the matrix instead of a separate one) and leave the rows zero for the next strand
+    unsigned long long *byte_sum = nullptr;
+    int zero_after = 0;
 };
 cudaError_t launch_k3_choose(const K3Args &a, cudaStream_t s);
 cudaError_t launch_k3_export(const K3Args &a, cudaStream_t s);
@@ -311,6 +339,10 @@ struct ClsArgs {
     const lime_pair_sim *bin[LIME_MAXFILES];
     const uint64_t *pos[LIME_MAXFILES];
     uint64_t n_records[LIME_MAXFILES];
+    // a strand that was run without a host synchronisation: its record count is still on the device; bin_cap
+    // bounds what may be read there
+    const unsigned long long *n_records_dev[LIME_MAXFILES];
+    uint64_t bin_cap[LIME_MAXFILES];
     uint32_t n_reads, n_refs;
     const uint32_t *v;                // [n_refs]
     const uint32_t *m;                // [6][n_refs] or null

@@ -1,4 +1,4 @@
-// k12_stream.cu -- steps 1 and 2a in ONE pass over lcp / da / ebwt, warp-autonomous version:
+// k12_stream.cu -- steps 1 and 2a in ONE pass over lcp / da / ebwt, warp-autonomous:
 // alpha-cluster detection (ClusterLCP.cpp:139-283) fused with the per-cluster similarity
 // accumulation (clusterAnalyze, ClusterBWT_DA.cpp:256-358).
 //
@@ -8,34 +8,32 @@
 // whose head lies in the first 480 positions (the chunk ownership rule of ClusterLCP.cpp:150-202,
 // the last word is look-ahead) and never synchronises with another warp:
 //
-//   stage    the next chunk of lcp / da / ebwt is copied global -> shared with cp.async while the
-//            current chunk is scored (the warp's only DRAM reads: no load latency on the critical path).
+//   stage    the next chunk of lcp / da / ebwt is copied global -> shared by the TMA engine: ONE lane
+//            issues three bulk copies (cp.async.bulk, UBLKCP in SASS) against the warp's mbarrier while
+//            the current chunk is scored; the warp's only DRAM reads, no load latency on the critical path.
 //   phase A  lane = position inside a word: two ballots per word give the head word (lcp < alpha)
 //            and the read word (da < n_reads); lane k keeps word k.
 //   phase B  lane = word: bit-parallel segmented OR-fills (Kogge-Stone inside the word, the same
-//            routine over the 32 words through ballots) decide which positions lie in a segment
+//            routine over the words through ballots) decide which positions lie in a segment
 //            that holds both a read and a genome: the "active" word.  No per-cluster loop.
 //   phase C  active positions (about a fifth of the input) are compacted from the stage into the
-//            warp's shared-memory stream (id, symbol class | cluster-start flag), word by word.
+//            warp's shared-memory stream, one packed word id | class << 27 | cluster-start << 31 each.
 //   phase D  32-lane windows slide over the stream, one lane per position: equal ids are grouped
 //            with __match_any_sync, symbol classes counted with ballots, every read leader meets
-//            every genome leader of its cluster by shuffle; updates (read, genome, t) are fire-and-forget
-//            adds to the similarity matrix (carries ruled out afterwards, see add_update).
+//            every genome leader of its cluster by shuffle.  An update (read, genome, t) is either
+//              MODE_DIRECT  a fire-and-forget add into the uint8 similarity matrix (one GPU), or
+//              MODE_FLAT    an 8-byte record appended to a flat list in local HBM (multi-GPU: the records
+//                           are routed to the read owner afterwards, xchg.cu).
 //   Clusters longer than 32 positions or running past the look-ahead are rare; they are appended
 //   to a list that the block-path kernel of k2_similarity.cu consumes afterwards.
 //
-// Algorithmic traffic: (8 + E) bytes per position, E = 1 with ebwt; + 16 B per cluster if EMIT.
+// lcp is read as uint32 (the file format, Tools.h:48) or -- template LCP8 -- as the byte min(lcp, 255)
+// a narrowed host load left on the device (lime_set_alpha_limit): the kernel only ever tests lcp < alpha.
+//
+// Algorithmic traffic: (8 + E) bytes per position, E = 1 with ebwt; + 16 B per cluster if records are emitted.
 #include "common.cuh"
 #include "score.cuh"
 #include <algorithm>
-
-// compile-time experiment switches for the next round of tuning (value 1: row address per read leader,
-// 2: arithmetic A/C/G/T classes, 4: packed 32-bit stream element, 8: phase C visits only the non-empty
-// words); 0 in every shipped build -- the SASS
-// of the default build is byte-identical with and without these blocks
-#ifndef LIME_K12_EXP
-#define LIME_K12_EXP 0
-#endif
 
 namespace lime {
 namespace k12s {
@@ -49,6 +47,10 @@ constexpr int OWN = CH - 32;              // owned positions per chunk; one word
 constexpr int NONE = 1 << 30;
 constexpr int MAXFAST = 32;               // longest cluster the window path takes
 constexpr int SCAP = CH + 32;             // stream capacity incl. one window of padding
+constexpr uint32_t ID_MASK = K12_ID_LIMIT;   // packed stream element: id | class << 27 | start << 31
+constexpr int CTAS_PER_SM = 8;
+
+enum { MODE_COUNT = 0, MODE_EMIT = 1, MODE_DIRECT = 2, MODE_FLAT = 3 };
 
 // x_i |= x_{i-1} while c_i (position i continues the run of i-1); Kogge-Stone, 5 steps
 __device__ __forceinline__ uint32_t fill_up(uint32_t x, uint32_t c)
@@ -75,145 +77,149 @@ __device__ __forceinline__ uint32_t mask_lt(int k)   // bits [0, k), k may be <=
     return k <= 0 ? 0u : (k >= 32 ? 0xffffffffu : ((1u << k) - 1u));
 }
 
+template <bool LCP8> struct LcpElem { typedef uint32_t type; };
+template <> struct LcpElem<true> { typedef uint8_t type; };
+
+template <bool LCP8>
 struct alignas(16) WarpSmem {
-    uint32_t lcp[CH];             // stage of the next chunk, filled by cp.async while this one is scored
-                                  // (dead after phase A: phase C keeps its per-word broadcast there)
+    typename LcpElem<LCP8>::type lcp[CH];   // stage of the next chunk, filled by the bulk copies while this one is
+                                            // scored (dead after phase A: phase C keeps its per-word broadcast there)
     uint32_t da[CH];
     uint8_t  eb[CH];
-    uint32_t cid[SCAP];           // compacted document ids
-    uint16_t cmeta[SCAP];         // compacted symbol class | start << 8
+    uint32_t st[SCAP];                      // compacted stream: id | class << 27 | start << 31
 };
-struct Smem {
-    WarpSmem w[WARPS];
-    uint8_t  cls[256];            // symbol -> class
+template <bool LCP8>
+struct alignas(16) Smem {
+    WarpSmem<LCP8> w[WARPS];
+    unsigned long long mbar[WARPS];         // one transaction barrier per warp
+    uint8_t cls[256];                       // symbol -> class
 };
 
-// 16-byte asynchronous global -> shared copy (LDGSTS), L1 bypassed
-__device__ __forceinline__ void cp_async16(unsigned smem_addr, const void *gmem)
+// ---- TMA bulk copy global -> shared against an mbarrier (sm_90+) ---------------------------------------
+__device__ __forceinline__ void mbar_init(unsigned mbar, unsigned count)
 {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gmem) : "memory");
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
 }
-// the same with an L2 eviction policy (createpolicy): the inputs are read once and should not push the
-// similarity matrix out of L2
-__device__ __forceinline__ void cp_async16_hint(unsigned smem_addr, const void *gmem, uint64_t pol)
+__device__ __forceinline__ void fence_mbar_init()
 {
-    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(smem_addr), "l"(gmem), "l"(pol) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
-// 0 evict_normal, 1 evict_first, 2 evict_last, 3 / 4 evict_last for one half / one quarter of the lines
-__device__ __forceinline__ uint64_t l2_policy(int kind)
+// generic-proxy accesses to shared memory issued so far are ordered before later async-proxy (TMA) accesses
+__device__ __forceinline__ void fence_proxy_async_smem()
+{
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned mbar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned bytes, unsigned mbar, uint64_t pol)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(mbar), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "K12_WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra K12_DONE_%=;\n"
+        "bra K12_WAIT_%=;\n"
+        "K12_DONE_%=:\n"
+        "}\n" ::"r"(mbar), "r"(parity) : "memory");
+}
+// L2 eviction policies: the inputs are read once (evict_first) and should not push the similarity matrix,
+// whose lines are re-visited by later adds (evict_last), out of L2: 2.11 -> 1.83 ms per strand in round 1
+__device__ __forceinline__ uint64_t policy_evict_first()
 {
     uint64_t p;
-    if (kind == 1) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
-    else if (kind == 2) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
-    else if (kind == 3) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 0.5;" : "=l"(p));
-    else if (kind == 4) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 0.25;" : "=l"(p));
-    else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_last()
+{
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
     return p;
 }
 __device__ __forceinline__ void red_add_hint(unsigned *addr, unsigned v, uint64_t pol)
 {
     asm volatile("red.relaxed.gpu.global.add.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(addr), "r"(v), "l"(pol) : "memory");
 }
-__device__ __forceinline__ void cp_async_wait_all()
+
+// four consecutive lcp values at position p (p a multiple of 4; buffers are 16-byte aligned), guarded at the end
+template <bool LCP8>
+__device__ __forceinline__ void load4_lcp(const void *base, uint64_t p, uint64_t n_total, uint32_t l[4])
 {
-    asm volatile("cp.async.wait_all;" ::: "memory");
+    if (p + 4 <= n_total) {
+        if (LCP8) {
+            const uint32_t v = __ldg(reinterpret_cast<const uint32_t *>(static_cast<const uint8_t *>(base) + p));
+            l[0] = v & 255u; l[1] = (v >> 8) & 255u; l[2] = (v >> 16) & 255u; l[3] = v >> 24;
+        } else {
+            const uint4 v = ldg128(static_cast<const uint32_t *>(base) + p);
+            l[0] = v.x; l[1] = v.y; l[2] = v.z; l[3] = v.w;
+        }
+    } else {
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const bool ok = p + e < n_total;
+            if (LCP8) l[e] = ok ? (uint32_t)__ldg(static_cast<const uint8_t *>(base) + p + e) : 0xffffffffu;
+            else      l[e] = ok ? __ldg(static_cast<const uint32_t *>(base) + p + e) : 0xffffffffu;
+        }
+    }
 }
 
-// PEER: the rows of the similarity matrix live in their owners' slabs (one GPU per read range, mapped
-// peer memory); every update is a fire-and-forget add that travels over NVLink / NVSwitch to the owner.
-template <bool SCORE, bool EMIT, bool EBWT, bool EXACT32, bool PEER = false>
-__global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constant__ K12Args P)
+template <int MODE, bool EBWT, bool LCP8>
+__global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __grid_constant__ K12Args P)
 {
-    __shared__ Smem sm;
+    constexpr bool SCORE = MODE >= MODE_DIRECT;
+    constexpr bool EMIT = MODE == MODE_EMIT;
+    typedef typename LcpElem<LCP8>::type lcp_t;
+    __shared__ Smem<LCP8> sm;
     const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    if (SCORE) {
+    if (SCORE && EBWT) {
         for (int i = threadIdx.x; i < 256; i += THREADS) sm.cls[i] = d_class_table.v[i];
     }
+    WarpSmem<LCP8> &ws = sm.w[warp];
+    const unsigned mb = (unsigned)__cvta_generic_to_shared(&sm.mbar[warp]);
+    if (lane == 0) { mbar_init(mb, 1u); fence_mbar_init(); }
     __syncthreads();
-    WarpSmem &ws = sm.w[warp];
     const int w = (int)lane;                                  // the word this lane owns in phase B
 
-    const uint64_t n_chunks = (P.n_own + OWN - 1) / OWN;
-    const uint64_t stride = (uint64_t)gridDim.x * WARPS;
+    const uint32_t n_chunks = (uint32_t)((P.n_own + OWN - 1) / OWN);       // < 2^32: checked by the launcher
+    const uint32_t stride = gridDim.x * WARPS;
     unsigned cl_count = 0;                                    // clusters counted by this lane
-    unsigned long long max_len = 0;                           // longest cluster seen by this lane
-    unsigned updates = 0;                                     // updates issued by this lane (a lane sees < 2^32 pairs)
-
-    SimAcc acc;
-    acc.sim8 = P.sim8; acc.pitch8 = P.pitch8; acc.sim32 = P.sim32; acc.lo = P.lo; acc.hi = P.hi;
-    acc.n_refs = P.n_refs; acc.carry = P.carry; acc.sum_t = P.sum_t;
-    acc.peer = PEER ? P.peer_dev : nullptr;
-    // Matrix updates are fire-and-forget adds of t << 8*(g&3) to the 32-bit word that holds the uint8
-    // cell: no return value to wait for.  A carry out of a byte (true cell sum > 255, where the
-    // reference wraps, ClusterBWT_DA.cpp:183,247) lowers the byte sum of the matrix by 255 or 256, so
-    // the host proves their absence afterwards by comparing the byte sum of the matrix with the
-    // total of all t (sum_t) and otherwise reruns the pass into exact 32-bit cells.
-    // L2 policies: the inputs are read once (evict_first), the lines of the similarity matrix should stay
-    // (evict_last); together 4.23 -> 3.67 ms per step on the BASELINE workload.  Experiment switches:
-    // dbg 1024 = inputs evict_normal, 2048 = adds without a policy, 4096 / 8192 = evict_last for 1/2, 1/4 of the lines
-    const uint64_t pol_in = l2_policy((P.dbg & 1024u) ? 0 : 1);
-    const uint64_t pol_mat = l2_policy((P.dbg & 4096u) ? 3 : (P.dbg & 8192u) ? 4 : 2);
-
-    const bool red_mode = P.sum_t != nullptr;
+    unsigned max_len = 0;                                     // longest cluster seen by this lane (open tails apart)
+    unsigned updates = 0;                                     // updates issued by this lane
     unsigned long long t_total = 0;                           // sum of t added by this lane
-    auto add_update = [&](uint32_t r, uint32_t g, uint32_t t) {
-        updates++;
-        if (P.dbg & 2u) return;
-        if (EXACT32) { sim_add<true>(acc, r, g, t); return; }
-        if (PEER) {
-            uint8_t *row = peer_row(P.peer, P.pitch8, r);
-            if (P.dbg & 0x3f0u) {                   // experiments: where do the adds go
-                const uint32_t q = r / P.peer.per;
-                uint32_t rem = r - q * P.peer.per;
-                uint32_t dst = q;
-                if (P.dbg & 16u) dst = P.peer_self;                                  // all local
-                if (P.dbg & 64u) dst = (P.peer_self + 1u) % P.peer_world;            // all to the next rank
-                if (P.dbg & 128u) dst = (P.peer_self + 1u + q % 3u) % P.peer_world;  // three peers
-                if (P.dbg & 256u) rem &= 0x3ffffu;                                   // 28 MB per owner
-                row = P.peer.base[dst] + (size_t)rem * P.pitch8;
-            }
-            red_add_hint(reinterpret_cast<unsigned *>(row) + (g >> 2), t << ((g & 3u) * 8u), pol_mat);
-            t_total += t;
-            return;
-        }
-        if (red_mode) {
-            unsigned *wp = reinterpret_cast<unsigned *>(acc.sim8 + (size_t)r * acc.pitch8) + (g >> 2);
-            if (P.dbg & 2048u) atomicAdd(wp, t << ((g & 3u) * 8u));
-            else red_add_hint(wp, t << ((g & 3u) * 8u), pol_mat);
-            t_total += t;
-            return;
-        }
-        acc.sum_t = nullptr;
-        sim_add<false>(acc, r, g, t);
-    };
+    const lcp_t *g_lcp = static_cast<const lcp_t *>(P.lcp);
+    const uint64_t pol_mat = policy_evict_last();
 
-    // Stage pipeline: the chunk after the current one is copied global -> shared asynchronously
-    // (16 bytes per lane and copy) while the current one is scored; whole chunks only, the tail of
-    // the buffer and unaligned buffers are loaded synchronously.
+    // flat mode: the warp appends its records to blocks of K12_FLAT_BLK slots taken from one global cursor;
+    // a block is filled completely before the next is taken, the last one is padded with null records
+    unsigned long long fl_base = 0;
+    unsigned fl_fill = K12_FLAT_BLK;
+
+    // Stage pipeline: the chunk after the current one is copied global -> shared by three bulk copies
+    // while the current one is scored; whole chunks only, the tail of the buffer and unaligned buffers
+    // are loaded synchronously.
     const bool aligned = ((reinterpret_cast<uintptr_t>(P.lcp) | reinterpret_cast<uintptr_t>(P.da) |
                            (SCORE && EBWT ? reinterpret_cast<uintptr_t>(P.ebwt) : 0)) & 15u) == 0;
-    // per-lane source / destination of its 16-byte pieces (piece k of lcp / da is 512 bytes further)
-    const char *g_lcp = reinterpret_cast<const char *>(P.lcp) + 16 * lane;
-    const char *g_da = reinterpret_cast<const char *>(P.da) + 16 * lane;
-    const char *g_eb = reinterpret_cast<const char *>(P.ebwt) + 16 * lane;
-    const unsigned s_lcp = (unsigned)__cvta_generic_to_shared(&ws.lcp[4 * lane]);
-    const unsigned s_da = (unsigned)__cvta_generic_to_shared(&ws.da[4 * lane]);
-    const unsigned s_eb = (unsigned)__cvta_generic_to_shared(&ws.eb[16 * lane]);
-    auto stage_issue = [&](uint64_t cc) -> bool {
+    constexpr unsigned STAGE_BYTES = CH * sizeof(lcp_t) + CH * 4u + (SCORE && EBWT ? (unsigned)CH : 0u);
+    auto stage_issue = [&](uint32_t cc) -> bool {             // all lanes, after a __syncwarp: the stage is free
         if (cc >= n_chunks) return false;
-        const uint64_t aa = cc * OWN;
+        const uint64_t aa = (uint64_t)cc * OWN;
         if (!aligned || aa + CH > P.n_total) return false;
-        const char *pl = g_lcp + 4 * aa, *pd = g_da + 4 * aa;
-#pragma unroll
-        for (int k = 0; k < CH / 128; k++) {
-            cp_async16_hint(s_lcp + 512 * k, pl + 512 * k, pol_in);
-            cp_async16_hint(s_da + 512 * k, pd + 512 * k, pol_in);
-        }
-        if (SCORE && EBWT) {
-            const char *pe = g_eb + aa;
-#pragma unroll
-            for (int k = 0; k < CH / 512; k++) cp_async16_hint(s_eb + 512 * k, pe + 512 * k, pol_in);
+        if (lane == 0) {
+            const uint64_t pol_in = policy_evict_first();
+            fence_proxy_async_smem();
+            mbar_expect_tx(mb, STAGE_BYTES);
+            bulk_g2s((unsigned)__cvta_generic_to_shared(ws.lcp), g_lcp + aa, CH * sizeof(lcp_t), mb, pol_in);
+            bulk_g2s((unsigned)__cvta_generic_to_shared(ws.da), P.da + aa, CH * 4u, mb, pol_in);
+            if (SCORE && EBWT) bulk_g2s((unsigned)__cvta_generic_to_shared(ws.eb), P.ebwt + aa, CH, mb, pol_in);
         }
         return true;
     };
@@ -221,19 +227,20 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
     const uint32_t V_full = w < WORDS ? 0xffffffffu : 0u;
     const uint32_t XM_full = w < WORDS - 1 ? 0xffffffffu : (w == WORDS - 1 ? 0x7fffffffu : 0u);
     const uint32_t BL_full = mask_lt(OWN - w * 32);
-    const uint64_t c_first = (uint64_t)blockIdx.x * WARPS + warp;
+    const uint32_t c_first = blockIdx.x * WARPS + warp;
     bool staged = stage_issue(c_first);
+    unsigned parity = 0;
 
-    for (uint64_t c = c_first; c < n_chunks; c += stride) {
-        const uint64_t a = c * OWN;                                  // buffer-local start of the chunk
+    for (uint32_t c = c_first; c < n_chunks; c += stride) {
+        const uint64_t a = (uint64_t)c * OWN;                        // buffer-local start of the chunk
         const int Lt = (int)min((uint64_t)OWN, P.n_own - a);         // owned positions
         const int Lext = (int)min((uint64_t)CH, P.n_total - a);      // real positions in the chunk
 
         // ---- phase A: head / read words (lane = position inside a word) ------------------------------
         uint32_t H = 0xffffffffu, R = 0;                             // lanes >= WORDS: beyond the chunk
         if (staged) {
-            cp_async_wait_all();
-            __syncwarp();
+            mbar_wait(mb, parity);
+            parity ^= 1u;
 #pragma unroll
             for (int k = 0; k < WORDS; k++) {
                 const uint32_t l = ws.lcp[32 * k + lane];
@@ -244,12 +251,13 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
             }
         } else {
             // tail of the buffer (or unaligned buffers): guarded loads, da / ebwt put into the stage
-            const uint32_t *pl = P.lcp + a + lane, *pd = P.da + a + lane;
+            const lcp_t *pl = g_lcp + a + lane;
+            const uint32_t *pd = P.da + a + lane;
             const uint8_t *pe = P.ebwt + a + lane;
 #pragma unroll
             for (int k = 0; k < WORDS; k++) {
                 const bool ok = 32 * k + (int)lane < Lext;
-                const uint32_t l = ok ? __ldcs(pl + 32 * k) : 0u;              // virtual head
+                const uint32_t l = ok ? (uint32_t)__ldcs(pl + 32 * k) : 0u;    // virtual head
                 const uint32_t d = ok ? __ldcs(pd + 32 * k) : 0xffffffffu;     // neither read nor real
                 const uint32_t hk = __ballot_sync(FULL, l < P.alpha);
                 const uint32_t rk = __ballot_sync(FULL, d < P.n_reads);
@@ -332,17 +340,13 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
                 }
                 uint32_t l[4], d[4];
                 const uint64_t p = p0 + 4ull * lane;
+                load4_lcp<LCP8>(P.lcp, p, P.n_total, l);
                 if (p + 4 <= P.n_total) {
-                    const uint4 lv = ldg128(P.lcp + p), dv = ldg128(P.da + p);
-                    l[0] = lv.x; l[1] = lv.y; l[2] = lv.z; l[3] = lv.w;
+                    const uint4 dv = ldg128(P.da + p);
                     d[0] = dv.x; d[1] = dv.y; d[2] = dv.z; d[3] = dv.w;
                 } else {
 #pragma unroll
-                    for (int e = 0; e < 4; e++) {
-                        const bool ok = p + e < P.n_total;
-                        l[e] = ok ? __ldg(P.lcp + p + e) : 0xffffffffu;
-                        d[e] = ok ? __ldg(P.da + p + e) : 0u;
-                    }
+                    for (int e = 0; e < 4; e++) d[e] = p + e < P.n_total ? __ldg(P.da + p + e) : 0u;
                 }
                 unsigned hn = 0;
 #pragma unroll
@@ -378,15 +382,14 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
         const bool own_tail = open_tail && tail_mixed && (hl >> 5) == w;
         const unsigned count = __popc(heads) + (own_tail ? 1u : 0u);
         cl_count += count;
-        if (own_tail) max_len = max(max_len, tail_len);
+        if (own_tail) atomicMax(P.max_len, tail_len);                     // rare; may exceed 32 bits
 
-        if (!SCORE && !EMIT) {
+        if (MODE == MODE_COUNT) {
             // counting pass of the two-pass record emission: clusters owned by this chunk
             const unsigned total = __reduce_add_sync(FULL, count);
             if (lane == 0) P.tile_state[c] = total;
             continue;
         }
-        unsigned long long rec_base = 0;
         if (EMIT) {
             unsigned incl = count;
 #pragma unroll
@@ -397,7 +400,7 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
             const unsigned total = __shfl_sync(FULL, incl, 31);
             const unsigned long long e0 = P.tile_state[c];                // exclusive prefix of the counting pass
             if (lane == 0 && c == n_chunks - 1) *P.n_clusters = e0 + total;
-            rec_base = e0 + (incl - count);
+            unsigned long long rec_base = e0 + (incl - count);
             // every owned head: length to the next head, record in ascending pStart order
             uint32_t hb = heads;
             while (hb) {
@@ -406,13 +409,14 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
                 const uint32_t m = H & ~((2u << b) - 1u);              // next head in this word (b < 31 or m == 0)
                 const int j = (b < 31 && m) ? w * 32 + __ffs(m) - 1 : nh_above;
                 const int len = j - (w * 32 + b);
-                max_len = max(max_len, (unsigned long long)len);
+                max_len = max(max_len, (unsigned)len);
                 if (rec_base < P.out_cap)
                     *reinterpret_cast<ulonglong2 *>(&P.out[rec_base]) = make_ulonglong2(P.pos_base + a + w * 32 + b, (unsigned long long)len);
                 rec_base++;
             }
             if (own_tail && rec_base < P.out_cap)
                 *reinterpret_cast<ulonglong2 *>(&P.out[rec_base]) = make_ulonglong2(P.pos_base + a + hl, tail_len);
+            continue;
         }
         if (SCORE) {
             // Only the last head of a word can start a cluster longer than 32 positions (any other has
@@ -429,7 +433,7 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
                 const int src = __ffs(lm) - 1;
                 lm &= lm - 1;
                 const int i = __shfl_sync(FULL, ci0, src), j = __shfl_sync(FULL, nh_above, src);
-                if (!EMIT && w == src) max_len = max(max_len, (unsigned long long)(j - i));
+                if (w == src) max_len = max(max_len, (unsigned)(j - i));
                 if (lane == 0) {
                     const unsigned long long slot = atomicAdd(P.long_count, 1ull);
                     if (slot < P.long_cap)
@@ -443,12 +447,10 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
                     *reinterpret_cast<ulonglong2 *>(&P.long_list[slot]) = make_ulonglong2(P.pos_base + a + hl, tail_len);
             }
         }
-        if (!SCORE) continue;
-        if (P.dbg & 8u) { issue_next(); continue; }
 
         // ---- phase C: compact the active positions into the warp's stream ------------------------------
         // lane = position inside a word again: per word one broadcast of (active, head, offset), the
-        // active lanes copy id / symbol / start flag from the stage; words without active positions
+        // active lanes copy id / symbol class / start flag from the stage; words without active positions
         // are skipped (warp-uniform)
         int n_act;
         {
@@ -464,74 +466,36 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
             if (w < WORDS) info[w] = make_uint4(Aw, H, incl - cnt, 0u);
             __syncwarp();
             if (n_act) {
-#if LIME_K12_EXP & 8
-                // experiment (not built by default): visit only the words that hold active positions
-                for (unsigned nzw = __ballot_sync(FULL, w < WORDS && Aw != 0u); nzw; nzw &= nzw - 1u) {
-                    const int k = __ffs(nzw) - 1;
-                    const uint4 inf = info[k];
-#else
 #pragma unroll
                 for (int k = 0; k < WORDS; k++) {
                     const uint4 inf = info[k];
                     if (inf.x == 0u) continue;
-#endif
                     if ((inf.x >> lane) & 1u) {
                         const uint32_t o = inf.z + __popc(inf.x & lt_mask);
-#if !(LIME_K12_EXP & 4)
-                        ws.cid[o] = ws.da[32 * k + lane];
-#endif
-#if LIME_K12_EXP & 2
-                        // experiment (not built by default): A,C,G,T mapped arithmetically, the table only for the rest
-                        uint32_t cl0 = 0u;
-                        if (EBWT) {
-                            const uint32_t sy = ws.eb[32 * k + lane], d = sy - 0x41u;
-                            const uint32_t x = (sy >> 1) & 3u;
-                            cl0 = (d < 20u && ((0x80045u >> d) & 1u)) ? (x ^ (x >> 1)) : (uint32_t)sm.cls[sy];
-                        }
-#else
                         const uint32_t cl0 = EBWT ? (uint32_t)sm.cls[ws.eb[32 * k + lane]] : 0u;
-#endif
-#if LIME_K12_EXP & 4
-                        // experiment (not built by default): one packed element id | class << 27 | start << 31
-                        // (ids < 2^27 - 1, checked by the launcher): one store here, one load in phase D
-                        ws.cid[o] = ws.da[32 * k + lane] | (cl0 << 27) | (((inf.y >> lane) & 1u) << 31);
-#else
-                        ws.cmeta[o] = (uint16_t)(cl0 | (((inf.y >> lane) & 1u) << 8));
-#endif
+                        ws.st[o] = ws.da[32 * k + lane] | (cl0 << 27) | (((inf.y >> lane) & 1u) << 31);
                     }
                 }
             }
         }
         issue_next();                                                     // includes the __syncwarp
         if (n_act == 0) continue;                                         // warp-uniform
-        ws.cid[n_act + lane] = 0xffffffffu;                               // one window of padding: lone starts
-#if !(LIME_K12_EXP & 4)
-        ws.cmeta[n_act + lane] = 0x100u;
-#endif
+        ws.st[n_act + lane] = 0xffffffffu;                                // one window of padding: lone starts
         __syncwarp();
-        if (P.dbg & 4u) continue;
 
         // ---- phase D: score the clusters of the stream, 32-lane windows --------------------------------
         unsigned longest = 0;                                             // warp-uniform
+        unsigned t_chunk = 0;                                             // sum of t of this lane in this chunk
         for (int i = 0; i < n_act;) {
-#if LIME_K12_EXP & 4
-            const uint32_t pk = ws.cid[i + lane];
-            uint32_t id = pk & 0x07ffffffu;
-            if (id == 0x07ffffffu) id = 0xffffffffu;                      // padding
-            const uint32_t meta = ((pk >> 27) & 15u) | ((pk >> 31) << 8);
-#define K12_NEXT_IS_START ((ws.cid[i + 32] >> 31) != 0u)
-#else
-            uint32_t id = ws.cid[i + lane];
-            const uint32_t meta = ws.cmeta[i + lane];
-#define K12_NEXT_IS_START (ws.cmeta[i + 32] & 0x100u)
-#endif
-            uint32_t sb = __ballot_sync(FULL, (meta & 0x100u) != 0);      // bit 0 is set: i is a start
-            if (!K12_NEXT_IS_START) {
+            const uint32_t pk = ws.st[i + lane];
+            uint32_t id = pk & ID_MASK;                                   // ID_MASK itself: padding
+            uint32_t sb = __ballot_sync(FULL, (pk >> 31) != 0u);          // bit 0 is set: i is a start
+            if (!(ws.st[i + 32] >> 31)) {
                 // the last cluster of the window is cut: leave it to the next window (turn its lanes
                 // into lone starts; a cluster has at most 32 positions, so it does not start at lane 0)
                 const int ls = 31 - __clz(sb);
                 sb |= 0xffffffffu << ls;
-                if ((int)lane >= ls) id = 0xffffffffu;
+                if ((int)lane >= ls) id = ID_MASK;
                 i += ls;
             } else {
                 i += 32;
@@ -552,15 +516,15 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
             if (!EBWT) {
                 vec.x = (unsigned)__popc(mm);
             } else {
-                const uint32_t cls = meta & 0xffu;
+                const uint32_t cls = (pk >> 27) & 15u;
+                const bool real = id != ID_MASK;
                 const unsigned c0 = __ballot_sync(FULL, (cls & 1u) != 0), c1 = __ballot_sync(FULL, (cls & 2u) != 0);
-                const unsigned rest = __ballot_sync(FULL, cls >= 4u && id != 0xffffffffu);
+                const unsigned rest = __ballot_sync(FULL, cls >= 4u && real);
                 vec.x = (unsigned)__popc(mm & ~c1 & ~c0) | ((unsigned)__popc(mm & ~c1 & c0) << 8) |
                         ((unsigned)__popc(mm & c1 & ~c0) << 16) | ((unsigned)__popc(mm & c1 & c0) << 24);
                 wide = rest != 0;                                              // a class beyond A,C,G,T
                 if (wide) {
                     // exact per-class counts for every class present in the window
-                    const bool real = id != 0xffffffffu;
                     unsigned present = __reduce_or_sync(FULL, real ? (1u << cls) : 0u);
                     iupac = (present & 0x7ff0u) != 0;
                     vec = make_uint4(0, 0, 0, 0);
@@ -579,14 +543,13 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
             // every read leader against every genome leader of its cluster
             unsigned gl = __ballot_sync(FULL, leader && !is_read) & cm;
             if (!(leader && is_read)) gl = 0;
-#if LIME_K12_EXP & 1
-            // experiment (not built by default): the row address once per read leader instead of once per pair
-            unsigned *row_w = reinterpret_cast<unsigned *>(acc.sim8 + (size_t)(gl ? id : 0u) * acc.pitch8);
-#endif
+            // the row of a read leader, once per window
+            unsigned *row_w = nullptr;
+            if (MODE == MODE_DIRECT) row_w = reinterpret_cast<unsigned *>(P.sim8 + (size_t)(gl ? id : 0u) * P.pitch8);
             while (__any_sync(FULL, gl != 0)) {
                 const int src = gl ? 31 - __clz(gl) : 0;
                 const uint32_t Gx = __shfl_sync(FULL, vec.x, src);
-                const uint32_t gid = __shfl_sync(FULL, id, src);
+                const uint32_t g = __shfl_sync(FULL, id, src) - P.n_reads;
                 uint32_t t;
                 if (!EBWT) t = min(vec.x, Gx);
                 else if (!wide) t = score_acgt(vec.x, Gx);
@@ -599,26 +562,53 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
                 }
                 if (gl == 0) t = 0;
                 else gl ^= 1u << src;
-#if LIME_K12_EXP & 1
-                if (t) {
-                    if (!PEER && !EXACT32 && red_mode && !(P.dbg & 0x802u)) {
-                        const uint32_t g = gid - P.n_reads;
-                        updates++;
+                if (MODE == MODE_DIRECT) {
+                    // Fire-and-forget add of t << 8*(g&3) on the 32-bit word that holds the uint8 cell: no
+                    // return value to wait for.  A carry out of a byte (true cell sum > 255, where the
+                    // reference wraps, ClusterBWT_DA.cpp:183,247) lowers the byte sum of the matrix by 255
+                    // or 256, so the host proves their absence afterwards by comparing the byte sum of the
+                    // matrix with the total of all t (sum_t) and otherwise redoes the strand exactly.
+                    if (t) {
                         red_add_hint(row_w + (g >> 2), t << ((g & 3u) * 8u), pol_mat);
-                        t_total += t;
-                    } else add_update(id, gid - P.n_reads, t);
+                        updates++;
+                        t_chunk += t;
+                    }
+                } else {
+                    // MODE_FLAT: record {read, genome << 8 | t} appended to the warp's current block
+                    const unsigned m = __ballot_sync(FULL, t != 0u);
+                    if (m) {                                                  // warp-uniform
+                        const unsigned n = (unsigned)__popc(m);
+                        const bool spill = fl_fill + n > (unsigned)K12_FLAT_BLK;
+                        unsigned long long nb = 0;
+                        if (spill) {
+                            if (lane == 0) nb = atomicAdd(P.flat_count, (unsigned long long)K12_FLAT_BLK);
+                            nb = __shfl_sync(FULL, nb, 0);
+                        }
+                        const unsigned idx = fl_fill + (unsigned)__popc(m & lt_mask);
+                        const unsigned long long dst = idx < (unsigned)K12_FLAT_BLK ? fl_base + idx : nb + (idx - K12_FLAT_BLK);
+                        if (t) {
+                            if (dst < P.flat_cap) P.flat[dst] = make_uint2(id, (g << 8) | t);
+                            updates++;
+                            t_chunk += t;
+                        }
+                        if (spill) { fl_base = nb; fl_fill = fl_fill + n - K12_FLAT_BLK; }
+                        else fl_fill += n;
+                    }
                 }
-#else
-                if (t) add_update(id, gid - P.n_reads, t);
-#endif
             }
         }
-        max_len = max(max_len, (unsigned long long)longest);
+        max_len = max(max_len, longest);
+        t_total += t_chunk;
+    }
+    if (MODE == MODE_FLAT && fl_fill < (unsigned)K12_FLAT_BLK) {
+        // null records (t = 0) up to the end of the warp's last block: every slot below flat_count is defined
+        for (unsigned i = fl_fill + lane; i < (unsigned)K12_FLAT_BLK; i += 32)
+            if (fl_base + i < P.flat_cap) P.flat[fl_base + i] = make_uint2(0xffffffffu, 0u);
     }
     // ---- totals of this warp: one atomic per warp and scalar -------------------------------------------
     {
-        unsigned c2 = cl_count;
-        unsigned long long mx = max_len, up = updates, tt = t_total;
+        unsigned c2 = cl_count, mx = max_len;
+        unsigned long long up = updates, tt = t_total;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             c2 += __shfl_xor_sync(FULL, c2, o);
@@ -626,9 +616,9 @@ __global__ void __launch_bounds__(THREADS, 7) stream_kernel(const __grid_constan
             up += __shfl_xor_sync(FULL, up, o);
             tt += __shfl_xor_sync(FULL, tt, o);
         }
-        if (lane == 0 && !(P.dbg & 1u)) {
+        if (lane == 0) {
             if (!EMIT && c2) atomicAdd(P.n_clusters, (unsigned long long)c2);
-            if (mx) atomicMax(P.max_len, mx);
+            if (mx) atomicMax(P.max_len, (unsigned long long)mx);
             if (SCORE && up) atomicAdd(P.n_updates, up);
             if (SCORE && tt) atomicAdd(P.sum_t, tt);
         }
@@ -657,46 +647,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) chunk_scan_kernel(unsigned long 
     if (threadIdx.x == SCAN_THREADS - 1 && total) *total = part[threadIdx.x];
 }
 
-// ---- byte sum of the matrix (carry check of the fire-and-forget adds) -------------------------------
-constexpr int SUM_THREADS = 256;
-__global__ void __launch_bounds__(SUM_THREADS) bytesum_kernel(const uint4 *p, uint64_t n16, unsigned long long *out)
-{
-    unsigned acc4 = 0;                                          // <= 2^32 / 1020 vectors per thread
-    unsigned long long total = 0;
-    for (uint64_t i = (uint64_t)blockIdx.x * SUM_THREADS + threadIdx.x; i < n16; i += (uint64_t)gridDim.x * SUM_THREADS) {
-        const uint4 v = __ldcs(p + i);
-        acc4 = __dp4a(v.x, 0x01010101u, acc4); acc4 = __dp4a(v.y, 0x01010101u, acc4);
-        acc4 = __dp4a(v.z, 0x01010101u, acc4); acc4 = __dp4a(v.w, 0x01010101u, acc4);
-        if (acc4 > 0xf0000000u) { total += acc4; acc4 = 0; }
-    }
-    total += acc4;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(FULL, total, o);
-    __shared__ unsigned long long part[SUM_THREADS / 32];
-    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = total;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned long long t = 0;
-        for (int k = 0; k < SUM_THREADS / 32; k++) t += part[k];
-        if (t) atomicAdd(out, t);
-    }
-}
-
 } // namespace k12s
-
-// bytes must be a multiple of 16 and p 16-byte aligned (the matrix pitch is)
-cudaError_t launch_bytesum(const uint8_t *p, uint64_t bytes, unsigned long long *out, cudaStream_t s)
-{
-    const uint64_t n16 = bytes / 16;
-    if (!n16) return cudaSuccess;
-    const unsigned grid = (unsigned)std::min<uint64_t>((n16 + k12s::SUM_THREADS - 1) / k12s::SUM_THREADS, 148ull * 16);
-    k12s::bytesum_kernel<<<grid, k12s::SUM_THREADS, 0, s>>>(reinterpret_cast<const uint4 *>(p), n16, out);
-    return cudaGetLastError();
-}
 
 uint64_t k12s_num_chunks(uint64_t n_own) { return (n_own + k12s::OWN - 1) / k12s::OWN; }
 
-template <bool SC, bool EM, bool EB, bool EX, bool PE = false>
+template <int MODE, bool EB, bool L8>
 static unsigned grid_of(uint64_t n_own)
 {
     static int ctas_per_sm = 0, sms = 0;
@@ -704,7 +659,7 @@ static unsigned grid_of(uint64_t n_own)
         int dev = 0;
         if (cudaGetDevice(&dev) != cudaSuccess) return 0;
         if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, k12s::stream_kernel<SC, EM, EB, EX, PE>, k12s::THREADS, 0) != cudaSuccess) return 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, k12s::stream_kernel<MODE, EB, L8>, k12s::THREADS, 0) != cudaSuccess) return 0;
         if (ctas_per_sm < 1) ctas_per_sm = 1;
     }
     const uint64_t chunks = k12s_num_chunks(n_own);
@@ -712,62 +667,58 @@ static unsigned grid_of(uint64_t n_own)
     return (unsigned)std::min<uint64_t>(want, (uint64_t)sms * ctas_per_sm);
 }
 
-template <bool SC, bool EM, bool EB, bool EX, bool PE = false>
+template <int MODE, bool EB, bool L8>
 static cudaError_t launch_variant(const K12Args &a, cudaStream_t s)
 {
     // persistent grid, warps stride over chunks
-    const unsigned grid = grid_of<SC, EM, EB, EX, PE>(a.n_own);
+    const unsigned grid = grid_of<MODE, EB, L8>(a.n_own);
     if (!grid) return cudaErrorUnknown;
-    k12s::stream_kernel<SC, EM, EB, EX, PE><<<grid, k12s::THREADS, 0, s>>>(a);
+    k12s::stream_kernel<MODE, EB, L8><<<grid, k12s::THREADS, 0, s>>>(a);
     return cudaGetLastError();
 }
 
-#define LIME_K12S_DISPATCH(CALL)                                                              \
-    if (!score)                        return emit ? CALL(false, true, false, false) : CALL(false, false, false, false); \
-    if (emit) {                                                                               \
-        if (ebwt && !exact32)          return CALL(true, true, true, false);                 \
-        if (ebwt && exact32)           return CALL(true, true, true, true);                  \
-        if (!ebwt && !exact32)         return CALL(true, true, false, false);                \
-        return CALL(true, true, false, true);                                                 \
-    }                                                                                         \
-    if (ebwt && !exact32)              return CALL(true, false, true, false);                \
-    if (ebwt && exact32)               return CALL(true, false, true, true);                 \
-    if (!ebwt && !exact32)             return CALL(true, false, false, false);               \
-    return CALL(true, false, false, true);
+template <int MODE, bool EB>
+static cudaError_t launch_lcp(const K12Args &a, cudaStream_t s)
+{
+    return a.lcp8 ? launch_variant<MODE, EB, true>(a, s) : launch_variant<MODE, EB, false>(a, s);
+}
 
-// per-chunk cluster counts / record offsets (EMIT) are per chunk; the long-cluster list holds at most one record per
+// per-chunk cluster counts / record offsets are per chunk; the long-cluster list holds at most one record per
 // 33 positions plus one open tail per chunk
 uint64_t k12_num_tiles(uint64_t n_own) { return k12s_num_chunks(n_own); }
 uint64_t k12_long_cap(uint64_t n_total) { return n_total / (k12s::MAXFAST + 1) + k12_num_tiles(n_total) + 16; }
 
-// Records (.clrs) are emitted in two passes: a counting pass (phases A + B only) leaves the number of
-// clusters of every chunk in tile_state, an exclusive scan turns it into record offsets, and the
-// emitting pass (with or without scoring) reads its offset there -- no look-back between warps.
-cudaError_t launch_k12(const K12Args &a, bool score, bool emit, bool exact32, cudaStream_t s)
+// what: K12_DETECT  records (.clrs) in two passes: a counting pass (phases A + B only) leaves the number of
+//                   clusters of every chunk in tile_state, an exclusive scan turns it into record offsets,
+//                   the emitting pass reads its offset there -- no look-back between warps;
+//       K12_COUNT   nClusters / maxLen only (the counting pass alone);
+//       K12_DIRECT / K12_FLAT  score, see the head of this file.
+cudaError_t launch_k12(const K12Args &a, int what, cudaStream_t s)
 {
     if (a.n_own == 0) return cudaSuccess;
-#if LIME_K12_EXP & 4
-    if ((uint64_t)a.n_reads + a.n_refs >= 0x07ffffffull) return cudaErrorInvalidValue;   // packed stream elements
-#endif
-    if (a.peer_on) {
-        // multi-GPU peer mode: scoring only, fire-and-forget adds into the owners' slabs
-        if (!score || emit || exact32 || !a.sum_t) return cudaErrorInvalidValue;
-        return a.ebwt ? launch_variant<true, false, true, false, true>(a, s)
-                      : launch_variant<true, false, false, false, true>(a, s);
-    }
-    if (emit) {
-        cudaError_t e = launch_variant<false, false, false, false>(a, s);
+    if (k12s_num_chunks(a.n_own) >= 0xffffffffull) return cudaErrorInvalidValue;
+    if (a.lcp8 && a.alpha > 255) return cudaErrorInvalidValue;
+    if (what == K12_COUNT) return launch_lcp<k12s::MODE_COUNT, false>(a, s);
+    if (what == K12_DETECT) {
+        cudaError_t e = launch_lcp<k12s::MODE_COUNT, false>(a, s);
         if (e != cudaSuccess) return e;
         k12s::chunk_scan_kernel<<<1, k12s::SCAN_THREADS, 0, s>>>(a.tile_state, k12s_num_chunks(a.n_own), nullptr);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
-        e = cudaMemsetAsync(a.n_clusters, 0, sizeof(unsigned long long), s);      // the counting pass added its total
+        // the counting pass added its totals: the emitting pass writes nClusters itself and finds the same maxLen
+        e = cudaMemsetAsync(a.n_clusters, 0, sizeof(unsigned long long), s);
         if (e != cudaSuccess) return e;
+        return launch_lcp<k12s::MODE_EMIT, false>(a, s);
     }
+    // packed stream elements: ids below K12_ID_LIMIT (the ABI routes larger collections through the cluster list)
+    if ((uint64_t)a.n_reads + a.n_refs >= K12_ID_LIMIT) return cudaErrorInvalidValue;
     const bool ebwt = a.ebwt != nullptr;
-#define LIME_LV(SC, EM, EB, EX) launch_variant<SC, EM, EB, EX>(a, s)
-    LIME_K12S_DISPATCH(LIME_LV)
-#undef LIME_LV
+    if (what == K12_DIRECT) return ebwt ? launch_lcp<k12s::MODE_DIRECT, true>(a, s) : launch_lcp<k12s::MODE_DIRECT, false>(a, s);
+    if (what == K12_FLAT) {
+        if (a.n_refs >= (1u << 24)) return cudaErrorInvalidValue;        // record = genome << 8 | t
+        return ebwt ? launch_lcp<k12s::MODE_FLAT, true>(a, s) : launch_lcp<k12s::MODE_FLAT, false>(a, s);
+    }
+    return cudaErrorInvalidValue;
 }
 
 } // namespace lime

@@ -27,8 +27,21 @@ __device__ __forceinline__ void sim_add(const K2Args &P, uint32_t r, uint32_t g,
 {
     SimAcc acc;
     acc.sim8 = P.sim8; acc.pitch8 = P.pitch8; acc.sim32 = P.sim32; acc.lo = P.lo; acc.hi = P.hi;
-    acc.n_refs = P.n_refs; acc.carry = P.carry; acc.sum_t = P.sum_t; acc.peer = P.peer;
+    acc.n_refs = P.n_refs; acc.carry = P.carry; acc.sum_t = P.sum_t;
     lime::sim_add<EXACT32>(acc, r, g, t);
+}
+
+// multi-GPU: the update leaves as a record {read, genome << 8 | t} (FlatOut); the lanes of the warp that are
+// here together take their slots with one atomic
+__device__ __forceinline__ void flat_append(const FlatOut &F, uint32_t r, uint32_t g, uint32_t t)
+{
+    const unsigned m = __activemask();
+    const unsigned lane = lane_id();
+    const int leader = __ffs(m) - 1;
+    unsigned long long base = 0;
+    if ((int)lane == leader) base = atomicAdd(F.count, (unsigned long long)__popc(m));
+    base = __shfl_sync(m, base, leader) + __popc(m & ((1u << lane) - 1u));
+    if (base < F.cap) F.rec[base] = make_uint2(r, (g << 8) | t);
 }
 
 // ---- warp path: clusters of <= 32 positions ---------------------------------------------------
@@ -252,7 +265,12 @@ __global__ void __launch_bounds__(BLOCK_THREADS) block_kernel(K2Args P)
                 const uint32_t hg = __ldcg(&glist[gi]);
                 const uint4 G = __ldcg(reinterpret_cast<const uint4 *>(&cnt[(size_t)hg * 8]));
                 const uint32_t t = (iupac ? score_iupac(R, G) : score_plain(R, G)) & 0xffu;
-                if (t) { sim_add<EXACT32>(P, r, __ldcg(&keys[hg]) - P.n_reads, t); updates++; }
+                if (t) {
+                    const uint32_t g = __ldcg(&keys[hg]) - P.n_reads;
+                    if (P.flat.rec) flat_append(P.flat, r, g, t);
+                    else sim_add<EXACT32>(P, r, g, t);
+                    updates++;
+                }
             }
         }
         __syncthreads();

@@ -166,9 +166,30 @@ __global__ void import_kernel(const lime_pair_sim *tr, uint64_t n, uint8_t *sim8
 // Used when an upper bound of the record count is known beforehand (1 + reads + similarity updates),
 // so the record buffer can be sized without a counting pass.  A row is read once from HBM; the emit
 // step re-reads the CTA's 256 rows from L1/L2.  LPR lanes share a row (16 bytes per lane and step).
+__device__ __forceinline__ uint32_t sum_bytes(const uint4 &v, uint32_t acc)
+{
+    acc = __dp4a(v.x, 0x01010101u, acc); acc = __dp4a(v.y, 0x01010101u, acc);
+    acc = __dp4a(v.z, 0x01010101u, acc); acc = __dp4a(v.w, 0x01010101u, acc);
+    return acc;
+}
+// one atomic per CTA for the byte sum of the rows it read (carry proof of the fire-and-forget adds)
+__device__ __forceinline__ void publish_byte_sum(unsigned long long *out, uint32_t mine, unsigned long long *s_part)
+{
+    unsigned long long v = mine;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long t = 0;
+        for (int k = 0; k < WARPS; k++) t += s_part[k];
+        if (t) atomicAdd(out, t);
+    }
+}
+
 template <int LPR>
 __device__ __forceinline__ void row_stats(const uint8_t *row, uint32_t chunks, unsigned sub, bool on,
-                                          uint32_t &mx, uint32_t &nnz)
+                                          uint32_t &mx, uint32_t &nnz, uint32_t &bsum)
 {
     uint32_t m = 0;
     nnz = 0;
@@ -177,6 +198,7 @@ __device__ __forceinline__ void row_stats(const uint8_t *row, uint32_t chunks, u
             const uint4 v = __ldg(reinterpret_cast<const uint4 *>(row) + c);
             m = __vmaxu4(__vmaxu4(m, v.x), __vmaxu4(__vmaxu4(v.y, v.z), v.w));
             nnz += __popc(nz_bytes(v.x)) + __popc(nz_bytes(v.y)) + __popc(nz_bytes(v.z)) + __popc(nz_bytes(v.w));
+            bsum = sum_bytes(v, bsum);
         }
     }
     __syncwarp();
@@ -199,6 +221,7 @@ __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
     __shared__ uint32_t s_cnt[TILE_READS];
     __shared__ uint32_t s_off[TILE_READS];
     __shared__ uint32_t s_warp_sum[WARPS];
+    __shared__ unsigned long long s_part[WARPS];
     __shared__ unsigned s_tile;
     __shared__ unsigned long long s_excl;
     const int tid = threadIdx.x;
@@ -212,12 +235,13 @@ __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
     const uint32_t chunks = (uint32_t)(P.pitch8 / 16);
     const float normf = (float)P.norm;
     if (!TRIPLES && tile == 0 && tid == 0 && P.bin_cap) { P.bin[0].sim = 0.0f; P.bin[0].idRef = 0; }   // sentinel (:376-382)
+    uint32_t bsum = 0;                                // byte sum of the cells this thread read (< 2^32: <= 2 MB per thread)
 
     // ---- count ----
     for (int k = 0; k < ROWS_PER_WARP; k += RPW) {
         const uint32_t lr = r0 + warp * ROWS_PER_WARP + k + grp;
         uint32_t mx = 0, nnz = 0;
-        row_stats<LPR>(P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8, chunks, sub, lr < n, mx, nnz);
+        row_stats<LPR>(P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8, chunks, sub, lr < n, mx, nnz, bsum);
         if (sub == 0) {
             const float ns = __fdiv_rn((float)mx, normf);
             const bool pass = TRIPLES ? (nnz != 0) : (ns > P.beta);
@@ -262,13 +286,19 @@ __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
         const uint32_t lr = r0 + slot;
         const uint32_t cnt = s_cnt[slot];
         const bool on = lr < n && cnt != 0;
-        const uint8_t *row = P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8;
+        uint8_t *row = P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8;
         const unsigned long long o = tile_base + s_off[slot];
         uint32_t mx = 0, written = 0;
+        if (!P.zero_after && !__any_sync(FULL, on)) continue;
         for (uint32_t c0 = 0; c0 < chunks; c0 += LPR) {
             const uint32_t ch = c0 + sub;
             uint4 v = make_uint4(0, 0, 0, 0);
-            if (on && ch < chunks) v = __ldg(reinterpret_cast<const uint4 *>(row) + ch);
+            if ((on || (P.zero_after && lr < n)) && ch < chunks) {
+                v = *(reinterpret_cast<const uint4 *>(row) + ch);
+                // leave the matrix zero for the next strand (only the 16-byte pieces that hold something)
+                if (P.zero_after && (v.x | v.y | v.z | v.w)) *(reinterpret_cast<uint4 *>(row) + ch) = make_uint4(0, 0, 0, 0);
+                if (!on) v = make_uint4(0, 0, 0, 0);
+            }
             const uint32_t wv[4] = {v.x, v.y, v.z, v.w};
             uint32_t mine = 0;
 #pragma unroll
@@ -315,6 +345,7 @@ __global__ void __launch_bounds__(THREADS) choose_kernel(K3Args P)
             P.bin[o] = h;
         }
     }
+    if (P.byte_sum) publish_byte_sum(P.byte_sum, bsum, s_part);
 }
 
 // ---- single pass for rows of at most 128 bytes (n_refs <= 128): sparse-aware ----------------------
@@ -343,6 +374,7 @@ __global__ void __launch_bounds__(THREADS) choose_sparse_kernel(K3Args P)
     __shared__ uint32_t s_off[TILE_READS];
     __shared__ uint32_t s_max[TILE_READS];
     __shared__ uint32_t s_warp_sum[WARPS];
+    __shared__ unsigned long long s_part[WARPS];
     __shared__ unsigned s_tile;
     __shared__ unsigned long long s_excl;
     const int tid = threadIdx.x;
@@ -368,8 +400,18 @@ __global__ void __launch_bounds__(THREADS) choose_sparse_kernel(K3Args P)
             if (lr < n && sub < chunks)
                 held[st] = __ldcs(reinterpret_cast<const uint4 *>(P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8) + sub);
         }
+        uint32_t bsum = 0;
 #pragma unroll
-        for (int st = 0; st < STEPS; st++) s_rows[(warp * ROWS_PER_WARP + st * RPW + grp) * LPR + sub] = held[st];
+        for (int st = 0; st < STEPS; st++) {
+            s_rows[(warp * ROWS_PER_WARP + st * RPW + grp) * LPR + sub] = held[st];
+            bsum = sum_bytes(held[st], bsum);
+            // leave the matrix zero for the next strand (only the 16-byte pieces that hold something)
+            if (P.zero_after && (held[st].x | held[st].y | held[st].z | held[st].w)) {
+                const uint32_t lr = r0 + warp * ROWS_PER_WARP + st * RPW + grp;
+                *(reinterpret_cast<uint4 *>(P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8) + sub) = make_uint4(0, 0, 0, 0);
+            }
+        }
+        if (P.byte_sum) publish_byte_sum(P.byte_sum, bsum, s_part);     // every thread of the CTA gets here
         __syncwarp();
     }
     // ---- count ----
@@ -527,7 +569,40 @@ __global__ void __launch_bounds__(THREADS) export_kernel(K3Args P)
     }
 }
 
+// ---- byte sum of the matrix (carry check of the fire-and-forget adds when no choose pass follows) -------
+constexpr int SUM_THREADS = 256;
+__global__ void __launch_bounds__(SUM_THREADS) bytesum_kernel(const uint4 *p, uint64_t n16, unsigned long long *out)
+{
+    unsigned acc4 = 0;                                          // <= 2^32 / 1020 vectors per thread
+    unsigned long long total = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * SUM_THREADS + threadIdx.x; i < n16; i += (uint64_t)gridDim.x * SUM_THREADS) {
+        acc4 = sum_bytes(__ldcs(p + i), acc4);
+        if (acc4 > 0xf0000000u) { total += acc4; acc4 = 0; }
+    }
+    total += acc4;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(FULL, total, o);
+    __shared__ unsigned long long part[SUM_THREADS / 32];
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = total;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long t = 0;
+        for (int k = 0; k < SUM_THREADS / 32; k++) t += part[k];
+        if (t) atomicAdd(out, t);
+    }
+}
+
 } // namespace k3
+
+// bytes must be a multiple of 16 and p 16-byte aligned (the matrix pitch is)
+cudaError_t launch_bytesum(const uint8_t *p, uint64_t bytes, unsigned long long *out, cudaStream_t s)
+{
+    const uint64_t n16 = bytes / 16;
+    if (!n16) return cudaSuccess;
+    const unsigned grid = (unsigned)std::min<uint64_t>((n16 + k3::SUM_THREADS - 1) / k3::SUM_THREADS, 148ull * 16);
+    k3::bytesum_kernel<<<grid, k3::SUM_THREADS, 0, s>>>(reinterpret_cast<const uint4 *>(p), n16, out);
+    return cudaGetLastError();
+}
 
 uint64_t k3_num_tiles(uint32_t n_reads) { return ((uint64_t)n_reads + k3::TILE_READS - 1) / k3::TILE_READS; }
 

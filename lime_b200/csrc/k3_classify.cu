@@ -103,11 +103,12 @@ __global__ void __launch_bounds__(128) classify_kernel(ClsArgs P)
 #pragma unroll
     for (int i = 0; i < NF; i++) {
         const uint64_t p = P.pos[i][r];
+        const uint64_t n_rec = P.n_records_dev[i] ? min((uint64_t)*P.n_records_dev[i], P.bin_cap[i]) : P.n_records[i];
         if (p) {
-            if (p >= P.n_records[i]) { bad = 1; R.mx[i] = 0.0f; R.size[i] = 0; R.e[i] = nullptr; continue; }
+            if (p >= n_rec) { bad = 1; R.mx[i] = 0.0f; R.size[i] = 0; R.e[i] = nullptr; continue; }
             const lime_pair_sim h = P.bin[i][p];
             R.mx[i] = h.sim; R.size[i] = h.idRef; R.e[i] = P.bin[i] + p + 1;
-            if (p + 1 + h.idRef > P.n_records[i]) { bad = 1; R.size[i] = 0; }
+            if (p + 1 + h.idRef > n_rec) { bad = 1; R.size[i] = 0; }
         } else { R.mx[i] = 0.0f; R.size[i] = 0; R.e[i] = nullptr; }
         if (R.mx[i] != 0.0f) {                                   // :506-509
             if (!any || R.mx[i] > highest) highest = R.mx[i];

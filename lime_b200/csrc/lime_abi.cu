@@ -9,7 +9,7 @@ static std::string g_init_error;
 
 extern "C" {
 
-const char *lime_version(void) { return "lime-b200 0.1 (sm_100a)"; }
+const char *lime_version(void) { return "lime-b200 0.2 (sm_100a)"; }
 
 const char *lime_last_error(const lime_ctx *ctx) { return ctx ? ctx->err.c_str() : g_init_error.c_str(); }
 
@@ -42,10 +42,11 @@ void lime_destroy(lime_ctx *ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     for (auto &p : ctx->prof_events) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
-    peer_release(ctx);
+    xchg_release(ctx);
     load_release(ctx);
+    if (ctx->strand_host) cudaFreeHost(ctx->strand_host);
     DevBuf *bufs[] = {&ctx->in_lcp, &ctx->in_da, &ctx->in_ebwt, &ctx->clusters, &ctx->tile_state,
-                      &ctx->scalars, &ctx->sim_own, &ctx->sim32, &ctx->large_list, &ctx->long_recs, &ctx->k2_scratch,
+                      &ctx->scalars, &ctx->strand_state, &ctx->sim_own, &ctx->sim32, &ctx->large_list, &ctx->long_recs, &ctx->k2_scratch,
                       &ctx->row_counts, &ctx->cls_out, &ctx->tax_tables};
     for (DevBuf *b : bufs) b->release();
     for (auto &s : ctx->slots) { s.bin.release(); s.pos.release(); }
@@ -99,11 +100,11 @@ int lime_load(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint
             (reinterpret_cast<uintptr_t>(ebwt) & 3))
             return fail(ctx, LIME_ERR_ARG, "lime_load: device lcp/da must be 16-byte aligned, ebwt 4-byte aligned");
         ctx->d_lcp = lcp; ctx->d_da = da; ctx->d_ebwt = ebwt;
-        ctx->lcp_clamped = false;
+        ctx->lcp8 = false;
     } else {
         // narrowed lcp transfer (lime_abi_load.cu) when the caller has promised alpha <= 255
         const bool narrow = lcp && ctx->alpha_limit >= 1 && ctx->alpha_limit <= 255 && n >= (1ull << 16);
-        if (lcp || n == 0) CK(ctx->in_lcp.reserve(std::max<uint64_t>(n, 4) * 4), "cudaMalloc lcp");
+        if ((lcp && !narrow) || n == 0) CK(ctx->in_lcp.reserve(std::max<uint64_t>(n, 4) * 4), "cudaMalloc lcp");
         CK(ctx->in_da.reserve(std::max<uint64_t>(n, 4) * 4), "cudaMalloc da");
         if (ebwt) CK(ctx->in_ebwt.reserve(std::max<uint64_t>(n, 16)), "cudaMalloc ebwt");
         if (narrow) {
@@ -114,15 +115,17 @@ int lime_load(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint
             CK(cudaMemcpyAsync(ctx->in_da.p, da, n * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D da");
             if (ebwt) CK(cudaMemcpyAsync(ctx->in_ebwt.p, ebwt, n, cudaMemcpyHostToDevice, ctx->stream), "H2D ebwt");
         }
-        ctx->lcp_clamped = narrow;
-        ctx->d_lcp = (lcp || n == 0) ? ctx->in_lcp.as<uint32_t>() : nullptr; ctx->d_da = ctx->in_da.as<uint32_t>();
+        // a narrowed load leaves min(lcp, 255) as bytes on the device; the kernels read those
+        ctx->lcp8 = narrow;
+        ctx->d_lcp = narrow ? ctx->in_lcp8.p : ((lcp || n == 0) ? ctx->in_lcp.p : nullptr);
+        ctx->d_da = ctx->in_da.as<uint32_t>();
         ctx->d_ebwt = ebwt ? ctx->in_ebwt.as<uint8_t>() : nullptr;
     }
     ctx->n_own = n_own; ctx->n_halo = n_halo; ctx->pos_base = pos_base; ctx->is_last = is_last;
     ctx->n_reads = n_reads; ctx->n_refs = n_refs;
     // similarity accumulator: dense uint8 [n_reads][pitch], zeroed
-    if (ctx->peer.active) {
-        // peer mode: the rows live in the owners' slabs, zeroed by lime_peer_zero
+    if (ctx->xchg.active) {
+        // exchange mode: the rows of the owned reads live in the slabs of lime_xchg_alloc
         ctx->loaded = true;
         return LIME_OK;
     }
@@ -134,8 +137,11 @@ int lime_load(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint
     } else if (ctx->sim_rows < n_reads || ctx->sim_pitch < n_refs) {
         return fail(ctx, LIME_ERR_ARG, "lime_load: bound similarity matrix is too small");
     }
-    if (ctx->sim_rows * ctx->sim_pitch)
+    // the choose pass of lime_strand_run leaves the matrix zero: nothing to clear then
+    const bool clean = ctx->sim_clean && ctx->sim_clean_ptr == ctx->d_sim && ctx->sim_clean_bytes == ctx->sim_rows * ctx->sim_pitch;
+    if (ctx->sim_rows * ctx->sim_pitch && !clean)
         CK(cudaMemsetAsync(ctx->d_sim, 0, ctx->sim_rows * ctx->sim_pitch, ctx->stream), "memset similarity matrix");
+    ctx->sim_clean = true; ctx->sim_clean_ptr = ctx->d_sim; ctx->sim_clean_bytes = ctx->sim_rows * ctx->sim_pitch;
     ctx->loaded = true;
     return LIME_OK;
 }
@@ -145,43 +151,10 @@ int lime_cluster_detect(lime_ctx *ctx, uint32_t alpha, uint64_t *n_clusters, uin
     if (!ctx) return LIME_ERR_ARG;
     if (!ctx->loaded) return fail(ctx, LIME_ERR_STATE, "lime_cluster_detect: nothing loaded");
     if (!ctx->d_lcp && ctx->n_own) return fail(ctx, LIME_ERR_STATE, "lime_cluster_detect: loaded without lcp");
-    if (ctx->lcp_clamped && alpha > 255)
-        return fail(ctx, LIME_ERR_STATE, "lime_cluster_detect: lcp was loaded narrowed (lime_set_alpha_limit <= 255), alpha > 255 needs a reload");
-    CK(cudaSetDevice(ctx->device), "cudaSetDevice");
-    const uint64_t n_total = ctx->n_own + ctx->n_halo;
-    const uint64_t tiles = k12_num_tiles(ctx->n_own);
-    CK(ctx->tile_state.reserve(std::max<uint64_t>(tiles, 1) * 8), "cudaMalloc tile state");
-    // capacity guess: mixed clusters are a few percent of the positions; retry once when short
-    uint64_t cap = std::max<uint64_t>(ctx->cl_cap, std::max<uint64_t>(1024, n_total / 8));
     unsigned long long host_sc[SC_COUNT];
-    for (int attempt = 0; attempt < 2; attempt++) {
-        CK(ctx->clusters.reserve(cap * sizeof(lime_cluster)), "cudaMalloc clusters");
-        ctx->cl_cap = ctx->clusters.cap / sizeof(lime_cluster);
-        CK(cudaMemsetAsync(ctx->scalars.p, 0, sizeof(unsigned long long) * SC_COUNT, ctx->stream), "memset scalars");
-        CK(cudaMemsetAsync(ctx->tile_state.p, 0, std::max<uint64_t>(tiles, 1) * 8, ctx->stream), "memset tile state");
-        K12Args a = {};
-        a.lcp = ctx->d_lcp; a.da = ctx->d_da; a.ebwt = nullptr;
-        a.n_own = ctx->n_own; a.n_total = n_total; a.pos_base = ctx->pos_base; a.is_last = ctx->is_last;
-        a.alpha = alpha; a.n_reads = ctx->n_reads; a.n_refs = ctx->n_refs;
-        a.out = ctx->clusters.as<lime_cluster>(); a.out_cap = ctx->cl_cap;
-        a.tile_state = ctx->tile_state.as<unsigned long long>();
-        a.n_clusters = scalar<unsigned long long>(ctx, SC_NCLUSTERS);
-        a.max_len = scalar<unsigned long long>(ctx, SC_MAXLEN);
-        a.err = scalar<unsigned int>(ctx, SC_ERR);
-        if (tiles) {
-            LaunchScope ls(ctx, KID_K1_DETECT);
-            CK(launch_k12(a, false, true, false, ctx->stream), "k1_detect launch");
-        }
-        CK(cudaMemcpyAsync(host_sc, ctx->scalars.p, sizeof(host_sc), cudaMemcpyDeviceToHost, ctx->stream), "D2H scalars");
-        CK(cudaStreamSynchronize(ctx->stream), "k1_detect");
-        if ((unsigned)host_sc[SC_ERR] & 1u)
-            return fail(ctx, LIME_ERR_HALO, "lime_cluster_detect: a cluster runs past the halo of this shard");
-        if (host_sc[SC_NCLUSTERS] <= ctx->cl_cap) break;
-        cap = host_sc[SC_NCLUSTERS];
-    }
-    ctx->n_clusters = host_sc[SC_NCLUSTERS];
+    const int rc = detect_into_ctx(ctx, alpha, host_sc);
+    if (rc) return rc;
     ctx->max_len = host_sc[SC_MAXLEN];
-    ctx->alpha = alpha;
     ctx->have_clusters = true;
     if (n_clusters) *n_clusters = ctx->n_clusters;
     if (max_len) *max_len = ctx->max_len;
@@ -225,5 +198,47 @@ int lime_clusters_set(lime_ctx *ctx, const lime_cluster *cl, uint64_t n, uint64_
 }
 
 } // extern "C"
+
+// the detection passes (count, scan, emit): cluster records of this shard into ctx->clusters, ascending pStart;
+// sets ctx->n_clusters / alpha, returns the scalars
+int detect_into_ctx(lime_ctx *ctx, uint32_t alpha, unsigned long long host_sc[SC_COUNT])
+{
+    if (ctx->lcp8 && alpha > 255)
+        return fail(ctx, LIME_ERR_STATE, "lcp was loaded narrowed (lime_set_alpha_limit <= 255), alpha > 255 needs a reload");
+    CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+    const uint64_t n_total = ctx->n_own + ctx->n_halo;
+    const uint64_t tiles = k12_num_tiles(ctx->n_own);
+    CK(ctx->tile_state.reserve(std::max<uint64_t>(tiles, 1) * 8), "cudaMalloc tile state");
+    // capacity guess: mixed clusters are a few percent of the positions; retry once when short
+    uint64_t cap = std::max<uint64_t>(ctx->cl_cap, std::max<uint64_t>(1024, n_total / 8));
+    for (int attempt = 0; attempt < 2; attempt++) {
+        CK(ctx->clusters.reserve(cap * sizeof(lime_cluster)), "cudaMalloc clusters");
+        ctx->cl_cap = ctx->clusters.cap / sizeof(lime_cluster);
+        CK(cudaMemsetAsync(ctx->scalars.p, 0, sizeof(unsigned long long) * SC_COUNT, ctx->stream), "memset scalars");
+        CK(cudaMemsetAsync(ctx->tile_state.p, 0, std::max<uint64_t>(tiles, 1) * 8, ctx->stream), "memset tile state");
+        K12Args a = {};
+        a.lcp = ctx->d_lcp; a.lcp8 = ctx->lcp8 ? 1 : 0; a.da = ctx->d_da; a.ebwt = nullptr;
+        a.n_own = ctx->n_own; a.n_total = n_total; a.pos_base = ctx->pos_base; a.is_last = ctx->is_last;
+        a.alpha = alpha; a.n_reads = ctx->n_reads; a.n_refs = ctx->n_refs;
+        a.out = ctx->clusters.as<lime_cluster>(); a.out_cap = ctx->cl_cap;
+        a.tile_state = ctx->tile_state.as<unsigned long long>();
+        a.n_clusters = scalar<unsigned long long>(ctx, SC_NCLUSTERS);
+        a.max_len = scalar<unsigned long long>(ctx, SC_MAXLEN);
+        a.err = scalar<unsigned int>(ctx, SC_ERR);
+        if (tiles) {
+            LaunchScope ls(ctx, KID_K1_DETECT);
+            CK(launch_k12(a, K12_DETECT, ctx->stream), "k1_detect launch");
+        }
+        CK(cudaMemcpyAsync(host_sc, ctx->scalars.p, sizeof(unsigned long long) * SC_COUNT, cudaMemcpyDeviceToHost, ctx->stream), "D2H scalars");
+        CK(cudaStreamSynchronize(ctx->stream), "k1_detect");
+        if ((unsigned)host_sc[SC_ERR] & 1u)
+            return fail(ctx, LIME_ERR_HALO, "lime_cluster_detect: a cluster runs past the halo of this shard");
+        if (host_sc[SC_NCLUSTERS] <= ctx->cl_cap) break;
+        cap = host_sc[SC_NCLUSTERS];
+    }
+    ctx->n_clusters = host_sc[SC_NCLUSTERS];
+    ctx->alpha = alpha;
+    return LIME_OK;
+}
 
 // the remaining entry points live in lime_abi_steps.cu

@@ -3,6 +3,28 @@
 #include <algorithm>
 #include <vector>
 
+// Evaluate the device state of a strand that was run without a synchronisation (ctx->strand_host holds the copy).
+// LIME_ERR_RETRY: the result of that strand is not usable (record buffer too small, or a similarity cell
+// exceeded 255 and wrapped where the reference wraps, ClusterBWT_DA.cpp:183,247): redo it with the
+// synchronising calls, which size exactly and take the exact path.
+int strand_readback(lime_ctx *ctx, int slot)
+{
+    Slot &S = ctx->slots[slot];
+    const unsigned long long *h = ctx->strand_host + (size_t)slot * SS_COUNT;
+    S.deferred = false;
+    S.n_records = h[SS_NRECORDS];
+    S.status[0] = h[SS_NCLUSTERS]; S.status[1] = h[SS_MAXLEN]; S.status[2] = h[SS_NRECORDS]; S.status[3] = h[SS_NUPDATES];
+    ctx->rec_hint = std::max<uint64_t>(ctx->rec_hint, h[SS_NRECORDS]);
+    if (h[SS_ERR] & 1ull) { S.valid = false; return fail(ctx, LIME_ERR_HALO, "a cluster runs past the halo of this shard"); }
+    if (h[SS_MAXLEN] > LIME_SIZE_MAX_BUF) { S.valid = false; return fail(ctx, LIME_ERR_MAXLEN, "maximum cluster size is greater than sizeMaxBuf"); }
+    if (h[SS_ERR] & 12ull) { S.valid = false; return fail(ctx, (h[SS_ERR] & 8ull) ? LIME_ERR_ARG : LIME_ERR_RETRY, (h[SS_ERR] & 8ull) ? "exchange: update record out of range" : "exchange: an inbox region overflowed"); }
+    if (S.kind == 2 && h[SS_FLAT_COUNT] > ctx->xchg.flat_cap) { S.valid = false; return fail(ctx, LIME_ERR_RETRY, "exchange: the update list overflowed"); }
+    if (h[SS_NRECORDS] > S.bin_cap) { S.valid = false; return fail(ctx, LIME_ERR_RETRY, "deferred strand: record buffer too small"); }
+    const unsigned long long added = S.kind == 2 ? h[SS_APPLIED_T] : h[SS_SUMT];
+    if (added != h[SS_BYTESUM] || (h[SS_ERR] >> 32) != 0) { S.valid = false; return fail(ctx, LIME_ERR_RETRY, "deferred strand: a similarity cell exceeded 255"); }
+    return LIME_OK;
+}
+
 extern "C" {
 
 int lime_classify(lime_ctx *ctx, int n_files, uint32_t n_refs,
@@ -39,6 +61,9 @@ int lime_classify(lime_ctx *ctx, int n_files, uint32_t n_refs,
         a.bin[i] = on ? ctx->slots[i].bin.as<lime_pair_sim>() : nullptr;
         a.pos[i] = on ? ctx->slots[i].pos.as<uint64_t>() : nullptr;
         a.n_records[i] = on ? ctx->slots[i].n_records : 0;
+        const bool dev = on && ctx->slots[i].deferred;
+        a.n_records_dev[i] = dev ? strand_scalar<unsigned long long>(ctx, i, SS_NRECORDS) : nullptr;
+        a.bin_cap[i] = on ? ctx->slots[i].bin_cap : 0;
     }
     a.n_reads = n_reads; a.n_refs = n_refs; a.v = d_v; a.m = d_m;
     a.tax_rank = tax_rank; a.higher = use_m ? 1 : 0;
@@ -68,12 +93,26 @@ int lime_classify(lime_ctx *ctx, int n_files, uint32_t n_refs,
     }
     unsigned err = 0;
     CK(cudaMemcpyAsync(&err, a.err, 4, cudaMemcpyDeviceToHost, ctx->stream), "D2H err");
+    bool any_deferred = false;
+    for (int i = 0; i < n_files; i++) any_deferred |= ctx->slots[i].deferred;
+    if (any_deferred)
+        CK(cudaMemcpyAsync(ctx->strand_host, ctx->strand_state.p, sizeof(unsigned long long) * SS_COUNT * LIME_MAXFILES,
+                           cudaMemcpyDeviceToHost, ctx->stream), "D2H strand state");
     if (n_reads) {
         if (out_tax) CK(cudaMemcpyAsync(out_tax, a.out_tax, (uint64_t)n_reads * 4, cudaMemcpyDeviceToHost, ctx->stream), "D2H tax");
         if (out_sim) CK(cudaMemcpyAsync(out_sim, a.out_sim, (uint64_t)n_reads * 4, cudaMemcpyDeviceToHost, ctx->stream), "D2H sim");
         if (out_type) CK(cudaMemcpyAsync(out_type, a.out_type, n_reads, cudaMemcpyDeviceToHost, ctx->stream), "D2H type");
     }
     CK(cudaStreamSynchronize(ctx->stream), "k3_classify");
+    // the strands that ran without a host synchronisation: their scalars and error flags, read back just now
+    int deferred_rc = LIME_OK;
+    for (int i = 0; i < n_files; i++) {
+        Slot &S = ctx->slots[i];
+        if (!S.deferred) continue;
+        const int rc = strand_readback(ctx, i);
+        if (rc && !deferred_rc) deferred_rc = rc;
+    }
+    if (deferred_rc) { ctx->cls_n_valid = false; return deferred_rc; }
     ctx->cls_n = n_reads; ctx->cls_n_valid = !(err & 1u);
     if (err & 1u) return fail(ctx, LIME_ERR_ROWS, "lime_classify: a .res row is not strictly ascending in genome id (or out of range)");
     return LIME_OK;

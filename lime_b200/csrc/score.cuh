@@ -1,5 +1,5 @@
 // score.cuh -- scoring of one (read, genome) pair inside one cluster and the accumulator update,
-// shared by the fused kernel (k12_fused.cu) and the cluster-list kernels (k2_similarity.cu).
+// shared by the fused kernel (k12_stream.cu) and the cluster-list kernels (k2_similarity.cu).
 #pragma once
 #include "common.cuh"
 
@@ -88,7 +88,6 @@ struct SimAcc {
     uint32_t *sim32; uint32_t lo, hi, n_refs;
     unsigned int *carry;
     unsigned long long *sum_t;        // optional: total of t added through the checked path
-    const PeerTable *peer = nullptr;  // optional: rows live in the owners' slabs (peer memory)
 };
 
 template <bool EXACT32>
@@ -97,7 +96,7 @@ __device__ __forceinline__ void sim_add(const SimAcc &P, uint32_t r, uint32_t g,
     if (EXACT32) {
         if (r >= P.lo && r < P.hi) atomicAdd(&P.sim32[(size_t)(r - P.lo) * P.n_refs + g], t);
     } else {
-        uint8_t *row = P.peer ? peer_row(*P.peer, P.pitch8, r) : P.sim8 + (size_t)r * P.pitch8;
+        uint8_t *row = P.sim8 + (size_t)r * P.pitch8;
         unsigned *w = reinterpret_cast<unsigned *>(row) + (g >> 2);
         const unsigned sh = (g & 3u) * 8u;
         const unsigned old = atomicAdd(w, t << sh);

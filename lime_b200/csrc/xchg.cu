@@ -1,0 +1,187 @@
+// xchg.cu -- multi-GPU routing of similarity updates (the exchange step of north_star: partial (read, genome,
+// count) triples go to the GPU that owns the read).
+//
+// With the position range sharded over GPUs, a GPU meets reads of every owner.  The fused kernel
+// (k12_stream.cu, MODE_FLAT) and the block path append every update `SimArray_[r][g] += t`
+// (ClusterBWT_DA.cpp:183,247) as a record {r, g << 8 | t} to a flat list in local HBM.  Then
+//   route_kernel  streams that list once, sorts each tile of 2048 records by owner in shared memory and
+//                 writes every owner's run with coalesced stores straight into that owner's inbox -- peer
+//                 memory over NVLink / NVSwitch (CUDA IPC mapping), or local memory for its own reads.
+//                 Space in an inbox region (one per source GPU) is taken with a LOCAL atomic: only this GPU
+//                 writes to its region, so nothing remote is ever read or updated atomically.
+//   apply_kernel  (on the owner, after all sources have finished) adds the records of every source region
+//                 to the owner's uint8 rows with fire-and-forget adds and sums their t for the carry proof.
+// The only collective is the all-gather of the per-owner record counts in between, which is also the barrier.
+#include "common.cuh"
+#include <algorithm>
+
+namespace lime {
+namespace xchg {
+
+constexpr int THREADS = 256;
+constexpr int PER_THREAD = 8;
+constexpr int TILE = THREADS * PER_THREAD;      // records per tile
+
+struct RouteArgs {
+    const uint2 *flat;
+    const unsigned long long *flat_count;       // slots in use (device); clamped to flat_cap
+    uint64_t flat_cap;
+    uint32_t world, per, magic;                 // owner of read r = r / per; magic = min(floor(2^32 / per), 2^32 - 1)
+    uint32_t n_refs;
+    uint2 *dst[XCHG_MAX];                       // owner o's inbox region for this source and strand
+    uint64_t inbox_cap;                         // records per region
+    unsigned long long *sent;                   // [world] records written per owner (device, local)
+    unsigned long long *err;                    // bit 2: a region overflowed, bit 3: record out of range
+};
+
+__device__ __forceinline__ uint32_t owner_of(uint32_t r, uint32_t per, uint32_t magic, uint32_t &rem)
+{
+    uint32_t q = __umulhi(r, magic);            // quotient or quotient - 1
+    rem = r - q * per;
+    if (rem >= per) { q++; rem -= per; }
+    return q;
+}
+
+__global__ void __launch_bounds__(THREADS) route_kernel(const RouteArgs P)
+{
+    __shared__ uint2 s_rec[TILE];
+    __shared__ unsigned s_cnt[XCHG_MAX], s_off[XCHG_MAX + 1];
+    __shared__ unsigned long long s_base[XCHG_MAX];
+    const unsigned tid = threadIdx.x, lane = tid & 31u;
+    const unsigned long long n = min(*P.flat_count, (unsigned long long)P.flat_cap);
+    const unsigned long long n_tiles = (n + TILE - 1) / TILE;
+    for (unsigned long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        if (tid < XCHG_MAX) s_cnt[tid] = 0;
+        __syncthreads();
+        uint2 rec[PER_THREAD];
+        unsigned own[PER_THREAD], idx[PER_THREAD];
+#pragma unroll
+        for (int k = 0; k < PER_THREAD; k++) {
+            const unsigned long long i = tile * TILE + (unsigned long long)k * THREADS + tid;
+            rec[k] = i < n ? __ldcs(P.flat + i) : make_uint2(0u, 0u);
+        }
+#pragma unroll
+        for (int k = 0; k < PER_THREAD; k++) {
+            bool valid = (rec[k].y & 0xffu) != 0u;                     // t = 0: padding of a warp's last block
+            uint32_t rem = 0, q = 0;
+            if (valid) {
+                q = owner_of(rec[k].x, P.per, P.magic, rem);
+                if (q >= P.world || (rec[k].y >> 8) >= P.n_refs) { valid = false; atomicOr(P.err, 8ull); }
+            }
+            rec[k].x = rem;                                            // row inside the owner's slab
+            // the lanes that go to the same owner take their slots with one shared-memory atomic
+            const unsigned mm = __match_any_sync(FULL, valid ? q : 0xffffffffu);
+            unsigned base = 0;
+            const int leader = __ffs(mm) - 1;
+            if (valid && (int)lane == leader) base = atomicAdd(&s_cnt[q], (unsigned)__popc(mm));
+            base = __shfl_sync(FULL, base, leader);
+            own[k] = valid ? q : 0xffffffffu;
+            idx[k] = base + __popc(mm & ((1u << lane) - 1u));
+        }
+        __syncthreads();
+        if (tid == 0) {
+            unsigned run = 0;
+            for (unsigned o = 0; o < P.world; o++) { s_off[o] = run; run += s_cnt[o]; }
+            s_off[P.world] = run;
+        }
+        if (tid < P.world && s_cnt[tid]) s_base[tid] = atomicAdd(&P.sent[tid], (unsigned long long)s_cnt[tid]);
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < PER_THREAD; k++)
+            if (own[k] != 0xffffffffu) s_rec[s_off[own[k]] + idx[k]] = rec[k];
+        __syncthreads();
+        // sorted by owner: consecutive threads write consecutive records of one owner's run
+        const unsigned total = s_off[P.world];
+        for (unsigned i = tid; i < total; i += THREADS) {
+            unsigned o = 0;
+            while (i >= s_off[o + 1]) o++;
+            const unsigned long long d = s_base[o] + (i - s_off[o]);
+            if (d < P.inbox_cap) P.dst[o][d] = s_rec[i];
+            else atomicOr(P.err, 4ull);
+        }
+        __syncthreads();
+    }
+    __threadfence_system();                     // the stores to peer memory are performed before the kernel ends
+}
+
+struct ApplyArgs {
+    const uint2 *src;                           // this owner's inbox regions of one strand: [world][inbox_cap]
+    uint64_t inbox_cap;
+    const unsigned long long *counts_all;       // [world][world] records sent by source p to owner o (all-gathered)
+    uint32_t world, rank;
+    uint8_t *slab; uint64_t pitch;
+    uint32_t rows, n_refs;
+    unsigned long long *applied_t;              // sum of t added (carry proof: must equal the byte sum of the slab)
+    unsigned long long *applied_n;
+    unsigned long long *err;                    // bit 2: a source sent more than a region holds, bit 3: bad record
+};
+
+// gridDim.y = sources
+__global__ void __launch_bounds__(THREADS) apply_kernel(const ApplyArgs P)
+{
+    const unsigned p = blockIdx.y;
+    unsigned long long n = P.counts_all[(size_t)p * P.world + P.rank];
+    if (n > P.inbox_cap) { if (threadIdx.x == 0 && blockIdx.x == 0) atomicOr(P.err, 4ull); n = P.inbox_cap; }
+    const uint2 *src = P.src + (size_t)p * P.inbox_cap;
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    unsigned long long tsum = 0, cnt = 0;
+    // two records per 16-byte load; regions are 16-byte aligned
+    const unsigned long long n2 = n / 2;
+    const uint4 *src2 = reinterpret_cast<const uint4 *>(src);
+    for (unsigned long long i = (unsigned long long)blockIdx.x * THREADS + threadIdx.x; i < n2 + (n & 1ull);
+         i += (unsigned long long)gridDim.x * THREADS) {
+        uint2 r[2];
+        int m = 2;
+        if (i < n2) { const uint4 v = *(src2 + i); r[0] = make_uint2(v.x, v.y); r[1] = make_uint2(v.z, v.w); }
+        else { r[0] = src[n - 1]; r[1] = make_uint2(0u, 0u); m = 1; }
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+            if (k >= m) continue;
+            const uint32_t row = r[k].x, g = r[k].y >> 8, t = r[k].y & 0xffu;
+            if (row >= P.rows || g >= P.n_refs) { atomicOr(P.err, 8ull); continue; }
+            unsigned *w = reinterpret_cast<unsigned *>(P.slab + (size_t)row * P.pitch) + (g >> 2);
+            asm volatile("red.relaxed.gpu.global.add.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(w), "r"(t << ((g & 3u) * 8u)), "l"(pol) : "memory");
+            tsum += t; cnt++;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { tsum += __shfl_xor_sync(FULL, tsum, o); cnt += __shfl_xor_sync(FULL, cnt, o); }
+    __shared__ unsigned long long s_t[THREADS / 32], s_n[THREADS / 32];
+    if ((threadIdx.x & 31) == 0) { s_t[threadIdx.x >> 5] = tsum; s_n[threadIdx.x >> 5] = cnt; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long a = 0, b = 0;
+        for (int k = 0; k < THREADS / 32; k++) { a += s_t[k]; b += s_n[k]; }
+        if (a) atomicAdd(P.applied_t, a);
+        if (b) atomicAdd(P.applied_n, b);
+    }
+}
+
+} // namespace xchg
+
+cudaError_t launch_xchg_route(const XchgRoute &a, cudaStream_t s)
+{
+    xchg::RouteArgs P;
+    P.flat = a.flat; P.flat_count = a.flat_count; P.flat_cap = a.flat_cap;
+    P.world = a.world; P.per = a.per;
+    P.magic = (uint32_t)std::min<uint64_t>((1ull << 32) / std::max<uint32_t>(a.per, 1u), 0xffffffffull);
+    P.n_refs = a.n_refs;
+    for (int o = 0; o < XCHG_MAX; o++) P.dst[o] = o < (int)a.world ? a.dst[o] : nullptr;
+    P.inbox_cap = a.inbox_cap; P.sent = a.sent; P.err = a.err;
+    xchg::route_kernel<<<148 * 4, xchg::THREADS, 0, s>>>(P);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_xchg_apply(const XchgApply &a, cudaStream_t s)
+{
+    xchg::ApplyArgs P;
+    P.src = a.src; P.inbox_cap = a.inbox_cap; P.counts_all = a.counts_all; P.world = a.world; P.rank = a.rank;
+    P.slab = a.slab; P.pitch = a.pitch; P.rows = a.rows; P.n_refs = a.n_refs;
+    P.applied_t = a.applied_t; P.applied_n = a.applied_n; P.err = a.err;
+    const dim3 grid((148 * 8 + a.world - 1) / a.world, a.world);
+    xchg::apply_kernel<<<grid, xchg::THREADS, 0, s>>>(P);
+    return cudaGetLastError();
+}
+
+} // namespace lime

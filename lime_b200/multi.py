@@ -5,12 +5,16 @@ Sharding (north_star):
     to the shard that holds its head -- the thread-chunk rule of ClusterLCP.cpp:150-202 -- so each
     rank also needs the first `halo` positions of the next shard (the "run past the chunk end" of
     :246-264).  `exchange_halo` moves them rank k+1 -> rank k (point to point over NVLink);
-  * each rank accumulates a PARTIAL similarity matrix over all reads from its positions
-    (lime_cluster_similarity);
-  * reads are owned by contiguous ranges; the non-zero cells of the other ranks' ranges leave as
-    (read, genome, count) triples (lime_sim_export), are routed by read owner with ONE all-to-all
-    (NCCL over NVLink / NVSwitch) and added on arrival (lime_sim_import, uint8 wrap = the
-    reference's cell, so sum-then-wrap equals the single-GPU result);
+  * reads are owned by contiguous ranges and the similarity rows of a read live on its owner only.
+    `XchgJob` (the default): every update (read, genome, t) of a rank's positions is appended to a local
+    list by the fused kernel, sorted by owner and written into the owner's inbox over NVLink
+    (lime_xchg_accumulate, bulk stores into CUDA-IPC mapped peer memory); one tiny all-gather of the
+    record counts per strand is the only collective and the barrier; the owner adds the records to
+    its rows (lime_xchg_apply).  Nothing synchronises with the host until Classify;
+  * `ShardedJob` (the exact route, used when a cell exceeds 255 and must wrap like the reference's
+    uint8 cell, Tools.h:68): each rank accumulates a PARTIAL matrix over all reads, the non-zero
+    cells of the other ranks' ranges leave as (read, genome, count) triples (lime_sim_export), are
+    routed by read owner with ONE all-to-all (NCCL) and added on arrival (lime_sim_import);
   * the owner runs clusterChoose and, after all strands, Classify on its read range; the
     assignments are gathered.
 nClusters / maxLen are the reference's reduction(+) / reduction(max) (ClusterLCP.cpp:140): one
@@ -97,31 +101,41 @@ class CudaBackend:
     def classify(self, n_files, n_refs, v, m, tax_rank, higher):
         return self.ctx.classify(n_files, n_refs, v, m, tax_rank, higher)
 
-    # ---- peer-memory accumulation (PeerJob) -------------------------------------------------------
-    def peer_setup(self, dist, world, rank, rows, n_refs, n_slabs):
-        """Allocate this rank's slabs, all-gather the CUDA IPC handles, map every owner's slabs."""
+    # ---- rows on the read owner, updates routed as records (XchgJob) ---------------------------------
+    def xchg_setup(self, dist, world, rank, per, n_refs, n_strands, flat_cap, inbox_cap):
+        """Allocate slabs / update list / inbox, all-gather the CUDA IPC handles, map every rank's inbox."""
         torch = self.torch
-        mine = torch.from_numpy(self.ctx.peer_alloc(rows, n_refs, n_slabs).copy()).to(self.device)
+        self.ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+        mine = torch.from_numpy(self.ctx.xchg_alloc(world, rank, per, n_refs, n_strands, flat_cap, inbox_cap).copy()).to(self.device)
         parts = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(parts, mine)
-        self.ctx.peer_open(world, rank, torch.stack(parts).cpu().numpy(), rows)
-        dist.barrier()                       # every rank has mapped every slab
+        self.ctx.xchg_open(torch.stack(parts).cpu().numpy() if world > 1 else None)
+        self._sent = torch.zeros(n_strands, world, dtype=torch.int64, device=self.device)
+        self._counts = torch.zeros(n_strands, world * world, dtype=torch.int64, device=self.device)
+        dist.barrier()                       # every rank has mapped every inbox
 
-    def peer_zero(self):
-        self.ctx.peer_zero()
+    def xchg_accumulate(self, alpha, ebwt_mode, strand):
+        """-> device tensor [world]: records this rank sent to every owner (filled asynchronously)."""
+        self.ctx.xchg_accumulate(alpha, ebwt_mode, strand, self._sent[strand].data_ptr())
+        return self._sent[strand]
 
-    def peer_accumulate(self, alpha, ebwt_mode, slab):
-        return self.ctx.peer_accumulate(alpha, ebwt_mode, slab)
+    def xchg_counts_buffer(self, strand):
+        return self._counts[strand]
 
-    def peer_select(self, slab, total_updates, byte_sums, k):
-        """byte_sums: int64 tensor of the job; element k receives the slab's byte sum (asynchronously)."""
-        self.ctx.peer_select(slab, total_updates, byte_sums.data_ptr() + 8 * k)
+    def xchg_apply(self, strand, counts_all):
+        self.ctx.xchg_apply(strand, counts_all.data_ptr())
 
-    def peer_zero_slab(self, slab):
-        self.ctx.peer_zero_slab(slab)
+    def xchg_choose(self, strand, norm, beta, n_own):
+        self.ctx.xchg_choose(strand, norm, beta, n_own)
 
-    def peer_close(self):
-        self.ctx.peer_close()
+    def xchg_status(self, strand):
+        return self.ctx.xchg_status(strand)
+
+    def strand_status(self, slot):
+        return self.ctx.strand_status(slot)
+
+    def xchg_close(self):
+        self.ctx.xchg_close()
 
     def classify_tensors(self, n_files, n_refs, v, m, tax_rank, higher, pad_to):
         """Classify and leave the assignments on the device: (type u8, taxid i32, sim-bits i32) tensors
@@ -215,30 +229,42 @@ class ShardedJob:
         self.n_strands = max(self.n_strands, slot + 1)
         return self.stats[-1]
 
+    def classify_own(self, v, m=None, tax_rank=1, higher=False, gather=True):
+        """Classify on the owned read range -> ("dev", device tensors padded for the gather) or ("host", arrays)."""
+        per = self.ranges[0][1] - self.ranges[0][0]
+        on_device = hasattr(self.be, "classify_tensors") and gather and self.world > 1
+        with self.timer("classify"):
+            if on_device:
+                return "dev", self.be.classify_tensors(self.n_strands, self.n_refs, v, m, tax_rank, higher, per)
+            return "host", self.be.classify(self.n_strands, self.n_refs, v, m, tax_rank, higher)
+
     def finish(self, v, m=None, tax_rank=1, higher=False, gather=True):
         """Classify on the owned read range, then gather the assignments of all reads.
         gather=True: every rank returns them; "root": rank 0 returns them, the others (None,)*3;
         False: every rank returns its own read range only."""
+        res = self.classify_own(v, m, tax_rank, higher, gather)
+        if not gather or self.world == 1:
+            return res[1]          # the backend's (page-locked, context-owned) arrays: valid until the next classify
+        return self.gather_assignments(res, gather)
+
+    def gather_assignments(self, res, gather=True):
         torch, dist = self.torch, self.dist
         per = self.ranges[0][1] - self.ranges[0][0]
         k = self.hi - self.lo
-        on_device = hasattr(self.be, "classify_tensors") and gather and self.world > 1
-        with self.timer("classify"):
-            if on_device:
-                mine = self.be.classify_tensors(self.n_strands, self.n_refs, v, m, tax_rank, higher, per)
-            else:
-                typ, tax, sim = self.be.classify(self.n_strands, self.n_refs, v, m, tax_rank, higher)
-        if not gather or self.world == 1:
-            return typ, tax, sim          # the backend's (page-locked, context-owned) arrays: valid until the next classify
+        on_device = res[0] == "dev"
         with self.timer("gather"):
             # three contiguous all-gathers (type u8, taxid u32, sim f32 bits); every rank owns `per`
             # reads except possibly the last ones, so the padded concatenation IS the read order
-            if not on_device:
+            if on_device:
+                mine = res[1]
+            else:
+                typ, tax, sim = res[1]
                 mine = []
                 for arr, tdt, ndt in ((typ, torch.uint8, np.uint8), (tax, torch.int32, np.int32), (sim, torch.int32, np.int32)):
                     t = torch.zeros(per, dtype=tdt)
                     t[:k] = torch.from_numpy(np.ascontiguousarray(arr).view(ndt)[:k].copy())
-                    mine.append(t)
+                    dev = getattr(self.be, "device", None)
+                    mine.append(t.to(dev) if dev is not None else t)
             outs = []
             fetch = gather is True or self.rank == 0
             for t in mine:
@@ -255,7 +281,7 @@ class ShardedJob:
                         outs.append(host)
                     else:
                         outs.append(whole)
-            if fetch and on_device:
+            if fetch and mine and mine[0].is_cuda:
                 torch.cuda.synchronize()
         if not fetch:
             return None, None, None
@@ -264,25 +290,34 @@ class ShardedJob:
 
 
 class CarryDetected(RuntimeError):
-    """A similarity cell exceeded 255 during a peer-memory job: redo it with ShardedJob, whose
-    backend reruns the pass into exact 32-bit cells (the uint8 wrap of SimArray_, Tools.h:68)."""
+    """The exchange job cannot stand: a similarity cell exceeded 255 (redo it with ShardedJob, whose
+    backend reruns the pass into exact 32-bit cells -- the uint8 wrap of SimArray_, Tools.h:68), or a
+    record list / inbox was too small (`overflow`: redo it with larger lists)."""
+
+    def __init__(self, msg, overflow=False):
+        super().__init__(msg)
+        self.overflow = overflow
 
 
-class PeerJob:
-    """The same job as ShardedJob with the exchange folded into the compute kernel: every rank holds
-    only the similarity rows of the reads it owns (one slab per strand) and maps the slabs of all other
-    ranks (CUDA IPC over NVLink / NVSwitch); the fused kernel adds every (read, genome, t) straight
-    into the owner's slab (lime_peer_accumulate).  No partial matrices, no triples, no all-to-all:
-    the collectives left are three tiny all-gathers per job that double as the barriers
-      zeroed slabs -> [adds of all strands] -> scalars -> [choose, classify] -> byte sums (carry check).
+def xchg_capacities(n_positions, world, density=0.25):
+    """Record capacities of an XchgJob for shards of n_positions: the update list of a strand (the bench
+    workload issues 0.11 updates per position) and one inbox region (a source's share for one owner)."""
+    flat_cap = int(n_positions * density) + (1 << 20)
+    inbox_cap = int(flat_cap * 1.5 / world) + (1 << 16)
+    return flat_cap, inbox_cap
 
-        job = PeerJob(dist, torch, backend, rank, world, n_reads, n_refs, n_strands)
-        job.begin()
+
+class XchgJob:
+    """The job of ShardedJob with the similarity rows on the read owner only: compute and routing are
+    queued per strand without a host synchronisation (lime_xchg_accumulate -> all-gather of the record
+    counts -> lime_xchg_apply -> lime_xchg_choose); Classify reads the strands' state back.
+
+        job = XchgJob(dist, torch, backend, rank, world, n_reads, n_refs, n_strands, flat_cap, inbox_cap)
         for s, shard in enumerate(strands): job.run_strand(s, shard, alpha, beta, ebwt_mode, read_len)
         typ, tax, sim = job.finish(v, m, tax_rank, higher)
     """
 
-    def __init__(self, dist, torch, backend, rank, world, n_reads, n_refs, n_strands, timer=None):
+    def __init__(self, dist, torch, backend, rank, world, n_reads, n_refs, n_strands, flat_cap, inbox_cap, timer=None):
         self.dist, self.torch, self.be = dist, torch, backend
         self.rank, self.world = rank, world
         self.n_reads, self.n_refs, self.n_strands = n_reads, n_refs, n_strands
@@ -290,94 +325,89 @@ class PeerJob:
         self.lo, self.hi = self.ranges[rank]
         self.per = max(self.ranges[0][1] - self.ranges[0][0], 1)
         self.timer = timer or (lambda name: _NoTimer())
-        self.stats, self._local, self._pending = [], [], []
+        self.stats, self._pending = [], []
+        self.flat_cap, self.inbox_cap = int(flat_cap), int(inbox_cap)
         self._inner = ShardedJob(dist, torch, backend, rank, world, n_reads, n_refs)   # finish() = classify + gather
-        backend.peer_setup(dist, world, rank, self.per, n_refs, n_strands)
-        self._dirty, self.closed = False, False
-        self._bs = torch.zeros(n_strands, dtype=torch.int64)
-        if getattr(backend, "device", None) is not None:
-            self._bs = self._bs.to(backend.device)
-
-    def _all_gather_i64(self, values):
-        """Every rank's vector of integers, as a (world, len) int64 numpy array; also a barrier."""
-        torch, dist = self.torch, self.dist
-        t = self._inner._cpu_or_dev(values)
-        parts = [torch.empty_like(t) for _ in range(self.world)]
-        dist.all_gather(parts, t)
-        return torch.stack(parts).cpu().numpy().reshape(self.world, -1)
+        backend.xchg_setup(dist, world, rank, self.per, n_refs, n_strands, self.flat_cap, self.inbox_cap)
+        self.closed = False
 
     def begin(self):
-        """Nobody may add before every rank's slabs are zero: true after the constructor (fresh slabs,
-        then the handle all-gather) and after every finish() (slabs cleared before its last all-gather);
-        an abandoned job needs the explicit zero + barrier."""
         if self.closed:
-            raise RuntimeError("PeerJob is closed")
-        if self._dirty:
-            with self.timer("zero"):
-                self.be.peer_zero()
-                self.dist.barrier()
-        self._dirty = True
-        self.stats, self._local, self._pending = [], [], []
+            raise RuntimeError("XchgJob is closed")
+        self.stats, self._pending = [], []
 
     def run_strand(self, slot, shard, alpha, beta, ebwt_mode, read_len):
-        be = self.be
+        be, dist = self.be, self.dist
         with self.timer("compute"):
             be.load(shard["lcp"], shard["da"], shard["ebwt"] if ebwt_mode else None, shard["n_own"], shard["n_halo"],
                     shard["pos_base"], shard["is_last"], self.n_reads, self.n_refs)
-            n_cl, max_len, updates, sum_t = be.peer_accumulate(alpha, ebwt_mode, slot)
-        self._local += [n_cl, max_len, updates, sum_t]
-        self._pending.append((slot, norm_of(read_len, alpha), beta))
+            sent = be.xchg_accumulate(alpha, ebwt_mode, slot)
+        with self.timer("counts"):
+            counts = be.xchg_counts_buffer(slot)
+            dist.all_gather_into_tensor(counts, sent)          # [source][owner]; also: every source has delivered
+        with self.timer("apply"):
+            be.xchg_apply(slot, counts)
+        with self.timer("choose"):
+            be.xchg_choose(slot, norm_of(read_len, alpha), beta, self.hi - self.lo)
+        self._pending.append(slot)
 
     def finish(self, v, m=None, tax_rank=1, higher=False, gather=True):
-        be = self.be
-        with self.timer("scalars"):
-            # every rank's (nClusters, maxLen, updates, sum_t) per strand; completing it means every
-            # rank's adds have landed (each rank synchronised its kernels before contributing)
-            sc = self._all_gather_i64(self._local).reshape(self.world, len(self._pending), 4)
-        with self.timer("choose"):
-            for k, (slot, norm, beta) in enumerate(self._pending):
-                be.peer_select(slot, int(sc[:, k, 2].sum()), self._bs, k)
-                n_rec = be.choose(slot, norm, beta, 0, self.hi - self.lo)
-                be.peer_zero_slab(slot)                   # ready for the next job once `check` has completed
-                self.stats.append({"n_clusters": int(sc[:, k, 0].sum()), "max_len": int(sc[:, k, 1].max()),
-                                   "n_records_local": int(n_rec), "updates": int(sc[:, k, 2].sum())})
+        from ._lib import ERR_RETRY, LimeError
+        torch, dist = self.torch, self.dist
         inner = self._inner
         inner.timer, inner.n_strands = self.timer, len(self._pending)
-        out = inner.finish(v, m, tax_rank, higher, gather=gather)
+        code, res, msg = 0, None, ""
+        try:
+            res = inner.classify_own(v, m, tax_rank, higher, gather)      # also reads the strands' state back
+        except LimeError as e:
+            code, msg = e.code, str(e)
         with self.timer("check"):
-            parts = [self.torch.empty_like(self._bs) for _ in range(self.world)]
-            self.dist.all_gather(parts, self._bs)
-            bs = self.torch.stack(parts).cpu().numpy().reshape(self.world, -1)
-            self._dirty = False
-            for k in range(len(self._pending)):
-                if int(bs[:, k].sum()) != int(sc[:, k, 3].sum()) and not os.environ.get("LIME_DEBUG"):
-                    raise CarryDetected(f"strand {k}: byte sum {int(bs[:, k].sum())} != total added {int(sc[:, k, 3].sum())}")
-        return out
+            # the ranks agree on the outcome (every rank takes the same branch), then on the scalars
+            st = [self.be.xchg_status(s) for s in self._pending]
+            over = int(any(x["list_slots"] > self.flat_cap or (x["err"] & 4) for x in st))
+            flag = inner._cpu_or_dev([code, -over])
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            code_all, over_all = int(flag[0].item()), -int(flag[1].item())
+            if code_all == ERR_RETRY:
+                raise CarryDetected(msg or "another rank must redo its strands", overflow=bool(over_all))
+            if code_all != 0:
+                raise LimeError(code_all, msg or "a rank of the job failed")
+            tot = inner._cpu_or_dev([x["n_clusters"] for x in st] + [x["updates"] for x in st])
+            mx = inner._cpu_or_dev([x["max_len"] for x in st])
+            dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+            dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+            k = len(st)
+            self.stats = [{"n_clusters": int(tot[i].item()), "max_len": int(mx[i].item()), "updates": int(tot[k + i].item()),
+                           "n_records_local": st[i]["n_records"]} for i in range(k)]
+        if not gather or self.world == 1:
+            return res[1]
+        return inner.gather_assignments(res, gather)
 
     def close(self):
-        """Collective: unmaps and frees the slabs; the backend then allocates whole matrices again."""
+        """Collective: unmaps and frees slabs and inboxes; the backend then allocates whole matrices again."""
         if self.closed:
             return
         self.closed = True
         self.dist.barrier()
-        self.be.peer_close()
+        self.be.xchg_close()
 
 
 def run_sharded(dist, torch, backend, rank, world, n_reads, n_refs, shards, alpha, beta, ebwt_mode, read_len,
-                v, m=None, tax_rank=1, higher=False, gather=True, peer_job=None):
-    """One classification job over `world` ranks: through `peer_job` (a PeerJob, reused between calls)
-    when given, and again through the exchange route when that one reports a cell above 255 -- every rank
-    sees the same all-gathered sums, so all ranks take the same branch; the peer job is closed then (its
-    slabs are released so that the backend allocates whole matrices again).  shards: this rank's shard
-    of every strand (dicts as for run_strand).  Returns (assignments, per-strand stats, route)."""
-    if peer_job is not None and not peer_job.closed:
+                v, m=None, tax_rank=1, higher=False, gather=True, xchg_job=None):
+    """One classification job over `world` ranks: through `xchg_job` (an XchgJob, reused between calls)
+    when given, and again through the exact exchange route when that one reports a cell above 255 (or lists
+    that were too small) -- every rank sees the same all-reduced outcome, so all ranks take the same branch;
+    the exchange job is closed then (its buffers are released so that the backend allocates whole matrices
+    again).  shards: this rank's shard of every strand (dicts as for run_strand).
+    Returns (assignments, per-strand stats, route)."""
+    if xchg_job is not None and not xchg_job.closed:
         try:
-            peer_job.begin()
+            xchg_job.begin()
             for s, sh in enumerate(shards):
-                peer_job.run_strand(s, sh, alpha, beta, ebwt_mode, read_len)
-            return peer_job.finish(v, m, tax_rank, higher, gather=gather), list(peer_job.stats), "peer"
+                xchg_job.run_strand(s, sh, alpha, beta, ebwt_mode, read_len)
+            return xchg_job.finish(v, m, tax_rank, higher, gather=gather), list(xchg_job.stats), "xchg"
         except CarryDetected:
-            peer_job.close()
+            xchg_job.close()
     job = ShardedJob(dist, torch, backend, rank, world, n_reads, n_refs)
     for s, sh in enumerate(shards):
         job.run_strand(s, sh, alpha, beta, ebwt_mode, read_len)

@@ -7,7 +7,7 @@ reads them there; nothing is written to disk unless the caller copies a slot out
 """
 import numpy as np
 
-from ._lib import MEM_HOST, MEM_DEVICE  # noqa: F401
+from ._lib import MEM_HOST, MEM_DEVICE, ERR_RETRY, LimeError  # noqa: F401
 
 
 def norm_of(read_len, alpha):
@@ -34,10 +34,27 @@ def run_strand(ctx, slot, strand, n_reads, n_refs, read_len, alpha, beta, ebwt_m
 
 
 def run_job(ctx, strands, n_reads, n_refs, read_len, alpha, beta, ebwt_mode, v_corRef, m_corRef=None,
-            tax_rank=1, higher=False, mem=MEM_HOST, fused=True):
+            tax_rank=1, higher=False, mem=MEM_HOST, fused=True, deferred=None):
     """A whole single-end (2 strands) or paired-end (4 strands) job: steps 1-2 per strand, then
-    step 3.  Returns ((type u8, taxid u32, sim f32) per read, per-strand stats)."""
+    step 3.  Returns ((type u8, taxid u32, sim f32) per read, per-strand stats).
+
+    deferred (default: with the fused path): the strands are queued without a host synchronisation
+    (lime_strand_run) and checked by lime_classify; LIME_ERR_RETRY redoes the job with the
+    synchronising calls (exact sizes, exact uint8-wrap path)."""
     assert len(strands) in (2, 4)            # Classify.cpp:334-338
+    if deferred is None:
+        deferred = fused
+    if deferred and fused:
+        try:
+            for s, st in enumerate(strands):
+                ebwt = st.get("ebwt") if ebwt_mode else None
+                ctx.load(st["lcp"], st["da"], ebwt, n_reads, n_refs, mem=mem, n_total=st["n"])
+                ctx.strand_run(s, alpha, ebwt_mode, norm_of(read_len, alpha), beta)
+            out = ctx.classify(len(strands), n_refs, v_corRef, m_corRef, tax_rank, higher)
+            return out, [ctx.strand_status(s)[:3] for s in range(len(strands))]
+        except LimeError as e:
+            if e.code != ERR_RETRY:
+                raise
     stats = [run_strand(ctx, s, st, n_reads, n_refs, read_len, alpha, beta, ebwt_mode, mem, fused)
              for s, st in enumerate(strands)]
     out = ctx.classify(len(strands), n_refs, v_corRef, m_corRef, tax_rank, higher)

@@ -170,43 +170,124 @@ def test_export_import_roundtrip(ctx, oracle, n_refs, ebwt_mode, alpha):
     assert np.array_equal(ctx.sim_matrix(), want)
 
 
-@pytest.mark.parametrize("ebwt_mode,alpha", [(1, 16), (0, 12)])
-def test_peer_slab_accumulation(oracle, ebwt_mode, alpha):
-    """lime_peer_*: the fused kernel adding into owner slabs (K12<PEER>), here with one owner in one
-    process (CUDA IPC cannot map a process's own allocation twice; 2 and 8 owners are checked under
-    torchrun by tools/gpu_multi_check.py).  Slab contents, byte-sum carry proof, choose on the slab,
-    slab reuse after lime_peer_zero_slab."""
+@pytest.mark.parametrize("ebwt_mode,alpha,world", [(1, 16, 4), (0, 12, 3), (1, 12, 1)])
+def test_xchg_loopback(oracle, ebwt_mode, alpha, world):
+    """lime_xchg_*: the fused kernel appending update records (K12 MODE_FLAT + block path), route_kernel sorting
+    them by owner, apply_kernel adding them to the owner's slab -- here with `world` virtual owners on one GPU
+    (loopback; real peers are checked under torchrun by test_gpu_multi.py).  Each virtual rank must end with
+    exactly the oracle's rows of its reads, the carry proof (sum of t applied == byte sum), the records of
+    clusterChoose and the assignments; slabs are reused by a second job without clearing."""
     import torch
     from lime_b200.api import LimeContext
-    case = C.synth_case(f"synth_peer{ebwt_mode}", 1_500_000, 15_000, 37, seed=91 + ebwt_mode, p_long=2e-5, max_seg=60000)
+    case = C.synth_case(f"synth_xchg{ebwt_mode}", 1_500_000, 15_000, 37, seed=91 + ebwt_mode, p_long=2e-5, max_seg=60000)
+    n_reads, n_refs = case["n_reads"], case["n_refs"]
     ebwt = case["ebwt"] if ebwt_mode else None
-    cl, mx = oracle.cluster_detect(case["lcp"], case["da"], case["n_reads"], alpha)
-    sim_o = oracle.similarity(cl, case["da"], ebwt, case["n_reads"], case["n_refs"])
+    cl, mx = oracle.cluster_detect(case["lcp"], case["da"], n_reads, alpha)
+    sim_o = oracle.similarity(cl, case["da"], ebwt, n_reads, n_refs)
     norm = (case["read_len"] + 1 - alpha) & 0xFFFFFFFF
-    bin_o, pos_o = oracle.choose(sim_o, norm, np.float32(0.25))
-    c = LimeContext(0)
-    try:
-        handle = c.peer_alloc(case["n_reads"], case["n_refs"], 2)
-        c.peer_open(1, 0, handle, case["n_reads"])
-        bs = torch.zeros(2, dtype=torch.int64, device="cuda:0")
-        for rep in range(2):                                    # second round: reused slabs
-            for slab in (0, 1):
-                c.load(case["lcp"], case["da"], ebwt, case["n_reads"], case["n_refs"])
-                n_cl, max_len, updates, sum_t = c.peer_accumulate(alpha, ebwt_mode, slab)
-                assert (n_cl, max_len) == (cl.shape[0], mx)
-                assert sum_t == int(sim_o.astype(np.int64).sum()) and updates >= np.count_nonzero(sim_o)
-            for slab in (0, 1):
-                c.peer_select(slab, updates, bs.data_ptr() + 8 * slab)
-                assert np.array_equal(c.sim_matrix(), sim_o)
-                n_rec = c.choose(slab, norm, 0.25, 0, case["n_reads"])
-                bin_g, pos_g = c.choose_result(slab)
-                assert n_rec == bin_o.shape[0] and bin_g.tobytes() == bin_o.tobytes() and pos_g.tobytes() == pos_o.tobytes()
-                c.peer_zero_slab(slab)
-            torch.cuda.synchronize()
-            assert bs.tolist() == [sum_t, sum_t]
-        c.peer_close()
-    finally:
-        c.close()
+    v = (np.arange(n_refs, dtype=np.uint32) // 3) + 50
+    per = (n_reads + world - 1) // world
+    for rank in range(world):
+        lo, hi = min(rank * per, n_reads), min((rank + 1) * per, n_reads)
+        bin_o, pos_o = oracle.choose(sim_o[lo:hi], norm, np.float32(0.25))
+        exp = oracle.classify([bin_o, bin_o], [pos_o, pos_o], n_refs, v, None, 1, False)
+        c = LimeContext(0)
+        try:
+            c.set_stream(torch.cuda.current_stream().cuda_stream)
+            c.xchg_alloc(world, rank, per, n_refs, 2, 400_000, 300_000)
+            c.xchg_open(None)
+            sent = torch.zeros(2, world, dtype=torch.int64, device="cuda:0")
+            for rep in range(2):
+                for strand in (0, 1):
+                    c.load(case["lcp"], case["da"], ebwt, n_reads, n_refs)
+                    c.xchg_accumulate(alpha, ebwt_mode, strand, sent[strand].data_ptr())
+                    counts = torch.zeros(world, world, dtype=torch.int64, device="cuda:0")
+                    counts[rank] = sent[strand]                         # this source's row of the all-gather
+                    c.xchg_apply(strand, counts.data_ptr())
+                    slab = c.sim_matrix(rows=per)
+                    assert np.array_equal(slab[:hi - lo], sim_o[lo:hi]) and not slab[hi - lo:].any()
+                    c.xchg_choose(strand, norm, 0.25, hi - lo)
+                got = c.classify(2, n_refs, v, None, 1, False)
+                for g, e in zip(got, exp):
+                    assert np.asarray(g).tobytes() == e.tobytes()
+                for strand in (0, 1):
+                    st = c.xchg_status(strand)
+                    assert (st["n_clusters"], st["max_len"]) == (cl.shape[0], mx) and st["err"] == 0
+                    assert st["applied_t"] == st["byte_sum"] == int(sim_o[lo:hi].astype(np.int64).sum())
+                    assert st["n_records"] == bin_o.shape[0]
+                    assert c.strand_status(strand)[:3] == (cl.shape[0], mx, bin_o.shape[0])
+                    bin_g, pos_g = c.choose_result(strand)
+                    assert bin_g.tobytes() == bin_o.tobytes() and pos_g.tobytes() == pos_o.tobytes()
+                assert int(sent.sum(dim=1)[0]) >= np.count_nonzero(sim_o)
+            c.xchg_close()
+        finally:
+            c.close()
+
+
+def test_xchg_reports_cells_above_255_and_short_lists(oracle):
+    """The wrap corpus case through the record exchange: the carry proof fails (sum of t applied != byte sum of
+    the slab) and lime_classify answers LIME_ERR_RETRY; the same for an update list that is too small."""
+    import torch
+    from lime_b200.api import LimeContext, LimeError
+    case = C.wrap_case()
+    v = np.arange(case["n_refs"], dtype=np.uint32)
+    for flat_cap, why in ((1 << 20, "255"), (256, "overflow")):
+        c = LimeContext(0)
+        try:
+            c.set_stream(torch.cuda.current_stream().cuda_stream)
+            c.xchg_alloc(1, 0, case["n_reads"], case["n_refs"], 2, flat_cap, 1 << 20)
+            c.xchg_open(None)
+            sent = torch.zeros(2, 1, dtype=torch.int64, device="cuda:0")
+            for strand in (0, 1):
+                c.load(case["lcp"], case["da"], case["ebwt"], case["n_reads"], case["n_refs"])
+                c.xchg_accumulate(16, 1, strand, sent[strand].data_ptr())
+                c.xchg_apply(strand, sent[strand].data_ptr())
+                c.xchg_choose(strand, 85, 0.0, case["n_reads"])
+            with pytest.raises(LimeError) as e:
+                c.classify(2, case["n_refs"], v, None, 1, False)
+            assert e.value.code == -8 and why in str(e.value)
+        finally:
+            c.close()
+
+
+def test_deferred_strands_equal_the_synchronous_calls(ctx, oracle):
+    """lime_strand_run (no host synchronisation, one choose pass that also sums the bytes and clears the
+    matrix) against lime_cluster_similarity + lime_choose, on the narrow- and the wide-row choose kernels;
+    the wrap case must come back as LIME_ERR_RETRY from lime_classify and run_job must then redo it exactly."""
+    from lime_b200.api import LimeError
+    from lime_b200.pipeline import run_job
+    for n_refs, ebwt_mode, alpha in ((40, 1, 16), (300, 0, 12), (130, 1, 16)):
+        cases = [C.synth_case(f"synth_def{n_refs}_{s}", 900_000 + 77 * s, 9_000, n_refs, seed=310 + n_refs + s, p_long=2e-5, max_seg=30000)
+                 for s in range(2)]
+        v = (np.arange(n_refs, dtype=np.uint32) // 2) + 9
+        strands = [{"ebwt": c["ebwt"], "lcp": c["lcp"], "da": c["da"], "n": c["lcp"].shape[0]} for c in cases]
+        exp, scal = _expected_job(oracle, cases, 9_000, n_refs, 100, alpha, 0.25, ebwt_mode, v, None, 1, False)
+        for rep in range(3):                      # the first strand of a context sizes the buffers, then deferred
+            got, stats = run_job(ctx, strands, 9_000, n_refs, 100, alpha, 0.25, ebwt_mode, v, None, 1, False, deferred=True)
+            assert [tuple(int(x) for x in st) for st in stats] == [tuple(int(x) for x in sc) for sc in scal]
+            for g, e in zip(got, exp):
+                assert np.asarray(g).tobytes() == e.tobytes()
+            for s, c in enumerate(cases):
+                cl, _ = oracle.cluster_detect(c["lcp"], c["da"], 9_000, alpha)
+                b, p = oracle.choose(oracle.similarity(cl, c["da"], c["ebwt"] if ebwt_mode else None, 9_000, n_refs),
+                                     (100 + 1 - alpha), np.float32(0.25))
+                bg, pg = ctx.choose_result(s)
+                assert bg.tobytes() == b.tobytes() and pg.tobytes() == p.tobytes()
+    # cells above 255: the deferred strand is refused, the job falls back to the exact path
+    w = C.wrap_case()
+    vw = np.arange(w["n_refs"], dtype=np.uint32)
+    ws = [{"ebwt": w["ebwt"], "lcp": w["lcp"], "da": w["da"], "n": w["lcp"].shape[0]}] * 2
+    expw, _ = _expected_job(oracle, [w, w], w["n_reads"], w["n_refs"], 100, 16, 0.0, 1, vw, None, 1, False)
+    ctx.load(w["lcp"], w["da"], w["ebwt"], w["n_reads"], w["n_refs"])
+    ctx.strand_run(0, 16, 1, 85, 0.0)
+    ctx.load(w["lcp"], w["da"], w["ebwt"], w["n_reads"], w["n_refs"])
+    ctx.strand_run(1, 16, 1, 85, 0.0)
+    with pytest.raises(LimeError) as e:
+        ctx.classify(2, w["n_refs"], vw, None, 1, False)
+    assert e.value.code == -8
+    gotw, _ = run_job(ctx, ws, w["n_reads"], w["n_refs"], 100, 16, 0.0, 1, vw, None, 1, False, deferred=True)
+    for g, e2 in zip(gotw, expw):
+        assert np.asarray(g).tobytes() == e2.tobytes()
 
 
 def test_sharded_loads_union_equals_whole(ctx, oracle):
@@ -346,12 +427,19 @@ def _expected_job(oracle, cases, n_reads, n_refs, read_len, alpha, beta, ebwt_mo
     return oracle.classify(bins, poss, n_refs, v, m, tax_rank, higher), scal
 
 
-@pytest.mark.parametrize("shape", ["cfg3_ebwt0_4strands", "cfg4_higher_len150_trlcp32", "cfg5_alpha12", "cfg5_alpha20", "cfg5_alpha24"])
+@pytest.mark.parametrize("shape", ["cfg3_ebwt0_4strands", "cfg4_higher_len150_trlcp32", "cfg5_alpha12", "cfg5_alpha20", "cfg5_alpha24",
+                                   "cfg3_930genomes", "cfg4_1000genomes"])
 def test_baseline_config_shapes(ctx, oracle, shape):
     """Reduced-size versions of BASELINE.json configs 3-5 (config 2 is the bench workload, config 1 the exact
     paired-end test above): whole jobs through the fused path, assignments and per-strand scalars bit-exact."""
     from lime_b200.pipeline import run_job, synthetic_lineage
-    if shape == "cfg3_ebwt0_4strands":
+    if shape == "cfg3_930genomes":
+        # the row width of config 3 (930 genomes, lineage Datasets/Reference_database.csv has 930 rows): the wide-row
+        # choose kernel, export / classify over 930-wide rows (ClusterBWT_DA.cpp:385-402, Classify.cpp:171-260)
+        n, n_reads, n_refs, read_len, alpha, ebwt_mode, higher, n_str, kw = 1_200_000, 6_000, 930, 100, 16, 0, False, 4, {}
+    elif shape == "cfg4_1000genomes":
+        n, n_reads, n_refs, read_len, alpha, ebwt_mode, higher, n_str, kw = 1_200_000, 6_000, 1000, 150, 16, 1, True, 4, {"trlcp": 32}
+    elif shape == "cfg3_ebwt0_4strands":
         n, n_reads, n_refs, read_len, alpha, ebwt_mode, higher, n_str, kw = 600_000, 20_000, 93, 100, 16, 0, False, 4, {}
     elif shape == "cfg4_higher_len150_trlcp32":
         n, n_reads, n_refs, read_len, alpha, ebwt_mode, higher, n_str, kw = 700_000, 12_000, 100, 150, 16, 1, True, 4, {"trlcp": 32}

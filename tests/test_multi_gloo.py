@@ -66,42 +66,74 @@ class OracleBackend:
         return self.o.classify(bins, poss, n_refs, v, m, tax_rank, higher)
 
 
-    # ---- peer-memory emulation (PeerJob): every owner's slabs are one shared file; the ranks add in turn,
-    # which plays the role of the kernel's atomic adds into the owner's memory
-    def peer_setup(self, dist, world, rank, rows, n_refs, n_slabs):
-        self.pd = (dist, world, rank, rows)
-        path = lambda r: os.path.join(self.shm_dir, f"slab{r}.u8")
-        mine = np.memmap(path(rank), dtype=np.uint8, mode="w+", shape=(n_slabs, rows, n_refs))
-        mine[:] = 0
-        mine.flush()
+    # ---- emulation of the record exchange (XchgJob): every rank's inbox is one shared file, a source
+    # writes its records {row, genome << 8 | count} into its own region of the owner's file (what
+    # route_kernel does over NVLink); the all-gather of the counts is the barrier, as on the GPUs
+    def xchg_setup(self, dist, world, rank, per, n_refs, n_strands, flat_cap, inbox_cap):
+        self.xd = (dist, world, rank, per, n_strands, inbox_cap)
+        path = lambda r: os.path.join(self.shm_dir, f"inbox{r}.i64")
+        np.memmap(path(rank), dtype=np.int64, mode="w+", shape=(n_strands, world, inbox_cap)).flush()
         dist.barrier()
-        self.slabs = [np.memmap(path(r), dtype=np.uint8, mode="r+", shape=(n_slabs, rows, n_refs)) for r in range(world)]
+        self.inbox = [np.memmap(path(r), dtype=np.int64, mode="r+", shape=(n_strands, world, inbox_cap)) for r in range(world)]
+        self.x_state = {}
 
-    def peer_zero(self):
-        self.slabs[self.pd[2]][:] = 0
-
-    def peer_accumulate(self, alpha, ebwt_mode, slab):
-        dist, world, rank, rows = self.pd
+    def xchg_accumulate(self, alpha, ebwt_mode, strand):
+        dist, world, rank, per, n_strands, cap = self.xd
         n_cl, mx = self.cluster_similarity(alpha, ebwt_mode)
-        for turn in range(world):
-            if turn == rank:
-                for k in range(world):
-                    lo, hi = k * rows, min((k + 1) * rows, self.n_reads)
-                    if hi > lo:
-                        self.slabs[k][slab, :hi - lo] += self.sim[lo:hi]            # uint8 wrap, as the cell
-                        self.slabs[k].flush()
-            dist.barrier()
-        return n_cl, mx, int(np.count_nonzero(self.sim)), int(self.sim.astype(np.int64).sum())
+        sent = np.zeros(world, np.int64)
+        over = False
+        for k in range(world):
+            lo, hi = k * per, min((k + 1) * per, self.n_reads)
+            if hi <= lo:
+                continue
+            r, g = np.nonzero(self.sim[lo:hi])
+            c = self.sim[lo:hi][r, g].astype(np.int64)
+            rec = r.astype(np.int64) | (((g.astype(np.int64) << 8) | c) << 32)
+            sent[k] = rec.shape[0]
+            over |= rec.shape[0] > cap
+            self.inbox[k][strand, rank, :min(rec.shape[0], cap)] = rec[:cap]
+            self.inbox[k].flush()
+        self.x_state[strand] = dict(n_clusters=n_cl, max_len=mx, updates=int(np.count_nonzero(self.sim)), list_slots=0,
+                                    err=4 if over else 0)
+        return self.torch.from_numpy(sent)
 
-    def peer_select(self, slab, total_updates, byte_sums, k):
-        self.sim = np.array(self.slabs[self.pd[2]][slab])
-        byte_sums[k] = int(self.sim.astype(np.int64).sum())
+    def xchg_counts_buffer(self, strand):
+        return self.torch.zeros(self.xd[1] * self.xd[1], dtype=self.torch.int64)
 
-    def peer_zero_slab(self, slab):
-        self.slabs[self.pd[2]][slab] = 0
+    def xchg_apply(self, strand, counts_all):
+        dist, world, rank, per, n_strands, cap = self.xd
+        counts = counts_all.numpy().reshape(world, world)
+        mine = np.memmap(self.inbox[rank].filename, dtype=np.int64, mode="r", shape=(n_strands, world, cap))
+        slab = np.zeros((per, self.n_refs), np.int64)
+        for p in range(world):
+            t = np.array(mine[strand, p, :min(int(counts[p, rank]), cap)])
+            np.add.at(slab, (t & 0xFFFFFFFF, (t >> 40)), (t >> 32) & 0xFF)
+        st = self.x_state[strand]
+        st["applied_t"] = int(slab.sum())
+        self.sim = (slab & 0xFF).astype(np.uint8)               # the uint8 cell wraps
+        st["byte_sum"] = int(self.sim.astype(np.int64).sum())
 
-    def peer_close(self):
-        self.slabs = None
+    def xchg_choose(self, strand, norm, beta, n_own):
+        self.slots[strand] = self.o.choose(self.sim[:n_own], norm, np.float32(beta))
+        self.x_state[strand]["n_records"] = int(self.slots[strand][0].shape[0])
+
+    def xchg_status(self, strand):
+        return dict(self.x_state[strand])
+
+    def xchg_close(self):
+        self.inbox, self.x_state = None, {}
+
+    def classify_checked(self, n_files, n_refs, v, m, tax_rank, higher):
+        """lime_classify after deferred strands: LIME_ERR_RETRY when a cell exceeded 255 or a list overflowed."""
+        from lime_b200._lib import ERR_RETRY, LimeError
+        for s, st in getattr(self, "x_state", {}).items():
+            if st["applied_t"] != st["byte_sum"] or st["err"]:
+                raise LimeError(ERR_RETRY, "deferred strand: a similarity cell exceeded 255")
+        return self.classify_plain(n_files, n_refs, v, m, tax_rank, higher)
+
+
+OracleBackend.classify_plain = OracleBackend.classify
+OracleBackend.classify = OracleBackend.classify_checked
 
 
 def _free_port():
@@ -122,7 +154,7 @@ def _worker(rank, world, port, strands, n_reads, n_refs, read_len, alpha, beta, 
     be = OracleBackend(Oracle(), torch)
     if peer_dir:
         be.shm_dir = peer_dir
-        job = multi.PeerJob(dist, torch, be, rank, world, n_reads, n_refs, len(strands))
+        job = multi.XchgJob(dist, torch, be, rank, world, n_reads, n_refs, len(strands), 1 << 16, 1 << 15)
         job.begin()
     else:
         job = multi.ShardedJob(dist, torch, be, rank, world, n_reads, n_refs)
@@ -141,7 +173,7 @@ def _worker(rank, world, port, strands, n_reads, n_refs, read_len, alpha, beta, 
         job.run_strand(s, job_shards[-1], alpha, beta, 1, read_len)
     typ, tax, sim = job.finish(v, m, 1, m is not None)
     if peer_dir:
-        # the slabs are reused by the next job without an explicit zero + barrier
+        # slabs and inboxes are reused by the next job
         first = [np.array(x) for x in (typ, tax, sim)]
         job.begin()
         for s, sh in enumerate(job_shards):
@@ -209,18 +241,19 @@ def _worker_fallback(rank, world, port, case, alpha, beta, halo, v, q, peer_dir)
     t[2][:b - a] = torch.from_numpy(case["ebwt"][a:b])
     h = multi.exchange_halo(dist, rank, world, t, b - a, halo)
     shard = dict(lcp=t[0], da=t[1], ebwt=t[2], n_own=b - a, n_halo=h, pos_base=a, is_last=rank == world - 1)
-    pj = multi.PeerJob(dist, torch, be, rank, world, case["n_reads"], case["n_refs"], 2)
+    pj = multi.XchgJob(dist, torch, be, rank, world, case["n_reads"], case["n_refs"], 2, 1 << 12, 1 << 10)
     out, stats, route = multi.run_sharded(dist, torch, be, rank, world, case["n_reads"], case["n_refs"], [shard, shard],
-                                          alpha, beta, 1, case["read_len"], v, peer_job=pj)
+                                          alpha, beta, 1, case["read_len"], v, xchg_job=pj)
     pj.close()
     q.put((rank, out, stats, route))
     dist.barrier()
     dist.destroy_process_group()
 
 
-def test_peer_job_falls_back_when_a_cell_exceeds_255(oracle, tmp_path):
-    """Cell sums above 255 (the uint8 wrap of SimArray_): the byte-sum proof of the peer-memory job fails on
-    every rank and run_sharded redoes the job through the exchange route, whose result wraps like the reference."""
+def test_xchg_job_falls_back_when_a_cell_exceeds_255(oracle, tmp_path):
+    """Cell sums above 255 (the uint8 wrap of SimArray_): the byte-sum proof of the record-exchange job fails
+    (the ranks agree on it by an all-reduce) and run_sharded redoes the job through the exact route, whose
+    result wraps like the reference."""
     import torch.multiprocessing as mp
     case = C.wrap_case(n=30000)
     alpha, beta, world = 16, 0.0, 2
@@ -247,7 +280,7 @@ def test_peer_job_falls_back_when_a_cell_exceeds_255(oracle, tmp_path):
 
 
 def test_owner_division_by_multiply_high():
-    """peer_row() of csrc/common.cuh finds a read's owner with q = umulhi(r, magic), magic =
+    """owner_of() of csrc/xchg.cu finds a read's owner with q = umulhi(r, magic), magic =
     min(floor(2^32 / per), 2^32 - 1), and one correction step; restated here and checked against
     integer division over the whole 32-bit range of read ids for awkward divisors."""
     rng = np.random.default_rng(11)

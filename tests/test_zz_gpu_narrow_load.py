@@ -1,16 +1,12 @@
-"""GPU: lime_set_alpha_limit + lime_load(LIME_MEM_HOST) (lcp crosses PCIe as min(lcp, 255) bytes, widened on
-the device, lime_b200/csrc/lime_abi_load.cu) gives the same clusters, similarity matrix and records as the
-plain load and as the oracle.  The file sorts last on purpose: this path was written after the round's GPU
-minutes were spent, so its first run on a B200 is the driver's round-end run -- hence the non-strict xfail
-(an XPASS is the verification; a failure must not hide the rest of the suite)."""
+"""GPU: lime_set_alpha_limit + lime_load(LIME_MEM_HOST) (lcp crosses PCIe as min(lcp, 255) bytes and stays that
+way on the device: the stream kernel's LCP8 variants read the bytes, lime_b200/csrc/lime_abi_load.cu) gives the
+same clusters, similarity matrix and records as the plain load and as the oracle."""
 import numpy as np
 import pytest
 
 import corpus as C
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.xfail(strict=False, reason="narrowed lcp transfer: first GPU run is the round-end run"),
-              pytest.mark.timeout(600)]
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(600)]
 
 CHUNK = 8 << 20      # LIME_STAGE_CHUNK (common.cuh)
 

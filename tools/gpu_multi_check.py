@@ -30,8 +30,11 @@ def main():
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
 
     ok = True
-    for (n, n_reads, n_refs, ebwt_mode, alpha, n_strands, halo) in ((3_000_001, 30_000, 40, 1, 16, 2, 4096),
-                                                                   (2_500_003, 20_000, 9, 0, 12, 4, 70_000)):
+    big = os.environ.get("LIME_CHECK_BIG")          # one case of >= 50 M positions per strand (bench-scale kernels)
+    cases = [(3_000_001, 30_000, 40, 1, 16, 2, 4096), (2_500_003, 20_000, 9, 0, 12, 4, 70_000), (2_000_003, 9_000, 930, 0, 16, 4, 70_000)]
+    if big:
+        cases.append((int(big), 300_000, 100, 1, 16, 2, 70_000))
+    for (n, n_reads, n_refs, ebwt_mode, alpha, n_strands, halo) in cases:
         rows, v, m = synthetic_lineage(n_refs)
         whole, shards = [], []
         for s in range(n_strands):
@@ -75,10 +78,11 @@ def main():
         for s, sh in enumerate(shards):
             job.run_strand(s, sh, alpha, 0.25, ebwt_mode, 100)
         got = job.finish(v, m, 1, True)
-        # the same job with the exchange folded into the kernel (adds over peer memory)
-        pj = multi.PeerJob(dist, torch, be, rank, world, n_reads, n_refs, n_strands)
+        # the same job with the rows on the read owner and the updates routed as records over NVLink (XchgJob)
+        flat_cap, inbox_cap = multi.xchg_capacities(max(sh["n_own"] + sh["n_halo"] for sh in shards), world, density=1.0)
+        pj = multi.XchgJob(dist, torch, be, rank, world, n_reads, n_refs, n_strands, flat_cap, inbox_cap)
         got_p = None
-        for rep in range(2):                       # twice: the slabs are reused
+        for rep in range(2):                       # twice: slabs and inboxes are reused
             pj.begin()
             for s, sh in enumerate(shards):
                 pj.run_strand(s, sh, alpha, 0.25, ebwt_mode, 100)
@@ -92,7 +96,7 @@ def main():
         sc = all(js["n_clusters"] == st[0] and js["max_len"] == st[1] for js, st in zip(job.stats, stats))
         sc = sc and all(js["n_clusters"] == st[0] and js["max_len"] == st[1] for js, st in zip(pj.stats, stats))
         kinds = {chr(t): int((got[0] == t).sum()) for t in np.unique(got[0])}
-        print(f"rank {rank}/{world}: n={n} strands={n_strands} ebwt={ebwt_mode} alpha={alpha}: assignments equal={same} peer-memory job equal={same_p} "
+        print(f"rank {rank}/{world}: n={n} strands={n_strands} ebwt={ebwt_mode} alpha={alpha}: assignments equal={same} record-exchange job equal={same_p} "
               f"scalars equal={sc} {kinds} triples sent={[js['triples_sent'] for js in job.stats]}", flush=True)
         ok = ok and same and same_p and sc
     flag = torch.tensor([0 if ok else 1], device=dev)
