@@ -193,6 +193,7 @@ int lime_similarity(lime_ctx *ctx, int ebwt_mode)
     CK(cudaSetDevice(ctx->device), "cudaSetDevice");
     for (int i = 0; i < 4; i++) ctx->sim_stats[i] = 0;
     ctx->sim_done = true;
+    ctx->sim_clean = false;
     if (ctx->n_clusters == 0 || ctx->n_reads == 0 || ctx->n_refs == 0) return LIME_OK;
     CK(ctx->large_list.reserve(ctx->n_clusters * 8), "cudaMalloc block-path list");
     CK(ctx->k2_scratch.reserve(k2_block_scratch_bytes() * (uint64_t)k2_block_grid()), "cudaMalloc block-path scratch");
