@@ -3,18 +3,23 @@
 
     python bench.py --gpus N --steps K --warmup W            (ours; torchrun for N > 1)
     python bench.py --impl reference --gpus N --steps K ...  (the reference's CPU pipeline)
+    python bench.py --config cfg3|cfg4 ...                   (the north-star shapes, strong scaling)
+    python bench.py --n 1000000000 --alpha 12 ...            (config 5 sweep points on the cfg2 model)
 
-Workload (BASELINE.json configs[1]): single-end synthetic, 2 M reads x 100 bp + 100 genomes,
+Default workload (BASELINE.json configs[1]): single-end synthetic, 2 M reads x 100 bp + 100 genomes,
 N = 402 M eBWT symbols per strand, two strands (F, RC), EBWT=1, alpha=16, beta=0.25, TaxRank=1.
 One step = the whole job: per strand cluster detection (step 1), similarity accumulation and
-clusterChoose (step 2), then Classify over both strands (step 3).  At N > 1 GPUs the position
-range of every strand is sharded contiguously (weak scaling: every GPU holds 402 M symbols per
-strand and the job has N x 2 M reads).
+clusterChoose (step 2), then Classify over all strands (step 3).  At N > 1 GPUs the position
+range of every strand is sharded contiguously (cfg2: weak scaling, every GPU holds 402 M symbols per
+strand and the job has N x 2 M reads; cfg3 / cfg4: strong scaling of one fixed job).
 
 value  = symbols of all strands / step time, inputs resident in HBM (CUDA events).
 e2e    = the same through the C ABI with HOST buffers: pinned host -> device copies of
          lcp/da/ebwt and the device -> host copy of the assignments inside the timed region.
-The oracle / reference binaries are used only for cpu_baseline and --impl reference.
+parity = BASELINE.md's gate: before a value is printed the GPU result is compared byte for byte with the
+         reference's files (.out, .res.bin, .res.pos, CSV) of the SAME input (N = 1), resp. with the
+         single-GPU job (N > 1).  A mismatch aborts the run.
+The oracle / reference binaries are used only for cpu_baseline, the parity gate and --impl reference.
 """
 import argparse
 import json
@@ -32,18 +37,34 @@ if ROOT not in sys.path:
 
 import numpy as np  # noqa: E402
 
-WORKLOAD = dict(name="cfg2 single-end synthetic: 2M reads x 100bp + 100 genomes, 402M symbols/strand, "
-                     "2 strands (F,RC), EBWT=1, alpha=16, beta=0.25, TaxRank=1",
-                n=402_000_000, n_reads=2_000_000, n_refs=100, read_len=100, alpha=16, beta=0.25,
-                ebwt=1, n_strands=2, tax_rank=1, seed=20261104 + 2)
-CPU_SAMPLE_N = 1 << 28          # positions per strand of the CPU-timed prefix sample (~4.5 s per run on 16 cores)
 METRIC = "ebwt_symbols_per_s"
 UNIT = "symbols/s"
+HALO = 70_000          # positions a shard sees of the next one: more than sizeMaxBuf (65536, ClusterBWT_DA.cpp:558)
+BLOCKS = 8             # strong-scaled configs: a strand is 8 independent draws of the runs model, whatever N
+
+CONFIGS = {
+    # BASELINE.json configs[1]; the line the driver records
+    "cfg2": dict(name="cfg2 single-end synthetic: 2M reads x 100bp + 100 genomes, 402M symbols/strand, "
+                      "2 strands (F,RC), EBWT=1, alpha=16, beta=0.25, TaxRank=1",
+                 n=402_000_000, n_reads=2_000_000, n_refs=100, read_len=100, alpha=16, beta=0.25, ebwt=1, n_strands=2,
+                 tax_rank=1, higher=False, trlcp=None, scaling="weak", seed=20261104 + 2),
+    # configs[2]: setA2 shape, 4 strands x 1.5 G symbols, EBWT=0, 930 genomes (the row count of
+    # Datasets/Reference_database.csv), strong scaling over 1-8 GPUs
+    "cfg3": dict(name="cfg3 setA2-shape paired-end: 4 strands x 1.5G symbols, 10M reads x 100bp, 930 genomes, EBWT=0, "
+                      "alpha=16, beta=0.25, TaxRank=1",
+                 n=1_500_000_000, n_reads=10_000_000, n_refs=930, read_len=100, alpha=16, beta=0.25, ebwt=0, n_strands=4,
+                 tax_rank=1, higher=False, trlcp=None, scaling="strong", seed=20261104 + 3),
+    # configs[3]: the north-star run, 10 G symbols (4 strands x 2.5 G), HIGHER=1, lcp truncated at 32
+    "cfg4": dict(name="cfg4 HIGHER=1 paired-end: 4 strands x 2.5G symbols (10G total), 10M reads x 150bp, 1000 genomes, "
+                      "EBWT=1, lcp truncated at 32, alpha=16, beta=0.25, TaxRank=1",
+                 n=2_500_000_000, n_reads=10_000_000, n_refs=1000, read_len=150, alpha=16, beta=0.25, ebwt=1, n_strands=4,
+                 tax_rank=1, higher=True, trlcp=32, scaling="strong", seed=20261104 + 4),
+}
 
 
 def _small(w, n, n_reads):
     w = dict(w)
-    w.update(n=n, n_reads=n_reads, name=f"REDUCED test shape n={n} n_reads={n_reads} (not the benchmark)")
+    w.update(n=n, n_reads=n_reads, name=f"REDUCED test shape n={n} n_reads={n_reads} of {w['name']} (not the benchmark)")
     return w
 
 
@@ -112,13 +133,27 @@ def _extend_for_clocks(step, t0, min_seconds=0.7):
     return time.time()
 
 
+def _peak():
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        if "hbm_gbs" in peaks:
+            return float(peaks["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
 # ------------------------------------------------------------------------------------------------
-# the reference's CPU pipeline on a bounded sample (oracle/_ref binaries; the one place bench.py
-# executes anything under oracle/)
+# inputs
 # ------------------------------------------------------------------------------------------------
-def _lineage_file(path, n_refs):
+def _lineage(w):
     from lime_b200.pipeline import synthetic_lineage
-    rows, v, m = synthetic_lineage(n_refs)
+    rows, v, m = synthetic_lineage(w["n_refs"])
+    return rows, v, (m if w["higher"] else None)
+
+
+def _lineage_file(path, w):
+    rows, v, m = _lineage(w)
     with open(path, "w") as f:
         f.write("Acc;Species_TaxID;Genus_TaxID;Family_TaxID;Order_TaxID;Class_TaxID;Phylum_TaxID\n")
         for r in rows:
@@ -126,16 +161,51 @@ def _lineage_file(path, n_refs):
     return v, m
 
 
+def _block_arrays(w, s, blk, n_blk, dev, lo=0, hi=None):
+    """Positions [lo, hi) of block `blk` of strand s: an independent draw of the runs model with the job's read
+    and genome ids (strong-scaled configs: the strand is the concatenation of BLOCKS blocks, whatever N)."""
+    from lime_b200 import datagen
+    read_frac = w["n_reads"] * (w["read_len"] + 1) / float(w["n"])
+    return datagen.synth_arrays(n_blk, w["n_reads"], w["n_refs"], w["read_len"], seed=w["seed"] + 1000 * s + 17 * blk,
+                                device=dev, lo=lo, hi=hi, read_frac=read_frac, trlcp=w["trlcp"])
+
+
+def _strand_arrays(w, s, dev, hi=None):
+    """A whole strand on one device (N = 1)."""
+    import torch
+    from lime_b200 import datagen
+    if w["scaling"] == "weak":
+        return datagen.synth_arrays(w["n"], w["n_reads"], w["n_refs"], w["read_len"], seed=w["seed"] + 1000 * s, device=dev,
+                                    trlcp=w["trlcp"], hi=hi)
+    n_blk = w["n"] // BLOCKS
+    n = n_blk * BLOCKS if hi is None else min(hi, n_blk * BLOCKS)
+    e = torch.empty(n, dtype=torch.uint8, device=dev)
+    l = torch.empty(n, dtype=torch.int32, device=dev)
+    d = torch.empty(n, dtype=torch.int32, device=dev)
+    for b in range(BLOCKS):
+        a0 = b * n_blk
+        if a0 >= n:
+            break
+        k = min(n_blk, n - a0)
+        eb, lb, db = _block_arrays(w, s, b, n_blk, dev, hi=k)
+        e[a0:a0 + k] = eb; l[a0:a0 + k] = lb; d[a0:a0 + k] = db
+        del eb, lb, db
+    return e, l, d
+
+
 def _scratch_dir():
     for base in ("/dev/shm", tempfile.gettempdir()):
         try:
-            if os.path.isdir(base) and shutil.disk_usage(base).free > (8 << 30):
+            if os.path.isdir(base) and shutil.disk_usage(base).free > (12 << 30):
                 return tempfile.mkdtemp(prefix="lime_bench_", dir=base)
         except OSError:
             pass
     return tempfile.mkdtemp(prefix="lime_bench_")
 
 
+# ------------------------------------------------------------------------------------------------
+# the reference's CPU pipeline (oracle/_ref binaries; the one place bench.py executes anything under oracle/)
+# ------------------------------------------------------------------------------------------------
 class CpuReference:
     """Runs the unmodified reference (ClusterLCP, ClusterBWT_DA, Classify from oracle/_ref) with
     the schedule of LiME_paired.sh: ClusterLCP of all strands concurrently (:44-53), ClusterBWT_DA
@@ -146,19 +216,20 @@ class CpuReference:
         self.ref = Reference()
         self.kind = "reference" if self.ref.available() else "port"
         self.w, self.sample_n = w, min(sample_n, w["n"])
+        self.same_config = self.sample_n == w["n"]
         self.cores = os.cpu_count() or 1
         self.dir = _scratch_dir()
         self.fastas = []
 
     def write_inputs(self, strands_host):
-        """strands_host: list of (ebwt u8, lcp u32, da u32) numpy prefixes."""
+        """strands_host: list of (ebwt u8, lcp u32, da u32) numpy arrays."""
         from lime_b200 import datagen
         for s, (e, l, d) in enumerate(strands_host):
             fasta = os.path.join(self.dir, f"strand{s}+Refs.fasta")
             datagen.write_strand(fasta, e, l, d)
             self.fastas.append(fasta)
         self.lineage = os.path.join(self.dir, "lineage.csv")
-        self.v, self.m = _lineage_file(self.lineage, self.w["n_refs"])
+        self.v, self.m = _lineage_file(self.lineage, self.w)
         self.host = strands_host
 
     def step(self):
@@ -178,7 +249,8 @@ class CpuReference:
                                    stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True)
                 assert r.returncode == 0, r.stderr
             out = os.path.join(self.dir, "out.csv")
-            r = subprocess.run([exe("Classify_higher0"), str(len(self.fastas))] + [f + ".res" for f in self.fastas] +
+            r = subprocess.run([exe("Classify_higher1" if w["higher"] else "Classify_higher0"), str(len(self.fastas))] +
+                               [f + ".res" for f in self.fastas] +
                                [str(w["n_reads"]), str(w["n_refs"]), out, self.lineage, str(w["tax_rank"]),
                                 str(self.cores)], cwd=self.dir, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True)
             assert r.returncode == 0, r.stderr
@@ -192,12 +264,23 @@ class CpuReference:
                 sim = orc.similarity(cl, d, e if w["ebwt"] else None, w["n_reads"], w["n_refs"])
                 b, p = orc.choose(sim, norm_of(w["read_len"], w["alpha"]), np.float32(w["beta"]))
                 bins.append(b); poss.append(p)
-            orc.classify(bins, poss, w["n_refs"], self.v, None, w["tax_rank"], False)
+            orc.classify(bins, poss, w["n_refs"], self.v, self.m, w["tax_rank"], w["higher"])
         return time.perf_counter() - t0
 
+    def files_of(self, s):
+        """The reference's outputs of strand s after a step: (.out bytes, .res.bin bytes, .res.pos bytes)."""
+        f = self.fastas[s]
+        stem = f[:f.find(".fasta")]
+        return open(stem + ".out", "rb").read(), open(f + ".res.bin", "rb").read(), open(f + ".res.pos", "rb").read()
+
+    def csv(self):
+        return open(os.path.join(self.dir, "out.csv"), "rb").read()
+
     def describe(self):
-        return (f"prefix of {self.sample_n} positions per strand x {len(self.fastas)} strands of the same workload "
-                f"(all {self.w['n_reads']} reads, {self.w['n_refs']} genomes), files in {os.path.dirname(self.dir) or self.dir}, "
+        what = ("the whole workload" if self.same_config else
+                f"prefix of {self.sample_n} positions per strand (extrapolated per symbol)")
+        return (f"{what}: {self.sample_n} positions x {len(self.fastas)} strands (all {self.w['n_reads']} reads, "
+                f"{self.w['n_refs']} genomes), files in {os.path.dirname(self.dir) or self.dir}, "
                 f"page cache warm; ClusterLCP x{len(self.fastas)} concurrent, ClusterBWT_DA x{len(self.fastas)} sequential, "
                 f"Classify {len(self.fastas)}; threads={self.cores if self.kind == 'reference' else 1}")
 
@@ -207,12 +290,11 @@ class CpuReference:
 
 def _host_sample(w, sample_n, device):
     """The first sample_n positions of every strand, as numpy arrays in the file formats."""
-    from lime_b200 import datagen
     out = []
     for s in range(w["n_strands"]):
-        e, l, d = datagen.synth_arrays(w["n"], w["n_reads"], w["n_refs"], w["read_len"], seed=w["seed"] + 1000 * s,
-                                       device=device, hi=sample_n)
+        e, l, d = _strand_arrays(w, s, device, hi=sample_n)
         out.append((e.cpu().numpy(), l.cpu().numpy().view(np.uint32), d.cpu().numpy().view(np.uint32)))
+        del e, l, d
     return out
 
 
@@ -234,8 +316,8 @@ def run_reference_arm(args, w):
         line = {
             "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": w["name"], "sample": cpu.describe()},
+            "higher_is_better": True, "scaling": w["scaling"], "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": w["name"], "sample": cpu.describe(), "same_config": cpu.same_config},
             "reads_per_s": w["n_reads"] * (cpu.sample_n / w["n"]) * args.steps / total,
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cpu.cores if cpu.kind == "reference" else 1,
                              "kind": cpu.kind, "sample": cpu.describe()},
@@ -254,28 +336,48 @@ def _alg_bytes(kname, st, w):
     """Algorithmic bytes of one launch of kernel family `kname` for a strand with stats st
     (DESIGN.md 'kernels')."""
     E = 1 if w["ebwt"] else 0
-    n, C, P, nr, ng = st["n"], st["n_clusters"], st["cluster_positions"], st["n_reads_total"], w["n_refs"]
+    n, nr, ng = st["n"], st["n_reads_total"], w["n_refs"]
     if kname == "k1_detect":
-        return 8 * n + 16 * C
-    if kname in ("k2_warp", "k2_block"):
-        return (4 + E) * P + 16 * C          # da (+ebwt) of the clustered positions + the records
+        return 8 * n + 16 * st["n_clusters"]
     if kname == "k12_fused":
         return (8 + E) * n
-    if kname == "k3_count":
-        return nr * ng + 8 * nr
-    if kname == "k3_emit":
-        return nr * ng + 8 * st["n_records"]
+    if kname == "k3_choose":
+        return nr * ng + 8 * st["n_records"] + 8 * nr
     if kname == "k3_classify":
         return 8 * st["n_records"] + 8 * nr + 9 * nr
     return 0
 
 
+def _parity_gate(ctx, cpu, w, out, stats):
+    """.out, .res.bin, .res.pos of every strand and the final CSV, byte for byte against
+    the reference's files of the same input.  Returns the parity record; raises SystemExit on a mismatch."""
+    from lime_b200 import api
+    files = []
+    for s in range(w["n_strands"]):
+        out_ref, bin_ref, pos_ref = cpu.files_of(s)
+        n_cl, max_len, n_rec = (int(x) for x in stats[s][:3])
+        aux = (np.array([w["n_reads"], w["n_refs"], w["alpha"]], dtype="<u4").tobytes() +
+               np.array([max_len, n_cl], dtype="<u8").tobytes())                       # ClusterLCP.cpp:304-308
+        bin_g, pos_g = ctx.choose_result(s)
+        for name, a, b in ((f"strand{s}.out", aux, out_ref), (f"strand{s}.res.bin", bin_g.tobytes(), bin_ref),
+                           (f"strand{s}.res.pos", pos_g.tobytes(), pos_ref)):
+            if a != b:
+                raise SystemExit(f"bench.py: PARITY FAILED on {name} ({len(a)} vs {len(b)} bytes): no value is reported")
+            files.append(name)
+        del bin_g, pos_g
+    path = os.path.join(cpu.dir, "gpu.csv")
+    api.write_csv(path, out[0], out[1], out[2])
+    if open(path, "rb").read() != cpu.csv():
+        raise SystemExit("bench.py: PARITY FAILED on the classification CSV: no value is reported")
+    files.append("out.csv")
+    return {"checked": True, "against": "the unmodified reference (oracle/_ref) on the same input, byte for byte",
+            "files": files, "n": cpu.sample_n, "strands": w["n_strands"]}
+
+
 def run_ours(args, w):
     import torch
-    import torch.distributed as dist
-    from lime_b200 import datagen
     from lime_b200.api import LimeContext, MEM_DEVICE, MEM_HOST
-    from lime_b200.pipeline import run_job, synthetic_lineage
+    from lime_b200.pipeline import run_job
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -290,38 +392,63 @@ def run_ours(args, w):
     ctx = LimeContext(local)
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
-    rows, v, m = synthetic_lineage(w["n_refs"])
+    rows, v, m = _lineage(w)
+    use_ebwt = bool(w["ebwt"])
 
     # ---- synthetic inputs, resident in HBM ----------------------------------------------------
     strands_dev, keep = [], []
     for s in range(w["n_strands"]):
-        e, l, d = datagen.synth_arrays(w["n"], w["n_reads"], w["n_refs"], w["read_len"], seed=w["seed"] + 1000 * s,
-                                       device=dev)
+        e, l, d = _strand_arrays(w, s, dev)
+        if not use_ebwt:
+            e = None                                     # the EBWT=0 build never opens .ebwt (ClusterBWT_DA.cpp:16-18)
         keep.append((e, l, d))
-        strands_dev.append({"ebwt": e.data_ptr(), "lcp": l.data_ptr(), "da": d.data_ptr(), "n": w["n"]})
+        strands_dev.append({"ebwt": e.data_ptr() if e is not None else None, "lcp": l.data_ptr(), "da": d.data_ptr(),
+                            "n": int(l.shape[0])})
+    n_pos = strands_dev[0]["n"]
     torch.cuda.synchronize()
 
     def step_resident():
         return run_job(ctx, strands_dev, w["n_reads"], w["n_refs"], w["read_len"], w["alpha"], w["beta"], w["ebwt"],
-                       v, None, w["tax_rank"], False, mem=MEM_DEVICE, fused=not args.unfused)
+                       v, m, w["tax_rank"], w["higher"], mem=MEM_DEVICE, fused=not args.unfused)
 
     # ---- warm-up (also gathers the per-strand statistics the roofline needs) -------------------
-    for _ in range(max(args.warmup, 1)):
+    for _ in range(max(args.warmup, 3)):
         out, stats = step_resident()
-    strand_stats = []
-    for s in range(w["n_strands"]):
-        # cluster statistics of strand s (outside the timed region)
-        ctx.load(strands_dev[s]["lcp"], strands_dev[s]["da"], strands_dev[s]["ebwt"], w["n_reads"], w["n_refs"],
-                 mem=MEM_DEVICE, n_total=w["n"])
-        n_cl, max_len = ctx.cluster_detect(w["alpha"])
-        cl = ctx.clusters()
-        strand_stats.append({"n": w["n"], "n_clusters": int(n_cl), "max_len": int(max_len),
-                             "cluster_positions": int(cl["len"].sum()), "n_records": int(stats[s][2]),
-                             "n_reads_total": w["n_reads"]})
-        del cl
-    out, stats = step_resident()          # leave the slots in a consistent state
-    out = tuple(x.copy() for x in out)    # classify() returns views of context-owned pinned buffers
+    out = tuple(np.array(x, copy=True) for x in out)    # classify() returns views of context-owned pinned buffers
+    stats = [tuple(int(x) for x in st) for st in stats]
     kinds = {chr(t): int((out[0] == t).sum()) for t in np.unique(out[0])}
+    strand_stats = [{"n": n_pos, "n_clusters": st[0], "max_len": st[1], "n_records": st[2], "n_reads_total": w["n_reads"]}
+                    for st in stats]
+
+    # ---- CPU baseline beside it + the parity gate (rank 0, N = 1 only) -------------------------------------
+    cpu_baseline, parity = None, {"checked": False, "why": "--no-cpu"}
+    if not args.no_cpu:
+        cpu = CpuReference(w, args.cpu_sample)
+        try:
+            k = cpu.sample_n
+            sample = [((e[:k].cpu().numpy() if e is not None else np.zeros(k, np.uint8)), l[:k].cpu().numpy().view(np.uint32),
+                       d[:k].cpu().numpy().view(np.uint32)) for (e, l, d) in keep]
+            cpu.write_inputs(sample)
+            del sample
+            cpu.step()                                   # warms the page cache
+            t = cpu.step()
+            cpu_baseline = {"value": cpu.sample_n * w["n_strands"] / t, "unit": UNIT,
+                            "cores": cpu.cores if cpu.kind == "reference" else 1, "kind": cpu.kind,
+                            "sample": cpu.describe(), "seconds": t, "same_config": cpu.same_config}
+            if cpu.kind == "reference":
+                if cpu.same_config:
+                    parity = _parity_gate(ctx, cpu, w, out, stats)
+                else:
+                    # the GPU path on the very prefix the reference ran on
+                    pre = [{"ebwt": sd["ebwt"], "lcp": sd["lcp"], "da": sd["da"], "n": k} for sd in strands_dev]
+                    out_p, stats_p = run_job(ctx, pre, w["n_reads"], w["n_refs"], w["read_len"], w["alpha"], w["beta"], w["ebwt"],
+                                             v, m, w["tax_rank"], w["higher"], mem=MEM_DEVICE, fused=not args.unfused)
+                    parity = _parity_gate(ctx, cpu, w, out_p, stats_p)
+                    step_resident()                      # slots back to the full job
+            else:
+                parity = {"checked": False, "why": "oracle/_ref not built on this box"}
+        finally:
+            cpu.close()
 
     # ---- timed region: K steps, resident inputs -------------------------------------------------
     clocks = ClockSampler(local)
@@ -338,30 +465,31 @@ def run_ours(args, w):
         step_resident()
     ev1.record(stream)
     torch.cuda.synchronize()
-    t1 = time.time()
     ms_total = ev0.elapsed_time(ev1)
     launches = ctx.launch_count() - l0
     prof = ctx.prof()
     ctx.prof_enable(False)
+    # the same steps again without the per-launch events of the kernel profile (they cost host time)
+    torch.cuda.synchronize()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step_resident()
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    ms_plain = ev0.elapsed_time(ev1)
     t1x = _extend_for_clocks(lambda: (step_resident(), torch.cuda.synchronize()), t0)
     clk = clocks.summary(t0, t1x)
     clk["window"] = "timed region + untimed repeats of the same step up to 0.7 s (nvidia-smi -lms 50)"
 
-    ms_step = ms_total / args.steps
-    symbols = w["n"] * w["n_strands"]
+    ms_step = min(ms_total, ms_plain) / args.steps
+    symbols = n_pos * w["n_strands"]
     value = symbols / (ms_step * 1e-3)
 
     # ---- roofline of the dominant kernel ----------------------------------------------------------
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    peak_gbs, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    peak_gbs, peak_src = _peak()
     kern = {k: x for k, x in prof.items() if x["launches"]}
     kernel_ms_total = sum(x["ms"] for x in kern.values())
     top = max(kern, key=lambda k: kern[k]["ms"])
-    per_strand_launches = kern[top]["launches"] / (args.steps * (1 if top == "k3_classify" else w["n_strands"]))
     if top == "k3_classify":
         agg = dict(strand_stats[0]); agg["n_records"] = sum(s["n_records"] for s in strand_stats)
         alg = _alg_bytes(top, agg, w) * args.steps
@@ -370,48 +498,54 @@ def run_ours(args, w):
     avg_launch_ms = kern[top]["ms"] / kern[top]["launches"]
     alg_per_launch = alg / kern[top]["launches"]
     achieved = alg_per_launch / (avg_launch_ms * 1e-3) / 1e9
-    traffic = None
+    traffic, traffic_src = None, None
     try:
         tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        traffic = tr.get(top, {}).get("dram_bytes_per_launch")
+        ent = tr.get(top, {})
+        if ent.get("workload", "cfg2") == args.config and not args.n:
+            traffic = ent.get("dram_bytes_per_launch")
+            traffic_src = "static: profiles/traffic.json (%s), one ncu --set full capture of this kernel on this workload" % ent.get("capture", "?")
     except Exception:
         pass
+    job_alg = sum((8 + w["ebwt"]) * s["n"] for s in strand_stats)
     roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
-                "frac": achieved / peak_gbs, "traffic": traffic, "peak_source": peak_src,
-                "alg_bytes_per_launch": alg_per_launch, "avg_launch_ms": avg_launch_ms,
-                "launches_per_strand": per_strand_launches,
+                "frac": achieved / peak_gbs, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                "alg_bytes_per_launch": alg_per_launch, "alg_bytes_per_symbol": 8 + w["ebwt"], "avg_launch_ms": avg_launch_ms,
+                "launches_per_step": kern[top]["launches"] / args.steps,
                 "kernel_share_of_step": kern[top]["ms"] / ms_total,
                 "kernels_ms_per_step": {k: x["ms"] / args.steps for k, x in kern.items()},
                 "kernel_time_fraction_of_step": kernel_ms_total / ms_total,
-                "job_alg_bytes_per_step": sum((8 + w["ebwt"]) * s["n"] for s in strand_stats),
-                "job_frac_of_peak": sum((8 + w["ebwt"]) * s["n"] for s in strand_stats) / (ms_step * 1e-3) / 1e9 / peak_gbs}
+                "ms_per_step_with_kernel_events": ms_total / args.steps, "ms_per_step_plain": ms_plain / args.steps,
+                "job_alg_bytes_per_step": job_alg,
+                "job_frac_of_peak": job_alg / (ms_step * 1e-3) / 1e9 / peak_gbs}
 
     # ---- e2e: host buffers through the C ABI ----------------------------------------------------------
     e2e = None
-    if not args.no_e2e:
+    host_bytes = sum((8 + w["ebwt"]) * sd["n"] for sd in strands_dev)
+    if not args.no_e2e and (host_bytes <= (24 << 30) or args.e2e):
         strands_host, pins = [], []
         for (e, l, d) in keep:
-            pe = torch.empty(e.shape, dtype=e.dtype, pin_memory=True); pe.copy_(e)
+            pe = None
+            if e is not None:
+                pe = torch.empty(e.shape, dtype=e.dtype, pin_memory=True); pe.copy_(e)
             pl = torch.empty(l.shape, dtype=l.dtype, pin_memory=True); pl.copy_(l)
             pd = torch.empty(d.shape, dtype=d.dtype, pin_memory=True); pd.copy_(d)
             pins.append((pe, pl, pd))
-            strands_host.append({"ebwt": pe.numpy(), "lcp": pl.numpy().view(np.uint32), "da": pd.numpy().view(np.uint32),
-                                 "n": w["n"]})
+            strands_host.append({"ebwt": pe.numpy() if pe is not None else None, "lcp": pl.numpy().view(np.uint32),
+                                 "da": pd.numpy().view(np.uint32), "n": int(pl.shape[0])})
         torch.cuda.synchronize()
 
         def step_host():
             return run_job(ctx, strands_host, w["n_reads"], w["n_refs"], w["read_len"], w["alpha"], w["beta"],
-                           w["ebwt"], v, None, w["tax_rank"], False, mem=MEM_HOST, fused=not args.unfused)
-        h2d = sum((8 + w["ebwt"]) * w["n"] for _ in range(w["n_strands"])) + 4 * w["n_refs"]
+                           w["ebwt"], v, m, w["tax_rank"], w["higher"], mem=MEM_HOST, fused=not args.unfused)
         d2h = 9 * w["n_reads"]
-        e2e_steps = max(1, min(args.steps, 5))
+        e2e_steps = max(1, args.steps)
 
-        def time_host(note, h2d_bytes, check_counts=False):
+        def time_host(note, h2d_bytes):
             out_h, st_h = step_host()
             for a, b in zip(out, out_h):
-                assert a.tobytes() == b.tobytes(), "host-buffer path disagrees with the resident path"
-            if check_counts:
-                assert [tuple(x) for x in st_h] == [tuple(x) for x in stats], "per-strand counts disagree with the resident path"
+                assert a.tobytes() == np.asarray(b).tobytes(), "host-buffer path disagrees with the resident path"
+            assert [tuple(int(y) for y in x) for x in st_h] == stats, "per-strand counts disagree with the resident path"
             torch.cuda.synchronize()
             ev0.record(stream)
             tw0 = time.perf_counter()
@@ -423,66 +557,41 @@ def run_ours(args, w):
             e_ms = max(ev0.elapsed_time(ev1), (tw1 - tw0) * 1e3) / e2e_steps
             return {"value": symbols / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e_ms, "steps": e2e_steps,
-                    "reads_per_s": w["n_reads"] / (e_ms * 1e-3), "note": note}
-        e2e = time_host("lime_load(LIME_MEM_HOST) from pinned host arrays per strand + assignments copied back; "
-                        "PCIe-bound", h2d)
-
-    # ---- CPU baseline beside it (rank 0, N = 1 only) ----------------------------------------------------
-    cpu_baseline = None
-    if not args.no_cpu:
-        cpu = CpuReference(w, args.cpu_sample)
-        try:
-            sample = []
-            for (e, l, d) in keep:
-                k = cpu.sample_n
-                sample.append((e[:k].cpu().numpy(), l[:k].cpu().numpy().view(np.uint32), d[:k].cpu().numpy().view(np.uint32)))
-            cpu.write_inputs(sample)
-            cpu.step()                                   # warms the page cache
-            t = cpu.step()
-            cpu_baseline = {"value": cpu.sample_n * w["n_strands"] / t, "unit": UNIT,
-                            "cores": cpu.cores if cpu.kind == "reference" else 1, "kind": cpu.kind,
-                            "sample": cpu.describe(), "seconds": t}
-        finally:
-            cpu.close()
+                    "reads_per_s": w["n_reads"] / (e_ms * 1e-3), "h2d_GBps": h2d_bytes / (e_ms * 1e-3) / 1e9, "note": note}
+        modes = {}
+        if w["alpha"] <= 255 and not args.no_narrow:
+            # the drop-in executables know alpha from argv and promise it (lime_set_alpha_limit): lcp crosses PCIe
+            # as min(lcp, 255) bytes, narrowed on host threads inside the timed region, and stays bytes on the device
+            ctx.set_alpha_limit(w["alpha"])
+            try:
+                modes["narrow_lcp"] = time_host(
+                    "lime_set_alpha_limit(alpha) + lime_load(LIME_MEM_HOST) per strand from pinned host arrays: lcp narrowed to "
+                    "bytes by %d host threads inside the timed region; assignments copied back; PCIe-bound"
+                    % max(1, ctx.lib.lime_host_threads() - 1), host_bytes - 3 * symbols + 4 * w["n_refs"])
+            finally:
+                ctx.set_alpha_limit(0)
+        if args.e2e_plain or not modes:
+            modes["plain"] = time_host("lime_load(LIME_MEM_HOST) per strand from pinned host arrays + assignments copied back; "
+                                       "PCIe-bound", host_bytes + 4 * w["n_refs"])
+        best = max(modes, key=lambda k: modes[k]["value"])
+        e2e = dict(modes[best])
+        e2e["mode"] = best
+        e2e["modes"] = {k: {q: x[q] for q in ("value", "ms_per_step", "h2d_bytes_per_step", "h2d_GBps")} for k, x in modes.items()}
+        del pins, strands_host
+    elif not args.no_e2e:
+        e2e = {"value": None, "note": "skipped: %.0f GB of page-locked host arrays per step; run with --e2e" % (host_bytes / 1e9)}
     clocks.stop()
 
-    # ---- e2e again with the narrowed lcp transfer (lime_set_alpha_limit): the same host arrays, lcp crosses
-    # PCIe as min(lcp, 255) bytes (narrowed on host threads inside the timed region) and is widened on
-    # the device.  Same call sequence and results (checked against the resident path first); the faster
-    # verified mode is the e2e figure, both are reported.  Last GPU work of the run, and a failure
-    # here only loses this leg.
-    if e2e is not None and w["alpha"] <= 255 and not args.no_narrow:
-        plain = dict(e2e)
-        try:
-            ctx.set_alpha_limit(w["alpha"])
-            h2d_n = sum((5 + w["ebwt"]) * w["n"] for _ in range(w["n_strands"])) + 4 * w["n_refs"]
-            nar = time_host("lime_set_alpha_limit(alpha) + lime_load(LIME_MEM_HOST): lcp narrowed to bytes by %d host "
-                            "threads inside the timed region, widened on the device; pinned host arrays; assignments "
-                            "copied back" % max(1, ctx.lib.lime_host_threads() - 1), h2d_n, check_counts=True)
-            ctx.set_alpha_limit(0)
-            if nar["value"] > plain["value"]:
-                e2e = nar
-            e2e["modes"] = {"plain": {k: plain[k] for k in ("value", "ms_per_step", "h2d_bytes_per_step")},
-                            "narrow_lcp": {k: nar[k] for k in ("value", "ms_per_step", "h2d_bytes_per_step")}}
-        except BaseException as ex:                      # noqa: BLE001 -- report, keep the plain figure
-            try:
-                ctx.set_alpha_limit(0)
-            except Exception:
-                pass
-            e2e = plain
-            e2e["modes"] = {"plain": {k: plain[k] for k in ("value", "ms_per_step", "h2d_bytes_per_step")},
-                            "narrow_lcp": {"error": "%s: %s" % (type(ex).__name__, ex)}}
-    if e2e is not None:
-        del pins, strands_host
-
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 1),
-        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": w["scaling"], "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
-        "config": {"workload": w["name"], "l2": "inputs (3.6 GB per strand) are larger than L2; no flush needed",
+        "config": {"workload": w["name"], "config": args.config, "alpha": w["alpha"],
+                   "l2": "inputs (%.1f GB per strand) are larger than L2; no flush needed" % ((8 + w["ebwt"]) * n_pos / 1e9),
                    "parallelism": "1 GPU", "symbols_per_step": symbols, "reads_per_step": w["n_reads"],
                    "strand_stats": strand_stats, "assignments": kinds},
         "reads_per_s": w["n_reads"] / (ms_step * 1e-3),
+        "parity": parity,
         "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches),
         "clocks": clk,
     }
@@ -491,16 +600,18 @@ def run_ours(args, w):
 
 
 class _SyncTimer:
-    """Per-phase wall timer with a device synchronise on both sides (diagnostic step only)."""
+    """Per-phase wall timer with a device synchronise and a barrier on both sides (diagnostic step only)."""
 
-    def __init__(self, torch):
-        self.torch, self.ms = torch, {}
+    def __init__(self, torch, dist):
+        self.torch, self.dist, self.ms = torch, dist, {}
 
     def __call__(self, name):
         outer = self
 
         class T:
             def __enter__(self_inner):
+                outer.torch.cuda.synchronize()
+                outer.dist.barrier()
                 outer.torch.cuda.synchronize()
                 self_inner.t = time.perf_counter()
 
@@ -511,85 +622,154 @@ class _SyncTimer:
         return T()
 
 
-class _HostTimer:
-    """Per-phase host wall time WITHOUT device synchronisation (where the host thread spends a step)."""
+def _make_shards(w, world, rank, dev):
+    """This rank's shard of every strand, halo in place.  weak: every rank holds one 402 M-position shard
+    (second half of block k ++ first half of block k+1, so shard boundaries fall INSIDE segments and clusters
+    straddle them), the job has world x n_reads reads.  strong: the strand is BLOCKS fixed blocks, rank k owns
+    blocks [k * BLOCKS / world, (k+1) * BLOCKS / world)."""
+    import torch
+    from lime_b200 import datagen
+    shards = []
+    if w["scaling"] == "weak":
+        S = w["n"]
+        n_reads = w["n_reads"] * world
+        read_frac = w["n_reads"] * (w["read_len"] + 1) / float(S)
+        for s in range(w["n_strands"]):
+            bufs = [torch.zeros(S + HALO, dtype=torch.uint8, device=dev), torch.zeros(S + HALO, dtype=torch.int32, device=dev),
+                    torch.zeros(S + HALO, dtype=torch.int32, device=dev)]
+            half = S // 2
+            last = rank == world - 1
+            for blk, lo, hi, at in ((rank, half, S, 0), (rank + 1, 0, half, S - half), (rank + 1, half, half + (0 if last else HALO), S)):
+                if hi <= lo:
+                    continue
+                e, l, d = datagen.synth_arrays(S, n_reads, w["n_refs"], w["read_len"], seed=w["seed"] + 1000 * s + 17 * blk,
+                                               device=dev, lo=lo, hi=hi, read_frac=read_frac, trlcp=w["trlcp"])
+                bufs[0][at:at + hi - lo] = e; bufs[1][at:at + hi - lo] = l; bufs[2][at:at + hi - lo] = d
+                del e, l, d
+            shards.append(dict(ebwt=bufs[0] if w["ebwt"] else None, lcp=bufs[1], da=bufs[2], n_own=S, n_halo=0 if last else HALO,
+                               pos_base=rank * S, is_last=last))
+        return shards, n_reads, S * world
+    assert BLOCKS % world == 0, "strong-scaled configs need a GPU count that divides %d" % BLOCKS
+    n_blk = w["n"] // BLOCKS
+    per = BLOCKS // world
+    own = per * n_blk
+    last = rank == world - 1
+    for s in range(w["n_strands"]):
+        bufs = [torch.zeros(own + HALO, dtype=torch.uint8, device=dev) if w["ebwt"] else None,
+                torch.zeros(own + HALO, dtype=torch.int32, device=dev), torch.zeros(own + HALO, dtype=torch.int32, device=dev)]
+        for j in range(per + (0 if last else 1)):
+            blk = rank * per + j
+            k = n_blk if j < per else HALO
+            e, l, d = _block_arrays(w, s, blk, n_blk, dev, hi=k)
+            at = j * n_blk
+            if bufs[0] is not None:
+                bufs[0][at:at + k] = e
+            bufs[1][at:at + k] = l; bufs[2][at:at + k] = d
+            del e, l, d
+        shards.append(dict(ebwt=bufs[0], lcp=bufs[1], da=bufs[2], n_own=own, n_halo=0 if last else HALO,
+                           pos_base=rank * own, is_last=last))
+    return shards, w["n_reads"], n_blk * BLOCKS
 
-    def __init__(self):
-        self.ms = {}
 
-    def __call__(self, name):
-        outer = self
-
-        class T:
-            def __enter__(self_inner):
-                self_inner.t = time.perf_counter()
-
-            def __exit__(self_inner, *a):
-                outer.ms[name] = outer.ms.get(name, 0.0) + (time.perf_counter() - self_inner.t) * 1e3
-                return False
-        return T()
+def _multi_parity(args, w, world, rank, dev, dist, torch, ctx, be):
+    """Before any timing: a reduced job of the same model (>= 50 M positions per strand) sharded over the ranks
+    against the single-GPU job on the whole arrays, which every rank computes for itself."""
+    from lime_b200 import datagen, multi
+    from lime_b200.api import MEM_DEVICE
+    from lime_b200.pipeline import run_job
+    n = max(50_000_000, 8_000_000 * world) if not args.small else 4_000_000
+    n_reads = max(1000, int(w["n_reads"] * (n / w["n"]) * (world if w["scaling"] == "weak" else 1)))
+    n_reads = min(n_reads, n // 8)
+    rows, v, m = _lineage(w)
+    read_frac = min(0.9, n_reads * (w["read_len"] + 1) / float(n))
+    whole, shards = [], []
+    for s in range(w["n_strands"]):
+        e, l, d = datagen.synth_arrays(n, n_reads, w["n_refs"], w["read_len"], seed=w["seed"] + 555 + s, device=dev,
+                                       trlcp=w["trlcp"], read_frac=read_frac)
+        whole.append((e, l, d))
+        lo, hi = multi.shard_ranges(n, world)[rank]
+        k = min(HALO, n - hi)
+        shards.append(dict(ebwt=e[lo:hi + k].clone() if w["ebwt"] else None, lcp=l[lo:hi + k].clone(), da=d[lo:hi + k].clone(),
+                           n_own=hi - lo, n_halo=k, pos_base=lo, is_last=rank == world - 1))
+    torch.cuda.synchronize()
+    strands = [{"ebwt": e.data_ptr() if w["ebwt"] else None, "lcp": l.data_ptr(), "da": d.data_ptr(), "n": n} for (e, l, d) in whole]
+    exp, st1 = run_job(ctx, strands, n_reads, w["n_refs"], w["read_len"], w["alpha"], w["beta"], w["ebwt"], v, m,
+                       w["tax_rank"], w["higher"], mem=MEM_DEVICE)
+    exp = tuple(np.array(x, copy=True) for x in exp)
+    flat_cap, inbox_cap = multi.xchg_capacities(max(sh["n_own"] + sh["n_halo"] for sh in shards), world)
+    xj = multi.XchgJob(dist, torch, be, rank, world, n_reads, w["n_refs"], w["n_strands"], flat_cap, inbox_cap)
+    got, st, route = multi.run_sharded(dist, torch, be, rank, world, n_reads, w["n_refs"], shards, w["alpha"], w["beta"], w["ebwt"],
+                                       w["read_len"], v, m, w["tax_rank"], w["higher"], gather=True, xchg_job=xj)
+    if not xj.closed:
+        xj.close()
+    same = all(np.asarray(a).tobytes() == b.tobytes() for a, b in zip(got, exp))
+    same = same and all(js["n_clusters"] == int(s1[0]) and js["max_len"] == int(s1[1]) for js, s1 in zip(st, st1))
+    flag = torch.tensor([int(same)], device=dev, dtype=torch.int64)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    del whole, shards
+    torch.cuda.empty_cache()
+    if int(flag.item()) != 1:
+        raise SystemExit("bench.py: PARITY FAILED: the sharded job differs from the single-GPU job: no value is reported")
+    return {"checked": True, "against": "the single-GPU job on the whole arrays, computed on every rank (assignments of all reads, "
+            "nClusters, maxLen)", "n": n, "strands": w["n_strands"], "n_reads": n_reads, "route": route}
 
 
 def run_ours_multi(args, w, world, rank, local):
-    """N > 1: weak scaling.  Every rank holds one 402 M-position shard of every strand of an
-    N x 402 M-position job with N x 2 M reads; see lime_b200/multi.py for the exchange."""
+    """N > 1: see lime_b200/multi.py for the exchange."""
     import torch
     import torch.distributed as dist
-    from lime_b200 import datagen, multi
+    from lime_b200 import multi
     from lime_b200.api import LimeContext
-    from lime_b200.pipeline import synthetic_lineage
 
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     ctx = LimeContext(local)
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
-    S, HALO = w["n"], 8192
-    n_reads = w["n_reads"] * world
-    read_frac = w["n_reads"] * (w["read_len"] + 1) / float(S)
-    rows, v, m = synthetic_lineage(w["n_refs"])
-
-    # shard k of strand s = second half of block k ++ first half of block k+1 (blocks are independent
-    # draws of the runs model), so shard boundaries fall INSIDE segments and clusters straddle them
-    shards = []
-    for s in range(w["n_strands"]):
-        bufs = [torch.zeros(S + HALO, dtype=torch.uint8, device=dev), torch.zeros(S + HALO, dtype=torch.int32, device=dev),
-                torch.zeros(S + HALO, dtype=torch.int32, device=dev)]
-        half = S // 2
-        for blk, lo, hi, at in ((rank, half, S, 0), (rank + 1, 0, half, S - half)):
-            e, l, d = datagen.synth_arrays(S, n_reads, w["n_refs"], w["read_len"], seed=w["seed"] + 1000 * s + 17 * blk,
-                                           device=dev, lo=lo, hi=hi, read_frac=read_frac)
-            bufs[0][at:at + hi - lo] = e; bufs[1][at:at + hi - lo] = l; bufs[2][at:at + hi - lo] = d
-            del e, l, d
-        torch.cuda.synchronize()
-        h = multi.exchange_halo(dist, rank, world, [bufs[1], bufs[2], bufs[0]], S, HALO)
-        shards.append(dict(ebwt=bufs[0], lcp=bufs[1], da=bufs[2], n_own=S, n_halo=h, pos_base=rank * S,
-                           is_last=rank == world - 1))
-    torch.cuda.synchronize()
     be = multi.CudaBackend(ctx, torch, dev)
-    # LIME_MULTI=peer: updates go straight to the read owner's slab over NVLink (PeerJob); =exchange: partial
-    # matrices + triples all-to-all (ShardedJob, also the exact fallback).  Default: whichever was measured
-    # faster on this pool (profiles/README.md): peer adds on 2 GPUs, the exchange beyond (remote adds over
-    # a footprint of several owners collapse to 0.3 G adds/s on 8 GPUs)
-    mode = os.environ.get("LIME_MULTI", "auto")
-    peer = mode == "peer" or (mode == "auto" and world <= 2)
-    if peer:
-        job = multi.PeerJob(dist, torch, be, rank, world, n_reads, w["n_refs"], w["n_strands"])
-    else:
-        job = multi.ShardedJob(dist, torch, be, rank, world, n_reads, w["n_refs"])
+    rows, v, m = _lineage(w)
+    parity = _multi_parity(args, w, world, rank, dev, dist, torch, ctx, be) if not args.no_parity else {"checked": False, "why": "--no-parity"}
 
-    def step(gather=True, src=None):
-        job.stats = []
-        if peer:
-            job.begin()
-        for s, sh in enumerate(src or shards):
-            job.run_strand(s, sh, w["alpha"], w["beta"], w["ebwt"], w["read_len"])
-        # every rank fetches the assignments of the reads it owns (9 B per read, as at N = 1)
-        return job.finish(v, None, w["tax_rank"], False, gather=False)
+    shards, n_reads, n_strand_total = _make_shards(w, world, rank, dev)
+    torch.cuda.synchronize()
+    S_local = shards[0]["n_own"]
+    # LIME_MULTI=exchange forces the exact triples route (partial matrices + all-to-all); default: the record exchange
+    mode = os.environ.get("LIME_MULTI", "xchg")
+    density = float(os.environ.get("LIME_XCHG_DENSITY", "0.25"))
+    job = None
 
-    for _ in range(max(args.warmup, 1)):
+    def make_job(density):
+        if mode == "exchange":
+            return multi.ShardedJob(dist, torch, be, rank, world, n_reads, w["n_refs"])
+        flat_cap, inbox_cap = multi.xchg_capacities(S_local + HALO, world, density)
+        return multi.XchgJob(dist, torch, be, rank, world, n_reads, w["n_refs"], w["n_strands"], flat_cap, inbox_cap)
+    job = make_job(density)
+    route = {"name": "xchg" if mode != "exchange" else "exchange"}
+
+    def step(src=None):
+        nonlocal job
+        for attempt in range(3):
+            try:
+                job.stats = []
+                if hasattr(job, "begin"):
+                    job.begin()
+                for s, sh in enumerate(src or shards):
+                    job.run_strand(s, sh, w["alpha"], w["beta"], w["ebwt"], w["read_len"])
+                # every rank fetches the assignments of the reads it owns (9 B per read, as at N = 1)
+                return job.finish(v, m, w["tax_rank"], w["higher"], gather=False)
+            except multi.CarryDetected as e:
+                job.close()
+                if e.overflow and attempt == 0:
+                    job = make_job(density * 4)            # lists too small for this input: once more, larger
+                    route["regrown"] = True
+                else:
+                    job = multi.ShardedJob(dist, torch, be, rank, world, n_reads, w["n_refs"])
+                    route["name"] = "exchange (fallback: %s)" % e
+        raise SystemExit("bench.py: no route completed the job")
+
+    for _ in range(max(args.warmup, 3)):
         out = step()
-    cnt = torch.tensor([int((out[0] == ord(c)).sum()) for c in "CUAH"], device=dev, dtype=torch.int64)
+    cnt = torch.tensor([int((np.asarray(out[0]) == ord(c)).sum()) for c in "CUAH"], device=dev, dtype=torch.int64)
     dist.all_reduce(cnt)
     kinds = {c: int(x) for c, x in zip("CUAH", cnt.tolist()) if x}
     stats = list(job.stats)
@@ -608,17 +788,24 @@ def run_ours_multi(args, w, world, rank, local):
         step()
     ev1.record(stream)
     dist.barrier(); torch.cuda.synchronize()
-    t1 = time.time()
-    ms = torch.tensor([max(ev0.elapsed_time(ev1), 0.0)], device=dev, dtype=torch.float64)
-    dist.all_reduce(ms, op=dist.ReduceOp.MAX)                     # max over ranks
-    ms_step = float(ms.item()) / args.steps
+    ms_prof = ev0.elapsed_time(ev1)
     launches = torch.tensor([ctx.launch_count() - l0], device=dev, dtype=torch.int64)
     dist.all_reduce(launches, op=dist.ReduceOp.SUM)
     prof = ctx.prof(); ctx.prof_enable(False)
+    # the same K steps without the per-launch events of the kernel profile
+    dist.barrier(); torch.cuda.synchronize()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step()
+    ev1.record(stream)
+    dist.barrier(); torch.cuda.synchronize()
+    ms = torch.tensor([min(ms_prof, ev0.elapsed_time(ev1))], device=dev, dtype=torch.float64)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)                     # max over ranks
+    ms_step = float(ms.item()) / args.steps
     k12_all = torch.zeros(world, device=dev, dtype=torch.float64)
     k12_all[rank] = prof.get("k12_fused", {}).get("ms", 0.0) / max(prof.get("k12_fused", {}).get("launches", 1), 1)
     dist.all_reduce(k12_all)
-    n_ext = torch.tensor([max(0, int(0.7 / max(ms_step * 1e-3, 1e-4)) - args.steps)], device=dev, dtype=torch.int64)
+    n_ext = torch.tensor([max(0, int(0.7 / max(ms_step * 1e-3, 1e-4)) - 2 * args.steps)], device=dev, dtype=torch.int64)
     dist.broadcast(n_ext, 0)                                       # same number of extra steps on every rank
     for _ in range(int(n_ext.item())):
         step()
@@ -628,153 +815,176 @@ def run_ours_multi(args, w, world, rank, local):
         clk["window"] = "timed region + untimed repeats of the same step up to 0.7 s (nvidia-smi -lms 50)"
         clocks.stop()
 
-    if os.environ.get("LIME_TRACE"):
-        ht = _HostTimer()
-        job.timer = ht
-        dist.barrier(); torch.cuda.synchronize()
-        t_h = time.perf_counter()
-        for _ in range(3):
-            step()
-        torch.cuda.synchronize()
-        print(f"[trace] rank {rank}: 3 steps {1e3 * (time.perf_counter() - t_h):.2f} ms, host ms per phase (3 steps): "
-              + ", ".join(f"{k}={v:.2f}" for k, v in ht.ms.items()), file=sys.stderr, flush=True)
-    # one diagnostic step with synchronising per-phase timers (not part of the timed region)
-    tm = _SyncTimer(torch)
+    # one diagnostic step with barrier + synchronise around every phase (not part of the timed region): where the
+    # step goes on the slowest rank, and the NVLink rate of the routing kernel
+    tm = _SyncTimer(torch, dist)
     job.timer = tm
+    if hasattr(job, "_inner"):
+        job._inner.timer = tm
     step()
     job.timer = lambda name: multi._NoTimer()
-    sent = sum(st.get("triples_sent", 0) for st in job.stats) * 8
-    PH = ("zero", "compute", "export", "counts", "all_to_all", "import", "choose", "scalars", "classify", "gather", "check")
+    if hasattr(job, "_inner"):
+        job._inner.timer = job.timer
+    PH = ("compute", "export", "counts", "all_to_all", "import", "apply", "choose", "scalars", "classify", "gather", "check")
     phases = torch.tensor([tm.ms.get(k, 0.0) for k in PH], device=dev, dtype=torch.float64)
     dist.all_reduce(phases, op=dist.ReduceOp.MAX)
+    sent = sum(st.get("triples_sent", 0) for st in job.stats) * 8
+    upd = sum(st.get("updates", 0) for st in job.stats)            # all ranks, all strands
     sent_t = torch.tensor([sent], device=dev, dtype=torch.int64)
     dist.all_reduce(sent_t, op=dist.ReduceOp.MAX)
+    route_ms = prof.get("x_route", {}).get("ms", 0.0) / max(prof.get("x_route", {}).get("launches", 1), 1)
 
     # ---- e2e: the same step with every rank's shards in page-locked HOST memory (lime_load(LIME_MEM_HOST) per
-    # strand inside the timed region) and each rank's assignments copied back to its host, max over ranks.
-    # Every rank first proves, without collectives, that it can load its host shards; the leg runs only
-    # if all ranks can (a rank dropping out of a step would leave the others in a collective).
+    # strand inside the timed region, lcp narrowed to bytes on host threads) and each rank's assignments copied
+    # back to its host, max over ranks.
     e2e = None
-    if not args.no_e2e and os.environ.get("LIME_BENCH_MULTI_E2E", "1") != "0":
+    host_bytes = sum((8 + w["ebwt"]) * (sh["n_own"] + sh["n_halo"]) for sh in shards)
+    if not args.no_e2e and os.environ.get("LIME_BENCH_MULTI_E2E", "1") != "0" and host_bytes <= (24 << 30):
         ok, why, host_shards = 1, "", []
         try:
             for sh in shards:
                 hs = dict(sh)
                 for k in ("ebwt", "lcp", "da"):
+                    if sh[k] is None:
+                        continue
                     t = torch.empty(sh[k].shape, dtype=sh[k].dtype, pin_memory=True)
                     t.copy_(sh[k])
                     hs[k] = t
                 host_shards.append(hs)
-            torch.cuda.synchronize()
-            for hs in host_shards:
-                be.load(hs["lcp"], hs["da"], hs["ebwt"] if w["ebwt"] else None, hs["n_own"], hs["n_halo"],
-                        hs["pos_base"], hs["is_last"], n_reads, w["n_refs"])
             torch.cuda.synchronize()
         except BaseException as ex:                      # noqa: BLE001
             ok, why = 0, "%s: %s" % (type(ex).__name__, ex)
         flag = torch.tensor([ok], device=dev, dtype=torch.int64)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         if int(flag.item()) == 1:
-            out_d = tuple(np.array(x, copy=True) for x in step())
-            out_h = tuple(np.array(x, copy=True) for x in step(src=host_shards))
-            same = torch.tensor([int(all(a.tobytes() == b.tobytes() for a, b in zip(out_d, out_h)))], device=dev,
-                                dtype=torch.int64)
-            dist.all_reduce(same, op=dist.ReduceOp.MIN)
-            e2e_steps = max(1, min(args.steps, 5))
-            dist.barrier(); torch.cuda.synchronize()
-            ev0.record(stream)
-            tw0 = time.perf_counter()
-            for _ in range(e2e_steps):
-                step(src=host_shards)
-            ev1.record(stream)
-            torch.cuda.synchronize()
-            tw1 = time.perf_counter()
-            dist.barrier()
+            if w["alpha"] <= 255 and not args.no_narrow:
+                ctx.set_alpha_limit(w["alpha"])
+            try:
+                out_d = tuple(np.array(x, copy=True) for x in step())
+                out_h = tuple(np.array(x, copy=True) for x in step(src=host_shards))
+                same = torch.tensor([int(all(a.tobytes() == b.tobytes() for a, b in zip(out_d, out_h)))], device=dev,
+                                    dtype=torch.int64)
+                dist.all_reduce(same, op=dist.ReduceOp.MIN)
+                e2e_steps = max(1, args.steps)
+                dist.barrier(); torch.cuda.synchronize()
+                ev0.record(stream)
+                tw0 = time.perf_counter()
+                for _ in range(e2e_steps):
+                    step(src=host_shards)
+                ev1.record(stream)
+                torch.cuda.synchronize()
+                tw1 = time.perf_counter()
+                dist.barrier()
+            finally:
+                ctx.set_alpha_limit(0)
             e_ms = torch.tensor([max(ev0.elapsed_time(ev1), (tw1 - tw0) * 1e3)], device=dev, dtype=torch.float64)
             dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
             e_ms = float(e_ms.item()) / e2e_steps
-            h2d = sum((8 + w["ebwt"]) * (hs["n_own"] + hs["n_halo"]) for hs in host_shards)
+            narrow = w["alpha"] <= 255 and not args.no_narrow
+            h2d = sum((8 + w["ebwt"] - (3 if narrow else 0)) * (hs["n_own"] + hs["n_halo"]) for hs in host_shards)
             h2d_t = torch.tensor([h2d], device=dev, dtype=torch.int64)
             dist.all_reduce(h2d_t)
             if int(same.item()) == 1:
-                e2e = {"value": S * w["n_strands"] * world / (e_ms * 1e-3), "unit": UNIT,
+                e2e = {"value": n_strand_total * w["n_strands"] / (e_ms * 1e-3), "unit": UNIT,
                        "h2d_bytes_per_step": int(h2d_t.item()), "d2h_bytes_per_step": 9 * n_reads,
                        "ms_per_step": e_ms, "steps": e2e_steps, "reads_per_s": n_reads / (e_ms * 1e-3),
-                       "note": "every rank: lime_load(LIME_MEM_HOST) of its shard of each strand from page-locked host "
-                               "arrays + its assignments copied back; max over ranks; results equal to the resident step"}
+                       "h2d_GBps_per_gpu": int(h2d_t.item()) / world / (e_ms * 1e-3) / 1e9,
+                       "note": "every rank: lime_load(LIME_MEM_HOST) of its shard of each strand from page-locked host arrays"
+                               + (" (lcp narrowed to bytes by host threads inside the timed region)" if narrow else "")
+                               + " + its assignments copied back; max over ranks; results equal to the resident step"}
             else:
                 e2e = {"error": "host-buffer step disagrees with the resident step"}
         else:
             e2e = {"error": "host-shard pre-flight failed on some rank" + (": " + why if why else "")}
         del host_shards
+    elif not args.no_e2e:
+        e2e = {"value": None, "note": "skipped (%.0f GB of page-locked host arrays per rank)" % (host_bytes / 1e9)}
 
     if rank == 0:
-        symbols = S * w["n_strands"] * world
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except Exception:
-            pass
-        peak_gbs, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback")
+        symbols = n_strand_total * w["n_strands"]
+        peak_gbs, peak_src = _peak()
         kern = {k: x for k, x in prof.items() if x["launches"]}
         top = max(kern, key=lambda k: kern[k]["ms"])
-        alg_per_launch = (8 + w["ebwt"]) * (S + 0)
+        alg_per_launch = (8 + w["ebwt"]) * S_local
         avg_ms = kern[top]["ms"] / kern[top]["launches"]
         achieved = alg_per_launch / (avg_ms * 1e-3) / 1e9 if top == "k12_fused" else None
         ph = {k: float(x) for k, x in zip(PH, phases.tolist()) if x > 0}
-        a2a_ms = ph.get("all_to_all", 0.0)
-        par = (f"position-sharded x{world}, halo {HALO}; similarity rows live on the read owner's GPU and every update is a "
-               "red.add over NVLink / NVSwitch peer memory issued by the fused kernel (no partial matrix, no all-to-all)" if peer else
-               f"position-sharded x{world}, halo {HALO}, triples all-to-all by read owner")
+        par = (f"position-sharded x{world}, halo {HALO}; similarity rows live on the read owner's GPU only: the fused kernel appends "
+               "update records, a routing kernel sorts them by owner and stores each run into the owner's inbox over NVLink / "
+               "NVSwitch peer memory (CUDA IPC), the owner adds them; one 8-byte-per-rank all-gather per strand is the only "
+               "collective" if route["name"] == "xchg" else
+               f"position-sharded x{world}, halo {HALO}, partial matrices + triples all-to-all by read owner ({route['name']})")
+        remote = upd * (world - 1) // world
         line = {
             "metric": METRIC, "value": symbols / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 1), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": w["scaling"],
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": w["name"] + f"; x{world} weak scaling: {world} position shards of {S} symbols per strand, {n_reads} reads",
-                       "l2": "inputs (3.6 GB per strand and GPU) are larger than L2; no flush needed",
+            "config": {"workload": w["name"] + (f"; x{world} weak scaling: {world} position shards of {S_local} symbols per strand, {n_reads} reads"
+                                                if w["scaling"] == "weak" else f"; strong scaling over {world} GPUs: {S_local} symbols per strand and GPU"),
+                       "config": args.config, "alpha": w["alpha"],
+                       "l2": "inputs (%.1f GB per strand and GPU) are larger than L2; no flush needed" % ((8 + w["ebwt"]) * S_local / 1e9),
                        "parallelism": par + "; every rank copies the assignments of its own read range to its host",
                        "symbols_per_step": symbols, "reads_per_step": n_reads, "strand_stats": stats, "assignments": kinds},
             "reads_per_s": n_reads / (ms_step * 1e-3),
+            "parity": parity,
             "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
                          "frac": (achieved / peak_gbs) if achieved else None, "traffic": None, "peak_source": peak_src,
                          "alg_bytes_per_launch": alg_per_launch, "avg_launch_ms": avg_ms,
                          "kernels_ms_per_step_rank0": {k: x["ms"] / args.steps for k, x in kern.items()},
                          "k12_ms_per_launch_by_rank": [round(float(x), 3) for x in k12_all.tolist()],
                          "job_frac_of_aggregate_peak": (8 + w["ebwt"]) * symbols / (ms_step * 1e-3) / 1e9 / (peak_gbs * world)},
-            "exchange": {"mode": "peer-memory adds" if peer else "triples all-to-all", "phases_ms_max_over_ranks": ph,
-                         "all_to_all_bytes_sent_per_rank_max": int(sent_t.item()),
-                         "all_to_all_GBps_per_rank": (int(sent_t.item()) / (a2a_ms * 1e-3) / 1e9) if a2a_ms > 0 else None,
-                         "remote_updates_per_rank_and_step": (sum(st.get("updates", 0) for st in stats) // world * (world - 1) // world) if peer else None,
-                         "nvlink_peak_GBps_per_direction": 900, "note": "phase times from one extra synchronised step"},
+            "exchange": {"route": route, "phases_ms_max_over_ranks": ph,
+                         "note": "phase times from one extra step with a barrier and a synchronise around every phase",
+                         "updates_per_step_all_ranks": upd,
+                         "remote_record_bytes_per_rank_and_step": 8 * remote // world if route["name"] == "xchg" else None,
+                         "route_kernel_ms_per_launch_rank0": route_ms if route["name"] == "xchg" else None,
+                         "route_kernel_nvlink_GBps_rank0": (8 * remote / world / max(len(stats), 1) / (route_ms * 1e-3) / 1e9)
+                         if route["name"] == "xchg" and route_ms > 0 else None,
+                         "all_to_all_bytes_sent_per_rank_max": int(sent_t.item()) or None,
+                         "nvlink_peak_GBps_per_direction": 900},
             "cpu_baseline": None, "e2e": e2e, "gpu_launches": int(launches.item()), "clocks": clk,
         }
         print(json.dumps(line), flush=True)
     dist.barrier()
-    if peer:
+    if hasattr(job, "close"):
         job.close()
     ctx.close()
     dist.destroy_process_group()
 
 
 def main():
-    if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "WARN"):
-        os.environ["NCCL_DEBUG"] = "NONE"          # NCCL would print its version banner on stdout next to the JSON line
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--cpu-sample", type=int, default=CPU_SAMPLE_N)
+    ap.add_argument("--config", default="cfg2", choices=sorted(CONFIGS))
+    ap.add_argument("--n", type=int, default=0, help="positions per strand instead of the config's (config 5 sweep)")
+    ap.add_argument("--alpha", type=int, default=0, help="alpha instead of the config's (config 5 sweep)")
+    ap.add_argument("--cpu-sample", type=int, default=0,
+                    help="positions per strand the CPU reference runs on (default: the whole workload up to 2^29, a prefix beyond)")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--no-narrow", action="store_true", help="skip the e2e leg with the narrowed lcp transfer")
+    ap.add_argument("--e2e", action="store_true", help="run the e2e leg even when it needs > 24 GB of page-locked memory")
+    ap.add_argument("--e2e-plain", action="store_true", help="also time the e2e leg without the narrowed lcp transfer")
+    ap.add_argument("--no-narrow", action="store_true", help="e2e without the narrowed lcp transfer")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the sharded-vs-single-GPU check before timing")
     ap.add_argument("--small", action="store_true", help="reduced shape for functional testing only")
     ap.add_argument("--unfused", action="store_true", help="cluster list between steps 1 and 2 (for comparison)")
     args = ap.parse_args()
-    w = dict(WORKLOAD)
+    w = dict(CONFIGS[args.config])
+    if args.n:
+        w["n_reads"] = max(1000, int(w["n_reads"] * (args.n / w["n"])))
+        w["n"] = args.n
+        w["name"] += f" [sweep point: {args.n} symbols per strand, {w['n_reads']} reads]"
+    if args.alpha:
+        w["alpha"] = args.alpha
+        w["name"] += f" [alpha {args.alpha}]"
     if args.small:
-        w = _small(w, 4_000_000, 20_000)
-        args.cpu_sample = min(args.cpu_sample, 1 << 20)
+        w = _small(w, 4_000_000 if w["scaling"] == "weak" else 8_000_000, 20_000)
+    if not args.cpu_sample:
+        args.cpu_sample = w["n"] if w["n"] <= (1 << 29) else (1 << 28)
+    args.cpu_sample = min(args.cpu_sample, w["n"])
     if args.impl == "reference":
         run_reference_arm(args, w)
     else:
