@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liblime_b200.so")
+# LIME_B200_LIB: another build of the same library (kernel tuning experiments, tools/gpu_k12_variants.sh)
+LIB_PATH = os.environ.get("LIME_B200_LIB") or os.path.join(_HERE, "liblime_b200.so")
 
 OK = 0
 ERR_ARG, ERR_CUDA, ERR_MAXLEN, ERR_HALO, ERR_STATE, ERR_NOMEM, ERR_ROWS, ERR_RETRY = -1, -2, -3, -4, -5, -6, -7, -8

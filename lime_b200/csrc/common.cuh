@@ -183,6 +183,7 @@ struct lime_ctx {
     // step-1 scratch
     lime::DevBuf tile_state;        // u64 per tile
     lime::DevBuf scalars;           // small block of device scalars (see abi)
+    uint64_t l2_policy[2] = {0, 0}; // createpolicy words: evict_first, evict_last (k12_policies, lime_init)
     lime::DevBuf strand_state;      // [LIME_MAXFILES][SS_COUNT] u64: scalars of the strands run without a host sync
     unsigned long long *strand_host = nullptr;   // page-locked mirror of strand_state
     uint64_t rec_hint = 0;          // records of the largest strand result seen (sizes the next deferred one)
@@ -285,7 +286,10 @@ struct K12Args {
     uint2 *flat;                      // K12_FLAT: the record list (FlatOut)
     unsigned long long *flat_count;
     uint64_t flat_cap;
+    // L2 policy words (createpolicy): inputs evict_first, matrix lines evict_last; from k12_policies()
+    uint64_t pol_evict_first, pol_evict_last;
 };
+cudaError_t k12_policies(uint64_t out[2]);
 cudaError_t launch_bytesum(const uint8_t *p, uint64_t bytes, unsigned long long *out, cudaStream_t s);
 cudaError_t launch_k12(const K12Args &a, int what, cudaStream_t s);
 uint64_t k12_num_tiles(uint64_t n_own);

@@ -48,7 +48,14 @@ constexpr int NONE = 1 << 30;
 constexpr int MAXFAST = 32;               // longest cluster the window path takes
 constexpr int SCAP = CH + 32;             // stream capacity incl. one window of padding
 constexpr uint32_t ID_MASK = K12_ID_LIMIT;   // packed stream element: id | class << 27 | start << 31
-constexpr int CTAS_PER_SM = 8;
+#ifndef LIME_K12_CTAS
+#define LIME_K12_CTAS 8                   // 8 x 4 warps: <= 64 registers, 27.4 KB of shared memory per CTA
+#endif
+constexpr int CTAS_PER_SM = LIME_K12_CTAS;
+#ifndef LIME_K12_UNROLL_A
+#define LIME_K12_UNROLL_A 16              // words of phase A in flight together
+#endif
+constexpr int UNROLL_A = LIME_K12_UNROLL_A;
 
 enum { MODE_COUNT = 0, MODE_EMIT = 1, MODE_DIRECT = 2, MODE_FLAT = 3 };
 
@@ -92,6 +99,7 @@ template <bool LCP8>
 struct alignas(16) Smem {
     WarpSmem<LCP8> w[WARPS];
     unsigned long long mbar[WARPS];         // one transaction barrier per warp
+    unsigned pipe[WARPS];                   // per warp: bit 0 = a staged chunk is in flight, bit 1 = its barrier phase
     uint8_t cls[256];                       // symbol -> class
 };
 
@@ -144,6 +152,12 @@ __device__ __forceinline__ uint64_t policy_evict_last()
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
     return p;
 }
+// the two policy words, once per process (they are kernel parameters afterwards: no registers held for them)
+__global__ void policy_kernel(uint64_t *out)
+{
+    out[0] = policy_evict_first();
+    out[1] = policy_evict_last();
+}
 __device__ __forceinline__ void red_add_hint(unsigned *addr, unsigned v, uint64_t pol)
 {
     asm volatile("red.relaxed.gpu.global.add.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(addr), "r"(v), "l"(pol) : "memory");
@@ -171,6 +185,91 @@ __device__ __forceinline__ void load4_lcp(const void *base, uint64_t p, uint64_t
     }
 }
 
+// ---- one similarity update (read, genome g, t) -----------------------------------------------------------
+// MODE_DIRECT: fire-and-forget add of t << 8*(g&3) on the 32-bit word that holds the uint8 cell: no return
+//   value to wait for.  A carry out of a byte (true cell sum > 255, where the reference wraps,
+//   ClusterBWT_DA.cpp:183,247) lowers the byte sum of the matrix by 255 or 256, so the host proves their
+//   absence afterwards by comparing the byte sum of the matrix with the total of all t (sum_t) and otherwise
+//   redoes the strand exactly.
+// MODE_FLAT: record {read, genome << 8 | t} appended to the warp's current block of the flat list; a block of
+//   K12_FLAT_BLK slots is filled completely before the next one is taken from the global cursor.
+// Called by all 32 lanes together (t = 0: nothing to add for this lane).
+struct UpdState {
+    unsigned updates;                 // warp-uniform: updates issued by the warp
+    unsigned t_total;                 // per lane: sum of their t
+    unsigned long long fl_base;       // warp-uniform: first slot of the current block
+    unsigned fl_fill;                 // warp-uniform: slots used in it (K12_FLAT_BLK: none taken yet)
+};
+template <int MODE>
+__device__ __forceinline__ void emit_update(const K12Args &P, UpdState &U, unsigned lane, uint32_t read, uint32_t g, uint32_t t,
+                                            unsigned *row_w)
+{
+    if (MODE == MODE_DIRECT) {
+        if (t) {
+            red_add_hint(row_w + (g >> 2), t << ((g & 3u) * 8u), P.pol_evict_last);
+            U.t_total += t;
+        }
+        U.updates += (unsigned)__popc(__ballot_sync(FULL, t != 0u));
+    } else {
+        const unsigned m = __ballot_sync(FULL, t != 0u);
+        if (m) {                                                  // warp-uniform
+            const unsigned n = (unsigned)__popc(m);
+            const bool spill = U.fl_fill + n > (unsigned)K12_FLAT_BLK;
+            unsigned long long nb = 0;
+            if (spill) {
+                if (lane == 0) nb = atomicAdd(P.flat_count, (unsigned long long)K12_FLAT_BLK);
+                nb = __shfl_sync(FULL, nb, 0);
+            }
+            const unsigned idx = U.fl_fill + (unsigned)__popc(m & ((1u << lane) - 1u));
+            const unsigned long long dst = idx < (unsigned)K12_FLAT_BLK ? U.fl_base + idx : nb + (idx - K12_FLAT_BLK);
+            if (t) {
+                if (dst < P.flat_cap) P.flat[dst] = make_uint2(read, (g << 8) | t);
+                U.t_total += t;
+            }
+            U.updates += n;
+            if (spill) { U.fl_base = nb; U.fl_fill = U.fl_fill + n - K12_FLAT_BLK; }
+            else U.fl_fill += n;
+        }
+    }
+}
+
+// A window that holds a symbol class beyond A, C, G, T (N, IUPAC codes, the end marker: about one window in
+// a hundred): exact per-class counts of all 16 classes and the full matcher.  Kept out of line so that its
+// registers (two 16-byte count vectors, the matcher's arrays) do not weigh on the common path.
+template <int MODE>
+__device__ __noinline__ void wide_window(const K12Args &P, UpdState &U, uint32_t id, uint32_t cls, unsigned mm, unsigned cm,
+                                         bool leader)
+{
+    const unsigned lane = lane_id();
+    const bool real = id != ID_MASK, is_read = id < P.n_reads;
+    unsigned present = __reduce_or_sync(FULL, real ? (1u << cls) : 0u);
+    const bool iupac = (present & 0x7ff0u) != 0;
+    uint4 vec = make_uint4(0, 0, 0, 0);
+    while (present) {
+        const int cc = __ffs(present) - 1;
+        present &= present - 1;
+        const unsigned b = __ballot_sync(FULL, real && cls == (uint32_t)cc);
+        const unsigned v = (unsigned)__popc(mm & b) << ((cc & 3) * 8);
+        if ((cc >> 2) == 0) vec.x |= v; else if ((cc >> 2) == 1) vec.y |= v;
+        else if ((cc >> 2) == 2) vec.z |= v; else vec.w |= v;
+    }
+    unsigned gl = __ballot_sync(FULL, leader && !is_read) & cm;
+    if (!(leader && is_read)) gl = 0;
+    unsigned *row_w = nullptr;
+    if (MODE == MODE_DIRECT) row_w = reinterpret_cast<unsigned *>(P.sim8 + (size_t)(gl ? id : 0u) * P.pitch8);
+    while (__any_sync(FULL, gl != 0)) {
+        const int src = gl ? 31 - __clz(gl) : 0;
+        uint4 Gv;
+        Gv.x = __shfl_sync(FULL, vec.x, src); Gv.y = __shfl_sync(FULL, vec.y, src);
+        Gv.z = __shfl_sync(FULL, vec.z, src); Gv.w = __shfl_sync(FULL, vec.w, src);
+        const uint32_t g = __shfl_sync(FULL, id, src) - P.n_reads;
+        uint32_t t = (iupac ? score_iupac(vec, Gv) : score_plain(vec, Gv)) & 0xffu;
+        if (gl == 0) t = 0;
+        else gl ^= 1u << src;
+        emit_update<MODE>(P, U, lane, id, g, t, row_w);
+    }
+}
+
 template <int MODE, bool EBWT, bool LCP8>
 __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __grid_constant__ K12Args P)
 {
@@ -191,17 +290,14 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
 
     const uint32_t n_chunks = (uint32_t)((P.n_own + OWN - 1) / OWN);       // < 2^32: checked by the launcher
     const uint32_t stride = gridDim.x * WARPS;
-    unsigned cl_count = 0;                                    // clusters counted by this lane
-    unsigned max_len = 0;                                     // longest cluster seen by this lane (open tails apart)
-    unsigned updates = 0;                                     // updates issued by this lane
-    unsigned long long t_total = 0;                           // sum of t added by this lane
+    // warp-uniform running totals (the compiler keeps them in uniform registers, off the vector register file)
+    unsigned cl_count = 0;                                    // clusters owned by this warp's chunks
+    unsigned max_len = 0;                                     // longest cluster seen by this warp (open tails apart)
+    // updates issued / sum of their t per lane (32 bits: a lane adds < 2^32 for every input the launcher
+    // accepts), and in flat mode the warp's current block of the record list
+    UpdState U;
+    U.updates = 0; U.t_total = 0; U.fl_base = 0; U.fl_fill = K12_FLAT_BLK;
     const lcp_t *g_lcp = static_cast<const lcp_t *>(P.lcp);
-    const uint64_t pol_mat = policy_evict_last();
-
-    // flat mode: the warp appends its records to blocks of K12_FLAT_BLK slots taken from one global cursor;
-    // a block is filled completely before the next is taken, the last one is padded with null records
-    unsigned long long fl_base = 0;
-    unsigned fl_fill = K12_FLAT_BLK;
 
     // Stage pipeline: the chunk after the current one is copied global -> shared by three bulk copies
     // while the current one is scored; whole chunks only, the tail of the buffer and unaligned buffers
@@ -214,7 +310,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
         const uint64_t aa = (uint64_t)cc * OWN;
         if (!aligned || aa + CH > P.n_total) return false;
         if (lane == 0) {
-            const uint64_t pol_in = policy_evict_first();
+            const uint64_t pol_in = P.pol_evict_first;
             fence_proxy_async_smem();
             mbar_expect_tx(mb, STAGE_BYTES);
             bulk_g2s((unsigned)__cvta_generic_to_shared(ws.lcp), g_lcp + aa, CH * sizeof(lcp_t), mb, pol_in);
@@ -223,13 +319,14 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
         }
         return true;
     };
-    // masks of a whole chunk (every chunk but the last ones of the buffer)
-    const uint32_t V_full = w < WORDS ? 0xffffffffu : 0u;
-    const uint32_t XM_full = w < WORDS - 1 ? 0xffffffffu : (w == WORDS - 1 ? 0x7fffffffu : 0u);
-    const uint32_t BL_full = mask_lt(OWN - w * 32);
     const uint32_t c_first = blockIdx.x * WARPS + warp;
-    bool staged = stage_issue(c_first);
-    unsigned parity = 0;
+    // whether a staged chunk is in flight and the phase of its barrier live in shared memory, not in registers
+    unsigned &pipe = sm.pipe[warp];
+    {
+        const bool st0 = stage_issue(c_first);
+        if (lane == 0) pipe = st0 ? 1u : 0u;
+        __syncwarp();
+    }
 
     for (uint32_t c = c_first; c < n_chunks; c += stride) {
         const uint64_t a = (uint64_t)c * OWN;                        // buffer-local start of the chunk
@@ -238,10 +335,10 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
 
         // ---- phase A: head / read words (lane = position inside a word) ------------------------------
         uint32_t H = 0xffffffffu, R = 0;                             // lanes >= WORDS: beyond the chunk
-        if (staged) {
-            mbar_wait(mb, parity);
-            parity ^= 1u;
-#pragma unroll
+        const unsigned pst = pipe;
+        if (pst & 1u) {
+            mbar_wait(mb, pst >> 1);
+#pragma unroll UNROLL_A
             for (int k = 0; k < WORDS; k++) {
                 const uint32_t l = ws.lcp[32 * k + lane];
                 const uint32_t d = ws.da[32 * k + lane];
@@ -271,20 +368,22 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
         }
         // the stage is free once da / ebwt of the active positions are compacted (phase C); without
         // scoring right away.  The copy lands while this chunk is scored.
-        bool issued = false;
         auto issue_next = [&]() {
-            if (!issued) { __syncwarp(); staged = stage_issue(c + stride); issued = true; }
+            __syncwarp();
+            const bool st = stage_issue(c + stride);
+            // the phase bit flips whenever a staged chunk has been consumed
+            if (lane == 0) pipe = (st ? 1u : 0u) | ((((pst >> 1) ^ pst) & 1u) << 1);
+            __syncwarp();
         };
         if (!SCORE) issue_next();
 
         // ---- phase B: per-word segment flags (lane w owns word w) -------------------------------------
         // A segment holds a read and a genome iff two neighbours inside it differ in kind:
         // X_i = (read_i != read_{i+1}) and i+1 is not a head.  One flag to spread over the segment.
-        const bool whole = Lext == CH && Lt == OWN;                       // warp-uniform
-        const uint32_t V = whole ? V_full : mask_lt(Lext - w * 32);
+        const uint32_t V = mask_lt(Lext - w * 32);
         const uint32_t Hup = __shfl_down_sync(FULL, H, 1), Rup = __shfl_down_sync(FULL, R, 1);
         const uint32_t Hn = (H >> 1) | (Hup << 31), Rn = (R >> 1) | (Rup << 31);
-        const uint32_t X = (R ^ Rn) & ~Hn & (whole ? XM_full : mask_lt(Lext - w * 32 - 1));   // the last position has no neighbour
+        const uint32_t X = (R ^ Rn) & ~Hn & mask_lt(Lext - w * 32 - 1);   // the last position has no neighbour
         const bool hasHead = H != 0;
         const uint32_t lowmask = hasHead ? ((H & (0u - H)) - 1u) : 0xffffffffu;           // below the first head
         const uint32_t himask = hasHead ? (0xffffffffu << (31 - __clz(H))) : 0xffffffffu; // at / above the last head
@@ -303,7 +402,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
         // first head at or after Lt (E), last head before Lt (hl)
         int E = NONE, hl = -1;
         {
-            const uint32_t below_lt = whole ? BL_full : mask_lt(Lt - w * 32);
+            const uint32_t below_lt = mask_lt(Lt - w * 32);
             const uint32_t he = w < WORDS ? (H & ~below_lt) : 0u, hb = H & below_lt;   // lanes >= WORDS own no word
             const uint32_t Em = __ballot_sync(FULL, he != 0), Bm = __ballot_sync(FULL, hb != 0);
             if (Em) {
@@ -381,13 +480,13 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
         const uint32_t heads = H & Aw;                                    // heads of owned clusters
         const bool own_tail = open_tail && tail_mixed && (hl >> 5) == w;
         const unsigned count = __popc(heads) + (own_tail ? 1u : 0u);
-        cl_count += count;
+        const unsigned chunk_count = __reduce_add_sync(FULL, count);
+        cl_count += chunk_count;
         if (own_tail) atomicMax(P.max_len, tail_len);                     // rare; may exceed 32 bits
 
         if (MODE == MODE_COUNT) {
             // counting pass of the two-pass record emission: clusters owned by this chunk
-            const unsigned total = __reduce_add_sync(FULL, count);
-            if (lane == 0) P.tile_state[c] = total;
+            if (lane == 0) P.tile_state[c] = chunk_count;
             continue;
         }
         if (EMIT) {
@@ -403,19 +502,21 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
             unsigned long long rec_base = e0 + (incl - count);
             // every owned head: length to the next head, record in ascending pStart order
             uint32_t hb = heads;
+            unsigned lane_max = 0;
             while (hb) {
                 const int b = __ffs(hb) - 1;
                 hb &= hb - 1;
                 const uint32_t m = H & ~((2u << b) - 1u);              // next head in this word (b < 31 or m == 0)
                 const int j = (b < 31 && m) ? w * 32 + __ffs(m) - 1 : nh_above;
                 const int len = j - (w * 32 + b);
-                max_len = max(max_len, (unsigned)len);
+                lane_max = max(lane_max, (unsigned)len);
                 if (rec_base < P.out_cap)
                     *reinterpret_cast<ulonglong2 *>(&P.out[rec_base]) = make_ulonglong2(P.pos_base + a + w * 32 + b, (unsigned long long)len);
                 rec_base++;
             }
             if (own_tail && rec_base < P.out_cap)
                 *reinterpret_cast<ulonglong2 *>(&P.out[rec_base]) = make_ulonglong2(P.pos_base + a + hl, tail_len);
+            max_len = max(max_len, __reduce_max_sync(FULL, lane_max));
             continue;
         }
         if (SCORE) {
@@ -433,7 +534,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
                 const int src = __ffs(lm) - 1;
                 lm &= lm - 1;
                 const int i = __shfl_sync(FULL, ci0, src), j = __shfl_sync(FULL, nh_above, src);
-                if (w == src) max_len = max(max_len, (unsigned)(j - i));
+                max_len = max(max_len, (unsigned)(j - i));
                 if (lane == 0) {
                     const unsigned long long slot = atomicAdd(P.long_count, 1ull);
                     if (slot < P.long_cap)
@@ -485,7 +586,6 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
 
         // ---- phase D: score the clusters of the stream, 32-lane windows --------------------------------
         unsigned longest = 0;                                             // warp-uniform
-        unsigned t_chunk = 0;                                             // sum of t of this lane in this chunk
         for (int i = 0; i < n_act;) {
             const uint32_t pk = ws.st[i + lane];
             uint32_t id = pk & ID_MASK;                                   // ID_MASK itself: padding
@@ -510,33 +610,22 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
             const bool leader = (mm & lt_mask) == 0;
             longest = max(longest, __reduce_max_sync(FULL, (unsigned)__popc(cm)));
 
-            // per-class counts of my id: popc(my group & lanes of that class)
-            uint4 vec = make_uint4(0, 0, 0, 0);
-            bool wide = false, iupac = false;
+            // per-class counts of my id: popc(my group & lanes of that class), A / C / G / T in the four bytes
+            uint32_t vec = 0;
             if (!EBWT) {
-                vec.x = (unsigned)__popc(mm);
+                vec = (unsigned)__popc(mm);
             } else {
                 const uint32_t cls = (pk >> 27) & 15u;
-                const bool real = id != ID_MASK;
-                const unsigned c0 = __ballot_sync(FULL, (cls & 1u) != 0), c1 = __ballot_sync(FULL, (cls & 2u) != 0);
-                const unsigned rest = __ballot_sync(FULL, cls >= 4u && real);
-                vec.x = (unsigned)__popc(mm & ~c1 & ~c0) | ((unsigned)__popc(mm & ~c1 & c0) << 8) |
-                        ((unsigned)__popc(mm & c1 & ~c0) << 16) | ((unsigned)__popc(mm & c1 & c0) << 24);
-                wide = rest != 0;                                              // a class beyond A,C,G,T
-                if (wide) {
-                    // exact per-class counts for every class present in the window
-                    unsigned present = __reduce_or_sync(FULL, real ? (1u << cls) : 0u);
-                    iupac = (present & 0x7ff0u) != 0;
-                    vec = make_uint4(0, 0, 0, 0);
-                    while (present) {
-                        const int cc = __ffs(present) - 1;
-                        present &= present - 1;
-                        const unsigned b = __ballot_sync(FULL, real && cls == (uint32_t)cc);
-                        const unsigned v = (unsigned)__popc(mm & b) << ((cc & 3) * 8);
-                        if ((cc >> 2) == 0) vec.x |= v; else if ((cc >> 2) == 1) vec.y |= v;
-                        else if ((cc >> 2) == 2) vec.z |= v; else vec.w |= v;
-                    }
+                const unsigned rest = __ballot_sync(FULL, cls >= 4u && id != ID_MASK);
+                if (rest) {                                                    // a class beyond A,C,G,T (warp-uniform, rare)
+                    UpdState W = U;
+                    wide_window<MODE>(P, W, id, cls, mm, cm, leader);
+                    U = W;
+                    continue;
                 }
+                const unsigned c0 = __ballot_sync(FULL, (cls & 1u) != 0), c1 = __ballot_sync(FULL, (cls & 2u) != 0);
+                vec = (unsigned)__popc(mm & ~c1 & ~c0) | ((unsigned)__popc(mm & ~c1 & c0) << 8) |
+                      ((unsigned)__popc(mm & c1 & ~c0) << 16) | ((unsigned)__popc(mm & c1 & c0) << 24);
             }
             // reads wrap at 256 (:123,206), genomes saturate at 255 (:96-97,222-223): counts <= 32 here
 
@@ -548,74 +637,28 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
             if (MODE == MODE_DIRECT) row_w = reinterpret_cast<unsigned *>(P.sim8 + (size_t)(gl ? id : 0u) * P.pitch8);
             while (__any_sync(FULL, gl != 0)) {
                 const int src = gl ? 31 - __clz(gl) : 0;
-                const uint32_t Gx = __shfl_sync(FULL, vec.x, src);
+                const uint32_t Gx = __shfl_sync(FULL, vec, src);
                 const uint32_t g = __shfl_sync(FULL, id, src) - P.n_reads;
-                uint32_t t;
-                if (!EBWT) t = min(vec.x, Gx);
-                else if (!wide) t = score_acgt(vec.x, Gx);
-                else {
-                    uint4 Gv;
-                    Gv.x = Gx;
-                    Gv.y = __shfl_sync(FULL, vec.y, src); Gv.z = __shfl_sync(FULL, vec.z, src);
-                    Gv.w = __shfl_sync(FULL, vec.w, src);
-                    t = (iupac ? score_iupac(vec, Gv) : score_plain(vec, Gv)) & 0xffu;
-                }
+                uint32_t t = EBWT ? score_acgt(vec, Gx) : min(vec, Gx);
                 if (gl == 0) t = 0;
                 else gl ^= 1u << src;
-                if (MODE == MODE_DIRECT) {
-                    // Fire-and-forget add of t << 8*(g&3) on the 32-bit word that holds the uint8 cell: no
-                    // return value to wait for.  A carry out of a byte (true cell sum > 255, where the
-                    // reference wraps, ClusterBWT_DA.cpp:183,247) lowers the byte sum of the matrix by 255
-                    // or 256, so the host proves their absence afterwards by comparing the byte sum of the
-                    // matrix with the total of all t (sum_t) and otherwise redoes the strand exactly.
-                    if (t) {
-                        red_add_hint(row_w + (g >> 2), t << ((g & 3u) * 8u), pol_mat);
-                        updates++;
-                        t_chunk += t;
-                    }
-                } else {
-                    // MODE_FLAT: record {read, genome << 8 | t} appended to the warp's current block
-                    const unsigned m = __ballot_sync(FULL, t != 0u);
-                    if (m) {                                                  // warp-uniform
-                        const unsigned n = (unsigned)__popc(m);
-                        const bool spill = fl_fill + n > (unsigned)K12_FLAT_BLK;
-                        unsigned long long nb = 0;
-                        if (spill) {
-                            if (lane == 0) nb = atomicAdd(P.flat_count, (unsigned long long)K12_FLAT_BLK);
-                            nb = __shfl_sync(FULL, nb, 0);
-                        }
-                        const unsigned idx = fl_fill + (unsigned)__popc(m & lt_mask);
-                        const unsigned long long dst = idx < (unsigned)K12_FLAT_BLK ? fl_base + idx : nb + (idx - K12_FLAT_BLK);
-                        if (t) {
-                            if (dst < P.flat_cap) P.flat[dst] = make_uint2(id, (g << 8) | t);
-                            updates++;
-                            t_chunk += t;
-                        }
-                        if (spill) { fl_base = nb; fl_fill = fl_fill + n - K12_FLAT_BLK; }
-                        else fl_fill += n;
-                    }
-                }
+                emit_update<MODE>(P, U, lane, id, g, t, row_w);
             }
         }
         max_len = max(max_len, longest);
-        t_total += t_chunk;
     }
-    if (MODE == MODE_FLAT && fl_fill < (unsigned)K12_FLAT_BLK) {
+    if (MODE == MODE_FLAT && U.fl_fill < (unsigned)K12_FLAT_BLK) {
         // null records (t = 0) up to the end of the warp's last block: every slot below flat_count is defined
-        for (unsigned i = fl_fill + lane; i < (unsigned)K12_FLAT_BLK; i += 32)
-            if (fl_base + i < P.flat_cap) P.flat[fl_base + i] = make_uint2(0xffffffffu, 0u);
+        for (unsigned i = U.fl_fill + lane; i < (unsigned)K12_FLAT_BLK; i += 32)
+            if (U.fl_base + i < P.flat_cap) P.flat[U.fl_base + i] = make_uint2(0xffffffffu, 0u);
     }
     // ---- totals of this warp: one atomic per warp and scalar -------------------------------------------
     {
-        unsigned c2 = cl_count, mx = max_len;
-        unsigned long long up = updates, tt = t_total;
+        const unsigned c2 = cl_count, mx = max_len;
+        const unsigned long long up = U.updates;
+        unsigned long long tt = U.t_total;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            c2 += __shfl_xor_sync(FULL, c2, o);
-            mx = max(mx, __shfl_xor_sync(FULL, mx, o));
-            up += __shfl_xor_sync(FULL, up, o);
-            tt += __shfl_xor_sync(FULL, tt, o);
-        }
+        for (int o = 16; o > 0; o >>= 1) tt += __shfl_xor_sync(FULL, tt, o);
         if (lane == 0) {
             if (!EMIT && c2) atomicAdd(P.n_clusters, (unsigned long long)c2);
             if (mx) atomicMax(P.max_len, (unsigned long long)mx);
@@ -693,6 +736,17 @@ uint64_t k12_long_cap(uint64_t n_total) { return n_total / (k12s::MAXFAST + 1) +
 //                   the emitting pass reads its offset there -- no look-back between warps;
 //       K12_COUNT   nClusters / maxLen only (the counting pass alone);
 //       K12_DIRECT / K12_FLAT  score, see the head of this file.
+cudaError_t k12_policies(uint64_t out[2])
+{
+    uint64_t *d = nullptr;
+    cudaError_t e = cudaMalloc(&d, 16);
+    if (e != cudaSuccess) return e;
+    k12s::policy_kernel<<<1, 1>>>(d);
+    e = cudaMemcpy(out, d, 16, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    return e;
+}
+
 cudaError_t launch_k12(const K12Args &a, int what, cudaStream_t s)
 {
     if (a.n_own == 0) return cudaSuccess;

@@ -30,6 +30,7 @@ int lime_init(lime_ctx **out, int device)
     ctx->device = device;
     e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = ctx->scalars.reserve(sizeof(unsigned long long) * SC_COUNT);
+    if (e == cudaSuccess) e = k12_policies(ctx->l2_policy);
     if (e != cudaSuccess) { g_init_error = cudaGetErrorString(e); delete ctx; return LIME_ERR_CUDA; }
     ctx->stream = ctx->own_stream;
     *out = ctx;
@@ -225,6 +226,7 @@ int detect_into_ctx(lime_ctx *ctx, uint32_t alpha, unsigned long long host_sc[SC
         a.n_clusters = scalar<unsigned long long>(ctx, SC_NCLUSTERS);
         a.max_len = scalar<unsigned long long>(ctx, SC_MAXLEN);
         a.err = scalar<unsigned int>(ctx, SC_ERR);
+        a.pol_evict_first = ctx->l2_policy[0]; a.pol_evict_last = ctx->l2_policy[1];
         if (tiles) {
             LaunchScope ls(ctx, KID_K1_DETECT);
             CK(launch_k12(a, K12_DETECT, ctx->stream), "k1_detect launch");

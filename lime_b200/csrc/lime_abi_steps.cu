@@ -63,6 +63,7 @@ int queue_k12_score(lime_ctx *ctx, uint32_t alpha, bool ebwt, unsigned long long
     a.sim8 = ctx->d_sim; a.pitch8 = ctx->sim_pitch;
     a.n_updates = sc + SS_NUPDATES; a.sum_t = sc + SS_SUMT;
     a.flat = flat.rec; a.flat_count = flat.count; a.flat_cap = flat.cap;
+    a.pol_evict_first = ctx->l2_policy[0]; a.pol_evict_last = ctx->l2_policy[1];
     if (k12_num_tiles(ctx->n_own) == 0) return LIME_OK;
     {
         LaunchScope ls(ctx, KID_K12_FUSED);

@@ -54,6 +54,58 @@ def exact_collection(reads, genomes, terminator=b"$"):
     return ebwt, lcp, da
 
 
+def exact_collection_fast(reads, genomes, terminator=b"$"):
+    """The same arrays as exact_collection for collections of 10^5..10^7 positions: prefix doubling and a
+    vectorised LCP in numpy instead of sorting Python strings (tests/test_oracle_vs_reference.py checks the
+    two against each other)."""
+    seqs = list(reads) + list(genomes)
+    D = len(seqs)
+    lens = np.array([len(x) for x in seqs], dtype=np.int64)
+    n = int(lens.sum()) + D
+    text = np.empty(n, dtype=np.int64)                 # letters D + byte, end marker of document d = d
+    doc = np.empty(n, dtype=np.uint32)
+    off = np.empty(n, dtype=np.int64)
+    starts = np.concatenate([[0], np.cumsum(lens + 1)[:-1]])
+    for d, x in enumerate(seqs):
+        a = int(starts[d]); L = len(x)
+        text[a:a + L] = np.frombuffer(x.encode(), dtype=np.uint8).astype(np.int64) + D
+        text[a + L] = d
+        doc[a:a + L + 1] = d
+        off[a:a + L + 1] = np.arange(L + 1)
+    # prefix doubling
+    rank = np.unique(text, return_inverse=True)[1].astype(np.int64)
+    k = 1
+    while True:
+        nxt = np.full(n, -1, dtype=np.int64)
+        nxt[:n - k] = rank[k:]
+        order = np.lexsort((nxt, rank))
+        ro, no = rank[order], nxt[order]
+        new = np.empty(n, dtype=np.int64)
+        new[order] = np.cumsum(np.concatenate([[0], ((ro[1:] != ro[:-1]) | (no[1:] != no[:-1])).astype(np.int64)]))
+        rank = new
+        if int(rank.max()) == n - 1:
+            break
+        k *= 2
+    sa = np.empty(n, dtype=np.int64)
+    sa[rank] = np.arange(n)
+    # lcp of neighbours: compare column by column while the pair still matches (end markers are unique)
+    lcp = np.zeros(n, dtype=np.uint32)
+    act = np.arange(1, n)
+    a, b = sa[act - 1], sa[act]
+    depth = 0
+    while act.size:
+        ok = (np.maximum(a, b) + depth < n)
+        ok[ok] = text[a[ok] + depth] == text[b[ok] + depth]
+        ok &= text[np.minimum(a + depth, n - 1)] >= D            # never across an end marker
+        lcp[act[ok]] += 1
+        act, a, b = act[ok], a[ok], b[ok]
+        depth += 1
+    da = doc[sa]
+    term = terminator[0]
+    prev = np.where(off[sa] > 0, text[np.maximum(sa - 1, 0)] - D, term)
+    return prev.astype(np.uint8), lcp, da.astype(np.uint32)
+
+
 def random_dna(rng, n, alphabet="ACGT"):
     return "".join(rng.choice(list(alphabet), size=n))
 

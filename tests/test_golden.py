@@ -98,3 +98,68 @@ def test_cuda_reproduces_reference_classify(ctx, tmp_path, path):
             o = str(tmp_path / "o.csv")
             api.write_csv(o, typ, tax, sim)
             assert open(o, "rb").read() == g[f"csv_h{higher}_t{tax_rank}"].tobytes()
+
+
+# ---- BASELINE config 1 stand-in: the real example reads against three pseudo-genomes, 4 strands, the reference's
+# own outputs (tests/golden/make_config1.py, LiME_paired.sh defaults alpha=16 beta=0.25 TaxRank=1) -------------------
+CONFIG1 = os.path.join(HERE, "golden", "config1_example.npz")
+
+
+def _config1_known_answers(g, csv_bytes):
+    """Every read of an accession listed in the lineage file is classified to that accession's species, the reads
+    of the fourth accession (not in the database) stay unclassified."""
+    lineage = g["lineage"].tobytes().decode()
+    tax = {l.split(";")[0]: l.split(";")[1] for l in lineage.splitlines()[1:] if l.strip()}
+    rows = [l.split(",") for l in csv_bytes.decode().splitlines()[1:]]
+    assert len(rows) == int(g["n_reads"])
+    for row, acc in zip(rows, g["acc_of"]):
+        if str(acc) in tax:
+            assert row[0] == "C" and row[2] == tax[str(acc)]
+        else:
+            assert row[0] == "U"
+
+
+def test_oracle_reproduces_reference_on_the_example_reads(oracle, tmp_path):
+    g = np.load(CONFIG1)
+    n_reads, n_refs = int(g["n_reads"]), int(g["n_refs"])
+    lin = str(tmp_path / "LineageFile.csv")
+    open(lin, "wb").write(g["lineage"].tobytes())
+    bins, poss = [], []
+    for s in range(4):
+        cl, mx = oracle.cluster_detect(g[f"lcp_{s}"], g[f"da_{s}"], n_reads, 16)
+        assert cl.tobytes() == g[f"clrs_{s}"].tobytes()
+        out = g[f"out_{s}"].tobytes()
+        assert int.from_bytes(out[12:20], "little") == mx and int.from_bytes(out[20:28], "little") == cl.shape[0]
+        b, p = oracle.choose(oracle.similarity(cl, g[f"da_{s}"], g[f"ebwt_{s}"], n_reads, n_refs), 100 + 1 - 16, np.float32(0.25))
+        assert b.tobytes() == g[f"res_bin_{s}"].tobytes() and p.tobytes() == g[f"res_pos_{s}"].tobytes()
+        bins.append(b); poss.append(p)
+    v, m, found = oracle.fix_rank(lin, 1, n_refs, False)
+    assert found == n_refs
+    o = str(tmp_path / "o.csv")
+    oracle.write_csv(o, *oracle.classify(bins, poss, n_refs, v, None, 1, False))
+    assert open(o, "rb").read() == g["csv"].tobytes()
+    _config1_known_answers(g, g["csv"].tobytes())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("deferred", [False, True])
+def test_cuda_reproduces_reference_on_the_example_reads(ctx, tmp_path, deferred):
+    from lime_b200 import api
+    from lime_b200.pipeline import run_job
+    g = np.load(CONFIG1)
+    n_reads, n_refs = int(g["n_reads"]), int(g["n_refs"])
+    lin = str(tmp_path / "LineageFile.csv")
+    open(lin, "wb").write(g["lineage"].tobytes())
+    v, m, found = api.fix_rank(lin, 1, n_refs, False)
+    assert found == n_refs
+    strands = [{"ebwt": g[f"ebwt_{s}"], "lcp": g[f"lcp_{s}"], "da": g[f"da_{s}"], "n": g[f"lcp_{s}"].shape[0]} for s in range(4)]
+    for rep in range(2 if deferred else 1):
+        out, stats = run_job(ctx, strands, n_reads, n_refs, 100, 16, 0.25, 1, v, None, 1, False, deferred=deferred)
+        for s in range(4):
+            ref_out = g[f"out_{s}"].tobytes()
+            assert (int(stats[s][1]), int(stats[s][0])) == (int.from_bytes(ref_out[12:20], "little"), int.from_bytes(ref_out[20:28], "little"))
+            b, p = ctx.choose_result(s)
+            assert b.tobytes() == g[f"res_bin_{s}"].tobytes() and p.tobytes() == g[f"res_pos_{s}"].tobytes()
+        o = str(tmp_path / "o.csv")
+        api.write_csv(o, *out)
+        assert open(o, "rb").read() == g["csv"].tobytes()
