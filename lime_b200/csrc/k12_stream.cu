@@ -56,6 +56,9 @@ constexpr int CTAS_PER_SM = LIME_K12_CTAS;
 #define LIME_K12_UNROLL_A 16              // words of phase A in flight together
 #endif
 constexpr int UNROLL_A = LIME_K12_UNROLL_A;
+#ifndef LIME_K12_L2PF
+#define LIME_K12_L2PF 1                   // prefetch the chunk after the next one into L2
+#endif
 
 enum { MODE_COUNT = 0, MODE_EMIT = 1, MODE_DIRECT = 2, MODE_FLAT = 3 };
 
@@ -125,6 +128,11 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned
 {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(mbar), "l"(pol) : "memory");
+}
+// DRAM -> L2 ahead of the copy proper: the bulk copy of a chunk then completes with L2 latency
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src, unsigned bytes)
+{
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity)
 {
@@ -316,6 +324,15 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
             bulk_g2s((unsigned)__cvta_generic_to_shared(ws.lcp), g_lcp + aa, CH * sizeof(lcp_t), mb, pol_in);
             bulk_g2s((unsigned)__cvta_generic_to_shared(ws.da), P.da + aa, CH * 4u, mb, pol_in);
             if (SCORE && EBWT) bulk_g2s((unsigned)__cvta_generic_to_shared(ws.eb), P.ebwt + aa, CH, mb, pol_in);
+#if LIME_K12_L2PF
+            // and the chunk after that one from DRAM into L2: a whole chunk period ahead of its copy
+            const uint64_t ab = aa + (uint64_t)stride * OWN;
+            if (ab + CH <= P.n_total) {
+                bulk_prefetch_l2(g_lcp + ab, CH * sizeof(lcp_t));
+                bulk_prefetch_l2(P.da + ab, CH * 4u);
+                if (SCORE && EBWT) bulk_prefetch_l2(P.ebwt + ab, CH);
+            }
+#endif
         }
         return true;
     };
@@ -586,11 +603,16 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
 
         // ---- phase D: score the clusters of the stream, 32-lane windows --------------------------------
         unsigned longest = 0;                                             // warp-uniform
-        for (int i = 0; i < n_act;) {
-            const uint32_t pk = ws.st[i + lane];
+        // software pipeline over the windows: the elements of the next window are loaded while this one is scored
+        int i = 0;
+        uint32_t pk = ws.st[lane], nx = ws.st[32];
+        while (i < n_act) {
+            // equal ids of the window; restricted to the lanes of the own cluster further down.  (Issued first: the
+            // match is the longest-latency operation of the window set-up.)
+            const unsigned mraw = __match_any_sync(FULL, pk & ID_MASK);
             uint32_t id = pk & ID_MASK;                                   // ID_MASK itself: padding
             uint32_t sb = __ballot_sync(FULL, (pk >> 31) != 0u);          // bit 0 is set: i is a start
-            if (!(ws.st[i + 32] >> 31)) {
+            if (!(nx >> 31)) {
                 // the last cluster of the window is cut: leave it to the next window (turn its lanes
                 // into lone starts; a cluster has at most 32 positions, so it does not start at lane 0)
                 const int ls = 31 - __clz(sb);
@@ -600,13 +622,19 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
             } else {
                 i += 32;
             }
+            const uint32_t cur = pk;
+            {
+                const bool more = i < n_act;                              // warp-uniform
+                pk = more ? ws.st[i + lane] : 0xffffffffu;
+                nx = more ? ws.st[i + 32] : 0xffffffffu;
+            }
             const uint32_t le_mask = lt_mask | (1u << lane);
             const uint32_t start_bit = 0x80000000u >> __clz(sb & le_mask);     // first lane of my cluster
             const uint32_t later = sb & ~le_mask;
             const uint32_t upper = (later & (0u - later)) - 1u;                // lanes below the next start (all if none)
             const uint32_t cm = upper & ~(start_bit - 1u);                     // lanes of my cluster
             const bool is_read = id < P.n_reads;
-            const unsigned mm = __match_any_sync(FULL, id) & cm;               // lanes with my id in my cluster
+            const unsigned mm = mraw & cm;                                     // lanes with my id in my cluster
             const bool leader = (mm & lt_mask) == 0;
             longest = max(longest, __reduce_max_sync(FULL, (unsigned)__popc(cm)));
 
@@ -615,7 +643,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
             if (!EBWT) {
                 vec = (unsigned)__popc(mm);
             } else {
-                const uint32_t cls = (pk >> 27) & 15u;
+                const uint32_t cls = (cur >> 27) & 15u;
                 const unsigned rest = __ballot_sync(FULL, cls >= 4u && id != ID_MASK);
                 if (rest) {                                                    // a class beyond A,C,G,T (warp-uniform, rare)
                     UpdState W = U;

@@ -19,9 +19,9 @@ int strand_readback(lime_ctx *ctx, int slot)
     if (h[SS_MAXLEN] > LIME_SIZE_MAX_BUF) { S.valid = false; return fail(ctx, LIME_ERR_MAXLEN, "maximum cluster size is greater than sizeMaxBuf"); }
     if (h[SS_ERR] & 12ull) { S.valid = false; return fail(ctx, (h[SS_ERR] & 8ull) ? LIME_ERR_ARG : LIME_ERR_RETRY, (h[SS_ERR] & 8ull) ? "exchange: update record out of range" : "exchange: an inbox region overflowed"); }
     if (S.kind == 2 && h[SS_FLAT_COUNT] > ctx->xchg.flat_cap) { S.valid = false; return fail(ctx, LIME_ERR_RETRY, "exchange: the update list overflowed"); }
-    if (h[SS_NRECORDS] > S.bin_cap) { S.valid = false; return fail(ctx, LIME_ERR_RETRY, "deferred strand: record buffer too small"); }
     const unsigned long long added = S.kind == 2 ? h[SS_APPLIED_T] : h[SS_SUMT];
     if (added != h[SS_BYTESUM] || (h[SS_ERR] >> 32) != 0) { S.valid = false; return fail(ctx, LIME_ERR_RETRY, "deferred strand: a similarity cell exceeded 255"); }
+    if (h[SS_NRECORDS] > S.bin_cap) { S.valid = false; return fail(ctx, LIME_ERR_RETRY, "deferred strand: record buffer too small"); }
     return LIME_OK;
 }
 
