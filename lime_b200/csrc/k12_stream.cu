@@ -56,9 +56,6 @@ constexpr int CTAS_PER_SM = LIME_K12_CTAS;
 #define LIME_K12_UNROLL_A 16              // words of phase A in flight together
 #endif
 constexpr int UNROLL_A = LIME_K12_UNROLL_A;
-#ifndef LIME_K12_L2PF
-#define LIME_K12_L2PF 1                   // prefetch the chunk after the next one into L2
-#endif
 
 enum { MODE_COUNT = 0, MODE_EMIT = 1, MODE_DIRECT = 2, MODE_FLAT = 3 };
 
@@ -128,11 +125,6 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned
 {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(mbar), "l"(pol) : "memory");
-}
-// DRAM -> L2 ahead of the copy proper: the bulk copy of a chunk then completes with L2 latency
-__device__ __forceinline__ void bulk_prefetch_l2(const void *src, unsigned bytes)
-{
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity)
 {
@@ -285,7 +277,9 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
     constexpr bool EMIT = MODE == MODE_EMIT;
     typedef typename LcpElem<LCP8>::type lcp_t;
     __shared__ Smem<LCP8> sm;
-    const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
+    // the warp index through a shuffle: the compiler then knows that it, the chunk counters and the stage addresses
+    // derived from it are warp-uniform and keeps them in uniform registers (bulk copies take uniform operands)
+    const unsigned lane = lane_id(), warp = __shfl_sync(FULL, threadIdx.x >> 5, 0);
     const uint32_t lt_mask = (1u << lane) - 1u;
     if (SCORE && EBWT) {
         for (int i = threadIdx.x; i < 256; i += THREADS) sm.cls[i] = d_class_table.v[i];
@@ -324,15 +318,6 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
             bulk_g2s((unsigned)__cvta_generic_to_shared(ws.lcp), g_lcp + aa, CH * sizeof(lcp_t), mb, pol_in);
             bulk_g2s((unsigned)__cvta_generic_to_shared(ws.da), P.da + aa, CH * 4u, mb, pol_in);
             if (SCORE && EBWT) bulk_g2s((unsigned)__cvta_generic_to_shared(ws.eb), P.ebwt + aa, CH, mb, pol_in);
-#if LIME_K12_L2PF
-            // and the chunk after that one from DRAM into L2: a whole chunk period ahead of its copy
-            const uint64_t ab = aa + (uint64_t)stride * OWN;
-            if (ab + CH <= P.n_total) {
-                bulk_prefetch_l2(g_lcp + ab, CH * sizeof(lcp_t));
-                bulk_prefetch_l2(P.da + ab, CH * 4u);
-                if (SCORE && EBWT) bulk_prefetch_l2(P.ebwt + ab, CH);
-            }
-#endif
         }
         return true;
     };
