@@ -56,6 +56,12 @@ constexpr int CTAS_PER_SM = LIME_K12_CTAS;
 #define LIME_K12_UNROLL_A 16              // words of phase A in flight together
 #endif
 constexpr int UNROLL_A = LIME_K12_UNROLL_A;
+#ifndef LIME_K12_TMA
+#define LIME_K12_TMA 0                    // stage by TMA bulk copies (1) or by per-lane 16-byte cp.async (0)
+#endif
+#ifndef LIME_K12_BLOCKED
+#define LIME_K12_BLOCKED 1                // one contiguous chunk range per CTA (1) or a grid stride (0)
+#endif
 
 enum { MODE_COUNT = 0, MODE_EMIT = 1, MODE_DIRECT = 2, MODE_FLAT = 3 };
 
@@ -121,6 +127,15 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned
 {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(mbar), "l"(pol) : "memory");
+}
+// 16-byte asynchronous global -> shared copy (LDGSTS), L1 bypassed, with an L2 eviction policy
+__device__ __forceinline__ void cp_async16_hint(unsigned smem_addr, const void *gmem, uint64_t pol)
+{
+    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(smem_addr), "l"(gmem), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all()
+{
+    asm volatile("cp.async.wait_all;" ::: "memory");
 }
 __device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity)
 {
@@ -306,6 +321,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
         if (cc >= n_chunks) return false;
         const uint64_t aa = cc * OWN;
         if (!aligned || aa + CH > P.n_total) return false;
+#if LIME_K12_TMA
         if (lane == 0) {
             const uint64_t pol_in = P.pol_evict_first;
             fence_proxy_async_smem();
@@ -314,17 +330,39 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
             bulk_g2s((unsigned)__cvta_generic_to_shared(ws.da), P.da + aa, CH * 4u, mb, pol_in);
             if (SCORE && EBWT) bulk_g2s((unsigned)__cvta_generic_to_shared(ws.eb), P.ebwt + aa, CH, mb, pol_in);
         }
+#else
+        {
+            // 16 bytes per lane and copy: piece k of an array lies 512 bytes after piece k - 1
+            const uint64_t pol_in = P.pol_evict_first;
+            const char *pl = reinterpret_cast<const char *>(g_lcp + aa) + 16 * lane;
+            const char *pd = reinterpret_cast<const char *>(P.da + aa) + 16 * lane;
+            const unsigned s_lcp = (unsigned)__cvta_generic_to_shared(ws.lcp) + 16 * lane;
+            const unsigned s_da = (unsigned)__cvta_generic_to_shared(ws.da) + 16 * lane;
+#pragma unroll
+            for (int k = 0; k < (int)(CH * sizeof(lcp_t) / 512); k++) cp_async16_hint(s_lcp + 512 * k, pl + 512 * k, pol_in);
+#pragma unroll
+            for (int k = 0; k < CH * 4 / 512; k++) cp_async16_hint(s_da + 512 * k, pd + 512 * k, pol_in);
+            if (SCORE && EBWT)
+                cp_async16_hint((unsigned)__cvta_generic_to_shared(ws.eb) + 16 * lane, P.ebwt + aa + 16 * lane, pol_in);
+        }
+#endif
         return true;
     };
     // Chunk schedule: every CTA takes ONE contiguous range of chunks (its warps interleaved inside it), so that the
     // bulk copies of a CTA walk through memory page by page.  (With a plain grid stride every copy of every warp
     // touched a new 2 MB page, and the TMA unit serves one TLB miss at a time: ~210 cycles per copy, the L2
     // latency of the page-table read -- which bounded the kernel at 1.8 ms whatever its instruction count.)
+#if LIME_K12_BLOCKED
     const uint32_t per_cta = (n_chunks + gridDim.x - 1) / gridDim.x;
     auto chunk_of = [&](uint32_t t) -> uint64_t {              // t-th chunk of this warp, or beyond n_chunks
         const uint32_t l = t * WARPS + warp;
         return l < per_cta ? (uint64_t)blockIdx.x * per_cta + l : (uint64_t)n_chunks;
     };
+#else
+    auto chunk_of = [&](uint32_t t) -> uint64_t {
+        return (uint64_t)blockIdx.x * WARPS + warp + (uint64_t)t * gridDim.x * WARPS;
+    };
+#endif
     const uint64_t c_first = chunk_of(0);
     // whether a staged chunk is in flight and the phase of its barrier live in shared memory, not in registers
     unsigned &pipe = sm.pipe[warp];
@@ -344,7 +382,12 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
         uint32_t H = 0xffffffffu, R = 0;                             // lanes >= WORDS: beyond the chunk
         const unsigned pst = pipe;
         if (pst & 1u) {
+#if LIME_K12_TMA
             mbar_wait(mb, pst >> 1);
+#else
+            cp_async_wait_all();
+            __syncwarp();
+#endif
 #pragma unroll UNROLL_A
             for (int k = 0; k < WORDS; k++) {
                 const uint32_t l = ws.lcp[32 * k + lane];

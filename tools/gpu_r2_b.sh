@@ -5,7 +5,7 @@ tag=${1:-r02b}
 mkdir -p gpurun_out
 timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/${tag}_pytest_gpu.log 2>&1; echo "pytest gpu rc=$?"; tail -12 gpurun_out/${tag}_pytest_gpu.log
 CMD="python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu"
-for v in "" _c7; do
+for v in "" _s _t; do
   export LIME_B200_LIB=$PWD/lime_b200/liblime_b200$v.so
   timeout 300 $CMD > gpurun_out/${tag}_bench$v.json 2> gpurun_out/${tag}_bench$v.err; echo "bench$v rc=$?"
   python - <<PY
