@@ -317,6 +317,10 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
     const bool aligned = ((reinterpret_cast<uintptr_t>(P.lcp) | reinterpret_cast<uintptr_t>(P.da) |
                            (SCORE && EBWT ? reinterpret_cast<uintptr_t>(P.ebwt) : 0)) & 15u) == 0;
     constexpr unsigned STAGE_BYTES = CH * sizeof(lcp_t) + CH * 4u + (SCORE && EBWT ? (unsigned)CH : 0u);
+#if !LIME_K12_TMA
+    // this lane's 16 bytes of the stage; deliberately from threadIdx (not provably warp-uniform, see stage_issue)
+    const unsigned s_stage = (unsigned)__cvta_generic_to_shared(&sm.w[threadIdx.x >> 5]) + 16 * (threadIdx.x & 31u);
+#endif
     auto stage_issue = [&](uint64_t cc) -> bool {             // all lanes, after a __syncwarp: the stage is free
         if (cc >= n_chunks) return false;
         const uint64_t aa = cc * OWN;
@@ -332,18 +336,22 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
         }
 #else
         {
-            // 16 bytes per lane and copy: piece k of an array lies 512 bytes after piece k - 1
-            const uint64_t pol_in = P.pol_evict_first;
+            // 16 bytes per lane and copy: piece k of an array lies 512 bytes after piece k - 1.  The policy word is
+            // made here (one instruction): taken from the kernel parameters it lands in a uniform register, and
+            // LDGSTS with a uniform cache-hint operand faults as an illegal instruction on sm_100a
+            const uint64_t pol_in = policy_evict_first();
             const char *pl = reinterpret_cast<const char *>(g_lcp + aa) + 16 * lane;
             const char *pd = reinterpret_cast<const char *>(P.da + aa) + 16 * lane;
-            const unsigned s_lcp = (unsigned)__cvta_generic_to_shared(ws.lcp) + 16 * lane;
-            const unsigned s_da = (unsigned)__cvta_generic_to_shared(ws.da) + 16 * lane;
+            // (the shared address comes from a per-lane register set up once, s_stage: an address that ptxas can
+            // split into register + uniform register makes it emit an LDGSTS form that faults on sm_100a)
+            const unsigned s_lcp = s_stage;
+            const unsigned s_da = s_stage + (unsigned)(CH * sizeof(lcp_t));
 #pragma unroll
             for (int k = 0; k < (int)(CH * sizeof(lcp_t) / 512); k++) cp_async16_hint(s_lcp + 512 * k, pl + 512 * k, pol_in);
 #pragma unroll
             for (int k = 0; k < CH * 4 / 512; k++) cp_async16_hint(s_da + 512 * k, pd + 512 * k, pol_in);
             if (SCORE && EBWT)
-                cp_async16_hint((unsigned)__cvta_generic_to_shared(ws.eb) + 16 * lane, P.ebwt + aa + 16 * lane, pol_in);
+                cp_async16_hint(s_da + CH * 4u, P.ebwt + aa + 16 * lane, pol_in);
         }
 #endif
         return true;

@@ -5,7 +5,7 @@ tag=${1:-r02b}
 mkdir -p gpurun_out
 timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/${tag}_pytest_gpu.log 2>&1; echo "pytest gpu rc=$?"; tail -12 gpurun_out/${tag}_pytest_gpu.log
 CMD="python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu"
-for v in "" _s _t; do
+for v in "" _s; do
   export LIME_B200_LIB=$PWD/lime_b200/liblime_b200$v.so
   timeout 300 $CMD > gpurun_out/${tag}_bench$v.json 2> gpurun_out/${tag}_bench$v.err; echo "bench$v rc=$?"
   python - <<PY
@@ -19,3 +19,5 @@ PY
   timeout 300 ncu --set full --clock-control none --import-source on -k "regex:stream_kernel" -s 2 -c 1 -o gpurun_out/${tag}_k12$v python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu > gpurun_out/${tag}_ncu_k12$v.log 2>&1
   echo "k12$v capture rc=$?"
 done
+unset LIME_B200_LIB
+timeout 300 python tools/k12_modes.py > gpurun_out/${tag}_modes.log 2>&1; echo "modes rc=$?"; cat gpurun_out/${tag}_modes.log | cut -c1-400
