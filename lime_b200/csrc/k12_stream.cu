@@ -59,6 +59,9 @@ constexpr int UNROLL_A = LIME_K12_UNROLL_A;
 #ifndef LIME_K12_TMA
 #define LIME_K12_TMA 0                    // stage by TMA bulk copies (1) or by per-lane 16-byte cp.async (0)
 #endif
+#ifndef LIME_K12_L2PF
+#define LIME_K12_L2PF 1                   // pull the chunk after the next one into L2 (per-lane prefetch instructions)
+#endif
 #ifndef LIME_K12_BLOCKED
 #define LIME_K12_BLOCKED 1                // one contiguous chunk range per CTA (1) or a grid stride (0)
 #endif
@@ -321,7 +324,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
     // this lane's 16 bytes of the stage; deliberately from threadIdx (not provably warp-uniform, see stage_issue)
     const unsigned s_stage = (unsigned)__cvta_generic_to_shared(&sm.w[threadIdx.x >> 5]) + 16 * (threadIdx.x & 31u);
 #endif
-    auto stage_issue = [&](uint64_t cc) -> bool {             // all lanes, after a __syncwarp: the stage is free
+    auto stage_issue = [&](uint64_t cc, uint64_t cc2) -> bool {   // all lanes, after a __syncwarp: the stage is free; cc2: the chunk after cc
         if (cc >= n_chunks) return false;
         const uint64_t aa = cc * OWN;
         if (!aligned || aa + CH > P.n_total) return false;
@@ -352,6 +355,23 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
             for (int k = 0; k < CH * 4 / 512; k++) cp_async16_hint(s_da + 512 * k, pd + 512 * k, pol_in);
             if (SCORE && EBWT)
                 cp_async16_hint(s_da + CH * 4u, P.ebwt + aa + 16 * lane, pol_in);
+#if LIME_K12_L2PF
+            // ... and the chunk after that one is pulled from DRAM into L2 a whole chunk period ahead, one 128-byte
+            // line per lane: its copy then completes with L2 latency, whatever the DRAM queues look like
+            {
+                const uint64_t ab = cc2 * OWN;
+                if (cc2 < n_chunks && ab + CH <= P.n_total) {
+                    constexpr unsigned L_LCP = CH * sizeof(lcp_t) / 128, L_DA = CH * 4 / 128, L_EB = (SCORE && EBWT) ? CH / 128 : 0;
+                    const char *q = nullptr;
+                    if (lane < L_LCP) q = reinterpret_cast<const char *>(g_lcp + ab) + 128 * lane;
+                    else if (lane < L_LCP + L_DA) q = reinterpret_cast<const char *>(P.da + ab) + 128 * (lane - L_LCP);
+                    if (q) asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
+                    if (L_EB && lane < L_EB) asm volatile("prefetch.global.L2 [%0];" ::"l"(P.ebwt + ab + 128 * lane));
+                    if (L_LCP + L_DA > 32 && lane < L_LCP + L_DA - 32)      // (never with 512-position chunks)
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(P.da + ab) + 128 * (lane + 32 - L_LCP)));
+                }
+            }
+#endif
         }
 #endif
         return true;
@@ -375,7 +395,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
     // whether a staged chunk is in flight and the phase of its barrier live in shared memory, not in registers
     unsigned &pipe = sm.pipe[warp];
     {
-        const bool st0 = stage_issue(c_first);
+        const bool st0 = stage_issue(c_first, chunk_of(1));
         if (lane == 0) pipe = st0 ? 1u : 0u;
         __syncwarp();
     }
@@ -428,7 +448,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
         // scoring right away.  The copy lands while this chunk is scored.
         auto issue_next = [&]() {
             __syncwarp();
-            const bool st = stage_issue(chunk_of(t_it + 1));
+            const bool st = stage_issue(chunk_of(t_it + 1), chunk_of(t_it + 2));
             // the phase bit flips whenever a staged chunk has been consumed
             if (lane == 0) pipe = (st ? 1u : 0u) | ((((pst >> 1) ^ pst) & 1u) << 1);
             __syncwarp();
