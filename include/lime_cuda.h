@@ -204,11 +204,14 @@ int  lime_sim_import(lime_ctx *ctx, const void *dev_triples, uint64_t n_triples)
  *   lime_xchg_accumulate  lime_cluster_similarity with every update appended to a local list (capacity
  *                         flat_cap records), then sorted by owner and written into this rank's region of each
  *                         owner's inbox -- bulk stores over NVLink / NVSwitch, nothing remote is read or updated
- *                         atomically.  dev_sent (DEVICE memory, [world] uint64) receives the records sent to
- *                         every owner;
- *   (caller)              all-gather of dev_sent over the ranks -> dev_counts_all [world][world] (source major):
- *                         the job's only collective per strand, and the barrier "every source has delivered";
- *   lime_xchg_apply       adds the records of all regions of this rank's inbox to the slab;
+ *                         atomically.  Inside an owner the records are also split by row block of its slab (each
+ *                         block small enough for L2).  dev_sent (DEVICE memory, lime_xchg_counts_len() uint64 =
+ *                         [world][row blocks]) receives the records sent to every owner and block;
+ *   (caller)              all-gather of dev_sent over the ranks -> dev_counts_all [world][lime_xchg_counts_len()]
+ *                         (source major): the job's only collective per strand, and the barrier "every source
+ *                         has delivered";
+ *   lime_xchg_apply       adds the records of all regions of this rank's inbox to the slab, row block after row
+ *                         block (the slab's lines stay in L2 while their records arrive);
  *   lime_xchg_choose      clusterChoose (ClusterBWT_DA.cpp:361-450) of the owned reads into strand slot `strand`.
  * None of the three synchronises with the host.  lime_classify then classifies the owned reads and reads the
  * strands' device state back: LIME_ERR_RETRY means the job must be redone through lime_sim_export / lime_sim_import
@@ -225,6 +228,7 @@ int  lime_sim_import(lime_ctx *ctx, const void *dev_triples, uint64_t n_triples)
 int  lime_xchg_alloc(lime_ctx *ctx, int world, int rank, uint32_t reads_per_rank, uint32_t n_refs, int n_strands,
                      uint64_t flat_cap, uint64_t inbox_cap, uint8_t *ipc_handle);
 int  lime_xchg_open(lime_ctx *ctx, const uint8_t *ipc_handles);
+int  lime_xchg_counts_len(lime_ctx *ctx);
 int  lime_xchg_close(lime_ctx *ctx);
 int  lime_xchg_accumulate(lime_ctx *ctx, uint32_t alpha, int ebwt_mode, int strand, uint64_t *dev_sent);
 int  lime_xchg_apply(lime_ctx *ctx, int strand, const uint64_t *dev_counts_all);

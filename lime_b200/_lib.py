@@ -60,6 +60,7 @@ SIGNATURES = {
     "lime_classify_result": (C.c_int, [vp, vp, vp, vp, C.c_int]),
     "lime_xchg_alloc": (C.c_int, [vp, C.c_int, C.c_int, C.c_uint32, C.c_uint32, C.c_int, C.c_uint64, C.c_uint64, vp]),
     "lime_xchg_open": (C.c_int, [vp, vp]),
+    "lime_xchg_counts_len": (C.c_int, [vp]),
     "lime_xchg_close": (C.c_int, [vp]),
     "lime_xchg_accumulate": (C.c_int, [vp, C.c_uint32, C.c_int, C.c_int, vp]),
     "lime_xchg_apply": (C.c_int, [vp, C.c_int, vp]),

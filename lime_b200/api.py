@@ -191,6 +191,10 @@ class LimeContext:
             handles = np.ascontiguousarray(handles, dtype=np.uint8).reshape(-1)
         self._ck(self.lib.lime_xchg_open(self.h, _ptr(handles)))
 
+    def xchg_counts_len(self):
+        """uint64 counters a rank contributes to the all-gather of a strand: world x row blocks."""
+        return int(self.lib.lime_xchg_counts_len(self.h))
+
     def xchg_close(self):
         self._ck(self.lib.lime_xchg_close(self.h))
 

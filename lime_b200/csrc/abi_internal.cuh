@@ -26,10 +26,10 @@ enum {
     SS_ERR,            // bit0 halo exhausted, bit2 inbox region overflow, bit3 record out of range
     SS_TILE_COUNTER,   // u32 used
     SS_FLAT_COUNT, SS_APPLIED_T, SS_APPLIED_N,
-    SS_SENT = 16,      // [XCHG_MAX] records routed to every owner
-    SS_COUNT = 32
+    SS_SENT = 16,      // [XCHG_MAX][XCHG_SUB_MAX] records routed to every (owner, row block)
+    SS_COUNT = 160
 };
-static_assert(SS_SENT + lime::XCHG_MAX <= SS_COUNT, "strand state block");
+static_assert(SS_SENT + lime::XCHG_MAX * lime::XCHG_SUB_MAX <= SS_COUNT, "strand state block");
 
 static int fail(lime_ctx *c, int code, const std::string &msg)
 {

@@ -136,12 +136,15 @@ struct ProfEvent { int kid; cudaEvent_t a, b; };
 
 // multi-GPU exchange of similarity updates (lime_abi_xchg.cu): the rows of a read live on its owner only
 constexpr int XCHG_MAX = 16;
+constexpr int XCHG_SUB_MAX = 8;            // row blocks an owner's slab is applied in (each small enough for L2)
 struct XchgState {
     bool active = false, loopback = false;
     int world = 0, rank = 0, n_strands = 0;
     uint32_t per = 0;                      // reads per owner
     uint64_t rows = 0, pitch = 0;          // per slab
-    uint64_t flat_cap = 0, inbox_cap = 0;  // records
+    uint64_t flat_cap = 0, inbox_cap = 0;  // records; inbox_cap per (source, strand) region = n_sub * sub_cap
+    uint32_t n_sub = 1, sub_rows = 1;      // row blocks of a slab and rows per block
+    uint64_t sub_cap = 0;
     DevBuf slabs;                          // [n_strands][rows][pitch] uint8: the similarity rows of the owned reads
     DevBuf flat;                           // [flat_cap] records {read, genome << 8 | t} of the strand being scored
     void *inbox_own = nullptr;             // [n_strands][world][inbox_cap] records, plain cudaMalloc (CUDA IPC)
@@ -300,15 +303,16 @@ uint64_t k12_long_cap(uint64_t n_total);
 struct XchgRoute {
     const uint2 *flat; const unsigned long long *flat_count; uint64_t flat_cap;
     uint32_t world, per, n_refs;
+    uint32_t n_sub, sub_rows;
     uint2 *dst[XCHG_MAX];             // owner o's inbox region for this source and strand (peer or local memory)
-    uint64_t inbox_cap;
-    unsigned long long *sent;         // [world] device counters (local)
+    uint64_t sub_cap;
+    unsigned long long *sent;         // [world][n_sub] device counters (local)
     unsigned long long *err;
 };
 struct XchgApply {
-    const uint2 *src; uint64_t inbox_cap;
-    const unsigned long long *counts_all;   // [world][world], device
-    uint32_t world, rank;
+    const uint2 *src; uint64_t sub_cap;
+    const unsigned long long *counts_all;   // [world][world][n_sub], device
+    uint32_t world, rank, n_sub, sub;
     uint8_t *slab; uint64_t pitch; uint32_t rows, n_refs;
     unsigned long long *applied_t, *applied_n, *err;
 };

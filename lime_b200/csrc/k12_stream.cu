@@ -60,10 +60,15 @@ constexpr int UNROLL_A = LIME_K12_UNROLL_A;
 #define LIME_K12_TMA 0                    // stage by TMA bulk copies (1) or by per-lane 16-byte cp.async (0)
 #endif
 #ifndef LIME_K12_L2PF
-#define LIME_K12_L2PF 1                   // pull the chunk after the next one into L2 (per-lane prefetch instructions)
+#define LIME_K12_L2PF 0                   // pull the chunk after the next one into L2 (per-lane prefetch instructions): measured slower
+#endif
+#ifdef LIME_K12_EXP_SMALLTARGET           // measurement only: all adds into the first 64 Ki rows (7 MB, L2-resident); results are wrong
+#define K12_EXP_ROWMASK & 0xffffu
+#else
+#define K12_EXP_ROWMASK
 #endif
 #ifndef LIME_K12_BLOCKED
-#define LIME_K12_BLOCKED 1                // one contiguous chunk range per CTA (1) or a grid stride (0)
+#define LIME_K12_BLOCKED 0                // one contiguous chunk range per CTA (1) or a grid stride (0): the stride measured faster
 #endif
 
 enum { MODE_COUNT = 0, MODE_EMIT = 1, MODE_DIRECT = 2, MODE_FLAT = 3 };
@@ -723,7 +728,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
             if (!(leader && is_read)) gl = 0;
             // the row of a read leader, once per window
             unsigned *row_w = nullptr;
-            if (MODE == MODE_DIRECT) row_w = reinterpret_cast<unsigned *>(P.sim8 + (size_t)(gl ? id : 0u) * P.pitch8);
+            if (MODE == MODE_DIRECT) row_w = reinterpret_cast<unsigned *>(P.sim8 + (size_t)(gl ? (id K12_EXP_ROWMASK) : 0u) * P.pitch8);
             while (__any_sync(FULL, gl != 0)) {
                 const int src = gl ? 31 - __clz(gl) : 0;
                 const uint32_t Gx = __shfl_sync(FULL, vec, src);

@@ -51,7 +51,11 @@ int lime_xchg_alloc(lime_ctx *ctx, int world, int rank, uint32_t reads_per_rank,
     S.world = world; S.rank = rank; S.n_strands = n_strands; S.per = reads_per_rank;
     S.rows = reads_per_rank; S.pitch = lime_sim_pitch(n_refs);
     S.flat_cap = std::max<uint64_t>((flat_cap + K12_FLAT_BLK - 1) / K12_FLAT_BLK * K12_FLAT_BLK, K12_FLAT_BLK);
-    S.inbox_cap = std::max<uint64_t>((inbox_cap + 255) / 256 * 256, 256);
+    // the slab is applied in row blocks of at most 32 MB, so that its lines stay in L2 while their records arrive
+    S.n_sub = (uint32_t)std::min<uint64_t>(XCHG_SUB_MAX, std::max<uint64_t>(1, (S.rows * S.pitch + (32ull << 20) - 1) / (32ull << 20)));
+    S.sub_rows = (uint32_t)((S.rows + S.n_sub - 1) / S.n_sub);
+    S.sub_cap = std::max<uint64_t>(((inbox_cap + S.n_sub - 1) / S.n_sub * 5 / 4 + 255) / 256 * 256, 256);
+    S.inbox_cap = S.sub_cap * S.n_sub;
     const uint64_t slab_bytes = std::max<uint64_t>(S.rows * S.pitch * (uint64_t)n_strands, 16);
     CK(S.slabs.reserve(slab_bytes), "cudaMalloc slabs");
     CK(cudaMemsetAsync(S.slabs.p, 0, slab_bytes, ctx->stream), "memset slabs");
@@ -85,6 +89,12 @@ int lime_xchg_open(lime_ctx *ctx, const uint8_t *ipc_handles)
     S.active = true;
     ctx->sim_bound = false; ctx->d_sim = nullptr; ctx->sim_rows = 0; ctx->sim_pitch = S.pitch; ctx->sim_clean = false;
     return LIME_OK;
+}
+
+int lime_xchg_counts_len(lime_ctx *ctx)
+{
+    if (!ctx || !ctx->xchg.inbox_own) return 0;
+    return ctx->xchg.world * (int)ctx->xchg.n_sub;
 }
 
 int lime_xchg_close(lime_ctx *ctx)
@@ -124,15 +134,16 @@ int lime_xchg_accumulate(lime_ctx *ctx, uint32_t alpha, int ebwt_mode, int stran
     XchgRoute R = {};
     R.flat = F.rec; R.flat_count = F.count; R.flat_cap = F.cap;
     R.world = (uint32_t)S.world; R.per = S.per; R.n_refs = ctx->n_refs;
+    R.n_sub = S.n_sub; R.sub_rows = S.sub_rows;
     // region of this source in owner o's inbox (loopback: all owners are this GPU, the owner index picks the region)
     for (int o = 0; o < S.world; o++)
         R.dst[o] = static_cast<uint2 *>(S.inbox_map[o]) + ((uint64_t)strand * S.world + (S.loopback ? o : S.rank)) * S.inbox_cap;
-    R.inbox_cap = S.inbox_cap; R.sent = sc + SS_SENT; R.err = sc + SS_ERR;
+    R.sub_cap = S.sub_cap; R.sent = sc + SS_SENT; R.err = sc + SS_ERR;
     {
         LaunchScope ls(ctx, KID_X_ROUTE);
         CK(launch_xchg_route(R, ctx->stream), "x_route launch");
     }
-    CK(cudaMemcpyAsync(dev_sent, sc + SS_SENT, sizeof(unsigned long long) * S.world, cudaMemcpyDeviceToDevice, ctx->stream), "D2D record counts");
+    CK(cudaMemcpyAsync(dev_sent, sc + SS_SENT, sizeof(unsigned long long) * S.world * S.n_sub, cudaMemcpyDeviceToDevice, ctx->stream), "D2D record counts");
     return LIME_OK;
 }
 
@@ -146,13 +157,14 @@ int lime_xchg_apply(lime_ctx *ctx, int strand, const uint64_t *dev_counts_all)
     unsigned long long *sc = strand_scalar<unsigned long long>(ctx, strand, 0);
     XchgApply A = {};
     A.src = static_cast<const uint2 *>(S.inbox_own) + (uint64_t)strand * S.world * S.inbox_cap;
-    A.inbox_cap = S.inbox_cap;
+    A.sub_cap = S.sub_cap;
     A.counts_all = reinterpret_cast<const unsigned long long *>(dev_counts_all);
-    A.world = (uint32_t)S.world; A.rank = (uint32_t)S.rank;
+    A.world = (uint32_t)S.world; A.rank = (uint32_t)S.rank; A.n_sub = S.n_sub;
     A.slab = S.slabs.as<uint8_t>() + (uint64_t)strand * S.rows * S.pitch; A.pitch = S.pitch;
     A.rows = (uint32_t)S.rows; A.n_refs = ctx->n_refs;
     A.applied_t = sc + SS_APPLIED_T; A.applied_n = sc + SS_APPLIED_N; A.err = sc + SS_ERR;
-    {
+    for (uint32_t sub = 0; sub < S.n_sub; sub++) {             // row block after row block: the slab lines stay in L2
+        A.sub = sub;
         LaunchScope ls(ctx, KID_X_APPLY);
         CK(launch_xchg_apply(A, ctx->stream), "x_apply launch");
     }

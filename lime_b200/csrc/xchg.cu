@@ -9,8 +9,11 @@
 //                 memory over NVLink / NVSwitch (CUDA IPC mapping), or local memory for its own reads.
 //                 Space in an inbox region (one per source GPU) is taken with a LOCAL atomic: only this GPU
 //                 writes to its region, so nothing remote is ever read or updated atomically.
-//   apply_kernel  (on the owner, after all sources have finished) adds the records of every source region
-//                 to the owner's uint8 rows with fire-and-forget adds and sums their t for the carry proof.
+//                 Inside an owner the records are also split by row block (n_sub blocks of the slab, each small
+//                 enough for L2), so that the owner can apply block after block with its slab lines in L2.
+//   apply_kernel  (on the owner, after all sources have finished) adds the records of one row block from every
+//                 source region to the owner's uint8 rows with fire-and-forget adds and sums their t for the carry
+//                 proof; one launch per row block.
 // The only collective is the all-gather of the per-owner record counts in between, which is also the barrier.
 #include "common.cuh"
 #include <algorithm>
@@ -22,15 +25,17 @@ constexpr int THREADS = 256;
 constexpr int PER_THREAD = 8;
 constexpr int TILE = THREADS * PER_THREAD;      // records per tile
 
+constexpr int BINS_MAX = XCHG_MAX * XCHG_SUB_MAX;
 struct RouteArgs {
     const uint2 *flat;
     const unsigned long long *flat_count;       // slots in use (device); clamped to flat_cap
     uint64_t flat_cap;
     uint32_t world, per, magic;                 // owner of read r = r / per; magic = min(floor(2^32 / per), 2^32 - 1)
+    uint32_t n_sub, sub_rows, sub_magic;        // row block of a row inside its owner's slab = row / sub_rows
     uint32_t n_refs;
-    uint2 *dst[XCHG_MAX];                       // owner o's inbox region for this source and strand
-    uint64_t inbox_cap;                         // records per region
-    unsigned long long *sent;                   // [world] records written per owner (device, local)
+    uint2 *dst[XCHG_MAX];                       // owner o's inbox region for this source and strand: [n_sub][sub_cap]
+    uint64_t sub_cap;                           // records per row block of a region
+    unsigned long long *sent;                   // [world][n_sub] records written (device, local)
     unsigned long long *err;                    // bit 2: a region overflowed, bit 3: record out of range
 };
 
@@ -45,13 +50,14 @@ __device__ __forceinline__ uint32_t owner_of(uint32_t r, uint32_t per, uint32_t 
 __global__ void __launch_bounds__(THREADS) route_kernel(const RouteArgs P)
 {
     __shared__ uint2 s_rec[TILE];
-    __shared__ unsigned s_cnt[XCHG_MAX], s_off[XCHG_MAX + 1];
-    __shared__ unsigned long long s_base[XCHG_MAX];
+    __shared__ unsigned s_cnt[BINS_MAX], s_off[BINS_MAX + 1];
+    __shared__ unsigned long long s_base[BINS_MAX];
     const unsigned tid = threadIdx.x, lane = tid & 31u;
+    const unsigned n_bins = P.world * P.n_sub;
     const unsigned long long n = min(*P.flat_count, (unsigned long long)P.flat_cap);
     const unsigned long long n_tiles = (n + TILE - 1) / TILE;
     for (unsigned long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        if (tid < XCHG_MAX) s_cnt[tid] = 0;
+        if (tid < BINS_MAX) s_cnt[tid] = 0;
         __syncthreads();
         uint2 rec[PER_THREAD];
         unsigned own[PER_THREAD], idx[PER_THREAD];
@@ -67,9 +73,13 @@ __global__ void __launch_bounds__(THREADS) route_kernel(const RouteArgs P)
             if (valid) {
                 q = owner_of(rec[k].x, P.per, P.magic, rem);
                 if (q >= P.world || (rec[k].y >> 8) >= P.n_refs) { valid = false; atomicOr(P.err, 8ull); }
+                else {
+                    uint32_t r2;
+                    q = q * P.n_sub + owner_of(rem, P.sub_rows, P.sub_magic, r2);      // bin = (owner, row block)
+                }
             }
             rec[k].x = rem;                                            // row inside the owner's slab
-            // the lanes that go to the same owner take their slots with one shared-memory atomic
+            // the lanes that go to the same bin take their slots with one shared-memory atomic
             const unsigned mm = __match_any_sync(FULL, valid ? q : 0xffffffffu);
             unsigned base = 0;
             const int leader = __ffs(mm) - 1;
@@ -79,24 +89,37 @@ __global__ void __launch_bounds__(THREADS) route_kernel(const RouteArgs P)
             idx[k] = base + __popc(mm & ((1u << lane) - 1u));
         }
         __syncthreads();
-        if (tid == 0) {
-            unsigned run = 0;
-            for (unsigned o = 0; o < P.world; o++) { s_off[o] = run; run += s_cnt[o]; }
-            s_off[P.world] = run;
+        if (tid < 32) {
+            // exclusive prefix of the bin counts (n_bins <= 128: four per lane)
+            unsigned c4[4], sum = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) { const unsigned b = 4 * tid + j; c4[j] = b < n_bins ? s_cnt[b] : 0u; sum += c4[j]; }
+            unsigned incl = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned y = __shfl_up_sync(FULL, incl, o);
+                if (tid >= (unsigned)o) incl += y;
+            }
+            unsigned run = incl - sum;
+#pragma unroll
+            for (int j = 0; j < 4; j++) { const unsigned b = 4 * tid + j; if (b < n_bins) s_off[b] = run; run += c4[j]; }
+            if (tid == 31) s_off[n_bins] = incl;
         }
-        if (tid < P.world && s_cnt[tid]) s_base[tid] = atomicAdd(&P.sent[tid], (unsigned long long)s_cnt[tid]);
+        if (tid >= 64 && tid - 64 < n_bins && s_cnt[tid - 64])
+            s_base[tid - 64] = atomicAdd(&P.sent[tid - 64], (unsigned long long)s_cnt[tid - 64]);
         __syncthreads();
 #pragma unroll
         for (int k = 0; k < PER_THREAD; k++)
             if (own[k] != 0xffffffffu) s_rec[s_off[own[k]] + idx[k]] = rec[k];
         __syncthreads();
-        // sorted by owner: consecutive threads write consecutive records of one owner's run
-        const unsigned total = s_off[P.world];
+        // sorted by bin: consecutive threads write consecutive records of one bin's run
+        const unsigned total = s_off[n_bins];
         for (unsigned i = tid; i < total; i += THREADS) {
-            unsigned o = 0;
-            while (i >= s_off[o + 1]) o++;
-            const unsigned long long d = s_base[o] + (i - s_off[o]);
-            if (d < P.inbox_cap) P.dst[o][d] = s_rec[i];
+            unsigned lo = 0, hi = n_bins;                              // last bin with s_off <= i
+            while (hi - lo > 1) { const unsigned mid = (lo + hi) >> 1; if (s_off[mid] <= i) lo = mid; else hi = mid; }
+            const unsigned long long d = s_base[lo] + (i - s_off[lo]);
+            const unsigned o = lo / P.n_sub, sb = lo - o * P.n_sub;
+            if (d < P.sub_cap) P.dst[o][(size_t)sb * P.sub_cap + d] = s_rec[i];
             else atomicOr(P.err, 4ull);
         }
         __syncthreads();
@@ -105,10 +128,10 @@ __global__ void __launch_bounds__(THREADS) route_kernel(const RouteArgs P)
 }
 
 struct ApplyArgs {
-    const uint2 *src;                           // this owner's inbox regions of one strand: [world][inbox_cap]
-    uint64_t inbox_cap;
-    const unsigned long long *counts_all;       // [world][world] records sent by source p to owner o (all-gathered)
-    uint32_t world, rank;
+    const uint2 *src;                           // this owner's inbox regions of one strand: [world][n_sub][sub_cap]
+    uint64_t sub_cap;
+    const unsigned long long *counts_all;       // [world][world][n_sub] records sent by source p to (owner o, row block)
+    uint32_t world, rank, n_sub, sub;           // sub: the row block this launch applies
     uint8_t *slab; uint64_t pitch;
     uint32_t rows, n_refs;
     unsigned long long *applied_t;              // sum of t added (carry proof: must equal the byte sum of the slab)
@@ -120,9 +143,9 @@ struct ApplyArgs {
 __global__ void __launch_bounds__(THREADS) apply_kernel(const ApplyArgs P)
 {
     const unsigned p = blockIdx.y;
-    unsigned long long n = P.counts_all[(size_t)p * P.world + P.rank];
-    if (n > P.inbox_cap) { if (threadIdx.x == 0 && blockIdx.x == 0) atomicOr(P.err, 4ull); n = P.inbox_cap; }
-    const uint2 *src = P.src + (size_t)p * P.inbox_cap;
+    unsigned long long n = P.counts_all[((size_t)p * P.world + P.rank) * P.n_sub + P.sub];
+    if (n > P.sub_cap) { if (threadIdx.x == 0 && blockIdx.x == 0) atomicOr(P.err, 4ull); n = P.sub_cap; }
+    const uint2 *src = P.src + ((size_t)p * P.n_sub + P.sub) * P.sub_cap;
     uint64_t pol;
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
     unsigned long long tsum = 0, cnt = 0;
@@ -166,9 +189,11 @@ cudaError_t launch_xchg_route(const XchgRoute &a, cudaStream_t s)
     P.flat = a.flat; P.flat_count = a.flat_count; P.flat_cap = a.flat_cap;
     P.world = a.world; P.per = a.per;
     P.magic = (uint32_t)std::min<uint64_t>((1ull << 32) / std::max<uint32_t>(a.per, 1u), 0xffffffffull);
+    P.n_sub = a.n_sub; P.sub_rows = a.sub_rows;
+    P.sub_magic = (uint32_t)std::min<uint64_t>((1ull << 32) / std::max<uint32_t>(a.sub_rows, 1u), 0xffffffffull);
     P.n_refs = a.n_refs;
     for (int o = 0; o < XCHG_MAX; o++) P.dst[o] = o < (int)a.world ? a.dst[o] : nullptr;
-    P.inbox_cap = a.inbox_cap; P.sent = a.sent; P.err = a.err;
+    P.sub_cap = a.sub_cap; P.sent = a.sent; P.err = a.err;
     xchg::route_kernel<<<148 * 4, xchg::THREADS, 0, s>>>(P);
     return cudaGetLastError();
 }
@@ -176,7 +201,8 @@ cudaError_t launch_xchg_route(const XchgRoute &a, cudaStream_t s)
 cudaError_t launch_xchg_apply(const XchgApply &a, cudaStream_t s)
 {
     xchg::ApplyArgs P;
-    P.src = a.src; P.inbox_cap = a.inbox_cap; P.counts_all = a.counts_all; P.world = a.world; P.rank = a.rank;
+    P.src = a.src; P.sub_cap = a.sub_cap; P.counts_all = a.counts_all; P.world = a.world; P.rank = a.rank;
+    P.n_sub = a.n_sub; P.sub = a.sub;
     P.slab = a.slab; P.pitch = a.pitch; P.rows = a.rows; P.n_refs = a.n_refs;
     P.applied_t = a.applied_t; P.applied_n = a.applied_n; P.err = a.err;
     const dim3 grid((148 * 8 + a.world - 1) / a.world, a.world);

@@ -110,12 +110,13 @@ class CudaBackend:
         parts = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(parts, mine)
         self.ctx.xchg_open(torch.stack(parts).cpu().numpy() if world > 1 else None)
-        self._sent = torch.zeros(n_strands, world, dtype=torch.int64, device=self.device)
-        self._counts = torch.zeros(n_strands, world * world, dtype=torch.int64, device=self.device)
+        k = self.ctx.xchg_counts_len()          # world x row blocks of a slab
+        self._sent = torch.zeros(n_strands, k, dtype=torch.int64, device=self.device)
+        self._counts = torch.zeros(n_strands, world * k, dtype=torch.int64, device=self.device)
         dist.barrier()                       # every rank has mapped every inbox
 
     def xchg_accumulate(self, alpha, ebwt_mode, strand):
-        """-> device tensor [world]: records this rank sent to every owner (filled asynchronously)."""
+        """-> device tensor [world x row blocks]: records this rank sent to every owner (filled asynchronously)."""
         self.ctx.xchg_accumulate(alpha, ebwt_mode, strand, self._sent[strand].data_ptr())
         return self._sent[strand]
 

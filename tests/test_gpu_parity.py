@@ -196,12 +196,13 @@ def test_xchg_loopback(oracle, ebwt_mode, alpha, world):
             c.set_stream(torch.cuda.current_stream().cuda_stream)
             c.xchg_alloc(world, rank, per, n_refs, 2, 2_000_000, 300_000)
             c.xchg_open(None)
-            sent = torch.zeros(2, world, dtype=torch.int64, device="cuda:0")
+            k = c.xchg_counts_len()                                     # world x row blocks
+            sent = torch.zeros(2, k, dtype=torch.int64, device="cuda:0")
             for rep in range(2):
                 for strand in (0, 1):
                     c.load(case["lcp"], case["da"], ebwt, n_reads, n_refs)
                     c.xchg_accumulate(alpha, ebwt_mode, strand, sent[strand].data_ptr())
-                    counts = torch.zeros(world, world, dtype=torch.int64, device="cuda:0")
+                    counts = torch.zeros(world, k, dtype=torch.int64, device="cuda:0")
                     counts[rank] = sent[strand]                         # this source's row of the all-gather
                     c.xchg_apply(strand, counts.data_ptr())
                     slab = c.sim_matrix(rows=per)
@@ -237,7 +238,7 @@ def test_xchg_reports_cells_above_255_and_short_lists(oracle):
             c.set_stream(torch.cuda.current_stream().cuda_stream)
             c.xchg_alloc(1, 0, case["n_reads"], case["n_refs"], 2, flat_cap, 1 << 20)
             c.xchg_open(None)
-            sent = torch.zeros(2, 1, dtype=torch.int64, device="cuda:0")
+            sent = torch.zeros(2, c.xchg_counts_len(), dtype=torch.int64, device="cuda:0")
             for strand in (0, 1):
                 c.load(case["lcp"], case["da"], case["ebwt"], case["n_reads"], case["n_refs"])
                 c.xchg_accumulate(16, 1, strand, sent[strand].data_ptr())
