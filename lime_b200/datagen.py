@@ -56,8 +56,8 @@ def exact_collection(reads, genomes, terminator=b"$"):
 
 def exact_collection_fast(reads, genomes, terminator=b"$"):
     """The same arrays as exact_collection for collections of 10^5..10^7 positions: prefix doubling and a
-    vectorised LCP in numpy instead of sorting Python strings (tests/test_oracle_vs_reference.py checks the
-    two against each other)."""
+    vectorised LCP in numpy instead of sorting Python strings (tests/test_datagen.py checks the two against
+    each other)."""
     seqs = list(reads) + list(genomes)
     D = len(seqs)
     lens = np.array([len(x) for x in seqs], dtype=np.int64)
