@@ -48,28 +48,7 @@ constexpr int NONE = 1 << 30;
 constexpr int MAXFAST = 32;               // longest cluster the window path takes
 constexpr int SCAP = CH + 32;             // stream capacity incl. one window of padding
 constexpr uint32_t ID_MASK = K12_ID_LIMIT;   // packed stream element: id | class << 27 | start << 31
-#ifndef LIME_K12_CTAS
-#define LIME_K12_CTAS 8                   // 8 x 4 warps: <= 64 registers, 27.4 KB of shared memory per CTA
-#endif
-constexpr int CTAS_PER_SM = LIME_K12_CTAS;
-#ifndef LIME_K12_UNROLL_A
-#define LIME_K12_UNROLL_A 16              // words of phase A in flight together
-#endif
-constexpr int UNROLL_A = LIME_K12_UNROLL_A;
-#ifndef LIME_K12_TMA
-#define LIME_K12_TMA 0                    // stage by TMA bulk copies (1) or by per-lane 16-byte cp.async (0)
-#endif
-#ifndef LIME_K12_L2PF
-#define LIME_K12_L2PF 0                   // pull the chunk after the next one into L2 (per-lane prefetch instructions): measured slower
-#endif
-#ifdef LIME_K12_EXP_SMALLTARGET           // measurement only: all adds into the first 64 Ki rows (7 MB, L2-resident); results are wrong
-#define K12_EXP_ROWMASK & 0xffffu
-#else
-#define K12_EXP_ROWMASK
-#endif
-#ifndef LIME_K12_BLOCKED
-#define LIME_K12_BLOCKED 0                // one contiguous chunk range per CTA (1) or a grid stride (0): the stride measured faster
-#endif
+constexpr int CTAS_PER_SM = 8;            // 8 x 4 warps: 64 registers, 27.4 KB of shared memory per CTA
 
 enum { MODE_COUNT = 0, MODE_EMIT = 1, MODE_DIRECT = 2, MODE_FLAT = 3 };
 
@@ -135,15 +114,6 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned
 {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(mbar), "l"(pol) : "memory");
-}
-// 16-byte asynchronous global -> shared copy (LDGSTS), L1 bypassed, with an L2 eviction policy
-__device__ __forceinline__ void cp_async16_hint(unsigned smem_addr, const void *gmem, uint64_t pol)
-{
-    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(smem_addr), "l"(gmem), "l"(pol) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all()
-{
-    asm volatile("cp.async.wait_all;" ::: "memory");
 }
 __device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity)
 {
@@ -325,15 +295,10 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
     const bool aligned = ((reinterpret_cast<uintptr_t>(P.lcp) | reinterpret_cast<uintptr_t>(P.da) |
                            (SCORE && EBWT ? reinterpret_cast<uintptr_t>(P.ebwt) : 0)) & 15u) == 0;
     constexpr unsigned STAGE_BYTES = CH * sizeof(lcp_t) + CH * 4u + (SCORE && EBWT ? (unsigned)CH : 0u);
-#if !LIME_K12_TMA
-    // this lane's 16 bytes of the stage; deliberately from threadIdx (not provably warp-uniform, see stage_issue)
-    const unsigned s_stage = (unsigned)__cvta_generic_to_shared(&sm.w[threadIdx.x >> 5]) + 16 * (threadIdx.x & 31u);
-#endif
-    auto stage_issue = [&](uint64_t cc, uint64_t cc2) -> bool {   // all lanes, after a __syncwarp: the stage is free; cc2: the chunk after cc
+    auto stage_issue = [&](uint64_t cc) -> bool {             // all lanes, after a __syncwarp: the stage is free
         if (cc >= n_chunks) return false;
         const uint64_t aa = cc * OWN;
         if (!aligned || aa + CH > P.n_total) return false;
-#if LIME_K12_TMA
         if (lane == 0) {
             const uint64_t pol_in = P.pol_evict_first;
             fence_proxy_async_smem();
@@ -342,65 +307,21 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
             bulk_g2s((unsigned)__cvta_generic_to_shared(ws.da), P.da + aa, CH * 4u, mb, pol_in);
             if (SCORE && EBWT) bulk_g2s((unsigned)__cvta_generic_to_shared(ws.eb), P.ebwt + aa, CH, mb, pol_in);
         }
-#else
-        {
-            // 16 bytes per lane and copy: piece k of an array lies 512 bytes after piece k - 1.  The policy word is
-            // made here (one instruction): taken from the kernel parameters it lands in a uniform register, and
-            // LDGSTS with a uniform cache-hint operand faults as an illegal instruction on sm_100a
-            const uint64_t pol_in = policy_evict_first();
-            const char *pl = reinterpret_cast<const char *>(g_lcp + aa) + 16 * lane;
-            const char *pd = reinterpret_cast<const char *>(P.da + aa) + 16 * lane;
-            // (the shared address comes from a per-lane register set up once, s_stage: an address that ptxas can
-            // split into register + uniform register makes it emit an LDGSTS form that faults on sm_100a)
-            const unsigned s_lcp = s_stage;
-            const unsigned s_da = s_stage + (unsigned)(CH * sizeof(lcp_t));
-#pragma unroll
-            for (int k = 0; k < (int)(CH * sizeof(lcp_t) / 512); k++) cp_async16_hint(s_lcp + 512 * k, pl + 512 * k, pol_in);
-#pragma unroll
-            for (int k = 0; k < CH * 4 / 512; k++) cp_async16_hint(s_da + 512 * k, pd + 512 * k, pol_in);
-            if (SCORE && EBWT)
-                cp_async16_hint(s_da + CH * 4u, P.ebwt + aa + 16 * lane, pol_in);
-#if LIME_K12_L2PF
-            // ... and the chunk after that one is pulled from DRAM into L2 a whole chunk period ahead, one 128-byte
-            // line per lane: its copy then completes with L2 latency, whatever the DRAM queues look like
-            {
-                const uint64_t ab = cc2 * OWN;
-                if (cc2 < n_chunks && ab + CH <= P.n_total) {
-                    constexpr unsigned L_LCP = CH * sizeof(lcp_t) / 128, L_DA = CH * 4 / 128, L_EB = (SCORE && EBWT) ? CH / 128 : 0;
-                    const char *q = nullptr;
-                    if (lane < L_LCP) q = reinterpret_cast<const char *>(g_lcp + ab) + 128 * lane;
-                    else if (lane < L_LCP + L_DA) q = reinterpret_cast<const char *>(P.da + ab) + 128 * (lane - L_LCP);
-                    if (q) asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
-                    if (L_EB && lane < L_EB) asm volatile("prefetch.global.L2 [%0];" ::"l"(P.ebwt + ab + 128 * lane));
-                    if (L_LCP + L_DA > 32 && lane < L_LCP + L_DA - 32)      // (never with 512-position chunks)
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(P.da + ab) + 128 * (lane + 32 - L_LCP)));
-                }
-            }
-#endif
-        }
-#endif
         return true;
     };
-    // Chunk schedule: every CTA takes ONE contiguous range of chunks (its warps interleaved inside it), so that the
-    // bulk copies of a CTA walk through memory page by page.  (With a plain grid stride every copy of every warp
-    // touched a new 2 MB page, and the TMA unit serves one TLB miss at a time: ~210 cycles per copy, the L2
-    // latency of the page-table read -- which bounded the kernel at 1.8 ms whatever its instruction count.)
-#if LIME_K12_BLOCKED
-    const uint32_t per_cta = (n_chunks + gridDim.x - 1) / gridDim.x;
-    auto chunk_of = [&](uint32_t t) -> uint64_t {              // t-th chunk of this warp, or beyond n_chunks
-        const uint32_t l = t * WARPS + warp;
-        return l < per_cta ? (uint64_t)blockIdx.x * per_cta + l : (uint64_t)n_chunks;
-    };
-#else
+    // Chunk schedule: a grid stride, warp by warp.  (One contiguous range per CTA was measured too: 1.93 instead of
+    // 1.84 ms; so was pulling the chunk after the next one into L2 ahead of its copy, by bulk prefetch or by
+    // per-lane prefetch instructions: 2.0-2.1 ms; and per-lane cp.async instead of the bulk copies: the same
+    // 1.84 ms.  What bounds the kernel is the time a chunk's copy takes to arrive while the random adds into the
+    // 224 MB matrix miss L2: with the adds confined to an L2-resident 7 MB it runs at 1.41 ms.  profiles/README.md)
     auto chunk_of = [&](uint32_t t) -> uint64_t {
         return (uint64_t)blockIdx.x * WARPS + warp + (uint64_t)t * gridDim.x * WARPS;
     };
-#endif
     const uint64_t c_first = chunk_of(0);
     // whether a staged chunk is in flight and the phase of its barrier live in shared memory, not in registers
     unsigned &pipe = sm.pipe[warp];
     {
-        const bool st0 = stage_issue(c_first, chunk_of(1));
+        const bool st0 = stage_issue(c_first);
         if (lane == 0) pipe = st0 ? 1u : 0u;
         __syncwarp();
     }
@@ -415,13 +336,8 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
         uint32_t H = 0xffffffffu, R = 0;                             // lanes >= WORDS: beyond the chunk
         const unsigned pst = pipe;
         if (pst & 1u) {
-#if LIME_K12_TMA
             mbar_wait(mb, pst >> 1);
-#else
-            cp_async_wait_all();
-            __syncwarp();
-#endif
-#pragma unroll UNROLL_A
+#pragma unroll
             for (int k = 0; k < WORDS; k++) {
                 const uint32_t l = ws.lcp[32 * k + lane];
                 const uint32_t d = ws.da[32 * k + lane];
@@ -453,7 +369,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
         // scoring right away.  The copy lands while this chunk is scored.
         auto issue_next = [&]() {
             __syncwarp();
-            const bool st = stage_issue(chunk_of(t_it + 1), chunk_of(t_it + 2));
+            const bool st = stage_issue(chunk_of(t_it + 1));
             // the phase bit flips whenever a staged chunk has been consumed
             if (lane == 0) pipe = (st ? 1u : 0u) | ((((pst >> 1) ^ pst) & 1u) << 1);
             __syncwarp();
@@ -728,7 +644,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) stream_kernel(const __gr
             if (!(leader && is_read)) gl = 0;
             // the row of a read leader, once per window
             unsigned *row_w = nullptr;
-            if (MODE == MODE_DIRECT) row_w = reinterpret_cast<unsigned *>(P.sim8 + (size_t)(gl ? (id K12_EXP_ROWMASK) : 0u) * P.pitch8);
+            if (MODE == MODE_DIRECT) row_w = reinterpret_cast<unsigned *>(P.sim8 + (size_t)(gl ? id : 0u) * P.pitch8);
             while (__any_sync(FULL, gl != 0)) {
                 const int src = gl ? 31 - __clz(gl) : 0;
                 const uint32_t Gx = __shfl_sync(FULL, vec, src);
