@@ -69,4 +69,39 @@ for sync_mode in (0, 1):
     ctx.xchg_close()
     ctx.close()
 dist.barrier()
+
+# ---- part 2: the whole XchgJob (2 strands) against the single-GPU job, slot by slot ----------------------------
+dist.init_process_group("nccl", device_id=dev) if not dist.is_initialized() else None
+from lime_b200.pipeline import run_job, synthetic_lineage
+rows_, v, m = synthetic_lineage(n_refs)
+ctx = LimeContext(local)
+ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+strands = [{"ebwt": e.data_ptr(), "lcp": l.data_ptr(), "da": d.data_ptr(), "n": n}] * 2
+exp, st1 = run_job(ctx, strands, n_reads, n_refs, 100, alpha, 0.25, 1, v, m, 1, True, mem=MEM_DEVICE, deferred=False)
+exp = [np.array(x, copy=True) for x in exp]
+exp_slots = [tuple(np.array(a, copy=True) for a in ctx.choose_result(s)) for s in range(2)]
+sims = []
+for s in range(2):
+    ctx.load(l.data_ptr(), d.data_ptr(), e.data_ptr(), n_reads, n_refs, mem=MEM_DEVICE, n_total=n)
+    ctx.cluster_similarity(alpha, 1, False)
+    sims.append(ctx.sim_matrix().copy())
+be = multi.CudaBackend(ctx, torch, dev)
+shard = dict(lcp=sl, da=sd, ebwt=se, n_own=hi - lo, n_halo=k, pos_base=lo, is_last=rank == world - 1)
+job = multi.XchgJob(dist, torch, be, rank, world, n_reads, n_refs, 2, 2_000_000, 1_500_000)
+for rep in range(2):
+    job.begin()
+    for s in range(2):
+        job.run_strand(s, shard, alpha, 0.25, 1, 100)
+    got = [np.array(x, copy=True) for x in job.finish(v, m, 1, True, gather=False)]
+    diff = [int((np.asarray(g).view(np.uint8) != np.asarray(x[r_lo:r_hi]).view(np.uint8)).sum()) for g, x in zip(got, exp)]
+    print(f"rank {rank} job rep={rep}: own-range assignment byte diffs (type, tax, sim) = {diff}; stats {job.stats}", flush=True)
+    from oracle.oracle import Oracle          # diagnostic tool only
+    orc = Oracle()
+    for s in range(2):
+        b, p = ctx.choose_result(s)
+        bo, po = orc.choose(sims[s][r_lo:r_hi], 85, np.float32(0.25))
+        print(f"   rank {rank} slot {s}: records {b.shape[0]} vs {bo.shape[0]}, bin equal {b.tobytes() == bo.tobytes()}, pos equal {p.tobytes() == po.tobytes()}", flush=True)
+job.close()
+ctx.close()
+dist.barrier()
 dist.destroy_process_group()
