@@ -101,6 +101,14 @@ for rep in range(2):
         b, p = ctx.choose_result(s)
         bo, po = orc.choose(sims[s][r_lo:r_hi], 85, np.float32(0.25))
         print(f"   rank {rank} slot {s}: records {b.shape[0]} vs {bo.shape[0]}, bin equal {b.tobytes() == bo.tobytes()}, pos equal {p.tobytes() == po.tobytes()}", flush=True)
+for rep in range(2):
+    job.begin()
+    for s in range(2):
+        job.run_strand(s, shard, alpha, 0.25, 1, 100)
+    got = [np.array(x, copy=True) for x in job.finish(v, m, 1, True, gather=True)]
+    for name, g, x in zip(("type", "tax", "sim"), got, exp):
+        bad = np.flatnonzero(np.asarray(g).view(np.uint8).reshape(len(g), -1).any(axis=1) != np.asarray(x).view(np.uint8).reshape(len(x), -1).any(axis=1)) if False else np.flatnonzero(np.asarray(g) != np.asarray(x))
+        print(f"rank {rank} gathered rep={rep} {name}: {bad.shape[0]} of {len(x)} differ; first {bad[:5].tolist()} got {np.asarray(g)[bad[:5]].tolist()} want {np.asarray(x)[bad[:5]].tolist()} shape {np.asarray(g).shape} {np.asarray(g).dtype}", flush=True)
 job.close()
 ctx.close()
 dist.barrier()
