@@ -95,6 +95,11 @@ def main():
         same_p = all(np.array_equal(np.asarray(a).view(np.uint8), np.asarray(b).view(np.uint8)) for a, b in zip(got_p, exp))
         sc = all(js["n_clusters"] == st[0] and js["max_len"] == st[1] for js, st in zip(job.stats, stats))
         sc = sc and all(js["n_clusters"] == st[0] and js["max_len"] == st[1] for js, st in zip(pj.stats, stats))
+        if not same_p:
+            for name, a, b in zip(("type", "tax", "sim"), got_p, exp):
+                bad = np.flatnonzero(np.asarray(a) != np.asarray(b))
+                print(f"rank {rank}: record-exchange {name}: {bad.shape[0]} of {len(b)} reads differ, first {bad[:6].tolist()} "
+                      f"got {np.asarray(a)[bad[:6]].tolist()} want {np.asarray(b)[bad[:6]].tolist()}; xchg stats {pj.stats}", flush=True)
         kinds = {chr(t): int((got[0] == t).sum()) for t in np.unique(got[0])}
         print(f"rank {rank}/{world}: n={n} strands={n_strands} ebwt={ebwt_mode} alpha={alpha}: assignments equal={same} record-exchange job equal={same_p} "
               f"scalars equal={sc} {kinds} triples sent={[js['triples_sent'] for js in job.stats]}", flush=True)
