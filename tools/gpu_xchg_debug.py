@@ -70,46 +70,55 @@ for sync_mode in (0, 1):
     ctx.close()
 dist.barrier()
 
-# ---- part 2: the whole XchgJob (2 strands) against the single-GPU job, slot by slot ----------------------------
-dist.init_process_group("nccl", device_id=dev) if not dist.is_initialized() else None
+# ---- part 2: the whole XchgJob (2 strands with DIFFERENT data) against the single-GPU job, slot by slot -------------
 from lime_b200.pipeline import run_job, synthetic_lineage
 rows_, v, m = synthetic_lineage(n_refs)
 ctx = LimeContext(local)
 ctx.set_stream(torch.cuda.current_stream().cuda_stream)
-strands = [{"ebwt": e.data_ptr(), "lcp": l.data_ptr(), "da": d.data_ptr(), "n": n}] * 2
+data = [(e, l, d)]
+e2, l2, d2 = datagen.synth_arrays(n, n_reads, n_refs, 100, seed=78, device=dev, p_long=2e-5, max_seg=60000)
+data.append((e2, l2, d2))
+strands = [{"ebwt": a.data_ptr(), "lcp": b.data_ptr(), "da": c.data_ptr(), "n": n} for (a, b, c) in data]
 exp, st1 = run_job(ctx, strands, n_reads, n_refs, 100, alpha, 0.25, 1, v, m, 1, True, mem=MEM_DEVICE, deferred=False)
 exp = [np.array(x, copy=True) for x in exp]
-exp_slots = [tuple(np.array(a, copy=True) for a in ctx.choose_result(s)) for s in range(2)]
 sims = []
-for s in range(2):
-    ctx.load(l.data_ptr(), d.data_ptr(), e.data_ptr(), n_reads, n_refs, mem=MEM_DEVICE, n_total=n)
+for (a, b, c) in data:
+    ctx.load(b.data_ptr(), c.data_ptr(), a.data_ptr(), n_reads, n_refs, mem=MEM_DEVICE, n_total=n)
     ctx.cluster_similarity(alpha, 1, False)
     sims.append(ctx.sim_matrix().copy())
 be = multi.CudaBackend(ctx, torch, dev)
-shard = dict(lcp=sl, da=sd, ebwt=se, n_own=hi - lo, n_halo=k, pos_base=lo, is_last=rank == world - 1)
-job = multi.XchgJob(dist, torch, be, rank, world, n_reads, n_refs, 2, 2_000_000, 1_500_000)
-for rep in range(2):
-    job.begin()
-    for s in range(2):
-        job.run_strand(s, shard, alpha, 0.25, 1, 100)
-    got = [np.array(x, copy=True) for x in job.finish(v, m, 1, True, gather=False)]
-    diff = [int((np.asarray(g).view(np.uint8) != np.asarray(x[r_lo:r_hi]).view(np.uint8)).sum()) for g, x in zip(got, exp)]
-    print(f"rank {rank} job rep={rep}: own-range assignment byte diffs (type, tax, sim) = {diff}; stats {job.stats}", flush=True)
-    from oracle.oracle import Oracle          # diagnostic tool only
-    orc = Oracle()
-    for s in range(2):
-        b, p = ctx.choose_result(s)
-        bo, po = orc.choose(sims[s][r_lo:r_hi], 85, np.float32(0.25))
-        print(f"   rank {rank} slot {s}: records {b.shape[0]} vs {bo.shape[0]}, bin equal {b.tobytes() == bo.tobytes()}, pos equal {p.tobytes() == po.tobytes()}", flush=True)
-for rep in range(2):
-    job.begin()
-    for s in range(2):
-        job.run_strand(s, shard, alpha, 0.25, 1, 100)
-    got = [np.array(x, copy=True) for x in job.finish(v, m, 1, True, gather=True)]
-    for name, g, x in zip(("type", "tax", "sim"), got, exp):
-        bad = np.flatnonzero(np.asarray(g).view(np.uint8).reshape(len(g), -1).any(axis=1) != np.asarray(x).view(np.uint8).reshape(len(x), -1).any(axis=1)) if False else np.flatnonzero(np.asarray(g) != np.asarray(x))
-        print(f"rank {rank} gathered rep={rep} {name}: {bad.shape[0]} of {len(x)} differ; first {bad[:5].tolist()} got {np.asarray(g)[bad[:5]].tolist()} want {np.asarray(x)[bad[:5]].tolist()} shape {np.asarray(g).shape} {np.asarray(g).dtype}", flush=True)
-job.close()
+shards = [dict(lcp=b[lo:hi + k].clone(), da=c[lo:hi + k].clone(), ebwt=a[lo:hi + k].clone(), n_own=hi - lo, n_halo=k, pos_base=lo,
+               is_last=rank == world - 1) for (a, b, c) in data]
+from oracle.oracle import Oracle          # diagnostic tool only
+orc = Oracle()
+for check_slabs in (1, 0):
+    job = multi.XchgJob(dist, torch, be, rank, world, n_reads, n_refs, 2, 2_000_000, 1_500_000)
+    for rep in range(2):
+        job.begin()
+        for s in range(2):
+            if check_slabs:
+                # run_strand by hand, looking at the slab between apply and choose
+                be.load(shards[s]["lcp"], shards[s]["da"], shards[s]["ebwt"], shards[s]["n_own"], shards[s]["n_halo"], shards[s]["pos_base"],
+                        shards[s]["is_last"], n_reads, n_refs)
+                sent = be.xchg_accumulate(alpha, 1, s)
+                counts = be.xchg_counts_buffer(s)
+                dist.all_gather_into_tensor(counts, sent)
+                be.xchg_apply(s, counts)
+                slab = ctx.sim_matrix(rows=per)
+                bad = int((slab[:r_hi - r_lo] != sims[s][r_lo:r_hi]).sum())
+                print(f"rank {rank} rep={rep} strand {s}: slab mismatching cells={bad}; sent {sent.tolist()} counts {counts.tolist()}", flush=True)
+                be.xchg_choose(s, 85, 0.25, r_hi - r_lo)
+                job._pending.append(s)
+            else:
+                job.run_strand(s, shards[s], alpha, 0.25, 1, 100)
+        got = [np.array(x, copy=True) for x in job.finish(v, m, 1, True, gather=False)]
+        diff = [int((np.asarray(g) != np.asarray(x[r_lo:r_hi])).sum()) for g, x in zip(got, exp)]
+        print(f"rank {rank} check_slabs={check_slabs} rep={rep}: own-range assignment diffs (type, tax, sim) = {diff}", flush=True)
+        for s in range(2):
+            b, p = ctx.choose_result(s)
+            bo, po = orc.choose(sims[s][r_lo:r_hi], 85, np.float32(0.25))
+            print(f"   rank {rank} slot {s}: records {b.shape[0]} vs {bo.shape[0]}, bin equal {b.tobytes() == bo.tobytes()}, pos equal {p.tobytes() == po.tobytes()}", flush=True)
+    job.close()
 ctx.close()
 dist.barrier()
 dist.destroy_process_group()
