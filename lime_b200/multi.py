@@ -345,7 +345,12 @@ class XchgJob:
             sent = be.xchg_accumulate(alpha, ebwt_mode, slot)
         with self.timer("counts"):
             counts = be.xchg_counts_buffer(slot)
+            mode = os.environ.get("LIME_XCHG_SYNC", "0")
+            if mode in ("1", "3"):
+                self.torch.cuda.synchronize(); dist.barrier()
             dist.all_gather_into_tensor(counts, sent)          # [source][owner]; also: every source has delivered
+            if mode in ("2", "3"):
+                self.torch.cuda.synchronize(); dist.barrier()
         with self.timer("apply"):
             be.xchg_apply(slot, counts)
         with self.timer("choose"):
