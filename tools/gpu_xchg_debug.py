@@ -18,7 +18,7 @@ rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int
 torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
-n, n_reads, n_refs, alpha, halo = 2_000_003, 20_000, 40, 16, 70_000
+n, n_reads, n_refs, alpha, halo = int(os.environ.get('DBG_N', 2_000_003)), int(os.environ.get('DBG_READS', 20_000)), 40, 16, int(os.environ.get('DBG_HALO', 70_000))
 e, l, d = datagen.synth_arrays(n, n_reads, n_refs, 100, seed=77, device=dev, p_long=2e-5, max_seg=60000)
 torch.cuda.synchronize()
 ref = LimeContext(local)
@@ -107,6 +107,9 @@ for check_slabs in (1, 0):
                 slab = ctx.sim_matrix(rows=per)
                 bad = int((slab[:r_hi - r_lo] != sims[s][r_lo:r_hi]).sum())
                 print(f"rank {rank} rep={rep} strand {s}: slab mismatching cells={bad}; sent {sent.tolist()} counts {counts.tolist()}", flush=True)
+                if bad:
+                    rr, gg = np.nonzero(slab[:r_hi - r_lo] != sims[s][r_lo:r_hi])
+                    print(f"   rank {rank}: bad cells (row, genome, got, want): {[(int(a), int(b), int(slab[a, b]), int(sims[s][r_lo + a, b])) for a, b in list(zip(rr, gg))[:10]]}; status {ctx.xchg_status(s)}", flush=True)
                 be.xchg_choose(s, 85, 0.25, r_hi - r_lo)
                 job._pending.append(s)
             else:
