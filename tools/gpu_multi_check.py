@@ -89,6 +89,7 @@ def main():
             for s, sh in enumerate(shards):
                 pj.run_strand(s, sh, alpha, 0.25, ebwt_mode, 100)
             got_p = [np.array(a) for a in pj.finish(v, m, 1, True)]
+            xst = [be.xchg_status(s) for s in range(n_strands)]
         pj.close()
         # single-GPU job on the whole arrays (every rank computes it, cheap at this size)
         strands = [{"ebwt": e.data_ptr(), "lcp": l.data_ptr(), "da": d.data_ptr(), "n": n} for (e, l, d) in whole]
@@ -100,6 +101,14 @@ def main():
         sc = all(js["n_clusters"] == st[0] and js["max_len"] == st[1] for js, st in zip(job.stats, stats))
         sc = sc and all(js["n_clusters"] == st[0] and js["max_len"] == st[1] for js, st in zip(pj.stats, stats))
         if not same_p:
+            for s in range(n_strands):
+                e_, l_, d_ = whole[s]
+                ctx.load(l_.data_ptr(), d_.data_ptr(), e_.data_ptr() if ebwt_mode else None, n_reads, n_refs, mem=MEM_DEVICE, n_total=n)
+                ctx.cluster_similarity(alpha, ebwt_mode, False)
+                simm = ctx.sim_matrix()
+                r_lo, r_hi = pj.lo, pj.hi
+                print(f"rank {rank}: strand {s}: expected sum of own rows {int(simm[r_lo:r_hi].astype(np.int64).sum())}, nonzero cells {int((simm[r_lo:r_hi] != 0).sum())}; "
+                      f"xchg status of the last job: {xst[s]}", flush=True)
             for name, a, b in zip(("type", "tax", "sim"), got_p, exp):
                 bad = np.flatnonzero(np.asarray(a) != np.asarray(b))
                 print(f"rank {rank}: record-exchange {name}: {bad.shape[0]} of {len(b)} reads differ, first {bad[:6].tolist()} "
