@@ -31,17 +31,19 @@ __device__ __forceinline__ void sim_add(const K2Args &P, uint32_t r, uint32_t g,
     lime::sim_add<EXACT32>(acc, r, g, t);
 }
 
-// multi-GPU: the update leaves as a record {read, genome << 8 | t} (FlatOut); the lanes of the warp that are
-// here together take their slots with one atomic
-__device__ __forceinline__ void flat_append(const FlatOut &F, uint32_t r, uint32_t g, uint32_t t)
+// multi-GPU: the update leaves as a record {read, genome << 8 | t} (FlatOut).  Called by ALL 32 lanes of a warp
+// from converged code (t = 0: nothing to append for this lane); the lanes with a record take their slots with one
+// atomic.  (Not __activemask() inside the `if (t)`: the compiler may predicate that branch, the mask then names
+// lanes without a record and the slot arithmetic goes wrong.)
+__device__ __forceinline__ void flat_append_warp(const FlatOut &F, uint32_t r, uint32_t g, uint32_t t)
 {
-    const unsigned m = __activemask();
     const unsigned lane = lane_id();
-    const int leader = __ffs(m) - 1;
+    const unsigned m = __ballot_sync(FULL, t != 0u);
+    if (m == 0u) return;
     unsigned long long base = 0;
-    if ((int)lane == leader) base = atomicAdd(F.count, (unsigned long long)__popc(m));
-    base = __shfl_sync(m, base, leader) + __popc(m & ((1u << lane) - 1u));
-    if (base < F.cap) F.rec[base] = make_uint2(r, (g << 8) | t);
+    if (lane == 0) base = atomicAdd(F.count, (unsigned long long)__popc(m));
+    base = __shfl_sync(FULL, base, 0) + __popc(m & ((1u << lane) - 1u));
+    if (t != 0u && base < F.cap) F.rec[base] = make_uint2(r, (g << 8) | t);
 }
 
 // ---- warp path: clusters of <= 32 positions ---------------------------------------------------
@@ -261,16 +263,18 @@ __global__ void __launch_bounds__(BLOCK_THREADS) block_kernel(K2Args P)
             const uint32_t hr = __ldcg(&rlist[ri]);
             const uint32_t r = __ldcg(&keys[hr]);
             const uint4 R = __ldcg(reinterpret_cast<const uint4 *>(&cnt[(size_t)hr * 8]));
-            for (uint32_t gi = lane; gi < ng; gi += 32) {
-                const uint32_t hg = __ldcg(&glist[gi]);
-                const uint4 G = __ldcg(reinterpret_cast<const uint4 *>(&cnt[(size_t)hg * 8]));
-                const uint32_t t = (iupac ? score_iupac(R, G) : score_plain(R, G)) & 0xffu;
-                if (t) {
-                    const uint32_t g = __ldcg(&keys[hg]) - P.n_reads;
-                    if (P.flat.rec) flat_append(P.flat, r, g, t);
-                    else sim_add<EXACT32>(P, r, g, t);
-                    updates++;
+            for (uint32_t g0 = 0; g0 < ng; g0 += 32) {                 // warp-uniform trip count
+                const uint32_t gi = g0 + lane;
+                uint32_t t = 0, g = 0;
+                if (gi < ng) {
+                    const uint32_t hg = __ldcg(&glist[gi]);
+                    const uint4 G = __ldcg(reinterpret_cast<const uint4 *>(&cnt[(size_t)hg * 8]));
+                    t = (iupac ? score_iupac(R, G) : score_plain(R, G)) & 0xffu;
+                    g = __ldcg(&keys[hg]) - P.n_reads;
                 }
+                if (P.flat.rec) flat_append_warp(P.flat, r, g, t);
+                else if (t) sim_add<EXACT32>(P, r, g, t);
+                if (t) updates++;
             }
         }
         __syncthreads();
