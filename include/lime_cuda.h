@@ -217,6 +217,8 @@ int  lime_sim_import(lime_ctx *ctx, const void *dev_triples, uint64_t n_triples)
  * strands' device state back: LIME_ERR_RETRY means the job must be redone through lime_sim_export / lime_sim_import
  * (a cell exceeded 255, where the reference wraps, or a list / inbox was too small); the ranks agree on that
  * by their own collective.  lime_strand_status gives nClusters / maxLen / records / updates of this rank's shard.
+ * world, reads_per_rank, n_refs, n_strands and inbox_cap of lime_xchg_alloc must be the same on every rank: a source
+ * addresses its region inside the owner's inbox with them (flat_cap is local).
  * Call order on every rank: lime_xchg_alloc -> all-gather the 64-byte handles -> lime_xchg_open (once); per job
  * and strand: lime_load, lime_xchg_accumulate, all-gather, lime_xchg_apply, lime_xchg_choose; lime_classify.
  * lime_xchg_open(ctx, NULL) is a loopback for tests on one GPU: all owners' regions are local, rank k applies

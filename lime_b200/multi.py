@@ -327,8 +327,12 @@ class XchgJob:
         self.per = max(self.ranges[0][1] - self.ranges[0][0], 1)
         self.timer = timer or (lambda name: _NoTimer())
         self.stats, self._pending = [], []
-        self.flat_cap, self.inbox_cap = int(flat_cap), int(inbox_cap)
         self._inner = ShardedJob(dist, torch, backend, rank, world, n_reads, n_refs)   # finish() = classify + gather
+        # a source addresses its region inside the owner's inbox with the region size: the capacities must be
+        # the same on every rank (shards differ in length, e.g. the last one has no halo) -> agree on the maximum
+        caps = self._inner._cpu_or_dev([int(flat_cap), int(inbox_cap)])
+        dist.all_reduce(caps, op=dist.ReduceOp.MAX)
+        self.flat_cap, self.inbox_cap = int(caps[0].item()), int(caps[1].item())
         backend.xchg_setup(dist, world, rank, self.per, n_refs, n_strands, self.flat_cap, self.inbox_cap)
         self.closed = False
 
@@ -345,12 +349,7 @@ class XchgJob:
             sent = be.xchg_accumulate(alpha, ebwt_mode, slot)
         with self.timer("counts"):
             counts = be.xchg_counts_buffer(slot)
-            mode = os.environ.get("LIME_XCHG_SYNC", "0")
-            if mode in ("1", "3"):
-                self.torch.cuda.synchronize(); dist.barrier()
             dist.all_gather_into_tensor(counts, sent)          # [source][owner]; also: every source has delivered
-            if mode in ("2", "3"):
-                self.torch.cuda.synchronize(); dist.barrier()
         with self.timer("apply"):
             be.xchg_apply(slot, counts)
         with self.timer("choose"):
