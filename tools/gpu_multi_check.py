@@ -31,7 +31,7 @@ def main():
 
     ok = True
     big = os.environ.get("LIME_CHECK_BIG")          # one case of >= 50 M positions per strand (bench-scale kernels)
-    cases = [(3_000_001, 30_000, 40, 1, 16, 2, 4096), (2_500_003, 20_000, 9, 0, 12, 4, 70_000), (2_000_003, 9_000, 930, 0, 16, 4, 70_000)]
+    cases = [(3_000_001, 30_000, 40, 1, 16, 2, 4096), (2_500_003, 20_000, 9, 0, 12, 4, 70_000), (2_000_003, 60_000, 930, 0, 16, 4, 70_000)]
     if big:
         cases.append((int(big), 300_000, 100, 1, 16, 2, 70_000))
     for (n, n_reads, n_refs, ebwt_mode, alpha, n_strands, halo) in cases:
@@ -83,13 +83,18 @@ def main():
         # the same job with the rows on the read owner and the updates routed as records over NVLink (XchgJob)
         flat_cap, inbox_cap = multi.xchg_capacities(max(sh["n_own"] + sh["n_halo"] for sh in shards), world, density=1.0)
         pj = multi.XchgJob(dist, torch, be, rank, world, n_reads, n_refs, n_strands, flat_cap, inbox_cap)
-        got_p = None
-        for rep in range(2):                       # twice: slabs and inboxes are reused
-            pj.begin()
-            for s, sh in enumerate(shards):
-                pj.run_strand(s, sh, alpha, 0.25, ebwt_mode, 100)
-            got_p = [np.array(a) for a in pj.finish(v, m, 1, True)]
-            xst = [be.xchg_status(s) for s in range(n_strands)]
+        got_p, carried = None, False
+        try:
+            for rep in range(2):                       # twice: slabs and inboxes are reused
+                pj.begin()
+                for s, sh in enumerate(shards):
+                    pj.run_strand(s, sh, alpha, 0.25, ebwt_mode, 100)
+                got_p = [np.array(a) for a in pj.finish(v, m, 1, True)]
+                xst = [be.xchg_status(s) for s in range(n_strands)]
+        except multi.CarryDetected as ex:
+            # legitimate only if the single-GPU job takes the exact path too (checked below)
+            carried, got_p = True, None
+            print(f"rank {rank}: record exchange refused the job: {ex}", flush=True)
         pj.close()
         # single-GPU job on the whole arrays (every rank computes it, cheap at this size)
         strands = [{"ebwt": e.data_ptr(), "lcp": l.data_ptr(), "da": d.data_ptr(), "n": n} for (e, l, d) in whole]
@@ -97,9 +102,19 @@ def main():
         if got is None:
             got, job.stats = exp, [{"n_clusters": st[0], "max_len": st[1], "triples_sent": 0} for st in stats]
         same = all(np.array_equal(np.asarray(a).view(np.uint8), np.asarray(b).view(np.uint8)) for a, b in zip(got, exp))
-        same_p = all(np.array_equal(np.asarray(a).view(np.uint8), np.asarray(b).view(np.uint8)) for a, b in zip(got_p, exp))
+        if carried:
+            # a cell above 255 must also show on one GPU: the synchronising calls then take the exact path
+            exact = 0
+            for (e_, l_, d_) in whole:
+                ctx.load(l_.data_ptr(), d_.data_ptr(), e_.data_ptr() if ebwt_mode else None, n_reads, n_refs, mem=MEM_DEVICE, n_total=n)
+                ctx.cluster_similarity(alpha, ebwt_mode, False)
+                exact += int(ctx.sim_stats()["exact_pass"])
+            same_p = exact > 0
+            got_p = exp
+        else:
+            same_p = all(np.array_equal(np.asarray(a).view(np.uint8), np.asarray(b).view(np.uint8)) for a, b in zip(got_p, exp))
         sc = all(js["n_clusters"] == st[0] and js["max_len"] == st[1] for js, st in zip(job.stats, stats))
-        sc = sc and all(js["n_clusters"] == st[0] and js["max_len"] == st[1] for js, st in zip(pj.stats, stats))
+        sc = sc and (carried or all(js["n_clusters"] == st[0] and js["max_len"] == st[1] for js, st in zip(pj.stats, stats)))
         if not same_p:
             for s in range(n_strands):
                 e_, l_, d_ = whole[s]
