@@ -511,6 +511,187 @@ __global__ void __launch_bounds__(THREADS) choose_sparse_kernel(K3Args P)
     }
 }
 
+// ---- single pass for rows of 129 .. 1024 genomes (9 .. 64 sixteen-byte pieces): sparse-aware, streaming ---------
+// The shapes of BASELINE configs 3 and 4 (930 / 1000 genomes): a row is 1 KB but holds a handful of non-zero
+// cells.  Phase 1 streams the CTA's 256 rows once -- four rows (up to eight 16-byte loads per lane) in flight
+// per warp -- and keeps only the non-zero pieces, in (row, piece) order, in a per-warp shared-memory stash; a
+// piece is cleared in the matrix as soon as it is stashed (zero_after).  Phases 2 and 3 work on the stash with
+// one lane per row: row maximum and record count, then (after the block scan + look-back that places the tile)
+// the records.  A warp whose stash is full leaves the remaining rows to a plain re-read from global memory.
+constexpr int WIDE_STASH = 256;                   // pieces per warp (32 rows)
+constexpr unsigned WIDE_REREAD = 0xffffu;
+
+template <int NB>                                 // 32-piece blocks per row: 1 (<= 32 pieces) or 2 (<= 64)
+__global__ void __launch_bounds__(THREADS) choose_wide_kernel(K3Args P)
+{
+    __shared__ uint4 s_val[WARPS][WIDE_STASH];
+    __shared__ uint16_t s_piece[WARPS][WIDE_STASH];
+    __shared__ uint32_t s_cnt[TILE_READS];
+    __shared__ uint32_t s_off[TILE_READS];
+    __shared__ uint32_t s_max[TILE_READS];
+    __shared__ uint16_t s_first[TILE_READS], s_nent[TILE_READS];
+    __shared__ uint32_t s_warp_sum[WARPS];
+    __shared__ unsigned long long s_part[WARPS];
+    __shared__ unsigned s_tile;
+    __shared__ unsigned long long s_excl;
+    const int tid = threadIdx.x;
+    const unsigned lane = lane_id(), warp = tid >> 5;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    if (tid == 0) s_tile = atomicAdd(P.tile_counter, 1u);
+    __syncthreads();
+    const unsigned tile = s_tile;
+    const uint32_t n = P.read_end - P.read_begin;
+    const uint32_t r0 = tile * TILE_READS;
+    const uint32_t chunks = (uint32_t)(P.pitch8 / 16);           // <= 32 * NB
+    const float normf = (float)P.norm;
+    if (tile == 0 && tid == 0 && P.bin_cap) { P.bin[0].sim = 0.0f; P.bin[0].idRef = 0; }   // sentinel (:376-382)
+
+    // ---- phase 1: stream the warp's 32 rows, stash the non-zero pieces ----
+    uint32_t bsum = 0;
+    unsigned cntw = 0;                                           // pieces stashed by this warp (warp-uniform)
+    constexpr int RF = 4;                                        // rows in flight
+    for (int k0 = 0; k0 < ROWS_PER_WARP; k0 += RF) {
+        uint4 v[RF][NB];
+#pragma unroll
+        for (int j = 0; j < RF; j++) {
+            const uint32_t lr = r0 + warp * ROWS_PER_WARP + k0 + j;
+            const uint4 *row = reinterpret_cast<const uint4 *>(P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8);
+#pragma unroll
+            for (int b = 0; b < NB; b++) {
+                const uint32_t c = 32u * b + lane;
+                v[j][b] = (lr < n && c < chunks) ? __ldcs(row + c) : make_uint4(0, 0, 0, 0);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < RF; j++) {
+            const int slot = warp * ROWS_PER_WARP + k0 + j;
+            const uint32_t lr = r0 + slot;
+            unsigned m[NB], total = 0;
+#pragma unroll
+            for (int b = 0; b < NB; b++) {
+                m[b] = __ballot_sync(FULL, (v[j][b].x | v[j][b].y | v[j][b].z | v[j][b].w) != 0u);
+                total += __popc(m[b]);
+            }
+            const bool fits = cntw + total <= (unsigned)WIDE_STASH;
+            if (lane == 0) { s_first[slot] = (uint16_t)cntw; s_nent[slot] = fits ? (uint16_t)total : (uint16_t)WIDE_REREAD; }
+            if (!fits) continue;                                  // warp-uniform: this row is re-read in phase 2 / 3
+#pragma unroll
+            for (int b = 0; b < NB; b++) {
+                if ((m[b] >> lane) & 1u) {
+                    const unsigned e = cntw + __popc(m[b] & lt_mask);
+                    s_val[warp][e] = v[j][b];
+                    s_piece[warp][e] = (uint16_t)(32u * b + lane);
+                    bsum = sum_bytes(v[j][b], bsum);
+                    // leave the matrix zero for the next strand
+                    if (P.zero_after)
+                        *(reinterpret_cast<uint4 *>(P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8) + 32u * b + lane) = make_uint4(0, 0, 0, 0);
+                }
+                cntw += __popc(m[b]);
+            }
+        }
+    }
+    __syncwarp();
+    // ---- phase 2: one lane per row: maximum and number of non-zero cells ----
+    const int slot = warp * ROWS_PER_WARP + (int)lane;
+    const uint32_t lr = r0 + slot;
+    const unsigned first = s_first[slot], nent = s_nent[slot];
+    const uint8_t *rowg = P.sim8 + (size_t)(P.read_begin + lr) * P.pitch8;
+    {
+        uint32_t mx = 0, nnz = 0;
+        if (nent != WIDE_REREAD) {
+            for (unsigned e = first; e < first + nent; e++) {
+                const uint4 x = s_val[warp][e];
+                mx = __vmaxu4(__vmaxu4(mx, x.x), __vmaxu4(__vmaxu4(x.y, x.z), x.w));
+                nnz += __popc(nz_mask16(x));
+            }
+        } else if (lr < n) {
+            for (uint32_t c = 0; c < chunks; c++) {
+                const uint4 x = *(reinterpret_cast<const uint4 *>(rowg) + c);
+                mx = __vmaxu4(__vmaxu4(mx, x.x), __vmaxu4(__vmaxu4(x.y, x.z), x.w));
+                nnz += __popc(nz_mask16(x));
+                bsum = sum_bytes(x, bsum);
+            }
+        }
+        mx = max(max(mx & 0xff, (mx >> 8) & 0xff), max((mx >> 16) & 0xff, mx >> 24));
+        const float ns = __fdiv_rn((float)mx, normf);
+        s_cnt[slot] = (lr < n && ns > P.beta) ? 1u + nnz : 0u;
+        s_max[slot] = mx;
+    }
+    __syncthreads();
+    // ---- offsets ----
+    const uint32_t c = s_cnt[tid];
+    uint32_t incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(FULL, incl, o);
+        if (lane >= (unsigned)o) incl += y;
+    }
+    if (lane == 31) s_warp_sum[warp] = incl;
+    __syncthreads();
+    uint32_t warp_off = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < WARPS; w++) {
+        const uint32_t x = s_warp_sum[w];
+        if (w < (int)warp) warp_off += x;
+        total += x;
+    }
+    if (warp == 0) {
+        const unsigned long long e = lookback_exclusive(P.tile_state, tile, total);
+        if (lane == 0) {
+            s_excl = e;
+            if (tile == gridDim.x - 1) *P.n_records = 1ull + e + total;
+        }
+    }
+    s_off[tid] = warp_off + (incl - c);
+    __syncthreads();
+    const unsigned long long tile_base = 1ull + s_excl;
+    {
+        const uint32_t lr2 = r0 + tid;
+        if (lr2 < n) P.pos[lr2] = c ? tile_base + s_off[tid] : 0ull;
+    }
+    // ---- phase 3: one lane per row: the records, ascending genome order (pieces are stashed in that order) ----
+    {
+        const bool on = s_cnt[slot] != 0;                        // implies lr < n
+        unsigned long long dst = tile_base + s_off[slot];
+        if (on && dst < P.bin_cap) {
+            lime_pair_sim h;
+            h.sim = __fdiv_rn((float)s_max[slot], normf);
+            h.idRef = s_cnt[slot] - 1u;
+            P.bin[dst] = h;
+        }
+        dst++;
+        auto emit_piece = [&](const uint4 &x, uint32_t piece) {
+            const uint32_t wv[4] = {x.x, x.y, x.z, x.w};
+            uint32_t mm = nz_mask16(x);
+            while (mm) {
+                const int b = __ffs(mm) - 1;
+                mm &= mm - 1;
+                const uint32_t cell = (wv[b >> 2] >> ((b & 3) * 8)) & 0xffu;
+                if (dst < P.bin_cap) {
+                    lime_pair_sim rec;
+                    rec.sim = __fdiv_rn((float)cell, normf);
+                    rec.idRef = 16u * piece + (uint32_t)b;
+                    P.bin[dst] = rec;
+                }
+                dst++;
+            }
+        };
+        if (nent != WIDE_REREAD) {
+            if (on)
+                for (unsigned e = first; e < first + nent; e++) emit_piece(s_val[warp][e], s_piece[warp][e]);
+        } else if (lr < n) {
+            for (uint32_t cc = 0; cc < chunks; cc++) {
+                uint4 *p = reinterpret_cast<uint4 *>(const_cast<uint8_t *>(rowg)) + cc;
+                const uint4 x = *p;
+                if ((x.x | x.y | x.z | x.w) == 0u) continue;
+                if (on) emit_piece(x, cc);
+                if (P.zero_after) *p = make_uint4(0, 0, 0, 0);
+            }
+        }
+    }
+    if (P.byte_sum) publish_byte_sum(P.byte_sum, bsum, s_part);
+}
+
 // ---- export of the non-zero cells of a row range as triples, in no particular order ----------------
 // (the multi-GPU exchange format {read id, genome << 8 | count}; the importer adds them in any order).
 // A pure streaming pass: one 16-cell chunk per lane, warp-aggregated append with one atomic per warp.
@@ -624,8 +805,9 @@ cudaError_t launch_k3_choose(const K3Args &a, cudaStream_t s)
     else if (chunks <= 2)  k3::choose_sparse_kernel<2><<<g, k3::THREADS, 0, s>>>(a);
     else if (chunks <= 4)  k3::choose_sparse_kernel<4><<<g, k3::THREADS, 0, s>>>(a);
     else if (chunks <= 8)  k3::choose_sparse_kernel<8><<<g, k3::THREADS, 0, s>>>(a);
-    else if (chunks <= 16) k3::choose_kernel<16><<<g, k3::THREADS, 0, s>>>(a);
-    else                   k3::choose_kernel<32><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 32) k3::choose_wide_kernel<1><<<g, k3::THREADS, 0, s>>>(a);
+    else if (chunks <= 64) k3::choose_wide_kernel<2><<<g, k3::THREADS, 0, s>>>(a);
+    else                   k3::choose_kernel<32><<<g, k3::THREADS, 0, s>>>(a);   // more than 1024 genomes
     return cudaGetLastError();
 }
 cudaError_t launch_k3_export(const K3Args &a, cudaStream_t s)

@@ -170,6 +170,53 @@ def test_export_import_roundtrip(ctx, oracle, n_refs, ebwt_mode, alpha):
     assert np.array_equal(ctx.sim_matrix(), want)
 
 
+def _pieces_per_warp(sim):
+    """Largest number of non-zero 16-byte pieces among the 32-row groups of a matrix (the wide-row choose
+    kernel stashes up to 256 per group and re-reads the rest from global memory)."""
+    rows, refs = sim.shape
+    pad = np.zeros((-rows % 32 + rows, -refs % 16 + refs), dtype=np.uint8)
+    pad[:rows, :refs] = sim
+    nz = pad.reshape(pad.shape[0], -1, 16).any(axis=2).sum(axis=1)
+    return int(nz.reshape(-1, 32).sum(axis=1).max())
+
+
+@pytest.mark.parametrize("n_refs", [129, 130, 512, 513, 930, 1000, 1024, 1025])
+def test_choose_wide_rows_sparse_and_dense(ctx, oracle, n_refs):
+    """lime_choose on matrices written cell by cell (lime_sim_import): 129..1024 genomes take the streaming
+    kernel; a sparse band, a dense band (stash overflow -> re-read), empty rows, rows below beta, a ragged tail."""
+    import torch
+    rng = np.random.default_rng(n_refs)
+    n_reads = 256 * 3 + 77
+    # a load without clusters: zero matrix of the right shape, and lime_choose takes its single-pass kernel
+    ctx.load(np.zeros(4000, dtype=np.uint32), rng.integers(0, n_reads + n_refs, size=4000).astype(np.uint32), None, n_reads, n_refs)
+    assert ctx.cluster_similarity(16, 0, False) == (0, 0)
+    sim = np.zeros((n_reads, n_refs), dtype=np.uint8)
+    sparse = rng.random((n_reads, n_refs)) < 3.0 / n_refs
+    sim[sparse] = rng.integers(1, 256, size=int(sparse.sum()), dtype=np.uint8)
+    dense_rows = np.r_[40:75, 300:420, n_reads - 5:n_reads]
+    d = rng.random((dense_rows.shape[0], n_refs)) < 0.6
+    sim[dense_rows] = np.where(d, rng.integers(1, 256, size=d.shape, dtype=np.uint8), 0).astype(np.uint8)
+    sim[100:140] = 0
+    sim[200:230] = np.minimum(sim[200:230], 9)                                   # below beta
+    sim[50, :] = 255
+    sim[51, n_refs - 1] = 1
+    assert _pieces_per_warp(sim) > 256
+    r, g = np.nonzero(sim)
+    tr = np.empty((r.shape[0], 2), dtype=np.uint32)
+    tr[:, 0] = r
+    tr[:, 1] = (g.astype(np.uint32) << 8) | sim[r, g]
+    buf = torch.from_numpy(tr.view(np.int64).reshape(-1).copy()).to("cuda:0")
+    ctx.sim_import(buf.data_ptr(), buf.numel())
+    assert np.array_equal(ctx.sim_matrix(), sim)
+    for norm, beta in ((85, 0.25), (135, 0.0), (85, 0.9)):
+        n_rec = ctx.choose(0, norm, beta)
+        bin_g, pos_g = ctx.choose_result(0)
+        bin_o, pos_o = oracle.choose(sim, norm, np.float32(beta))
+        assert n_rec == bin_o.shape[0]
+        assert bin_g.tobytes() == bin_o.tobytes() and pos_g.tobytes() == pos_o.tobytes()
+    assert np.array_equal(ctx.sim_matrix(), sim)                                  # lime_choose leaves the matrix alone
+
+
 @pytest.mark.parametrize("ebwt_mode,alpha,world", [(1, 16, 4), (0, 12, 3), (1, 12, 1)])
 def test_xchg_loopback(oracle, ebwt_mode, alpha, world):
     """lime_xchg_*: the fused kernel appending update records (K12 MODE_FLAT + block path), route_kernel sorting
