@@ -202,25 +202,30 @@ int  lime_sim_import(lime_ctx *ctx, const void *dev_triples, uint64_t n_triples)
  * inbox_cap records per source rank and strand, which the other processes map (CUDA IPC).  The reference's
  * `SimArray_[read][genome] += t` (ClusterBWT_DA.cpp:183,247) becomes a record {read, genome << 8 | t}:
  *   lime_xchg_accumulate  lime_cluster_similarity with every update appended to a local list (capacity
- *                         flat_cap records), then sorted by owner and written into this rank's region of each
- *                         owner's inbox -- bulk stores over NVLink / NVSwitch, nothing remote is read or updated
+ *                         flat_cap records; two lists, used alternately by the strands), then -- on a side
+ *                         stream of the library -- sorted by owner and written into this rank's region of each
+ *                         owner's inbox: bulk stores over NVLink / NVSwitch, nothing remote is read or updated
  *                         atomically.  Inside an owner the records are also split by row block of its slab (each
- *                         block small enough for L2).  dev_sent (DEVICE memory, lime_xchg_counts_len() uint64 =
- *                         [world][row blocks]) receives the records sent to every owner and block;
- *   (caller)              all-gather of dev_sent over the ranks -> dev_counts_all [world][lime_xchg_counts_len()]
- *                         (source major): the job's only collective per strand, and the barrier "every source
- *                         has delivered";
- *   lime_xchg_apply       adds the records of all regions of this rank's inbox to the slab, row block after row
- *                         block (the slab's lines stay in L2 while their records arrive);
- *   lime_xchg_choose      clusterChoose (ClusterBWT_DA.cpp:361-450) of the owned reads into strand slot `strand`.
- * None of the three synchronises with the host.  lime_classify then classifies the owned reads and reads the
- * strands' device state back: LIME_ERR_RETRY means the job must be redone through lime_sim_export / lime_sim_import
- * (a cell exceeded 255, where the reference wraps, or a list / inbox was too small); the ranks agree on that
- * by their own collective.  lime_strand_status gives nClusters / maxLen / records / updates of this rank's shard.
+ *                         block small enough for L2).  Behind the records the rank stores its record counts and
+ *                         a flag (the number of this accumulation) into a mailbox at the head of the owner's inbox;
+ *   lime_xchg_apply       (side stream) waits on the device until every source's flag is up -- bounded, 20 s --
+ *                         then adds the records of all regions of this rank's inbox to the slab, row block after
+ *                         row block (the slab's lines stay in L2 while their records arrive);
+ *   lime_xchg_choose      (side stream) clusterChoose (ClusterBWT_DA.cpp:361-450) of the owned reads into strand
+ *                         slot `strand`.
+ * None of the three synchronises with the host and there is no collective: records, counts and flags travel as
+ * stores to peer memory, and the side-stream work of strand s runs beside lime_load + lime_xchg_accumulate of
+ * strand s + 1 on the context's stream.  lime_classify joins the two streams, classifies the owned reads and reads
+ * the strands' device state back: LIME_ERR_RETRY means the job must be redone through lime_sim_export /
+ * lime_sim_import (a cell exceeded 255, where the reference wraps, or a list / inbox was too small); the ranks
+ * agree on that by their own collective -- which every job needs anyway before the next one starts, because a job
+ * rewrites the inboxes of the one before.  lime_strand_status gives nClusters / maxLen / records / updates of
+ * this rank's shard.
  * world, reads_per_rank, n_refs, n_strands and inbox_cap of lime_xchg_alloc must be the same on every rank: a source
- * addresses its region inside the owner's inbox with them (flat_cap is local).
- * Call order on every rank: lime_xchg_alloc -> all-gather the 64-byte handles -> lime_xchg_open (once); per job
- * and strand: lime_load, lime_xchg_accumulate, all-gather, lime_xchg_apply, lime_xchg_choose; lime_classify.
+ * addresses its region inside the owner's inbox with them (flat_cap is local).  Every rank must make the same
+ * sequence of lime_xchg_accumulate calls (the flag value is their count per strand).
+ * Call order on every rank: lime_xchg_alloc -> all-gather the 64-byte handles -> lime_xchg_open (once) -> barrier;
+ * per job and strand: lime_load, lime_xchg_accumulate, lime_xchg_apply, lime_xchg_choose; lime_classify.
  * lime_xchg_open(ctx, NULL) is a loopback for tests on one GPU: all owners' regions are local, rank k applies
  * region k.  lime_xchg_status synchronises and returns nClusters, maxLen, updates, list slots used, sum of t
  * applied, byte sum of the slab, records, error bits of one strand.
@@ -230,10 +235,9 @@ int  lime_sim_import(lime_ctx *ctx, const void *dev_triples, uint64_t n_triples)
 int  lime_xchg_alloc(lime_ctx *ctx, int world, int rank, uint32_t reads_per_rank, uint32_t n_refs, int n_strands,
                      uint64_t flat_cap, uint64_t inbox_cap, uint8_t *ipc_handle);
 int  lime_xchg_open(lime_ctx *ctx, const uint8_t *ipc_handles);
-int  lime_xchg_counts_len(lime_ctx *ctx);
 int  lime_xchg_close(lime_ctx *ctx);
-int  lime_xchg_accumulate(lime_ctx *ctx, uint32_t alpha, int ebwt_mode, int strand, uint64_t *dev_sent);
-int  lime_xchg_apply(lime_ctx *ctx, int strand, const uint64_t *dev_counts_all);
+int  lime_xchg_accumulate(lime_ctx *ctx, uint32_t alpha, int ebwt_mode, int strand);
+int  lime_xchg_apply(lime_ctx *ctx, int strand);
 int  lime_xchg_choose(lime_ctx *ctx, int strand, uint32_t norm, float beta, uint32_t n_own_reads);
 int  lime_xchg_status(lime_ctx *ctx, int strand, uint64_t out[8]);
 

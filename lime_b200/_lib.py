@@ -60,10 +60,9 @@ SIGNATURES = {
     "lime_classify_result": (C.c_int, [vp, vp, vp, vp, C.c_int]),
     "lime_xchg_alloc": (C.c_int, [vp, C.c_int, C.c_int, C.c_uint32, C.c_uint32, C.c_int, C.c_uint64, C.c_uint64, vp]),
     "lime_xchg_open": (C.c_int, [vp, vp]),
-    "lime_xchg_counts_len": (C.c_int, [vp]),
     "lime_xchg_close": (C.c_int, [vp]),
-    "lime_xchg_accumulate": (C.c_int, [vp, C.c_uint32, C.c_int, C.c_int, vp]),
-    "lime_xchg_apply": (C.c_int, [vp, C.c_int, vp]),
+    "lime_xchg_accumulate": (C.c_int, [vp, C.c_uint32, C.c_int, C.c_int]),
+    "lime_xchg_apply": (C.c_int, [vp, C.c_int]),
     "lime_xchg_choose": (C.c_int, [vp, C.c_int, C.c_uint32, C.c_float, C.c_uint32]),
     "lime_xchg_status": (C.c_int, [vp, C.c_int, u64p]),
     "lime_strand_run": (C.c_int, [vp, C.c_int, C.c_uint32, C.c_int, C.c_uint32, C.c_float]),

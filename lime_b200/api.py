@@ -191,18 +191,16 @@ class LimeContext:
             handles = np.ascontiguousarray(handles, dtype=np.uint8).reshape(-1)
         self._ck(self.lib.lime_xchg_open(self.h, _ptr(handles)))
 
-    def xchg_counts_len(self):
-        """uint64 counters a rank contributes to the all-gather of a strand: world x row blocks."""
-        return int(self.lib.lime_xchg_counts_len(self.h))
-
     def xchg_close(self):
         self._ck(self.lib.lime_xchg_close(self.h))
 
-    def xchg_accumulate(self, alpha, ebwt_mode, strand, dev_sent_ptr):
-        self._ck(self.lib.lime_xchg_accumulate(self.h, alpha, 1 if ebwt_mode else 0, strand, C.c_void_p(dev_sent_ptr)))
+    def xchg_accumulate(self, alpha, ebwt_mode, strand):
+        """Score the loaded shard into update records; routing to the owners is queued on the library's side stream."""
+        self._ck(self.lib.lime_xchg_accumulate(self.h, alpha, 1 if ebwt_mode else 0, strand))
 
-    def xchg_apply(self, strand, dev_counts_all_ptr):
-        self._ck(self.lib.lime_xchg_apply(self.h, strand, C.c_void_p(dev_counts_all_ptr)))
+    def xchg_apply(self, strand):
+        """Side stream: wait (on the device) for every source's records of this strand, add them to the slab."""
+        self._ck(self.lib.lime_xchg_apply(self.h, strand))
 
     def xchg_choose(self, strand, norm, beta, n_own_reads):
         self._ck(self.lib.lime_xchg_choose(self.h, strand, norm, beta, n_own_reads))

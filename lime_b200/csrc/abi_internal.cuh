@@ -7,7 +7,7 @@ using namespace lime;
 
 
 static const char *const kKernelNames[KID_COUNT] = {
-    "k12_fused", "k12_check", "k1_detect", "k2_warp", "k2_block", "k2_narrow", "k3_choose", "k3_export", "k3_import", "k3_count", "k3_emit", "k3_classify", "x_route", "x_apply"};
+    "k12_fused", "k12_check", "k1_detect", "k2_warp", "k2_block", "k2_narrow", "k3_choose", "k3_export", "k3_import", "k3_count", "k3_emit", "k3_classify", "x_route", "x_apply", "x_publish", "x_wait"};
 
 // device scalar block layout (u64 slots)
 enum {
@@ -57,11 +57,13 @@ template <class T> static T *strand_scalar(lime_ctx *c, int slot, int k)
 // lime_abi_steps.cu / lime_abi_xchg.cu
 // the fused kernel + the block path over the clusters it sets aside, asynchronous; scalars land in `sc`
 // (a device block laid out as SS_*); flat: records instead of adds into ctx->d_sim
-int queue_k12_score(lime_ctx *ctx, uint32_t alpha, bool ebwt, unsigned long long *sc, const lime::FlatOut &flat);
+int queue_k12_score(lime_ctx *ctx, uint32_t alpha, bool ebwt, unsigned long long *sc, const lime::FlatOut &flat, int max_ctas_per_sm = 0);
 int reserve_score_scratch(lime_ctx *ctx);
 int queue_choose_deferred(lime_ctx *ctx, int slot, uint32_t norm, float beta, uint32_t n, uint64_t cap, int kind);
 int detect_into_ctx(lime_ctx *ctx, uint32_t alpha, unsigned long long host_sc[SC_COUNT]);
 void xchg_release(lime_ctx *ctx);
+// the context's stream waits for everything queued on the exchange's side stream (no-op without an exchange)
+int xchg_join(lime_ctx *ctx);
 int strand_readback(lime_ctx *ctx, int slot);
 // lime_abi_load.cu
 int load_host_narrow(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint8_t *ebwt, uint64_t n);

@@ -116,6 +116,8 @@ enum KernelId {
     KID_K3_CLASSIFY,
     KID_X_ROUTE,
     KID_X_APPLY,
+    KID_X_PUBLISH,
+    KID_X_WAIT,
     KID_COUNT
 };
 
@@ -137,6 +139,7 @@ struct ProfEvent { int kid; cudaEvent_t a, b; };
 // multi-GPU exchange of similarity updates (lime_abi_xchg.cu): the rows of a read live on its owner only
 constexpr int XCHG_MAX = 16;
 constexpr int XCHG_SUB_MAX = 8;            // row blocks an owner's slab is applied in (each small enough for L2)
+constexpr int XCHG_MAIL_STRIDE = XCHG_SUB_MAX + 1;   // uint64 per (strand, source) in an inbox header: counts + flag
 struct XchgState {
     bool active = false, loopback = false;
     int world = 0, rank = 0, n_strands = 0;
@@ -146,9 +149,25 @@ struct XchgState {
     uint32_t n_sub = 1, sub_rows = 1;      // row blocks of a slab and rows per block
     uint64_t sub_cap = 0;
     DevBuf slabs;                          // [n_strands][rows][pitch] uint8: the similarity rows of the owned reads
-    DevBuf flat;                           // [flat_cap] records {read, genome << 8 | t} of the strand being scored
-    void *inbox_own = nullptr;             // [n_strands][world][inbox_cap] records, plain cudaMalloc (CUDA IPC)
+    DevBuf flat[2];                        // [flat_cap] records {read, genome << 8 | t}; strand s uses list s & 1, so
+                                           // that the next strand is scored while this one's list is being routed
+    // inbox: a mailbox header (mail_bytes: [n_strands][world][XCHG_MAIL_STRIDE] uint64 = the record counts of
+    // source p per row block + the epoch flag p raises after its records have landed), then the regions
+    // [n_strands][world][inbox_cap] records; plain cudaMalloc (CUDA IPC)
+    void *inbox_own = nullptr;
     void *inbox_map[XCHG_MAX] = {nullptr}; // every rank's inbox in this process (own included)
+    uint64_t mail_bytes = 0;
+    uint64_t epoch[LIME_MAXFILES] = {0};   // accumulations of strand s so far = the flag value its sources raise
+    // routing, applying and clusterChoose of strand s are queued on `tail` and run beside the scoring of strand
+    // s + 1 on the context's stream (the scoring kernel leaves k12_spare CTA slots of every SM to them)
+    cudaStream_t tail = nullptr;
+    cudaEvent_t ev_scored[LIME_MAXFILES] = {nullptr};   // main: list of strand s complete
+    cudaEvent_t ev_routed[2] = {nullptr};                // tail: list s & 1 has been read
+    cudaEvent_t ev_strand[LIME_MAXFILES] = {nullptr};    // tail: last operation queued for strand s
+    cudaEvent_t ev_join = nullptr;
+    bool routed_set[2] = {false, false}, strand_set[LIME_MAXFILES] = {false};
+    bool tail_dirty = false;
+    int k12_ctas = 0;                      // CTAs per SM of the scoring kernel while tail work may run (0 = all)
     DevBuf state;                          // device scalars, see lime_abi_xchg.cu
 };
 
@@ -291,6 +310,7 @@ struct K12Args {
     uint64_t flat_cap;
     // L2 policy words (createpolicy): inputs evict_first, matrix lines evict_last; from k12_policies()
     uint64_t pol_evict_first, pol_evict_last;
+    int max_ctas_per_sm;              // > 0: leave the other CTA slots of an SM to kernels of another stream
 };
 cudaError_t k12_policies(uint64_t out[2]);
 cudaError_t launch_bytesum(const uint8_t *p, uint64_t bytes, unsigned long long *out, cudaStream_t s);
@@ -309,15 +329,32 @@ struct XchgRoute {
     unsigned long long *sent;         // [world][n_sub] device counters (local)
     unsigned long long *err;
 };
+// after route_kernel: this source's counts for owner o -> mail[o][0 .. n_sub), then the flag mail[o][XCHG_SUB_MAX] = epoch
+struct XchgPublish {
+    const unsigned long long *sent;   // [world][n_sub]
+    unsigned long long *mail[XCHG_MAX];
+    uint32_t world, n_sub;
+    unsigned long long epoch;
+};
+// on the owner: until every source has raised `epoch` in mail[p][XCHG_SUB_MAX] (bounded: err bit 4 after 20 s)
+struct XchgWait {
+    const unsigned long long *mail;   // this strand's [world][XCHG_MAIL_STRIDE]
+    uint32_t world; int only;         // only >= 0: that source alone (loopback)
+    unsigned long long epoch;
+    unsigned long long *err;
+};
 struct XchgApply {
     const uint2 *src; uint64_t sub_cap;
-    const unsigned long long *counts_all;   // [world][world][n_sub], device
+    const unsigned long long *mail;   // this strand's [world][XCHG_MAIL_STRIDE]: records source p sent for row block j
+    int only;                         // >= 0: apply that source's region alone (loopback)
     uint32_t world, rank, n_sub, sub;
     uint8_t *slab; uint64_t pitch; uint32_t rows, n_refs;
     unsigned long long *applied_t, *applied_n, *err;
 };
 cudaError_t launch_xchg_route(const XchgRoute &a, cudaStream_t s);
 cudaError_t launch_xchg_apply(const XchgApply &a, cudaStream_t s);
+cudaError_t launch_xchg_publish(const XchgPublish &a, cudaStream_t s);
+cudaError_t launch_xchg_wait(const XchgWait &a, cudaStream_t s);
 
 struct K3Args {
     uint8_t *sim8; uint64_t pitch8;

@@ -705,7 +705,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) chunk_scan_kernel(unsigned long 
 uint64_t k12s_num_chunks(uint64_t n_own) { return (n_own + k12s::OWN - 1) / k12s::OWN; }
 
 template <int MODE, bool EB, bool L8>
-static unsigned grid_of(uint64_t n_own)
+static unsigned grid_of(uint64_t n_own, int max_ctas_per_sm)
 {
     static int ctas_per_sm = 0, sms = 0;
     if (!ctas_per_sm) {
@@ -717,14 +717,15 @@ static unsigned grid_of(uint64_t n_own)
     }
     const uint64_t chunks = k12s_num_chunks(n_own);
     const uint64_t want = (chunks + k12s::WARPS - 1) / k12s::WARPS;          // at least one chunk per warp
-    return (unsigned)std::min<uint64_t>(want, (uint64_t)sms * ctas_per_sm);
+    const int per_sm = max_ctas_per_sm > 0 ? std::min(max_ctas_per_sm, ctas_per_sm) : ctas_per_sm;
+    return (unsigned)std::min<uint64_t>(want, (uint64_t)sms * per_sm);
 }
 
 template <int MODE, bool EB, bool L8>
 static cudaError_t launch_variant(const K12Args &a, cudaStream_t s)
 {
     // persistent grid, CTAs stride over groups of chunks
-    const unsigned grid = grid_of<MODE, EB, L8>(a.n_own);
+    const unsigned grid = grid_of<MODE, EB, L8>(a.n_own, a.max_ctas_per_sm);
     if (!grid) return cudaErrorUnknown;
     k12s::stream_kernel<MODE, EB, L8><<<grid, k12s::THREADS, 0, s>>>(a);
     return cudaGetLastError();

@@ -17,6 +17,7 @@ int strand_readback(lime_ctx *ctx, int slot)
     ctx->rec_hint = std::max<uint64_t>(ctx->rec_hint, h[SS_NRECORDS]);
     if (h[SS_ERR] & 1ull) { S.valid = false; return fail(ctx, LIME_ERR_HALO, "a cluster runs past the halo of this shard"); }
     if (h[SS_MAXLEN] > LIME_SIZE_MAX_BUF) { S.valid = false; return fail(ctx, LIME_ERR_MAXLEN, "maximum cluster size is greater than sizeMaxBuf"); }
+    if (h[SS_ERR] & 16ull) { S.valid = false; return fail(ctx, LIME_ERR_STATE, "exchange: a source rank did not deliver its records within 20 s"); }
     if (h[SS_ERR] & 12ull) { S.valid = false; return fail(ctx, (h[SS_ERR] & 8ull) ? LIME_ERR_ARG : LIME_ERR_RETRY, (h[SS_ERR] & 8ull) ? "exchange: update record out of range" : "exchange: an inbox region overflowed"); }
     if (S.kind == 2 && h[SS_FLAT_COUNT] > ctx->xchg.flat_cap) { S.valid = false; return fail(ctx, LIME_ERR_RETRY, "exchange: the update list overflowed"); }
     const unsigned long long added = S.kind == 2 ? h[SS_APPLIED_T] : h[SS_SUMT];
@@ -43,6 +44,7 @@ int lime_classify(lime_ctx *ctx, int n_files, uint32_t n_refs,
             return fail(ctx, LIME_ERR_STATE, "lime_classify: strand slots cover different read ranges");
     }
     CK(cudaSetDevice(ctx->device), "cudaSetDevice");
+    { const int rc = xchg_join(ctx); if (rc) return rc; }        // strands finished on the exchange's side stream
     const uint32_t n_reads = ctx->slots[0].n_reads;
     const bool use_m = higher && m_corRef;
 

@@ -47,7 +47,7 @@ int reserve_score_scratch(lime_ctx *ctx)
 // the device).  Nothing synchronises here; the scalars land in the device block `sc` (layout SS_*), which
 // the caller has zeroed.  flat.rec != null: the updates leave as records (multi-GPU) instead of being added
 // to ctx->d_sim.
-int queue_k12_score(lime_ctx *ctx, uint32_t alpha, bool ebwt, unsigned long long *sc, const FlatOut &flat)
+int queue_k12_score(lime_ctx *ctx, uint32_t alpha, bool ebwt, unsigned long long *sc, const FlatOut &flat, int max_ctas_per_sm)
 {
     if (ctx->lcp8 && alpha > 255)
         return fail(ctx, LIME_ERR_STATE, "lcp was loaded narrowed (lime_set_alpha_limit <= 255), alpha > 255 needs a reload");
@@ -64,6 +64,7 @@ int queue_k12_score(lime_ctx *ctx, uint32_t alpha, bool ebwt, unsigned long long
     a.n_updates = sc + SS_NUPDATES; a.sum_t = sc + SS_SUMT;
     a.flat = flat.rec; a.flat_count = flat.count; a.flat_cap = flat.cap;
     a.pol_evict_first = ctx->l2_policy[0]; a.pol_evict_last = ctx->l2_policy[1];
+    a.max_ctas_per_sm = max_ctas_per_sm;
     if (k12_num_tiles(ctx->n_own) == 0) return LIME_OK;
     {
         LaunchScope ls(ctx, KID_K12_FUSED);
@@ -228,6 +229,7 @@ int lime_sim_copy(lime_ctx *ctx, uint8_t *out)
     if (!ctx->d_sim) return fail(ctx, LIME_ERR_STATE, "lime_sim_copy: no matrix selected");
     // exchange mode: the selected slab, i.e. the rows of the reads this rank owns
     const uint64_t rows = ctx->xchg.active ? ctx->sim_rows : ctx->n_reads;
+    { const int rc = xchg_join(ctx); if (rc) return rc; }
     CK(cudaMemcpy2DAsync(out, ctx->n_refs, ctx->d_sim, ctx->sim_pitch, ctx->n_refs, rows,
                          cudaMemcpyDeviceToHost, ctx->stream), "D2H similarity matrix");
     CK(cudaStreamSynchronize(ctx->stream), "D2H similarity matrix");
@@ -445,6 +447,7 @@ int lime_choose_copy(lime_ctx *ctx, int slot, lime_pair_sim *bin, uint64_t *pos)
     if (!ctx || slot < 0 || slot >= LIME_MAXFILES) return LIME_ERR_ARG;
     Slot &S = ctx->slots[slot];
     if (!S.valid) return fail(ctx, LIME_ERR_STATE, "lime_choose_copy: empty slot");
+    { const int rc = xchg_join(ctx); if (rc) return rc; }
     if (bin) CK(cudaMemcpyAsync(bin, S.bin.p, S.n_records * sizeof(lime_pair_sim), cudaMemcpyDeviceToHost, ctx->stream), "D2H records");
     if (pos && S.n_reads) CK(cudaMemcpyAsync(pos, S.pos.p, (uint64_t)S.n_reads * 8, cudaMemcpyDeviceToHost, ctx->stream), "D2H pos");
     CK(cudaStreamSynchronize(ctx->stream), "D2H slot");

@@ -11,10 +11,14 @@
 //                 writes to its region, so nothing remote is ever read or updated atomically.
 //                 Inside an owner the records are also split by row block (n_sub blocks of the slab, each small
 //                 enough for L2), so that the owner can apply block after block with its slab lines in L2.
-//   apply_kernel  (on the owner, after all sources have finished) adds the records of one row block from every
-//                 source region to the owner's uint8 rows with fire-and-forget adds and sums their t for the carry
-//                 proof; one launch per row block.
-// The only collective is the all-gather of the per-owner record counts in between, which is also the barrier.
+//   publish_kernel (behind route_kernel in stream order) stores this source's record counts into a mailbox at the
+//                 head of every owner's inbox and then raises a flag there (the number of the accumulation);
+//   wait_kernel   (on the owner) one warp polls the flags of all sources -- bounded, 20 s -- so that the kernels
+//                 queued behind it see every region complete;
+//   apply_kernel  adds the records of one row block from every source region to the owner's uint8 rows with
+//                 fire-and-forget adds and sums their t for the carry proof; one launch per row block.
+// No collective and no host synchronisation is involved: records, counts and flags all travel as stores to peer
+// memory, so the whole chain can be queued on a side stream and runs beside the scoring of the next strand.
 #include "common.cuh"
 #include <algorithm>
 
@@ -127,10 +131,43 @@ __global__ void __launch_bounds__(THREADS) route_kernel(const RouteArgs P)
     __threadfence_system();                     // the stores to peer memory are performed before the kernel ends
 }
 
+__global__ void publish_kernel(const XchgPublish P)
+{
+    const unsigned o = threadIdx.x;
+    if (o >= P.world) return;
+    volatile unsigned long long *m = P.mail[o];
+    for (unsigned j = 0; j < P.n_sub; j++) m[j] = P.sent[o * P.n_sub + j];
+    // route_kernel has completed (stream order) and fenced its stores; the counts before the flag
+    __threadfence_system();
+    m[XCHG_SUB_MAX] = P.epoch;
+    __threadfence_system();
+}
+
+__device__ __forceinline__ unsigned long long global_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+__global__ void wait_kernel(const XchgWait P)
+{
+    const unsigned p = threadIdx.x;
+    if (p >= P.world || (P.only >= 0 && (int)p != P.only)) return;
+    const volatile unsigned long long *flag = P.mail + (size_t)p * XCHG_MAIL_STRIDE + XCHG_SUB_MAX;
+    const unsigned long long t0 = global_ns();
+    while (*flag < P.epoch) {
+        __nanosleep(200);
+        if (global_ns() - t0 > 20000000000ull) { atomicOr(P.err, 16ull); break; }   // a source never delivered
+    }
+    __threadfence_system();
+}
+
 struct ApplyArgs {
     const uint2 *src;                           // this owner's inbox regions of one strand: [world][n_sub][sub_cap]
     uint64_t sub_cap;
-    const unsigned long long *counts_all;       // [world][world][n_sub] records sent by source p to (owner o, row block)
+    const unsigned long long *mail;             // [world][XCHG_MAIL_STRIDE]: records sent by source p for row block j
+    int only;
     uint32_t world, rank, n_sub, sub;           // sub: the row block this launch applies
     uint8_t *slab; uint64_t pitch;
     uint32_t rows, n_refs;
@@ -143,7 +180,8 @@ struct ApplyArgs {
 __global__ void __launch_bounds__(THREADS) apply_kernel(const ApplyArgs P)
 {
     const unsigned p = blockIdx.y;
-    unsigned long long n = P.counts_all[((size_t)p * P.world + P.rank) * P.n_sub + P.sub];
+    if (P.only >= 0 && (int)p != P.only) return;
+    unsigned long long n = P.mail[(size_t)p * XCHG_MAIL_STRIDE + P.sub];
     if (n > P.sub_cap) { if (threadIdx.x == 0 && blockIdx.x == 0) atomicOr(P.err, 4ull); n = P.sub_cap; }
     const uint2 *src = P.src + ((size_t)p * P.n_sub + P.sub) * P.sub_cap;
     uint64_t pol;
@@ -201,12 +239,24 @@ cudaError_t launch_xchg_route(const XchgRoute &a, cudaStream_t s)
 cudaError_t launch_xchg_apply(const XchgApply &a, cudaStream_t s)
 {
     xchg::ApplyArgs P;
-    P.src = a.src; P.sub_cap = a.sub_cap; P.counts_all = a.counts_all; P.world = a.world; P.rank = a.rank;
+    P.src = a.src; P.sub_cap = a.sub_cap; P.mail = a.mail; P.only = a.only; P.world = a.world; P.rank = a.rank;
     P.n_sub = a.n_sub; P.sub = a.sub;
     P.slab = a.slab; P.pitch = a.pitch; P.rows = a.rows; P.n_refs = a.n_refs;
     P.applied_t = a.applied_t; P.applied_n = a.applied_n; P.err = a.err;
     const dim3 grid((148 * 8 + a.world - 1) / a.world, a.world);
     xchg::apply_kernel<<<grid, xchg::THREADS, 0, s>>>(P);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_xchg_publish(const XchgPublish &a, cudaStream_t s)
+{
+    xchg::publish_kernel<<<1, 32, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_xchg_wait(const XchgWait &a, cudaStream_t s)
+{
+    xchg::wait_kernel<<<1, 32, 0, s>>>(a);
     return cudaGetLastError();
 }
 

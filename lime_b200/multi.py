@@ -110,21 +110,13 @@ class CudaBackend:
         parts = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(parts, mine)
         self.ctx.xchg_open(torch.stack(parts).cpu().numpy() if world > 1 else None)
-        k = self.ctx.xchg_counts_len()          # world x row blocks of a slab
-        self._sent = torch.zeros(n_strands, k, dtype=torch.int64, device=self.device)
-        self._counts = torch.zeros(n_strands, world * k, dtype=torch.int64, device=self.device)
-        dist.barrier()                       # every rank has mapped every inbox
+        dist.barrier()                       # every rank has mapped every inbox (and cleared its mailbox)
 
     def xchg_accumulate(self, alpha, ebwt_mode, strand):
-        """-> device tensor [world x row blocks]: records this rank sent to every owner (filled asynchronously)."""
-        self.ctx.xchg_accumulate(alpha, ebwt_mode, strand, self._sent[strand].data_ptr())
-        return self._sent[strand]
+        self.ctx.xchg_accumulate(alpha, ebwt_mode, strand)
 
-    def xchg_counts_buffer(self, strand):
-        return self._counts[strand]
-
-    def xchg_apply(self, strand, counts_all):
-        self.ctx.xchg_apply(strand, counts_all.data_ptr())
+    def xchg_apply(self, strand):
+        self.ctx.xchg_apply(strand)
 
     def xchg_choose(self, strand, norm, beta, n_own):
         self.ctx.xchg_choose(strand, norm, beta, n_own)
@@ -310,8 +302,11 @@ def xchg_capacities(n_positions, world, density=0.25):
 
 class XchgJob:
     """The job of ShardedJob with the similarity rows on the read owner only: compute and routing are
-    queued per strand without a host synchronisation (lime_xchg_accumulate -> all-gather of the record
-    counts -> lime_xchg_apply -> lime_xchg_choose); Classify reads the strands' state back.
+    queued per strand without a host synchronisation or a collective (lime_xchg_accumulate -> lime_xchg_apply
+    -> lime_xchg_choose; records, counts and "delivered" flags are stores to peer memory, and the routing /
+    applying / choosing of a strand runs beside the scoring of the next one); Classify reads the strands'
+    state back, then ONE all-gather lets the ranks agree on the outcome and the scalars -- it is also the
+    meeting point the next job needs before it may rewrite the inboxes.
 
         job = XchgJob(dist, torch, backend, rank, world, n_reads, n_refs, n_strands, flat_cap, inbox_cap)
         for s, shard in enumerate(strands): job.run_strand(s, shard, alpha, beta, ebwt_mode, read_len)
@@ -346,12 +341,9 @@ class XchgJob:
         with self.timer("compute"):
             be.load(shard["lcp"], shard["da"], shard["ebwt"] if ebwt_mode else None, shard["n_own"], shard["n_halo"],
                     shard["pos_base"], shard["is_last"], self.n_reads, self.n_refs)
-            sent = be.xchg_accumulate(alpha, ebwt_mode, slot)
-        with self.timer("counts"):
-            counts = be.xchg_counts_buffer(slot)
-            dist.all_gather_into_tensor(counts, sent)          # [source][owner]; also: every source has delivered
+            be.xchg_accumulate(alpha, ebwt_mode, slot)          # + routing, queued on the library's side stream
         with self.timer("apply"):
-            be.xchg_apply(slot, counts)
+            be.xchg_apply(slot)                                 # side stream: waits for every source's flag on the device
         with self.timer("choose"):
             be.xchg_choose(slot, norm_of(read_len, alpha), beta, self.hi - self.lo)
         self._pending.append(slot)
@@ -367,21 +359,21 @@ class XchgJob:
         except LimeError as e:
             code, msg = e.code, str(e)
         with self.timer("check"):
-            # the ranks agree on the outcome (every rank takes the same branch), then on the scalars
+            # the ranks agree on the outcome (every rank takes the same branch) and on the scalars: one all-gather
             st = [self.be.xchg_status(s) for s in self._pending]
             over = int(any(x["list_slots"] > self.flat_cap or (x["err"] & 4) for x in st))
-            flag = inner._cpu_or_dev([code, -over])
-            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-            code_all, over_all = int(flag[0].item()), -int(flag[1].item())
+            k = len(st)
+            mine = inner._cpu_or_dev([code, over] + [x["n_clusters"] for x in st] + [x["updates"] for x in st]
+                                     + [x["max_len"] for x in st])
+            rows = torch.empty(self.world * mine.numel(), dtype=mine.dtype, device=mine.device)
+            dist.all_gather_into_tensor(rows, mine)
+            rows = rows.cpu().view(self.world, -1)
+            code_all, over_all = int(rows[:, 0].min().item()), int(rows[:, 1].max().item())
             if code_all == ERR_RETRY:
                 raise CarryDetected(msg or "another rank must redo its strands", overflow=bool(over_all))
             if code_all != 0:
                 raise LimeError(code_all, msg or "a rank of the job failed")
-            tot = inner._cpu_or_dev([x["n_clusters"] for x in st] + [x["updates"] for x in st])
-            mx = inner._cpu_or_dev([x["max_len"] for x in st])
-            dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-            dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-            k = len(st)
+            tot, mx = rows[:, 2:2 + 2 * k].sum(dim=0), rows[:, 2 + 2 * k:].max(dim=0).values
             self.stats = [{"n_clusters": int(tot[i].item()), "max_len": int(mx[i].item()), "updates": int(tot[k + i].item()),
                            "n_records_local": st[i]["n_records"]} for i in range(k)]
         if not gather or self.world == 1:

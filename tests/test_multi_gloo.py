@@ -68,47 +68,60 @@ class OracleBackend:
 
     # ---- emulation of the record exchange (XchgJob): every rank's inbox is one shared file, a source
     # writes its records {row, genome << 8 | count} into its own region of the owner's file (what
-    # route_kernel does over NVLink); the all-gather of the counts is the barrier, as on the GPUs
+    # route_kernel does over NVLink), then its record count and a flag (the number of the accumulation) into the
+    # owner's mailbox (publish_kernel); the owner polls the flags of all sources (wait_kernel) -- no collective
     def xchg_setup(self, dist, world, rank, per, n_refs, n_strands, flat_cap, inbox_cap):
         self.xd = (dist, world, rank, per, n_strands, inbox_cap)
         path = lambda r: os.path.join(self.shm_dir, f"inbox{r}.i64")
+        mpath = lambda r: os.path.join(self.shm_dir, f"mail{r}.i64")
         np.memmap(path(rank), dtype=np.int64, mode="w+", shape=(n_strands, world, inbox_cap)).flush()
+        np.memmap(mpath(rank), dtype=np.int64, mode="w+", shape=(n_strands, world, 2)).flush()
         dist.barrier()
         self.inbox = [np.memmap(path(r), dtype=np.int64, mode="r+", shape=(n_strands, world, inbox_cap)) for r in range(world)]
-        self.x_state = {}
+        self.mail = [np.memmap(mpath(r), dtype=np.int64, mode="r+", shape=(n_strands, world, 2)) for r in range(world)]
+        self.x_state, self.epoch = {}, [0] * n_strands
 
     def xchg_accumulate(self, alpha, ebwt_mode, strand):
         dist, world, rank, per, n_strands, cap = self.xd
         n_cl, mx = self.cluster_similarity(alpha, ebwt_mode)
-        sent = np.zeros(world, np.int64)
         over = False
+        self.epoch[strand] += 1
         for k in range(world):
             lo, hi = k * per, min((k + 1) * per, self.n_reads)
-            if hi <= lo:
-                continue
-            r, g = np.nonzero(self.sim[lo:hi])
-            c = self.sim[lo:hi][r, g].astype(np.int64)
-            rec = r.astype(np.int64) | (((g.astype(np.int64) << 8) | c) << 32)
-            sent[k] = rec.shape[0]
-            over |= rec.shape[0] > cap
-            self.inbox[k][strand, rank, :min(rec.shape[0], cap)] = rec[:cap]
-            self.inbox[k].flush()
+            n = 0
+            if hi > lo:
+                r, g = np.nonzero(self.sim[lo:hi])
+                c = self.sim[lo:hi][r, g].astype(np.int64)
+                rec = r.astype(np.int64) | (((g.astype(np.int64) << 8) | c) << 32)
+                n = rec.shape[0]
+                over |= n > cap
+                self.inbox[k][strand, rank, :min(n, cap)] = rec[:cap]
+                self.inbox[k].flush()
+            self.mail[k][strand, rank, 0] = n                   # the count before the flag
+            self.mail[k].flush()
+            self.mail[k][strand, rank, 1] = self.epoch[strand]
+            self.mail[k].flush()
         self.x_state[strand] = dict(n_clusters=n_cl, max_len=mx, updates=int(np.count_nonzero(self.sim)), list_slots=0,
                                     err=4 if over else 0)
-        return self.torch.from_numpy(sent)
 
-    def xchg_counts_buffer(self, strand):
-        return self.torch.zeros(self.xd[1] * self.xd[1], dtype=self.torch.int64)
-
-    def xchg_apply(self, strand, counts_all):
+    def xchg_apply(self, strand):
+        import time
         dist, world, rank, per, n_strands, cap = self.xd
-        counts = counts_all.numpy().reshape(world, world)
         mine = np.memmap(self.inbox[rank].filename, dtype=np.int64, mode="r", shape=(n_strands, world, cap))
         slab = np.zeros((per, self.n_refs), np.int64)
-        for p in range(world):
-            t = np.array(mine[strand, p, :min(int(counts[p, rank]), cap)])
-            np.add.at(slab, (t & 0xFFFFFFFF, (t >> 40)), (t >> 32) & 0xFF)
         st = self.x_state[strand]
+        for p in range(world):
+            t0 = time.time()
+            while True:
+                mail = np.memmap(self.mail[rank].filename, dtype=np.int64, mode="r", shape=(n_strands, world, 2))
+                if int(mail[strand, p, 1]) >= self.epoch[strand]:
+                    break
+                if time.time() - t0 > 20:
+                    st["err"] |= 16
+                    break
+                time.sleep(0.001)
+            t = np.array(mine[strand, p, :min(int(mail[strand, p, 0]), cap)])
+            np.add.at(slab, (t & 0xFFFFFFFF, (t >> 40)), (t >> 32) & 0xFF)
         st["applied_t"] = int(slab.sum())
         self.sim = (slab & 0xFF).astype(np.uint8)               # the uint8 cell wraps
         st["byte_sum"] = int(self.sim.astype(np.int64).sum())

@@ -51,20 +51,16 @@ for world in (1, 8):
     flat_cap = int(n * 0.25) + (1 << 21)
     ctx.xchg_alloc(world, 0, per, n_refs, 2, flat_cap, int(flat_cap * 1.5 / world) + (1 << 16))
     ctx.xchg_open(None)
-    k = ctx.xchg_counts_len()
-    sent = torch.zeros(2, k, dtype=torch.int64, device=dev)
     for rep in range(reps + 2):
         if rep == 2:
             ctx.prof_enable(True); ctx.prof_reset()
         for s in range(2):
             ctx.load(l.data_ptr(), d.data_ptr(), e.data_ptr(), n_reads, n_refs, mem=MEM_DEVICE, n_total=n)
-            ctx.xchg_accumulate(alpha, 1, s, sent[s].data_ptr())
-            counts = torch.zeros(world, k, dtype=torch.int64, device=dev)
-            counts[0] = sent[s]
-            ctx.xchg_apply(s, counts.data_ptr())
+            ctx.xchg_accumulate(alpha, 1, s)
+            ctx.xchg_apply(s)
             ctx.xchg_choose(s, read_len + 1 - alpha, 0.25, min(per, n_reads))
         ctx.classify(2, n_refs, v, None, 1, False)
     show(f"records, {world} owner(s):", ctx.prof(), reps)
-    print("  status:", ctx.xchg_status(0), "sent", sent[0].tolist(), flush=True)
+    print("  status:", ctx.xchg_status(0), flush=True)
     ctx.prof_enable(False)
     ctx.close()
