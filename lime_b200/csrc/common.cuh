@@ -166,7 +166,7 @@ struct XchgState {
     cudaEvent_t ev_strand[LIME_MAXFILES] = {nullptr};    // tail: last operation queued for strand s
     cudaEvent_t ev_join = nullptr;
     bool routed_set[2] = {false, false}, strand_set[LIME_MAXFILES] = {false};
-    bool tail_dirty = false;
+    bool tail_dirty = false, use_tail = true;
     int k12_ctas = 0;                      // CTAs per SM of the scoring kernel while tail work may run (0 = all)
     DevBuf state;                          // device scalars, see lime_abi_xchg.cu
 };

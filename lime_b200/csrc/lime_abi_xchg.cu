@@ -59,13 +59,16 @@ namespace {
 // launches of this scope go to the exchange's side stream
 struct OnTail {
     lime_ctx *c; cudaStream_t keep;
-    explicit OnTail(lime_ctx *c_) : c(c_), keep(c_->stream) { c->stream = c->xchg.tail; c->xchg.tail_dirty = true; }
+    explicit OnTail(lime_ctx *c_) : c(c_), keep(c_->stream)
+    {
+        if (c->xchg.use_tail) { c->stream = c->xchg.tail; c->xchg.tail_dirty = true; }
+    }
     ~OnTail() { c->stream = keep; }
 };
 int mark_strand(lime_ctx *ctx, int strand)          // called with the side stream current
 {
     XchgState &S = ctx->xchg;
-    CK(cudaEventRecord(S.ev_strand[strand], S.tail), "cudaEventRecord");
+    CK(cudaEventRecord(S.ev_strand[strand], ctx->stream), "cudaEventRecord");
     S.strand_set[strand] = true;
     return LIME_OK;
 }
@@ -96,7 +99,9 @@ int lime_xchg_alloc(lime_ctx *ctx, int world, int rank, uint32_t reads_per_rank,
     S.rows = reads_per_rank; S.pitch = lime_sim_pitch(n_refs);
     S.flat_cap = std::max<uint64_t>((flat_cap + K12_FLAT_BLK - 1) / K12_FLAT_BLK * K12_FLAT_BLK, K12_FLAT_BLK);
     // the slab is applied in row blocks of at most 32 MB, so that its lines stay in L2 while their records arrive
-    S.n_sub = (uint32_t)std::min<uint64_t>(XCHG_SUB_MAX, std::max<uint64_t>(1, (S.rows * S.pitch + (32ull << 20) - 1) / (32ull << 20)));
+    uint64_t sub_bytes = 32ull << 20;
+    if (const char *e = getenv("LIME_XCHG_SUB_MB")) sub_bytes = std::max<uint64_t>(1, (uint64_t)atoll(e)) << 20;
+    S.n_sub = (uint32_t)std::min<uint64_t>(XCHG_SUB_MAX, std::max<uint64_t>(1, (S.rows * S.pitch + sub_bytes - 1) / sub_bytes));
     S.sub_rows = (uint32_t)((S.rows + S.n_sub - 1) / S.n_sub);
     S.sub_cap = std::max<uint64_t>(((inbox_cap + S.n_sub - 1) / S.n_sub * 5 / 4 + 255) / 256 * 256, 256);
     S.inbox_cap = S.sub_cap * S.n_sub;
@@ -126,6 +131,8 @@ int lime_xchg_alloc(lime_ctx *ctx, int world, int rank, uint32_t reads_per_rank,
     // side stream only fills the SMs the scoring kernel drains at its end; what it buys is the absence of any
     // collective or host synchronisation between the strands (6.61 -> 5.96 ms).
     S.k12_ctas = 0;
+    S.use_tail = true;
+    if (const char *e = getenv("LIME_XCHG_TAIL")) S.use_tail = atoi(e) != 0;     // 0: everything in the context's stream (A/B measurements)
     if (const char *e = getenv("LIME_XCHG_K12_CTAS")) S.k12_ctas = atoi(e);
     CK(ctx->strand_state.reserve(sizeof(unsigned long long) * SS_COUNT * (LIME_MAXFILES + 1)), "cudaMalloc strand state");
     if (!ctx->strand_host)
@@ -211,7 +218,7 @@ int lime_xchg_accumulate(lime_ctx *ctx, uint32_t alpha, int ebwt_mode, int stran
     }
     R.sub_cap = S.sub_cap; R.sent = sc + SS_SENT; R.err = sc + SS_ERR;
     OnTail on(ctx);
-    CK(cudaStreamWaitEvent(S.tail, S.ev_scored[strand], 0), "cudaStreamWaitEvent");
+    CK(cudaStreamWaitEvent(ctx->stream, S.ev_scored[strand], 0), "cudaStreamWaitEvent");
     {
         LaunchScope ls(ctx, KID_X_ROUTE);
         CK(launch_xchg_route(R, ctx->stream), "x_route launch");
@@ -220,7 +227,7 @@ int lime_xchg_accumulate(lime_ctx *ctx, uint32_t alpha, int ebwt_mode, int stran
         LaunchScope ls(ctx, KID_X_PUBLISH);
         CK(launch_xchg_publish(Pb, ctx->stream), "x_publish launch");
     }
-    CK(cudaEventRecord(S.ev_routed[fl], S.tail), "cudaEventRecord");
+    CK(cudaEventRecord(S.ev_routed[fl], ctx->stream), "cudaEventRecord");
     S.routed_set[fl] = true;
     return mark_strand(ctx, strand);
 }

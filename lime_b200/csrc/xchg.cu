@@ -21,13 +21,13 @@
 // memory, so the whole chain can be queued on a side stream and runs beside the scoring of the next strand.
 #include "common.cuh"
 #include <algorithm>
+#include <cstdlib>
 
 namespace lime {
 namespace xchg {
 
-constexpr int THREADS = 256;
-constexpr int PER_THREAD = 8;
-constexpr int TILE = THREADS * PER_THREAD;      // records per tile
+constexpr int THREADS = 256;                    // apply_kernel
+constexpr int PER_THREAD = 8;                   // route_kernel<T>: records per thread and tile (tile = T * 8 records)
 
 constexpr int BINS_MAX = XCHG_MAX * XCHG_SUB_MAX;
 struct RouteArgs {
@@ -51,9 +51,12 @@ __device__ __forceinline__ uint32_t owner_of(uint32_t r, uint32_t per, uint32_t 
     return q;
 }
 
-__global__ void __launch_bounds__(THREADS) route_kernel(const RouteArgs P)
+template <int T>
+__global__ void __launch_bounds__(T) route_kernel(const RouteArgs P)
 {
-    __shared__ uint2 s_rec[TILE];
+    constexpr int TILE = T * PER_THREAD;
+    constexpr int THREADS = T;
+    extern __shared__ uint2 s_rec[];             // TILE records (dynamic: 64 KB at 1024 threads)
     __shared__ unsigned s_cnt[BINS_MAX], s_off[BINS_MAX + 1];
     __shared__ unsigned long long s_base[BINS_MAX];
     const unsigned tid = threadIdx.x, lane = tid & 31u;
@@ -116,15 +119,28 @@ __global__ void __launch_bounds__(THREADS) route_kernel(const RouteArgs P)
         for (int k = 0; k < PER_THREAD; k++)
             if (own[k] != 0xffffffffu) s_rec[s_off[own[k]] + idx[k]] = rec[k];
         __syncthreads();
-        // sorted by bin: consecutive threads write consecutive records of one bin's run
-        const unsigned total = s_off[n_bins];
-        for (unsigned i = tid; i < total; i += THREADS) {
-            unsigned lo = 0, hi = n_bins;                              // last bin with s_off <= i
-            while (hi - lo > 1) { const unsigned mid = (lo + hi) >> 1; if (s_off[mid] <= i) lo = mid; else hi = mid; }
-            const unsigned long long d = s_base[lo] + (i - s_off[lo]);
-            const unsigned o = lo / P.n_sub, sb = lo - o * P.n_sub;
-            if (d < P.sub_cap) P.dst[o][(size_t)sb * P.sub_cap + d] = s_rec[i];
-            else atomicOr(P.err, 4ull);
+        // sorted by bin: a warp takes a bin's run and writes it with 16-byte stores (two records each; a single
+        // record in front when the destination starts on an odd slot, one behind when the rest is odd)
+        for (unsigned b = tid >> 5; b < n_bins; b += THREADS / 32) {
+            const unsigned first = s_off[b], cnt = s_off[b + 1] - first;
+            if (!cnt) continue;
+            const unsigned long long d0 = s_base[b];
+            unsigned m = cnt;
+            if (d0 + cnt > P.sub_cap) {                               // region full: keep what fits, report
+                m = d0 < P.sub_cap ? (unsigned)(P.sub_cap - d0) : 0u;
+                if (lane == 0) atomicOr(P.err, 4ull);
+            }
+            const unsigned o = b / P.n_sub, sb = b - o * P.n_sub;
+            uint2 *dst = P.dst[o] + (size_t)sb * P.sub_cap + d0;
+            const uint2 *src = s_rec + first;
+            const unsigned head = (unsigned)(d0 & 1ull) < m ? (unsigned)(d0 & 1ull) : m;
+            if (lane == 0 && head) dst[0] = src[0];
+            const unsigned pairs = (m - head) >> 1;
+            for (unsigned k = lane; k < pairs; k += 32) {
+                const uint2 a = src[head + 2 * k], c = src[head + 2 * k + 1];
+                *reinterpret_cast<uint4 *>(dst + head + 2 * k) = make_uint4(a.x, a.y, c.x, c.y);
+            }
+            if (lane == 0 && ((m - head) & 1u)) dst[m - 1] = src[m - 1];
         }
         __syncthreads();
     }
@@ -232,7 +248,23 @@ cudaError_t launch_xchg_route(const XchgRoute &a, cudaStream_t s)
     P.n_refs = a.n_refs;
     for (int o = 0; o < XCHG_MAX; o++) P.dst[o] = o < (int)a.world ? a.dst[o] : nullptr;
     P.sub_cap = a.sub_cap; P.sent = a.sent; P.err = a.err;
-    xchg::route_kernel<<<148 * 4, xchg::THREADS, 0, s>>>(P);
+    // tile = 8 records per thread; the longer the tile, the longer the run a bin gets (stores over NVLink want
+    // hundreds of bytes): 512 threads -> 4096 records, 32 KB of shared memory, 2-3 CTAs per SM
+    static int threads = 0;
+    if (!threads) {
+        threads = 512;
+        if (const char *e = getenv("LIME_XCHG_ROUTE_THREADS")) threads = atoi(e);
+    }
+    if (threads == 256) xchg::route_kernel<256><<<148 * 4, 256, 256 * 64, s>>>(P);
+    else if (threads == 1024) {
+        static bool once = false;
+        if (!once) {
+            const cudaError_t e = cudaFuncSetAttribute(xchg::route_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, 1024 * 64);
+            if (e != cudaSuccess) return e;
+            once = true;
+        }
+        xchg::route_kernel<1024><<<148 * 2, 1024, 1024 * 64, s>>>(P);
+    } else xchg::route_kernel<512><<<148 * 3, 512, 512 * 64, s>>>(P);
     return cudaGetLastError();
 }
 

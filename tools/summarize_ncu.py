@@ -67,7 +67,8 @@ def main():
                 tb = to_bytes(d["dram__bytes_read.sum"], u["dram__bytes_read.sum"]) + to_bytes(d["dram__bytes_write.sum"], u["dram__bytes_write.sum"])
                 for key, nice in names.items():
                     if key in kn:
-                        traffic[nice] = {"dram_bytes_per_launch": tb, "source": f"profiles/{f[:-8]}.txt", "kernel": kn}
+                        traffic[nice] = {"dram_bytes_per_launch": tb, "source": f"profiles/{f[:-8]}.txt", "kernel": kn,
+                                         "capture": f[:-8], "workload": os.environ.get("LIME_NCU_WORKLOAD", "cfg2")}
                 lines.append(f"  dram traffic per launch = {tb / 1e9:.3f} GB")
             except (KeyError, ValueError):
                 pass
