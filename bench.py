@@ -560,14 +560,24 @@ def run_ours(args, w):
                     "reads_per_s": w["n_reads"] / (e_ms * 1e-3), "h2d_GBps": h2d_bytes / (e_ms * 1e-3) / 1e9, "note": note}
         modes = {}
         if w["alpha"] <= 255 and not args.no_narrow:
-            # the drop-in executables know alpha from argv and promise it (lime_set_alpha_limit): lcp crosses PCIe
-            # as min(lcp, 255) bytes, narrowed on host threads inside the timed region, and stays bytes on the device
+            # the drop-in executables know alpha from argv and name it (lime_set_alpha): lcp crosses PCIe as the bit
+            # lcp < alpha, packed on host threads inside the timed region, expanded to bytes on the device
+            workers = max(1, ctx.lib.lime_host_threads() - 1)
+            ctx.set_alpha(w["alpha"])
+            try:
+                modes["lcp_bits"] = time_host(
+                    "lime_set_alpha(alpha) + lime_load(LIME_MEM_HOST) per strand from pinned host arrays: lcp packed to one bit "
+                    "per position (lcp < alpha) by %d host threads inside the timed region; assignments copied back; PCIe-bound"
+                    % workers, host_bytes - 4 * symbols + sum((sd["n"] + 7) // 8 for sd in strands_dev) + 4 * w["n_refs"])
+            finally:
+                ctx.set_alpha(0)
+            # the weaker promise alpha <= 255 (lime_set_alpha_limit): min(lcp, 255) as bytes
             ctx.set_alpha_limit(w["alpha"])
             try:
                 modes["narrow_lcp"] = time_host(
                     "lime_set_alpha_limit(alpha) + lime_load(LIME_MEM_HOST) per strand from pinned host arrays: lcp narrowed to "
                     "bytes by %d host threads inside the timed region; assignments copied back; PCIe-bound"
-                    % max(1, ctx.lib.lime_host_threads() - 1), host_bytes - 3 * symbols + 4 * w["n_refs"])
+                    % workers, host_bytes - 3 * symbols + 4 * w["n_refs"])
             finally:
                 ctx.set_alpha_limit(0)
         if args.e2e_plain or not modes:
@@ -835,7 +845,7 @@ def run_ours_multi(args, w, world, rank, local):
     route_ms = prof.get("x_route", {}).get("ms", 0.0) / max(prof.get("x_route", {}).get("launches", 1), 1)
 
     # ---- e2e: the same step with every rank's shards in page-locked HOST memory (lime_load(LIME_MEM_HOST) per
-    # strand inside the timed region, lcp narrowed to bytes on host threads) and each rank's assignments copied
+    # strand inside the timed region, lcp packed to bits on host threads) and each rank's assignments copied
     # back to its host, max over ranks.
     e2e = None
     host_bytes = sum((8 + w["ebwt"]) * (sh["n_own"] + sh["n_halo"]) for sh in shards)
@@ -858,7 +868,7 @@ def run_ours_multi(args, w, world, rank, local):
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         if int(flag.item()) == 1:
             if w["alpha"] <= 255 and not args.no_narrow:
-                ctx.set_alpha_limit(w["alpha"])
+                ctx.set_alpha(w["alpha"])                 # lcp crosses as the bit lcp < alpha
             try:
                 out_d = tuple(np.array(x, copy=True) for x in step())
                 out_h = tuple(np.array(x, copy=True) for x in step(src=host_shards))
@@ -876,12 +886,13 @@ def run_ours_multi(args, w, world, rank, local):
                 tw1 = time.perf_counter()
                 dist.barrier()
             finally:
-                ctx.set_alpha_limit(0)
+                ctx.set_alpha(0)
             e_ms = torch.tensor([max(ev0.elapsed_time(ev1), (tw1 - tw0) * 1e3)], device=dev, dtype=torch.float64)
             dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
             e_ms = float(e_ms.item()) / e2e_steps
             narrow = w["alpha"] <= 255 and not args.no_narrow
-            h2d = sum((8 + w["ebwt"] - (3 if narrow else 0)) * (hs["n_own"] + hs["n_halo"]) for hs in host_shards)
+            h2d = sum((4 + w["ebwt"]) * (hs["n_own"] + hs["n_halo"]) + ((hs["n_own"] + hs["n_halo"] + 7) // 8 if narrow else 4 * (hs["n_own"] + hs["n_halo"]))
+                      for hs in host_shards)
             h2d_t = torch.tensor([h2d], device=dev, dtype=torch.int64)
             dist.all_reduce(h2d_t)
             if int(same.item()) == 1:
@@ -890,7 +901,7 @@ def run_ours_multi(args, w, world, rank, local):
                        "ms_per_step": e_ms, "steps": e2e_steps, "reads_per_s": n_reads / (e_ms * 1e-3),
                        "h2d_GBps_per_gpu": int(h2d_t.item()) / world / (e_ms * 1e-3) / 1e9,
                        "note": "every rank: lime_load(LIME_MEM_HOST) of its shard of each strand from page-locked host arrays"
-                               + (" (lcp narrowed to bytes by host threads inside the timed region)" if narrow else "")
+                               + (" (lcp packed to the bit lcp < alpha by host threads inside the timed region)" if narrow else "")
                                + " + its assignments copied back; max over ranks; results equal to the resident step"}
             else:
                 e2e = {"error": "host-buffer step disagrees with the resident step"}

@@ -96,6 +96,15 @@ int  lime_load(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uin
  * called with alpha > 255 on a strand loaded that way fails with LIME_ERR_STATE.
  */
 int  lime_set_alpha_limit(lime_ctx *ctx, uint32_t max_alpha);
+/*
+ * One step further: lime_set_alpha names the alpha itself (the drop-in executables have it on their command
+ * line).  With 1 <= alpha <= 255, lime_load(LIME_MEM_HOST) ships ONE BIT per position -- lcp[i] < alpha, packed by
+ * the same host threads, bit j of byte i = position 8 i + j -- i.e. 1/8 + 4 (+1) bytes per position, and expands
+ * each chunk on the device into the bytes 0 (lcp < alpha) / 255 the kernels read.  Results are identical for that
+ * alpha; a step called with another alpha on a strand loaded that way fails with LIME_ERR_STATE.  0 = off (default);
+ * it takes precedence over lime_set_alpha_limit.
+ */
+int  lime_set_alpha(lime_ctx *ctx, uint32_t alpha);
 /* The host half on its own (no CUDA): out[i] = min(lcp[i], 255) with `threads` host threads (<= 0:
  * lime_host_threads()), and the same through the chunk loop lime_load runs (slots stage buffers of
  * `chunk` positions) over a simulated in-order copy queue that performs each copy copy_delay_us after
@@ -104,6 +113,11 @@ int  lime_host_threads(void);     /* LIME_HOST_THREADS, else min(cores in the af
 int  lime_host_narrow_lcp(const uint32_t *lcp, uint8_t *out, uint64_t n, int threads);
 int  lime_host_narrow_lcp_pipelined(const uint32_t *lcp, uint8_t *out, uint64_t n, uint64_t chunk,
                                     int threads, int slots, int copy_delay_us);
+/* The same two for the bit transfer of lime_set_alpha: out = ceil(n / 8) bytes, bit j of out[i] = lcp[8 i + j] < alpha,
+ * bits beyond n set; chunk must be a multiple of 512. */
+int  lime_host_pack_lcp(const uint32_t *lcp, uint8_t *out, uint64_t n, uint32_t alpha, int threads);
+int  lime_host_pack_lcp_pipelined(const uint32_t *lcp, uint8_t *out, uint64_t n, uint64_t chunk, uint32_t alpha,
+                                  int threads, int slots, int copy_delay_us);
 
 /* ---- step 1 : ClusterLCP.cpp:139-283 ------------------------------------------------------ */
 

@@ -101,6 +101,11 @@ class LimeContext:
         1..255 host-mode loads ship lcp as min(lcp, 255) bytes (identical results).  0 = no promise."""
         self._ck(self.lib.lime_set_alpha_limit(self.h, int(max_alpha)))
 
+    def set_alpha(self, alpha):
+        """lime_set_alpha: the strands loaded from now on will be run with exactly this alpha; with 1..255
+        host-mode loads ship one bit per position (lcp < alpha), identical results.  0 = off."""
+        self._ck(self.lib.lime_set_alpha(self.h, int(alpha)))
+
     def load(self, lcp, da, ebwt, n_reads, n_refs, n_own=None, n_halo=0, pos_base=0, is_last=True,
              mem=MEM_HOST, n_total=None):
         """lime_load.  Host mode takes numpy arrays; device mode takes pointers + n_total."""

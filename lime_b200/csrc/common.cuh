@@ -192,6 +192,10 @@ struct lime_ctx {
     // such a load leaves min(lcp, 255) as bytes on the device (lcp8) and the kernels read those
     uint32_t alpha_limit = 0;
     lime::DevBuf in_lcp8;
+    // lime_set_alpha: the caller names the alpha itself; a host load then ships the bit lcp < alpha and leaves the
+    // bytes 0 / 255 in in_lcp8; lcp_alpha = the alpha the resident lcp answers for (0: any alpha <= 255, or u32)
+    uint32_t alpha_exact = 0, lcp_alpha = 0;
+    lime::DevBuf in_lcpbits;
     uint8_t *stage[lime::LIME_STAGE_SLOTS] = {nullptr};
     cudaEvent_t stage_ev[lime::LIME_STAGE_SLOTS] = {nullptr};
     bool stage_busy = false;

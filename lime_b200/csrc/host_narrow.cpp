@@ -6,6 +6,7 @@
 // plain C++ (g++, AVX2 clone picked at load time), tested on the CPU (tests/test_narrow_lcp.py).
 #include <algorithm>
 #include <atomic>
+#include <immintrin.h>
 #include <cstdint>
 #include <cstdlib>
 #include <chrono>
@@ -26,6 +27,39 @@ void narrow_range(const uint32_t *__restrict__ src, uint8_t *__restrict__ dst, u
         const uint32_t v = src[i];
         dst[i] = (uint8_t)(v < 255u ? v : 255u);
     }
+}
+
+// bit j of dst[i] = (src[8 i + j] < alpha): the only thing the path ever asks of lcp, once alpha is known.
+// n positions, n a multiple of 8 except for the last call of an array; positions beyond n read as heads (1).
+void pack_range_scalar(const uint32_t *src, uint8_t *dst, uint64_t n, uint32_t alpha)
+{
+    for (uint64_t i = 0; i < n; i += 8) {
+        unsigned b = 0;
+        for (unsigned j = 0; j < 8; j++) b |= (unsigned)(i + j >= n || src[i + j] < alpha) << j;
+        dst[i >> 3] = (uint8_t)b;
+    }
+}
+__attribute__((target("avx2")))
+void pack_range_avx2(const uint32_t *src, uint8_t *dst, uint64_t n, uint32_t alpha)
+{
+    const __m256i flip = _mm256_set1_epi32((int)0x80000000u);
+    const __m256i a = _mm256_xor_si256(_mm256_set1_epi32((int)alpha), flip);
+    uint64_t i = 0;
+    for (; i + 32 <= n; i += 32) {                    // 4 bytes of bits per round
+        uint32_t w = 0;
+        for (int k = 0; k < 4; k++) {
+            const __m256i v = _mm256_xor_si256(_mm256_loadu_si256(reinterpret_cast<const __m256i *>(src + i + 8 * k)), flip);
+            w |= (uint32_t)_mm256_movemask_ps(_mm256_castsi256_ps(_mm256_cmpgt_epi32(a, v))) << (8 * k);
+        }
+        dst[(i >> 3) + 0] = (uint8_t)w; dst[(i >> 3) + 1] = (uint8_t)(w >> 8);
+        dst[(i >> 3) + 2] = (uint8_t)(w >> 16); dst[(i >> 3) + 3] = (uint8_t)(w >> 24);
+    }
+    if (i < n) pack_range_scalar(src + i, dst + (i >> 3), n - i, alpha);
+}
+void pack_range(const uint32_t *src, uint8_t *dst, uint64_t n, uint32_t alpha)
+{
+    static const bool avx2 = __builtin_cpu_supports("avx2");
+    if (avx2) pack_range_avx2(src, dst, n, alpha); else pack_range_scalar(src, dst, n, alpha);
 }
 
 } // namespace
@@ -57,6 +91,19 @@ extern "C" int lime_host_narrow_lcp(const uint32_t *lcp, uint8_t *out, uint64_t 
     return LIME_OK;
 }
 
+extern "C" int lime_host_pack_lcp(const uint32_t *lcp, uint8_t *out, uint64_t n, uint32_t alpha, int threads)
+{
+    if ((!lcp || !out) && n) return LIME_ERR_ARG;
+    if (threads <= 0) threads = lime_host_threads();
+    const uint64_t per = std::max<uint64_t>(((n + threads - 1) / threads + 511) / 512 * 512, 1u << 20);
+    std::vector<std::thread> pool;
+    for (uint64_t a = per; a < n; a += per)
+        pool.emplace_back(pack_range, lcp + a, out + (a >> 3), std::min(per, n - a), alpha);
+    pack_range(lcp, out, std::min(per, n), alpha);
+    for (auto &t : pool) t.join();
+    return LIME_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // The chunk pipeline of lime_load: `threads` workers narrow chunk after chunk into a ring of
 // `slots` page-locked stage buffers; the calling thread (lime_abi_load.cu) takes each finished chunk,
@@ -69,14 +116,15 @@ struct NarrowPipe {
     const uint32_t *src = nullptr;
     uint64_t n = 0, chunk = 0, n_chunks = 0;
     int threads = 0, slots = 0;
-    uint8_t *const *stage = nullptr;                 // [slots] buffers of `chunk` bytes
+    uint8_t *const *stage = nullptr;                 // [slots] buffers of `chunk` bytes (bits: chunk / 8)
+    uint32_t bits_alpha = 0;                         // 0: bytes min(lcp, 255); else one bit lcp < bits_alpha
     std::vector<std::atomic<int>> done;              // per chunk: workers that finished their slice
     std::atomic<uint64_t> free_upto{0};              // chunks < free_upto own a free slot
     std::vector<std::thread> pool;
 
-    NarrowPipe(const uint32_t *src_, uint64_t n_, uint64_t chunk_, int threads_, int slots_, uint8_t *const *stage_)
+    NarrowPipe(const uint32_t *src_, uint64_t n_, uint64_t chunk_, int threads_, int slots_, uint8_t *const *stage_, uint32_t bits_alpha_)
         : src(src_), n(n_), chunk(chunk_), n_chunks((n_ + chunk_ - 1) / chunk_), threads(threads_), slots(slots_),
-          stage(stage_), done((n_ + chunk_ - 1) / chunk_)
+          stage(stage_), bits_alpha(bits_alpha_), done((n_ + chunk_ - 1) / chunk_)
     {
         for (auto &d : done) d.store(0, std::memory_order_relaxed);
         free_upto.store((uint64_t)slots, std::memory_order_release);
@@ -92,10 +140,14 @@ struct NarrowPipe {
         for (uint64_t c = 0; c < n_chunks; c++) {
             while (c >= free_upto.load(std::memory_order_acquire)) std::this_thread::yield();
             const uint64_t base = c * chunk, len = std::min(chunk, n - base);
-            // slices on 64-byte boundaries of the output
-            const uint64_t per = ((len + threads - 1) / threads + 63) / 64 * 64;
+            // slices on 64-byte boundaries of the output (bits: 512 positions)
+            const uint64_t unit = bits_alpha ? 512 : 64;
+            const uint64_t per = ((len + threads - 1) / threads + unit - 1) / unit * unit;
             const uint64_t a = std::min(len, per * (uint64_t)t), b = std::min(len, a + per);
-            if (b > a) narrow_range(src + base + a, stage[c % slots] + a, b - a);
+            if (b > a) {
+                if (bits_alpha) pack_range(src + base + a, stage[c % slots] + (a >> 3), b - a, bits_alpha);
+                else narrow_range(src + base + a, stage[c % slots] + a, b - a);
+            }
             done[c].fetch_add(1, std::memory_order_release);
         }
     }
@@ -104,9 +156,10 @@ struct NarrowPipe {
     void released(uint64_t k) { free_upto.store(k + (uint64_t)slots, std::memory_order_release); }
 };
 
-NarrowPipe *narrow_pipe_open(const uint32_t *src, uint64_t n, uint64_t chunk, int threads, int slots, uint8_t *const *stage)
+NarrowPipe *narrow_pipe_open(const uint32_t *src, uint64_t n, uint64_t chunk, int threads, int slots, uint8_t *const *stage,
+                             uint32_t bits_alpha)
 {
-    return new NarrowPipe(src, n, chunk, threads, slots, stage);
+    return new NarrowPipe(src, n, chunk, threads, slots, stage, bits_alpha);
 }
 bool narrow_pipe_ready(const NarrowPipe *p, uint64_t c) { return p->ready(c); }
 void narrow_pipe_released(NarrowPipe *p, uint64_t k) { p->released(k); }
@@ -121,11 +174,11 @@ namespace {
 
 struct SimQueue {
     struct Job { int slot; uint64_t base, len, seq; };
-    uint8_t *out; uint8_t *const *stage; int delay_us;
+    uint8_t *out; uint8_t *const *stage; int delay_us; bool bits;
     std::mutex mu; std::deque<Job> jobs; bool stop = false;
     std::atomic<uint64_t> recorded[8], completed[8];
     std::thread worker;
-    SimQueue(uint8_t *out_, uint8_t *const *stage_, int delay_us_) : out(out_), stage(stage_), delay_us(delay_us_)
+    SimQueue(uint8_t *out_, uint8_t *const *stage_, int delay_us_, bool bits_) : out(out_), stage(stage_), delay_us(delay_us_), bits(bits_)
     {
         for (int s = 0; s < 8; s++) { recorded[s].store(0); completed[s].store(0); }
         worker = std::thread([this] { run(); });
@@ -146,7 +199,8 @@ struct SimQueue {
             }
             if (j.slot < 0) { std::this_thread::yield(); continue; }
             if (delay_us > 0) std::this_thread::sleep_for(std::chrono::microseconds(delay_us));
-            std::copy(stage[j.slot], stage[j.slot] + j.len, out + j.base);
+            if (bits) std::copy(stage[j.slot], stage[j.slot] + (j.len + 7) / 8, out + j.base / 8);
+            else std::copy(stage[j.slot], stage[j.slot] + j.len, out + j.base);
             completed[j.slot].store(j.seq, std::memory_order_release);
         }
     }
@@ -174,11 +228,11 @@ struct SimQueue {
 
 } // namespace
 
-extern "C" int lime_host_narrow_lcp_pipelined(const uint32_t *lcp, uint8_t *out, uint64_t n, uint64_t chunk,
-                                              int threads, int slots, int copy_delay_us)
+static int pipelined(const uint32_t *lcp, uint8_t *out, uint64_t n, uint64_t chunk, int threads, int slots, int copy_delay_us,
+                     uint32_t bits_alpha)
 {
     if ((!lcp || !out) && n) return LIME_ERR_ARG;
-    if (chunk == 0 || slots < 1 || slots > 8) return LIME_ERR_ARG;
+    if (chunk == 0 || slots < 1 || slots > 8 || (bits_alpha && chunk % 512)) return LIME_ERR_ARG;
     if (threads <= 0) threads = lime_host_threads();
     if (n == 0) return LIME_OK;
     std::vector<std::vector<uint8_t>> bufs(slots, std::vector<uint8_t>(chunk));
@@ -186,9 +240,22 @@ extern "C" int lime_host_narrow_lcp_pipelined(const uint32_t *lcp, uint8_t *out,
     for (auto &b : bufs) stage.push_back(b.data());
     int rc;
     {
-        SimQueue q(out, stage.data(), copy_delay_us);
-        rc = lime::narrow_transfer(q, lcp, n, chunk, threads, slots, stage.data());
+        SimQueue q(out, stage.data(), copy_delay_us, bits_alpha != 0);
+        rc = lime::narrow_transfer(q, lcp, n, chunk, threads, slots, stage.data(), bits_alpha);
         q.drain();
     }                                                      // joins the worker: every queued copy has run
     return rc ? LIME_ERR_CUDA : LIME_OK;
+}
+
+extern "C" int lime_host_narrow_lcp_pipelined(const uint32_t *lcp, uint8_t *out, uint64_t n, uint64_t chunk,
+                                              int threads, int slots, int copy_delay_us)
+{
+    return pipelined(lcp, out, n, chunk, threads, slots, copy_delay_us, 0);
+}
+
+extern "C" int lime_host_pack_lcp_pipelined(const uint32_t *lcp, uint8_t *out, uint64_t n, uint64_t chunk, uint32_t alpha,
+                                            int threads, int slots, int copy_delay_us)
+{
+    if (alpha == 0) return LIME_ERR_ARG;
+    return pipelined(lcp, out, n, chunk, threads, slots, copy_delay_us, alpha);
 }

@@ -27,23 +27,8 @@ __device__ __forceinline__ void sim_add(const K2Args &P, uint32_t r, uint32_t g,
 {
     SimAcc acc;
     acc.sim8 = P.sim8; acc.pitch8 = P.pitch8; acc.sim32 = P.sim32; acc.lo = P.lo; acc.hi = P.hi;
-    acc.n_refs = P.n_refs; acc.carry = P.carry; acc.sum_t = P.sum_t;
+    acc.n_refs = P.n_refs; acc.carry = P.carry;
     lime::sim_add<EXACT32>(acc, r, g, t);
-}
-
-// multi-GPU: the update leaves as a record {read, genome << 8 | t} (FlatOut).  Called by ALL 32 lanes of a warp
-// from converged code (t = 0: nothing to append for this lane); the lanes with a record take their slots with one
-// atomic.  (Not __activemask() inside the `if (t)`: the compiler may predicate that branch, the mask then names
-// lanes without a record and the slot arithmetic goes wrong.)
-__device__ __forceinline__ void flat_append_warp(const FlatOut &F, uint32_t r, uint32_t g, uint32_t t)
-{
-    const unsigned lane = lane_id();
-    const unsigned m = __ballot_sync(FULL, t != 0u);
-    if (m == 0u) return;
-    unsigned long long base = 0;
-    if (lane == 0) base = atomicAdd(F.count, (unsigned long long)__popc(m));
-    base = __shfl_sync(FULL, base, 0) + __popc(m & ((1u << lane) - 1u));
-    if (t != 0u && base < F.cap) F.rec[base] = make_uint2(r, (g << 8) | t);
 }
 
 // ---- warp path: clusters of <= 32 positions ---------------------------------------------------
@@ -162,13 +147,24 @@ __global__ void __launch_bounds__(WARP_THREADS) warp_kernel(K2Args P)
 }
 
 // ---- block path: clusters of 33 .. 65536 positions ---------------------------------------------
+// One CTA per cluster.  Positions are grouped by document id in a hash table in the CTA's (L2-resident) scratch
+// area; the table is then folded into two compact arrays -- reads {id, 16 class counts}, genomes likewise -- and
+// the pair phase runs out of shared memory: the genomes of the cluster (a tile of GT at a time) are staged there
+// once, a warp takes a read (its record is fetched one iteration ahead) and its lanes the genomes.  Nothing in
+// the pair loop waits on global memory: at alpha = 12 a strand holds hundreds of clusters of ~40,000 positions
+// (~18,000 reads x all genomes each), which an earlier version with three dependent L2 loads per pair, an atomic
+// whose return value was inspected and one global counter update per pair took 660 ms per strand to score.
+// RED: updates are fire-and-forget adds and the caller proves the absence of byte carries by the byte sum of the
+// matrix (the fused path, K12Args::sum_t); otherwise every add inspects the word it returns.
 constexpr int BLOCK_THREADS = 256;
+constexpr int BLOCK_WARPS = BLOCK_THREADS / 32;
+constexpr int GT = 1024;                             // genomes per shared-memory tile
 constexpr uint32_t HCAP = 2 * LIME_SIZE_MAX_BUF;     // slots per CTA table
 constexpr uint32_t EMPTY = 0xffffffffu;
-// per-CTA scratch layout: keys[HCAP] u32 | cnt[HCAP][8] u32 (16 x u16, later 16 x u8 in cnt[.][0..3])
-//                         | rlist[65536] u32 | glist[65536] u32
+// per-CTA scratch layout: keys[HCAP] u32 | cnt[HCAP][8] u32 (16 x u16 per slot) | rid[65536] u32 | gid[65536] u32
+//                         | rcnt[65536] uint4 (16 x u8) | gcnt[65536] uint4
 constexpr uint64_t SCRATCH_BYTES =
-    (uint64_t)HCAP * 4 + (uint64_t)HCAP * 32 + 2ull * LIME_SIZE_MAX_BUF * 4;
+    (uint64_t)HCAP * 4 + (uint64_t)HCAP * 32 + 2ull * LIME_SIZE_MAX_BUF * 4 + 2ull * LIME_SIZE_MAX_BUF * 16;
 
 __device__ __forceinline__ uint32_t hash32(uint32_t x)
 {
@@ -176,22 +172,48 @@ __device__ __forceinline__ uint32_t hash32(uint32_t x)
     return x;
 }
 
-template <bool EBWT, bool EXACT32>
+// a warp's cursor into the record list (multi-GPU): blocks of K12_FLAT_BLK slots, as the fused kernel takes them
+struct FlatCursor { unsigned long long base; unsigned fill; };
+__device__ __forceinline__ void flat_append_block(const FlatOut &F, FlatCursor &C, unsigned lane, uint32_t r, uint32_t g, uint32_t t)
+{
+    const unsigned m = __ballot_sync(FULL, t != 0u);
+    if (m == 0u) return;
+    const unsigned n = (unsigned)__popc(m);
+    const bool spill = C.fill + n > (unsigned)K12_FLAT_BLK;
+    unsigned long long nb = 0;
+    if (spill) {
+        if (lane == 0) nb = atomicAdd(F.count, (unsigned long long)K12_FLAT_BLK);
+        nb = __shfl_sync(FULL, nb, 0);
+    }
+    const unsigned idx = C.fill + (unsigned)__popc(m & ((1u << lane) - 1u));
+    const unsigned long long dst = idx < (unsigned)K12_FLAT_BLK ? C.base + idx : nb + (idx - K12_FLAT_BLK);
+    if (t != 0u && dst < F.cap) F.rec[dst] = make_uint2(r, (g << 8) | t);
+    if (spill) { C.base = nb; C.fill = C.fill + n - K12_FLAT_BLK; }
+    else C.fill += n;
+}
+
+template <bool EBWT, bool EXACT32, bool RED>
 __global__ void __launch_bounds__(BLOCK_THREADS) block_kernel(K2Args P)
 {
     __shared__ unsigned long long s_item;
     __shared__ unsigned s_nr, s_ng, s_iupac;
+    __shared__ uint4 s_gcnt[GT];
+    __shared__ uint32_t s_gid[GT];
     uint8_t *my = P.scratch + (size_t)blockIdx.x * P.scratch_per_cta;
     uint32_t *keys = reinterpret_cast<uint32_t *>(my);
     uint32_t *cnt = keys + HCAP;                       // [HCAP][8]
-    uint32_t *rlist = cnt + (size_t)HCAP * 8;
-    uint32_t *glist = rlist + LIME_SIZE_MAX_BUF;
+    uint32_t *rid = cnt + (size_t)HCAP * 8;
+    uint32_t *gid = rid + LIME_SIZE_MAX_BUF;
+    uint4 *rcnt = reinterpret_cast<uint4 *>(gid + LIME_SIZE_MAX_BUF);
+    uint4 *gcnt = rcnt + LIME_SIZE_MAX_BUF;
     const int tid = threadIdx.x;
     const unsigned lane = lane_id(), warp = tid >> 5;
     // the list may have overflowed (count > cap) and a cluster may exceed the buffers: the host
     // reports both as errors after the pass, the kernel just stays inside its arrays
     const unsigned long long n_large = min(*P.large_count, (unsigned long long)P.large_cap);
-    unsigned long long updates = 0;
+    unsigned long long updates = 0, tsum = 0;
+    FlatCursor fc; fc.base = 0; fc.fill = K12_FLAT_BLK;
+    const bool flat = P.flat.rec != nullptr;
 
     while (true) {
         if (tid == 0) { s_item = atomicAdd(P.large_next, 1ull); s_nr = 0; s_ng = 0; s_iupac = 0; }
@@ -232,11 +254,14 @@ __global__ void __launch_bounds__(BLOCK_THREADS) block_kernel(K2Args P)
         }
         __syncthreads();
 
-        // list reads / genomes; fold counts to uint8: reads wrap (:123), genomes saturate (:96-97)
+        // fold the table into the compact arrays; counts to uint8: reads wrap (:123), genomes saturate (:96-97)
         for (uint32_t h = tid; h < cap; h += BLOCK_THREADS) {
             const uint32_t id = __ldcg(&keys[h]);   // L2: the slot was written by an atomic
             if (id == EMPTY) continue;
             const bool is_read = id < P.n_reads;
+            const uint4 lo = __ldcg(reinterpret_cast<const uint4 *>(&cnt[(size_t)h * 8]));
+            const uint4 hi = __ldcg(reinterpret_cast<const uint4 *>(&cnt[(size_t)h * 8 + 4]));
+            const uint32_t in[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
             uint32_t out[4];
 #pragma unroll
             for (int w = 0; w < 4; w++) {
@@ -244,44 +269,65 @@ __global__ void __launch_bounds__(BLOCK_THREADS) block_kernel(K2Args P)
 #pragma unroll
                 for (int b = 0; b < 4; b++) {
                     const int cl = w * 4 + b;
-                    uint32_t v = (__ldcg(&cnt[(size_t)h * 8 + (cl >> 1)]) >> ((cl & 1) * 16)) & 0xffffu;
+                    uint32_t v = (in[cl >> 1] >> ((cl & 1) * 16)) & 0xffffu;
                     v = is_read ? (v & 0xffu) : min(v, 255u);
                     packed |= v << (b * 8);
                 }
                 out[w] = packed;
             }
-            *reinterpret_cast<uint4 *>(&cnt[(size_t)h * 8]) = make_uint4(out[0], out[1], out[2], out[3]);
-            if (is_read) rlist[atomicAdd(&s_nr, 1u)] = h;
-            else         glist[atomicAdd(&s_ng, 1u)] = h;
+            const uint4 pk = make_uint4(out[0], out[1], out[2], out[3]);
+            if (is_read) { const unsigned k = atomicAdd(&s_nr, 1u); rid[k] = id; rcnt[k] = pk; }
+            else         { const unsigned k = atomicAdd(&s_ng, 1u); gid[k] = id - P.n_reads; gcnt[k] = pk; }
         }
         __syncthreads();
 
-        // reads x genomes: a warp per read, lanes over genomes
+        // reads x genomes: the genomes from shared memory, a warp per read, lanes over genomes
         const uint32_t nr = s_nr, ng = s_ng;
         const bool iupac = s_iupac != 0;
-        for (uint32_t ri = warp; ri < nr; ri += BLOCK_THREADS / 32) {
-            const uint32_t hr = __ldcg(&rlist[ri]);
-            const uint32_t r = __ldcg(&keys[hr]);
-            const uint4 R = __ldcg(reinterpret_cast<const uint4 *>(&cnt[(size_t)hr * 8]));
-            for (uint32_t g0 = 0; g0 < ng; g0 += 32) {                 // warp-uniform trip count
-                const uint32_t gi = g0 + lane;
-                uint32_t t = 0, g = 0;
-                if (gi < ng) {
-                    const uint32_t hg = __ldcg(&glist[gi]);
-                    const uint4 G = __ldcg(reinterpret_cast<const uint4 *>(&cnt[(size_t)hg * 8]));
-                    t = (iupac ? score_iupac(R, G) : score_plain(R, G)) & 0xffu;
-                    g = __ldcg(&keys[hg]) - P.n_reads;
+        for (uint32_t gb = 0; gb < ng; gb += GT) {
+            const uint32_t gt = min((uint32_t)GT, ng - gb);
+            for (uint32_t i = tid; i < gt; i += BLOCK_THREADS) { s_gcnt[i] = __ldcg(gcnt + gb + i); s_gid[i] = __ldcg(gid + gb + i); }
+            __syncthreads();
+            uint32_t ri = warp;
+            uint4 Rn = make_uint4(0, 0, 0, 0);
+            uint32_t rn = 0;
+            if (ri < nr) { Rn = __ldcg(rcnt + ri); rn = __ldcg(rid + ri); }
+            while (ri < nr) {
+                const uint4 R = Rn;
+                const uint32_t r = rn;
+                const uint32_t nx = ri + BLOCK_WARPS;
+                if (nx < nr) { Rn = __ldcg(rcnt + nx); rn = __ldcg(rid + nx); }      // lands while this read is scored
+                unsigned *row_w = (!EXACT32 && !flat) ? reinterpret_cast<unsigned *>(P.sim8 + (size_t)r * P.pitch8) : nullptr;
+                for (uint32_t g0 = 0; g0 < gt; g0 += 32) {                 // warp-uniform trip count
+                    const uint32_t gi = g0 + lane;
+                    uint32_t t = 0, g = 0;
+                    if (gi < gt) {
+                        const uint4 G = s_gcnt[gi];
+                        t = (iupac ? score_iupac(R, G) : score_plain(R, G)) & 0xffu;
+                        g = s_gid[gi];
+                    }
+                    if (flat) flat_append_block(P.flat, fc, lane, r, g, t);
+                    else if (t) {
+                        if (RED) {
+                            asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(row_w + (g >> 2)), "r"(t << ((g & 3u) * 8u)) : "memory");
+                        } else sim_add<EXACT32>(P, r, g, t);
+                    }
+                    if (t) { updates++; tsum += t; }
                 }
-                if (P.flat.rec) flat_append_warp(P.flat, r, g, t);
-                else if (t) sim_add<EXACT32>(P, r, g, t);
-                if (t) updates++;
+                ri = nx;
             }
+            __syncthreads();
         }
-        __syncthreads();
+    }
+    if (flat && fc.fill < (unsigned)K12_FLAT_BLK) {
+        // null records (t = 0) up to the end of the warp's last block: every slot below the cursor is defined
+        for (unsigned i = fc.fill + lane; i < (unsigned)K12_FLAT_BLK; i += 32)
+            if (fc.base + i < P.flat.cap) P.flat.rec[fc.base + i] = make_uint2(0xffffffffu, 0u);
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) updates += __shfl_xor_sync(FULL, updates, o);
+    for (int o = 16; o > 0; o >>= 1) { updates += __shfl_xor_sync(FULL, updates, o); tsum += __shfl_xor_sync(FULL, tsum, o); }
     if (lane == 0 && updates) atomicAdd(P.n_updates, updates);
+    if (lane == 0 && tsum && P.sum_t) atomicAdd(P.sum_t, tsum);
 }
 
 // ---- exact pass epilogue: 32-bit cells -> uint8 cells (mod 256) ---------------------------------
@@ -299,7 +345,7 @@ __global__ void narrow_kernel(const uint32_t *sim32, uint32_t lo, uint32_t hi, u
 } // namespace k2
 
 uint64_t k2_block_scratch_bytes() { return k2::SCRATCH_BYTES; }
-int k2_block_grid() { return 148 * 2; }
+int k2_block_grid() { return 148 * 3; }       // 24 warps per SM; 7 MB of scratch per CTA
 
 cudaError_t launch_k2_warp(const K2Args &a, bool exact32, cudaStream_t s)
 {
@@ -318,10 +364,16 @@ cudaError_t launch_k2_warp(const K2Args &a, bool exact32, cudaStream_t s)
 cudaError_t launch_k2_block(const K2Args &a, bool exact32, cudaStream_t s, int grid)
 {
     const bool ebwt = a.ebwt != nullptr;
-    if (ebwt && !exact32)       k2::block_kernel<true, false><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);
-    else if (ebwt && exact32)   k2::block_kernel<true, true><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);
-    else if (!ebwt && !exact32) k2::block_kernel<false, false><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);
-    else                        k2::block_kernel<false, true><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);
+    // fire-and-forget adds when the caller proves the absence of byte carries by the byte sum (sum_t given)
+    const bool red = !exact32 && a.sum_t != nullptr && a.flat.rec == nullptr;
+    if (red) {
+        if (ebwt) k2::block_kernel<true, false, true><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);
+        else      k2::block_kernel<false, false, true><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);
+    }
+    else if (ebwt && !exact32)  k2::block_kernel<true, false, false><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);
+    else if (ebwt && exact32)   k2::block_kernel<true, true, false><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);
+    else if (!ebwt && !exact32) k2::block_kernel<false, false, false><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);
+    else                        k2::block_kernel<false, true, false><<<grid, k2::BLOCK_THREADS, 0, s>>>(a);
     return cudaGetLastError();
 }
 

@@ -101,15 +101,18 @@ int lime_load(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint
             (reinterpret_cast<uintptr_t>(ebwt) & 3))
             return fail(ctx, LIME_ERR_ARG, "lime_load: device lcp/da must be 16-byte aligned, ebwt 4-byte aligned");
         ctx->d_lcp = lcp; ctx->d_da = da; ctx->d_ebwt = ebwt;
-        ctx->lcp8 = false;
+        ctx->lcp8 = false; ctx->lcp_alpha = 0;
     } else {
-        // narrowed lcp transfer (lime_abi_load.cu) when the caller has promised alpha <= 255
-        const bool narrow = lcp && ctx->alpha_limit >= 1 && ctx->alpha_limit <= 255 && n >= (1ull << 16);
+        // narrowed lcp transfer (lime_abi_load.cu): one bit per position when the caller has named alpha
+        // (lime_set_alpha), one byte when it has promised alpha <= 255 (lime_set_alpha_limit)
+        const bool big = lcp && n >= (1ull << 16);
+        const uint32_t bits_alpha = big && ctx->alpha_exact >= 1 && ctx->alpha_exact <= 255 ? ctx->alpha_exact : 0;
+        const bool narrow = bits_alpha || (big && ctx->alpha_limit >= 1 && ctx->alpha_limit <= 255);
         if ((lcp && !narrow) || n == 0) CK(ctx->in_lcp.reserve(std::max<uint64_t>(n, 4) * 4), "cudaMalloc lcp");
         CK(ctx->in_da.reserve(std::max<uint64_t>(n, 4) * 4), "cudaMalloc da");
         if (ebwt) CK(ctx->in_ebwt.reserve(std::max<uint64_t>(n, 16)), "cudaMalloc ebwt");
         if (narrow) {
-            const int rc = load_host_narrow(ctx, lcp, da, ebwt, n);
+            const int rc = load_host_narrow(ctx, lcp, da, ebwt, n, bits_alpha);
             if (rc != LIME_OK) return rc;
         } else if (n) {
             if (lcp) CK(cudaMemcpyAsync(ctx->in_lcp.p, lcp, n * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D lcp");
@@ -117,7 +120,7 @@ int lime_load(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint
             if (ebwt) CK(cudaMemcpyAsync(ctx->in_ebwt.p, ebwt, n, cudaMemcpyHostToDevice, ctx->stream), "H2D ebwt");
         }
         // a narrowed load leaves min(lcp, 255) as bytes on the device; the kernels read those
-        ctx->lcp8 = narrow;
+        ctx->lcp8 = narrow; ctx->lcp_alpha = bits_alpha;
         ctx->d_lcp = narrow ? ctx->in_lcp8.p : ((lcp || n == 0) ? ctx->in_lcp.p : nullptr);
         ctx->d_da = ctx->in_da.as<uint32_t>();
         ctx->d_ebwt = ebwt ? ctx->in_ebwt.as<uint8_t>() : nullptr;
@@ -202,10 +205,18 @@ int lime_clusters_set(lime_ctx *ctx, const lime_cluster *cl, uint64_t n, uint64_
 
 // the detection passes (count, scan, emit): cluster records of this shard into ctx->clusters, ascending pStart;
 // sets ctx->n_clusters / alpha, returns the scalars
-int detect_into_ctx(lime_ctx *ctx, uint32_t alpha, unsigned long long host_sc[SC_COUNT])
+int check_alpha(lime_ctx *ctx, uint32_t alpha)
 {
+    if (ctx->lcp8 && ctx->lcp_alpha && alpha != ctx->lcp_alpha)
+        return fail(ctx, LIME_ERR_STATE, "lcp was loaded as the bit lcp < alpha of lime_set_alpha: another alpha needs a reload");
     if (ctx->lcp8 && alpha > 255)
         return fail(ctx, LIME_ERR_STATE, "lcp was loaded narrowed (lime_set_alpha_limit <= 255), alpha > 255 needs a reload");
+    return LIME_OK;
+}
+
+int detect_into_ctx(lime_ctx *ctx, uint32_t alpha, unsigned long long host_sc[SC_COUNT])
+{
+    { const int rc = check_alpha(ctx, alpha); if (rc) return rc; }
     CK(cudaSetDevice(ctx->device), "cudaSetDevice");
     const uint64_t n_total = ctx->n_own + ctx->n_halo;
     const uint64_t tiles = k12_num_tiles(ctx->n_own);

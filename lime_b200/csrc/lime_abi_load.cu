@@ -5,6 +5,10 @@
 // position instead of 4 + 4 (+1): host threads narrow lcp to min(lcp, 255) chunk by chunk into a ring
 // of page-locked stage buffers (host_narrow.cpp) while the previous chunks are on the bus; the bytes stay on
 // the device as they are: the kernels that read lcp (k12_stream.cu, template LCP8) take either width.
+// When the caller has named the alpha itself (lime_set_alpha), one BIT per position crosses instead -- lcp < alpha,
+// packed by the same host threads -- and expand_kernel turns every chunk into the bytes 0 (head) / 255 behind its
+// copy: 1/8 + 4 (+1) bytes per position on the bus; the kernels see an LCP8 array that answers lcp < alpha for
+// that alpha only (the steps check it).
 #include "abi_internal.cuh"
 #include "narrow_loop.h"
 #include <algorithm>
@@ -17,8 +21,30 @@ void load_release(lime_ctx *ctx)
         if (ctx->stage_ev[s]) { cudaEventSynchronize(ctx->stage_ev[s]); cudaEventDestroy(ctx->stage_ev[s]); ctx->stage_ev[s] = nullptr; }
         if (ctx->stage[s]) { cudaFreeHost(ctx->stage[s]); ctx->stage[s] = nullptr; }
     }
-    ctx->in_lcp8.release();
+    ctx->in_lcp8.release(); ctx->in_lcpbits.release();
 }
+
+namespace lime {
+// out[8 i + j] = bit j of bits[i] ? 0 : 255 for the n positions of a chunk: a thread expands two bytes into 16
+__global__ void __launch_bounds__(256) expand_kernel(const uint8_t *__restrict__ bits, uint8_t *__restrict__ out, uint64_t n)
+{
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t p = t * 16;
+    if (p >= n) return;
+    const unsigned b = (unsigned)bits[2 * t] | (p + 8 < n ? (unsigned)bits[2 * t + 1] << 8 : 0xff00u);
+    uint32_t w[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const unsigned nib = (b >> (4 * k)) & 15u;
+        // bit set -> byte 0x00, clear -> 0xff: spread the 4 bits to the low bit of each byte, then 0xff * (1 - bit)
+        const uint32_t spread = (nib & 1u) | ((nib & 2u) << 7) | ((nib & 4u) << 14) | ((nib & 8u) << 21);
+        w[k] = (0x01010101u - spread) * 0xffu;
+    }
+    if (p + 16 <= n) *reinterpret_cast<uint4 *>(out + p) = make_uint4(w[0], w[1], w[2], w[3]);
+    else
+        for (uint64_t e = 0; p + e < n; e++) out[p + e] = (uint8_t)(w[e >> 2] >> (8 * (e & 3)));
+}
+} // namespace lime
 
 namespace {
 
@@ -27,14 +53,24 @@ struct CudaQueue {
     lime_ctx *ctx;
     const uint32_t *da; const uint8_t *ebwt;
     uint8_t *d8;
+    uint8_t *dbits;       // non-null: the stage holds one bit per position; expanded into d8 behind the copy
     int error(cudaError_t e, const char *what) { fail_cuda(ctx, e, what); return e == cudaErrorMemoryAllocation ? LIME_ERR_NOMEM : LIME_ERR_CUDA; }
     int stage_copy(int slot, uint64_t base, uint64_t len)
     {
         ctx->stage_busy = true;
-        cudaError_t e = cudaMemcpyAsync(d8 + base, ctx->stage[slot], len, cudaMemcpyHostToDevice, ctx->stream);
+        cudaError_t e;
+        if (dbits) e = cudaMemcpyAsync(dbits + base / 8, ctx->stage[slot], (len + 7) / 8, cudaMemcpyHostToDevice, ctx->stream);
+        else e = cudaMemcpyAsync(d8 + base, ctx->stage[slot], len, cudaMemcpyHostToDevice, ctx->stream);
         if (e != cudaSuccess) return error(e, "H2D lcp (narrowed)");
         e = cudaEventRecord(ctx->stage_ev[slot], ctx->stream);
         if (e != cudaSuccess) return error(e, "cudaEventRecord");
+        if (dbits) {
+            const uint64_t threads = (len + 15) / 16;
+            ctx->launches++;
+            lime::expand_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, ctx->stream>>>(dbits + base / 8, d8 + base, len);
+            e = cudaGetLastError();
+            if (e != cudaSuccess) return error(e, "expand launch");
+        }
         return 0;
     }
     int slot_state(int slot)
@@ -59,10 +95,11 @@ struct CudaQueue {
 } // namespace
 
 // lcp, da (and ebwt) of n positions: host -> device, lcp narrowed.  The device arrays are reserved by the caller.
-int load_host_narrow(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint8_t *ebwt, uint64_t n)
+int load_host_narrow(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint8_t *ebwt, uint64_t n, uint32_t bits_alpha)
 {
     const uint64_t chunk = LIME_STAGE_CHUNK;
     CK(ctx->in_lcp8.reserve((n + 15) / 16 * 16), "cudaMalloc narrowed lcp");
+    if (bits_alpha) CK(ctx->in_lcpbits.reserve((n + 7) / 8 + 16), "cudaMalloc lcp bits");
     for (int s = 0; s < LIME_STAGE_SLOTS; s++) {
         if (!ctx->stage[s]) CK(cudaHostAlloc((void **)&ctx->stage[s], chunk, cudaHostAllocDefault), "cudaHostAlloc lcp stage");
         if (!ctx->stage_ev[s]) CK(cudaEventCreateWithFlags(&ctx->stage_ev[s], cudaEventDisableTiming), "cudaEventCreate");
@@ -71,13 +108,20 @@ int load_host_narrow(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, con
     ctx->stage_busy = false;
     // the calling thread only queues copies (it yields while it waits): one core is left to it
     const int threads = std::max(1, lime_host_threads() - 1);
-    CudaQueue q{ctx, da, ebwt, ctx->in_lcp8.as<uint8_t>()};
-    return narrow_transfer(q, lcp, n, chunk, threads, LIME_STAGE_SLOTS, ctx->stage);
+    CudaQueue q{ctx, da, ebwt, ctx->in_lcp8.as<uint8_t>(), bits_alpha ? ctx->in_lcpbits.as<uint8_t>() : nullptr};
+    return narrow_transfer(q, lcp, n, chunk, threads, LIME_STAGE_SLOTS, ctx->stage, bits_alpha);
 }
 
 extern "C" int lime_set_alpha_limit(lime_ctx *ctx, uint32_t max_alpha)
 {
     if (!ctx) return LIME_ERR_ARG;
     ctx->alpha_limit = max_alpha;
+    return LIME_OK;
+}
+
+extern "C" int lime_set_alpha(lime_ctx *ctx, uint32_t alpha)
+{
+    if (!ctx) return LIME_ERR_ARG;
+    ctx->alpha_exact = alpha;
     return LIME_OK;
 }

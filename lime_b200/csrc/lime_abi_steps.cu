@@ -49,8 +49,7 @@ int reserve_score_scratch(lime_ctx *ctx)
 // to ctx->d_sim.
 int queue_k12_score(lime_ctx *ctx, uint32_t alpha, bool ebwt, unsigned long long *sc, const FlatOut &flat, int max_ctas_per_sm)
 {
-    if (ctx->lcp8 && alpha > 255)
-        return fail(ctx, LIME_ERR_STATE, "lcp was loaded narrowed (lime_set_alpha_limit <= 255), alpha > 255 needs a reload");
+    { const int rc = check_alpha(ctx, alpha); if (rc) return rc; }
     K12Args a = {};
     a.lcp = ctx->d_lcp; a.lcp8 = ctx->lcp8 ? 1 : 0; a.da = ctx->d_da; a.ebwt = ebwt ? ctx->d_ebwt : nullptr;
     a.n_own = ctx->n_own; a.n_total = ctx->n_own + ctx->n_halo; a.pos_base = ctx->pos_base; a.is_last = ctx->is_last;

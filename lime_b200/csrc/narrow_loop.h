@@ -9,7 +9,10 @@
 namespace lime {
 
 struct NarrowPipe;
-NarrowPipe *narrow_pipe_open(const uint32_t *src, uint64_t n, uint64_t chunk, int threads, int slots, uint8_t *const *stage);
+// bits_alpha = 0: a chunk is staged as the bytes min(lcp, 255); else as one bit per position, lcp < bits_alpha
+// (bit j of byte i = position 8 i + j of the chunk; chunk must be a multiple of 512)
+NarrowPipe *narrow_pipe_open(const uint32_t *src, uint64_t n, uint64_t chunk, int threads, int slots, uint8_t *const *stage,
+                             uint32_t bits_alpha);
 bool narrow_pipe_ready(const NarrowPipe *p, uint64_t c);
 void narrow_pipe_released(NarrowPipe *p, uint64_t k);
 void narrow_pipe_close(NarrowPipe *p);
@@ -22,9 +25,10 @@ void narrow_pipe_close(NarrowPipe *p);
 // Returns 0 or the first error of Q.  On return every chunk has been queued; the last `slots` copies may
 // still be pending (the stage buffers must outlive them).
 template <class Q>
-int narrow_transfer(Q &q, const uint32_t *lcp, uint64_t n, uint64_t chunk, int threads, int slots, uint8_t *const *stage)
+int narrow_transfer(Q &q, const uint32_t *lcp, uint64_t n, uint64_t chunk, int threads, int slots, uint8_t *const *stage,
+                    uint32_t bits_alpha = 0)
 {
-    NarrowPipe *pipe = narrow_pipe_open(lcp, n, chunk, threads, slots, stage);
+    NarrowPipe *pipe = narrow_pipe_open(lcp, n, chunk, threads, slots, stage, bits_alpha);
     struct Closer { NarrowPipe *p; ~Closer() { narrow_pipe_close(p); } } closer{pipe};
     const uint64_t n_chunks = (n + chunk - 1) / chunk;
     uint64_t queued = 0, released = 0;       // chunks whose copy is queued / known to be done

@@ -87,7 +87,6 @@ struct SimAcc {
     uint8_t *sim8; uint64_t pitch8;
     uint32_t *sim32; uint32_t lo, hi, n_refs;
     unsigned int *carry;
-    unsigned long long *sum_t;        // optional: total of t added through the checked path
 };
 
 template <bool EXACT32>
@@ -101,7 +100,6 @@ __device__ __forceinline__ void sim_add(const SimAcc &P, uint32_t r, uint32_t g,
         const unsigned sh = (g & 3u) * 8u;
         const unsigned old = atomicAdd(w, t << sh);
         if (((old >> sh) & 0xffu) + t > 0xffu) *P.carry = 1u;
-        if (P.sum_t) atomicAdd(P.sum_t, (unsigned long long)t);
     }
 }
 

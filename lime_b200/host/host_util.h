@@ -75,13 +75,15 @@ inline int device_from_env()
     return e ? atoi(e) : 0;
 }
 
-// The executables know alpha from their command line before they read a file: they promise it to the library
-// (lime_set_alpha_limit), so that lime_load ships lcp as min(lcp, 255) bytes when alpha <= 255 -- 6 instead of
-// 9 bytes per position over PCIe, identical results.  LIME_NARROW_LCP=0 switches it off.
+// The executables know alpha from their command line before they read a file: they name it to the library
+// (lime_set_alpha), so that lime_load ships lcp as the bit lcp < alpha when alpha <= 255 -- 5.1 instead of
+// 9 bytes per position over PCIe, identical results.  LIME_NARROW_LCP=0 switches it off, LIME_NARROW_LCP=8 ships
+// the bytes min(lcp, 255) instead (lime_set_alpha_limit).
 inline void alpha_limit_from_env(lime_ctx *ctx, uint32_t alpha)
 {
     const char *e = getenv("LIME_NARROW_LCP");
-    if (!e || atoi(e) > 0) lime_set_alpha_limit(ctx, alpha);
+    if (e && atoi(e) == 8) lime_set_alpha_limit(ctx, alpha);
+    else if (!e || atoi(e) > 0) lime_set_alpha(ctx, alpha);
 }
 
 } // namespace limehost

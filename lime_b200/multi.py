@@ -294,8 +294,9 @@ class CarryDetected(RuntimeError):
 
 def xchg_capacities(n_positions, world, density=0.25):
     """Record capacities of an XchgJob for shards of n_positions: the update list of a strand (the bench
-    workload issues 0.11 updates per position) and one inbox region (a source's share for one owner)."""
-    flat_cap = int(n_positions * density) + (1 << 20)
+    workload issues 0.11 updates per position; every warp that appends takes whole blocks of 256 slots, hence
+    the 3 Mi of slack) and one inbox region (a source's share for one owner)."""
+    flat_cap = int(n_positions * density) + (3 << 20)
     inbox_cap = int(flat_cap * 1.5 / world) + (1 << 16)
     return flat_cap, inbox_cap
 

@@ -69,3 +69,44 @@ def test_clamped_lcp_decides_every_head_test_for_alpha_up_to_255():
         assert np.array_equal(lcp < alpha, nar < alpha)
     # and the limit is tight: alpha = 256 is not decided by the byte
     assert not np.array_equal(lcp < 256, nar.astype(np.uint32) < 256)
+
+
+# ---- the bit transfer of lime_set_alpha: bit j of out[i] = lcp[8 i + j] < alpha ---------------------------------
+def _bits(lcp, alpha):
+    pad = np.ones((-lcp.shape[0]) % 8, dtype=bool)            # positions beyond n read as heads
+    return np.packbits(np.concatenate([lcp < alpha, pad]), bitorder="little")
+
+
+@pytest.mark.parametrize("n", [0, 1, 7, 8, 9, 31, 32, 33, 511, 512, 513, 4097, (1 << 20) + 3, 3 * (1 << 20) + 77])
+@pytest.mark.parametrize("threads,alpha", [(1, 16), (3, 1), (8, 255), (2, 256), (5, 0x80000001)])
+def test_pack_plain(n, threads, alpha):
+    lib = _lib.load()
+    lcp = _lcp(n, 5 + n)
+    nb = (n + 7) // 8
+    out = np.full(nb + 8, 0xAB, dtype=np.uint8)
+    assert lib.lime_host_pack_lcp(_ptr(lcp), _ptr(out), n, alpha, threads) == 0
+    assert np.array_equal(out[:nb], _bits(lcp, alpha))
+    assert (out[nb:] == 0xAB).all()
+
+
+@pytest.mark.parametrize("delay_us", [0, 50])
+@pytest.mark.parametrize("n,chunk,threads,slots", [
+    (1, 512, 2, 1), (512, 512, 3, 2), (513, 512, 3, 3), (5000, 512, 5, 3), (100003, 4096, 7, 3),
+    (100003, 4096, 1, 1), (1 << 20, 1 << 16, 4, 2), ((1 << 21) + 11, 1 << 17, 15, 3), (5, 1 << 20, 16, 3)])
+def test_pack_pipelined(n, chunk, threads, slots, delay_us):
+    lib = _lib.load()
+    lcp = _lcp(n, 13 + n)
+    nb = (n + 7) // 8
+    out = np.full(nb + 8, 0xCD, dtype=np.uint8)
+    assert lib.lime_host_pack_lcp_pipelined(_ptr(lcp), _ptr(out), n, chunk, 16, threads, slots, delay_us) == 0
+    assert np.array_equal(out[:nb], _bits(lcp, 16))
+    assert (out[nb:] == 0xCD).all()
+
+
+def test_pack_pipelined_rejects_bad_arguments():
+    lib = _lib.load()
+    lcp = _lcp(10, 1)
+    out = np.zeros(10, dtype=np.uint8)
+    assert lib.lime_host_pack_lcp_pipelined(_ptr(lcp), _ptr(out), 10, 100, 16, 1, 1, 0) != 0     # chunk not a multiple of 512
+    assert lib.lime_host_pack_lcp_pipelined(_ptr(lcp), _ptr(out), 10, 512, 0, 1, 1, 0) != 0       # alpha 0
+    assert lib.lime_host_pack_lcp(None, _ptr(out), 10, 16, 1) != 0

@@ -1,4 +1,4 @@
-"""GPU: lime_set_alpha_limit + lime_load(LIME_MEM_HOST) (lcp crosses PCIe as min(lcp, 255) bytes and stays that
+"""GPU: lime_set_alpha_limit / lime_set_alpha + lime_load(LIME_MEM_HOST) (lcp crosses PCIe as min(lcp, 255) bytes and stays that
 way on the device: the stream kernel's LCP8 variants read the bytes, lime_b200/csrc/lime_abi_load.cu) gives the
 same clusters, similarity matrix and records as the plain load and as the oracle."""
 import numpy as np
@@ -99,3 +99,50 @@ def test_alpha_above_255_is_refused_on_a_narrowed_strand(ctx):
         ctx.cluster_detect(256)
     finally:
         ctx.set_alpha_limit(0)
+
+
+@pytest.mark.parametrize("n", [70_001, 2 * CHUNK + 12_345])
+@pytest.mark.parametrize("ebwt_mode,fused,alpha", [(1, True, 16), (0, False, 12), (1, True, 255), (0, True, 1)])
+def test_bit_load_equals_plain_load(ctx, oracle, n, ebwt_mode, fused, alpha):
+    """lime_set_alpha: lcp crosses as the bit lcp < alpha and is expanded to the bytes 0 / 255 on the device."""
+    case = _big_lcp(C.synth_case("bits", n, max(1000, n // 300), 40, seed=19 + ebwt_mode), max(alpha, 2), 5)
+    ctx.set_alpha(0)
+    plain = _results(ctx, case, alpha, ebwt_mode, fused)
+    ctx.set_alpha(alpha)
+    try:
+        got1 = _results(ctx, case, alpha, ebwt_mode, fused)
+        got2 = _results(ctx, case, alpha, ebwt_mode, fused)         # stage buffers reused
+    finally:
+        ctx.set_alpha(0)
+    cl_o, max_o = oracle.cluster_detect(case["lcp"], case["da"], case["n_reads"], alpha)
+    assert tuple(plain[0]) == (cl_o.shape[0], max_o)
+    for got in (got1, got2):
+        assert tuple(got[0]) == tuple(plain[0])
+        assert np.array_equal(got[1], cl_o)
+        assert np.array_equal(got[2], plain[2])
+        assert got[3:] == plain[3:]
+
+
+def test_another_alpha_is_refused_on_a_bit_loaded_strand(ctx):
+    from lime_b200.api import LimeError
+    case = C.synth_case("bits_refuse", 70_001, 1000, 40, seed=29)
+    ctx.set_alpha(16)
+    try:
+        ctx.load(case["lcp"], case["da"], case["ebwt"], case["n_reads"], case["n_refs"])
+        for other in (15, 17, 300):
+            with pytest.raises(LimeError) as e:
+                ctx.cluster_detect(other)
+            assert e.value.code == -5
+        with pytest.raises(LimeError) as e:
+            ctx.cluster_similarity(12, 1, False)
+        assert e.value.code == -5
+        ctx.cluster_detect(16)
+    finally:
+        ctx.set_alpha(0)
+    # alpha above 255: the load stays plain and any alpha works
+    ctx.set_alpha(1000)
+    try:
+        ctx.load(case["lcp"], case["da"], case["ebwt"], case["n_reads"], case["n_refs"])
+        ctx.cluster_detect(256)
+    finally:
+        ctx.set_alpha(0)
