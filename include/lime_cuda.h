@@ -255,6 +255,34 @@ int  lime_xchg_apply(lime_ctx *ctx, int strand);
 int  lime_xchg_choose(lime_ctx *ctx, int strand, uint32_t norm, float beta, uint32_t n_own_reads);
 int  lime_xchg_status(lime_ctx *ctx, int strand, uint64_t out[8]);
 
+/* ---- clusterChoose without any allocation -------------------------------------------------------------- */
+
+/*
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  It is lime_choose
+ * (clusterChoose, ClusterBWT_DA.cpp:361-450) of all rows of a caller-owned matrix, context-free, on the current
+ * device and the given stream, and it calls no cudaMalloc / cudaFree or other allocating routine: the kernel's
+ * scratch (tile counter, record count, one look-back word per 256 reads) is a static device array of
+ * LIME_CHOOSE_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.
+ *   dev_sim        DEVICE, [n_reads][pitch] uint8, 16-byte aligned, pitch a multiple of 16 and >= n_refs; read only
+ *   dev_bin        DEVICE, bin_cap records: the .res.bin image, record 0 = the sentinel (writes are guarded by bin_cap;
+ *                  1 + n_reads + non-zero cells always suffices)
+ *   dev_pos        DEVICE, n_reads uint64: the .res.pos image
+ *   dev_n_records  DEVICE uint64 or NULL: the record count incl. the sentinel, written in stream order (no
+ *                  synchronisation when n_records is NULL)
+ *   n_records      HOST uint64 or NULL: the same, after a stream synchronisation; then LIME_ERR_NOMEM if it exceeds
+ *                  bin_cap.  One of the two must be given.
+ *   err            optional buffer for the message of a failure (err_len bytes)
+ * n_reads above LIME_CHOOSE_STATIC_MAX_READS is rejected with LIME_ERR_ARG.  All calls share the scratch array, which
+ * keeps the last call's contents: every call first clears the part it uses (in stream order), and calls that overlap
+ * on one GPU (two streams, two threads) race -- serialise them.
+ */
+#define LIME_CHOOSE_STATIC_MAX_READS      16777216ull
+#define LIME_CHOOSE_STATIC_SCRATCH_BYTES  (256ull + (LIME_CHOOSE_STATIC_MAX_READS / 256ull) * 8ull)
+int  lime_choose_static(uint8_t *dev_sim, uint64_t pitch, uint32_t n_reads, uint32_t n_refs, uint32_t norm, float beta,
+                        lime_pair_sim *dev_bin, uint64_t bin_cap, uint64_t *dev_pos, uint64_t *dev_n_records,
+                        uint64_t *n_records, void *stream, char *err, uint64_t err_len);
+
 /* ---- step 3 : Classify.cpp:474-702 -------------------------------------------------------- */
 
 /*

@@ -68,6 +68,8 @@ SIGNATURES = {
     "lime_xchg_apply": (C.c_int, [vp, C.c_int]),
     "lime_xchg_choose": (C.c_int, [vp, C.c_int, C.c_uint32, C.c_float, C.c_uint32]),
     "lime_xchg_status": (C.c_int, [vp, C.c_int, u64p]),
+    "lime_choose_static": (C.c_int, [vp, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_float, vp, C.c_uint64, vp, vp, vp, vp,
+                                     C.c_char_p, C.c_uint64]),
     "lime_strand_run": (C.c_int, [vp, C.c_int, C.c_uint32, C.c_int, C.c_uint32, C.c_float]),
     "lime_strand_status": (C.c_int, [vp, C.c_int, u64p]),
     "lime_launch_count": (C.c_uint64, [vp]),

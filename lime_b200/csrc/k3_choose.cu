@@ -840,3 +840,104 @@ cudaError_t launch_k3_emit(const K3Args &a, cudaStream_t s)
 }
 
 } // namespace lime
+
+// ---- clusterChoose without any allocation (lime_choose_static) ------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch of the single-pass
+// kernels -- the tile counter, the record count and one look-back word per tile of 256 reads -- lives in a
+// file-scope device array, so every GPU that loads the library holds LIME_STATIC_SCRATCH_BYTES until exit.
+// All calls share the array: it keeps the last call's contents (the part a call uses is cleared first, in stream
+// order), and two calls that overlap on one GPU race.
+namespace lime {
+namespace k3 {
+constexpr uint64_t STATIC_MAX_READS = LIME_CHOOSE_STATIC_MAX_READS;
+constexpr uint64_t STATIC_MAX_TILES = (STATIC_MAX_READS + TILE_READS - 1) / TILE_READS;
+constexpr uint64_t STATIC_HEAD = 256;                                   // bytes: [0] tile counter, [8] record count
+constexpr uint64_t STATIC_BYTES = STATIC_HEAD + STATIC_MAX_TILES * 8;   // 512.25 KB
+static __device__ __align__(256) unsigned char g_choose_scratch[STATIC_BYTES];
+constexpr int STATIC_MAX_DEVICES = 64;
+} // namespace k3
+} // namespace lime
+
+static void static_msg(char *err, uint64_t err_len, const char *what, const char *detail = nullptr)
+{
+    if (!err || !err_len) return;
+    snprintf(err, (size_t)err_len, "lime_choose_static: %s%s%s", what, detail ? ": " : "", detail ? detail : "");
+}
+
+extern "C" int lime_choose_static(uint8_t *dev_sim, uint64_t pitch, uint32_t n_reads, uint32_t n_refs, uint32_t norm, float beta,
+                                  lime_pair_sim *dev_bin, uint64_t bin_cap, uint64_t *dev_pos, uint64_t *dev_n_records,
+                                  uint64_t *n_records, void *stream, char *err, uint64_t err_len)
+{
+    using namespace lime;
+    if (err && err_len) err[0] = 0;
+    if (n_reads > k3::STATIC_MAX_READS) {
+        char d[128];
+        snprintf(d, sizeof d, "%u reads exceed the static scratch (LIME_CHOOSE_STATIC_MAX_READS = %llu)", n_reads,
+                 (unsigned long long)k3::STATIC_MAX_READS);
+        static_msg(err, err_len, "size beyond the maximum", d);
+        return LIME_ERR_ARG;
+    }
+    if (!dev_bin || bin_cap < 1 || (n_reads && (!dev_sim || !dev_pos)) || pitch % 16 || pitch < n_refs ||
+        (reinterpret_cast<uintptr_t>(dev_sim) & 15) || (!dev_n_records && !n_records)) {
+        static_msg(err, err_len, "bad argument (device pointers, pitch a multiple of 16 and >= n_refs, 16-byte aligned matrix, "
+                                 "bin_cap >= 1, one of dev_n_records / n_records)");
+        return LIME_ERR_ARG;
+    }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= k3::STATIC_MAX_DEVICES) {
+        static_msg(err, err_len, "cudaGetDevice", e != cudaSuccess ? cudaGetErrorString(e) : "device ordinal out of range");
+        return LIME_ERR_CUDA;
+    }
+    // the array's name is a host-side stand-in here: its device address, once per device, with that device current
+    static unsigned char *scratch_of[k3::STATIC_MAX_DEVICES] = {nullptr};
+    unsigned char *scratch = scratch_of[dev];
+    if (!scratch) {
+        e = cudaGetSymbolAddress(reinterpret_cast<void **>(&scratch), k3::g_choose_scratch);
+        if (e != cudaSuccess || !scratch) {
+            static_msg(err, err_len, "cudaGetSymbolAddress", cudaGetErrorString(e));
+            return LIME_ERR_CUDA;
+        }
+        scratch_of[dev] = scratch;
+    }
+    const uint64_t tiles = k3_num_tiles(n_reads);
+    // what must start at zero: the counters and the look-back words of the tiles this call uses
+    e = cudaMemsetAsync(scratch, 0, k3::STATIC_HEAD + tiles * 8, s);
+    if (e != cudaSuccess) { static_msg(err, err_len, "cudaMemsetAsync", cudaGetErrorString(e)); return LIME_ERR_CUDA; }
+    unsigned long long *d_count = reinterpret_cast<unsigned long long *>(scratch + 8);
+    if (tiles == 0) {
+        // no reads: the sentinel record alone (ClusterBWT_DA.cpp:376-382)
+        e = cudaMemsetAsync(dev_bin, 0, sizeof(lime_pair_sim), s);
+        const unsigned long long one = 1;
+        if (e == cudaSuccess) e = cudaMemcpyAsync(d_count, &one, 8, cudaMemcpyHostToDevice, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);          // `one` is a stack variable
+    } else {
+        K3Args a;
+        a.sim8 = dev_sim; a.pitch8 = pitch; a.n_refs = n_refs;
+        a.read_begin = 0; a.read_end = n_reads; a.norm = norm; a.beta = beta;
+        a.tile_counter = reinterpret_cast<unsigned int *>(scratch);
+        a.n_records = d_count;
+        a.tile_state = reinterpret_cast<unsigned long long *>(scratch + k3::STATIC_HEAD);
+        a.pos = dev_pos; a.bin = dev_bin; a.bin_cap = bin_cap;
+        e = launch_k3_choose(a, s);
+    }
+    if (e != cudaSuccess) { static_msg(err, err_len, "launch", cudaGetErrorString(e)); return LIME_ERR_CUDA; }
+    if (dev_n_records) {
+        e = cudaMemcpyAsync(dev_n_records, d_count, 8, cudaMemcpyDeviceToDevice, s);
+        if (e != cudaSuccess) { static_msg(err, err_len, "copy of the record count", cudaGetErrorString(e)); return LIME_ERR_CUDA; }
+    }
+    if (n_records) {
+        unsigned long long total = 0;
+        e = cudaMemcpyAsync(&total, d_count, 8, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) { static_msg(err, err_len, "read-back of the record count", cudaGetErrorString(e)); return LIME_ERR_CUDA; }
+        *n_records = total;
+        if (total > bin_cap) {
+            static_msg(err, err_len, "dev_bin is too small for the records of this matrix (nothing was written past bin_cap)");
+            return LIME_ERR_NOMEM;
+        }
+    }
+    return LIME_OK;
+}
