@@ -563,12 +563,14 @@ def run_ours(args, w):
             # the drop-in executables know alpha from argv and name it (lime_set_alpha): lcp crosses PCIe as the bit
             # lcp < alpha, packed on host threads inside the timed region, expanded to bytes on the device
             workers = max(1, ctx.lib.lime_host_threads() - 1)
+            da3 = w["n_reads"] + w["n_refs"] <= (1 << 24) and os.environ.get("LIME_PACK_DA", "1") != "0"
             ctx.set_alpha(w["alpha"])
             try:
                 modes["lcp_bits"] = time_host(
                     "lime_set_alpha(alpha) + lime_load(LIME_MEM_HOST) per strand from pinned host arrays: lcp packed to one bit "
                     "per position (lcp < alpha) by %d host threads inside the timed region; assignments copied back; PCIe-bound"
-                    % workers, host_bytes - 4 * symbols + sum((sd["n"] + 7) // 8 for sd in strands_dev) + 4 * w["n_refs"])
+                    % workers + ("; da as 3 bytes per position" if da3 else ""),
+                    host_bytes - (5 if da3 else 4) * symbols + sum((sd["n"] + 7) // 8 for sd in strands_dev) + 4 * w["n_refs"])
             finally:
                 ctx.set_alpha(0)
             # the weaker promise alpha <= 255 (lime_set_alpha_limit): min(lcp, 255) as bytes
@@ -891,7 +893,8 @@ def run_ours_multi(args, w, world, rank, local):
             dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
             e_ms = float(e_ms.item()) / e2e_steps
             narrow = w["alpha"] <= 255 and not args.no_narrow
-            h2d = sum((4 + w["ebwt"]) * (hs["n_own"] + hs["n_halo"]) + ((hs["n_own"] + hs["n_halo"] + 7) // 8 if narrow else 4 * (hs["n_own"] + hs["n_halo"]))
+            da_b = 3 if narrow and n_reads + w["n_refs"] <= (1 << 24) and os.environ.get("LIME_PACK_DA", "1") != "0" else 4
+            h2d = sum((da_b + w["ebwt"]) * (hs["n_own"] + hs["n_halo"]) + ((hs["n_own"] + hs["n_halo"] + 7) // 8 if narrow else 4 * (hs["n_own"] + hs["n_halo"]))
                       for hs in host_shards)
             h2d_t = torch.tensor([h2d], device=dev, dtype=torch.int64)
             dist.all_reduce(h2d_t)
@@ -901,7 +904,7 @@ def run_ours_multi(args, w, world, rank, local):
                        "ms_per_step": e_ms, "steps": e2e_steps, "reads_per_s": n_reads / (e_ms * 1e-3),
                        "h2d_GBps_per_gpu": int(h2d_t.item()) / world / (e_ms * 1e-3) / 1e9,
                        "note": "every rank: lime_load(LIME_MEM_HOST) of its shard of each strand from page-locked host arrays"
-                               + (" (lcp packed to the bit lcp < alpha by host threads inside the timed region)" if narrow else "")
+                               + (" (lcp packed to the bit lcp < alpha%s by host threads inside the timed region)" % (", da to 3 bytes per position" if da_b == 3 else "") if narrow else "")
                                + " + its assignments copied back; max over ranks; results equal to the resident step"}
             else:
                 e2e = {"error": "host-buffer step disagrees with the resident step"}

@@ -102,7 +102,10 @@ int  lime_set_alpha_limit(lime_ctx *ctx, uint32_t max_alpha);
  * the same host threads, bit j of byte i = position 8 i + j -- i.e. 1/8 + 4 (+1) bytes per position, and expands
  * each chunk on the device into the bytes 0 (lcp < alpha) / 255 the kernels read.  Results are identical for that
  * alpha; a step called with another alpha on a strand loaded that way fails with LIME_ERR_STATE.  0 = off (default);
- * it takes precedence over lime_set_alpha_limit.
+ * it takes precedence over lime_set_alpha_limit.  In this mode da crosses as 3 bytes per position while every document
+ * id fits (n_reads + n_refs <= 2^24; packed by the same host threads, expanded on the device into the uint32 array the
+ * kernels read): 1/8 + 3 (+1) bytes per position in all.  The ids of the array must then be below n_reads + n_refs, as
+ * the file format demands (Tools.h:48); the environment variable LIME_PACK_DA=0 leaves da as it is.
  */
 int  lime_set_alpha(lime_ctx *ctx, uint32_t alpha);
 /* The host half on its own (no CUDA): out[i] = min(lcp[i], 255) with `threads` host threads (<= 0:
@@ -118,6 +121,11 @@ int  lime_host_narrow_lcp_pipelined(const uint32_t *lcp, uint8_t *out, uint64_t 
 int  lime_host_pack_lcp(const uint32_t *lcp, uint8_t *out, uint64_t n, uint32_t alpha, int threads);
 int  lime_host_pack_lcp_pipelined(const uint32_t *lcp, uint8_t *out, uint64_t n, uint64_t chunk, uint32_t alpha,
                                   int threads, int slots, int copy_delay_us);
+/* da as 3 bytes per position (out = 3 n bytes, little endian), alone and through the same chunk loop together with
+ * the lcp bits. */
+int  lime_host_pack_da3(const uint32_t *da, uint8_t *out, uint64_t n);
+int  lime_host_pack_lcp_da3_pipelined(const uint32_t *lcp, const uint32_t *da, uint8_t *out_bits, uint8_t *out_da3, uint64_t n,
+                                      uint64_t chunk, uint32_t alpha, int threads, int slots, int copy_delay_us);
 
 /* ---- step 1 : ClusterLCP.cpp:139-283 ------------------------------------------------------ */
 

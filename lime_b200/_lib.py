@@ -42,6 +42,8 @@ SIGNATURES = {
     "lime_set_alpha_limit": (C.c_int, [vp, C.c_uint32]),
     "lime_set_alpha": (C.c_int, [vp, C.c_uint32]),
     "lime_host_pack_lcp": (C.c_int, [vp, vp, C.c_uint64, C.c_uint32, C.c_int]),
+    "lime_host_pack_da3": (C.c_int, [vp, vp, C.c_uint64]),
+    "lime_host_pack_lcp_da3_pipelined": (C.c_int, [vp, vp, vp, vp, C.c_uint64, C.c_uint64, C.c_uint32, C.c_int, C.c_int, C.c_int]),
     "lime_host_pack_lcp_pipelined": (C.c_int, [vp, vp, C.c_uint64, C.c_uint64, C.c_uint32, C.c_int, C.c_int, C.c_int]),
     "lime_host_threads": (C.c_int, []),
     "lime_host_narrow_lcp": (C.c_int, [vp, vp, C.c_uint64, C.c_int]),

@@ -66,7 +66,7 @@ void xchg_release(lime_ctx *ctx);
 int xchg_join(lime_ctx *ctx);
 int strand_readback(lime_ctx *ctx, int slot);
 // lime_abi_load.cu
-int load_host_narrow(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint8_t *ebwt, uint64_t n, uint32_t bits_alpha);
+int load_host_narrow(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint8_t *ebwt, uint64_t n, uint32_t bits_alpha, bool da3);
 // LIME_ERR_STATE when the resident lcp cannot answer lcp < alpha (narrowed to bytes and alpha > 255, or packed for another alpha)
 int check_alpha(lime_ctx *ctx, uint32_t alpha);
 void load_release(lime_ctx *ctx);

@@ -195,7 +195,9 @@ struct lime_ctx {
     // lime_set_alpha: the caller names the alpha itself; a host load then ships the bit lcp < alpha and leaves the
     // bytes 0 / 255 in in_lcp8; lcp_alpha = the alpha the resident lcp answers for (0: any alpha <= 255, or u32)
     uint32_t alpha_exact = 0, lcp_alpha = 0;
-    lime::DevBuf in_lcpbits;
+    lime::DevBuf in_lcpbits, in_da3;
+    uint64_t stage_bytes = 0;               // size of each page-locked stage buffer
+    bool da3_loaded = false;                // the last host load shipped da as 3 bytes per position
     uint8_t *stage[lime::LIME_STAGE_SLOTS] = {nullptr};
     cudaEvent_t stage_ev[lime::LIME_STAGE_SLOTS] = {nullptr};
     bool stage_busy = false;

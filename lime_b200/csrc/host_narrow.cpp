@@ -62,6 +62,35 @@ void pack_range(const uint32_t *src, uint8_t *dst, uint64_t n, uint32_t alpha)
     if (avx2) pack_range_avx2(src, dst, n, alpha); else pack_range_scalar(src, dst, n, alpha);
 }
 
+// dst[3 i .. 3 i + 2] = the low three bytes of src[i] (document ids below 2^24), little endian
+void pack3_scalar(const uint32_t *src, uint8_t *dst, uint64_t n)
+{
+    for (uint64_t i = 0; i < n; i++) {
+        const uint32_t v = src[i];
+        dst[3 * i] = (uint8_t)v; dst[3 * i + 1] = (uint8_t)(v >> 8); dst[3 * i + 2] = (uint8_t)(v >> 16);
+    }
+}
+__attribute__((target("avx2")))
+void pack3_avx2(const uint32_t *src, uint8_t *dst, uint64_t n)
+{
+    const __m256i sh = _mm256_setr_epi8(0, 1, 2, 4, 5, 6, 8, 9, 10, 12, 13, 14, -1, -1, -1, -1,
+                                        0, 1, 2, 4, 5, 6, 8, 9, 10, 12, 13, 14, -1, -1, -1, -1);
+    uint64_t i = 0;
+    // a round stores 2 x 16 bytes for 24: the 4 bytes of slack fall on positions this call writes afterwards, so
+    // the last 8 .. 15 positions are left to the scalar loop and nothing is written beyond 3 n
+    for (; i + 16 <= n; i += 8) {
+        const __m256i v = _mm256_shuffle_epi8(_mm256_loadu_si256(reinterpret_cast<const __m256i *>(src + i)), sh);
+        _mm_storeu_si128(reinterpret_cast<__m128i *>(dst + 3 * i), _mm256_castsi256_si128(v));
+        _mm_storeu_si128(reinterpret_cast<__m128i *>(dst + 3 * i + 12), _mm256_extracti128_si256(v, 1));
+    }
+    pack3_scalar(src + i, dst + 3 * i, n - i);
+}
+void pack3(const uint32_t *src, uint8_t *dst, uint64_t n)
+{
+    static const bool avx2 = __builtin_cpu_supports("avx2");
+    if (avx2) pack3_avx2(src, dst, n); else pack3_scalar(src, dst, n);
+}
+
 } // namespace
 
 extern "C" int lime_host_threads(void)
@@ -118,13 +147,15 @@ struct NarrowPipe {
     int threads = 0, slots = 0;
     uint8_t *const *stage = nullptr;                 // [slots] buffers of `chunk` bytes (bits: chunk / 8)
     uint32_t bits_alpha = 0;                         // 0: bytes min(lcp, 255); else one bit lcp < bits_alpha
+    const uint32_t *da3 = nullptr;                   // non-null: da of the chunk as 3 bytes per position at stage + chunk
     std::vector<std::atomic<int>> done;              // per chunk: workers that finished their slice
     std::atomic<uint64_t> free_upto{0};              // chunks < free_upto own a free slot
     std::vector<std::thread> pool;
 
-    NarrowPipe(const uint32_t *src_, uint64_t n_, uint64_t chunk_, int threads_, int slots_, uint8_t *const *stage_, uint32_t bits_alpha_)
+    NarrowPipe(const uint32_t *src_, uint64_t n_, uint64_t chunk_, int threads_, int slots_, uint8_t *const *stage_, uint32_t bits_alpha_,
+               const uint32_t *da3_)
         : src(src_), n(n_), chunk(chunk_), n_chunks((n_ + chunk_ - 1) / chunk_), threads(threads_), slots(slots_),
-          stage(stage_), bits_alpha(bits_alpha_), done((n_ + chunk_ - 1) / chunk_)
+          stage(stage_), bits_alpha(bits_alpha_), da3(da3_), done((n_ + chunk_ - 1) / chunk_)
     {
         for (auto &d : done) d.store(0, std::memory_order_relaxed);
         free_upto.store((uint64_t)slots, std::memory_order_release);
@@ -147,6 +178,7 @@ struct NarrowPipe {
             if (b > a) {
                 if (bits_alpha) pack_range(src + base + a, stage[c % slots] + (a >> 3), b - a, bits_alpha);
                 else narrow_range(src + base + a, stage[c % slots] + a, b - a);
+                if (da3) pack3(da3 + base + a, stage[c % slots] + chunk + 3 * a, b - a);
             }
             done[c].fetch_add(1, std::memory_order_release);
         }
@@ -157,9 +189,9 @@ struct NarrowPipe {
 };
 
 NarrowPipe *narrow_pipe_open(const uint32_t *src, uint64_t n, uint64_t chunk, int threads, int slots, uint8_t *const *stage,
-                             uint32_t bits_alpha)
+                             uint32_t bits_alpha, const uint32_t *da3)
 {
-    return new NarrowPipe(src, n, chunk, threads, slots, stage, bits_alpha);
+    return new NarrowPipe(src, n, chunk, threads, slots, stage, bits_alpha, da3);
 }
 bool narrow_pipe_ready(const NarrowPipe *p, uint64_t c) { return p->ready(c); }
 void narrow_pipe_released(NarrowPipe *p, uint64_t k) { p->released(k); }
@@ -175,6 +207,7 @@ namespace {
 struct SimQueue {
     struct Job { int slot; uint64_t base, len, seq; };
     uint8_t *out; uint8_t *const *stage; int delay_us; bool bits;
+    uint8_t *out_da3 = nullptr; uint64_t chunk = 0;
     std::mutex mu; std::deque<Job> jobs; bool stop = false;
     std::atomic<uint64_t> recorded[8], completed[8];
     std::thread worker;
@@ -201,6 +234,7 @@ struct SimQueue {
             if (delay_us > 0) std::this_thread::sleep_for(std::chrono::microseconds(delay_us));
             if (bits) std::copy(stage[j.slot], stage[j.slot] + (j.len + 7) / 8, out + j.base / 8);
             else std::copy(stage[j.slot], stage[j.slot] + j.len, out + j.base);
+            if (out_da3) std::copy(stage[j.slot] + chunk, stage[j.slot] + chunk + 3 * j.len, out_da3 + 3 * j.base);
             completed[j.slot].store(j.seq, std::memory_order_release);
         }
     }
@@ -229,19 +263,21 @@ struct SimQueue {
 } // namespace
 
 static int pipelined(const uint32_t *lcp, uint8_t *out, uint64_t n, uint64_t chunk, int threads, int slots, int copy_delay_us,
-                     uint32_t bits_alpha)
+                     uint32_t bits_alpha, const uint32_t *da = nullptr, uint8_t *out_da3 = nullptr)
 {
+    if ((da != nullptr) != (out_da3 != nullptr)) return LIME_ERR_ARG;
     if ((!lcp || !out) && n) return LIME_ERR_ARG;
     if (chunk == 0 || slots < 1 || slots > 8 || (bits_alpha && chunk % 512)) return LIME_ERR_ARG;
     if (threads <= 0) threads = lime_host_threads();
     if (n == 0) return LIME_OK;
-    std::vector<std::vector<uint8_t>> bufs(slots, std::vector<uint8_t>(chunk));
+    std::vector<std::vector<uint8_t>> bufs(slots, std::vector<uint8_t>(da ? 4 * chunk : chunk));
     std::vector<uint8_t *> stage;
     for (auto &b : bufs) stage.push_back(b.data());
     int rc;
     {
         SimQueue q(out, stage.data(), copy_delay_us, bits_alpha != 0);
-        rc = lime::narrow_transfer(q, lcp, n, chunk, threads, slots, stage.data(), bits_alpha);
+        q.out_da3 = out_da3; q.chunk = chunk;
+        rc = lime::narrow_transfer(q, lcp, n, chunk, threads, slots, stage.data(), bits_alpha, da);
         q.drain();
     }                                                      // joins the worker: every queued copy has run
     return rc ? LIME_ERR_CUDA : LIME_OK;
@@ -258,4 +294,18 @@ extern "C" int lime_host_pack_lcp_pipelined(const uint32_t *lcp, uint8_t *out, u
 {
     if (alpha == 0) return LIME_ERR_ARG;
     return pipelined(lcp, out, n, chunk, threads, slots, copy_delay_us, alpha);
+}
+
+extern "C" int lime_host_pack_da3(const uint32_t *da, uint8_t *out, uint64_t n)
+{
+    if ((!da || !out) && n) return LIME_ERR_ARG;
+    pack3(da, out, n);
+    return LIME_OK;
+}
+
+extern "C" int lime_host_pack_lcp_da3_pipelined(const uint32_t *lcp, const uint32_t *da, uint8_t *out_bits, uint8_t *out_da3, uint64_t n,
+                                                uint64_t chunk, uint32_t alpha, int threads, int slots, int copy_delay_us)
+{
+    if (alpha == 0 || ((!da || !out_da3) && n)) return LIME_ERR_ARG;
+    return pipelined(lcp, out_bits, n, chunk, threads, slots, copy_delay_us, alpha, da, out_da3);
 }

@@ -112,7 +112,11 @@ int lime_load(lime_ctx *ctx, const uint32_t *lcp, const uint32_t *da, const uint
         CK(ctx->in_da.reserve(std::max<uint64_t>(n, 4) * 4), "cudaMalloc da");
         if (ebwt) CK(ctx->in_ebwt.reserve(std::max<uint64_t>(n, 16)), "cudaMalloc ebwt");
         if (narrow) {
-            const int rc = load_host_narrow(ctx, lcp, da, ebwt, n, bits_alpha);
+            // with a named alpha da crosses as 3 bytes per position while every document id fits (LIME_PACK_DA=0: as it is)
+            static const bool pack_da = !(getenv("LIME_PACK_DA") && atoi(getenv("LIME_PACK_DA")) == 0);
+            const bool da3 = bits_alpha && pack_da && (uint64_t)n_reads + n_refs <= (1ull << 24);
+            ctx->da3_loaded = da3;
+            const int rc = load_host_narrow(ctx, lcp, da, ebwt, n, bits_alpha, da3);
             if (rc != LIME_OK) return rc;
         } else if (n) {
             if (lcp) CK(cudaMemcpyAsync(ctx->in_lcp.p, lcp, n * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D lcp");

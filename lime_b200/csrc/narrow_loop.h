@@ -11,8 +11,10 @@ namespace lime {
 struct NarrowPipe;
 // bits_alpha = 0: a chunk is staged as the bytes min(lcp, 255); else as one bit per position, lcp < bits_alpha
 // (bit j of byte i = position 8 i + j of the chunk; chunk must be a multiple of 512)
+// da3 non-null: the workers also stage da of the chunk as 3 bytes per position (ids below 2^24) at stage + chunk
+// (a stage buffer then holds 4 * chunk bytes)
 NarrowPipe *narrow_pipe_open(const uint32_t *src, uint64_t n, uint64_t chunk, int threads, int slots, uint8_t *const *stage,
-                             uint32_t bits_alpha);
+                             uint32_t bits_alpha, const uint32_t *da3);
 bool narrow_pipe_ready(const NarrowPipe *p, uint64_t c);
 void narrow_pipe_released(NarrowPipe *p, uint64_t k);
 void narrow_pipe_close(NarrowPipe *p);
@@ -26,9 +28,9 @@ void narrow_pipe_close(NarrowPipe *p);
 // still be pending (the stage buffers must outlive them).
 template <class Q>
 int narrow_transfer(Q &q, const uint32_t *lcp, uint64_t n, uint64_t chunk, int threads, int slots, uint8_t *const *stage,
-                    uint32_t bits_alpha = 0)
+                    uint32_t bits_alpha = 0, const uint32_t *da3 = nullptr)
 {
-    NarrowPipe *pipe = narrow_pipe_open(lcp, n, chunk, threads, slots, stage, bits_alpha);
+    NarrowPipe *pipe = narrow_pipe_open(lcp, n, chunk, threads, slots, stage, bits_alpha, da3);
     struct Closer { NarrowPipe *p; ~Closer() { narrow_pipe_close(p); } } closer{pipe};
     const uint64_t n_chunks = (n + chunk - 1) / chunk;
     uint64_t queued = 0, released = 0;       // chunks whose copy is queued / known to be done

@@ -110,3 +110,36 @@ def test_pack_pipelined_rejects_bad_arguments():
     assert lib.lime_host_pack_lcp_pipelined(_ptr(lcp), _ptr(out), 10, 100, 16, 1, 1, 0) != 0     # chunk not a multiple of 512
     assert lib.lime_host_pack_lcp_pipelined(_ptr(lcp), _ptr(out), 10, 512, 0, 1, 1, 0) != 0       # alpha 0
     assert lib.lime_host_pack_lcp(None, _ptr(out), 10, 16, 1) != 0
+
+
+# ---- da as 3 bytes per position (document ids below 2^24) ------------------------------------------------------------
+def _da3(da):
+    return da.astype("<u4").view(np.uint8).reshape(-1, 4)[:, :3].reshape(-1)
+
+
+@pytest.mark.parametrize("n", [0, 1, 7, 8, 9, 15, 16, 17, 31, 33, 4097, (1 << 20) + 3])
+def test_pack_da3_plain(n):
+    lib = _lib.load()
+    da = np.random.default_rng(n).integers(0, 1 << 24, n, dtype=np.uint32)
+    if n:
+        da[0], da[-1] = 0xFFFFFF, 0xABCDEF
+    out = np.full(3 * n + 8, 0xAB, dtype=np.uint8)
+    assert lib.lime_host_pack_da3(_ptr(da), _ptr(out), n) == 0
+    assert np.array_equal(out[:3 * n], _da3(da))
+    assert (out[3 * n:] == 0xAB).all()           # nothing written past the end (the vector loop stores 16 for 12)
+
+
+@pytest.mark.parametrize("delay_us", [0, 50])
+@pytest.mark.parametrize("n,chunk,threads,slots", [
+    (1, 512, 2, 1), (513, 512, 3, 3), (5000, 512, 5, 3), (100003, 4096, 7, 3), ((1 << 21) + 11, 1 << 17, 15, 3), (5, 1 << 20, 16, 3)])
+def test_pack_lcp_bits_and_da3_pipelined(n, chunk, threads, slots, delay_us):
+    """Both halves of a stage slot (lcp bits, da as 3 bytes) through the loop lime_load runs."""
+    lib = _lib.load()
+    lcp = _lcp(n, 17 + n)
+    da = np.random.default_rng(n + 1).integers(0, 1 << 24, n, dtype=np.uint32)
+    nb = (n + 7) // 8
+    out = np.full(nb + 8, 0xCD, dtype=np.uint8)
+    out3 = np.full(3 * n + 8, 0xEF, dtype=np.uint8)
+    assert lib.lime_host_pack_lcp_da3_pipelined(_ptr(lcp), _ptr(da), _ptr(out), _ptr(out3), n, chunk, 16, threads, slots, delay_us) == 0
+    assert np.array_equal(out[:nb], _bits(lcp, 16)) and (out[nb:] == 0xCD).all()
+    assert np.array_equal(out3[:3 * n], _da3(da)) and (out3[3 * n:] == 0xEF).all()

@@ -146,3 +146,26 @@ def test_another_alpha_is_refused_on_a_bit_loaded_strand(ctx):
         ctx.cluster_detect(256)
     finally:
         ctx.set_alpha(0)
+
+
+def test_bit_load_keeps_da_whole_when_ids_need_more_than_three_bytes(ctx):
+    """n_reads + n_refs > 2^24: lcp still crosses as bits, da as it is (ids up to 2^24 + 4 in the array)."""
+    n, n_reads, n_refs = 200_003, (1 << 24) - 2, 7
+    rng = np.random.default_rng(31)
+    case = C.synth_case("bits_wide_ids", n, 5000, n_refs, seed=31)
+    da = case["da"].copy()
+    genome = da >= 5000
+    da[genome] = da[genome] - 5000 + n_reads                       # genomes sit above 2^24 - 2
+    reads = np.flatnonzero(~genome)
+    da[reads[::3]] = rng.integers(1 << 23, n_reads, reads[::3].size).astype(np.uint32)
+    wide = dict(case, da=da, n_reads=n_reads)
+    ctx.set_alpha(0)
+    plain = _results(ctx, wide, 16, 1, True)
+    ctx.set_alpha(16)
+    try:
+        got = _results(ctx, wide, 16, 1, True)
+    finally:
+        ctx.set_alpha(0)
+    assert tuple(got[0]) == tuple(plain[0]) and np.array_equal(got[1], plain[1])
+    assert np.array_equal(got[2], plain[2]) and got[3:] == plain[3:]
+    assert plain[0][0] > 0 and plain[2].any()                        # clusters were found and scored
