@@ -469,15 +469,64 @@ def run_ours(args, w):
     launches = ctx.launch_count() - l0
     prof = ctx.prof()
     ctx.prof_enable(False)
-    # the same steps again without the per-launch events of the kernel profile (they cost host time)
+    # The reported K steps: no per-launch events, and two jobs in flight -- a second context on its own stream, the strands
+    # of job k + 1 are queued (lime_load of borrowed device arrays + lime_strand_run never wait) before the host waits for
+    # job k's assignments, so the result copy and the host's gaps of job k run beside the scoring of job k + 1.
+    # LIME_BENCH_INFLIGHT=1: one job at a time.
+    inflight = 1
+    ctx2 = None
+    if not args.unfused and os.environ.get("LIME_BENCH_INFLIGHT", "2") != "1":
+        ctx2 = LimeContext(local)
+        stream2 = torch.cuda.Stream()
+        ctx2.set_stream(stream2.cuda_stream)
+        out2, stats2 = run_job(ctx2, strands_dev, w["n_reads"], w["n_refs"], w["read_len"], w["alpha"], w["beta"], w["ebwt"],
+                               v, m, w["tax_rank"], w["higher"], mem=MEM_DEVICE, fused=True)
+        assert all(a.tobytes() == np.asarray(b).tobytes() for a, b in zip(out, out2)), "second context disagrees"
+        assert [tuple(int(y) for y in x) for x in stats2] == stats
+        inflight = 2
+
+    def steps_resident(k_steps):
+        if inflight == 1:
+            for _ in range(k_steps):
+                step_resident()
+            return
+        from lime_b200.pipeline import norm_of
+        from lime_b200.api import LimeError
+        pair, prev = (ctx, ctx2), None
+        try:
+            for k in range(k_steps):
+                c = pair[k % 2]
+                for s_, st in enumerate(strands_dev):
+                    c.load(st["lcp"], st["da"], st["ebwt"] if w["ebwt"] else None, w["n_reads"], w["n_refs"], mem=MEM_DEVICE, n_total=st["n"])
+                    c.strand_run(s_, w["alpha"], w["ebwt"], norm_of(w["read_len"], w["alpha"]), w["beta"])
+                if prev is not None:
+                    prev.classify(w["n_strands"], w["n_refs"], v, m, w["tax_rank"], w["higher"])
+                prev = c
+            prev.classify(w["n_strands"], w["n_refs"], v, m, w["tax_rank"], w["higher"])
+        except LimeError:
+            # a strand that must be redone exactly (not expected on this workload): one job at a time from here on
+            torch.cuda.synchronize()
+            for _ in range(k_steps):
+                step_resident()
+
+    steps_resident(4)
+    ev_b = torch.cuda.Event()
     torch.cuda.synchronize()
     ev0.record(stream)
-    for _ in range(args.steps):
-        step_resident()
+    steps_resident(args.steps)
+    if ctx2 is not None:
+        ev_b.record(stream2)
+        stream.wait_event(ev_b)
     ev1.record(stream)
     torch.cuda.synchronize()
     ms_plain = ev0.elapsed_time(ev1)
-    t1x = _extend_for_clocks(lambda: (step_resident(), torch.cuda.synchronize()), t0)
+    t1x = _extend_for_clocks(lambda: (steps_resident(2), torch.cuda.synchronize()), t0)
+    if ctx2 is not None:
+        ctx2.close()
+        ctx2 = None
+        inflight_used, inflight = 2, 1
+    else:
+        inflight_used = 1
     clk = clocks.summary(t0, t1x)
     clk["window"] = "timed region + untimed repeats of the same step up to 0.7 s (nvidia-smi -lms 50)"
 
@@ -600,7 +649,7 @@ def run_ours(args, w):
         "data": "synthetic",
         "config": {"workload": w["name"], "config": args.config, "alpha": w["alpha"],
                    "l2": "inputs (%.1f GB per strand) are larger than L2; no flush needed" % ((8 + w["ebwt"]) * n_pos / 1e9),
-                   "parallelism": "1 GPU", "symbols_per_step": symbols, "reads_per_step": w["n_reads"],
+                   "parallelism": "1 GPU, %d job(s) in flight" % inflight_used, "symbols_per_step": symbols, "reads_per_step": w["n_reads"],
                    "strand_stats": strand_stats, "assignments": kinds},
         "reads_per_s": w["n_reads"] / (ms_step * 1e-3),
         "parity": parity,
@@ -757,6 +806,16 @@ def run_ours_multi(args, w, world, rank, local):
         return multi.XchgJob(dist, torch, be, rank, world, n_reads, w["n_refs"], w["n_strands"], flat_cap, inbox_cap)
     job = make_job(density)
     route = {"name": "xchg" if mode != "exchange" else "exchange"}
+    # Two jobs in flight (record exchange only): a second context with its own slabs, lists, inboxes and side stream, so
+    # that the scoring of job k + 1 is queued before the host waits for job k -- the routing / applying / clusterChoose of
+    # job k's last strand then run beside it.  LIME_BENCH_INFLIGHT=1: one job at a time.
+    ctx2 = job2 = None
+    if mode != "exchange" and os.environ.get("LIME_BENCH_INFLIGHT", "2") != "1":
+        ctx2 = LimeContext(local)
+        ctx2.set_stream(stream.cuda_stream)
+        be2 = multi.CudaBackend(ctx2, torch, dev)
+        flat_cap, inbox_cap = multi.xchg_capacities(S_local + HALO, world, density)
+        job2 = multi.XchgJob(dist, torch, be2, rank, world, n_reads, w["n_refs"], w["n_strands"], flat_cap, inbox_cap)
 
     def step(src=None):
         nonlocal job
@@ -779,8 +838,45 @@ def run_ours_multi(args, w, world, rank, local):
                     route["name"] = "exchange (fallback: %s)" % e
         raise SystemExit("bench.py: no route completed the job")
 
+    def steps(k_steps, src=None):
+        """k_steps whole jobs; with a second context two of them are in flight."""
+        nonlocal job2
+        out = None
+        if job2 is None or job2.closed or getattr(job, "closed", True):
+            for _ in range(k_steps):
+                out = step(src)
+            return out
+        pair, prev = (job, job2), None
+        try:
+            for k in range(k_steps):
+                j = pair[k % 2]
+                j.begin()
+                for s_, sh in enumerate(src or shards):
+                    j.run_strand(s_, sh, w["alpha"], w["beta"], w["ebwt"], w["read_len"])     # queues, never waits
+                if prev is not None:
+                    out = prev.finish(v, m, w["tax_rank"], w["higher"], gather=False)
+                prev = j
+            return prev.finish(v, m, w["tax_rank"], w["higher"], gather=False)
+        except multi.CarryDetected as e:
+            # not expected on this workload: back to one job at a time (step() then takes the exact route)
+            torch.cuda.synchronize()
+            job2.close()
+            route["inflight_fallback"] = str(e)
+            for _ in range(k_steps):
+                out = step(src)
+            return out
+
     for _ in range(max(args.warmup, 3)):
         out = step()
+    if job2 is not None:
+        out_a = tuple(np.array(x, copy=True) for x in out)
+        out_b = steps(2)                                     # the second job of the pair ran on the second context
+        same2 = torch.tensor([int(all(a.tobytes() == np.asarray(b).tobytes() for a, b in zip(out_a, out_b)))], device=dev, dtype=torch.int64)
+        dist.all_reduce(same2, op=dist.ReduceOp.MIN)
+        if int(same2.item()) != 1:
+            raise SystemExit("bench.py: the second context's job differs from the first one's")
+        steps(2)
+    route["jobs_in_flight"] = 2 if job2 is not None and not job2.closed else 1
     cnt = torch.tensor([int((np.asarray(out[0]) == ord(c)).sum()) for c in "CUAH"], device=dev, dtype=torch.int64)
     dist.all_reduce(cnt)
     kinds = {c: int(x) for c, x in zip("CUAH", cnt.tolist()) if x}
@@ -790,25 +886,30 @@ def run_ours_multi(args, w, world, rank, local):
     if rank == 0:
         clocks.start()
         time.sleep(0.3)
-    ctx.prof_enable(True); ctx.prof_reset()
-    l0 = ctx.launch_count()
+    ctxs = [ctx] + ([ctx2] if ctx2 is not None else [])
+    for c in ctxs:
+        c.prof_enable(True); c.prof_reset()
+    l0 = sum(c.launch_count() for c in ctxs)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     dist.barrier(); torch.cuda.synchronize()
     t0 = time.time()
     ev0.record(stream)
-    for _ in range(args.steps):
-        step()
+    steps(args.steps)
     ev1.record(stream)
     dist.barrier(); torch.cuda.synchronize()
     ms_prof = ev0.elapsed_time(ev1)
-    launches = torch.tensor([ctx.launch_count() - l0], device=dev, dtype=torch.int64)
+    launches = torch.tensor([sum(c.launch_count() for c in ctxs) - l0], device=dev, dtype=torch.int64)
     dist.all_reduce(launches, op=dist.ReduceOp.SUM)
-    prof = ctx.prof(); ctx.prof_enable(False)
+    prof = {}
+    for c in ctxs:
+        for k_, x in c.prof().items():
+            y = prof.setdefault(k_, {"ms": 0.0, "launches": 0})
+            y["ms"] += x["ms"]; y["launches"] += x["launches"]
+        c.prof_enable(False)
     # the same K steps without the per-launch events of the kernel profile
     dist.barrier(); torch.cuda.synchronize()
     ev0.record(stream)
-    for _ in range(args.steps):
-        step()
+    steps(args.steps)
     ev1.record(stream)
     dist.barrier(); torch.cuda.synchronize()
     ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev, dtype=torch.float64)      # the reported K steps
@@ -819,8 +920,7 @@ def run_ours_multi(args, w, world, rank, local):
     dist.all_reduce(k12_all)
     n_ext = torch.tensor([max(0, int(0.7 / max(ms_step * 1e-3, 1e-4)) - 2 * args.steps)], device=dev, dtype=torch.int64)
     dist.broadcast(n_ext, 0)                                       # same number of extra steps on every rank
-    for _ in range(int(n_ext.item())):
-        step()
+    steps(int(n_ext.item())) if int(n_ext.item()) else None
     dist.barrier(); torch.cuda.synchronize()
     clk = clocks.summary(t0, time.time()) if rank == 0 else None
     if rank == 0:
@@ -870,7 +970,8 @@ def run_ours_multi(args, w, world, rank, local):
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         if int(flag.item()) == 1:
             if w["alpha"] <= 255 and not args.no_narrow:
-                ctx.set_alpha(w["alpha"])                 # lcp crosses as the bit lcp < alpha
+                for c in ctxs:
+                    c.set_alpha(w["alpha"])               # lcp crosses as the bit lcp < alpha
             try:
                 out_d = tuple(np.array(x, copy=True) for x in step())
                 out_h = tuple(np.array(x, copy=True) for x in step(src=host_shards))
@@ -881,14 +982,14 @@ def run_ours_multi(args, w, world, rank, local):
                 dist.barrier(); torch.cuda.synchronize()
                 ev0.record(stream)
                 tw0 = time.perf_counter()
-                for _ in range(e2e_steps):
-                    step(src=host_shards)
+                steps(e2e_steps, src=host_shards)
                 ev1.record(stream)
                 torch.cuda.synchronize()
                 tw1 = time.perf_counter()
                 dist.barrier()
             finally:
-                ctx.set_alpha(0)
+                for c in ctxs:
+                    c.set_alpha(0)
             e_ms = torch.tensor([max(ev0.elapsed_time(ev1), (tw1 - tw0) * 1e3)], device=dev, dtype=torch.float64)
             dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
             e_ms = float(e_ms.item()) / e2e_steps
@@ -927,7 +1028,8 @@ def run_ours_multi(args, w, world, rank, local):
                "update records, a routing kernel sorts them by owner and stores each run into the owner's inbox over NVLink / "
                "NVSwitch peer memory (CUDA IPC) followed by its counts and a flag, the owner polls the flags on the device and "
                "adds the records; no collective per strand, routing / applying / clusterChoose of strand s run on a side stream "
-               "beside the scoring of strand s + 1; one all-gather of the scalars per job" if route["name"] == "xchg" else
+               "beside the scoring of strand s + 1; one all-gather of the scalars per job; %d job(s) in flight (a second context, so that "
+               "the scoring of job k + 1 is queued before the host waits for job k)" % route.get("jobs_in_flight", 1) if route["name"] == "xchg" else
                f"position-sharded x{world}, halo {HALO}, partial matrices + triples all-to-all by read owner ({route['name']})")
         remote = upd * (world - 1) // world
         line = {
@@ -963,8 +1065,12 @@ def run_ours_multi(args, w, world, rank, local):
         }
         print(json.dumps(line), flush=True)
     dist.barrier()
+    if job2 is not None and not job2.closed:
+        job2.close()
     if hasattr(job, "close"):
         job.close()
+    if ctx2 is not None:
+        ctx2.close()
     ctx.close()
     dist.destroy_process_group()
 

@@ -73,15 +73,32 @@ void pack3_scalar(const uint32_t *src, uint8_t *dst, uint64_t n)
 __attribute__((target("avx2")))
 void pack3_avx2(const uint32_t *src, uint8_t *dst, uint64_t n)
 {
-    const __m256i sh = _mm256_setr_epi8(0, 1, 2, 4, 5, 6, 8, 9, 10, 12, 13, 14, -1, -1, -1, -1,
-                                        0, 1, 2, 4, 5, 6, 8, 9, 10, 12, 13, 14, -1, -1, -1, -1);
     uint64_t i = 0;
-    // a round stores 2 x 16 bytes for 24: the 4 bytes of slack fall on positions this call writes afterwards, so
-    // the last 8 .. 15 positions are left to the scalar loop and nothing is written beyond 3 n
-    for (; i + 16 <= n; i += 8) {
-        const __m256i v = _mm256_shuffle_epi8(_mm256_loadu_si256(reinterpret_cast<const __m256i *>(src + i)), sh);
-        _mm_storeu_si128(reinterpret_cast<__m128i *>(dst + 3 * i), _mm256_castsi256_si128(v));
-        _mm_storeu_si128(reinterpret_cast<__m128i *>(dst + 3 * i + 12), _mm256_extracti128_si256(v, 1));
+    if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+        // 16 positions -> 48 bytes = three aligned 16-byte non-temporal stores: the stage buffer is written once and
+        // read by the DMA engine, so the lines need not be fetched into the cache first
+        const __m128i sh = _mm_setr_epi8(0, 1, 2, 4, 5, 6, 8, 9, 10, 12, 13, 14, -1, -1, -1, -1);
+        for (; i + 16 <= n; i += 16) {
+            const __m128i a = _mm_shuffle_epi8(_mm_loadu_si128(reinterpret_cast<const __m128i *>(src + i)), sh);
+            const __m128i b = _mm_shuffle_epi8(_mm_loadu_si128(reinterpret_cast<const __m128i *>(src + i + 4)), sh);
+            const __m128i c = _mm_shuffle_epi8(_mm_loadu_si128(reinterpret_cast<const __m128i *>(src + i + 8)), sh);
+            const __m128i d = _mm_shuffle_epi8(_mm_loadu_si128(reinterpret_cast<const __m128i *>(src + i + 12)), sh);
+            __m128i *o = reinterpret_cast<__m128i *>(dst + 3 * i);
+            _mm_stream_si128(o + 0, _mm_or_si128(a, _mm_slli_si128(b, 12)));                       // a[0..12) b[0..4)
+            _mm_stream_si128(o + 1, _mm_or_si128(_mm_srli_si128(b, 4), _mm_slli_si128(c, 8)));     // b[4..12) c[0..8)
+            _mm_stream_si128(o + 2, _mm_or_si128(_mm_srli_si128(c, 8), _mm_slli_si128(d, 4)));     // c[8..12) d[0..12)
+        }
+        _mm_sfence();           // non-temporal stores are ordered before the release store that publishes the slice
+    } else {
+        const __m256i sh = _mm256_setr_epi8(0, 1, 2, 4, 5, 6, 8, 9, 10, 12, 13, 14, -1, -1, -1, -1,
+                                            0, 1, 2, 4, 5, 6, 8, 9, 10, 12, 13, 14, -1, -1, -1, -1);
+        // a round stores 2 x 16 bytes for 24: the 4 bytes of slack fall on positions this call writes afterwards, so
+        // the last 8 .. 15 positions are left to the scalar loop and nothing is written beyond 3 n
+        for (; i + 16 <= n; i += 8) {
+            const __m256i v = _mm256_shuffle_epi8(_mm256_loadu_si256(reinterpret_cast<const __m256i *>(src + i)), sh);
+            _mm_storeu_si128(reinterpret_cast<__m128i *>(dst + 3 * i), _mm256_castsi256_si128(v));
+            _mm_storeu_si128(reinterpret_cast<__m128i *>(dst + 3 * i + 12), _mm256_extracti128_si256(v, 1));
+        }
     }
     pack3_scalar(src + i, dst + 3 * i, n - i);
 }

@@ -123,10 +123,13 @@ def test_pack_da3_plain(n):
     da = np.random.default_rng(n).integers(0, 1 << 24, n, dtype=np.uint32)
     if n:
         da[0], da[-1] = 0xFFFFFF, 0xABCDEF
-    out = np.full(3 * n + 8, 0xAB, dtype=np.uint8)
-    assert lib.lime_host_pack_da3(_ptr(da), _ptr(out), n) == 0
-    assert np.array_equal(out[:3 * n], _da3(da))
-    assert (out[3 * n:] == 0xAB).all()           # nothing written past the end (the vector loop stores 16 for 12)
+    for shift in (0, 1, 4):                      # 16-byte aligned output (non-temporal stores) and not
+        buf = np.full(3 * n + 64, 0xAB, dtype=np.uint8)
+        off = (-buf.ctypes.data) % 16 + shift
+        out = buf[off:]
+        assert lib.lime_host_pack_da3(_ptr(da), C.c_void_p(buf.ctypes.data + off), n) == 0
+        assert np.array_equal(out[:3 * n], _da3(da))
+        assert (out[3 * n:] == 0xAB).all() and (buf[:off] == 0xAB).all()    # nothing written outside (the vector loop stores 16 for 12)
 
 
 @pytest.mark.parametrize("delay_us", [0, 50])
