@@ -617,8 +617,8 @@ def run_ours(args, w):
             try:
                 modes["lcp_bits"] = time_host(
                     "lime_set_alpha(alpha) + lime_load(LIME_MEM_HOST) per strand from pinned host arrays: lcp packed to one bit "
-                    "per position (lcp < alpha) by %d host threads inside the timed region; assignments copied back; PCIe-bound"
-                    % workers + ("; da as 3 bytes per position" if da3 else ""),
+                    "per position (lcp < alpha) by %d host threads inside the timed region; assignments copied back"
+                    % workers + ("; da as 3 bytes per position; bound by the packing threads (the bus runs below its rate)" if da3 else "; PCIe-bound"),
                     host_bytes - (5 if da3 else 4) * symbols + sum((sd["n"] + 7) // 8 for sd in strands_dev) + 4 * w["n_refs"])
             finally:
                 ctx.set_alpha(0)
@@ -784,9 +784,10 @@ def run_ours_multi(args, w, world, rank, local):
 
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
-    if world >= 4 and "LIME_PACK_DA" not in os.environ:
-        # host loads of 4 or more ranks are bound by the host's memory system, not by PCIe (8 ranks: 13.6 GB/s per GPU):
-        # repacking da to 3 bytes costs host traffic and saves none where it counts (measured: 21.2 -> 11.7 G symbols/s)
+    if "LIME_PACK_DA" not in os.environ:
+        # host loads of several ranks are bound by the host's cores and memory system, not by PCIe (2 ranks: 21.7 GB/s per
+        # GPU, 8 ranks: 13.6): repacking da to 3 bytes costs host work and saves none where it counts (measured, G symbols/s:
+        # N=2 13.5 -> 10.5, N=8 21.2 -> 11.7), so only the one-GPU e2e leg uses it
         os.environ["LIME_PACK_DA"] = "0"
     ctx = LimeContext(local)
     stream = torch.cuda.current_stream()

@@ -333,6 +333,51 @@ def test_deferred_strands_equal_the_synchronous_calls(ctx, oracle):
         assert np.asarray(g).tobytes() == e2.tobytes()
 
 
+def test_two_jobs_in_flight_on_two_contexts(oracle):
+    """bench.py's schedule: two contexts on two streams, the strands of job k + 1 are queued (lime_load of device
+    arrays + lime_strand_run) before lime_classify of job k is called.  Every job must equal the oracle's."""
+    import torch
+    from lime_b200.api import LimeContext, MEM_DEVICE
+    n_reads, n_refs, alpha, read_len = 9_000, 40, 16, 100
+    cases = [C.synth_case(f"inflight_{s}", 700_000 + 31 * s, n_reads, n_refs, seed=520 + s, p_long=2e-5, max_seg=30000) for s in range(4)]
+    v = (np.arange(n_refs, dtype=np.uint32) // 2) + 9
+    jobs = [(cases[0], cases[1]), (cases[2], cases[3]), (cases[1], cases[2])]        # three different jobs
+    exp = [_expected_job(oracle, list(j), n_reads, n_refs, read_len, alpha, 0.25, 1, v, None, 1, False)[0] for j in jobs]
+    dev = {id(c): tuple(torch.from_numpy(c[k].view(np.int32) if c[k].dtype == np.uint32 else c[k]).to("cuda:0") for k in ("lcp", "da", "ebwt"))
+           for c in cases}
+    ctxs, streams = [LimeContext(0), LimeContext(0)], [torch.cuda.Stream(), torch.cuda.Stream()]
+    try:
+        for c, st in zip(ctxs, streams):
+            c.set_stream(st.cuda_stream)
+        torch.cuda.synchronize()
+
+        def launch(c, job):
+            for s, case in enumerate(job):
+                l, d, e = dev[id(case)]
+                c.load(l.data_ptr(), d.data_ptr(), e.data_ptr(), n_reads, n_refs, mem=MEM_DEVICE, n_total=case["lcp"].shape[0])
+                c.strand_run(s, alpha, 1, read_len + 1 - alpha, 0.25)
+
+        for rep in range(3):
+            order = [jobs[(rep + k) % 3] for k in range(6)]
+            want = [exp[(rep + k) % 3] for k in range(6)]
+            prev = None
+            for k, job in enumerate(order):
+                c = ctxs[k % 2]
+                launch(c, job)
+                if prev is not None:
+                    got = prev[0].classify(2, n_refs, v, None, 1, False)
+                    for g, e in zip(got, prev[1]):
+                        assert np.asarray(g).tobytes() == e.tobytes(), (rep, k)
+                prev = (c, want[k])
+            got = prev[0].classify(2, n_refs, v, None, 1, False)
+            for g, e in zip(got, prev[1]):
+                assert np.asarray(g).tobytes() == e.tobytes()
+    finally:
+        torch.cuda.synchronize()
+        for c in ctxs:
+            c.close()
+
+
 def test_sharded_loads_union_equals_whole(ctx, oracle):
     """Position shards with a halo (lime_load n_own / n_halo / pos_base / is_last): the clusters of
     the shards are a partition of the whole array's clusters and the matrices add up mod 256."""
