@@ -851,17 +851,9 @@ def run_ours_multi(args, w, world, rank, local):
             for _ in range(k_steps):
                 out = step(src)
             return out
-        pair, prev = (job, job2), None
         try:
-            for k in range(k_steps):
-                j = pair[k % 2]
-                j.begin()
-                for s_, sh in enumerate(src or shards):
-                    j.run_strand(s_, sh, w["alpha"], w["beta"], w["ebwt"], w["read_len"])     # queues, never waits
-                if prev is not None:
-                    out = prev.finish(v, m, w["tax_rank"], w["higher"], gather=False)
-                prev = j
-            return prev.finish(v, m, w["tax_rank"], w["higher"], gather=False)
+            return multi.run_jobs_in_flight((job, job2), k_steps, src or shards, w["alpha"], w["beta"], w["ebwt"], w["read_len"],
+                                            v, m, w["tax_rank"], w["higher"], gather=False)
         except multi.CarryDetected as e:
             # not expected on this workload: back to one job at a time (step() then takes the exact route)
             torch.cuda.synchronize()

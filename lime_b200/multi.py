@@ -412,6 +412,38 @@ def run_sharded(dist, torch, backend, rank, world, n_reads, n_refs, shards, alph
     return job.finish(v, m, tax_rank, higher, gather=gather), list(job.stats), "exchange"
 
 
+def run_jobs_in_flight(jobs, k_steps, shards, alpha, beta, ebwt_mode, read_len, v, m=None, tax_rank=1, higher=False, gather=False):
+    """k_steps classification jobs over the same shards with len(jobs) of them in flight: `jobs` are XchgJobs on
+    different backends (contexts) of this rank; the strands of job k + 1 are queued -- run_strand never waits on a
+    CUDA backend -- before finish() of job k is called, so job k's routing / applying / clusterChoose tail, its
+    Classify, result copy and the ranks' agreement run beside the scoring of job k + 1.  Every rank must call this with
+    the same k_steps (finish() holds a collective).  Returns the assignments of the last job; CarryDetected from a
+    finish() propagates after the jobs already queued have been drained (their results are dropped)."""
+    assert jobs and k_steps >= 1
+    pending, out = [], None
+    try:
+        for k in range(k_steps):
+            j = jobs[k % len(jobs)]
+            if len(pending) == len(jobs):                   # this context's previous job first
+                out = pending.pop(0).finish(v, m, tax_rank, higher, gather=gather)
+            j.begin()
+            for s, sh in enumerate(shards):
+                j.run_strand(s, sh, alpha, beta, ebwt_mode, read_len)
+            pending.append(j)
+            if len(pending) > 1 or len(jobs) == 1:
+                out = pending.pop(0).finish(v, m, tax_rank, higher, gather=gather)
+        while pending:
+            out = pending.pop(0).finish(v, m, tax_rank, higher, gather=gather)
+        return out
+    except CarryDetected:
+        while pending:                                      # every rank drains the same jobs: the collectives stay matched
+            try:
+                pending.pop(0).finish(v, m, tax_rank, higher, gather=gather)
+            except CarryDetected:
+                pass
+        raise
+
+
 class _NoTimer:
     def __enter__(self):
         return self

@@ -193,6 +193,16 @@ def _worker(rank, world, port, strands, n_reads, n_refs, read_len, alpha, beta, 
             job.run_strand(s, sh, alpha, beta, 1, read_len)
         typ, tax, sim = job.finish(v, m, 1, m is not None)
         assert all(a.tobytes() == np.asarray(b).tobytes() for a, b in zip(first, (typ, tax, sim)))
+        # bench.py's schedule: a second context (backend) of this rank, job k + 1 queued before job k is finished
+        be2 = OracleBackend(Oracle(), torch)
+        be2.shm_dir = os.path.join(peer_dir, "second")
+        os.makedirs(be2.shm_dir, exist_ok=True)
+        job2 = multi.XchgJob(dist, torch, be2, rank, world, n_reads, n_refs, len(strands), 1 << 16, 1 << 15)
+        for k_steps in (1, 2, 3):
+            typ, tax, sim = multi.run_jobs_in_flight((job, job2), k_steps, job_shards, alpha, beta, 1, read_len, v, m, 1,
+                                                     m is not None, gather=True)
+            assert all(a.tobytes() == np.asarray(b).tobytes() for a, b in zip(first, (typ, tax, sim))), k_steps
+        job2.close()
         job.close()
     q.put((rank, typ, tax, sim, job.stats))
     dist.barrier()
