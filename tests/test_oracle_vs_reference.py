@@ -97,6 +97,51 @@ def test_step3_matches_reference(tmp_path, oracle, reference, n_files, higher, t
     assert "C" in kinds and "U" in kinds and (("H" in kinds) if higher else ("A" in kinds))
 
 
+@pytest.mark.parametrize("shape", ["cfg3_930genomes_ebwt0", "cfg4_1000genomes_higher1_trlcp32", "cfg5_alpha12", "cfg5_alpha20", "cfg5_alpha24"])
+def test_baseline_config_shapes_match_reference(tmp_path, oracle, reference, shape):
+    """Whole jobs in the shapes of BASELINE configs 3, 4 and 5 (reduced sizes), the three reference executables chained
+    through their files against the oracle: .clrs, .res.bin / .res.pos of every strand and the CSV, byte for byte."""
+    from lime_b200.pipeline import synthetic_lineage
+    if shape.startswith("cfg3"):
+        n, n_reads, n_refs, read_len, alpha, ebwt, higher, n_str, kw = 260_000, 1500, 930, 100, 16, False, False, 4, {}
+    elif shape.startswith("cfg4"):
+        n, n_reads, n_refs, read_len, alpha, ebwt, higher, n_str, kw = 260_000, 1500, 1000, 150, 16, True, True, 4, {"trlcp": 32}
+    else:
+        n, n_reads, n_refs, read_len, alpha, ebwt, higher, n_str, kw = 200_000, 3000, 50, 100, int(shape[10:]), True, False, 2, {}
+    rows, v, m = synthetic_lineage(n_refs)
+    lin = os.path.join(tmp_path, "lineage.csv")
+    with open(lin, "w", newline="") as f:
+        f.write(C.lineage_text(rows))
+    vo, mo, found = oracle.fix_rank(lin, 1, n_refs, higher)
+    assert found == n_refs and np.array_equal(vo, v)
+    stems, bins, poss = [], [], []
+    for s_ in range(n_str):
+        case = C.synth_case(f"{shape}_{s_}", n + 17 * s_, n_reads, n_refs, read_len=read_len, seed=800 + s_, p_long=2e-5, max_seg=20000, **kw)
+        d = tmp_path / f"strand{s_}"
+        d.mkdir()
+        fasta = _write_case(str(d), case)
+        cl_ref, aux = reference.cluster_lcp(fasta, n_reads, n_refs, alpha, 2)
+        cl, max_len = oracle.cluster_detect(case["lcp"], case["da"], n_reads, alpha)
+        assert aux["nClusters"] == cl.shape[0] and aux["maxLen"] == max_len and np.array_equal(cl_ref, cl)
+        assert max_len <= 65536
+        bin_ref, pos_ref, r = reference.cluster_bwt_da(fasta, read_len, 0.25, 2, ebwt=ebwt)
+        assert bin_ref is not None, r.stderr
+        sim = oracle.similarity(cl, case["da"], case["ebwt"] if ebwt else None, n_reads, n_refs)
+        b, p_ = oracle.choose(sim, (read_len + 1 - alpha) & 0xFFFFFFFF, np.float32(0.25))
+        assert bin_ref.tobytes() == b.tobytes() and pos_ref.tobytes() == p_.tobytes()
+        stem = os.path.join(tmp_path, f"s{s_}.res")
+        b.tofile(stem + ".bin"); p_.tofile(stem + ".pos")
+        stems.append(stem); bins.append(b); poss.append(p_)
+    out_ref = os.path.join(tmp_path, "ref.csv")
+    r = reference.classify(stems, n_reads, n_refs, out_ref, lin, 1, threads=2, higher=higher)
+    assert r.returncode == 0, r.stderr
+    typ, tax, simc = oracle.classify(bins, poss, n_refs, vo, mo, 1, higher)
+    out_o = os.path.join(tmp_path, "oracle.csv")
+    oracle.write_csv(out_o, typ, tax, simc)
+    assert open(out_ref, "rb").read() == open(out_o, "rb").read()
+    assert "C" in set(chr(t) for t in typ)
+
+
 def test_lineage_without_final_newline_is_rejected_like_reference(tmp_path, oracle, reference):
     lin = os.path.join(tmp_path, "lineage.csv")
     with open(lin, "w", newline="") as f:
