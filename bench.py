@@ -475,7 +475,9 @@ def run_ours(args, w):
     # LIME_BENCH_INFLIGHT=1: one job at a time.
     inflight = 1
     ctx2 = None
-    if not args.unfused and os.environ.get("LIME_BENCH_INFLIGHT", "2") != "1":
+    free_now, total_mem = torch.cuda.mem_get_info()
+    if (not args.unfused and os.environ.get("LIME_BENCH_INFLIGHT", "2") != "1"
+            and free_now > 1.25 * (w["n_reads"] * ((w["n_refs"] + 15) // 16 * 16) + 20 * w["n_reads"]) + (4 << 30)):   # its matrix and slots
         ctx2 = LimeContext(local)
         stream2 = torch.cuda.Stream()
         ctx2.set_stream(stream2.cuda_stream)
@@ -825,18 +827,10 @@ def run_ours_multi(args, w, world, rank, local):
             return multi.ShardedJob(dist, torch, be, rank, world, n_reads, w["n_refs"])
         flat_cap, inbox_cap = multi.xchg_capacities(S_local + HALO, world, density)
         return multi.XchgJob(dist, torch, be, rank, world, n_reads, w["n_refs"], w["n_strands"], flat_cap, inbox_cap)
+    free0 = torch.cuda.mem_get_info()[0]
     job = make_job(density)
     route = {"name": "xchg" if mode != "exchange" else "exchange"}
-    # Two jobs in flight (record exchange only): a second context with its own slabs, lists, inboxes and side stream, so
-    # that the scoring of job k + 1 is queued before the host waits for job k -- the routing / applying / clusterChoose of
-    # job k's last strand then run beside it.  LIME_BENCH_INFLIGHT=1: one job at a time.
     ctx2 = job2 = None
-    if mode != "exchange" and os.environ.get("LIME_BENCH_INFLIGHT", "2") != "1":
-        ctx2 = LimeContext(local)
-        ctx2.set_stream(stream.cuda_stream)
-        be2 = multi.CudaBackend(ctx2, torch, dev)
-        flat_cap, inbox_cap = multi.xchg_capacities(S_local + HALO, world, density)
-        job2 = multi.XchgJob(dist, torch, be2, rank, world, n_reads, w["n_refs"], w["n_strands"], flat_cap, inbox_cap)
 
     def step(src=None):
         nonlocal job
@@ -881,6 +875,22 @@ def run_ours_multi(args, w, world, rank, local):
 
     for _ in range(max(args.warmup, 3)):
         out = step()
+    # Two jobs in flight (record exchange only): a second context with its own slabs, lists, inboxes and side stream, so
+    # that the scoring of job k + 1 is queued before the host waits for job k -- the routing / applying / clusterChoose of
+    # job k's last strand then run beside it.  Only when every rank has the memory for it (what the first job took, and a
+    # quarter more); LIME_BENCH_INFLIGHT=1: one job at a time.
+    if mode != "exchange" and not getattr(job, "closed", True) and os.environ.get("LIME_BENCH_INFLIGHT", "2") != "1":
+        torch.cuda.synchronize()
+        free1 = torch.cuda.mem_get_info()[0]
+        fits = torch.tensor([int(free1 > 1.25 * max(free0 - free1, 0) + (2 << 30))], device=dev, dtype=torch.int64)
+        dist.all_reduce(fits, op=dist.ReduceOp.MIN)
+        if int(fits.item()) == 1:
+            ctx2 = LimeContext(local)
+            ctx2.set_stream(stream.cuda_stream)
+            be2 = multi.CudaBackend(ctx2, torch, dev)
+            job2 = multi.XchgJob(dist, torch, be2, rank, world, n_reads, w["n_refs"], w["n_strands"], job.flat_cap, job.inbox_cap)
+        else:
+            route["one_job_in_flight_because"] = "no memory for a second context on some rank"
     if job2 is not None:
         out_a = tuple(np.array(x, copy=True) for x in out)
         out_b = steps(2)                                     # the second job of the pair ran on the second context
